@@ -1,0 +1,280 @@
+/*
+ * svtme_b200.h — C ABI of the B200-native open-loop motion-estimation path.
+ *
+ * Drop-in boundary for ONE stage of SVT-AV1 (reference: Patman86/SVT-AV1-Mod-by-Patman):
+ * the pre-ME pyramid (1/4, 1/16 pictures), pre-HME, HME level 0/1/2 and the full-pel integer
+ * search that fills the per-64x64 best-MV/SAD tables of the 85 square PUs.
+ *
+ * Two groups of entry points:
+ *   (1) production ABI  svtme_*         — picture granular; replaces the body of the PAME branch of
+ *       svt_aom_motion_estimation_kernel (Source/Lib/Codec/me_process.c:126-313) and
+ *       svt_aom_downsample_filtering_input_picture (Source/Lib/Codec/pic_analysis_process.c:1922).
+ *   (2) kernel-test ABI *_b200          — the RTCD signatures of Source/Lib/Codec/aom_dsp_rtcd.h
+ *       (lines 776, 838-854) as synchronous host wrappers (H2D, launch, D2H) so that SadTest /
+ *       PictureOperatorTest shaped harnesses can be pointed at the CUDA kernels unchanged.
+ *
+ * Plain C: pointers + sizes only, no C++/torch types. All functions return 0 on success and a
+ * negative SVTME_ERR_* otherwise (kernel-test wrappers that mirror `void` RTCD functions abort()
+ * on a CUDA failure — there is NO CPU fallback anywhere in this library).
+ */
+#ifndef SVTME_B200_H
+#define SVTME_B200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SVTME_OK 0
+#define SVTME_ERR_INVALID -1   /* bad argument / unsupported parameter combination */
+#define SVTME_ERR_NOMEM -2     /* host or device allocation failed (EB_ErrorInsufficientResources) */
+#define SVTME_ERR_CUDA -3      /* CUDA runtime error; svtme_last_error() has the text */
+#define SVTME_ERR_NOTFOUND -4  /* picture number not resident */
+
+#define SVTME_MAX_LISTS 2      /* MAX_NUM_OF_REF_PIC_LIST  definitions.h:2349 */
+#define SVTME_MAX_REFS 4       /* MAX_REF_IDX / REF_LIST_MAX_DEPTH definitions.h:2364 */
+#define SVTME_PU_COUNT 85      /* SQUARE_PU_COUNT: 1 + 4 + 16 + 64 */
+#define SVTME_MAX_SAD_VALUE (128u * 128u * 255u) /* MAX_SAD_VALUE motion_estimation.h:85 */
+
+typedef struct SvtMeSearchArea {
+    uint16_t width, height;    /* SearchArea me_context.h:319-322 */
+} SvtMeSearchArea;
+
+typedef struct SvtMeSearchAreaMinMax {
+    SvtMeSearchArea sa_min, sa_max; /* SearchAreaMinMax me_context.h:323-326 */
+} SvtMeSearchAreaMinMax;
+
+/*
+ * Scalar ME parameters of one picture. Field names and meaning follow MeContext
+ * (Source/Lib/Codec/me_context.h:366-509) as filled by svt_aom_sig_deriv_me
+ * (enc_mode_config.c:684-823) plus the per-picture fields set in me_process.c:219-227 and the
+ * PictureParentControlSet / SequenceControlSet scalars motion_estimation.c reads.
+ * svtme_derive_params() fills it from (preset, resolution, qp, ...) exactly like the reference.
+ */
+typedef struct SvtMeParams {
+    /* search areas */
+    SvtMeSearchAreaMinMax me_sa;          /* full-pel min/max search area */
+    SvtMeSearchAreaMinMax hme_l0_sa;      /* total HME level-0 area (all quadrants) */
+    SvtMeSearchArea hme_l1_sa, hme_l2_sa; /* refinement windows */
+    uint16_t num_hme_sa_w, num_hme_sa_h;  /* always 2x2 (enc_mode_config.c:144-145) */
+    /* flags */
+    uint8_t enable_hme_flag, enable_hme_level0_flag, enable_hme_level1_flag, enable_hme_level2_flag;
+    uint8_t hme_search_method, me_search_method; /* 0 SUB_SAD_SEARCH, 1 FULL_SAD_SEARCH (definitions.h:2079-2080) */
+    uint8_t reduce_hme_l0_sr_th_min, reduce_hme_l0_sr_th_max;
+    /* PreHmeCtrls me_context.h:334-339 */
+    uint8_t prehme_enable, prehme_skip_search_line, prehme_l1_early_exit, _pad0;
+    SvtMeSearchAreaMinMax prehme_sa_cfg[2];
+    /* MeHmeRefPruneCtrls me_context.h:280-290 */
+    uint8_t enable_me_hme_ref_pruning, _pad1;
+    uint16_t prune_ref_if_hme_sad_dev_bigger_than_th;
+    uint16_t prune_ref_if_me_sad_dev_bigger_than_th;
+    uint16_t zz_sad_pct;
+    uint32_t zz_sad_th;
+    uint32_t phme_sad_th;
+    uint16_t phme_sad_pct;
+    /* MeSrCtrls me_context.h:292-305 */
+    uint8_t enable_me_sr_adjustment, distance_based_hme_resizing;
+    uint16_t reduce_me_sr_based_on_mv_length_th;
+    uint16_t stationary_hme_sad_abs_th;
+    uint16_t stationary_me_sr_divisor;
+    uint16_t reduce_me_sr_based_on_hme_sad_abs_th;
+    uint16_t me_sr_divisor_for_low_hme_sad;
+    /* Me8x8VarCtrls me_context.h:310-318 */
+    uint8_t me_8x8_var_enabled, _pad2;
+    uint32_t me_sr_div4_th, me_sr_div2_th, me_sr_mult2_th;
+    /* MvBasedSearchAdj me_context.h:355-363 */
+    uint8_t mv_sa_adj_enabled, mv_sa_adj_nearest_ref_only;
+    uint16_t mv_sa_adj_mv_size_th, mv_sa_adj_sa_multiplier;
+    /* misc MeContext scalars */
+    int32_t prune_me_candidates_th;
+    uint8_t use_best_unipred_cand_only, _pad3[3];
+    uint32_t me_early_exit_th, me_safe_limit_zz_th, prev_me_stage_based_exit_th;
+    /* per-picture, me_process.c:219-227 */
+    uint8_t num_of_list_to_search;
+    uint8_t num_of_ref_pic_to_search[2];
+    uint8_t temporal_layer_index;
+    uint8_t is_ref;
+    /* pcs / scs scalars read by motion_estimation.c */
+    uint8_t hierarchical_levels;        /* pcs->hierarchical_levels        :2496 */
+    uint8_t similar_brightness_refs;    /* pcs->similar_brightness_refs    :2497 */
+    uint8_t enable_me_8x8;              /* pcs->enable_me_8x8              :2785 */
+    uint8_t enable_me_16x16;            /* pcs->enable_me_16x16 */
+    uint8_t max_number_of_pus_per_sb;   /* pcs->max_number_of_pus_per_sb (85) */
+    uint8_t only_l_bwd;                 /* scs->mrp_ctrls.only_l_bwd       :2852 */
+    uint8_t gm_enabled;                 /* pcs->gm_ctrls.enabled           :3219 */
+    uint8_t gm_use_distance_based_active_th;
+    uint8_t input_resolution_le_480p;   /* scs->input_resolution <= INPUT_SIZE_480p_RANGE */
+    uint8_t max_cand, max_refs, max_l0; /* pcs->pa_me_data->max_* (pd_process.c:3510-3512) */
+    uint8_t _pad4[3];
+    uint64_t picture_number;                                 /* pcs->picture_number */
+    uint64_t ref_picture_number[SVTME_MAX_LISTS][SVTME_MAX_REFS]; /* me_ds_ref_array[][].picture_number */
+} SvtMeParams;
+
+/* Encoder-level inputs of svt_aom_sig_deriv_me + the flag derivations around it. */
+typedef struct SvtMeDeriveInput {
+    int32_t enc_mode;            /* preset: -1 (MR) .. 13 */
+    uint32_t width, height;      /* luma size -> EbInputResolution (sequence_control_set.c:113-131) */
+    uint32_t qp;                 /* scs->static_config.qp (default 35) */
+    uint8_t rtc_tune;            /* pred_structure == SVT_AV1_PRED_LOW_DELAY_B */
+    uint8_t sc_class1;           /* screen-content class 1 */
+    uint8_t hierarchical_levels; /* pcs->hierarchical_levels */
+    uint8_t temporal_layer_index;
+    uint8_t is_ref;
+    uint8_t slice_type_b;        /* 1: B_SLICE (two lists), 0: P_SLICE */
+    uint8_t ref_list0_count_try, ref_list1_count_try; /* pd_process.c:3666-3677 */
+    uint32_t frame_rate_q16;     /* scs->frame_rate (Q16) — low-frame-rate scaling :346-350 */
+    uint8_t safe_limit_nref;     /* scs->mrp_ctrls.safe_limit_nref */
+    uint8_t only_l_bwd;
+    uint8_t use_best_me_unipred_cand_only;
+    uint8_t similar_brightness_refs;
+    uint32_t safe_limit_zz_th;
+    uint8_t ref_count_used_list0, ref_count_used_list1; /* MeSbResults allocation pcs.c:90-95 */
+    uint8_t gm_level_enabled, gm_use_distance_based_active_th;
+} SvtMeDeriveInput;
+
+/* Host-side mirror of svt_aom_sig_deriv_me (enc_mode_config.c:684-823), set_hme_search_params
+ * (:141-213), set_me_search_params (:218-353), the HME level flags (:1798-1809) and
+ * svt_aom_get_enable_me_8x8 (:76-96). Pure host code. */
+int svtme_derive_params(const SvtMeDeriveInput *in, SvtMeParams *out);
+
+/*
+ * Per-picture outputs, host memory, caller-owned. n_b64 = ceil(aligned_w/64)*ceil(aligned_h/64),
+ * n_pu = exported PU count (85 / 21 / 5, see svtme_exported_pu_count()). Layouts are those of
+ * MeSbResults (me_sb_results.h:29-50; allocation pcs.c:97-119), one record per b64 back to back,
+ * and of the PictureParentControlSet per-b64 arrays (motion_estimation.c:3065-3076,3216-3217).
+ * Any pointer may be NULL (that output is skipped).
+ */
+typedef struct SvtMeOut {
+    uint8_t *total_me_candidate_index; /* [n_b64][n_pu] */
+    uint32_t *me_mv_array;             /* [n_b64][n_pu*max_refs]  MvCandidate.as_int */
+    uint8_t *me_candidate_array;       /* [n_b64][n_pu*max_cand]  MeCandidate bitfield byte */
+    uint32_t *me_64x64_distortion;     /* [n_b64] */
+    uint32_t *me_32x32_distortion;
+    uint32_t *me_16x16_distortion;
+    uint32_t *me_8x8_distortion;
+    uint32_t *me_8x8_cost_variance;
+    uint32_t *rc_me_distortion;
+    uint8_t *stationary_block_present_sb;
+    uint8_t *rc_me_allow_gm;
+    /* optional deep state for parity checks (MeContext.p_sb_best_sad/mv, search_results) */
+    uint32_t *p_sb_best_sad;           /* [n_b64][2][4][85], entries of refs not searched = 0 */
+    uint32_t *p_sb_best_mv;            /* [n_b64][2][4][85] */
+    int16_t *hme_sc;                   /* [n_b64][2][4][2]  (x,y) search centres */
+    uint64_t *hme_sad;                 /* [n_b64][2][4]     search_results[].hme_sad at exit */
+    uint8_t *do_ref;                   /* [n_b64][2][4] */
+} SvtMeOut;
+
+typedef struct SvtMeHandle SvtMeHandle;
+
+/* One handle per GPU (one process per GPU in multi-GPU runs). width/height: luma size of the
+ * source pictures; capacity: number of pyramids kept resident (pa-ref ring). */
+int svtme_open(int device, uint32_t width, uint32_t height, uint32_t capacity, SvtMeHandle **out);
+void svtme_close(SvtMeHandle *h);
+const char *svtme_last_error(void);
+
+uint32_t svtme_b64_count(const SvtMeHandle *h);
+uint32_t svtme_exported_pu_count(const SvtMeParams *p);
+
+/* Upload one 8-bit luma plane (host memory) and build pad + 1/4 + 1/16 on the device.
+ * Replaces svt_aom_pad_input_pictures (pic_analysis_process.c:1981) for luma and
+ * svt_aom_downsample_filtering_input_picture (:1922). Asynchronous on the handle's stream. */
+int svtme_put_picture(SvtMeHandle *h, uint64_t pic_num, const uint8_t *luma, uint32_t stride);
+/* Same, source already in device memory (tightly described by stride). */
+int svtme_put_picture_device(SvtMeHandle *h, uint64_t pic_num, const void *d_luma, uint32_t stride);
+/* Copy the padded planes back (level 0 full, 1 quarter, 2 sixteenth) incl. the reference's pads
+ * (72/32/16): the CPU stages that still read them (picture statistics, TF) need them. */
+int svtme_get_plane(SvtMeHandle *h, uint64_t pic_num, int level, uint8_t *dst, uint32_t dst_stride,
+                    uint32_t pad);
+int svtme_release_picture(SvtMeHandle *h, uint64_t pic_num);
+/* Device pointers of a resident pyramid level (for P2P / NCCL exchange between GPUs). */
+int svtme_plane_device_ptr(SvtMeHandle *h, uint64_t pic_num, int level, void **ptr, size_t *bytes);
+/* Declare a picture resident whose planes were written externally (NCCL recv) */
+int svtme_adopt_picture(SvtMeHandle *h, uint64_t pic_num);
+
+/* Open-loop ME of one picture against refs[list][idx] (picture numbers previously put).
+ * Replaces the b64 loop of me_process.c:174-289 calling svt_aom_motion_estimation_b64
+ * (motion_estimation.c:3146). Synchronous: results are in `out` on return. */
+int svtme_run_picture(SvtMeHandle *h, const SvtMeParams *params, uint64_t cur,
+                      const uint64_t refs[SVTME_MAX_LISTS][SVTME_MAX_REFS], SvtMeOut *out);
+
+/* Batched form: n independent pictures, one launch sequence, one D2H. */
+typedef struct SvtMeJob {
+    SvtMeParams params;
+    uint64_t cur;
+    uint64_t refs[SVTME_MAX_LISTS][SVTME_MAX_REFS];
+    SvtMeOut out;
+} SvtMeJob;
+int svtme_run_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n);
+/* Device-only part of the batched form (no D2H); svtme_fetch_results completes it. */
+int svtme_launch_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n);
+int svtme_fetch_results(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n);
+int svtme_sync(SvtMeHandle *h);
+/* CUDA-event time (ms) of the ME kernel launches of the last svtme_launch_pictures call, and
+ * the number of kernels this library has launched so far. */
+float svtme_last_kernel_ms(SvtMeHandle *h);
+uint64_t svtme_launch_count(void);
+
+/* ---------------- kernel-test ABI: RTCD signatures (aom_dsp_rtcd.h) ---------------- */
+
+/* svt_sad_loop_kernel  aom_dsp_rtcd.h:776 / compute_sad_c.c:58 */
+void svt_sad_loop_kernel_b200(uint8_t *src, uint32_t src_stride, uint8_t *ref, uint32_t ref_stride,
+                              uint32_t block_height, uint32_t block_width, uint64_t *best_sad,
+                              int16_t *x_search_center, int16_t *y_search_center,
+                              uint32_t src_stride_raw, uint8_t skip_search_line,
+                              int16_t search_area_width, int16_t search_area_height);
+/* svt_ext_all_sad_calculation_8x8_16x16  aom_dsp_rtcd.h:850 / motion_estimation.c:337 */
+void svt_ext_all_sad_calculation_8x8_16x16_b200(uint8_t *src, uint32_t src_stride, uint8_t *ref,
+                                                uint32_t ref_stride, uint32_t mv,
+                                                uint32_t *p_best_sad_8x8, uint32_t *p_best_sad_16x16,
+                                                uint32_t *p_best_mv8x8, uint32_t *p_best_mv16x16,
+                                                uint32_t p_eight_sad16x16[16][8],
+                                                uint32_t p_eight_sad8x8[64][8], uint8_t sub_sad);
+/* svt_ext_eight_sad_calculation_32x32_64x64  aom_dsp_rtcd.h:851 / motion_estimation.c:369 */
+void svt_ext_eight_sad_calculation_32x32_64x64_b200(uint32_t p_sad16x16[16][8],
+                                                    uint32_t *p_best_sad_32x32,
+                                                    uint32_t *p_best_sad_64x64,
+                                                    uint32_t *p_best_mv32x32,
+                                                    uint32_t *p_best_mv64x64, uint32_t mv,
+                                                    uint32_t p_sad32x32[4][8]);
+/* svt_ext_sad_calculation_8x8_16x16  aom_dsp_rtcd.h:839 / motion_estimation.c:98 */
+void svt_ext_sad_calculation_8x8_16x16_b200(uint8_t *src, uint32_t src_stride, uint8_t *ref,
+                                            uint32_t ref_stride, uint32_t *p_best_sad_8x8,
+                                            uint32_t *p_best_sad_16x16, uint32_t *p_best_mv8x8,
+                                            uint32_t *p_best_mv16x16, uint32_t mv,
+                                            uint32_t *p_sad16x16, uint32_t *p_sad8x8, uint8_t sub_sad);
+/* svt_ext_sad_calculation_32x32_64x64  aom_dsp_rtcd.h:845 / motion_estimation.c:172 */
+void svt_ext_sad_calculation_32x32_64x64_b200(uint32_t *p_sad16x16, uint32_t *p_best_sad_32x32,
+                                              uint32_t *p_best_sad_64x64, uint32_t *p_best_mv32x32,
+                                              uint32_t *p_best_mv64x64, uint32_t mv,
+                                              uint32_t *p_sad32x32);
+/* svt_initialize_buffer_32bits  aom_dsp_rtcd.h:852 / me_sad_calculation.c:14 */
+void svt_initialize_buffer_32bits_b200(uint32_t *pointer, uint32_t count128, uint32_t count32,
+                                       uint32_t value);
+/* svt_nxm_sad_kernel  aom_dsp_rtcd.h:854 / compute_sad_c.c:209 */
+uint32_t svt_nxm_sad_kernel_b200(const uint8_t *src, uint32_t src_stride, const uint8_t *ref,
+                                 uint32_t ref_stride, uint32_t height, uint32_t width);
+/* downsample_2d  aom_dsp_rtcd.h:838 / pic_analysis_process.c:131 */
+void svt_aom_downsample_2d_b200(uint8_t *input_samples, uint32_t input_stride,
+                                uint32_t input_area_width, uint32_t input_area_height,
+                                uint8_t *decim_samples, uint32_t decim_stride, uint32_t decim_step);
+/* svt_aom_generate_padding  pic_operators.c:338 */
+void svt_aom_generate_padding_b200(uint8_t *src_pic, uint32_t src_stride, uint32_t original_src_width,
+                                   uint32_t original_src_height, uint32_t padding_width,
+                                   uint32_t padding_height);
+/* Whole full-pel search of one 64x64 block (open_loop_me_fullpel_search_sblock,
+ * motion_estimation.c:781): src = 64x64 block, ref points at the top-left search position.
+ * best tables (85 entries, search order) are read-modify-write like p_sb_best_sad/mv. */
+void svt_open_loop_me_fullpel_search_sblock_b200(const uint8_t *src, uint32_t src_stride,
+                                                 const uint8_t *ref, uint32_t ref_stride,
+                                                 int16_t x_search_area_origin,
+                                                 int16_t y_search_area_origin,
+                                                 uint32_t search_area_width,
+                                                 uint32_t search_area_height, uint8_t sub_sad,
+                                                 uint32_t *p_sb_best_sad, uint32_t *p_sb_best_mv);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SVTME_B200_H */

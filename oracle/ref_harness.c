@@ -1,0 +1,395 @@
+/*
+ * ref_harness.c — thin driver around the UNMODIFIED reference sources, compiled where they lie
+ * under /root/reference by oracle/Makefile into oracle/_ref/libsvtref.so (git-ignored).
+ * TEST INFRASTRUCTURE ONLY: used to pin oracle/me_oracle*.c, to generate tests/golden/, and as
+ * the "reference" CPU baseline of bench.py. No reference source is copied into this repo; this
+ * file only includes the reference's headers and calls its functions:
+ *   svt_aom_motion_estimation_b64      Source/Lib/Codec/motion_estimation.c:3146
+ *   svt_aom_sig_deriv_me               Source/Lib/Codec/enc_mode_config.c:684
+ *   svt_aom_downsample_filtering_input_picture  Source/Lib/Codec/pic_analysis_process.c:1922
+ *   svt_aom_generate_padding           Source/Lib/Codec/pic_operators.c:338
+ *   RTCD pointers                      Source/Lib/Codec/aom_dsp_rtcd.h:776,838-854
+ */
+#include <stdlib.h>
+#include <string.h>
+#include <stdio.h>
+
+/* Instantiate the RTCD function-pointer globals here (the reference does it in aom_dsp_rtcd.c /
+ * common_dsp_rtcd.c, which drag in the whole library). */
+#define AOM_RTCD_C
+#define RTCD_C
+#include "aom_dsp_rtcd.h"
+#include "common_dsp_rtcd.h"
+#include "pcs.h"
+#include "sequence_control_set.h"
+#include "me_context.h"
+#include "motion_estimation.h"
+#include "reference_object.h"
+#include "pic_operators.h"
+#include "pic_analysis_process.h"
+#include "enc_mode_config.h"
+#include "compute_sad_c.h"
+#include "me_sad_calculation.h"
+
+#include "svtme_b200.h"
+
+void svt_aom_get_max_allocated_me_refs(uint8_t ref_count_used_list0, uint8_t ref_count_used_list1,
+                                       uint8_t *max_ref_to_alloc, uint8_t *max_cand_to_alloc); /* Codec/pcs.c:90 */
+
+/* ---- symbols the pulled-in objects reference but this path never reaches ---- */
+void svt_log(int level, const char *tag, const char *fmt, ...) { (void)level; (void)tag; (void)fmt; }
+void svt_aom_assert_err(uint32_t condition, char *err_msg) {
+    if (!condition) { fprintf(stderr, "ref assert: %s\n", err_msg); abort(); }
+}
+
+/* AVX2 entry points of Source/Lib/ASM_AVX2/compute_sad_intrin_avx2.c + picture_operators */
+void svt_sad_loop_kernel_avx2_intrin(uint8_t *, uint32_t, uint8_t *, uint32_t, uint32_t, uint32_t, uint64_t *,
+                                     int16_t *, int16_t *, uint32_t, uint8_t, int16_t, int16_t);
+void svt_ext_all_sad_calculation_8x8_16x16_avx2(uint8_t *, uint32_t, uint8_t *, uint32_t, uint32_t, uint32_t *,
+                                                uint32_t *, uint32_t *, uint32_t *, uint32_t[16][8],
+                                                uint32_t[64][8], Bool);
+void svt_ext_eight_sad_calculation_32x32_64x64_avx2(uint32_t[16][8], uint32_t *, uint32_t *, uint32_t *,
+                                                    uint32_t *, uint32_t, uint32_t[4][8]);
+void svt_ext_sad_calculation_8x8_16x16_avx2_intrin(uint8_t *, uint32_t, uint8_t *, uint32_t, uint32_t *,
+                                                   uint32_t *, uint32_t *, uint32_t *, uint32_t, uint32_t *,
+                                                   uint32_t *, Bool);
+void svt_ext_sad_calculation_32x32_64x64_sse4_intrin(uint32_t *, uint32_t *, uint32_t *, uint32_t *, uint32_t *,
+                                                     uint32_t, uint32_t *);
+uint32_t svt_nxm_sad_kernel_helper_avx2(const uint8_t *, uint32_t, const uint8_t *, uint32_t, uint32_t, uint32_t);
+
+static void *memcpy_shim(void *d, void const *s, size_t n) { return memcpy(d, s, n); }
+static void memcpy_void(void *d, void const *s, size_t n) { memcpy(d, s, n); }
+
+static int g_simd = -1;
+
+/* What svt_aom_setup_rtcd_internal (aom_dsp_rtcd.c:187, x86 block :499-514) does for the ME
+ * pointers: C first, overwritten by AVX2 when allowed. simd: 0 = C_DEFAULT, 1 = AVX2. */
+int ref_set_simd(int simd) {
+    (void)memcpy_shim;
+    svt_memcpy                                 = memcpy_void;
+    svt_sad_loop_kernel                        = svt_sad_loop_kernel_c;
+    svt_ext_all_sad_calculation_8x8_16x16      = svt_ext_all_sad_calculation_8x8_16x16_c;
+    svt_ext_eight_sad_calculation_32x32_64x64  = svt_ext_eight_sad_calculation_32x32_64x64_c;
+    svt_ext_sad_calculation_8x8_16x16          = svt_ext_sad_calculation_8x8_16x16_c;
+    svt_ext_sad_calculation_32x32_64x64        = svt_ext_sad_calculation_32x32_64x64_c;
+    svt_initialize_buffer_32bits               = svt_initialize_buffer_32bits_c;
+    svt_nxm_sad_kernel                         = svt_nxm_sad_kernel_helper_c;
+    svt_nxm_sad_kernel_sub_sampled             = svt_nxm_sad_kernel_helper_c;
+    downsample_2d                              = svt_aom_downsample_2d_c;
+#ifdef REF_HAVE_AVX2
+    if (simd && __builtin_cpu_supports("avx2")) {
+        svt_sad_loop_kernel                       = svt_sad_loop_kernel_avx2_intrin;
+        svt_ext_all_sad_calculation_8x8_16x16     = svt_ext_all_sad_calculation_8x8_16x16_avx2;
+        svt_ext_eight_sad_calculation_32x32_64x64 = svt_ext_eight_sad_calculation_32x32_64x64_avx2;
+        svt_ext_sad_calculation_8x8_16x16         = svt_ext_sad_calculation_8x8_16x16_avx2_intrin;
+        svt_nxm_sad_kernel                        = svt_nxm_sad_kernel_helper_avx2;
+        svt_nxm_sad_kernel_sub_sampled            = svt_nxm_sad_kernel_helper_avx2;
+        g_simd                                    = 1;
+        return 1;
+    }
+#endif
+    g_simd = 0;
+    return 0;
+}
+
+/* ---- planes ---- */
+typedef struct RefPlane {
+    uint8_t *buffer_y;
+    uint32_t stride_y, org_x, org_y, width, height;
+} RefPlane;
+typedef struct RefPyramid {
+    RefPlane full, quarter, sixteenth;
+    uint64_t picture_number;
+} RefPyramid;
+
+static void to_desc(const RefPlane *pl, EbPictureBufferDesc *d) {
+    memset(d, 0, sizeof(*d));
+    d->buffer_y  = pl->buffer_y;
+    d->stride_y  = (uint16_t)pl->stride_y;
+    d->org_x     = (uint16_t)pl->org_x;
+    d->org_y     = (uint16_t)pl->org_y;
+    d->width     = (uint16_t)pl->width;
+    d->height    = (uint16_t)pl->height;
+    d->max_width = (uint16_t)pl->width;
+    d->max_height = (uint16_t)pl->height;
+}
+
+static int plane_alloc(RefPlane *pl, uint32_t w, uint32_t h, uint32_t pad) {
+    pl->width = w; pl->height = h; pl->org_x = pl->org_y = pad;
+    pl->stride_y = w + 2 * pad;
+    pl->buffer_y = (uint8_t *)calloc((size_t)pl->stride_y * (h + 2 * pad), 1);
+    return pl->buffer_y ? 0 : -1;
+}
+
+void ref_pyramid_free(RefPyramid *pyr) {
+    free(pyr->full.buffer_y); free(pyr->quarter.buffer_y); free(pyr->sixteenth.buffer_y);
+    memset(pyr, 0, sizeof(*pyr));
+}
+
+/* Luma part of svt_aom_pad_input_pictures + svt_aom_downsample_filtering_input_picture, run
+ * through the reference functions. Same geometry as orc_pyramid_build (pads 72/32/16). */
+int ref_pyramid_build(RefPyramid *pyr, const uint8_t *luma, uint32_t stride, uint32_t width, uint32_t height,
+                      int hme_level1, uint64_t picture_number) {
+    if (g_simd < 0) ref_set_simd(0);
+    memset(pyr, 0, sizeof(*pyr));
+    pyr->picture_number = picture_number;
+    if (plane_alloc(&pyr->full, width, height, 72) || plane_alloc(&pyr->quarter, width >> 1, height >> 1, 32) ||
+        plane_alloc(&pyr->sixteenth, width >> 2, height >> 2, 16)) {
+        ref_pyramid_free(pyr);
+        return -1;
+    }
+    RefPlane *f = &pyr->full;
+    for (uint32_t y = 0; y < height; ++y)
+        memcpy(f->buffer_y + (size_t)(f->org_y + y) * f->stride_y + f->org_x, luma + (size_t)y * stride, width);
+    svt_aom_generate_padding(f->buffer_y, f->stride_y, f->width, f->height, f->org_x, f->org_y);
+    EbPictureBufferDesc df, dq, ds;
+    to_desc(&pyr->full, &df); to_desc(&pyr->quarter, &dq); to_desc(&pyr->sixteenth, &ds);
+    PictureParentControlSet *pcs = (PictureParentControlSet *)calloc(1, sizeof(*pcs));
+    if (!pcs) return -1;
+    pcs->enable_hme_flag = 1;
+    pcs->enable_hme_level0_flag = 1;
+    pcs->enable_hme_level1_flag = hme_level1 ? 1 : 0;
+    svt_aom_downsample_filtering_input_picture(pcs, &df, &dq, &ds);
+    free(pcs);
+    return 0;
+}
+
+/* ---- parameters ---- */
+static void params_to_ctx(const SvtMeParams *p, MeContext *c) {
+#define SA(dst, src) do { (dst).width = (src).width; (dst).height = (src).height; } while (0)
+    SA(c->me_sa.sa_min, p->me_sa.sa_min); SA(c->me_sa.sa_max, p->me_sa.sa_max);
+    SA(c->hme_l0_sa.sa_min, p->hme_l0_sa.sa_min); SA(c->hme_l0_sa.sa_max, p->hme_l0_sa.sa_max);
+    SA(c->hme_l1_sa, p->hme_l1_sa); SA(c->hme_l2_sa, p->hme_l2_sa);
+    c->num_hme_sa_w = p->num_hme_sa_w; c->num_hme_sa_h = p->num_hme_sa_h;
+    c->enable_hme_flag = p->enable_hme_flag; c->enable_hme_level0_flag = p->enable_hme_level0_flag;
+    c->enable_hme_level1_flag = p->enable_hme_level1_flag; c->enable_hme_level2_flag = p->enable_hme_level2_flag;
+    c->hme_search_method = p->hme_search_method; c->me_search_method = p->me_search_method;
+    c->reduce_hme_l0_sr_th_min = p->reduce_hme_l0_sr_th_min; c->reduce_hme_l0_sr_th_max = p->reduce_hme_l0_sr_th_max;
+    c->prehme_ctrl.enable = p->prehme_enable; c->prehme_ctrl.skip_search_line = p->prehme_skip_search_line;
+    c->prehme_ctrl.l1_early_exit = p->prehme_l1_early_exit;
+    for (int i = 0; i < 2; ++i) {
+        SA(c->prehme_ctrl.prehme_sa_cfg[i].sa_min, p->prehme_sa_cfg[i].sa_min);
+        SA(c->prehme_ctrl.prehme_sa_cfg[i].sa_max, p->prehme_sa_cfg[i].sa_max);
+    }
+    c->me_hme_prune_ctrls.enable_me_hme_ref_pruning = p->enable_me_hme_ref_pruning;
+    c->me_hme_prune_ctrls.prune_ref_if_hme_sad_dev_bigger_than_th = p->prune_ref_if_hme_sad_dev_bigger_than_th;
+    c->me_hme_prune_ctrls.prune_ref_if_me_sad_dev_bigger_than_th = p->prune_ref_if_me_sad_dev_bigger_than_th;
+    c->me_hme_prune_ctrls.zz_sad_th = p->zz_sad_th; c->me_hme_prune_ctrls.zz_sad_pct = p->zz_sad_pct;
+    c->me_hme_prune_ctrls.phme_sad_th = p->phme_sad_th; c->me_hme_prune_ctrls.phme_sad_pct = p->phme_sad_pct;
+    c->me_sr_adjustment_ctrls.enable_me_sr_adjustment = p->enable_me_sr_adjustment;
+    c->me_sr_adjustment_ctrls.distance_based_hme_resizing = p->distance_based_hme_resizing;
+    c->me_sr_adjustment_ctrls.reduce_me_sr_based_on_mv_length_th = p->reduce_me_sr_based_on_mv_length_th;
+    c->me_sr_adjustment_ctrls.stationary_hme_sad_abs_th = p->stationary_hme_sad_abs_th;
+    c->me_sr_adjustment_ctrls.stationary_me_sr_divisor = p->stationary_me_sr_divisor;
+    c->me_sr_adjustment_ctrls.reduce_me_sr_based_on_hme_sad_abs_th = p->reduce_me_sr_based_on_hme_sad_abs_th;
+    c->me_sr_adjustment_ctrls.me_sr_divisor_for_low_hme_sad = p->me_sr_divisor_for_low_hme_sad;
+    c->me_8x8_var_ctrls.enabled = p->me_8x8_var_enabled; c->me_8x8_var_ctrls.me_sr_div4_th = p->me_sr_div4_th;
+    c->me_8x8_var_ctrls.me_sr_div2_th = p->me_sr_div2_th; c->me_8x8_var_ctrls.me_sr_mult2_th = p->me_sr_mult2_th;
+    c->mv_based_sa_adj.enabled = p->mv_sa_adj_enabled; c->mv_based_sa_adj.nearest_ref_only = p->mv_sa_adj_nearest_ref_only;
+    c->mv_based_sa_adj.mv_size_th = p->mv_sa_adj_mv_size_th; c->mv_based_sa_adj.sa_multiplier = p->mv_sa_adj_sa_multiplier;
+    c->prune_me_candidates_th = p->prune_me_candidates_th;
+    c->use_best_unipred_cand_only = p->use_best_unipred_cand_only;
+    c->me_early_exit_th = p->me_early_exit_th; c->me_safe_limit_zz_th = p->me_safe_limit_zz_th;
+    c->prev_me_stage_based_exit_th = p->prev_me_stage_based_exit_th;
+    c->num_of_list_to_search = p->num_of_list_to_search;
+    c->num_of_ref_pic_to_search[0] = p->num_of_ref_pic_to_search[0];
+    c->num_of_ref_pic_to_search[1] = p->num_of_ref_pic_to_search[1];
+    c->temporal_layer_index = p->temporal_layer_index; c->is_ref = p->is_ref;
+    c->me_type = ME_OPEN_LOOP;
+#undef SA
+}
+
+static void ctx_to_params(const MeContext *c, SvtMeParams *p) {
+#define SA(dst, src) do { (dst).width = (src).width; (dst).height = (src).height; } while (0)
+    SA(p->me_sa.sa_min, c->me_sa.sa_min); SA(p->me_sa.sa_max, c->me_sa.sa_max);
+    SA(p->hme_l0_sa.sa_min, c->hme_l0_sa.sa_min); SA(p->hme_l0_sa.sa_max, c->hme_l0_sa.sa_max);
+    SA(p->hme_l1_sa, c->hme_l1_sa); SA(p->hme_l2_sa, c->hme_l2_sa);
+    p->num_hme_sa_w = c->num_hme_sa_w; p->num_hme_sa_h = c->num_hme_sa_h;
+    p->enable_hme_flag = c->enable_hme_flag; p->enable_hme_level0_flag = c->enable_hme_level0_flag;
+    p->enable_hme_level1_flag = c->enable_hme_level1_flag; p->enable_hme_level2_flag = c->enable_hme_level2_flag;
+    p->hme_search_method = c->hme_search_method; p->me_search_method = c->me_search_method;
+    p->reduce_hme_l0_sr_th_min = c->reduce_hme_l0_sr_th_min; p->reduce_hme_l0_sr_th_max = c->reduce_hme_l0_sr_th_max;
+    p->prehme_enable = c->prehme_ctrl.enable;
+    if (p->prehme_enable) {
+        p->prehme_skip_search_line = c->prehme_ctrl.skip_search_line;
+        p->prehme_l1_early_exit = c->prehme_ctrl.l1_early_exit;
+        for (int i = 0; i < 2; ++i) {
+            SA(p->prehme_sa_cfg[i].sa_min, c->prehme_ctrl.prehme_sa_cfg[i].sa_min);
+            SA(p->prehme_sa_cfg[i].sa_max, c->prehme_ctrl.prehme_sa_cfg[i].sa_max);
+        }
+    }
+    p->enable_me_hme_ref_pruning = c->me_hme_prune_ctrls.enable_me_hme_ref_pruning;
+    p->prune_ref_if_hme_sad_dev_bigger_than_th = c->me_hme_prune_ctrls.prune_ref_if_hme_sad_dev_bigger_than_th;
+    p->prune_ref_if_me_sad_dev_bigger_than_th = c->me_hme_prune_ctrls.prune_ref_if_me_sad_dev_bigger_than_th;
+    p->zz_sad_th = c->me_hme_prune_ctrls.zz_sad_th; p->zz_sad_pct = c->me_hme_prune_ctrls.zz_sad_pct;
+    p->phme_sad_th = c->me_hme_prune_ctrls.phme_sad_th; p->phme_sad_pct = c->me_hme_prune_ctrls.phme_sad_pct;
+    p->enable_me_sr_adjustment = c->me_sr_adjustment_ctrls.enable_me_sr_adjustment;
+    if (p->enable_me_sr_adjustment) {
+        p->distance_based_hme_resizing = c->me_sr_adjustment_ctrls.distance_based_hme_resizing;
+        p->reduce_me_sr_based_on_mv_length_th = c->me_sr_adjustment_ctrls.reduce_me_sr_based_on_mv_length_th;
+        p->stationary_hme_sad_abs_th = c->me_sr_adjustment_ctrls.stationary_hme_sad_abs_th;
+        p->stationary_me_sr_divisor = c->me_sr_adjustment_ctrls.stationary_me_sr_divisor;
+        p->reduce_me_sr_based_on_hme_sad_abs_th = c->me_sr_adjustment_ctrls.reduce_me_sr_based_on_hme_sad_abs_th;
+        p->me_sr_divisor_for_low_hme_sad = c->me_sr_adjustment_ctrls.me_sr_divisor_for_low_hme_sad;
+    }
+    p->me_8x8_var_enabled = c->me_8x8_var_ctrls.enabled; p->me_sr_div4_th = c->me_8x8_var_ctrls.me_sr_div4_th;
+    p->me_sr_div2_th = c->me_8x8_var_ctrls.me_sr_div2_th; p->me_sr_mult2_th = c->me_8x8_var_ctrls.me_sr_mult2_th;
+    p->mv_sa_adj_enabled = c->mv_based_sa_adj.enabled;
+    if (p->mv_sa_adj_enabled) {
+        p->mv_sa_adj_nearest_ref_only = c->mv_based_sa_adj.nearest_ref_only;
+        p->mv_sa_adj_mv_size_th = c->mv_based_sa_adj.mv_size_th; p->mv_sa_adj_sa_multiplier = c->mv_based_sa_adj.sa_multiplier;
+    }
+    p->prune_me_candidates_th = c->prune_me_candidates_th;
+    p->use_best_unipred_cand_only = c->use_best_unipred_cand_only;
+    p->me_early_exit_th = c->me_early_exit_th; p->me_safe_limit_zz_th = c->me_safe_limit_zz_th;
+    p->prev_me_stage_based_exit_th = c->prev_me_stage_based_exit_th;
+#undef SA
+}
+
+/* Runs the reference's own svt_aom_sig_deriv_me + svt_aom_get_enable_me_8x8 + input-resolution
+ * classification on a minimal scs/pcs and reports the MeContext it produced. */
+int ref_derive_params(const SvtMeDeriveInput *in, SvtMeParams *out) {
+    SequenceControlSet      *scs = (SequenceControlSet *)calloc(1, sizeof(*scs));
+    PictureParentControlSet *pcs = (PictureParentControlSet *)calloc(1, sizeof(*pcs));
+    MeContext               *ctx = (MeContext *)calloc(1, sizeof(*ctx));
+    if (!scs || !pcs || !ctx) return -1;
+    memset(out, 0, sizeof(*out));
+    EbInputResolution res;
+    svt_aom_derive_input_resolution(&res, in->width * in->height);
+    scs->input_resolution = res;
+    scs->static_config.pred_structure = in->rtc_tune ? SVT_AV1_PRED_LOW_DELAY_B : SVT_AV1_PRED_RANDOM_ACCESS;
+    scs->static_config.qp = in->qp;
+    scs->frame_rate = in->frame_rate_q16;
+    scs->mrp_ctrls.safe_limit_nref = in->safe_limit_nref;
+    scs->mrp_ctrls.safe_limit_zz_th = in->safe_limit_zz_th;
+    pcs->scs = scs;
+    pcs->enc_mode = (EncMode)in->enc_mode;
+    pcs->sc_class1 = in->sc_class1;
+    pcs->hierarchical_levels = in->hierarchical_levels;
+    pcs->temporal_layer_index = in->temporal_layer_index;
+    pcs->use_best_me_unipred_cand_only = in->use_best_me_unipred_cand_only;
+    /* HME level flags: enc_mode_config.c:1798-1809 (first-pass derivation), open-loop values */
+    pcs->enable_hme_flag = 1;
+    pcs->enable_hme_level0_flag = 1;
+    pcs->enable_hme_level1_flag = 1;
+    pcs->enable_hme_level2_flag = (in->sc_class1 || in->enc_mode <= ENC_M6) ? 1 : 0;
+    svt_aom_sig_deriv_me(scs, pcs, ctx);
+    ctx_to_params(ctx, out);
+    out->enable_me_8x8 = svt_aom_get_enable_me_8x8((EncMode)in->enc_mode, in->rtc_tune, res);
+    out->enable_me_16x16 = svt_aom_get_enable_me_16x16((EncMode)in->enc_mode);
+    out->input_resolution_le_480p = res <= INPUT_SIZE_480p_RANGE;
+    uint8_t mr, mc;
+    svt_aom_get_max_allocated_me_refs(in->ref_count_used_list0, in->ref_count_used_list1, &mr, &mc);
+    out->max_refs = mr; out->max_cand = mc; out->max_l0 = in->ref_count_used_list0;
+    free(scs); free(pcs); free(ctx);
+    return 0;
+}
+
+/* Whole picture through svt_aom_motion_estimation_b64, single thread, raster b64 order, with
+ * the pointer set-up of me_process.c:189-262. rows [row0,row1) of b64s. */
+int ref_me_picture_rows(const SvtMeParams *p, const RefPyramid *cur, const RefPyramid *refs[2][4], SvtMeOut *out,
+                        uint32_t row0, uint32_t row1) {
+    if (g_simd < 0) ref_set_simd(0);
+    const uint32_t W = cur->full.width, H = cur->full.height;
+    const uint32_t bw = (W + 63) / 64, bh = (H + 63) / 64, nb = bw * bh;
+    const uint32_t n_pu = p->enable_me_16x16 ? (p->enable_me_8x8 ? p->max_number_of_pus_per_sb : 21u) : 5u;
+    SequenceControlSet      *scs = (SequenceControlSet *)calloc(1, sizeof(*scs));
+    PictureParentControlSet *pcs = (PictureParentControlSet *)calloc(1, sizeof(*pcs));
+    MeContext               *ctx = (MeContext *)calloc(1, sizeof(*ctx));
+    MotionEstimationData    *med = (MotionEstimationData *)calloc(1, sizeof(*med));
+    MeSbResults             *res = (MeSbResults *)calloc(nb, sizeof(*res));
+    MeSbResults            **resp = (MeSbResults **)calloc(nb, sizeof(*resp));
+    B64Geom                 *geom = (B64Geom *)calloc(nb, sizeof(*geom));
+    uint32_t *d64 = calloc(nb, 4), *d32 = calloc(nb, 4), *d16 = calloc(nb, 4), *d8 = calloc(nb, 4), *var = calloc(nb, 4),
+             *rc = calloc(nb, 4);
+    uint8_t *stat = calloc(nb, 1), *gm = calloc(nb, 1);
+    uint8_t  *tot  = calloc((size_t)nb * n_pu, 1);
+    uint32_t *mvs  = calloc((size_t)nb * n_pu * p->max_refs, 4);
+    uint8_t  *cand = calloc((size_t)nb * n_pu * p->max_cand, 1);
+    if (!scs || !pcs || !ctx || !med || !res || !resp || !geom || !tot || !mvs || !cand) return -1;
+    for (uint32_t b = 0; b < nb; ++b) {
+        res[b].total_me_candidate_index = tot + (size_t)b * n_pu;
+        res[b].me_mv_array              = (MvCandidate *)(mvs + (size_t)b * n_pu * p->max_refs);
+        res[b].me_candidate_array       = (MeCandidate *)(cand + (size_t)b * n_pu * p->max_cand);
+        resp[b]                         = &res[b];
+        uint32_t ox = (b % bw) * 64, oy = (b / bw) * 64;
+        geom[b].org_x = (uint16_t)ox; geom[b].org_y = (uint16_t)oy;
+        geom[b].width = (uint8_t)((W - ox) < 64 ? W - ox : 64);
+        geom[b].height = (uint8_t)((H - oy) < 64 ? H - oy : 64);
+    }
+    med->me_results = resp; med->max_cand = p->max_cand; med->max_refs = p->max_refs; med->max_l0 = p->max_l0;
+    scs->input_resolution = p->input_resolution_le_480p ? INPUT_SIZE_480p_RANGE : INPUT_SIZE_1080p_RANGE;
+    scs->mrp_ctrls.only_l_bwd = p->only_l_bwd;
+    scs->static_config.restricted_motion_vector = 0;
+    pcs->scs = scs; pcs->pa_me_data = med; pcs->b64_geom = geom;
+    pcs->picture_number = p->picture_number;
+    pcs->aligned_width = (uint16_t)W; pcs->aligned_height = (uint16_t)H;
+    pcs->enable_me_8x8 = p->enable_me_8x8; pcs->enable_me_16x16 = p->enable_me_16x16;
+    pcs->max_number_of_pus_per_sb = p->max_number_of_pus_per_sb;
+    pcs->hierarchical_levels = p->hierarchical_levels; pcs->temporal_layer_index = p->temporal_layer_index;
+    pcs->similar_brightness_refs = p->similar_brightness_refs;
+    pcs->gm_ctrls.enabled = p->gm_enabled; pcs->gm_ctrls.use_distance_based_active_th = p->gm_use_distance_based_active_th;
+    pcs->me_64x64_distortion = d64; pcs->me_32x32_distortion = d32; pcs->me_16x16_distortion = d16;
+    pcs->me_8x8_distortion = d8; pcs->me_8x8_cost_variance = var; pcs->rc_me_distortion = rc;
+    pcs->stationary_block_present_sb = stat; pcs->rc_me_allow_gm = gm;
+    params_to_ctx(p, ctx);
+    EbPictureBufferDesc dcur, dref[2][4][3];
+    to_desc(&cur->full, &dcur);
+    for (int li = 0; li < p->num_of_list_to_search; ++li)
+        for (int ri = 0; ri < p->num_of_ref_pic_to_search[li]; ++ri) {
+            to_desc(&refs[li][ri]->full, &dref[li][ri][0]);
+            to_desc(&refs[li][ri]->quarter, &dref[li][ri][1]);
+            to_desc(&refs[li][ri]->sixteenth, &dref[li][ri][2]);
+            ctx->me_ds_ref_array[li][ri].picture_ptr           = &dref[li][ri][0];
+            ctx->me_ds_ref_array[li][ri].quarter_picture_ptr   = &dref[li][ri][1];
+            ctx->me_ds_ref_array[li][ri].sixteenth_picture_ptr = &dref[li][ri][2];
+            ctx->me_ds_ref_array[li][ri].picture_number        = p->ref_picture_number[li][ri];
+        }
+    if (row1 > bh) row1 = bh;
+    for (uint32_t by = row0; by < row1; ++by)
+        for (uint32_t bx = 0; bx < bw; ++bx) {
+            const uint32_t b = bx + by * bw, ox = bx * 64, oy = by * 64;
+            const RefPlane *f = &cur->full, *q = &cur->quarter, *x = &cur->sixteenth;
+            ctx->b64_src_ptr    = f->buffer_y + (size_t)(f->org_y + oy) * f->stride_y + f->org_x + ox;
+            ctx->b64_src_stride = f->stride_y;
+            ctx->quarter_b64_buffer = q->buffer_y + (size_t)(q->org_y + (oy >> 1)) * q->stride_y + q->org_x + (ox >> 1);
+            ctx->quarter_b64_buffer_stride = q->stride_y;
+            ctx->sixteenth_b64_buffer = x->buffer_y + (size_t)(x->org_y + (oy >> 2)) * x->stride_y + x->org_x + (ox >> 2);
+            ctx->sixteenth_b64_buffer_stride = x->stride_y;
+            ctx->me_type = ME_OPEN_LOOP;
+            /* not part of the reference: clear the tables of refs the block will not search so the
+             * deep-state dump is comparable (they are never read before being initialised). */
+            memset(ctx->p_sb_best_sad, 0, sizeof(ctx->p_sb_best_sad));
+            svt_aom_motion_estimation_b64(pcs, b, ox, oy, ctx, &dcur);
+            if (out->p_sb_best_sad) memcpy(out->p_sb_best_sad + (size_t)b * 2 * 4 * 85, ctx->p_sb_best_sad, sizeof(ctx->p_sb_best_sad));
+            if (out->p_sb_best_mv) memcpy(out->p_sb_best_mv + (size_t)b * 2 * 4 * 85, ctx->p_sb_best_mv, sizeof(ctx->p_sb_best_mv));
+            for (int li = 0; li < 2; ++li)
+                for (int ri = 0; ri < 4; ++ri) {
+                    const size_t k = ((size_t)b * 2 + li) * 4 + ri;
+                    if (out->hme_sc) { out->hme_sc[2 * k] = ctx->search_results[li][ri].hme_sc_x; out->hme_sc[2 * k + 1] = ctx->search_results[li][ri].hme_sc_y; }
+                    if (out->hme_sad) out->hme_sad[k] = ctx->search_results[li][ri].hme_sad;
+                    if (out->do_ref) out->do_ref[k] = ctx->search_results[li][ri].do_ref;
+                }
+        }
+    const size_t b0 = (size_t)row0 * bw, b1 = (size_t)row1 * bw;
+#define COPY(dst, src, per, sz) if (out->dst) memcpy(out->dst + b0 * (per), (src) + b0 * (per), (b1 - b0) * (per) * (sz))
+    COPY(total_me_candidate_index, tot, n_pu, 1);
+    COPY(me_mv_array, mvs, (size_t)n_pu * p->max_refs, 4);
+    COPY(me_candidate_array, cand, (size_t)n_pu * p->max_cand, 1);
+    COPY(me_64x64_distortion, d64, 1, 4); COPY(me_32x32_distortion, d32, 1, 4); COPY(me_16x16_distortion, d16, 1, 4);
+    COPY(me_8x8_distortion, d8, 1, 4); COPY(me_8x8_cost_variance, var, 1, 4); COPY(rc_me_distortion, rc, 1, 4);
+    COPY(stationary_block_present_sb, stat, 1, 1); COPY(rc_me_allow_gm, gm, 1, 1);
+#undef COPY
+    free(scs); free(pcs); free(ctx); free(med); free(res); free(resp); free(geom);
+    free(d64); free(d32); free(d16); free(d8); free(var); free(rc); free(stat); free(gm); free(tot); free(mvs); free(cand);
+    return 0;
+}
+
+int ref_me_picture(const SvtMeParams *p, const RefPyramid *cur, const RefPyramid *refs[2][4], SvtMeOut *out) {
+    return ref_me_picture_rows(p, cur, refs, out, 0, 0xffffffffu);
+}
+
+int ref_simd_level(void) { return g_simd; }
+unsigned ref_sizeof_params(void) { return (unsigned)sizeof(SvtMeParams); }
+unsigned ref_sizeof_derive_input(void) { return (unsigned)sizeof(SvtMeDeriveInput); }
+unsigned ref_sizeof_out(void) { return (unsigned)sizeof(SvtMeOut); }

@@ -1,0 +1,407 @@
+// svtme_api.cu — the C ABI of include/svtme_b200.h: picture-granular production entry points and
+// the RTCD-signature kernel-test wrappers. Host code only orchestrates: every pixel operation is
+// a CUDA kernel of this library; there is no CPU fallback (a CUDA failure is reported, never
+// papered over).
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <map>
+#include <mutex>
+#include <vector>
+#include "svtme_common.cuh"
+
+static thread_local char g_err[512] = "";
+static int fail(int code, const char *what, cudaError_t e = cudaSuccess) {
+    if (e != cudaSuccess)
+        snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
+    else
+        snprintf(g_err, sizeof(g_err), "%s", what);
+    return code;
+}
+#define CU(call)                                                  \
+    do {                                                          \
+        cudaError_t e_ = (call);                                  \
+        if (e_ != cudaSuccess) return fail(SVTME_ERR_CUDA, #call, e_); \
+    } while (0)
+
+extern "C" const char *svtme_last_error(void) { return g_err; }
+extern "C" uint64_t svtme_launch_count(void) { return g_svtme_launches; }
+extern "C" uint32_t svtme_sizeof_params(void) { return (uint32_t)sizeof(SvtMeParams); }
+extern "C" uint32_t svtme_sizeof_out(void) { return (uint32_t)sizeof(SvtMeOut); }
+extern "C" uint32_t svtme_sizeof_job(void) { return (uint32_t)sizeof(SvtMeJob); }
+extern "C" uint32_t svtme_sizeof_derive_input(void) { return (uint32_t)sizeof(SvtMeDeriveInput); }
+
+struct Slot {
+    DevPyramid pyr;
+    uint64_t pic_num;
+    bool used;
+};
+
+struct OutBuffers { // device + pinned host staging for one batch of jobs
+    size_t bytes = 0;
+    uint8_t *dev = nullptr;
+    uint8_t *host = nullptr;
+};
+
+struct SvtMeHandle {
+    int device;
+    uint32_t width, height, b64_cols, b64_rows, n_b64;
+    cudaStream_t stream;
+    uint8_t *pool; // all planes of all slots
+    size_t plane_bytes[3], slot_bytes;
+    std::vector<Slot> slots;
+    std::map<uint64_t, int> index;
+    uint8_t *stage_host; // pinned upload staging (one luma plane)
+    uint8_t *stage_dev;
+    DevJob *d_jobs;
+    DevJob *h_jobs; // pinned
+    uint32_t jobs_cap;
+    OutBuffers ob;
+    cudaEvent_t ev0, ev1;
+    float last_ms;
+    std::mutex mu;
+};
+
+static const int kOrgX[3] = {128, 64, 32}, kOrgY[3] = {72, 32, 16};
+// pads that are actually filled (>= the reference's 72/32/16 and >= every over-read of the kernels)
+static const int kPadL[3] = {128, 64, 32}, kPadR[3] = {128, 64, 32}, kPadT[3] = {72, 32, 16}, kPadB[3] = {72, 32, 16};
+
+static void layout_plane(DevPlane &pl, uint8_t *base, int level, int w, int h) {
+    pl.base = base;
+    pl.org_x = kOrgX[level];
+    pl.org_y = kOrgY[level];
+    pl.width = w >> level;
+    pl.height = h >> level;
+    pl.stride = up128(pl.width + kPadL[level] + kPadR[level]);
+}
+static size_t plane_size(int level, int w, int h) {
+    DevPlane pl;
+    layout_plane(pl, nullptr, level, w, h);
+    // one extra row of slack: staging may touch the 16 bytes after the last pad row's last chunk
+    return (size_t)pl.stride * (pl.height + kPadT[level] + kPadB[level] + 1);
+}
+
+extern "C" int svtme_open(int device, uint32_t width, uint32_t height, uint32_t capacity, SvtMeHandle **out) {
+    if (!out || width < 64 || height < 64 || (width & 7) || (height & 7) || capacity == 0 || width > 16384 || height > 8704)
+        return fail(SVTME_ERR_INVALID, "svtme_open: width/height must be multiples of 8, >= 64 (aligned luma size)");
+    CU(cudaSetDevice(device));
+    SvtMeHandle *h = new (std::nothrow) SvtMeHandle();
+    if (!h) return fail(SVTME_ERR_NOMEM, "svtme_open: host allocation");
+    h->device = device;
+    h->width = width;
+    h->height = height;
+    h->b64_cols = (width + 63) / 64;
+    h->b64_rows = (height + 63) / 64;
+    h->n_b64 = h->b64_cols * h->b64_rows;
+    h->slot_bytes = 0;
+    for (int l = 0; l < 3; ++l) {
+        h->plane_bytes[l] = (plane_size(l, width, height) + 255) & ~(size_t)255;
+        h->slot_bytes += h->plane_bytes[l];
+    }
+    h->pool = nullptr;
+    h->stage_host = h->stage_dev = nullptr;
+    h->d_jobs = h->h_jobs = nullptr;
+    h->jobs_cap = 0;
+    h->last_ms = 0.f;
+    cudaError_t e = cudaMalloc(&h->pool, h->slot_bytes * capacity);
+    if (e != cudaSuccess) { delete h; return fail(SVTME_ERR_NOMEM, "svtme_open: cudaMalloc pyramid pool", e); }
+    e = cudaMemset(h->pool, 0, h->slot_bytes * capacity);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMallocHost(&h->stage_host, (size_t)width * height);
+    if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
+    if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
+    if (e != cudaSuccess) { cudaFree(h->pool); delete h; return fail(SVTME_ERR_CUDA, "svtme_open", e); }
+    h->slots.resize(capacity);
+    for (uint32_t i = 0; i < capacity; ++i) {
+        uint8_t *b = h->pool + h->slot_bytes * i;
+        for (int l = 0; l < 3; ++l) {
+            layout_plane(h->slots[i].pyr.lvl[l], b, l, width, height);
+            b += h->plane_bytes[l];
+        }
+        h->slots[i].used = false;
+        h->slots[i].pic_num = 0;
+    }
+    *out = h;
+    return SVTME_OK;
+}
+
+extern "C" void svtme_close(SvtMeHandle *h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    cudaFree(h->pool);
+    cudaFreeHost(h->stage_host);
+    cudaFree(h->d_jobs);
+    cudaFreeHost(h->h_jobs);
+    cudaFree(h->ob.dev);
+    cudaFreeHost(h->ob.host);
+    cudaEventDestroy(h->ev0);
+    cudaEventDestroy(h->ev1);
+    cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+extern "C" uint32_t svtme_b64_count(const SvtMeHandle *h) { return h->n_b64; }
+
+static int find_slot(SvtMeHandle *h, uint64_t pic, bool create) {
+    auto it = h->index.find(pic);
+    if (it != h->index.end()) return it->second;
+    if (!create) return -1;
+    for (size_t i = 0; i < h->slots.size(); ++i)
+        if (!h->slots[i].used) {
+            h->slots[i].used = true;
+            h->slots[i].pic_num = pic;
+            h->index[pic] = (int)i;
+            return (int)i;
+        }
+    return -2;
+}
+
+static int build_pyramid(SvtMeHandle *h, Slot &s) {
+    const DevPlane &f = s.pyr.lvl[0], &q = s.pyr.lvl[1], &x = s.pyr.lvl[2];
+    svtme_launch_pad_plane(f, kPadL[0], kPadR[0], kPadT[0], kPadB[0], h->stream);
+    svtme_launch_downsample(f, q, x, 1, h->stream);
+    svtme_launch_pad_plane(q, kPadL[1], kPadR[1], kPadT[1], kPadB[1], h->stream);
+    svtme_launch_pad_plane(x, kPadL[2], kPadR[2], kPadT[2], kPadB[2], h->stream);
+    CU(cudaGetLastError());
+    return SVTME_OK;
+}
+
+extern "C" int svtme_put_picture(SvtMeHandle *h, uint64_t pic_num, const uint8_t *luma, uint32_t stride) {
+    if (!h || !luma || stride < h->width) return fail(SVTME_ERR_INVALID, "svtme_put_picture: bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(cudaSetDevice(h->device));
+    const int si = find_slot(h, pic_num, true);
+    if (si == -2) return fail(SVTME_ERR_NOMEM, "svtme_put_picture: pyramid ring full (release pictures or raise capacity)");
+    Slot &s = h->slots[si];
+    const DevPlane &f = s.pyr.lvl[0];
+    // the caller's buffer may be pageable: the copy is synchronous w.r.t. the host in that case
+    CU(cudaMemcpy2DAsync(const_cast<uint8_t *>(f.at(0, 0)), f.stride, luma, stride, h->width, h->height,
+                         cudaMemcpyHostToDevice, h->stream));
+    return build_pyramid(h, s);
+}
+
+extern "C" int svtme_put_picture_device(SvtMeHandle *h, uint64_t pic_num, const void *d_luma, uint32_t stride) {
+    if (!h || !d_luma || stride < h->width) return fail(SVTME_ERR_INVALID, "svtme_put_picture_device: bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(cudaSetDevice(h->device));
+    const int si = find_slot(h, pic_num, true);
+    if (si == -2) return fail(SVTME_ERR_NOMEM, "svtme_put_picture_device: pyramid ring full");
+    Slot &s = h->slots[si];
+    const DevPlane &f = s.pyr.lvl[0];
+    CU(cudaMemcpy2DAsync(const_cast<uint8_t *>(f.at(0, 0)), f.stride, d_luma, stride, h->width, h->height,
+                         cudaMemcpyDeviceToDevice, h->stream));
+    return build_pyramid(h, s);
+}
+
+extern "C" int svtme_adopt_picture(SvtMeHandle *h, uint64_t pic_num) {
+    if (!h) return fail(SVTME_ERR_INVALID, "svtme_adopt_picture: null handle");
+    std::lock_guard<std::mutex> lk(h->mu);
+    const int si = find_slot(h, pic_num, true);
+    if (si == -2) return fail(SVTME_ERR_NOMEM, "svtme_adopt_picture: pyramid ring full");
+    return SVTME_OK;
+}
+
+extern "C" int svtme_release_picture(SvtMeHandle *h, uint64_t pic_num) {
+    if (!h) return fail(SVTME_ERR_INVALID, "svtme_release_picture: null handle");
+    std::lock_guard<std::mutex> lk(h->mu);
+    auto it = h->index.find(pic_num);
+    if (it == h->index.end()) return fail(SVTME_ERR_NOTFOUND, "svtme_release_picture: picture not resident");
+    h->slots[it->second].used = false;
+    h->index.erase(it);
+    return SVTME_OK;
+}
+
+extern "C" int svtme_plane_device_ptr(SvtMeHandle *h, uint64_t pic_num, int level, void **ptr, size_t *bytes) {
+    if (!h || level < 0 || level > 2 || !ptr) return fail(SVTME_ERR_INVALID, "svtme_plane_device_ptr: bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    const int si = find_slot(h, pic_num, false);
+    if (si < 0) return fail(SVTME_ERR_NOTFOUND, "svtme_plane_device_ptr: picture not resident");
+    *ptr = h->slots[si].pyr.lvl[level].base;
+    if (bytes) *bytes = h->plane_bytes[level];
+    return SVTME_OK;
+}
+
+extern "C" int svtme_get_plane(SvtMeHandle *h, uint64_t pic_num, int level, uint8_t *dst, uint32_t dst_stride, uint32_t pad) {
+    if (!h || level < 0 || level > 2 || !dst) return fail(SVTME_ERR_INVALID, "svtme_get_plane: bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(cudaSetDevice(h->device));
+    const int si = find_slot(h, pic_num, false);
+    if (si < 0) return fail(SVTME_ERR_NOTFOUND, "svtme_get_plane: picture not resident");
+    const DevPlane &pl = h->slots[si].pyr.lvl[level];
+    if ((int)pad > kPadT[level] || (int)pad > kPadL[level] || dst_stride < pl.width + 2 * pad)
+        return fail(SVTME_ERR_INVALID, "svtme_get_plane: pad larger than the resident pad or stride too small");
+    CU(cudaMemcpy2DAsync(dst, dst_stride, pl.at(-(int)pad, -(int)pad), pl.stride, pl.width + 2 * pad, pl.height + 2 * pad,
+                         cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return SVTME_OK;
+}
+
+extern "C" int svtme_sync(SvtMeHandle *h) {
+    if (!h) return fail(SVTME_ERR_INVALID, "svtme_sync: null handle");
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    return SVTME_OK;
+}
+
+// ---- result buffers: per job one packed record, same order on device and in the pinned mirror
+struct OutLayout {
+    size_t total, mv, cand, d64, d32, d16, d8, var8, rc, stat, gm, bsad, bmv, sc, hsad, doref, end;
+};
+static OutLayout out_layout(uint32_t n_b64, uint32_t n_pu, const SvtMeParams &p, bool deep) {
+    OutLayout L;
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t r = o; o += (bytes + 15) & ~(size_t)15; return r; };
+    L.total = take((size_t)n_b64 * n_pu);
+    L.mv = take((size_t)n_b64 * n_pu * p.max_refs * 4);
+    L.cand = take((size_t)n_b64 * n_pu * p.max_cand);
+    L.d64 = take((size_t)n_b64 * 4); L.d32 = take((size_t)n_b64 * 4); L.d16 = take((size_t)n_b64 * 4);
+    L.d8 = take((size_t)n_b64 * 4); L.var8 = take((size_t)n_b64 * 4); L.rc = take((size_t)n_b64 * 4);
+    L.stat = take(n_b64); L.gm = take(n_b64);
+    if (deep) {
+        L.bsad = take((size_t)n_b64 * 2 * 4 * 85 * 4); L.bmv = take((size_t)n_b64 * 2 * 4 * 85 * 4);
+        L.sc = take((size_t)n_b64 * 2 * 4 * 2 * 2); L.hsad = take((size_t)n_b64 * 2 * 4 * 8); L.doref = take((size_t)n_b64 * 2 * 4);
+    } else
+        L.bsad = L.bmv = L.sc = L.hsad = L.doref = o;
+    L.end = o;
+    return L;
+}
+static bool wants_deep(const SvtMeOut &o) { return o.p_sb_best_sad || o.p_sb_best_mv || o.hme_sc || o.hme_sad || o.do_ref; }
+
+static int validate_params(const SvtMeParams &p) {
+    if (p.num_of_list_to_search < 1 || p.num_of_list_to_search > 2 || p.num_of_ref_pic_to_search[0] < 1 ||
+        p.num_of_ref_pic_to_search[0] > 4 || p.num_of_ref_pic_to_search[1] > 4 || p.max_number_of_pus_per_sb != 85 ||
+        p.num_hme_sa_w != 2 || p.num_hme_sa_h != 2 || p.max_refs == 0 || p.max_cand == 0)
+        return fail(SVTME_ERR_INVALID, "svtme: unsupported SvtMeParams (lists/refs/PU count/HME regions)");
+    if (p.num_of_list_to_search == 1 && p.num_of_ref_pic_to_search[1] != 0)
+        return fail(SVTME_ERR_INVALID, "svtme: num_of_ref_pic_to_search[1] must be 0 for a single-list picture");
+    return SVTME_OK;
+}
+
+extern "C" int svtme_launch_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n) {
+    if (!h || !jobs || n == 0) return fail(SVTME_ERR_INVALID, "svtme_launch_pictures: bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(cudaSetDevice(h->device));
+    if (n > h->jobs_cap) {
+        cudaFree(h->d_jobs);
+        cudaFreeHost(h->h_jobs);
+        h->d_jobs = h->h_jobs = nullptr;
+        h->jobs_cap = 0;
+        CU(cudaMalloc(&h->d_jobs, sizeof(DevJob) * n));
+        CU(cudaMallocHost(&h->h_jobs, sizeof(DevJob) * n));
+        h->jobs_cap = n;
+    }
+    size_t total = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        int rc = validate_params(jobs[i].params);
+        if (rc) return rc;
+        total += out_layout(h->n_b64, svtme_exported_pu_count(&jobs[i].params), jobs[i].params, wants_deep(jobs[i].out)).end;
+    }
+    if (total > h->ob.bytes) {
+        cudaFree(h->ob.dev);
+        cudaFreeHost(h->ob.host);
+        h->ob = OutBuffers();
+        CU(cudaMalloc(&h->ob.dev, total));
+        CU(cudaMallocHost(&h->ob.host, total));
+        h->ob.bytes = total;
+    }
+    size_t off = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        const SvtMeJob &j = jobs[i];
+        DevJob &d = h->h_jobs[i];
+        memset(&d, 0, sizeof(d));
+        d.prm = j.params;
+        const int sc = find_slot(h, j.cur, false);
+        if (sc < 0) return fail(SVTME_ERR_NOTFOUND, "svtme_launch_pictures: current picture not resident");
+        d.cur = h->slots[sc].pyr;
+        for (int li = 0; li < j.params.num_of_list_to_search; ++li)
+            for (int ri = 0; ri < j.params.num_of_ref_pic_to_search[li]; ++ri) {
+                const int sr = find_slot(h, j.refs[li][ri], false);
+                if (sr < 0) return fail(SVTME_ERR_NOTFOUND, "svtme_launch_pictures: reference picture not resident");
+                d.ref[li][ri] = h->slots[sr].pyr;
+            }
+        d.width = (int)h->width;
+        d.height = (int)h->height;
+        d.b64_cols = (int)h->b64_cols;
+        d.b64_rows = (int)h->b64_rows;
+        d.n_pu = (int)svtme_exported_pu_count(&j.params);
+        const bool deep = wants_deep(j.out);
+        const OutLayout L = out_layout(h->n_b64, d.n_pu, j.params, deep);
+        uint8_t *b = h->ob.dev + off;
+        d.total = b + L.total;
+        d.mv = (uint32_t *)(b + L.mv);
+        d.cand = b + L.cand;
+        d.dist64 = (uint32_t *)(b + L.d64); d.dist32 = (uint32_t *)(b + L.d32); d.dist16 = (uint32_t *)(b + L.d16);
+        d.dist8 = (uint32_t *)(b + L.d8); d.var8 = (uint32_t *)(b + L.var8); d.rc_dist = (uint32_t *)(b + L.rc);
+        d.stationary = b + L.stat; d.allow_gm = b + L.gm;
+        if (deep) {
+            d.best_sad = (uint32_t *)(b + L.bsad); d.best_mv = (uint32_t *)(b + L.bmv);
+            d.hme_sc = (int16_t *)(b + L.sc); d.hme_sad = (unsigned long long *)(b + L.hsad); d.do_ref = b + L.doref;
+        }
+        off += L.end;
+    }
+    // entries the stage never writes (pruned candidates) read as zero, like a fresh MeSbResults
+    CU(cudaMemsetAsync(h->ob.dev, 0, total, h->stream));
+    CU(cudaMemcpyAsync(h->d_jobs, h->h_jobs, sizeof(DevJob) * n, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaEventRecord(h->ev0, h->stream));
+    svtme_launch_me_stage(h->d_jobs, (int)n, (int)h->n_b64, h->stream);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(h->ev1, h->stream));
+    return SVTME_OK;
+}
+
+extern "C" int svtme_fetch_results(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n) {
+    if (!h || !jobs || n == 0) return fail(SVTME_ERR_INVALID, "svtme_fetch_results: bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(cudaSetDevice(h->device));
+    size_t total = 0;
+    for (uint32_t i = 0; i < n; ++i)
+        total += out_layout(h->n_b64, svtme_exported_pu_count(&jobs[i].params), jobs[i].params, wants_deep(jobs[i].out)).end;
+    if (total > h->ob.bytes) return fail(SVTME_ERR_INVALID, "svtme_fetch_results: does not match the last launch");
+    CU(cudaMemcpyAsync(h->ob.host, h->ob.dev, total, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+    size_t off = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        const SvtMeJob &j = jobs[i];
+        const uint32_t n_pu = svtme_exported_pu_count(&j.params), nb = h->n_b64;
+        const bool deep = wants_deep(j.out);
+        const OutLayout L = out_layout(nb, n_pu, j.params, deep);
+        const uint8_t *b = h->ob.host + off;
+#define CP(dst, o, bytes) if (j.out.dst) memcpy(j.out.dst, b + (o), (bytes))
+        CP(total_me_candidate_index, L.total, (size_t)nb * n_pu);
+        CP(me_mv_array, L.mv, (size_t)nb * n_pu * j.params.max_refs * 4);
+        CP(me_candidate_array, L.cand, (size_t)nb * n_pu * j.params.max_cand);
+        CP(me_64x64_distortion, L.d64, (size_t)nb * 4); CP(me_32x32_distortion, L.d32, (size_t)nb * 4);
+        CP(me_16x16_distortion, L.d16, (size_t)nb * 4); CP(me_8x8_distortion, L.d8, (size_t)nb * 4);
+        CP(me_8x8_cost_variance, L.var8, (size_t)nb * 4); CP(rc_me_distortion, L.rc, (size_t)nb * 4);
+        CP(stationary_block_present_sb, L.stat, nb); CP(rc_me_allow_gm, L.gm, nb);
+        if (deep) {
+            CP(p_sb_best_sad, L.bsad, (size_t)nb * 2 * 4 * 85 * 4); CP(p_sb_best_mv, L.bmv, (size_t)nb * 2 * 4 * 85 * 4);
+            CP(hme_sc, L.sc, (size_t)nb * 2 * 4 * 2 * 2); CP(hme_sad, L.hsad, (size_t)nb * 2 * 4 * 8); CP(do_ref, L.doref, (size_t)nb * 2 * 4);
+        }
+#undef CP
+        off += L.end;
+    }
+    return SVTME_OK;
+}
+
+extern "C" int svtme_run_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n) {
+    int rc = svtme_launch_pictures(h, jobs, n);
+    if (rc) return rc;
+    return svtme_fetch_results(h, jobs, n);
+}
+
+extern "C" int svtme_run_picture(SvtMeHandle *h, const SvtMeParams *params, uint64_t cur,
+                                 const uint64_t refs[SVTME_MAX_LISTS][SVTME_MAX_REFS], SvtMeOut *out) {
+    if (!params || !refs || !out) return fail(SVTME_ERR_INVALID, "svtme_run_picture: null argument");
+    SvtMeJob j;
+    memset(&j, 0, sizeof(j));
+    j.params = *params;
+    j.cur = cur;
+    memcpy(j.refs, refs, sizeof(j.refs));
+    j.out = *out;
+    return svtme_run_pictures(h, &j, 1);
+}
+
+extern "C" float svtme_last_kernel_ms(SvtMeHandle *h) { return h ? h->last_ms : 0.f; }

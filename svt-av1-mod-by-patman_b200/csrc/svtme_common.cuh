@@ -1,0 +1,73 @@
+// svtme_common.cuh — device-side data contracts of the B200 open-loop ME path (sm_100a).
+//
+// HBM layout of one resident source picture ("pyramid", the device twin of EbPaReferenceObject,
+// Source/Lib/Codec/reference_object.h:73-89): three 8-bit planes, each with replicate padding on
+// all sides, rows 128-byte aligned so that a 64x64 block row / 16-byte search-window chunk is a
+// single aligned vector load:
+//     level 0 full      org (128, 72)  stride = up128(W   + 256)
+//     level 1 quarter   org ( 64, 32)  stride = up128(W/2 + 128)
+//     level 2 sixteenth org ( 32, 16)  stride = up128(W/4 +  64)
+// The pads are at least the reference's (72/32/16, enc_handle.c:1276-1311,4082-4094); the LOGICAL
+// search limits (63 / 31 / 15 px, motion_estimation.c:838-839,942-943,1043-1044,1257-1258) are
+// parameters of the clipping code, not of this layout, so results do not depend on it.
+#pragma once
+#include <stdint.h>
+#include <cuda_runtime.h>
+#include "svtme_b200.h"
+
+#define SVTME_NL SVTME_MAX_LISTS
+#define SVTME_NR SVTME_MAX_REFS
+
+struct DevPlane {
+    uint8_t *base;   // first byte of the allocation (row 0 of the top pad)
+    int stride;      // bytes per row
+    int org_x, org_y;
+    int width, height;
+    __host__ __device__ const uint8_t *at(int x, int y) const {
+        return base + (size_t)(org_y + y) * stride + org_x + x;
+    }
+};
+
+struct DevPyramid {
+    DevPlane lvl[3];
+};
+
+// One picture's ME job as the stage kernel sees it (array in device memory, one per picture).
+struct DevJob {
+    SvtMeParams prm;
+    DevPyramid cur;
+    DevPyramid ref[SVTME_NL][SVTME_NR];
+    int width, height;      // aligned luma size
+    int b64_cols, b64_rows; // ceil(width/64), ceil(height/64)
+    int n_pu;               // exported PU count (85/21/5)
+    // outputs (device), layouts of SvtMeOut
+    uint8_t *total;
+    uint32_t *mv;
+    uint8_t *cand;
+    uint32_t *dist64, *dist32, *dist16, *dist8, *var8, *rc_dist;
+    uint8_t *stationary, *allow_gm;
+    uint32_t *best_sad, *best_mv; // deep state, may be null
+    int16_t *hme_sc;
+    unsigned long long *hme_sad;
+    uint8_t *do_ref;
+};
+
+static inline int up128(int v) { return (v + 127) & ~127; }
+
+// kernels (svtme_pyramid.cu)
+void svtme_launch_pad_plane(const DevPlane &pl, int pad_l, int pad_r, int pad_t, int pad_b, cudaStream_t st);
+void svtme_launch_downsample(const DevPlane &full, const DevPlane &quarter, const DevPlane &sixteenth,
+                             int hme_level1, cudaStream_t st);
+void svtme_launch_downsample_generic(const uint8_t *in, int in_stride, int w, int h, uint8_t *out, int out_stride,
+                                     int step, cudaStream_t st);
+// stage kernel (svtme_stage.cu)
+void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, cudaStream_t st);
+int svtme_stage_smem_bytes();
+// kernel-test entry points (svtme_stage.cu)
+void svtme_launch_sad_loop_test(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride,
+                                int block_height, int block_width, int ref_row_step_raw, int skip_line, int sa_w,
+                                int sa_h, unsigned long long *d_key, cudaStream_t st);
+void svtme_launch_fullpel_test(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride, int ox,
+                               int oy, int sa_w, int sa_h, int sub_sad, uint32_t *d_best_sad, uint32_t *d_best_mv,
+                               cudaStream_t st);
+extern unsigned long long g_svtme_launches;

@@ -1,0 +1,159 @@
+// svtme_pyramid.cu — pre-ME pyramid on the device (sm_100a).
+//
+// Replaces, bit-exactly:
+//   svt_aom_generate_padding                    Source/Lib/Codec/pic_operators.c:338-382
+//   svt_aom_downsample_2d_c                     Source/Lib/Codec/pic_analysis_process.c:131-161
+//   svt_aom_downsample_filtering_input_picture  Source/Lib/Codec/pic_analysis_process.c:1922-1979
+//
+// HBM-bound byte work: algorithmic traffic per picture = W*H read + 5/16 W*H written (+ pads).
+// One thread owns a 16x4 full-resolution patch (one 16-byte load per row, fully coalesced across
+// the warp), produces the 8x2 quarter pixels and the 4x1 sixteenth pixels from registers, so the
+// quarter plane is never re-read. Padding is "pixel = interior(clamp(x), clamp(y))", which is what
+// the reference's horizontal-then-vertical replicate produces.
+#include "svtme_common.cuh"
+
+unsigned long long g_svtme_launches = 0;
+
+// ------------------------------------------------------------------ padding
+// One thread per pad byte. Pad region = top band, bottom band, left/right bands of interior rows.
+__global__ void __launch_bounds__(256) pad_plane_kernel(uint8_t *org, int stride, int W, int H, int pl, int pr,
+                                                         int pt, int pb) {
+    const long long full_w = (long long)pl + W + pr;
+    const long long n_top = full_w * pt, n_bot = full_w * pb, n_side = (long long)(pl + pr) * H;
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    int x, y;
+    if (i < n_top) {
+        y = -pt + (int)(i / full_w);
+        x = -pl + (int)(i % full_w);
+    } else if ((i -= n_top) < n_bot) {
+        y = H + (int)(i / full_w);
+        x = -pl + (int)(i % full_w);
+    } else if ((i -= n_bot) < n_side) {
+        y = (int)(i / (pl + pr));
+        int k = (int)(i % (pl + pr));
+        x = k < pl ? -pl + k : W + (k - pl);
+    } else
+        return;
+    const int sx = min(max(x, 0), W - 1), sy = min(max(y, 0), H - 1);
+    org[(long long)y * stride + x] = org[(long long)sy * stride + sx];
+}
+
+void svtme_launch_pad_plane(const DevPlane &p, int pl, int pr, int pt, int pb, cudaStream_t st) {
+    const long long full_w = (long long)pl + p.width + pr;
+    const long long n = full_w * (pt + pb) + (long long)(pl + pr) * p.height;
+    if (n <= 0) return;
+    uint8_t *org = p.base + (size_t)p.org_y * p.stride + p.org_x;
+    pad_plane_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(org, p.stride, p.width, p.height, pl, pr, pt, pb);
+    ++g_svtme_launches;
+}
+
+// ------------------------------------------------------------------ fused 1/4 + 1/16 decimation
+__device__ __forceinline__ uint32_t avg4(uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    return (a + b + c + d + 2) >> 2;
+}
+
+// Horizontal pair sums of the 4 bytes of a word: returns (b0+b1) | (b2+b3) << 16.
+__device__ __forceinline__ uint32_t hpair(uint32_t w) { return (w & 0x00ff00ffu) + ((w >> 8) & 0x00ff00ffu); }
+
+// 2x2 box of two rows of 4 pixels each -> 2 output pixels (low 16 bits: out0, high: out1).
+__device__ __forceinline__ uint32_t box2(uint32_t top, uint32_t bot) {
+    uint32_t s = hpair(top) + hpair(bot) + 0x00020002u;
+    return (s >> 2) & 0x00ff00ffu;
+}
+
+// full(16x4 patch) -> quarter(8x2) -> sixteenth(4x1). W, H multiples of 8.
+// level1_on == 0: sixteenth comes straight from the full plane with decimation step 4 (the 2x2 at
+// rows {1,2}, cols {1,2} of each 4x4), pic_analysis_process.c:1958-1969.
+__global__ void __launch_bounds__(256)
+    downsample_fused_kernel(const uint8_t *__restrict__ f0, int fs, int W, int H, uint8_t *__restrict__ q0, int qs,
+                            uint8_t *__restrict__ s0, int ss, int level1_on) {
+    const int px = blockIdx.x * blockDim.x + threadIdx.x; // 16-pixel column group
+    const int py = blockIdx.y * blockDim.y + threadIdx.y; // 4-row group
+    const int x0 = px * 16, y0 = py * 4;
+    if (x0 >= W || y0 >= H) return;
+    const bool wide = (x0 + 16 <= W); // else 8 valid pixels (W % 8 == 0)
+    uint32_t r[4][4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const uint8_t *row = f0 + (size_t)(y0 + k) * fs + x0;
+        if (wide) {
+            uint4 v = *reinterpret_cast<const uint4 *>(row);
+            r[k][0] = v.x; r[k][1] = v.y; r[k][2] = v.z; r[k][3] = v.w;
+        } else {
+            uint2 v = *reinterpret_cast<const uint2 *>(row);
+            r[k][0] = v.x; r[k][1] = v.y; r[k][2] = 0; r[k][3] = 0;
+        }
+    }
+    // quarter rows 0,1: 8 pixels each, packed 2 per box2 result
+    uint32_t q[2][2]; // q[row][word] bytes = 4 quarter pixels
+#pragma unroll
+    for (int qr = 0; qr < 2; ++qr) {
+        uint32_t b0 = box2(r[2 * qr][0], r[2 * qr + 1][0]); // px 0,1
+        uint32_t b1 = box2(r[2 * qr][1], r[2 * qr + 1][1]); // px 2,3
+        uint32_t b2 = box2(r[2 * qr][2], r[2 * qr + 1][2]);
+        uint32_t b3 = box2(r[2 * qr][3], r[2 * qr + 1][3]);
+        q[qr][0] = (b0 & 0xff) | ((b0 >> 16) << 8) | ((b1 & 0xff) << 16) | ((b1 >> 16) << 24);
+        q[qr][1] = (b2 & 0xff) | ((b2 >> 16) << 8) | ((b3 & 0xff) << 16) | ((b3 >> 16) << 24);
+    }
+    if (level1_on) {
+        uint8_t *qrow = q0 + (size_t)(y0 >> 1) * qs + (x0 >> 1);
+        if (wide) {
+            *reinterpret_cast<uint2 *>(qrow) = make_uint2(q[0][0], q[0][1]);
+            *reinterpret_cast<uint2 *>(qrow + qs) = make_uint2(q[1][0], q[1][1]);
+        } else {
+            *reinterpret_cast<uint32_t *>(qrow) = q[0][0];
+            *reinterpret_cast<uint32_t *>(qrow + qs) = q[1][0];
+        }
+    }
+    uint32_t s4;
+    if (level1_on) {
+        uint32_t a = box2(q[0][0], q[1][0]), b = box2(q[0][1], q[1][1]);
+        s4 = (a & 0xff) | ((a >> 16) << 8) | ((b & 0xff) << 16) | ((b >> 16) << 24);
+    } else {
+        s4 = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { // 4x4 group k: rows 1,2 cols 1,2 -> bytes 1,2 of word k
+            uint32_t t = r[1][k], u = r[2][k];
+            uint32_t v = avg4((t >> 8) & 0xff, (t >> 16) & 0xff, (u >> 8) & 0xff, (u >> 16) & 0xff);
+            s4 |= v << (8 * k);
+        }
+    }
+    uint8_t *srow = s0 + (size_t)(y0 >> 2) * ss + (x0 >> 2);
+    if (wide)
+        *reinterpret_cast<uint32_t *>(srow) = s4;
+    else
+        *reinterpret_cast<uint16_t *>(srow) = (uint16_t)s4;
+}
+
+void svtme_launch_downsample(const DevPlane &f, const DevPlane &q, const DevPlane &s, int hme_level1,
+                             cudaStream_t st) {
+    dim3 blk(32, 8);
+    dim3 grd((f.width + 16 * 32 - 1) / (16 * 32), (f.height + 4 * 8 - 1) / (4 * 8));
+    downsample_fused_kernel<<<grd, blk, 0, st>>>(f.at(0, 0), f.stride, f.width, f.height,
+                                                 const_cast<uint8_t *>(q.at(0, 0)), q.stride,
+                                                 const_cast<uint8_t *>(s.at(0, 0)), s.stride, hme_level1);
+    ++g_svtme_launches;
+}
+
+// Generic svt_aom_downsample_2d (any size / step 2,4,8): one thread per output pixel.
+// Kernel-test ABI only (PictureOperatorTest.cc:225-335 shapes).
+__global__ void __launch_bounds__(256)
+    downsample_generic_kernel(const uint8_t *__restrict__ in, int is, int w, int h, uint8_t *__restrict__ out, int os,
+                              int step) {
+    const int ox = blockIdx.x * blockDim.x + threadIdx.x, oy = blockIdx.y * blockDim.y + threadIdx.y;
+    const int half = step >> 1;
+    const int hx = half + ox * step, vy = half + oy * step;
+    if (hx >= w || vy >= h) return;
+    const uint8_t *lo = in + (size_t)vy * is, *hi = lo - is;
+    out[(size_t)oy * os + ox] = (uint8_t)avg4(hi[hx - 1], hi[hx], lo[hx - 1], lo[hx]);
+}
+
+void svtme_launch_downsample_generic(const uint8_t *in, int is, int w, int h, uint8_t *out, int os, int step,
+                                     cudaStream_t st) {
+    const int half = step >> 1;
+    const int ow = w > half ? (w - half + step - 1) / step : 0, oh = h > half ? (h - half + step - 1) / step : 0;
+    if (ow <= 0 || oh <= 0) return;
+    dim3 blk(32, 8), grd((ow + 31) / 32, (oh + 7) / 8);
+    downsample_generic_kernel<<<grd, blk, 0, st>>>(in, is, w, h, out, os, step);
+    ++g_svtme_launches;
+}

@@ -1,0 +1,115 @@
+"""Host-side mirror of the reference's interface for the open-loop ME path.
+
+The product is the C ABI (include/svtme_b200.h, csrc/libsvtme_b200.so); this module only wraps it
+for Python callers (tests, bench): numpy arrays in, numpy arrays out, errors raised. It never
+computes pixels itself and has no CPU fallback: without the CUDA library it raises.
+
+Reference interface mirrored: the PAME branch of svt_aom_motion_estimation_kernel
+(Source/Lib/Codec/me_process.c:126-313) -> MeSession.run_picture(s);
+svt_aom_downsample_filtering_input_picture (pic_analysis_process.c:1922) -> MeSession.put_picture.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import abi
+
+
+class SvtMeError(RuntimeError):
+    pass
+
+
+def _check(rc, lib):
+    if rc != 0:
+        raise SvtMeError("svtme error %d: %s" % (rc, lib.svtme_last_error().decode()))
+
+
+def launch_count():
+    return int(abi.load_library().svtme_launch_count())
+
+
+class MeSession:
+    """One handle = one GPU (one process per GPU when sharding pictures across GPUs)."""
+
+    def __init__(self, device, width, height, capacity=16):
+        self.lib = abi.load_library()
+        self.h = C.c_void_p()
+        self.width, self.height = width, height
+        _check(self.lib.svtme_open(device, width, height, capacity, C.byref(self.h)), self.lib)
+        self.n_b64 = int(self.lib.svtme_b64_count(self.h))
+
+    def close(self):
+        if self.h:
+            self.lib.svtme_close(self.h)
+            self.h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def derive_params(self, derive_input):
+        p = abi.SvtMeParams()
+        _check(self.lib.svtme_derive_params(C.byref(derive_input), C.byref(p)), self.lib)
+        return p
+
+    def put_picture(self, pic_num, luma):
+        luma = np.ascontiguousarray(luma, dtype=np.uint8)
+        assert luma.shape == (self.height, self.width)
+        _check(self.lib.svtme_put_picture(self.h, pic_num, luma.ctypes.data, luma.strides[0]), self.lib)
+
+    def put_picture_device(self, pic_num, dev_ptr, stride):
+        _check(self.lib.svtme_put_picture_device(self.h, pic_num, dev_ptr, stride), self.lib)
+
+    def release_picture(self, pic_num):
+        _check(self.lib.svtme_release_picture(self.h, pic_num), self.lib)
+
+    def get_plane(self, pic_num, level, pad=None):
+        pad = (72, 32, 16)[level] if pad is None else pad
+        w, h = self.width >> level, self.height >> level
+        out = np.zeros((h + 2 * pad, w + 2 * pad), dtype=np.uint8)
+        _check(self.lib.svtme_get_plane(self.h, pic_num, level, out.ctypes.data, out.strides[0], pad), self.lib)
+        return out
+
+    def plane_device_ptr(self, pic_num, level):
+        ptr, n = C.c_void_p(), C.c_size_t()
+        _check(self.lib.svtme_plane_device_ptr(self.h, pic_num, level, C.byref(ptr), C.byref(n)), self.lib)
+        return ptr.value, n.value
+
+    def adopt_picture(self, pic_num):
+        _check(self.lib.svtme_adopt_picture(self.h, pic_num), self.lib)
+
+    def make_jobs(self, specs, deep=False):
+        """specs: list of (params, cur, {(list, idx): pic_num}). Returns (SvtMeJob array, [arrays])."""
+        jobs = (abi.SvtMeJob * len(specs))()
+        outs = []
+        for i, (p, cur, refs) in enumerate(specs):
+            jobs[i].params = p
+            jobs[i].cur = cur
+            for (li, ri), n in refs.items():
+                jobs[i].refs[li][ri] = n
+            out, arrays = abi.alloc_out(self.n_b64, p, deep=deep)
+            jobs[i].out = out
+            outs.append(arrays)
+        return jobs, outs
+
+    def run_jobs(self, jobs):
+        _check(self.lib.svtme_run_pictures(self.h, jobs, len(jobs)), self.lib)
+
+    def launch_jobs(self, jobs):
+        _check(self.lib.svtme_launch_pictures(self.h, jobs, len(jobs)), self.lib)
+
+    def fetch_jobs(self, jobs):
+        _check(self.lib.svtme_fetch_results(self.h, jobs, len(jobs)), self.lib)
+
+    def sync(self):
+        _check(self.lib.svtme_sync(self.h), self.lib)
+
+    def last_kernel_ms(self):
+        return float(self.lib.svtme_last_kernel_ms(self.h))
+
+    def run_picture(self, params, cur, refs, deep=False):
+        jobs, outs = self.make_jobs([(params, cur, refs)], deep=deep)
+        self.run_jobs(jobs)
+        return outs[0]

@@ -1,0 +1,295 @@
+#!/usr/bin/env python
+"""bench.py — open-loop ME throughput (SBs/sec, frames/sec) of the B200 path, the driver contract.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload 1080p_p8|4k_p4] [--impl reference]
+
+One "step" = one pass of the hot path over one batch of synthetic input: the pre-ME pyramid of all
+frames of the sequence + the open-loop ME (pre-HME, HME L0-L2, full-pel 85-PU search, candidate
+arrays) of every non-intra picture against its references.
+  value  : SBs/s with the raw luma frames already resident in HBM (device-timed, CUDA events)
+  e2e    : same metric through the public C ABI with HOST buffers: per step every frame is copied
+           H2D from pinned memory and every result table is copied back D2H, inside the timed region
+  N > 1  : one process per GPU; rank r owns its own independent stream (weak scaling, no data-path
+           collective); time = max over ranks.
+--impl reference times the reference's own CPU implementation of the same path (oracle/_ref: the
+unmodified reference sources with its AVX2 kernels; the oracle port if that library is absent) on
+all host threads, on a bounded sample of the same workload.
+"""
+import argparse
+import ctypes as C
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+PKG = "svt-av1-mod-by-patman_b200"
+
+WORKLOADS = {
+    # configs[1] of BASELINE.json: 1080p 8-bit, preset 8, 60 frames, refs 3+2 (mrp 9), 5 hierarchical levels
+    "1080p_p8": dict(width=1920, height=1080, preset=8, frames=60, levels=5, n_l0=3, n_l1=2),
+    # configs[2]: 4K (the ME stage sees the 8 MSBs of 10-bit input), preset 4, 120 frames, refs 4+3
+    "4k_p4": dict(width=3840, height=2160, preset=4, frames=120, levels=5, n_l0=4, n_l1=3),
+    "small": dict(width=640, height=360, preset=8, frames=12, levels=3, n_l0=2, n_l1=1),
+}
+
+
+def build_specs(abi, gop, wl, derive_fn):
+    """(params, cur, refs) per non-intra picture, decode order."""
+    U = importlib.import_module(PKG + ".me")
+    specs = []
+    for j in gop.ra_jobs(wl["frames"], wl["levels"], wl["n_l0"], wl["n_l1"]):
+        d = U.derive_input(wl["preset"], wl["width"], wl["height"], hierarchical_levels=wl["levels"],
+                           temporal_layer_index=j.temporal_layer, is_ref=int(j.is_ref), ref_list0_count_try=j.n_l0,
+                           ref_list1_count_try=j.n_l1, ref_count_used_list0=wl["n_l0"], ref_count_used_list1=wl["n_l1"])
+        p = derive_fn(d)
+        U.finish_params(p, d, j.picture_number, j.refs)
+        specs.append((p, j.picture_number, j.refs))
+    return specs
+
+
+class ClockSampler(threading.Thread):
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+            "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": int(self.rows[0][1]) if self.rows[0][1].isdigit() else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def cpu_reference_run(wl, specs, seq, n_pictures, threads, min_seconds=10.0):
+    """ME of the first n_pictures jobs on the host: compiled reference (AVX2) if present, else the
+    oracle port. b64 rows are spread over `threads` host threads (ctypes releases the GIL)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import _util as U  # oracle drivers: CPU-baseline leg only
+    ref = U.ref_lib()
+    which, kind = ("ref", "reference") if ref is not None else ("orc", "port")
+    simd = ref.ref_set_simd(1) if ref is not None else 0
+    lib = ref if ref is not None else U.oracle_lib()
+    jobs = specs[:n_pictures]
+    need = set()
+    for p, cur, refs in jobs:
+        need.add(cur)
+        need.update(refs.values())
+    t0 = time.perf_counter()
+    pyr = {n: U.CpuPyramid(which, seq[n], n) for n in sorted(need)}
+    t_pyr = time.perf_counter() - t0
+    n_rows = (wl["height"] + 63) // 64
+    t0 = time.perf_counter()
+    reps = 0
+    while True:
+        for p, cur, refs in jobs:
+            chunks = [(r * n_rows // threads, (r + 1) * n_rows // threads) for r in range(threads)]
+            ths = [threading.Thread(target=U.cpu_me_picture, args=(which, p, pyr[cur], {k: pyr[v] for k, v in refs.items()}),
+                                    kwargs=dict(deep=False, rows=c)) for c in chunks if c[1] > c[0]]
+            for t in ths:
+                t.start()
+            for t in ths:
+                t.join()
+        reps += 1
+        if time.perf_counter() - t0 >= min_seconds:
+            break
+    t_me = (time.perf_counter() - t0) / reps
+    n_b64 = ((wl["width"] + 63) // 64) * n_rows
+    # pyramid cost is charged per ME'd picture like on the GPU side (one pyramid per frame)
+    per_pic = t_me / len(jobs) + t_pyr / len(pyr)
+    return dict(sbs_per_s=n_b64 / per_pic, fps=1.0 / per_pic, kind=kind, simd="avx2" if simd else "c",
+                seconds=t_me * reps + t_pyr, pictures=len(jobs), reps=reps)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="1080p_p8", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--cpu-pictures", type=int, default=16, help="pictures in the bounded CPU sample")
+    ap.add_argument("--cpu-seconds", type=float, default=10.0, help="repeat the CPU sample for about this long")
+    args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    W, H, F = wl["width"], wl["height"], wl["frames"]
+    n_b64 = ((W + 63) // 64) * ((H + 63) // 64)
+    config = {"workload": "%s: %dx%d 8-bit luma, preset %d, %d frames, refs %d+%d, %d hierarchical levels, synthetic "
+                          "translating texture + moving rectangles + noise" % (args.workload, W, H, wl["preset"], F, wl["n_l0"],
+                                                                             wl["n_l1"], wl["levels"]),
+              "b64_per_frame": n_b64, "me_pictures_per_step": F - 1, "pyramids_per_step": F,
+              "l2": "inputs larger than L2: each step touches %.0f MB of frames+pyramids (L2 126 MB)" % (F * W * H * 2.7 / 1e6),
+              "sharding": "one independent stream per GPU (weak)"}
+    abi = importlib.import_module(PKG + ".abi")
+    gop = importlib.import_module(PKG + ".gop")
+    synth = importlib.import_module(PKG + ".synth")
+    threads = os.cpu_count() or 1
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        # parameters from the product's host-side derivation (validated == reference's in tests)
+        lib = abi.load_library()
+
+        def derive(d):
+            p = abi.SvtMeParams()
+            assert lib.svtme_derive_params(C.byref(d), C.byref(p)) == 0
+            return p
+        specs = build_specs(abi, gop, wl, derive)
+        seq = synth.synth_sequence(W, H, F, seed=1)
+        res = None
+        times = []
+        for i in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            res = cpu_reference_run(wl, specs, seq, args.cpu_pictures, threads, args.cpu_seconds)
+            if i >= args.warmup:
+                times.append((time.perf_counter() - t0, res["sbs_per_s"]))
+        val = float(np.mean([v for _, v in times])) if times else res["sbs_per_s"]
+        line = {"impl": "reference", "metric": "open-loop ME SBs/sec", "value": val, "unit": "SB/s", "n_gpus": args.gpus,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean([t for t, _ in times])) if times else None,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": config,
+                "frames_per_s": val / n_b64,
+                "cpu_baseline": {"value": val, "unit": "SB/s", "cores": threads, "kind": res["kind"],
+                                 "sample": "first %d ME pictures (+ their pyramids) of the workload, repeated %dx (%.1f s), %s kernels, %d threads over b64 rows"
+                                           % (res["pictures"], res["reps"], res["seconds"], res["simd"], threads)},
+                "e2e": {"value": val, "unit": "SB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    if world > 1:
+        dist.init_process_group("nccl", rank=rank, world_size=world)
+    torch.cuda.set_device(local_rank)
+    me = importlib.import_module(PKG + ".me")
+    seq = synth.synth_sequence(W, H, F, seed=1 + rank)
+    host = torch.from_numpy(seq).pin_memory()
+    dev = host.to("cuda", non_blocking=False)
+    ses = me.MeSession(local_rank, W, H, capacity=F)
+    stream = torch.cuda.Stream()  # a non-default stream: the library treats NULL as "use the private stream"
+    torch.cuda.set_stream(stream)
+    ses.set_stream(stream.cuda_stream)
+    specs = build_specs(abi, gop, wl, ses.derive_params)
+    jobs, outs = ses.make_jobs(specs, deep=False)
+    frame_bytes = W * H
+    d2h_bytes = sum(a.nbytes for o in outs for a in o.values())
+
+    def step_resident():
+        for f in range(F):
+            ses.put_picture_device(f, dev.data_ptr() + f * frame_bytes, W)
+        ses.launch_jobs(jobs)
+
+    def step_e2e():
+        for f in range(F):
+            ses.lib.svtme_put_picture(ses.h, f, host.data_ptr() + f * frame_bytes, W)
+        ses.run_jobs(jobs)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    for _ in range(max(3, args.warmup)):
+        step_resident()
+    torch.cuda.synchronize()
+    launches0 = me.launch_count()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ms_total = timed(step_resident, args.steps)
+    launches = me.launch_count() - launches0
+    # dominant kernel: the stage kernel of the last step (CUDA events inside the library, same stream)
+    work_ops = ses.last_work_ops()
+    kernel_ms = ses.last_kernel_ms()
+    for _ in range(max(1, args.warmup)):
+        step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+    ms_step = ms_total / args.steps
+    sbs_step = (F - 1) * n_b64
+    value = world * sbs_step / (ms_step * 1e-3)
+    e2e_val = world * sbs_step / (ms_e2e / args.steps * 1e-3)
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak, hbm_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback")
+        vsad = float(ses.lib.svtme_measure_vabsdiff4_ginst_per_s())
+        int_peak = vsad * 4 / 1e3  # T byte-SAD/s
+        int_achieved = work_ops / (kernel_ms * 1e-3) / 1e12
+        # algorithmic HBM bytes of the stage kernel: every job reads its own pyramid and those of its
+        # distinct references once (1 + 1/4 + 1/16 bytes per pixel) and writes its result tables
+        alg_bytes = sum((1 + len(set(refs.values()))) * W * H * 1.3125 for _, _, refs in specs) + d2h_bytes
+        cpu = cpu_reference_run(wl, specs, seq, args.cpu_pictures, threads, args.cpu_seconds)
+        line = {"metric": "open-loop ME SBs/sec", "value": value, "unit": "SB/s", "n_gpus": world, "steps": args.steps,
+                "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": config,
+                "frames_per_s": world * F / (ms_step * 1e-3),
+                "e2e": {"value": e2e_val, "unit": "SB/s", "h2d_bytes_per_step": F * frame_bytes, "d2h_bytes_per_step": d2h_bytes,
+                        "frames_per_s": world * F / (ms_e2e / args.steps * 1e-3), "ms_per_step": ms_e2e / args.steps},
+                "gpu_launches": int(launches),
+                "roofline": {"bound": "int_alu", "kernel": "me_stage_kernel", "achieved": int_achieved, "peak": int_peak,
+                             "unit": "Tbyte-SAD/s", "frac": int_achieved / int_peak if int_peak else None, "traffic": None,
+                             "peak_source": "VABSDIFF4.U8.ACC issue rate measured live in this run (%.0f Ginst/s x 4 bytes)" % vsad,
+                             "work_byte_ops_per_launch": work_ops, "kernel_ms": kernel_ms,
+                             "kernel_share_of_step": kernel_ms / ms_step},
+                "roofline_hbm": {"bound": "hbm", "kernel": "me_stage_kernel", "achieved": alg_bytes / (kernel_ms * 1e-3) / 1e9,
+                                 "peak": hbm_peak, "unit": "GB/s", "frac": alg_bytes / (kernel_ms * 1e-3) / 1e9 / hbm_peak,
+                                 "traffic": None, "peak_source": hbm_src},
+                "cpu_baseline": {"value": cpu["sbs_per_s"], "unit": "SB/s", "cores": threads, "kind": cpu["kind"],
+                                 "frames_per_s": cpu["fps"],
+                                 "sample": "first %d ME pictures (+ pyramids) of the same workload, repeated %dx (%.1f s), %s kernels, %d threads over b64 rows"
+                                           % (cpu["pictures"], cpu["reps"], cpu["seconds"], cpu["simd"], threads)},
+                "clocks": sampler.summary()}
+        print(json.dumps(line))
+    ses.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

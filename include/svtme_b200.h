@@ -215,6 +215,19 @@ int svtme_sync(SvtMeHandle *h);
  * the number of kernels this library has launched so far. */
 float svtme_last_kernel_ms(SvtMeHandle *h);
 uint64_t svtme_launch_count(void);
+/* Run the handle's work on a caller-owned CUDA stream (cudaStream_t passed as void*); NULL = private stream. */
+int svtme_set_stream(SvtMeHandle *h, void *cuda_stream);
+/* Algorithmic SAD byte-ops (search positions x block pixels compared) executed by the stage kernel in
+ * the last svtme_launch_pictures call: the numerator of the integer-SAD roofline. Synchronises. */
+int svtme_last_work_ops(SvtMeHandle *h, uint64_t *ops);
+/* Measured issue rate (Ginst/s, whole GPU) of VABSDIFF4.U8.ACC, 4 byte-SADs per instruction: the
+ * integer-SAD roofline denominator (not part of MEASURED_PEAKS.json). */
+double svtme_measure_vabsdiff4_ginst_per_s(void);
+/* sizeof() of the ABI structs as compiled into the library (layout check for FFI bindings). */
+uint32_t svtme_sizeof_params(void);
+uint32_t svtme_sizeof_out(void);
+uint32_t svtme_sizeof_job(void);
+uint32_t svtme_sizeof_derive_input(void);
 
 /* ---------------- kernel-test ABI: RTCD signatures (aom_dsp_rtcd.h) ---------------- */
 

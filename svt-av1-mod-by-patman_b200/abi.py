@@ -178,6 +178,9 @@ def load_library():
         "svtme_sync": (C.c_int, [vp]),
         "svtme_last_kernel_ms": (C.c_float, [vp]),
         "svtme_launch_count": (u64, []),
+        "svtme_set_stream": (C.c_int, [vp, vp]),
+        "svtme_last_work_ops": (C.c_int, [vp, P(u64)]),
+        "svtme_measure_vabsdiff4_ginst_per_s": (C.c_double, []),
         "svtme_sizeof_params": (u32, []),
         "svtme_sizeof_out": (u32, []),
         "svtme_sizeof_job": (u32, []),

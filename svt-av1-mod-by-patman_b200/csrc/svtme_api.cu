@@ -47,6 +47,8 @@ struct SvtMeHandle {
     int device;
     uint32_t width, height, b64_cols, b64_rows, n_b64;
     cudaStream_t stream;
+    bool own_stream;
+    std::vector<size_t> work_off; // offsets of the per-job work counters of the last launch
     uint8_t *pool; // all planes of all slots
     size_t plane_bytes[3], slot_bytes;
     std::vector<Slot> slots;
@@ -107,6 +109,7 @@ extern "C" int svtme_open(int device, uint32_t width, uint32_t height, uint32_t 
     if (e != cudaSuccess) { delete h; return fail(SVTME_ERR_NOMEM, "svtme_open: cudaMalloc pyramid pool", e); }
     e = cudaMemset(h->pool, 0, h->slot_bytes * capacity);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    h->own_stream = true;
     if (e == cudaSuccess) e = cudaMallocHost(&h->stage_host, (size_t)width * height);
     if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
     if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
@@ -137,7 +140,7 @@ extern "C" void svtme_close(SvtMeHandle *h) {
     cudaFreeHost(h->ob.host);
     cudaEventDestroy(h->ev0);
     cudaEventDestroy(h->ev1);
-    cudaStreamDestroy(h->stream);
+    if (h->own_stream) cudaStreamDestroy(h->stream);
     delete h;
 }
 
@@ -246,7 +249,7 @@ extern "C" int svtme_sync(SvtMeHandle *h) {
 
 // ---- result buffers: per job one packed record, same order on device and in the pinned mirror
 struct OutLayout {
-    size_t total, mv, cand, d64, d32, d16, d8, var8, rc, stat, gm, bsad, bmv, sc, hsad, doref, end;
+    size_t total, mv, cand, d64, d32, d16, d8, var8, rc, stat, gm, work, bsad, bmv, sc, hsad, doref, end;
 };
 static OutLayout out_layout(uint32_t n_b64, uint32_t n_pu, const SvtMeParams &p, bool deep) {
     OutLayout L;
@@ -258,6 +261,7 @@ static OutLayout out_layout(uint32_t n_b64, uint32_t n_pu, const SvtMeParams &p,
     L.d64 = take((size_t)n_b64 * 4); L.d32 = take((size_t)n_b64 * 4); L.d16 = take((size_t)n_b64 * 4);
     L.d8 = take((size_t)n_b64 * 4); L.var8 = take((size_t)n_b64 * 4); L.rc = take((size_t)n_b64 * 4);
     L.stat = take(n_b64); L.gm = take(n_b64);
+    L.work = take(8);
     if (deep) {
         L.bsad = take((size_t)n_b64 * 2 * 4 * 85 * 4); L.bmv = take((size_t)n_b64 * 2 * 4 * 85 * 4);
         L.sc = take((size_t)n_b64 * 2 * 4 * 2 * 2); L.hsad = take((size_t)n_b64 * 2 * 4 * 8); L.doref = take((size_t)n_b64 * 2 * 4);
@@ -306,6 +310,7 @@ extern "C" int svtme_launch_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint3
         h->ob.bytes = total;
     }
     size_t off = 0;
+    h->work_off.clear();
     for (uint32_t i = 0; i < n; ++i) {
         const SvtMeJob &j = jobs[i];
         DevJob &d = h->h_jobs[i];
@@ -334,10 +339,12 @@ extern "C" int svtme_launch_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint3
         d.dist64 = (uint32_t *)(b + L.d64); d.dist32 = (uint32_t *)(b + L.d32); d.dist16 = (uint32_t *)(b + L.d16);
         d.dist8 = (uint32_t *)(b + L.d8); d.var8 = (uint32_t *)(b + L.var8); d.rc_dist = (uint32_t *)(b + L.rc);
         d.stationary = b + L.stat; d.allow_gm = b + L.gm;
+        d.work_ops = (unsigned long long *)(b + L.work);
         if (deep) {
             d.best_sad = (uint32_t *)(b + L.bsad); d.best_mv = (uint32_t *)(b + L.bmv);
             d.hme_sc = (int16_t *)(b + L.sc); d.hme_sad = (unsigned long long *)(b + L.hsad); d.do_ref = b + L.doref;
         }
+        h->work_off.push_back(off + L.work);
         off += L.end;
     }
     // entries the stage never writes (pruned candidates) read as zero, like a fresh MeSbResults
@@ -405,3 +412,39 @@ extern "C" int svtme_run_picture(SvtMeHandle *h, const SvtMeParams *params, uint
 }
 
 extern "C" float svtme_last_kernel_ms(SvtMeHandle *h) { return h ? h->last_ms : 0.f; }
+
+// Run the handle's work on a caller-owned CUDA stream (e.g. torch's current stream, so that
+// torch.cuda.Event timing brackets these kernels). Pass NULL to return to the private stream.
+extern "C" int svtme_set_stream(SvtMeHandle *h, void *cuda_stream) {
+    if (!h) return fail(SVTME_ERR_INVALID, "svtme_set_stream: null handle");
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    if (h->own_stream) cudaStreamDestroy(h->stream);
+    if (cuda_stream) {
+        h->stream = (cudaStream_t)cuda_stream;
+        h->own_stream = false;
+    } else {
+        CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+        h->own_stream = true;
+    }
+    return SVTME_OK;
+}
+
+// Sum of the algorithmic SAD byte-ops (positions x block pixels actually compared) the stage
+// kernel executed in the last svtme_launch_pictures call. Synchronises the stream.
+extern "C" int svtme_last_work_ops(SvtMeHandle *h, uint64_t *ops) {
+    if (!h || !ops) return fail(SVTME_ERR_INVALID, "svtme_last_work_ops: bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    uint64_t sum = 0;
+    for (size_t o : h->work_off) {
+        unsigned long long v = 0;
+        CU(cudaMemcpy(&v, h->ob.dev + o, 8, cudaMemcpyDeviceToHost));
+        sum += v;
+    }
+    *ops = sum;
+    cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+    return SVTME_OK;
+}

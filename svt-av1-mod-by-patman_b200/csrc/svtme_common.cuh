@@ -50,6 +50,7 @@ struct DevJob {
     int16_t *hme_sc;
     unsigned long long *hme_sad;
     uint8_t *do_ref;
+    unsigned long long *work_ops; // algorithmic SAD byte-ops executed for this picture (roofline numerator)
 };
 
 static inline int up128(int v) { return (v + 127) & ~127; }

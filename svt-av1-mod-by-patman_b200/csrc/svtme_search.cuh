@@ -75,11 +75,11 @@ struct HJob {
 #define HME_KEY_INIT (0xffffffULL << 32)
 
 template <int G>
-__device__ __forceinline__ void hme_items(const HBlk &blk, const HJob &job, const uint8_t *arena, int copy_bytes, int m,
-                                          int y0, int bh, uint32_t *sadbuf, unsigned long long &best) {
+__device__ __forceinline__ void hme_items(const HBlk &blk, int sa_w, int skip_even, const uint8_t *arena, int copy_bytes,
+                                          int m, int x0, int y0, int bh, uint32_t *sadbuf, unsigned long long &best) {
     const int nbx = (blk.bw + 15) >> 4, nby = (blk.nrows + 7) >> 3, nb = nbx * nby;
     const int tile_w = 4 * G;
-    const int xt_n = (job.sa_w + tile_w - 1) / tile_w;
+    const int xt_n = (sa_w + tile_w - 1) / tile_w;
     const int n_items = bh * xt_n * 4 * nb;
     const bool masked = (blk.bw & 15) != 0;
     int cached_b = -1;
@@ -156,16 +156,16 @@ __device__ __forceinline__ void hme_items(const HBlk &blk, const HJob &job, cons
             }
         }
         const int yg = y0 + y;
-        if (job.skip_even && !(yg & 1)) continue;
+        if (skip_even && !(yg & 1)) continue;
 #pragma unroll
         for (int j = 0; j < G; ++j) {
             const int x = xt * tile_w + 4 * j + c;
-            if (x < job.sa_w) {
+            if (x < sa_w) {
                 if (nb == 1) {
-                    unsigned long long k = ((unsigned long long)acc[j] << 32) | ((unsigned)yg << 16) | (unsigned)x;
+                    unsigned long long k = ((unsigned long long)acc[j] << 32) | ((unsigned)yg << 16) | (unsigned)(x0 + x);
                     best = k < best ? k : best;
                 } else {
-                    atomicAdd(&sadbuf[y * job.sa_w + x], acc[j]);
+                    atomicAdd(&sadbuf[y * sa_w + x], acc[j]);
                 }
             }
         }
@@ -177,53 +177,56 @@ __device__ __forceinline__ void hme_items(const HBlk &blk, const HJob &job, cons
 __device__ void hme_search(const HBlk &blk, HJob *job, uint8_t *arena) {
     const int sa_w = job->sa_w, sa_h = job->sa_h;
     if (sa_w <= 0 || sa_h <= 0) return;
-    const int nb = ((blk.bw + 15) >> 4) * ((blk.nrows + 7) >> 3);
+    const int nbx = (blk.bw + 15) >> 4;
+    const int nb = nbx * ((blk.nrows + 7) >> 3);
     const int G = sa_w <= 8 ? 2 : (sa_w <= 16 ? 4 : 8);
     const int tile_w = 4 * G;
-    const int span = ((sa_w + tile_w - 1) / tile_w) * tile_w; // positions covered incl. masked ones
-    // bytes a copy row must hold: last word read = (span/4 - 1) + 4*(nbx-1) + (G+3 rounded to vector)
-    const int nbx = (blk.bw + 15) >> 4;
     const int vec_words = G == 2 ? 6 : ((G + 3 + 3) / 4) * 4;
-    const int words = (span / 4 - G) + 4 * (nbx - 1) + vec_words;
-    int m = (words + 3) / 4;
-    m |= 1; // odd chunk stride: consecutive rows start in different bank groups
     const int extra_rows = (blk.nrows - 1) * blk.row_step;
-    // band height: 4 copies of (bh + extra_rows) rows (+ per-position SAD buffer when nb > 1)
-    int bh = sa_h;
+    // Tile the search area so that 4 phase copies of (bh + extra_rows) rows x (wt + bw - 1) bytes
+    // (+ the per-position SAD buffer when the block spans several sub-blocks) fit the arena.
+    int wt = ((sa_w + tile_w - 1) / tile_w) * tile_w, bh = sa_h, m = 0;
     for (;;) {
-        int rows = bh + extra_rows;
-        int copy_chunks = rows * m;
+        const int words = (wt / 4 - G) + 4 * (nbx - 1) + vec_words;
+        m = ((words + 3) / 4) | 1; // odd chunk stride: consecutive rows start in different bank groups
+        int copy_chunks = (bh + extra_rows) * m;
         copy_chunks += (10 - (copy_chunks & 7)) & 7; // copy stride == 2 (mod 8) chunks
-        size_t need = (size_t)copy_chunks * 16 * 4 + (nb > 1 ? (size_t)bh * sa_w * 4 : 0);
-        if (need <= SVTME_ARENA_BYTES || bh == 1) break;
-        bh = max(1, bh / 2);
+        const size_t need = (size_t)copy_chunks * 16 * 4 + (nb > 1 ? (size_t)bh * wt * 4 : 0);
+        if (need <= SVTME_ARENA_BYTES) break;
+        if (bh > 8) bh = (bh + 1) / 2;
+        else if (wt > tile_w) { wt = ((wt / 2 + tile_w - 1) / tile_w) * tile_w; bh = sa_h; }
+        else if (bh > 1) bh = (bh + 1) / 2;
+        else break; // 1 row x one G-tile always fits (<= 64 rows x 9 chunks x 4 copies)
     }
     unsigned long long best = ~0ULL;
-    for (int y0 = 0; y0 < sa_h; y0 += bh) {
-        const int hb = min(bh, sa_h - y0);
-        const int rows = hb + extra_rows;
-        int copy_chunks = rows * m;
-        copy_chunks += (10 - (copy_chunks & 7)) & 7;
-        const int copy_bytes = copy_chunks * 16;
-        uint32_t *sadbuf = reinterpret_cast<uint32_t *>(arena + (size_t)copy_bytes * 4);
-        __syncthreads(); // previous users of the arena are done
-        stage_window4(arena, job->ref + (size_t)y0 * job->stride, job->stride, rows, m, 0, copy_bytes);
-        if (nb > 1)
-            for (int i = threadIdx.x; i < hb * sa_w; i += SVTME_THREADS) sadbuf[i] = 0;
-        __syncthreads();
-        if (G == 2)
-            hme_items<2>(blk, *job, arena, copy_bytes, m, y0, hb, sadbuf, best);
-        else if (G == 4)
-            hme_items<4>(blk, *job, arena, copy_bytes, m, y0, hb, sadbuf, best);
-        else
-            hme_items<8>(blk, *job, arena, copy_bytes, m, y0, hb, sadbuf, best);
-        if (nb > 1) {
+    for (int x0 = 0; x0 < sa_w; x0 += wt) {
+        const int wb = min(wt, sa_w - x0);
+        for (int y0 = 0; y0 < sa_h; y0 += bh) {
+            const int hb = min(bh, sa_h - y0);
+            const int rows = hb + extra_rows;
+            int copy_chunks = rows * m;
+            copy_chunks += (10 - (copy_chunks & 7)) & 7;
+            const int copy_bytes = copy_chunks * 16;
+            uint32_t *sadbuf = reinterpret_cast<uint32_t *>(arena + (size_t)copy_bytes * 4);
+            __syncthreads(); // previous users of the arena are done
+            stage_window4(arena, job->ref + (size_t)y0 * job->stride + x0, job->stride, rows, m, 0, copy_bytes);
+            if (nb > 1)
+                for (int i = threadIdx.x; i < hb * wb; i += SVTME_THREADS) sadbuf[i] = 0;
             __syncthreads();
-            for (int i = threadIdx.x; i < hb * sa_w; i += SVTME_THREADS) {
-                const int y = y0 + i / sa_w, x = i % sa_w;
-                if (job->skip_even && !(y & 1)) continue;
-                unsigned long long k = ((unsigned long long)sadbuf[i] << 32) | ((unsigned)y << 16) | (unsigned)x;
-                best = k < best ? k : best;
+            if (G == 2)
+                hme_items<2>(blk, wb, job->skip_even, arena, copy_bytes, m, x0, y0, hb, sadbuf, best);
+            else if (G == 4)
+                hme_items<4>(blk, wb, job->skip_even, arena, copy_bytes, m, x0, y0, hb, sadbuf, best);
+            else
+                hme_items<8>(blk, wb, job->skip_even, arena, copy_bytes, m, x0, y0, hb, sadbuf, best);
+            if (nb > 1) {
+                __syncthreads();
+                for (int i = threadIdx.x; i < hb * wb; i += SVTME_THREADS) {
+                    const int y = y0 + i / wb, x = x0 + i % wb;
+                    if (job->skip_even && !(y & 1)) continue;
+                    unsigned long long k = ((unsigned long long)sadbuf[i] << 32) | ((unsigned)y << 16) | (unsigned)x;
+                    best = k < best ? k : best;
+                }
             }
         }
     }

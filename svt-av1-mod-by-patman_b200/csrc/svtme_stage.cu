@@ -53,6 +53,7 @@ struct StageState {
     int fp_do, fp_sa_w, fp_sa_h, fp_ox, fp_oy, fp_probe;
     int16_t fp_xc, fp_yc;
     int c00_needed;
+    unsigned long long work_ops; // sum over executed searches of positions x block_w x rows
 };
 
 __device__ __forceinline__ int iabs(int v) { return v < 0 ? -v : v; }
@@ -852,6 +853,14 @@ int svtme_stage_smem_bytes() { return (int)sizeof(StageSmem); }
 __device__ void run_jobs(StageState *s, const HBlk &blk, uint8_t *arena) {
     const int n = s->n_jobs; // published by T0
     for (int j = 0; j < n; ++j) hme_search(blk, &s->jobs[j], arena);
+    if (threadIdx.x == 0) {
+        unsigned long long w = 0;
+        for (int j = 0; j < n; ++j) {
+            const int rows = s->jobs[j].skip_even ? s->jobs[j].sa_h / 2 : s->jobs[j].sa_h;
+            w += (unsigned long long)s->jobs[j].sa_w * rows * blk.bw * blk.nrows;
+        }
+        s->work_ops += w;
+    }
 }
 
 __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob *__restrict__ jobs, int b64_per_job) {
@@ -871,6 +880,7 @@ __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob
         s->pic_h = J.height;
         s->b64_w = min(64, J.width - org_x);
         s->b64_h = min(64, J.height - org_y);
+        s->work_ops = 0;
         init_state(s, p);
     }
     // source blocks -> shared memory (b64_src_ptr, quarter_b64_buffer, sixteenth_b64_buffer; me_process.c:189-213)
@@ -961,12 +971,14 @@ __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob
                 const int xc = s->fp_xc, yc = s->fp_yc;
                 fullpel_search(sm->src64, pl.at(org_x + xc, org_y + yc), pl.stride, xc, yc, 1, 1, sub_sad, 1, &s->tab,
                                sm->arena);
+                if (tid == 0) s->work_ops += 64ull * (sub_sad ? 32 : 64);
             }
             T0(plan_int_c(s, J));
             {
                 const int ox = s->fp_ox, oy = s->fp_oy;
                 fullpel_search(sm->src64, pl.at(org_x + ox, org_y + oy), pl.stride, ox, oy, s->fp_sa_w, s->fp_sa_h, sub_sad,
                                2, &s->tab, sm->arena);
+                if (tid == 0) s->work_ops += (unsigned long long)s->fp_sa_w * s->fp_sa_h * 64ull * (sub_sad ? 32 : 64);
             }
             if (tid < SVTME_PU_COUNT) {
                 s->best_sad[li][ri][tid] = (uint32_t)(s->tab.key[tid] >> 32);
@@ -983,7 +995,10 @@ __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob
     if (tid < p.max_number_of_pus_per_sb) construct_candidates(s, p, (uint32_t)tid, total, mvo, cando);
     __threadfence_block();
     __syncthreads();
-    if (tid == 0) finish_b64(s, J, b64, cando);
+    if (tid == 0) {
+        finish_b64(s, J, b64, cando);
+        if (J.work_ops) atomicAdd(J.work_ops, s->work_ops);
+    }
     // deep state for parity checks
     if (J.best_sad)
         for (int i = tid; i < NL * NR * SVTME_PU_COUNT; i += SVTME_THREADS) {

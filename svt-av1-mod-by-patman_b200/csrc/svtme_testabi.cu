@@ -336,3 +336,45 @@ extern "C" void svt_aom_generate_padding_b200(uint8_t *src_pic, uint32_t src_str
     CK(cudaGetLastError());
     CK(cudaMemcpy(src_pic, d.p, bytes, cudaMemcpyDeviceToHost));
 }
+
+// ---------------------------------------------------------------- integer-SAD roofline probe
+// Register-only VABSDIFF4.U8.ACC chains on every SM: the measured issue rate of the instruction the
+// search engines are built on (the roofline denominator MEASURED_PEAKS.json does not carry).
+__global__ void __launch_bounds__(256) vsad_rate_kernel(uint32_t *out, uint32_t seed, int iters) {
+    uint32_t a[8], acc[8];
+    const uint32_t b = seed * 0x9E3779B9u + threadIdx.x;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) { a[c] = b * (c + 1) + 12345u; acc[c] = c; }
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int c = 0; c < 8; ++c) asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %0;" : "+r"(acc[c]) : "r"(a[c]), "r"(b));
+    }
+    uint32_t s = 0;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) s += acc[c];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+extern "C" double svtme_measure_vabsdiff4_ginst_per_s(void) {
+    int dev = 0, sms = 0;
+    CK(cudaGetDevice(&dev));
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const int grid = sms * 8, iters = 4096;
+    DevBuf out((size_t)grid * 256 * 4);
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    float best = 1e30f;
+    for (int r = 0; r < 8; ++r) {
+        CK(cudaEventRecord(e0));
+        vsad_rate_kernel<<<grid, 256>>>((uint32_t *)out.p, (uint32_t)r, iters);
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        if (r >= 3 && ms < best) best = ms;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    return (double)grid * 256 * iters * 8 / (best * 1e-3) / 1e9;
+}

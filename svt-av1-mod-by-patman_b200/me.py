@@ -106,6 +106,14 @@ class MeSession:
     def sync(self):
         _check(self.lib.svtme_sync(self.h), self.lib)
 
+    def set_stream(self, cuda_stream_ptr):
+        _check(self.lib.svtme_set_stream(self.h, cuda_stream_ptr), self.lib)
+
+    def last_work_ops(self):
+        v = C.c_uint64()
+        _check(self.lib.svtme_last_work_ops(self.h, C.byref(v)), self.lib)
+        return int(v.value)
+
     def last_kernel_ms(self):
         return float(self.lib.svtme_last_kernel_ms(self.h))
 
@@ -113,3 +121,42 @@ class MeSession:
         jobs, outs = self.make_jobs([(params, cur, refs)], deep=deep)
         self.run_jobs(jobs)
         return outs[0]
+
+
+def derive_input(enc_mode, width, height, **kw):
+    """Encoder-level settings -> SvtMeDeriveInput (defaults: CRF qp 35, random access, 30 fps)."""
+    d = abi.SvtMeDeriveInput()
+    d.enc_mode, d.width, d.height = enc_mode, width, height
+    d.qp = kw.get("qp", 35)
+    d.hierarchical_levels = kw.get("hierarchical_levels", 5)
+    d.temporal_layer_index = kw.get("temporal_layer_index", 1)
+    d.is_ref = kw.get("is_ref", 1)
+    d.slice_type_b = kw.get("slice_type_b", 1)
+    d.ref_list0_count_try = kw.get("ref_list0_count_try", 1)
+    d.ref_list1_count_try = kw.get("ref_list1_count_try", 1)
+    d.frame_rate_q16 = kw.get("frame_rate_q16", 30 << 16)
+    d.ref_count_used_list0 = kw.get("ref_count_used_list0", max(1, d.ref_list0_count_try))
+    d.ref_count_used_list1 = kw.get("ref_count_used_list1", d.ref_list1_count_try)
+    for k in ("rtc_tune", "sc_class1", "safe_limit_nref", "only_l_bwd", "use_best_me_unipred_cand_only",
+              "similar_brightness_refs", "safe_limit_zz_th", "gm_level_enabled", "gm_use_distance_based_active_th"):
+        setattr(d, k, kw.get(k, 0))
+    return d
+
+
+def finish_params(p, d, picture_number, ref_numbers):
+    """Per-picture fields the encoder sets in me_process.c:219-227 / pd_process.c."""
+    p.num_of_list_to_search = 2 if d.slice_type_b else 1
+    p.num_of_ref_pic_to_search[0] = d.ref_list0_count_try
+    p.num_of_ref_pic_to_search[1] = d.ref_list1_count_try if d.slice_type_b else 0
+    p.temporal_layer_index = d.temporal_layer_index
+    p.is_ref = d.is_ref
+    p.hierarchical_levels = d.hierarchical_levels
+    p.similar_brightness_refs = d.similar_brightness_refs
+    p.max_number_of_pus_per_sb = 85
+    p.only_l_bwd = d.only_l_bwd
+    p.gm_enabled = d.gm_level_enabled
+    p.gm_use_distance_based_active_th = d.gm_use_distance_based_active_th
+    p.picture_number = picture_number
+    for (li, ri), n in ref_numbers.items():
+        p.ref_picture_number[li][ri] = n
+    return p

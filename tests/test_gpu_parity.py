@@ -1,0 +1,145 @@
+"""GPU parity tests (-m gpu): everything goes through the C ABI of libsvtme_b200.so and is compared
+bit-for-bit with the oracle restatement / the committed golden vectors. Nothing here reads
+/root/reference."""
+import ctypes as C
+import importlib
+import os
+import sys
+
+import numpy as np
+import pytest
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+import _util as U
+import make_golden as G
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+me = importlib.import_module(U.PKG + ".me")
+
+
+def gpu_stage(seq, p, cur, refs, W, H, deep=True):
+    with me.MeSession(0, W, H, capacity=len(set(refs.values())) + 1) as ses:
+        for n in set(refs.values()) | {cur}:
+            ses.put_picture(n, seq[n])
+        return ses.run_picture(p, cur, refs, deep=deep)
+
+
+def derive(ses_or_lib, d):
+    p = U.abi.SvtMeParams()
+    assert U.product_lib().svtme_derive_params(C.byref(d), C.byref(p)) == 0
+    return p
+
+
+@pytest.mark.parametrize("case", G.STAGE_CASES, ids=[c[0] for c in G.STAGE_CASES])
+def test_stage_matches_golden_and_oracle(case):
+    name, W, H, preset, tl, refs, cur, kw = case
+    seq, d = G.stage_case(*case)
+    p = U.finish_params(derive(None, d), d, cur, refs)
+    got = gpu_stage(seq, p, cur, refs, W, H)
+    want = np.load(os.path.join(GOLD, "stage_%s.npz" % name))
+    for k in want.files:
+        assert np.array_equal(want[k], got[k]), "golden " + k
+    pyr = {n: U.CpuPyramid("orc", seq[n], n) for n in set(refs.values()) | {cur}}
+    orc = U.cpu_me_picture("orc", p, pyr[cur], {k: pyr[v] for k, v in refs.items()})
+    for k in orc:
+        assert np.array_equal(orc[k], got[k]), "oracle " + k
+
+
+def test_pyramid_matches_golden_and_oracle():
+    seq = U.synth_sequence(328, 200, 1, seed=5)
+    want = np.load(os.path.join(GOLD, "pyramid.npz"))
+    with me.MeSession(0, 328, 200, capacity=1) as ses:
+        ses.put_picture(0, seq[0])
+        for lvl, k in enumerate(("full", "quarter", "sixteenth")):
+            got = ses.get_plane(0, lvl)
+            assert np.array_equal(want[k][:, :got.shape[1]], got), k
+
+
+@pytest.mark.parametrize("size", [(1920, 1080), (856, 480), (64, 64)])
+def test_pyramid_sizes_vs_oracle(size):
+    W, H = size
+    img = U.random_frames(W, H, 1, seed=W)[0]
+    pyr = U.CpuPyramid("orc", img, 0)
+    with me.MeSession(0, W, H, capacity=1) as ses:
+        ses.put_picture(0, img)
+        for lvl in range(3):
+            got = ses.get_plane(0, lvl)
+            assert np.array_equal(pyr.plane(lvl)[:, :got.shape[1]], got), lvl
+
+
+@pytest.mark.parametrize("preset,tl,refs,cur", [
+    (8, 3, {(0, 0): 2, (0, 1): 1, (0, 2): 0, (1, 0): 4, (1, 1): 5}, 3),
+    (4, 2, {(0, 0): 2, (0, 1): 1, (0, 2): 0, (0, 3): 0, (1, 0): 4, (1, 1): 5, (1, 2): 6}, 3),
+    (0, 1, {(0, 0): 0, (1, 0): 4}, 2),
+    (13, 1, {(0, 0): 1, (1, 0): 3}, 2),
+])
+def test_stage_edges_and_ragged_sizes_vs_oracle(preset, tl, refs, cur):
+    """Incomplete b64 rows/columns (height 1080-like remainder 56, width remainder 24) and motion
+    that pushes search windows into the picture padding."""
+    for (W, H), motion in [((472, 312), (9, -7)), ((216, 120), (-12, 10))]:
+        seq = U.synth_sequence(W, H, 7, seed=preset + W, motion=motion, noise=3.0)
+        l0 = 1 + max(ri for (li, ri) in refs if li == 0)
+        l1 = 1 + max([ri for (li, ri) in refs if li == 1], default=-1)
+        d = U.derive_input(preset, W, H, temporal_layer_index=tl, ref_list0_count_try=l0, ref_list1_count_try=l1,
+                           ref_count_used_list0=l0, ref_count_used_list1=l1)
+        p = U.finish_params(derive(None, d), d, cur, refs)
+        got = gpu_stage(seq, p, cur, refs, W, H)
+        pyr = {n: U.CpuPyramid("orc", seq[n], n) for n in set(refs.values()) | {cur}}
+        orc = U.cpu_me_picture("orc", p, pyr[cur], {k: pyr[v] for k, v in refs.items()})
+        for k in orc:
+            assert np.array_equal(orc[k], got[k]), (W, H, k)
+
+
+def test_stage_flat_and_random_pictures_tie_breaks():
+    """All-equal pictures make every position tie (first-in-raster-order must win); i.i.d. random
+    pictures give non-trivial minima everywhere (SadTest RANDOM pattern)."""
+    W, H = 256, 192
+    refs, cur = {(0, 0): 0, (0, 1): 1, (1, 0): 3}, 2
+    for kind in ("flat", "random"):
+        seq = np.full((4, H, W), 128, dtype=np.uint8) if kind == "flat" else U.random_frames(W, H, 4)
+        for preset in (4, 9):
+            d = U.derive_input(preset, W, H, temporal_layer_index=1, ref_list0_count_try=2, ref_list1_count_try=1,
+                               ref_count_used_list0=2, ref_count_used_list1=1)
+            p = U.finish_params(derive(None, d), d, cur, refs)
+            got = gpu_stage(seq, p, cur, refs, W, H)
+            pyr = {n: U.CpuPyramid("orc", seq[n], n) for n in range(4)}
+            orc = U.cpu_me_picture("orc", p, pyr[cur], {k: pyr[v] for k, v in refs.items()})
+            for k in orc:
+                assert np.array_equal(orc[k], got[k]), (kind, preset, k)
+
+
+def test_batched_jobs_equal_single_jobs():
+    W, H = 320, 192
+    seq = U.synth_sequence(W, H, 6, seed=11)
+    d = U.derive_input(8, W, H, temporal_layer_index=1, ref_list0_count_try=1, ref_list1_count_try=1)
+    with me.MeSession(0, W, H, capacity=6) as ses:
+        for n in range(6):
+            ses.put_picture(n, seq[n])
+        specs = []
+        for cur in (1, 2, 3, 4):
+            p = U.finish_params(derive(None, d), d, cur, {(0, 0): cur - 1, (1, 0): cur + 1})
+            specs.append((p, cur, {(0, 0): cur - 1, (1, 0): cur + 1}))
+        jobs, outs = ses.make_jobs(specs, deep=True)
+        ses.run_jobs(jobs)
+        for (p, cur, refs), batch in zip(specs, outs):
+            single = ses.run_picture(p, cur, refs, deep=True)
+            for k in single:
+                assert np.array_equal(single[k], batch[k]), (cur, k)
+
+
+def test_error_behaviour():
+    lib = U.product_lib()
+    h = C.c_void_p()
+    assert lib.svtme_open(0, 100, 100, 2, C.byref(h)) == -1  # not a multiple of 8
+    with me.MeSession(0, 128, 128, capacity=1) as ses:
+        img = np.zeros((128, 128), dtype=np.uint8)
+        ses.put_picture(0, img)
+        with pytest.raises(me.SvtMeError):
+            ses.put_picture(1, img)  # ring full
+        d = U.derive_input(8, 128, 128)
+        p = U.finish_params(derive(None, d), d, 0, {(0, 0): 5, (1, 0): 6})
+        with pytest.raises(me.SvtMeError):
+            ses.run_picture(p, 0, {(0, 0): 5, (1, 0): 6})  # references not resident
+        with pytest.raises(me.SvtMeError):
+            ses.release_picture(9)

@@ -1,0 +1,78 @@
+"""CPU tests (-m "not gpu") of the host side: parameter derivation against the reference's own
+svt_aom_sig_deriv_me (golden grid), ABI symbol export, struct layout, error behaviour."""
+import ctypes as C
+import gzip
+import json
+import os
+import re
+
+import numpy as np
+import pytest
+
+import _util as U
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def test_library_exports_every_header_symbol():
+    lib = U.product_lib()  # loads csrc/libsvtme_b200.so; no compute calls here
+    hdr = open(os.path.join(U.ROOT, "include", "svtme_b200.h")).read()
+    names = set(re.findall(r"\b(svtme_[a-z0-9_]+|svt_[a-z0-9_]+_b200)\s*\(", hdr))
+    assert len(names) >= 25
+    for n in sorted(names):
+        assert hasattr(lib, n), "symbol missing from libsvtme_b200.so: " + n
+
+
+def test_struct_layout_matches_library():
+    U.abi.check_layout(U.product_lib())
+    assert U.oracle_lib().orc_sizeof_params() == C.sizeof(U.abi.SvtMeParams)
+    assert U.oracle_lib().orc_sizeof_out() == C.sizeof(U.abi.SvtMeOut)
+
+
+def test_derive_params_matches_reference_grid():
+    lib = U.product_lib()
+    grid = json.load(gzip.open(os.path.join(GOLD, "params.json.gz"), "rt"))
+    assert len(grid) == 600
+    skip = {"num_of_list_to_search", "num_of_ref_pic_to_search", "temporal_layer_index", "is_ref", "hierarchical_levels",
+            "similar_brightness_refs", "max_number_of_pus_per_sb", "only_l_bwd", "gm_enabled",
+            "gm_use_distance_based_active_th", "picture_number", "ref_picture_number"}  # per-picture, not from sig_deriv_me
+    for row in grid:
+        d = U.abi.SvtMeDeriveInput()
+        for k, v in row["in"].items():
+            setattr(d, k, v)
+        p = U.abi.SvtMeParams()
+        assert lib.svtme_derive_params(C.byref(d), C.byref(p)) == 0
+        got = p.as_dict()
+        for k, v in row["out"].items():
+            if k in skip:
+                continue
+            assert got[k] == v, (row["in"], k, got[k], v)
+
+
+def test_derive_params_rejects_bad_preset():
+    lib = U.product_lib()
+    d = U.derive_input(14, 1920, 1080)
+    p = U.abi.SvtMeParams()
+    assert lib.svtme_derive_params(C.byref(d), C.byref(p)) == -1  # SVTME_ERR_INVALID
+
+
+def test_exported_pu_count():
+    lib = U.product_lib()
+    p = U.abi.SvtMeParams()
+    p.max_number_of_pus_per_sb = 85
+    for e16, e8, want in [(1, 1, 85), (1, 0, 21), (0, 0, 5)]:
+        p.enable_me_16x16, p.enable_me_8x8 = e16, e8
+        assert lib.svtme_exported_pu_count(C.byref(p)) == want == U.abi.exported_pu_count(p)
+
+
+def test_missing_library_is_a_hard_error(monkeypatch):
+    monkeypatch.setattr(U.abi, "_lib", None)
+    monkeypatch.setattr(U.abi, "LIB_PATH", "/nonexistent/libsvtme_b200.so")
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        U.abi.load_library()
+
+
+def test_synth_sequence_is_deterministic():
+    a = U.synth_sequence(128, 64, 3, seed=4)
+    b = U.synth_sequence(128, 64, 3, seed=4)
+    assert np.array_equal(a, b) and a.dtype == np.uint8 and a.shape == (3, 64, 128)

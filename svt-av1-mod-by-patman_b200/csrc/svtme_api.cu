@@ -261,7 +261,7 @@ static OutLayout out_layout(uint32_t n_b64, uint32_t n_pu, const SvtMeParams &p,
     L.d64 = take((size_t)n_b64 * 4); L.d32 = take((size_t)n_b64 * 4); L.d16 = take((size_t)n_b64 * 4);
     L.d8 = take((size_t)n_b64 * 4); L.var8 = take((size_t)n_b64 * 4); L.rc = take((size_t)n_b64 * 4);
     L.stat = take(n_b64); L.gm = take(n_b64);
-    L.work = take(8);
+    L.work = take(8 * (1 + SVTME_PHASES)); // work_ops, then per-phase cycle sums
     if (deep) {
         L.bsad = take((size_t)n_b64 * 2 * 4 * 85 * 4); L.bmv = take((size_t)n_b64 * 2 * 4 * 85 * 4);
         L.sc = take((size_t)n_b64 * 2 * 4 * 2 * 2); L.hsad = take((size_t)n_b64 * 2 * 4 * 8); L.doref = take((size_t)n_b64 * 2 * 4);
@@ -446,5 +446,22 @@ extern "C" int svtme_last_work_ops(SvtMeHandle *h, uint64_t *ops) {
     }
     *ops = sum;
     cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+    return SVTME_OK;
+}
+
+// Per-phase SM cycles (thread 0 of every b64 CTA, summed over all CTAs) of the last
+// svtme_launch_pictures call; see SVTME_PHASE_* in svtme_common.cuh. Synchronises the stream.
+extern "C" int svtme_last_phase_cycles(SvtMeHandle *h, uint64_t *cycles, uint32_t n) {
+    if (!h || !cycles) return fail(SVTME_ERR_INVALID, "svtme_last_phase_cycles: bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    if (n > SVTME_PHASES) n = SVTME_PHASES;
+    for (uint32_t k = 0; k < n; ++k) cycles[k] = 0;
+    for (size_t o : h->work_off) {
+        unsigned long long v[SVTME_PHASES];
+        CU(cudaMemcpy(v, h->ob.dev + o + 8, sizeof(v), cudaMemcpyDeviceToHost));
+        for (uint32_t k = 0; k < n; ++k) cycles[k] += v[k];
+    }
     return SVTME_OK;
 }

@@ -50,8 +50,13 @@ struct DevJob {
     int16_t *hme_sc;
     unsigned long long *hme_sad;
     uint8_t *do_ref;
-    unsigned long long *work_ops; // algorithmic SAD byte-ops executed for this picture (roofline numerator)
+    unsigned long long *work_ops; // [0] algorithmic SAD byte-ops executed for this picture (roofline numerator)
 };
+
+// phase slots behind work_ops (cycle sums of thread 0, one CTA per b64)
+#define SVTME_PHASES 12
+enum { SVTME_PH_SETUP = 0, SVTME_PH_ZZ, SVTME_PH_PREHME, SVTME_PH_L0, SVTME_PH_L1, SVTME_PH_L2, SVTME_PH_CENTRE,
+       SVTME_PH_INT_CHECK, SVTME_PH_INT_PROBE, SVTME_PH_INT_MAIN, SVTME_PH_FINISH, SVTME_PH_TOTAL };
 
 static inline int up128(int v) { return (v + 127) & ~127; }
 

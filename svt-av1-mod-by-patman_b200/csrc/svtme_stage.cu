@@ -47,6 +47,7 @@ struct StageState {
     uint32_t me_distortion[SVTME_PU_COUNT];
     FpTables tab;
     HJob jobs[MAX_JOBS];
+    HGeo geo[MAX_JOBS];
     JobMeta meta[MAX_JOBS];
     int n_jobs;
     // integer-search hand-over between plan steps
@@ -852,7 +853,7 @@ int svtme_stage_smem_bytes() { return (int)sizeof(StageSmem); }
 
 __device__ void run_jobs(StageState *s, const HBlk &blk, uint8_t *arena) {
     const int n = s->n_jobs; // published by T0
-    for (int j = 0; j < n; ++j) hme_search(blk, &s->jobs[j], arena);
+    hme_search_multi(blk, s->jobs, n, s->geo, arena);
     if (threadIdx.x == 0) {
         unsigned long long w = 0;
         for (int j = 0; j < n; ++j) {
@@ -871,6 +872,18 @@ __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob
     const uint32_t b64 = blockIdx.x % b64_per_job;
     const SvtMeParams &p = J.prm;
     const int tid = threadIdx.x;
+    long long t_prev = clock64(), t_start = t_prev;
+    unsigned long long ph[SVTME_PHASES];
+#pragma unroll
+    for (int k = 0; k < SVTME_PHASES; ++k) ph[k] = 0;
+#define PHASE(k)                                    \
+    do {                                            \
+        if (tid == 0) {                             \
+            const long long t_now = clock64();      \
+            ph[k] += (unsigned long long)(t_now - t_prev); \
+            t_prev = t_now;                         \
+        }                                           \
+    } while (0)
 
     const int org_x = (int)(b64 % J.b64_cols) * 64, org_y = (int)(b64 / J.b64_cols) * 64;
     if (tid == 0) {
@@ -912,12 +925,14 @@ __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob
     const HBlk blk_l1 = {sm->src32, hme_full ? 32 : 64, b64_w >> 1, hme_full ? (b64_h >> 1) : (b64_h >> 2), hme_full ? 1 : 2};
     const HBlk blk_l2 = {sm->src64, hme_full ? 64 : 128, b64_w, hme_full ? b64_h : (b64_h >> 1), hme_full ? 1 : 2};
 
+    PHASE(SVTME_PH_SETUP);
     // ---- hme_b64 :2511-2545
     if (p.me_early_exit_th || p.me_safe_limit_zz_th) {
         T0(plan_zz(s, J));
         run_jobs(s, blk_zz, sm->arena);
         T0(post_zz(s, p));
     }
+    PHASE(SVTME_PH_ZZ);
     if (p.prehme_enable) {
         for (int li = 0; li < p.num_of_list_to_search; ++li) {
             T0(plan_prehme(s, J, li));
@@ -926,6 +941,7 @@ __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob
         }
         T0(post_prehme_final(s, p));
     }
+    PHASE(SVTME_PH_PREHME);
     if (p.enable_hme_flag) {
         if (p.enable_hme_level0_flag) {
             const bool dependent = p.enable_me_sr_adjustment && p.distance_based_hme_resizing &&
@@ -939,18 +955,22 @@ __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob
             run_jobs(s, blk_l0, sm->arena);
             T0(post_level_jobs(s, p, 0, 4); post_l0_prehme(s, p));
         }
+        PHASE(SVTME_PH_L0);
         if (p.enable_hme_level1_flag) {
             T0(plan_l1(s, J));
             run_jobs(s, blk_l1, sm->arena);
             T0(post_level_jobs(s, p, 1, 2));
         }
+        PHASE(SVTME_PH_L1);
         if (p.enable_hme_level2_flag) {
             T0(plan_l2(s, J));
             run_jobs(s, blk_l2, sm->arena);
             T0(post_level_jobs(s, p, 2, 1));
         }
+        PHASE(SVTME_PH_L2);
     }
     T0(set_final_search_centre(s, p); if (p.enable_hme_flag) hme_prune_ref_and_adjust_sr(s, p));
+    PHASE(SVTME_PH_CENTRE);
 
     // ---- integer_search_b64 :1249-1586
     const bool sub_sad = p.me_search_method == 0;
@@ -966,14 +986,15 @@ __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob
                 s->tab.mv[tid] = 0;
             }
             __syncthreads();
+            PHASE(SVTME_PH_INT_CHECK);
             const DevPlane &pl = J.ref[li][ri].lvl[0];
             if (s->fp_probe) {
                 const int xc = s->fp_xc, yc = s->fp_yc;
-                fullpel_search(sm->src64, pl.at(org_x + xc, org_y + yc), pl.stride, xc, yc, 1, 1, sub_sad, 1, &s->tab,
-                               sm->arena);
+                fullpel_probe(sm->src64, pl.at(org_x + xc, org_y + yc), pl.stride, xc, yc, sub_sad, 1, &s->tab);
                 if (tid == 0) s->work_ops += 64ull * (sub_sad ? 32 : 64);
             }
             T0(plan_int_c(s, J));
+            PHASE(SVTME_PH_INT_PROBE);
             {
                 const int ox = s->fp_ox, oy = s->fp_oy;
                 fullpel_search(sm->src64, pl.at(org_x + ox, org_y + oy), pl.stride, ox, oy, s->fp_sa_w, s->fp_sa_h, sub_sad,
@@ -985,6 +1006,7 @@ __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob
                 s->best_mv[li][ri][tid] = s->tab.mv[tid];
             }
             __syncthreads();
+            PHASE(SVTME_PH_INT_MAIN);
         }
 
     // ---- pruning, candidates, statistics :3192-3221
@@ -997,7 +1019,13 @@ __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob
     __syncthreads();
     if (tid == 0) {
         finish_b64(s, J, b64, cando);
-        if (J.work_ops) atomicAdd(J.work_ops, s->work_ops);
+        PHASE(SVTME_PH_FINISH);
+        ph[SVTME_PH_TOTAL] = (unsigned long long)(clock64() - t_start);
+        if (J.work_ops) {
+            atomicAdd(J.work_ops, s->work_ops);
+#pragma unroll
+            for (int k = 0; k < SVTME_PHASES; ++k) atomicAdd(J.work_ops + 1 + k, ph[k]);
+        }
     }
     // deep state for parity checks
     if (J.best_sad)

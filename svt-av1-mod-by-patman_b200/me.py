@@ -114,6 +114,15 @@ class MeSession:
         _check(self.lib.svtme_last_work_ops(self.h, C.byref(v)), self.lib)
         return int(v.value)
 
+    PHASE_NAMES = ("setup", "zz_sad", "prehme", "hme_l0", "hme_l1", "hme_l2", "centre_prune", "check_00",
+                   "probe", "fullpel", "finish", "total")
+
+    def last_phase_cycles(self):
+        """Per-phase SM cycles of the last launch (thread 0 of every b64 CTA, summed)."""
+        v = (C.c_uint64 * len(self.PHASE_NAMES))()
+        _check(self.lib.svtme_last_phase_cycles(self.h, v, len(self.PHASE_NAMES)), self.lib)
+        return dict(zip(self.PHASE_NAMES, (int(x) for x in v)))
+
     def last_kernel_ms(self):
         return float(self.lib.svtme_last_kernel_ms(self.h))
 

@@ -33,25 +33,42 @@ __device__ __forceinline__ uint32_t vsad4(uint32_t a, uint32_t b, uint32_t acc) 
 //     arena + c*copy_bytes + rowoff(R)*16 + k*16,   rowoff(R) = R*m + skew*(R>>4)
 // (skew chunks are inserted every 16 rows by the full-pel engine to spread 16-row-apart accesses
 // over all banks). Reads up to 3+16 bytes past the last needed byte of a row: planes carry pads.
-__device__ __forceinline__ void stage_window4(uint8_t *arena, const uint8_t *__restrict__ g, int gstride, int rows,
-                                              int m, int skew, int copy_bytes) {
-    // One warp per row, lanes over the words of the row: no integer division anywhere. Each lane
-    // reads three ALIGNED global words (the row base is rounded down to 4 bytes) and derives the
+__device__ __noinline__ void stage_window4(uint8_t *arena, const uint8_t *__restrict__ g, int gstride, int rows,
+                                              int m, int skew, int copy_bytes, int nwords) {
+    // Flat (row, word) item list over the whole CTA, four items per thread in flight so that the
+    // global-load latency is paid once per four rows-worth of words, not once per row. Each item
+    // reads three ALIGNED global words (the row address is rounded down to 4 bytes) and derives the
     // four phase words with funnel shifts; neighbouring lanes hit the same L1 lines.
-    const int wpr = m * 4; // words per copy row
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int R = warp; R < rows; R += SVTME_THREADS / 32) {
-        const uintptr_t ai = reinterpret_cast<uintptr_t>(g + (size_t)R * gstride);
-        const uint32_t *al = reinterpret_cast<const uint32_t *>(ai & ~(uintptr_t)3);
-        const uint32_t mis = (uint32_t)(ai & 3);
-        uint8_t *dst = arena + ((size_t)(R * m + skew * (R >> 4)) << 4);
-        for (int kw = lane; kw < wpr; kw += 32) {
-            const uint32_t w0 = __ldg(al + kw), w1 = __ldg(al + kw + 1), w2 = __ldg(al + kw + 2);
+    // nwords <= 4*m: words of a copy row that are actually read by the search.
+    const int total = rows * nwords;
+    const uint32_t mg = 0xFFFFFFFFu / (uint32_t)nwords + 1u; // exact for total < 2^16
+    constexpr int U = 4;
+    for (int base = threadIdx.x; base < total; base += U * SVTME_THREADS) {
+        uint32_t w0[U], w1[U], w2[U], mis[U];
+        uint8_t *dst[U];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                const uint32_t o = c + mis; // byte offset of phase c inside (w0,w1,w2)
-                const uint32_t lo = o >= 4 ? w1 : w0, hi = o >= 4 ? w2 : w1;
-                *reinterpret_cast<uint32_t *>(dst + (size_t)c * copy_bytes + 4 * kw) = __funnelshift_r(lo, hi, (o & 3) * 8);
+        for (int u = 0; u < U; ++u) {
+            const int i = base + u * SVTME_THREADS;
+            if (i < total) {
+                const int R = (int)__umulhi((uint32_t)i, mg), kw = i - R * nwords;
+                const uintptr_t ai = reinterpret_cast<uintptr_t>(g + (size_t)R * gstride);
+                const uint32_t *al = reinterpret_cast<const uint32_t *>(ai & ~(uintptr_t)3) + kw;
+                mis[u] = (uint32_t)(ai & 3);
+                w0[u] = __ldg(al);
+                w1[u] = __ldg(al + 1);
+                w2[u] = mis[u] ? __ldg(al + 2) : 0u;
+                dst[u] = arena + ((size_t)(R * m + skew * (R >> 4)) << 4) + 4 * kw;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (base + u * SVTME_THREADS < total) {
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const uint32_t o = c + mis[u]; // byte offset of phase c inside (w0,w1,w2)
+                    const uint32_t lo = o >= 4 ? w1[u] : w0[u], hi = o >= 4 ? w2[u] : w1[u];
+                    *reinterpret_cast<uint32_t *>(dst[u] + (size_t)c * copy_bytes) = __funnelshift_r(lo, hi, (o & 3) * 8);
+                }
             }
         }
     }
@@ -60,13 +77,33 @@ __device__ __forceinline__ void stage_window4(uint8_t *arena, const uint8_t *__r
 // ------------------------------------------------------------------------------------------------
 // HME engine
 // ------------------------------------------------------------------------------------------------
-struct HBlk {            // the source block of this call (uniform over the CTA)
+#define SVTME_MAX_JOBS 32
+
+__device__ __forceinline__ uint32_t magic_div(uint32_t d) { return 0xFFFFFFFFu / d + 1u; } // exact for n < 2^16
+
+struct HBlk {            // the source block of a round (uniform over the CTA)
     const uint8_t *src;  // shared memory, compared row r at src + r*src_pitch
     int src_pitch;       // bytes between two COMPARED source rows
     int bw;              // block width in pixels (any value >= 1)
     int nrows;           // number of (sub-sampled) rows actually compared
     int row_step;        // reference rows between two compared rows (2 = SUB_SAD_SEARCH)
+    int nbx, nb;         // 16x8 register sub-blocks across / in total
+    uint32_t mg_nb, mg_nbx;
 };
+
+__device__ __forceinline__ HBlk make_hblk(const uint8_t *src, int src_pitch, int bw, int nrows, int row_step) {
+    HBlk b;
+    b.src = src;
+    b.src_pitch = src_pitch;
+    b.bw = bw;
+    b.nrows = nrows;
+    b.row_step = row_step;
+    b.nbx = (bw + 15) >> 4;
+    b.nb = b.nbx * ((nrows + 7) >> 3);
+    b.mg_nb = magic_div((uint32_t)max(b.nb, 1));
+    b.mg_nbx = magic_div((uint32_t)max(b.nbx, 1));
+    return b;
+}
 
 struct HJob {
     const uint8_t *ref;  // global: reference pixel under block(0,0) at search position (0,0)
@@ -86,7 +123,24 @@ struct HGeo {
     int sa_w, bh;        // positions in this tile
     int x0, y0;          // tile origin inside the job's search area
     int xt_n, n_items, G, skip_even;
-    uint32_t mg_xt;
+    int rows, cpr;       // staged rows, 16-byte chunks staged per copy row
+    int stage_units;     // rows * cpr
+    int scan_n;          // positions whose SAD is summed over sub-blocks in the SAD buffer (nb > 1)
+    uint32_t mg_xt, mg_cpr, mg_wb;
+    uint32_t need;       // arena bytes (copies + SAD buffer)
+    int big;             // does not fit as a whole: tiled single-job path
+    int stage_base, item_base, scan_base; // prefix sums inside the group
+};
+
+struct HGroup {
+    int j0, j1, big;
+    int stage_total, item_total, scan_total;
+};
+
+struct HPlan {           // shared-memory scratch of one round
+    HGeo geo[SVTME_MAX_JOBS];
+    HGroup grp[SVTME_MAX_JOBS];
+    int n_groups;
 };
 
 struct SrcRegs {         // one 16x8 source sub-block in registers
@@ -94,8 +148,6 @@ struct SrcRegs {         // one 16x8 source sub-block in registers
     uint32_t msk[4];
     int cached_b, rows_here;
 };
-
-__device__ __forceinline__ uint32_t magic_div(uint32_t d) { return 0xFFFFFFFFu / d + 1u; } // exact for n < 2^16
 
 __device__ __forceinline__ void load_src_regs(const HBlk &blk, int b, int bxi, int byi, SrcRegs &sr) {
     sr.cached_b = b;
@@ -124,15 +176,17 @@ __device__ __forceinline__ void load_src_regs(const HBlk &blk, int b, int bxi, i
 
 // One work item = G same-phase positions of one row against one 16x8 source sub-block.
 template <int G>
-__device__ __forceinline__ void hme_item(const HBlk &blk, const HGeo &g, const uint8_t *arena, int it, int nb, int nbx,
-                                         uint32_t mg_nb, uint32_t mg_nbx, SrcRegs &sr, unsigned long long &best) {
-    int t = nb == 1 ? it : (int)__umulhi((uint32_t)it, mg_nb);
+__device__ __forceinline__ void hme_item(const HBlk &blk, const HGeo &g, uint8_t *arena, int it, SrcRegs &sr,
+                                         unsigned long long &best) {
+    const int nb = blk.nb, nbx = blk.nbx;
+    int t = nb == 1 ? it : (int)__umulhi((uint32_t)it, blk.mg_nb);
     const int b = it - t * nb;
     const int c = t & 3;
     t >>= 2;
-    const int y = g.xt_n == 1 ? t : (int)__umulhi((uint32_t)t, g.mg_xt);
-    const int xt = t - y * g.xt_n;
-    const int byi = nbx == 1 ? b : (int)__umulhi((uint32_t)b, mg_nbx);
+    const int xt_n = g.xt_n;
+    const int y = xt_n == 1 ? t : (int)__umulhi((uint32_t)t, g.mg_xt);
+    const int xt = t - y * xt_n;
+    const int byi = nbx == 1 ? b : (int)__umulhi((uint32_t)b, blk.mg_nbx);
     const int bxi = b - byi * nbx;
     if (b != sr.cached_b) load_src_regs(blk, b, bxi, byi, sr);
     const bool masked = (blk.bw & 15) != 0;
@@ -140,12 +194,12 @@ __device__ __forceinline__ void hme_item(const HBlk &blk, const HGeo &g, const u
 #pragma unroll
     for (int j = 0; j < G; ++j) acc[j] = 0;
     const int q0 = xt * G + 4 * bxi; // first word of copy c this item needs
-    const uint8_t *base = arena + g.arena_off + (size_t)c * g.copy_bytes + 4 * q0;
+    const int m16 = g.m << 4;
+    const uint8_t *rp = arena + g.arena_off + (size_t)c * g.copy_bytes + 4 * q0 + (size_t)(y + 8 * byi * blk.row_step) * m16;
+    const int rstep = blk.row_step * m16;
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
         if (r < sr.rows_here) {
-            const int R = y + (8 * byi + r) * blk.row_step;
-            const uint8_t *rp = base + ((size_t)R * g.m << 4);
             uint32_t w[G + 4];
             if (G == 2) {
 #pragma unroll
@@ -163,6 +217,7 @@ __device__ __forceinline__ void hme_item(const HBlk &blk, const HGeo &g, const u
                     if (4 * k + 3 < G + 4) w[4 * k + 3] = v.w;
                 }
             }
+            rp += rstep;
             if (masked) {
 #pragma unroll
                 for (int j = 0; j < G; ++j)
@@ -178,7 +233,7 @@ __device__ __forceinline__ void hme_item(const HBlk &blk, const HGeo &g, const u
     }
     const int yg = g.y0 + y;
     if (g.skip_even && !(yg & 1)) return;
-    uint32_t *sadbuf = reinterpret_cast<uint32_t *>(const_cast<uint8_t *>(arena) + g.sad_off);
+    uint32_t *sadbuf = reinterpret_cast<uint32_t *>(arena + g.sad_off) + y * g.sa_w;
 #pragma unroll
     for (int j = 0; j < G; ++j) {
         const int x = xt * 4 * G + 4 * j + c;
@@ -187,31 +242,31 @@ __device__ __forceinline__ void hme_item(const HBlk &blk, const HGeo &g, const u
                 unsigned long long k = ((unsigned long long)acc[j] << 32) | ((unsigned)yg << 16) | (unsigned)(g.x0 + x);
                 best = k < best ? k : best;
             } else {
-                atomicAdd(&sadbuf[y * g.sa_w + x], acc[j]);
+                atomicAdd(&sadbuf[x], acc[j]);
             }
         }
     }
 }
 
-__device__ __forceinline__ void hme_item_any(const HBlk &blk, const HGeo &g, const uint8_t *arena, int it, int nb, int nbx,
-                                             uint32_t mg_nb, uint32_t mg_nbx, SrcRegs &sr, unsigned long long &best) {
+__device__ __forceinline__ void hme_item_any(const HBlk &blk, const HGeo &g, uint8_t *arena, int it, SrcRegs &sr,
+                                             unsigned long long &best) {
     if (g.G == 8)
-        hme_item<8>(blk, g, arena, it, nb, nbx, mg_nb, mg_nbx, sr, best);
+        hme_item<8>(blk, g, arena, it, sr, best);
     else if (g.G == 4)
-        hme_item<4>(blk, g, arena, it, nb, nbx, mg_nb, mg_nbx, sr, best);
+        hme_item<4>(blk, g, arena, it, sr, best);
     else
-        hme_item<2>(blk, g, arena, it, nb, nbx, mg_nb, mg_nbx, sr, best);
+        hme_item<2>(blk, g, arena, it, sr, best);
 }
 
-// Tile geometry for a (sub)area of wb x hb positions. Returns the arena bytes it needs.
-__device__ __forceinline__ uint32_t hme_geo(const HBlk &blk, int wb, int hb, int skip_even, HGeo &g) {
-    const int nbx = (blk.bw + 15) >> 4, nb = nbx * ((blk.nrows + 7) >> 3);
+// Tile geometry for a (sub)area of wb x hb positions; g.need = the arena bytes it takes.
+__device__ __forceinline__ void hme_geo(const HBlk &blk, int wb, int hb, int skip_even, HGeo &g) {
     const int G = wb <= 8 ? 2 : (wb <= 16 ? 4 : 8);
     const int tile_w = 4 * G;
     const int vec_words = G == 2 ? 6 : ((G + 3 + 3) / 4) * 4;
     const int xt_n = (wb + tile_w - 1) / tile_w;
-    const int words = (xt_n - 1) * G + 4 * (nbx - 1) + vec_words;
-    const int m = ((words + 3) / 4) | 1; // odd chunk stride: consecutive rows start in different bank groups
+    const int words = (xt_n - 1) * G + 4 * (blk.nbx - 1) + vec_words;
+    const int cpr = (words + 3) >> 2;
+    const int m = cpr | 1; // odd chunk stride: consecutive rows start in different bank groups
     const int rows = hb + (blk.nrows - 1) * blk.row_step;
     int copy_chunks = rows * m;
     copy_chunks += (10 - (copy_chunks & 7)) & 7; // copy stride == 2 (mod 8) chunks
@@ -219,37 +274,72 @@ __device__ __forceinline__ uint32_t hme_geo(const HBlk &blk, int wb, int hb, int
     g.m = m;
     g.sa_w = wb;
     g.bh = hb;
+    g.x0 = g.y0 = 0;
     g.xt_n = xt_n;
-    g.n_items = hb * xt_n * 4 * nb;
+    g.n_items = hb * xt_n * 4 * blk.nb;
     g.G = G;
     g.skip_even = skip_even;
+    g.rows = rows;
+    g.cpr = cpr;
+    g.stage_units = rows * cpr;
+    g.scan_n = blk.nb > 1 ? hb * wb : 0;
     g.mg_xt = magic_div((uint32_t)xt_n);
-    g.sad_off = 0;
-    return (uint32_t)g.copy_bytes * 4u + (nb > 1 ? (uint32_t)(hb * wb * 4 + 15) & ~15u : 0u);
+    g.mg_cpr = magic_div((uint32_t)cpr);
+    g.mg_wb = magic_div((uint32_t)wb);
+    g.need = (uint32_t)g.copy_bytes * 4u + (uint32_t)g.scan_n * 4u;
+    g.big = g.need > SVTME_ARENA_BYTES || g.n_items >= 65536 || g.stage_units >= 65536 || g.scan_n >= 65536;
+    g.arena_off = 0;
+    g.sad_off = (uint32_t)g.copy_bytes * 4u;
+    g.stage_base = g.item_base = g.scan_base = 0;
 }
 
-__device__ __forceinline__ void hme_reduce_store(unsigned long long best, HJob *job) {
+// Stage one 16-byte chunk of a window into its four phase copies: six aligned global words ->
+// v[t] = bytes 4t+mis.. (copy 0), then copies 1..3 are static funnel shifts of v.
+__device__ __forceinline__ void stage_unit_load(const uint8_t *__restrict__ row, int k, uint32_t (&w)[6], uint32_t &mis) {
+    const uintptr_t ai = reinterpret_cast<uintptr_t>(row);
+    const uint32_t *al = reinterpret_cast<const uint32_t *>(ai & ~(uintptr_t)3) + 4 * k;
+    mis = (uint32_t)(ai & 3);
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        unsigned long long v = __shfl_xor_sync(0xffffffffu, best, o);
-        best = v < best ? v : best;
+    for (int i = 0; i < 5; ++i) w[i] = __ldg(al + i);
+    w[5] = mis ? __ldg(al + 5) : 0u;
+}
+__device__ __forceinline__ void stage_unit_store(uint8_t *dst, int copy_bytes, const uint32_t (&w)[6], uint32_t mis) {
+    uint32_t v[5];
+#pragma unroll
+    for (int t = 0; t < 5; ++t) v[t] = __funnelshift_r(w[t], w[t + 1], mis * 8);
+    *reinterpret_cast<uint4 *>(dst) = make_uint4(v[0], v[1], v[2], v[3]);
+#pragma unroll
+    for (int c = 1; c < 4; ++c)
+        *reinterpret_cast<uint4 *>(dst + (size_t)c * copy_bytes) =
+            make_uint4(__funnelshift_r(v[0], v[1], 8 * c), __funnelshift_r(v[1], v[2], 8 * c),
+                       __funnelshift_r(v[2], v[3], 8 * c), __funnelshift_r(v[3], v[4], 8 * c));
+}
+
+// Minimum of 64-bit keys over the lanes that are flushing the same job, one atomic per such set.
+__device__ __forceinline__ void flush_key(HJob *jobs, int j, unsigned long long best) {
+    const unsigned act = __activemask();
+    const unsigned peers = __match_any_sync(act, j);
+    const uint32_t hi = (uint32_t)(best >> 32), lo = (uint32_t)best;
+    const uint32_t mhi = __reduce_min_sync(peers, hi);
+    const uint32_t mlo = __reduce_min_sync(peers, hi == mhi ? lo : 0xffffffffu);
+    if ((int)(threadIdx.x & 31) == __ffs(peers) - 1) {
+        const unsigned long long key = ((unsigned long long)mhi << 32) | mlo;
+        if (key < HME_KEY_INIT) atomicMin(&jobs[j].key, key);
     }
-    if ((threadIdx.x & 31) == 0 && best < HME_KEY_INIT) atomicMin(&job->key, best);
 }
 
 // One svt_sad_loop_kernel of ANY size: the search area is tiled so that each tile fits the arena.
 // All threads of the CTA must call it with identical arguments; job lives in shared memory and
 // job->key must be HME_KEY_INIT on entry.
-__device__ void hme_search(const HBlk &blk, HJob *job, uint8_t *arena) {
+__device__ __noinline__ void hme_search(const HBlk &blk, HJob *job, uint8_t *arena) {
     const int sa_w = job->sa_w, sa_h = job->sa_h;
     if (sa_w <= 0 || sa_h <= 0) return;
-    const int nbx = (blk.bw + 15) >> 4, nb = nbx * ((blk.nrows + 7) >> 3);
-    const uint32_t mg_nb = magic_div((uint32_t)nb), mg_nbx = magic_div((uint32_t)nbx);
+    const int nb = blk.nb;
     int wt = sa_w, bh = sa_h;
     HGeo g;
     for (;;) {
-        const uint32_t need = hme_geo(blk, wt, bh, job->skip_even, g);
-        if (need <= SVTME_ARENA_BYTES && g.n_items < 65536) break;
+        hme_geo(blk, wt, bh, job->skip_even, g);
+        if (!g.big) break;
         const int tile_w = 4 * g.G;
         if (bh > 8) bh = (bh + 1) / 2;
         else if (wt > tile_w) wt = ((wt / 2 + tile_w - 1) / tile_w) * tile_w;
@@ -265,24 +355,24 @@ __device__ void hme_search(const HBlk &blk, HJob *job, uint8_t *arena) {
         for (int y0 = 0; y0 < sa_h; y0 += bh) {
             const int hb = min(bh, sa_h - y0);
             hme_geo(blk, wb, hb, job->skip_even, g);
-            g.arena_off = 0;
-            g.sad_off = (uint32_t)g.copy_bytes * 4u;
             g.x0 = x0;
             g.y0 = y0;
             uint32_t *sadbuf = reinterpret_cast<uint32_t *>(arena + g.sad_off);
             __syncthreads(); // previous users of the arena are done
-            stage_window4(arena, job->ref + (size_t)y0 * job->stride + x0, job->stride, hb + (blk.nrows - 1) * blk.row_step,
-                          g.m, 0, g.copy_bytes);
-            if (nb > 1)
-                for (int i = threadIdx.x; i < hb * wb; i += SVTME_THREADS) sadbuf[i] = 0;
+            const uint8_t *g0 = job->ref + (size_t)y0 * job->stride + x0;
+            for (int i = threadIdx.x; i < g.stage_units; i += SVTME_THREADS) {
+                const int R = (int)__umulhi((uint32_t)i, g.mg_cpr), k = i - R * g.cpr;
+                uint32_t w[6], mis;
+                stage_unit_load(g0 + (size_t)R * job->stride, k, w, mis);
+                stage_unit_store(arena + ((size_t)(R * g.m + k) << 4), g.copy_bytes, w, mis);
+            }
+            for (int i = threadIdx.x; i < g.scan_n; i += SVTME_THREADS) sadbuf[i] = 0;
             __syncthreads();
-            for (int it = threadIdx.x; it < g.n_items; it += SVTME_THREADS)
-                hme_item_any(blk, g, arena, it, nb, nbx, mg_nb, mg_nbx, sr, best);
+            for (int it = threadIdx.x; it < g.n_items; it += SVTME_THREADS) hme_item_any(blk, g, arena, it, sr, best);
             if (nb > 1) {
                 __syncthreads();
-                const uint32_t mg_wb = magic_div((uint32_t)wb);
-                for (int i = threadIdx.x; i < hb * wb; i += SVTME_THREADS) {
-                    const int yy = (int)__umulhi((uint32_t)i, mg_wb);
+                for (int i = threadIdx.x; i < g.scan_n; i += SVTME_THREADS) {
+                    const int yy = (int)__umulhi((uint32_t)i, g.mg_wb);
                     const int y = y0 + yy, x = x0 + (i - yy * wb);
                     if (job->skip_even && !(y & 1)) continue;
                     unsigned long long k = ((unsigned long long)sadbuf[i] << 32) | ((unsigned)y << 16) | (unsigned)x;
@@ -291,14 +381,19 @@ __device__ void hme_search(const HBlk &blk, HJob *job, uint8_t *arena) {
             }
         }
     }
-    hme_reduce_store(best, job);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        unsigned long long v = __shfl_xor_sync(0xffffffffu, best, o);
+        best = v < best ? v : best;
+    }
+    if ((threadIdx.x & 31) == 0 && best < HME_KEY_INIT) atomicMin(&job->key, best);
     __syncthreads();
 }
 
 // SAD of the block at ONE position per job (zz-SAD, check_00_center): no staging, one warp per
 // job, lanes over (row, 4-byte column) with unaligned reference words assembled from two aligned
 // loads. All threads call with identical arguments.
-__device__ void hme_points(const HBlk &blk, HJob *jobs, int n) {
+__device__ __noinline__ void hme_points(const HBlk &blk, HJob *jobs, int n) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int wcols = (blk.bw + 3) >> 2, items = blk.nrows * wcols;
     const uint32_t mg_wc = magic_div((uint32_t)wcols);
@@ -323,102 +418,161 @@ __device__ void hme_points(const HBlk &blk, HJob *jobs, int n) {
     __syncthreads();
 }
 
-// A round of independent jobs on the same source block: jobs are packed into the arena as many
-// at a time as fit, staged together and searched as ONE flattened item list, so small jobs
-// (8x3 refinement windows, quadrant searches) share the barriers and fill the CTA.
-// `geo` is scratch in shared memory (one entry per job). All threads call with identical arguments.
-__device__ void hme_search_multi(const HBlk &blk, HJob *jobs, int n, HGeo *geo, uint8_t *arena) {
+// A round of independent jobs on the same source block. Jobs are packed into the arena as many
+// at a time as fit ("group"); staging, search items and the SAD-buffer scan of a group are each
+// ONE flattened list over the CTA, so twenty 16x6 refinement windows cost three barriers, not
+// sixty, and every global load of the group is in flight at once.
+// `pl` is scratch in shared memory. All threads call with identical arguments.
+__device__ __noinline__ void hme_search_multi(const HBlk &blk, HJob *jobs, int n, HPlan *pl, uint8_t *arena) {
     if (n <= 0) return;
-    bool all_points = true;
-    for (int j = 0; j < n; ++j) all_points = all_points && jobs[j].sa_w == 1 && jobs[j].sa_h == 1;
-    if (all_points) {
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int nb = blk.nb;
+    // ---- geometry: one thread per job
+    bool is_point = true;
+    if (tid < n) {
+        const HJob &job = jobs[tid];
+        is_point = job.sa_w == 1 && job.sa_h == 1;
+        HGeo g;
+        if (job.sa_w <= 0 || job.sa_h <= 0) {
+            hme_geo(blk, 1, 1, 0, g);
+            g.n_items = g.stage_units = g.scan_n = 0;
+            g.need = 0;
+            g.big = 0;
+        } else {
+            hme_geo(blk, job.sa_w, job.sa_h, job.skip_even, g);
+        }
+        pl->geo[tid] = g;
+    }
+    if (__syncthreads_and(is_point)) {
         hme_points(blk, jobs, n);
         return;
     }
-    const int nbx = (blk.bw + 15) >> 4, nb = nbx * ((blk.nrows + 7) >> 3);
-    const uint32_t mg_nb = magic_div((uint32_t)nb), mg_nbx = magic_div((uint32_t)nbx);
-    const int extra_rows = (blk.nrows - 1) * blk.row_step;
-    int j0 = 0;
-    while (j0 < n) {
-        // ---- pack jobs [j0, j1) (uniform: every thread computes the same plan)
-        uint32_t used = 0;
-        int j1 = j0, total_items = 0;
-        __syncthreads(); // arena + geo are free
-        while (j1 < n) {
-            HGeo g;
-            const HJob &job = jobs[j1];
-            if (job.sa_w <= 0 || job.sa_h <= 0) {
-                if (threadIdx.x == 0) { g.n_items = 0; g.bh = 0; g.sa_w = 0; g.G = 2; g.xt_n = 1; geo[j1] = g; }
-                ++j1;
-                continue;
+    // ---- grouping: warp 0, lane j <-> job j
+    if (tid < 32) {
+        const unsigned full = 0xffffffffu;
+        const bool valid = lane < n;
+        HGeo *g = &pl->geo[valid ? lane : 0];
+        const uint32_t need = valid ? g->need : 0u, copies = valid ? (uint32_t)g->copy_bytes * 4u : 0u;
+        const bool big = valid && g->big;
+        const int su = valid ? g->stage_units : 0, ni = valid ? g->n_items : 0, sc = valid ? g->scan_n : 0;
+        int start = 0, ng = 0;
+        while (start < n) {
+            const bool from = valid && lane >= start;
+            uint32_t ps = from ? need : 0u;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(full, ps, o);
+                if (lane >= o) ps += t;
             }
-            const uint32_t need = hme_geo(blk, job.sa_w, job.sa_h, job.skip_even, g);
-            if (need > SVTME_ARENA_BYTES || g.n_items >= 65536) break; // needs tiling: single-job path
-            if (used + need > SVTME_ARENA_BYTES || total_items + g.n_items >= (1 << 20)) break;
-            g.arena_off = used;
-            g.sad_off = used + (uint32_t)g.copy_bytes * 4u;
-            g.x0 = 0;
-            g.y0 = 0;
-            if (threadIdx.x == 0) geo[j1] = g;
-            used += need;
-            total_items += g.n_items;
-            ++j1;
+            const unsigned brk = __ballot_sync(full, from && (big || ps > SVTME_ARENA_BYTES));
+            int end = brk ? __ffs(brk) - 1 : n;
+            const int first_big = end == start;
+            if (first_big) end = start + 1;
+            const bool in = valid && lane >= start && lane < end;
+            uint32_t a0 = in ? copies : 0u;
+            int a1 = in ? su : 0, a2 = in ? ni : 0, a3 = in ? sc : 0;
+            uint32_t p0 = a0;
+            int p1 = a1, p2 = a2, p3 = a3;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t0 = __shfl_up_sync(full, p0, o);
+                const int t1 = __shfl_up_sync(full, p1, o), t2 = __shfl_up_sync(full, p2, o), t3 = __shfl_up_sync(full, p3, o);
+                if (lane >= o) { p0 += t0; p1 += t1; p2 += t2; p3 += t3; }
+            }
+            const uint32_t tot0 = __shfl_sync(full, p0, 31);
+            const int tot1 = __shfl_sync(full, p1, 31), tot2 = __shfl_sync(full, p2, 31), tot3 = __shfl_sync(full, p3, 31);
+            if (in && !first_big) {
+                g->arena_off = p0 - a0;
+                g->stage_base = p1 - a1;
+                g->item_base = p2 - a2;
+                g->scan_base = p3 - a3;
+                g->sad_off = tot0 + 4u * (uint32_t)(p3 - a3);
+            }
+            if (lane == 0) pl->grp[ng] = HGroup{start, end, first_big, tot1, tot2, tot3};
+            ++ng;
+            start = end;
         }
-        if (j1 == j0) { // the next job does not fit as a whole
-            hme_search(blk, &jobs[j0], arena);
-            ++j0;
+        if (lane == 0) pl->n_groups = ng;
+    }
+    __syncthreads();
+    const int n_groups = pl->n_groups;
+    for (int gi = 0; gi < n_groups; ++gi) {
+        const HGroup G = pl->grp[gi];
+        if (G.big) {
+            hme_search(blk, &jobs[G.j0], arena);
             continue;
         }
-        __syncthreads(); // geo published
-        // ---- stage every window of the group, clear the SAD buffers
-        for (int j = j0; j < j1; ++j) {
-            const HGeo &g = geo[j];
-            if (g.n_items == 0) continue;
-            stage_window4(arena + g.arena_off, jobs[j].ref, jobs[j].stride, g.bh + extra_rows, g.m, 0, g.copy_bytes);
-            if (nb > 1) {
-                uint32_t *sadbuf = reinterpret_cast<uint32_t *>(arena + g.sad_off);
-                for (int i = threadIdx.x; i < g.bh * g.sa_w; i += SVTME_THREADS) sadbuf[i] = 0;
+        if (G.item_total == 0) continue;
+        if (gi) __syncthreads(); // the previous group is done with the arena
+        const HGeo *geo = pl->geo;
+        // ---- staging, four chunks per thread in flight
+        {
+            constexpr int U = 4;
+            int cj = G.j0;
+            for (int base = tid; base < G.stage_total; base += U * SVTME_THREADS) {
+                uint32_t w[U][6], mis[U];
+                uint8_t *dst[U];
+                int cb[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int i = base + u * SVTME_THREADS;
+                    if (i < G.stage_total) {
+                        while (i >= geo[cj].stage_base + geo[cj].stage_units) ++cj;
+                        const HGeo &g = geo[cj];
+                        const int il = i - g.stage_base;
+                        const int R = (int)__umulhi((uint32_t)il, g.mg_cpr), k = il - R * g.cpr;
+                        stage_unit_load(jobs[cj].ref + (size_t)R * jobs[cj].stride, k, w[u], mis[u]);
+                        dst[u] = arena + g.arena_off + ((size_t)(R * g.m + k) << 4);
+                        cb[u] = g.copy_bytes;
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u)
+                    if (base + u * SVTME_THREADS < G.stage_total) stage_unit_store(dst[u], cb[u], w[u], mis[u]);
             }
         }
+        uint32_t *sadreg = reinterpret_cast<uint32_t *>(arena + geo[G.j0].sad_off);
+        for (int i = tid; i < G.scan_total; i += SVTME_THREADS) sadreg[i] = 0;
         __syncthreads();
-        // ---- one flattened item list over the group
+        // ---- search items
         {
             SrcRegs sr;
             sr.cached_b = -1;
             sr.rows_here = 0;
             unsigned long long best = ~0ULL;
-            int cj = j0, cbase = 0;
-            for (int it = threadIdx.x; it < total_items; it += SVTME_THREADS) {
-                while (it >= cbase + geo[cj].n_items) {
-                    if (nb == 1 && best != ~0ULL) {
-                        if (best < HME_KEY_INIT) atomicMin(&jobs[cj].key, best);
-                        best = ~0ULL;
-                    }
-                    cbase += geo[cj].n_items;
-                    ++cj;
+            int cj = G.j0, bj = -1;
+            for (int it = tid; it < G.item_total; it += SVTME_THREADS) {
+                while (it >= geo[cj].item_base + geo[cj].n_items) ++cj;
+                if (nb == 1 && cj != bj) {
+                    if (bj >= 0) flush_key(jobs, bj, best);
+                    best = ~0ULL;
+                    bj = cj;
                 }
-                hme_item_any(blk, geo[cj], arena, it - cbase, nb, nbx, mg_nb, mg_nbx, sr, best);
+                hme_item_any(blk, geo[cj], arena, it - geo[cj].item_base, sr, best);
             }
-            if (nb == 1 && best < HME_KEY_INIT) atomicMin(&jobs[cj].key, best);
+            if (nb == 1 && bj >= 0) flush_key(jobs, bj, best);
         }
+        // ---- multi-sub-block blocks: positions' SADs were summed in the SAD buffer
         if (nb > 1) {
             __syncthreads();
-            for (int j = j0; j < j1; ++j) {
-                const HGeo &g = geo[j];
-                if (g.n_items == 0) continue;
-                const uint32_t *sadbuf = reinterpret_cast<const uint32_t *>(arena + g.sad_off);
-                const uint32_t mg_wb = magic_div((uint32_t)g.sa_w);
-                unsigned long long best = ~0ULL;
-                for (int i = threadIdx.x; i < g.bh * g.sa_w; i += SVTME_THREADS) {
-                    const int y = (int)__umulhi((uint32_t)i, mg_wb), x = i - y * g.sa_w;
-                    if (g.skip_even && !(y & 1)) continue;
-                    unsigned long long k = ((unsigned long long)sadbuf[i] << 32) | ((unsigned)y << 16) | (unsigned)x;
-                    best = k < best ? k : best;
+            unsigned long long best = ~0ULL;
+            int cj = G.j0, bj = -1;
+            for (int i = tid; i < G.scan_total; i += SVTME_THREADS) {
+                while (i >= geo[cj].scan_base + geo[cj].scan_n) ++cj;
+                if (cj != bj) {
+                    if (bj >= 0) flush_key(jobs, bj, best);
+                    best = ~0ULL;
+                    bj = cj;
                 }
-                if (best < HME_KEY_INIT) atomicMin(&jobs[j].key, best);
+                const HGeo &g = geo[cj];
+                const int il = i - g.scan_base;
+                const int y = (int)__umulhi((uint32_t)il, g.mg_wb), x = il - y * g.sa_w;
+                if (g.skip_even && !(y & 1)) continue;
+                const unsigned long long k = ((unsigned long long)sadreg[i] << 32) | ((unsigned)y << 16) | (unsigned)x;
+                best = k < best ? k : best;
             }
+            if (bj >= 0) flush_key(jobs, bj, best);
         }
-        j0 = j1;
     }
     __syncthreads();
 }
@@ -499,7 +653,7 @@ __device__ __forceinline__ void fp_butterfly(uint32_t (&v)[G], int b, int &joff3
 }
 
 template <int G>
-__device__ __forceinline__ void fp_tile(const uint8_t *src64, const uint8_t *arena, int copy_bytes, int m, int tw, int th,
+__device__ __noinline__ void fp_tile(const uint8_t *src64, const uint8_t *arena, int copy_bytes, int m, int tw, int th,
                                         bool sub_sad, FpTables *tab) {
     const int tid = threadIdx.x, b = tid & 15, c = (tid >> 4) & 3, yl = tid >> 6;
     const int bx = ((b >> 2) & 1) * 2 + (b & 1), by = ((b >> 3) & 1) * 2 + ((b >> 1) & 1);
@@ -614,7 +768,7 @@ __device__ __forceinline__ void fp_tile(const uint8_t *src64, const uint8_t *are
 // block(0,0) at search position (0,0). (ox, oy): MV of search position (0,0). order_base: rank of
 // position (0,0) in the reference's evaluation order (see FpTables). src64: shared memory, 64x64
 // source block with row stride 64.
-__device__ void fullpel_search(const uint8_t *src64, const uint8_t *ref0, int ref_stride, int ox, int oy, int sa_w,
+__device__ __noinline__ void fullpel_search(const uint8_t *src64, const uint8_t *ref0, int ref_stride, int ox, int oy, int sa_w,
                                int sa_h, bool sub_sad, uint32_t order_base, FpTables *tab, uint8_t *arena) {
     if (sa_w <= 0 || sa_h <= 0) return;
     const int G = sa_w <= 8 ? 2 : (sa_w <= 16 ? 4 : 8);
@@ -631,7 +785,7 @@ __device__ void fullpel_search(const uint8_t *src64, const uint8_t *ref0, int re
             const int copy_chunks = rows * m + 4 * ((rows - 1) >> 4) + 4;
             const int copy_bytes = copy_chunks * 16;
             __syncthreads();
-            stage_window4(arena, ref0 + (size_t)ty0 * ref_stride + tx0, ref_stride, rows, m, 4, copy_bytes);
+            stage_window4(arena, ref0 + (size_t)ty0 * ref_stride + tx0, ref_stride, rows, m, 4, copy_bytes, words);
             for (int i = threadIdx.x; i < SVTME_PU_COUNT; i += SVTME_THREADS) tab->tile_best[i] = ~0u;
             __syncthreads();
             if (G == 2)
@@ -663,7 +817,7 @@ __device__ void fullpel_search(const uint8_t *src64, const uint8_t *ref0, int re
 // motion_estimation.c:1393-1425, i.e. open_loop_me_get_search_point_results_block): no staging.
 // Thread t owns two (SUB_SAD: one) rows of 8x8 block e = t >> 2, with e = 4 * slot16 + k in the
 // table's own order, so 8x8 / 16x16 sums are shuffles and only 32x32 / 64x64 go through smem.
-__device__ void fullpel_probe(const uint8_t *src64, const uint8_t *ref0, int ref_stride, int mvx, int mvy, bool sub_sad,
+__device__ __noinline__ void fullpel_probe(const uint8_t *src64, const uint8_t *ref0, int ref_stride, int mvx, int mvy, bool sub_sad,
                               uint32_t order, FpTables *tab) {
     const int tid = threadIdx.x, e = tid >> 2, q = tid & 3;
     const int b = e >> 2, k = e & 3;

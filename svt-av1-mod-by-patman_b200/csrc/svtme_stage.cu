@@ -13,7 +13,7 @@
 #define NL SVTME_NL
 #define NR SVTME_NR
 #define MAXU32 0xFFFFFFFFu
-#define MAX_JOBS 32
+#define MAX_JOBS SVTME_MAX_JOBS
 
 struct PreHme {
     uint16_t sa_w, sa_h;
@@ -47,7 +47,7 @@ struct StageState {
     uint32_t me_distortion[SVTME_PU_COUNT];
     FpTables tab;
     HJob jobs[MAX_JOBS];
-    HGeo geo[MAX_JOBS];
+    HPlan plan;
     JobMeta meta[MAX_JOBS];
     int n_jobs;
     // integer-search hand-over between plan steps
@@ -837,6 +837,7 @@ __device__ void finish_b64(StageState *s, const DevJob &J, uint32_t b64, const u
 // ---------------------------------------------------------------- the kernel
 struct StageSmem {
     StageState st;
+    DevJob job; // this picture's job descriptor, copied from global memory once
     __align__(16) uint8_t src64[64 * 64];
     __align__(16) uint8_t src32[32 * 32];
     __align__(16) uint8_t src16[16 * 16];
@@ -853,7 +854,7 @@ int svtme_stage_smem_bytes() { return (int)sizeof(StageSmem); }
 
 __device__ void run_jobs(StageState *s, const HBlk &blk, uint8_t *arena) {
     const int n = s->n_jobs; // published by T0
-    hme_search_multi(blk, s->jobs, n, s->geo, arena);
+    hme_search_multi(blk, s->jobs, n, &s->plan, arena);
     if (threadIdx.x == 0) {
         unsigned long long w = 0;
         for (int j = 0; j < n; ++j) {
@@ -868,10 +869,17 @@ __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob
     extern __shared__ __align__(16) uint8_t smem_raw[];
     StageSmem *sm = reinterpret_cast<StageSmem *>(smem_raw);
     StageState *s = &sm->st;
-    const DevJob &J = jobs[blockIdx.x / b64_per_job];
+    const int tid = threadIdx.x;
+    {
+        static_assert(sizeof(DevJob) % 4 == 0, "DevJob is copied as 32-bit words");
+        const uint32_t *gsrc = reinterpret_cast<const uint32_t *>(&jobs[blockIdx.x / b64_per_job]);
+        uint32_t *sdst = reinterpret_cast<uint32_t *>(&sm->job);
+        for (int i = tid; i < (int)(sizeof(DevJob) / 4); i += SVTME_THREADS) sdst[i] = __ldg(gsrc + i);
+    }
+    __syncthreads();
+    const DevJob &J = sm->job;
     const uint32_t b64 = blockIdx.x % b64_per_job;
     const SvtMeParams &p = J.prm;
-    const int tid = threadIdx.x;
     long long t_prev = clock64(), t_start = t_prev;
     unsigned long long ph[SVTME_PHASES];
 #pragma unroll
@@ -920,10 +928,10 @@ __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob
 
     const int b64_w = s->b64_w, b64_h = s->b64_h;
     const bool hme_full = p.hme_search_method == 1;
-    const HBlk blk_zz = {sm->src64, 128, b64_w, b64_h >> 1, 2};
-    const HBlk blk_l0 = {sm->src16, hme_full ? 16 : 32, b64_w >> 2, hme_full ? (b64_h >> 2) : (b64_h >> 3), hme_full ? 1 : 2};
-    const HBlk blk_l1 = {sm->src32, hme_full ? 32 : 64, b64_w >> 1, hme_full ? (b64_h >> 1) : (b64_h >> 2), hme_full ? 1 : 2};
-    const HBlk blk_l2 = {sm->src64, hme_full ? 64 : 128, b64_w, hme_full ? b64_h : (b64_h >> 1), hme_full ? 1 : 2};
+    const HBlk blk_zz = make_hblk(sm->src64, 128, b64_w, b64_h >> 1, 2);
+    const HBlk blk_l0 = make_hblk(sm->src16, hme_full ? 16 : 32, b64_w >> 2, hme_full ? (b64_h >> 2) : (b64_h >> 3), hme_full ? 1 : 2);
+    const HBlk blk_l1 = make_hblk(sm->src32, hme_full ? 32 : 64, b64_w >> 1, hme_full ? (b64_h >> 1) : (b64_h >> 2), hme_full ? 1 : 2);
+    const HBlk blk_l2 = make_hblk(sm->src64, hme_full ? 64 : 128, b64_w, hme_full ? b64_h : (b64_h >> 1), hme_full ? 1 : 2);
 
     PHASE(SVTME_PH_SETUP);
     // ---- hme_b64 :2511-2545
@@ -1056,6 +1064,7 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, cu
 // ---------------------------------------------------------------- kernel-test entry points
 struct TestSmem {
     HJob job;
+    HPlan plan;
     FpTables tab;
     __align__(16) uint8_t src[64 * 64];
     __align__(16) uint8_t arena[SVTME_ARENA_BYTES];
@@ -1082,8 +1091,8 @@ __global__ void __launch_bounds__(SVTME_THREADS) sad_loop_test_kernel(const uint
         sm->job.key = HME_KEY_INIT;
     }
     __syncthreads();
-    const HBlk b2 = {sm->src, 64, bw, bh, row_step};
-    hme_search(b2, &sm->job, sm->arena);
+    const HBlk b2 = make_hblk(sm->src, 64, bw, bh, row_step);
+    hme_search_multi(b2, &sm->job, 1, &sm->plan, sm->arena);
     if (threadIdx.x == 0) *out = sm->job.key;
 }
 

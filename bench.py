@@ -129,6 +129,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default="1080p_p8", choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--sharding", default="stream", choices=["stream", "picture"],
+                    help="N>1: 'stream' = one independent stream per rank (weak scaling, BASELINE configs[4]); "
+                         "'picture' = ONE stream, pictures dealt round-robin to the ranks (strong scaling, configs[3])")
     ap.add_argument("--cpu-pictures", type=int, default=16, help="pictures in the bounded CPU sample")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="repeat the CPU sample for about this long")
     args = ap.parse_args()
@@ -143,7 +146,8 @@ def main():
                                                                              wl["n_l1"], wl["levels"]),
               "b64_per_frame": n_b64, "me_pictures_per_step": F - 1, "pyramids_per_step": F,
               "l2": "inputs larger than L2: each step touches %.0f MB of frames+pyramids (L2 126 MB)" % (F * W * H * 2.7 / 1e6),
-              "sharding": "one independent stream per GPU (weak)"}
+              "sharding": "one independent stream per GPU (weak)" if args.sharding == "stream" else
+                          "one stream, pictures round-robin over GPUs in decode order, each GPU builds the pyramids it needs (strong)"}
     abi = importlib.import_module(PKG + ".abi")
     gop = importlib.import_module(PKG + ".gop")
     synth = importlib.import_module(PKG + ".synth")
@@ -186,7 +190,9 @@ def main():
         dist.init_process_group("nccl", rank=rank, world_size=world)
     torch.cuda.set_device(local_rank)
     me = importlib.import_module(PKG + ".me")
-    seq = synth.synth_sequence(W, H, F, seed=1 + rank)
+    shard = importlib.import_module(PKG + ".shard")
+    by_picture = args.sharding == "picture" and world > 1
+    seq = synth.synth_sequence(W, H, F, seed=1 if by_picture else 1 + rank)
     host = torch.from_numpy(seq).pin_memory()
     dev = host.to("cuda", non_blocking=False)
     ses = me.MeSession(local_rank, W, H, capacity=F)
@@ -194,17 +200,23 @@ def main():
     torch.cuda.set_stream(stream)
     ses.set_stream(stream.cuda_stream)
     specs = build_specs(abi, gop, wl, ses.derive_params)
+    if by_picture:
+        mine = shard.rank_plan(len(specs), world, rank)
+        frames_here = shard.pictures_for(specs, mine)
+        specs = [specs[i] for i in mine]
+    else:
+        frames_here = list(range(F))
     jobs, outs = ses.make_jobs(specs, deep=False)
     frame_bytes = W * H
     d2h_bytes = sum(a.nbytes for o in outs for a in o.values())
 
     def step_resident():
-        for f in range(F):
+        for f in frames_here:
             ses.put_picture_device(f, dev.data_ptr() + f * frame_bytes, W)
         ses.launch_jobs(jobs)
 
     def step_e2e():
-        for f in range(F):
+        for f in frames_here:
             ses.lib.svtme_put_picture(ses.h, f, host.data_ptr() + f * frame_bytes, W)
         ses.run_jobs(jobs)
 
@@ -247,9 +259,10 @@ def main():
     sampler.stop_flag = True
     sampler.join(timeout=2)
     ms_step = ms_total / args.steps
-    sbs_step = (F - 1) * n_b64
-    value = world * sbs_step / (ms_step * 1e-3)
-    e2e_val = world * sbs_step / (ms_e2e / args.steps * 1e-3)
+    sbs_step = (F - 1) * n_b64          # b64 of one whole stream
+    n_streams = 1 if by_picture else world
+    value = n_streams * sbs_step / (ms_step * 1e-3)
+    e2e_val = n_streams * sbs_step / (ms_e2e / args.steps * 1e-3)
 
     if rank == 0:
         peaks = {}
@@ -266,11 +279,13 @@ def main():
         alg_bytes = sum((1 + len(set(refs.values()))) * W * H * 1.3125 for _, _, refs in specs) + d2h_bytes
         cpu = cpu_reference_run(wl, specs, seq, args.cpu_pictures, threads, args.cpu_seconds)
         line = {"metric": "open-loop ME SBs/sec", "value": value, "unit": "SB/s", "n_gpus": world, "steps": args.steps,
-                "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+                "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True,
+                "scaling": "strong" if by_picture else "weak",
                 "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": config,
-                "frames_per_s": world * F / (ms_step * 1e-3),
-                "e2e": {"value": e2e_val, "unit": "SB/s", "h2d_bytes_per_step": F * frame_bytes, "d2h_bytes_per_step": d2h_bytes,
-                        "frames_per_s": world * F / (ms_e2e / args.steps * 1e-3), "ms_per_step": ms_e2e / args.steps},
+                "frames_per_s": n_streams * F / (ms_step * 1e-3),
+                "e2e": {"value": e2e_val, "unit": "SB/s", "h2d_bytes_per_step": len(frames_here) * frame_bytes,
+                        "d2h_bytes_per_step": d2h_bytes,
+                        "frames_per_s": n_streams * F / (ms_e2e / args.steps * 1e-3), "ms_per_step": ms_e2e / args.steps},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "int_alu", "kernel": "me_stage_kernel", "achieved": int_achieved, "peak": int_peak,
                              "unit": "Tbyte-SAD/s", "frac": int_achieved / int_peak if int_peak else None, "traffic": None,
@@ -278,7 +293,7 @@ def main():
                              "work_byte_ops_per_launch": work_ops, "kernel_ms": kernel_ms,
                              "kernel_share_of_step": kernel_ms / ms_step,
                              "phase_share": {k: round(v / max(1, phases["total"]), 4) for k, v in phases.items() if k != "total"},
-                             "cycles_per_b64": phases["total"] / max(1, sbs_step)},
+                             "cycles_per_b64": phases["total"] / max(1, len(specs) * n_b64)},
                 "roofline_hbm": {"bound": "hbm", "kernel": "me_stage_kernel", "achieved": alg_bytes / (kernel_ms * 1e-3) / 1e9,
                                  "peak": hbm_peak, "unit": "GB/s", "frac": alg_bytes / (kernel_ms * 1e-3) / 1e9 / hbm_peak,
                                  "traffic": None, "peak_source": hbm_src},

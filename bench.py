@@ -292,7 +292,9 @@ def main():
                              "peak_source": "VABSDIFF4.U8.ACC issue rate measured live in this run (%.0f Ginst/s x 4 bytes)" % vsad,
                              "work_byte_ops_per_launch": work_ops, "kernel_ms": kernel_ms,
                              "kernel_share_of_step": kernel_ms / ms_step,
-                             "phase_share": {k: round(v / max(1, phases["total"]), 4) for k, v in phases.items() if k != "total"},
+                             "phase_share": {k: round(v / max(1, phases["total"]), 4) for k, v in phases.items()
+                                             if k not in ("total", "n_hme_groups")},
+                             "hme_groups_per_b64": phases["n_hme_groups"] / max(1, len(specs) * n_b64),
                              "cycles_per_b64": phases["total"] / max(1, len(specs) * n_b64)},
                 "roofline_hbm": {"bound": "hbm", "kernel": "me_stage_kernel", "achieved": alg_bytes / (kernel_ms * 1e-3) / 1e9,
                                  "peak": hbm_peak, "unit": "GB/s", "frac": alg_bytes / (kernel_ms * 1e-3) / 1e9 / hbm_peak,

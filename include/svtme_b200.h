@@ -224,8 +224,9 @@ int svtme_last_work_ops(SvtMeHandle *h, uint64_t *ops);
 /* Profiling aid (no reference counterpart): SM cycles thread 0 of each b64 CTA spent per phase of
  * svt_aom_motion_estimation_b64 in the last launch, summed over CTAs. Slots: 0 setup, 1 zz-SAD,
  * 2 pre-HME, 3 HME L0, 4 HME L1, 5 HME L2, 6 search centre + HME pruning, 7 check_00_center,
- * 8 8x8-variance probe, 9 full-pel search, 10 candidates + statistics, 11 total. */
-#define SVTME_PHASES 12
+ * 8 8x8-variance probe, 9 full-pel search, 10 candidates + statistics, 11 total; cross-cuts: 12 all thread-0 plan/post steps, 13 HME engine,
+ * 14 full-pel engine + probe, 15 number of HME groups (a count, not cycles). */
+#define SVTME_PHASES 16
 int svtme_last_phase_cycles(SvtMeHandle *h, uint64_t *cycles, uint32_t n);
 /* Measured issue rate (Ginst/s, whole GPU) of VABSDIFF4.U8.ACC, 4 byte-SADs per instruction: the
  * integer-SAD roofline denominator (not part of MEASURED_PEAKS.json). */

@@ -54,9 +54,10 @@ struct DevJob {
 };
 
 // phase slots behind work_ops (cycle sums of thread 0, one CTA per b64)
-#define SVTME_PHASES 12
+#define SVTME_PHASES 16
 enum { SVTME_PH_SETUP = 0, SVTME_PH_ZZ, SVTME_PH_PREHME, SVTME_PH_L0, SVTME_PH_L1, SVTME_PH_L2, SVTME_PH_CENTRE,
-       SVTME_PH_INT_CHECK, SVTME_PH_INT_PROBE, SVTME_PH_INT_MAIN, SVTME_PH_FINISH, SVTME_PH_TOTAL };
+       SVTME_PH_INT_CHECK, SVTME_PH_INT_PROBE, SVTME_PH_INT_MAIN, SVTME_PH_FINISH, SVTME_PH_TOTAL,
+       SVTME_PH_SCALAR /* all thread-0 plan/post steps */, SVTME_PH_HME_ENGINE, SVTME_PH_FP_ENGINE, SVTME_PH_HME_GROUPS /* count */ };
 
 static inline int up128(int v) { return (v + 127) & ~127; }
 

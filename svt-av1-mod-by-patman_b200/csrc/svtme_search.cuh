@@ -19,8 +19,16 @@
 #pragma once
 #include "svtme_common.cuh"
 
-#define SVTME_THREADS 256
-#define SVTME_ARENA_BYTES (80 * 1024)
+#ifndef SVTME_THREADS
+#define SVTME_THREADS 128          // CTA size; 64-thread groups share one row lane of the full-pel engine
+#endif
+#ifndef SVTME_CTAS_PER_SM
+#define SVTME_CTAS_PER_SM 4
+#endif
+#ifndef SVTME_ARENA_BYTES
+#define SVTME_ARENA_BYTES (32 * 1024)
+#endif
+#define SVTME_FP_YL (SVTME_THREADS / 64) // row lanes of the full-pel engine
 
 __device__ __forceinline__ uint32_t vsad4(uint32_t a, uint32_t b, uint32_t acc) {
     uint32_t r;
@@ -122,7 +130,8 @@ struct HGeo {
     int copy_bytes, m;
     int sa_w, bh;        // positions in this tile
     int x0, y0;          // tile origin inside the job's search area
-    int xt_n, n_items, G, skip_even;
+    int xt_n, n_items, G, skip_even, variant;
+    int ref_off;         // byte offset of the tile origin from the job's ref pointer
     int rows, cpr;       // staged rows, 16-byte chunks staged per copy row
     int stage_units;     // rows * cpr
     int scan_n;          // positions whose SAD is summed over sub-blocks in the SAD buffer (nb > 1)
@@ -174,75 +183,89 @@ __device__ __forceinline__ void load_src_regs(const HBlk &blk, int b, int bxi, i
     }
 }
 
-// One work item = G same-phase positions of one row against one 16x8 source sub-block.
-template <int G>
+// One work item = G same-phase x-positions times TY y-positions (spaced row_step apart, so that
+// they share reference rows) against one 16x8 source sub-block. The window is staged ONCE,
+// byte-aligned to the search origin; phase c = x & 3 is applied in registers with funnel shifts
+// (G+4 SHF per reference row, amortised over 4*G*TY VABSDIFF4).
+template <int G, int TY, bool MASKED>
 __device__ __forceinline__ void hme_item(const HBlk &blk, const HGeo &g, uint8_t *arena, int it, SrcRegs &sr,
                                          unsigned long long &best) {
-    const int nb = blk.nb, nbx = blk.nbx;
+    const int nb = blk.nb, nbx = blk.nbx, rs = blk.row_step;
     int t = nb == 1 ? it : (int)__umulhi((uint32_t)it, blk.mg_nb);
     const int b = it - t * nb;
     const int c = t & 3;
     t >>= 2;
     const int xt_n = g.xt_n;
-    const int y = xt_n == 1 ? t : (int)__umulhi((uint32_t)t, g.mg_xt);
-    const int xt = t - y * xt_n;
+    const int yt = xt_n == 1 ? t : (int)__umulhi((uint32_t)t, g.mg_xt);
+    const int xt = t - yt * xt_n;
     const int byi = nbx == 1 ? b : (int)__umulhi((uint32_t)b, blk.mg_nbx);
     const int bxi = b - byi * nbx;
     if (b != sr.cached_b) load_src_regs(blk, b, bxi, byi, sr);
-    const bool masked = (blk.bw & 15) != 0;
-    uint32_t acc[G];
+    const int yb = (yt & (rs - 1)) + (yt >> (rs - 1)) * TY * rs; // rs is 1 or 2
+    uint32_t acc[TY][G];
 #pragma unroll
-    for (int j = 0; j < G; ++j) acc[j] = 0;
-    const int q0 = xt * G + 4 * bxi; // first word of copy c this item needs
-    const int m16 = g.m << 4;
-    const uint8_t *rp = arena + g.arena_off + (size_t)c * g.copy_bytes + 4 * q0 + (size_t)(y + 8 * byi * blk.row_step) * m16;
-    const int rstep = blk.row_step * m16;
+    for (int ty = 0; ty < TY; ++ty)
 #pragma unroll
-    for (int r = 0; r < 8; ++r) {
-        if (r < sr.rows_here) {
-            uint32_t w[G + 4];
+        for (int j = 0; j < G; ++j) acc[ty][j] = 0;
+    const int pitch = g.m << 4;
+    const uint8_t *base = arena + g.arena_off + 4 * (xt * G + 4 * bxi);
+    const uint32_t sh = 8 * c;
+    const int row0 = yb + 8 * byi * rs;
+#pragma unroll
+    for (int rho = 0; rho < TY + 7; ++rho) {
+        const int row = row0 + rho * rs;
+        if (rho < sr.rows_here + TY - 1 && row < g.rows) {
+            const uint8_t *rp = base + row * pitch + ((row >> 3) << 4);
+            uint32_t w[G + 5];
             if (G == 2) {
 #pragma unroll
                 for (int k = 0; k < 3; ++k) {
-                    uint2 v = *reinterpret_cast<const uint2 *>(rp + 8 * k);
+                    const uint2 v = *reinterpret_cast<const uint2 *>(rp + 8 * k);
                     w[2 * k] = v.x; w[2 * k + 1] = v.y;
                 }
             } else {
 #pragma unroll
-                for (int k = 0; k < (G + 3 + 3) / 4; ++k) {
-                    uint4 v = *reinterpret_cast<const uint4 *>(rp + 16 * k);
-                    if (4 * k + 0 < G + 4) w[4 * k + 0] = v.x;
-                    if (4 * k + 1 < G + 4) w[4 * k + 1] = v.y;
-                    if (4 * k + 2 < G + 4) w[4 * k + 2] = v.z;
-                    if (4 * k + 3 < G + 4) w[4 * k + 3] = v.w;
+                for (int k = 0; k < (G + 4) / 4; ++k) {
+                    const uint4 v = *reinterpret_cast<const uint4 *>(rp + 16 * k);
+                    w[4 * k] = v.x; w[4 * k + 1] = v.y; w[4 * k + 2] = v.z; w[4 * k + 3] = v.w;
                 }
             }
-            rp += rstep;
-            if (masked) {
+            w[G + 4] = *reinterpret_cast<const uint32_t *>(rp + 4 * (G + 4));
 #pragma unroll
-                for (int j = 0; j < G; ++j)
+            for (int i = 0; i < G + 4; ++i) w[i] = __funnelshift_r(w[i], w[i + 1], sh);
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) acc[j] = vsad4(sr.s[r][i], w[j + i] & sr.msk[i], acc[j]);
-            } else {
+            for (int ty = 0; ty < TY; ++ty) {
+                const int r = rho - ty;
+                if (r >= 0 && r < 8) {
+                    if (r < sr.rows_here) {
 #pragma unroll
-                for (int j = 0; j < G; ++j)
+                        for (int j = 0; j < G; ++j)
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) acc[j] = vsad4(sr.s[r][i], w[j + i], acc[j]);
+                            for (int i = 0; i < 4; ++i)
+                                acc[ty][j] = vsad4(sr.s[r][i], MASKED ? (w[j + i] & sr.msk[i]) : w[j + i], acc[ty][j]);
+                    }
+                }
             }
         }
     }
-    const int yg = g.y0 + y;
-    if (g.skip_even && !(yg & 1)) return;
-    uint32_t *sadbuf = reinterpret_cast<uint32_t *>(arena + g.sad_off) + y * g.sa_w;
+    uint32_t *sadbuf = reinterpret_cast<uint32_t *>(arena + g.sad_off);
 #pragma unroll
-    for (int j = 0; j < G; ++j) {
-        const int x = xt * 4 * G + 4 * j + c;
-        if (x < g.sa_w) {
-            if (nb == 1) {
-                unsigned long long k = ((unsigned long long)acc[j] << 32) | ((unsigned)yg << 16) | (unsigned)(g.x0 + x);
-                best = k < best ? k : best;
-            } else {
-                atomicAdd(&sadbuf[x], acc[j]);
+    for (int ty = 0; ty < TY; ++ty) {
+        const int y = yb + ty * rs;
+        const int yg = g.y0 + y;
+        if (y < g.bh && !(g.skip_even && !(yg & 1))) {
+#pragma unroll
+            for (int j = 0; j < G; ++j) {
+                const int x = xt * 4 * G + 4 * j + c;
+                if (x < g.sa_w) {
+                    if (nb == 1) {
+                        const unsigned long long k =
+                            ((unsigned long long)acc[ty][j] << 32) | ((unsigned)yg << 16) | (unsigned)(g.x0 + x);
+                        best = k < best ? k : best;
+                    } else {
+                        atomicAdd(&sadbuf[y * g.sa_w + x], acc[ty][j]);
+                    }
+                }
             }
         }
     }
@@ -250,33 +273,37 @@ __device__ __forceinline__ void hme_item(const HBlk &blk, const HGeo &g, uint8_t
 
 __device__ __forceinline__ void hme_item_any(const HBlk &blk, const HGeo &g, uint8_t *arena, int it, SrcRegs &sr,
                                              unsigned long long &best) {
-    if (g.G == 8)
-        hme_item<8>(blk, g, arena, it, sr, best);
-    else if (g.G == 4)
-        hme_item<4>(blk, g, arena, it, sr, best);
-    else
-        hme_item<2>(blk, g, arena, it, sr, best);
+    // few variants on purpose: the unrolled bodies are large and the kernel must stay I-cache friendly
+    switch (g.variant) {
+    case 0: hme_item<2, 4, false>(blk, g, arena, it, sr, best); break;
+    case 1: hme_item<4, 4, false>(blk, g, arena, it, sr, best); break;
+    case 2: hme_item<8, 2, false>(blk, g, arena, it, sr, best); break;
+    default: hme_item<2, 1, true>(blk, g, arena, it, sr, best); break; // partial block width (rare)
+    }
 }
 
 // Tile geometry for a (sub)area of wb x hb positions; g.need = the arena bytes it takes.
 __device__ __forceinline__ void hme_geo(const HBlk &blk, int wb, int hb, int skip_even, HGeo &g) {
-    const int G = wb <= 8 ? 2 : (wb <= 16 ? 4 : 8);
+    const bool masked = (blk.bw & 15) != 0;
+    const int G = (wb <= 8 || masked) ? 2 : (wb <= 16 ? 4 : 8);
     const int tile_w = 4 * G;
-    const int vec_words = G == 2 ? 6 : ((G + 3 + 3) / 4) * 4;
     const int xt_n = (wb + tile_w - 1) / tile_w;
-    const int words = (xt_n - 1) * G + 4 * (blk.nbx - 1) + vec_words;
+    const int rs = blk.row_step;
+    const int rpp = (hb + rs - 1) / rs; // positions per row-parity class
+    const int TY = masked ? 1 : (G == 8 ? 2 : 4);
+    g.variant = masked ? 3 : (G == 2 ? 0 : (G == 4 ? 1 : 2));
+    const int words = (xt_n - 1) * G + 4 * (blk.nbx - 1) + G + 5;
     const int cpr = (words + 3) >> 2;
-    const int m = cpr | 1; // odd chunk stride: consecutive rows start in different bank groups
-    const int rows = hb + (blk.nrows - 1) * blk.row_step;
-    int copy_chunks = rows * m;
-    copy_chunks += (10 - (copy_chunks & 7)) & 7; // copy stride == 2 (mod 8) chunks
-    g.copy_bytes = copy_chunks * 16;
+    const int m = cpr | 1; // odd chunk pitch; plus one skew chunk every 8 rows (see hme_item)
+    const int rows = hb + (blk.nrows - 1) * rs;
+    g.copy_bytes = (rows * m + (rows >> 3) + 1) * 16;
     g.m = m;
     g.sa_w = wb;
     g.bh = hb;
     g.x0 = g.y0 = 0;
+    g.ref_off = 0;
     g.xt_n = xt_n;
-    g.n_items = hb * xt_n * 4 * blk.nb;
+    g.n_items = rs * ((rpp + TY - 1) / TY) * xt_n * 4 * blk.nb;
     g.G = G;
     g.skip_even = skip_even;
     g.rows = rows;
@@ -286,33 +313,29 @@ __device__ __forceinline__ void hme_geo(const HBlk &blk, int wb, int hb, int ski
     g.mg_xt = magic_div((uint32_t)xt_n);
     g.mg_cpr = magic_div((uint32_t)cpr);
     g.mg_wb = magic_div((uint32_t)wb);
-    g.need = (uint32_t)g.copy_bytes * 4u + (uint32_t)g.scan_n * 4u;
+    g.need = (uint32_t)g.copy_bytes + (uint32_t)g.scan_n * 4u;
     g.big = g.need > SVTME_ARENA_BYTES || g.n_items >= 65536 || g.stage_units >= 65536 || g.scan_n >= 65536;
     g.arena_off = 0;
-    g.sad_off = (uint32_t)g.copy_bytes * 4u;
+    g.sad_off = (uint32_t)g.copy_bytes;
     g.stage_base = g.item_base = g.scan_base = 0;
 }
 
-// Stage one 16-byte chunk of a window into its four phase copies: six aligned global words ->
-// v[t] = bytes 4t+mis.. (copy 0), then copies 1..3 are static funnel shifts of v.
-__device__ __forceinline__ void stage_unit_load(const uint8_t *__restrict__ row, int k, uint32_t (&w)[6], uint32_t &mis) {
+// Stage one 16-byte chunk of a window row: five aligned global words -> byte-aligned chunk.
+__device__ __forceinline__ void stage_unit_load(const uint8_t *__restrict__ row, int k, uint32_t (&w)[5], uint32_t &mis) {
     const uintptr_t ai = reinterpret_cast<uintptr_t>(row);
     const uint32_t *al = reinterpret_cast<const uint32_t *>(ai & ~(uintptr_t)3) + 4 * k;
     mis = (uint32_t)(ai & 3);
 #pragma unroll
-    for (int i = 0; i < 5; ++i) w[i] = __ldg(al + i);
-    w[5] = mis ? __ldg(al + 5) : 0u;
+    for (int i = 0; i < 4; ++i) w[i] = __ldg(al + i);
+    w[4] = mis ? __ldg(al + 4) : 0u;
 }
-__device__ __forceinline__ void stage_unit_store(uint8_t *dst, int copy_bytes, const uint32_t (&w)[6], uint32_t mis) {
-    uint32_t v[5];
-#pragma unroll
-    for (int t = 0; t < 5; ++t) v[t] = __funnelshift_r(w[t], w[t + 1], mis * 8);
-    *reinterpret_cast<uint4 *>(dst) = make_uint4(v[0], v[1], v[2], v[3]);
-#pragma unroll
-    for (int c = 1; c < 4; ++c)
-        *reinterpret_cast<uint4 *>(dst + (size_t)c * copy_bytes) =
-            make_uint4(__funnelshift_r(v[0], v[1], 8 * c), __funnelshift_r(v[1], v[2], 8 * c),
-                       __funnelshift_r(v[2], v[3], 8 * c), __funnelshift_r(v[3], v[4], 8 * c));
+__device__ __forceinline__ void stage_unit_store(uint8_t *dst, const uint32_t (&w)[5], uint32_t mis) {
+    const uint32_t sh = mis * 8;
+    *reinterpret_cast<uint4 *>(dst) = make_uint4(__funnelshift_r(w[0], w[1], sh), __funnelshift_r(w[1], w[2], sh),
+                                                 __funnelshift_r(w[2], w[3], sh), __funnelshift_r(w[3], w[4], sh));
+}
+__device__ __forceinline__ uint8_t *stage_dst(uint8_t *arena, const HGeo &g, int R, int k) {
+    return arena + g.arena_off + ((size_t)(R * g.m + (R >> 3) + k) << 4);
 }
 
 // Minimum of 64-bit keys over the lanes that are flushing the same job, one atomic per such set.
@@ -326,68 +349,6 @@ __device__ __forceinline__ void flush_key(HJob *jobs, int j, unsigned long long 
         const unsigned long long key = ((unsigned long long)mhi << 32) | mlo;
         if (key < HME_KEY_INIT) atomicMin(&jobs[j].key, key);
     }
-}
-
-// One svt_sad_loop_kernel of ANY size: the search area is tiled so that each tile fits the arena.
-// All threads of the CTA must call it with identical arguments; job lives in shared memory and
-// job->key must be HME_KEY_INIT on entry.
-__device__ __noinline__ void hme_search(const HBlk &blk, HJob *job, uint8_t *arena) {
-    const int sa_w = job->sa_w, sa_h = job->sa_h;
-    if (sa_w <= 0 || sa_h <= 0) return;
-    const int nb = blk.nb;
-    int wt = sa_w, bh = sa_h;
-    HGeo g;
-    for (;;) {
-        hme_geo(blk, wt, bh, job->skip_even, g);
-        if (!g.big) break;
-        const int tile_w = 4 * g.G;
-        if (bh > 8) bh = (bh + 1) / 2;
-        else if (wt > tile_w) wt = ((wt / 2 + tile_w - 1) / tile_w) * tile_w;
-        else if (bh > 1) bh = (bh + 1) / 2;
-        else break; // one row x one G-tile always fits
-    }
-    unsigned long long best = ~0ULL;
-    SrcRegs sr;
-    sr.cached_b = -1;
-    sr.rows_here = 0;
-    for (int x0 = 0; x0 < sa_w; x0 += wt) {
-        const int wb = min(wt, sa_w - x0);
-        for (int y0 = 0; y0 < sa_h; y0 += bh) {
-            const int hb = min(bh, sa_h - y0);
-            hme_geo(blk, wb, hb, job->skip_even, g);
-            g.x0 = x0;
-            g.y0 = y0;
-            uint32_t *sadbuf = reinterpret_cast<uint32_t *>(arena + g.sad_off);
-            __syncthreads(); // previous users of the arena are done
-            const uint8_t *g0 = job->ref + (size_t)y0 * job->stride + x0;
-            for (int i = threadIdx.x; i < g.stage_units; i += SVTME_THREADS) {
-                const int R = (int)__umulhi((uint32_t)i, g.mg_cpr), k = i - R * g.cpr;
-                uint32_t w[6], mis;
-                stage_unit_load(g0 + (size_t)R * job->stride, k, w, mis);
-                stage_unit_store(arena + ((size_t)(R * g.m + k) << 4), g.copy_bytes, w, mis);
-            }
-            for (int i = threadIdx.x; i < g.scan_n; i += SVTME_THREADS) sadbuf[i] = 0;
-            __syncthreads();
-            for (int it = threadIdx.x; it < g.n_items; it += SVTME_THREADS) hme_item_any(blk, g, arena, it, sr, best);
-            if (nb > 1) {
-                __syncthreads();
-                for (int i = threadIdx.x; i < g.scan_n; i += SVTME_THREADS) {
-                    const int yy = (int)__umulhi((uint32_t)i, g.mg_wb);
-                    const int y = y0 + yy, x = x0 + (i - yy * wb);
-                    if (job->skip_even && !(y & 1)) continue;
-                    unsigned long long k = ((unsigned long long)sadbuf[i] << 32) | ((unsigned)y << 16) | (unsigned)x;
-                    best = k < best ? k : best;
-                }
-            }
-        }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        unsigned long long v = __shfl_xor_sync(0xffffffffu, best, o);
-        best = v < best ? v : best;
-    }
-    if ((threadIdx.x & 31) == 0 && best < HME_KEY_INIT) atomicMin(&job->key, best);
-    __syncthreads();
 }
 
 // SAD of the block at ONE position per job (zz-SAD, check_00_center): no staging, one warp per
@@ -418,6 +379,119 @@ __device__ __noinline__ void hme_points(const HBlk &blk, HJob *jobs, int n) {
     __syncthreads();
 }
 
+// ---- group helpers (separate functions: separate register allocations)
+__device__ __noinline__ void hme_group_stage(const HJob *jobs, const HGeo *geo, const HGroup &G, uint8_t *arena) {
+    constexpr int U = 8; // chunks per thread in flight
+    const int tid = threadIdx.x;
+    int cj = G.j0;
+    for (int base = tid; base < G.stage_total; base += U * SVTME_THREADS) {
+        uint32_t w[U][5], mis[U];
+        uint8_t *dst[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int i = base + u * SVTME_THREADS;
+            if (i < G.stage_total) {
+                while (i >= geo[cj].stage_base + geo[cj].stage_units) ++cj;
+                const HGeo &g = geo[cj];
+                const int il = i - g.stage_base;
+                const int R = (int)__umulhi((uint32_t)il, g.mg_cpr), k = il - R * g.cpr;
+                stage_unit_load(jobs[cj].ref + g.ref_off + (size_t)R * jobs[cj].stride, k, w[u], mis[u]);
+                dst[u] = stage_dst(arena, g, R, k);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (base + u * SVTME_THREADS < G.stage_total) stage_unit_store(dst[u], w[u], mis[u]);
+    }
+    uint32_t *sadreg = reinterpret_cast<uint32_t *>(arena + geo[G.j0].sad_off);
+    for (int i = tid; i < G.scan_total; i += SVTME_THREADS) sadreg[i] = 0;
+}
+
+__device__ __noinline__ void hme_group_items(const HBlk &blk, HJob *jobs, const HGeo *geo, const HGroup &G, uint8_t *arena) {
+    const int nb = blk.nb;
+    SrcRegs sr;
+    sr.cached_b = -1;
+    sr.rows_here = 0;
+    unsigned long long best = ~0ULL;
+    int cj = G.j0, bj = -1;
+    for (int it = threadIdx.x; it < G.item_total; it += SVTME_THREADS) {
+        while (it >= geo[cj].item_base + geo[cj].n_items) ++cj;
+        if (nb == 1 && cj != bj) {
+            if (bj >= 0) flush_key(jobs, bj, best);
+            best = ~0ULL;
+            bj = cj;
+        }
+        hme_item_any(blk, geo[cj], arena, it - geo[cj].item_base, sr, best);
+    }
+    if (nb == 1 && bj >= 0) flush_key(jobs, bj, best);
+}
+
+__device__ __noinline__ void hme_group_scan(HJob *jobs, const HGeo *geo, const HGroup &G, uint8_t *arena) {
+    const uint32_t *sadreg = reinterpret_cast<const uint32_t *>(arena + geo[G.j0].sad_off);
+    unsigned long long best = ~0ULL;
+    int cj = G.j0, bj = -1;
+    for (int i = threadIdx.x; i < G.scan_total; i += SVTME_THREADS) {
+        while (i >= geo[cj].scan_base + geo[cj].scan_n) ++cj;
+        if (cj != bj) {
+            if (bj >= 0) flush_key(jobs, bj, best);
+            best = ~0ULL;
+            bj = cj;
+        }
+        const HGeo &g = geo[cj];
+        const int il = i - g.scan_base;
+        const int yl = (int)__umulhi((uint32_t)il, g.mg_wb);
+        const int y = g.y0 + yl, x = g.x0 + il - yl * g.sa_w;
+        if (g.skip_even && !(y & 1)) continue;
+        const unsigned long long k = ((unsigned long long)sadreg[i] << 32) | ((unsigned)y << 16) | (unsigned)x;
+        best = k < best ? k : best;
+    }
+    if (bj >= 0) flush_key(jobs, bj, best);
+}
+
+// One svt_sad_loop_kernel too large for the arena as a whole: its search area is tiled (row bands,
+// then columns) and every tile runs through the group helpers as a one-job group.
+// All threads of the CTA call it with identical arguments; jobs[J].key must be HME_KEY_INIT on entry.
+__device__ __noinline__ void hme_search_tiled(const HBlk &blk, HJob *jobs, int J, HPlan *pl, uint8_t *arena) {
+    const HJob &job = jobs[J];
+    const int sa_w = job.sa_w, sa_h = job.sa_h;
+    if (sa_w <= 0 || sa_h <= 0) return;
+    int wt = sa_w, bh = sa_h;
+    HGeo g;
+    for (;;) {
+        hme_geo(blk, wt, bh, job.skip_even, g);
+        if (!g.big) break;
+        const int tile_w = 4 * g.G;
+        if (bh > 8) bh = (bh + 1) / 2;
+        else if (wt > tile_w) wt = ((wt / 2 + tile_w - 1) / tile_w) * tile_w;
+        else if (bh > 1) bh = (bh + 1) / 2;
+        else break; // one row x one G-tile always fits
+    }
+    for (int x0 = 0; x0 < sa_w; x0 += wt) {
+        const int wb = min(wt, sa_w - x0);
+        for (int y0 = 0; y0 < sa_h; y0 += bh) {
+            const int hb = min(bh, sa_h - y0);
+            __syncthreads(); // previous tile is done with the arena and with pl->geo[J]
+            if (threadIdx.x == 0) {
+                hme_geo(blk, wb, hb, job.skip_even, g);
+                g.x0 = x0;
+                g.y0 = y0;
+                g.ref_off = y0 * job.stride + x0;
+                pl->geo[J] = g;
+            }
+            __syncthreads();
+            const HGroup G = HGroup{J, J + 1, 0, pl->geo[J].stage_units, pl->geo[J].n_items, pl->geo[J].scan_n};
+            hme_group_stage(jobs, pl->geo, G, arena);
+            __syncthreads();
+            hme_group_items(blk, jobs, pl->geo, G, arena);
+            if (blk.nb > 1) {
+                __syncthreads();
+                hme_group_scan(jobs, pl->geo, G, arena);
+            }
+        }
+    }
+    __syncthreads();
+}
+
 // A round of independent jobs on the same source block. Jobs are packed into the arena as many
 // at a time as fit ("group"); staging, search items and the SAD-buffer scan of a group are each
 // ONE flattened list over the CTA, so twenty 16x6 refinement windows cost three barriers, not
@@ -444,6 +518,7 @@ __device__ __noinline__ void hme_search_multi(const HBlk &blk, HJob *jobs, int n
         pl->geo[tid] = g;
     }
     if (__syncthreads_and(is_point)) {
+        if (tid == 0) pl->n_groups = 0;
         hme_points(blk, jobs, n);
         return;
     }
@@ -452,7 +527,7 @@ __device__ __noinline__ void hme_search_multi(const HBlk &blk, HJob *jobs, int n
         const unsigned full = 0xffffffffu;
         const bool valid = lane < n;
         HGeo *g = &pl->geo[valid ? lane : 0];
-        const uint32_t need = valid ? g->need : 0u, copies = valid ? (uint32_t)g->copy_bytes * 4u : 0u;
+        const uint32_t need = valid ? g->need : 0u, copies = valid ? (uint32_t)g->copy_bytes : 0u;
         const bool big = valid && g->big;
         const int su = valid ? g->stage_units : 0, ni = valid ? g->n_items : 0, sc = valid ? g->scan_n : 0;
         int start = 0, ng = 0;
@@ -499,79 +574,17 @@ __device__ __noinline__ void hme_search_multi(const HBlk &blk, HJob *jobs, int n
     for (int gi = 0; gi < n_groups; ++gi) {
         const HGroup G = pl->grp[gi];
         if (G.big) {
-            hme_search(blk, &jobs[G.j0], arena);
+            hme_search_tiled(blk, jobs, G.j0, pl, arena);
             continue;
         }
         if (G.item_total == 0) continue;
         if (gi) __syncthreads(); // the previous group is done with the arena
-        const HGeo *geo = pl->geo;
-        // ---- staging, four chunks per thread in flight
-        {
-            constexpr int U = 4;
-            int cj = G.j0;
-            for (int base = tid; base < G.stage_total; base += U * SVTME_THREADS) {
-                uint32_t w[U][6], mis[U];
-                uint8_t *dst[U];
-                int cb[U];
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    const int i = base + u * SVTME_THREADS;
-                    if (i < G.stage_total) {
-                        while (i >= geo[cj].stage_base + geo[cj].stage_units) ++cj;
-                        const HGeo &g = geo[cj];
-                        const int il = i - g.stage_base;
-                        const int R = (int)__umulhi((uint32_t)il, g.mg_cpr), k = il - R * g.cpr;
-                        stage_unit_load(jobs[cj].ref + (size_t)R * jobs[cj].stride, k, w[u], mis[u]);
-                        dst[u] = arena + g.arena_off + ((size_t)(R * g.m + k) << 4);
-                        cb[u] = g.copy_bytes;
-                    }
-                }
-#pragma unroll
-                for (int u = 0; u < U; ++u)
-                    if (base + u * SVTME_THREADS < G.stage_total) stage_unit_store(dst[u], cb[u], w[u], mis[u]);
-            }
-        }
-        uint32_t *sadreg = reinterpret_cast<uint32_t *>(arena + geo[G.j0].sad_off);
-        for (int i = tid; i < G.scan_total; i += SVTME_THREADS) sadreg[i] = 0;
+        hme_group_stage(jobs, pl->geo, G, arena);
         __syncthreads();
-        // ---- search items
-        {
-            SrcRegs sr;
-            sr.cached_b = -1;
-            sr.rows_here = 0;
-            unsigned long long best = ~0ULL;
-            int cj = G.j0, bj = -1;
-            for (int it = tid; it < G.item_total; it += SVTME_THREADS) {
-                while (it >= geo[cj].item_base + geo[cj].n_items) ++cj;
-                if (nb == 1 && cj != bj) {
-                    if (bj >= 0) flush_key(jobs, bj, best);
-                    best = ~0ULL;
-                    bj = cj;
-                }
-                hme_item_any(blk, geo[cj], arena, it - geo[cj].item_base, sr, best);
-            }
-            if (nb == 1 && bj >= 0) flush_key(jobs, bj, best);
-        }
-        // ---- multi-sub-block blocks: positions' SADs were summed in the SAD buffer
-        if (nb > 1) {
+        hme_group_items(blk, jobs, pl->geo, G, arena);
+        if (nb > 1) { // multi-sub-block blocks: positions' SADs were summed in the SAD buffer
             __syncthreads();
-            unsigned long long best = ~0ULL;
-            int cj = G.j0, bj = -1;
-            for (int i = tid; i < G.scan_total; i += SVTME_THREADS) {
-                while (i >= geo[cj].scan_base + geo[cj].scan_n) ++cj;
-                if (cj != bj) {
-                    if (bj >= 0) flush_key(jobs, bj, best);
-                    best = ~0ULL;
-                    bj = cj;
-                }
-                const HGeo &g = geo[cj];
-                const int il = i - g.scan_base;
-                const int y = (int)__umulhi((uint32_t)il, g.mg_wb), x = il - y * g.sa_w;
-                if (g.skip_even && !(y & 1)) continue;
-                const unsigned long long k = ((unsigned long long)sadreg[i] << 32) | ((unsigned)y << 16) | (unsigned)x;
-                best = k < best ? k : best;
-            }
-            if (bj >= 0) flush_key(jobs, bj, best);
+            hme_group_scan(jobs, pl->geo, G, arena);
         }
     }
     __syncthreads();
@@ -588,8 +601,13 @@ __device__ __noinline__ void hme_search_multi(const HBlk &blk, HJob *jobs, int n
 // PU tables are kept as 64-bit keys  sad << 32 | order  where `order` is the position's rank in
 // the reference's evaluation order (the one-point probe ranks before the main search); an update
 // happens iff the new key is smaller, which is exactly the reference's sequential strict `<`.
+#if SVTME_ARENA_BYTES >= 64 * 1024
 #define FP_TW 64
 #define FP_TH 32
+#else
+#define FP_TW 32
+#define FP_TH 16
+#endif
 #define FP_IDX_BITS 11
 
 struct FpTables {               // shared memory
@@ -657,11 +675,11 @@ __device__ __noinline__ void fp_tile(const uint8_t *src64, const uint8_t *arena,
                                         bool sub_sad, FpTables *tab) {
     const int tid = threadIdx.x, b = tid & 15, c = (tid >> 4) & 3, yl = tid >> 6;
     const int bx = ((b >> 2) & 1) * 2 + (b & 1), by = ((b >> 3) & 1) * 2 + ((b >> 1) & 1);
-    const int xt_n = (tw + 4 * G - 1) / (4 * G), npass = (th + 3) >> 2;
+    const int xt_n = (tw + 4 * G - 1) / (4 * G), npass = (th + SVTME_FP_YL - 1) / SVTME_FP_YL;
     uint32_t k8[4] = {~0u, ~0u, ~0u, ~0u}, k16 = ~0u, k32 = ~0u, k64 = ~0u;
     const int npar = sub_sad ? 1 : 2;
     for (int pass = 0; pass < npass; ++pass) {
-        const int y = 4 * pass + yl;
+        const int y = SVTME_FP_YL * pass + yl;
         for (int xt = 0; xt < xt_n; ++xt) {
             uint32_t acc[G][4];
 #pragma unroll
@@ -781,7 +799,7 @@ __device__ __noinline__ void fullpel_search(const uint8_t *src64, const uint8_t 
             const int vec_words = G == 2 ? 6 : ((G + 3 + 3) / 4) * 4;
             const int words = (span / 4 - G) + 12 + vec_words;
             const int m = (words + 3) / 4;
-            const int rows = ((th + 3) & ~3) + last_row;
+            const int rows = ((th + SVTME_FP_YL - 1) / SVTME_FP_YL) * SVTME_FP_YL + last_row;
             const int copy_chunks = rows * m + 4 * ((rows - 1) >> 4) + 4;
             const int copy_bytes = copy_chunks * 16;
             __syncthreads();
@@ -819,29 +837,32 @@ __device__ __noinline__ void fullpel_search(const uint8_t *src64, const uint8_t 
 // table's own order, so 8x8 / 16x16 sums are shuffles and only 32x32 / 64x64 go through smem.
 __device__ __noinline__ void fullpel_probe(const uint8_t *src64, const uint8_t *ref0, int ref_stride, int mvx, int mvy, bool sub_sad,
                               uint32_t order, FpTables *tab) {
-    const int tid = threadIdx.x, e = tid >> 2, q = tid & 3;
-    const int b = e >> 2, k = e & 3;
-    const int bx = ((b >> 2) & 1) * 2 + (b & 1), by = ((b >> 3) & 1) * 2 + ((b >> 1) & 1);
-    const int x8 = 16 * bx + 8 * (k & 1), y8 = 16 * by + 8 * (k >> 1);
-    uint32_t acc = 0;
-    const int nr = sub_sad ? 1 : 2;
-    for (int i = 0; i < nr; ++i) {
-        const int y = y8 + 2 * q + i;
-        const uint2 sv = *reinterpret_cast<const uint2 *>(src64 + y * 64 + x8);
-        const uintptr_t ai = reinterpret_cast<uintptr_t>(ref0 + (size_t)y * ref_stride + x8);
-        const uint32_t *al = reinterpret_cast<const uint32_t *>(ai & ~(uintptr_t)3);
-        const uint32_t sh = (uint32_t)(ai & 3) * 8;
-        const uint32_t w0 = __ldg(al), w1 = __ldg(al + 1), w2 = sh ? __ldg(al + 2) : 0u;
-        acc = vsad4(sv.x, __funnelshift_r(w0, w1, sh), acc);
-        acc = vsad4(sv.y, __funnelshift_r(w1, w2, sh), acc);
+    const int tid = threadIdx.x;
+    for (int vt = tid; vt < 256; vt += SVTME_THREADS) { // 256 virtual threads: 64 8x8 blocks x 4 row pairs
+        const int e = vt >> 2, q = vt & 3;
+        const int b = e >> 2, k = e & 3;
+        const int bx = ((b >> 2) & 1) * 2 + (b & 1), by = ((b >> 3) & 1) * 2 + ((b >> 1) & 1);
+        const int x8 = 16 * bx + 8 * (k & 1), y8 = 16 * by + 8 * (k >> 1);
+        uint32_t acc = 0;
+        const int nr = sub_sad ? 1 : 2;
+        for (int i = 0; i < nr; ++i) {
+            const int y = y8 + 2 * q + i;
+            const uint2 sv = *reinterpret_cast<const uint2 *>(src64 + y * 64 + x8);
+            const uintptr_t ai = reinterpret_cast<uintptr_t>(ref0 + (size_t)y * ref_stride + x8);
+            const uint32_t *al = reinterpret_cast<const uint32_t *>(ai & ~(uintptr_t)3);
+            const uint32_t sh = (uint32_t)(ai & 3) * 8;
+            const uint32_t w0 = __ldg(al), w1 = __ldg(al + 1), w2 = sh ? __ldg(al + 2) : 0u;
+            acc = vsad4(sv.x, __funnelshift_r(w0, w1, sh), acc);
+            acc = vsad4(sv.y, __funnelshift_r(w1, w2, sh), acc);
+        }
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+        const uint32_t s8 = sub_sad ? acc << 1 : acc;
+        uint32_t s16 = s8 + __shfl_xor_sync(0xffffffffu, s8, 4);
+        s16 += __shfl_xor_sync(0xffffffffu, s16, 8);
+        if (q == 0) tab->tile_best[21 + e] = s8;
+        if ((vt & 15) == 0) tab->tile_best[5 + b] = s16;
     }
-    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
-    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
-    const uint32_t s8 = sub_sad ? acc << 1 : acc;
-    uint32_t s16 = s8 + __shfl_xor_sync(0xffffffffu, s8, 4);
-    s16 += __shfl_xor_sync(0xffffffffu, s16, 8);
-    if (q == 0) tab->tile_best[21 + e] = s8;
-    if ((tid & 15) == 0) tab->tile_best[5 + b] = s16;
     __syncthreads();
     if (tid < 5) {
         uint32_t sum = 0;

@@ -54,6 +54,7 @@ struct StageState {
     int fp_do, fp_sa_w, fp_sa_h, fp_ox, fp_oy, fp_probe;
     int16_t fp_xc, fp_yc;
     int c00_needed;
+    unsigned long long n_groups_total;
     unsigned long long work_ops; // sum over executed searches of positions x block_w x rows
 };
 
@@ -846,16 +847,21 @@ struct StageSmem {
 
 int svtme_stage_smem_bytes() { return (int)sizeof(StageSmem); }
 
-#define T0(stmt)                     \
-    do {                             \
-        if (threadIdx.x == 0) { stmt; } \
-        __syncthreads();             \
+#define T0(stmt)                                                    \
+    do {                                                            \
+        if (threadIdx.x == 0) {                                     \
+            const long long t0_ = clock64();                        \
+            stmt;                                                   \
+            ph[SVTME_PH_SCALAR] += (unsigned long long)(clock64() - t0_); \
+        }                                                           \
+        __syncthreads();                                            \
     } while (0)
 
 __device__ void run_jobs(StageState *s, const HBlk &blk, uint8_t *arena) {
     const int n = s->n_jobs; // published by T0
     hme_search_multi(blk, s->jobs, n, &s->plan, arena);
     if (threadIdx.x == 0) {
+        s->n_groups_total += s->plan.n_groups;
         unsigned long long w = 0;
         for (int j = 0; j < n; ++j) {
             const int rows = s->jobs[j].skip_even ? s->jobs[j].sa_h / 2 : s->jobs[j].sa_h;
@@ -865,7 +871,7 @@ __device__ void run_jobs(StageState *s, const HBlk &blk, uint8_t *arena) {
     }
 }
 
-__global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob *__restrict__ jobs, int b64_per_job) {
+__global__ void __launch_bounds__(SVTME_THREADS, SVTME_CTAS_PER_SM) me_stage_kernel(const DevJob *__restrict__ jobs, int b64_per_job) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     StageSmem *sm = reinterpret_cast<StageSmem *>(smem_raw);
     StageState *s = &sm->st;
@@ -893,6 +899,13 @@ __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob
         }                                           \
     } while (0)
 
+#define TIMED(slot, call)                                               \
+    do {                                                                \
+        const long long t1_ = clock64();                                \
+        call;                                                           \
+        if (tid == 0) ph[slot] += (unsigned long long)(clock64() - t1_); \
+    } while (0)
+
     const int org_x = (int)(b64 % J.b64_cols) * 64, org_y = (int)(b64 / J.b64_cols) * 64;
     if (tid == 0) {
         s->org_x = org_x;
@@ -902,14 +915,17 @@ __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob
         s->b64_w = min(64, J.width - org_x);
         s->b64_h = min(64, J.height - org_y);
         s->work_ops = 0;
+        s->n_groups_total = 0;
         init_state(s, p);
     }
     // source blocks -> shared memory (b64_src_ptr, quarter_b64_buffer, sixteenth_b64_buffer; me_process.c:189-213)
     {
         const DevPlane &f = J.cur.lvl[0], &q = J.cur.lvl[1], &x = J.cur.lvl[2];
-        const int r = tid >> 2, c4 = tid & 3; // 64 rows x 4 chunks of 16 bytes
-        *reinterpret_cast<uint4 *>(&sm->src64[r * 64 + c4 * 16]) =
-            *reinterpret_cast<const uint4 *>(f.at(org_x + c4 * 16, org_y + r));
+        for (int i = tid; i < 256; i += SVTME_THREADS) { // 64 rows x 4 chunks of 16 bytes
+            const int r = i >> 2, c4 = i & 3;
+            *reinterpret_cast<uint4 *>(&sm->src64[r * 64 + c4 * 16]) =
+                *reinterpret_cast<const uint4 *>(f.at(org_x + c4 * 16, org_y + r));
+        }
         if (tid < 64) {
             const int rq = tid >> 1, cq = tid & 1;
             *reinterpret_cast<uint4 *>(&sm->src32[rq * 32 + cq * 16]) =
@@ -937,14 +953,14 @@ __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob
     // ---- hme_b64 :2511-2545
     if (p.me_early_exit_th || p.me_safe_limit_zz_th) {
         T0(plan_zz(s, J));
-        run_jobs(s, blk_zz, sm->arena);
+        TIMED(SVTME_PH_HME_ENGINE, run_jobs(s, blk_zz, sm->arena));
         T0(post_zz(s, p));
     }
     PHASE(SVTME_PH_ZZ);
     if (p.prehme_enable) {
         for (int li = 0; li < p.num_of_list_to_search; ++li) {
             T0(plan_prehme(s, J, li));
-            run_jobs(s, blk_l0, sm->arena);
+            TIMED(SVTME_PH_HME_ENGINE, run_jobs(s, blk_l0, sm->arena));
             T0(post_prehme_jobs(s, p));
         }
         T0(post_prehme_final(s, p));
@@ -956,23 +972,23 @@ __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob
                 p.reduce_hme_l0_sr_th_min && p.reduce_hme_l0_sr_th_max;
             if (dependent) { // other refs' areas depend on (list0, ref0)'s level-0 vector (:1882-1895)
                 T0(plan_l0(s, J, true, false));
-                run_jobs(s, blk_l0, sm->arena);
+                TIMED(SVTME_PH_HME_ENGINE, run_jobs(s, blk_l0, sm->arena));
                 T0(post_level_jobs(s, p, 0, 4); post_l0_prehme(s, p));
             }
             T0(plan_l0(s, J, false, dependent));
-            run_jobs(s, blk_l0, sm->arena);
+            TIMED(SVTME_PH_HME_ENGINE, run_jobs(s, blk_l0, sm->arena));
             T0(post_level_jobs(s, p, 0, 4); post_l0_prehme(s, p));
         }
         PHASE(SVTME_PH_L0);
         if (p.enable_hme_level1_flag) {
             T0(plan_l1(s, J));
-            run_jobs(s, blk_l1, sm->arena);
+            TIMED(SVTME_PH_HME_ENGINE, run_jobs(s, blk_l1, sm->arena));
             T0(post_level_jobs(s, p, 1, 2));
         }
         PHASE(SVTME_PH_L1);
         if (p.enable_hme_level2_flag) {
             T0(plan_l2(s, J));
-            run_jobs(s, blk_l2, sm->arena);
+            TIMED(SVTME_PH_HME_ENGINE, run_jobs(s, blk_l2, sm->arena));
             T0(post_level_jobs(s, p, 2, 1));
         }
         PHASE(SVTME_PH_L2);
@@ -986,7 +1002,7 @@ __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob
         for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
             T0(plan_int_a(s, J, li, ri));
             if (!s->fp_do) continue;
-            run_jobs(s, blk_zz, sm->arena);
+            TIMED(SVTME_PH_HME_ENGINE, run_jobs(s, blk_zz, sm->arena));
             T0(plan_int_b(s, J, li, ri));
             // svt_initialize_buffer_32bits(p_sb_best_sad, 21, 1, MAX_SAD_VALUE) :1368
             if (tid < SVTME_PU_COUNT) {
@@ -998,15 +1014,15 @@ __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob
             const DevPlane &pl = J.ref[li][ri].lvl[0];
             if (s->fp_probe) {
                 const int xc = s->fp_xc, yc = s->fp_yc;
-                fullpel_probe(sm->src64, pl.at(org_x + xc, org_y + yc), pl.stride, xc, yc, sub_sad, 1, &s->tab);
+                TIMED(SVTME_PH_FP_ENGINE, fullpel_probe(sm->src64, pl.at(org_x + xc, org_y + yc), pl.stride, xc, yc, sub_sad, 1, &s->tab));
                 if (tid == 0) s->work_ops += 64ull * (sub_sad ? 32 : 64);
             }
             T0(plan_int_c(s, J));
             PHASE(SVTME_PH_INT_PROBE);
             {
                 const int ox = s->fp_ox, oy = s->fp_oy;
-                fullpel_search(sm->src64, pl.at(org_x + ox, org_y + oy), pl.stride, ox, oy, s->fp_sa_w, s->fp_sa_h, sub_sad,
-                               2, &s->tab, sm->arena);
+                TIMED(SVTME_PH_FP_ENGINE, fullpel_search(sm->src64, pl.at(org_x + ox, org_y + oy), pl.stride, ox, oy, s->fp_sa_w,
+                                                         s->fp_sa_h, sub_sad, 2, &s->tab, sm->arena));
                 if (tid == 0) s->work_ops += (unsigned long long)s->fp_sa_w * s->fp_sa_h * 64ull * (sub_sad ? 32 : 64);
             }
             if (tid < SVTME_PU_COUNT) {
@@ -1029,6 +1045,7 @@ __global__ void __launch_bounds__(SVTME_THREADS, 2) me_stage_kernel(const DevJob
         finish_b64(s, J, b64, cando);
         PHASE(SVTME_PH_FINISH);
         ph[SVTME_PH_TOTAL] = (unsigned long long)(clock64() - t_start);
+        ph[SVTME_PH_HME_GROUPS] = s->n_groups_total;
         if (J.work_ops) {
             atomicAdd(J.work_ops, s->work_ops);
 #pragma unroll

@@ -115,7 +115,7 @@ class MeSession:
         return int(v.value)
 
     PHASE_NAMES = ("setup", "zz_sad", "prehme", "hme_l0", "hme_l1", "hme_l2", "centre_prune", "check_00",
-                   "probe", "fullpel", "finish", "total")
+                   "probe", "fullpel", "finish", "total", "x_scalar", "x_hme_engine", "x_fp_engine", "n_hme_groups")
 
     def last_phase_cycles(self):
         """Per-phase SM cycles of the last launch (thread 0 of every b64 CTA, summed)."""

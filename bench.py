@@ -252,7 +252,7 @@ def main():
     # dominant kernel: the stage kernel of the last step (CUDA events inside the library, same stream)
     work_ops = ses.last_work_ops()
     kernel_ms = ses.last_kernel_ms()
-    phases = ses.last_phase_cycles()
+    phases = ses.last_phase_ms()
     for _ in range(max(1, args.warmup)):
         step_e2e()
     ms_e2e = timed(step_e2e, args.steps)
@@ -292,10 +292,7 @@ def main():
                              "peak_source": "VABSDIFF4.U8.ACC issue rate measured live in this run (%.0f Ginst/s x 4 bytes)" % vsad,
                              "work_byte_ops_per_launch": work_ops, "kernel_ms": kernel_ms,
                              "kernel_share_of_step": kernel_ms / ms_step,
-                             "phase_share": {k: round(v / max(1, phases["total"]), 4) for k, v in phases.items()
-                                             if k not in ("total", "n_hme_groups")},
-                             "hme_groups_per_b64": phases["n_hme_groups"] / max(1, len(specs) * n_b64),
-                             "cycles_per_b64": phases["total"] / max(1, len(specs) * n_b64)},
+                             "phase_ms": {k: round(v, 3) for k, v in phases.items()}},
                 "roofline_hbm": {"bound": "hbm", "kernel": "me_stage_kernel", "achieved": alg_bytes / (kernel_ms * 1e-3) / 1e9,
                                  "peak": hbm_peak, "unit": "GB/s", "frac": alg_bytes / (kernel_ms * 1e-3) / 1e9 / hbm_peak,
                                  "traffic": None, "peak_source": hbm_src},

@@ -221,13 +221,12 @@ int svtme_set_stream(SvtMeHandle *h, void *cuda_stream);
  * the last svtme_launch_pictures call: the numerator of the integer-SAD roofline. Synchronises. */
 int svtme_last_work_ops(SvtMeHandle *h, uint64_t *ops);
 
-/* Profiling aid (no reference counterpart): SM cycles thread 0 of each b64 CTA spent per phase of
- * svt_aom_motion_estimation_b64 in the last launch, summed over CTAs. Slots: 0 setup, 1 zz-SAD,
- * 2 pre-HME, 3 HME L0, 4 HME L1, 5 HME L2, 6 search centre + HME pruning, 7 check_00_center,
- * 8 8x8-variance probe, 9 full-pel search, 10 candidates + statistics, 11 total; cross-cuts: 12 all thread-0 plan/post steps, 13 HME engine,
- * 14 full-pel engine + probe, 15 number of HME groups (a count, not cycles). */
-#define SVTME_PHASES 16
-int svtme_last_phase_cycles(SvtMeHandle *h, uint64_t *cycles, uint32_t n);
+/* Profiling aid (no reference counterpart): device milliseconds of each launch slot of the stage
+ * pipeline in the last launch. Slots: 0 state clear, 1 zz-SAD, 2 pre-HME, 3 HME L0, 4 HME L1,
+ * 5 HME L2 + search centre + HME pruning, 6 integer search (check_00_center, probe, full-pel),
+ * 7 ME pruning + candidates + statistics. */
+#define SVTME_PHASES 8
+int svtme_last_phase_ms(SvtMeHandle *h, float *ms, uint32_t n);
 /* Measured issue rate (Ginst/s, whole GPU) of VABSDIFF4.U8.ACC, 4 byte-SADs per instruction: the
  * integer-SAD roofline denominator (not part of MEASURED_PEAKS.json). */
 double svtme_measure_vabsdiff4_ginst_per_s(void);

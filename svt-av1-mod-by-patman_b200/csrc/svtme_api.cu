@@ -60,6 +60,9 @@ struct SvtMeHandle {
     uint32_t jobs_cap;
     OutBuffers ob;
     cudaEvent_t ev0, ev1;
+    cudaEvent_t ph_ev[SVTME_PHASES];
+    void *d_states = nullptr; // per-b64 scratch of the stage pipeline
+    size_t states_bytes = 0;
     float last_ms;
     std::mutex mu;
 };
@@ -113,6 +116,7 @@ extern "C" int svtme_open(int device, uint32_t width, uint32_t height, uint32_t 
     if (e == cudaSuccess) e = cudaMallocHost(&h->stage_host, (size_t)width * height);
     if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
     if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
+    for (int k = 0; k < SVTME_PHASES && e == cudaSuccess; ++k) e = cudaEventCreate(&h->ph_ev[k]);
     if (e != cudaSuccess) { cudaFree(h->pool); delete h; return fail(SVTME_ERR_CUDA, "svtme_open", e); }
     h->slots.resize(capacity);
     for (uint32_t i = 0; i < capacity; ++i) {
@@ -140,6 +144,8 @@ extern "C" void svtme_close(SvtMeHandle *h) {
     cudaFreeHost(h->ob.host);
     cudaEventDestroy(h->ev0);
     cudaEventDestroy(h->ev1);
+    for (int k = 0; k < SVTME_PHASES; ++k) cudaEventDestroy(h->ph_ev[k]);
+    cudaFree(h->d_states);
     if (h->own_stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -261,7 +267,7 @@ static OutLayout out_layout(uint32_t n_b64, uint32_t n_pu, const SvtMeParams &p,
     L.d64 = take((size_t)n_b64 * 4); L.d32 = take((size_t)n_b64 * 4); L.d16 = take((size_t)n_b64 * 4);
     L.d8 = take((size_t)n_b64 * 4); L.var8 = take((size_t)n_b64 * 4); L.rc = take((size_t)n_b64 * 4);
     L.stat = take(n_b64); L.gm = take(n_b64);
-    L.work = take(8 * (1 + SVTME_PHASES)); // work_ops, then per-phase cycle sums
+    L.work = take(8);
     if (deep) {
         L.bsad = take((size_t)n_b64 * 2 * 4 * 85 * 4); L.bmv = take((size_t)n_b64 * 2 * 4 * 85 * 4);
         L.sc = take((size_t)n_b64 * 2 * 4 * 2 * 2); L.hsad = take((size_t)n_b64 * 2 * 4 * 8); L.doref = take((size_t)n_b64 * 2 * 4);
@@ -351,7 +357,17 @@ extern "C" int svtme_launch_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint3
     CU(cudaMemsetAsync(h->ob.dev, 0, total, h->stream));
     CU(cudaMemcpyAsync(h->d_jobs, h->h_jobs, sizeof(DevJob) * n, cudaMemcpyHostToDevice, h->stream));
     CU(cudaEventRecord(h->ev0, h->stream));
-    svtme_launch_me_stage(h->d_jobs, (int)n, (int)h->n_b64, h->stream);
+    {
+        const size_t need = (size_t)n * h->n_b64 * svtme_stage_state_bytes();
+        if (need > h->states_bytes) {
+            cudaFree(h->d_states);
+            h->d_states = nullptr;
+            h->states_bytes = 0;
+            CU(cudaMalloc(&h->d_states, need));
+            h->states_bytes = need;
+        }
+    }
+    svtme_launch_me_stage(h->d_jobs, (int)n, (int)h->n_b64, h->d_states, h->stream, h->ph_ev);
     CU(cudaGetLastError());
     CU(cudaEventRecord(h->ev1, h->stream));
     return SVTME_OK;
@@ -449,19 +465,17 @@ extern "C" int svtme_last_work_ops(SvtMeHandle *h, uint64_t *ops) {
     return SVTME_OK;
 }
 
-// Per-phase SM cycles (thread 0 of every b64 CTA, summed over all CTAs) of the last
-// svtme_launch_pictures call; see SVTME_PHASE_* in svtme_common.cuh. Synchronises the stream.
-extern "C" int svtme_last_phase_cycles(SvtMeHandle *h, uint64_t *cycles, uint32_t n) {
-    if (!h || !cycles) return fail(SVTME_ERR_INVALID, "svtme_last_phase_cycles: bad argument");
+// Device time of each launch slot of the stage pipeline in the last svtme_launch_pictures call
+// (names: SVTME_PHASE_NAMES). Synchronises the stream.
+extern "C" int svtme_last_phase_ms(SvtMeHandle *h, float *ms, uint32_t n) {
+    if (!h || !ms) return fail(SVTME_ERR_INVALID, "svtme_last_phase_ms: bad argument");
     std::lock_guard<std::mutex> lk(h->mu);
     CU(cudaSetDevice(h->device));
     CU(cudaStreamSynchronize(h->stream));
     if (n > SVTME_PHASES) n = SVTME_PHASES;
-    for (uint32_t k = 0; k < n; ++k) cycles[k] = 0;
-    for (size_t o : h->work_off) {
-        unsigned long long v[SVTME_PHASES];
-        CU(cudaMemcpy(v, h->ob.dev + o + 8, sizeof(v), cudaMemcpyDeviceToHost));
-        for (uint32_t k = 0; k < n; ++k) cycles[k] += v[k];
+    for (uint32_t k = 0; k < n; ++k) {
+        ms[k] = 0.f;
+        CU(cudaEventElapsedTime(&ms[k], k ? h->ph_ev[k - 1] : h->ev0, h->ph_ev[k]));
     }
     return SVTME_OK;
 }

@@ -53,11 +53,9 @@ struct DevJob {
     unsigned long long *work_ops; // [0] algorithmic SAD byte-ops executed for this picture (roofline numerator)
 };
 
-// phase slots behind work_ops (cycle sums of thread 0, one CTA per b64)
-#define SVTME_PHASES 16
-enum { SVTME_PH_SETUP = 0, SVTME_PH_ZZ, SVTME_PH_PREHME, SVTME_PH_L0, SVTME_PH_L1, SVTME_PH_L2, SVTME_PH_CENTRE,
-       SVTME_PH_INT_CHECK, SVTME_PH_INT_PROBE, SVTME_PH_INT_MAIN, SVTME_PH_FINISH, SVTME_PH_TOTAL,
-       SVTME_PH_SCALAR /* all thread-0 plan/post steps */, SVTME_PH_HME_ENGINE, SVTME_PH_FP_ENGINE, SVTME_PH_HME_GROUPS /* count */ };
+// launch slots of the stage pipeline (svtme_stage.cu), timed with one CUDA event after each
+#define SVTME_PHASES 8
+#define SVTME_PHASE_NAMES "state_clear", "zz_sad", "prehme", "hme_l0", "hme_l1", "hme_l2_centre", "integer_search", "finish"
 
 static inline int up128(int v) { return (v + 127) & ~127; }
 
@@ -68,8 +66,10 @@ void svtme_launch_downsample(const DevPlane &full, const DevPlane &quarter, cons
 void svtme_launch_downsample_generic(const uint8_t *in, int in_stride, int w, int h, uint8_t *out, int out_stride,
                                      int step, cudaStream_t st);
 // stage kernel (svtme_stage.cu)
-void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, cudaStream_t st);
-int svtme_stage_smem_bytes();
+// d_states: n_jobs * b64_per_job * svtme_stage_state_bytes() bytes of scratch; ev: SVTME_PHASES events or null
+void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, void *d_states, cudaStream_t st,
+                           cudaEvent_t *ev);
+size_t svtme_stage_state_bytes();
 // kernel-test entry points (svtme_stage.cu)
 void svtme_launch_sad_loop_test(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride,
                                 int block_height, int block_width, int ref_row_step_raw, int skip_line, int sa_w,

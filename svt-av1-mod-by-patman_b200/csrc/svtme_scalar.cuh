@@ -1,0 +1,831 @@
+// svtme_scalar.cuh — per-b64 state and the SCALAR control flow of svt_aom_motion_estimation_b64
+// (Source/Lib/Codec/motion_estimation.c:3146-3223; citations below are into that file): search-area
+// derivation, edge clipping in int16, early exits, reference pruning, candidate construction,
+// statistics. Every function works on a StageState through a pointer, so the same code runs on
+// a state block in global memory (one thread per b64, "scalar kernels") or in shared memory.
+#pragma once
+#include "svtme_search.cuh"
+
+#define NL SVTME_NL
+#define NR SVTME_NR
+#define MAXU32 0xFFFFFFFFu
+#define MAX_JOBS SVTME_MAX_JOBS
+
+struct PreHme {
+    uint16_t sa_w, sa_h;
+    int16_t col, row;
+    unsigned long long sad;
+    uint8_t valid;
+};
+
+struct RefResult {
+    int16_t hme_sc_x, hme_sc_y;
+    unsigned long long hme_sad;
+    uint8_t do_ref;
+};
+
+struct JobMeta { // what the post step needs to know about an HJob
+    int8_t li, ri, a, b; // a,b: search region / quadrant indices
+    int16_t ox, oy;      // search-area origin that was applied
+};
+
+struct StageState {
+    SvtMeSearchAreaMinMax hme_l0_sa;
+    int org_x, org_y, b64_w, b64_h, pic_w, pic_h;
+    int16_t cx[3][NL][NR][2][2], cy[3][NL][NR][2][2];
+    unsigned long long lsad[3][NL][NR][2][2];
+    RefResult sr[NL][NR];
+    uint32_t div[NL][NR];
+    uint32_t zz[NL][NR];
+    PreHme ph[NL][NR][2];
+    uint8_t performed_phme[NL][NR][2];
+    uint32_t best_sad[NL][NR][SVTME_PU_COUNT], best_mv[NL][NR][SVTME_PU_COUNT];
+    uint32_t me_distortion[SVTME_PU_COUNT];
+    FpTables tab;
+    HJob jobs[MAX_JOBS];
+    JobMeta meta[MAX_JOBS];
+    int n_jobs;
+    // integer-search hand-over between plan steps
+    int fp_do, fp_sa_w, fp_sa_h, fp_ox, fp_oy, fp_probe;
+    int16_t fp_xc, fp_yc;
+    int c00_needed;
+    unsigned long long work_ops; // sum over executed searches of positions x block_w x rows
+};
+
+__device__ __forceinline__ int iabs(int v) { return v < 0 ? -v : v; }
+__device__ __forceinline__ uint16_t scaled_dist(uint16_t dist) { // svt_aom_get_scaled_picture_distance :1239
+    return (uint16_t)(((dist * 5) / 8) + ((dist % 8) ? 1 : 0));
+}
+__device__ __forceinline__ uint16_t ref_dist(const SvtMeParams &p, int li, int ri) { // get_me_reference :1232
+    long long d = (long long)p.picture_number - (long long)p.ref_picture_number[li][ri];
+    return (uint16_t)(int16_t)(d < 0 ? -d : d);
+}
+
+__device__ void add_job(StageState *s, const DevPlane &pl, int x_tl, int y_tl, int sa_w, int sa_h, int skip, int li,
+                        int ri, int a, int b, int16_t ox, int16_t oy) {
+    const int n = s->n_jobs++;
+    HJob &j = s->jobs[n];
+    // (x_tl, y_tl) already include the plane origin of the REFERENCE geometry; rebase on ours
+    j.ref = pl.base + (size_t)y_tl * pl.stride + x_tl;
+    j.stride = pl.stride;
+    j.sa_w = sa_w;
+    j.sa_h = sa_h;
+    j.skip_even = skip;
+    j.key = HME_KEY_INIT;
+    s->meta[n] = JobMeta{(int8_t)li, (int8_t)ri, (int8_t)a, (int8_t)b, ox, oy};
+}
+
+// Window clipping shared by hme_level_0/1/2 (:820-1113), with the reference's no-op left/top size
+// corrections kept. pad_w/pad_h are the LOGICAL limits (org-1 of the reference's planes, 63 at L2).
+__device__ void clip_hme(int16_t org_x, int16_t org_y, int16_t W, int16_t H, int16_t pad_w, int16_t pad_h,
+                         int16_t &sa_w, int16_t &sa_h, int16_t &ox, int16_t &oy) {
+    if ((org_x + ox) < -pad_w) {
+        ox = -pad_w - org_x;
+        sa_w = sa_w - (-pad_w - (org_x + ox));
+    }
+    if ((org_x + ox) > W - 1) ox = ox - ((org_x + ox) - (W - 1));
+    if ((org_x + ox + sa_w) > W) sa_w = max(1, sa_w - ((org_x + ox + sa_w) - W));
+    sa_w = (sa_w < 8) ? sa_w : sa_w & ~0x07;
+    if ((org_y + oy) < -pad_h) {
+        oy = -pad_h - org_y;
+        sa_h = sa_h - (-pad_h - (org_y + oy));
+    }
+    if ((org_y + oy) > H - 1) oy = oy - ((org_y + oy) - (H - 1));
+    if (org_y + oy + sa_h > H) sa_h = max(1, sa_h - ((org_y + oy + sa_h) - H));
+}
+
+__device__ void set_quadrants(StageState *s, int lvl, int li, int ri, int16_t x, int16_t y, unsigned long long sad) {
+    for (int a = 0; a < 2; ++a)
+        for (int b = 0; b < 2; ++b) {
+            s->cx[lvl][li][ri][a][b] = x;
+            s->cy[lvl][li][ri][a][b] = y;
+            s->lsad[lvl][li][ri][a][b] = sad;
+        }
+}
+
+// ---------------------------------------------------------------- plan / post steps (thread 0)
+__device__ void init_state(StageState *s, const SvtMeParams &p) { // init_me_hme_data :3080-3140
+    for (int li = 0; li < NL; ++li)
+        for (int ri = 0; ri < NR; ++ri) {
+            RefResult &r = s->sr[li][ri];
+            r.hme_sc_x = r.hme_sc_y = 0;
+            r.do_ref = 1;
+            r.hme_sad = MAXU32;
+            s->div[li][ri] = 1;
+            s->zz[li][ri] = MAXU32;
+            for (int k = 0; k < 2; ++k) {
+                PreHme &d = s->ph[li][ri][k];
+                d.sa_w = d.sa_h = 0;
+                d.col = d.row = 0;
+                d.sad = 0;
+                d.valid = 0;
+                s->performed_phme[li][ri][k] = 0;
+            }
+            for (int l = 0; l < 3; ++l) set_quadrants(s, l, li, ri, 0, 0, 0);
+        }
+    s->hme_l0_sa = p.hme_l0_sa;
+}
+
+// zz-SAD jobs: one 1x1 search per reference at MV (0,0) (get_zz_sad :1737-1759)
+__device__ void plan_zz(StageState *s, const DevJob &J) {
+    const SvtMeParams &p = J.prm;
+    s->n_jobs = 0;
+    for (int li = 0; li < p.num_of_list_to_search; ++li)
+        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri)
+            if (p.temporal_layer_index > 0 || li == 0) {
+                const DevPlane &pl = J.ref[li][ri].lvl[0];
+                add_job(s, pl, pl.org_x + s->org_x, pl.org_y + s->org_y, 1, 1, 0, li, ri, 0, 0, 0, 0);
+            }
+}
+
+__device__ void post_zz(StageState *s, const SvtMeParams &p) { // init_zz_sad :2452-2507
+    uint32_t best = MAXU32;
+    for (int n = 0; n < s->n_jobs; ++n) {
+        const JobMeta &m = s->meta[n];
+        uint32_t z = (uint32_t)(s->jobs[n].key >> 32) << 1;
+        z = (z * 64 * 64) / (uint32_t)(s->b64_w * s->b64_h);
+        s->zz[m.li][m.ri] = z;
+        best = min(best, z);
+    }
+    if (p.temporal_layer_index > 0 && best < p.zz_sad_th)
+        for (int li = 0; li < p.num_of_list_to_search; ++li)
+            for (int ri = 1; ri < p.num_of_ref_pic_to_search[li]; ++ri)
+                if ((uint32_t)((s->zz[li][ri] - best) * 100) > (uint32_t)(p.zz_sad_pct * best)) s->sr[li][ri].do_ref = 0;
+    if (p.me_safe_limit_zz_th) {
+        const bool limit = p.hierarchical_levels > 0 && p.num_of_list_to_search == 2 &&
+            p.temporal_layer_index >= p.hierarchical_levels && p.similar_brightness_refs &&
+            s->zz[0][0] < p.me_safe_limit_zz_th && s->zz[1][0] < p.me_safe_limit_zz_th;
+        if (limit)
+            for (int li = 0; li < p.num_of_list_to_search; ++li)
+                for (int ri = 1; ri < p.num_of_ref_pic_to_search[li]; ++ri) s->sr[li][ri].do_ref = 0;
+    }
+}
+
+// check_prehme_early_exit :1763-1788
+__device__ bool prehme_early_exit(StageState *s, const SvtMeParams &p, int li, int ri, int sr) {
+    PreHme &d = s->ph[li][ri][sr];
+    if (p.me_early_exit_th && s->zz[li][ri] < p.me_early_exit_th) {
+        d.col = d.row = 0;
+        d.sad = 0;
+        d.valid = 1;
+        return true;
+    }
+    if (p.prehme_l1_early_exit) {
+        const PreHme &l0 = s->ph[0][ri][sr];
+        if (li == 1 && l0.valid && ((l0.sad < (32 * 32)) || ((iabs(l0.col) < 16) && (iabs(l0.row) < 16)))) {
+            d.col = (int16_t)-l0.col;
+            d.row = (int16_t)-l0.row;
+            d.sad = l0.sad;
+            d.valid = 1;
+            return true;
+        }
+    }
+    return false;
+}
+
+// prehme_b64 (:1791-1866) for one list: decide per (ref, region) and emit jobs (prehme_core :1641)
+__device__ void plan_prehme(StageState *s, const DevJob &J, int li) {
+    const SvtMeParams &p = J.prm;
+    s->n_jobs = 0;
+    if (!(p.temporal_layer_index > 0 || li == 0)) return;
+    for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
+        const uint32_t factor = scaled_dist(ref_dist(p, li, ri));
+        for (int sr = 0; sr < 2; ++sr) {
+            if (prehme_early_exit(s, p, li, ri, sr)) continue;
+            PreHme &d = s->ph[li][ri][sr];
+            if (!s->sr[li][ri].do_ref) {
+                d.col = d.row = 0;
+                d.sad = MAXU32;
+                continue;
+            }
+            d.sa_w = (uint16_t)min(p.prehme_sa_cfg[sr].sa_min.width * factor, (uint32_t)p.prehme_sa_cfg[sr].sa_max.width);
+            d.sa_h = (uint16_t)min(p.prehme_sa_cfg[sr].sa_min.height * factor, (uint32_t)p.prehme_sa_cfg[sr].sa_max.height);
+            const DevPlane &pl = J.ref[li][ri].lvl[2];
+            const int16_t org_x = (int16_t)s->org_x >> 2, org_y = (int16_t)s->org_y >> 2;
+            const int16_t pad_w = 15, pad_h = 15; // sixteenth org (16) - 1
+            const int16_t W = (int16_t)pl.width, H = (int16_t)pl.height;
+            int16_t sa_w = (int16_t)d.sa_w, sa_h = (int16_t)d.sa_h;
+            int16_t ox = -(int16_t)(sa_w >> 1), oy = -(int16_t)(sa_h >> 1);
+            ox = ((org_x + ox) < -pad_w) ? -pad_w - org_x : ox;
+            sa_w = ((org_x + ox) < -pad_w) ? sa_w - (-pad_w - (org_x + ox)) : sa_w;
+            ox = ((org_x + ox) > W - 1) ? ox - ((org_x + ox) - (W - 1)) : ox;
+            sa_w = ((org_x + ox + sa_w) > W) ? max(1, sa_w - ((org_x + ox + sa_w) - W)) : sa_w;
+            oy = ((org_y + oy) < -pad_h) ? -pad_h - org_y : oy;
+            sa_h = ((org_y + oy) < -pad_h) ? sa_h - (-pad_h - (org_y + oy)) : sa_h;
+            oy = ((org_y + oy) > H - 1) ? oy - ((org_y + oy) - (H - 1)) : oy;
+            sa_h = (org_y + oy + sa_h > H) ? max(1, sa_h - ((org_y + oy + sa_h) - H)) : sa_h;
+            add_job(s, pl, pl.org_x + org_x + ox, pl.org_y + org_y + oy, sa_w, sa_h, p.prehme_skip_search_line, li, ri, sr,
+                    0, ox, oy);
+        }
+    }
+}
+
+__device__ void post_prehme_jobs(StageState *s, const SvtMeParams &p) {
+    const bool full = p.hme_search_method == 1;
+    for (int n = 0; n < s->n_jobs; ++n) {
+        const JobMeta &m = s->meta[n];
+        const unsigned long long k = s->jobs[n].key;
+        PreHme &d = s->ph[m.li][m.ri][m.a];
+        d.sad = (k >> 32) * (full ? 1 : 2);
+        d.col = (int16_t)((int16_t)((int16_t)(k & 0xffff) + m.ox) * 4);
+        d.row = (int16_t)((int16_t)((int16_t)((k >> 16) & 0xffff) + m.oy) * 4);
+        d.valid = 1;
+        s->performed_phme[m.li][m.ri][m.a] = 1;
+    }
+}
+
+__device__ void post_prehme_final(StageState *s, const SvtMeParams &p) { // tail of prehme_b64 :1841-1866
+    uint32_t best_sad = MAXU32;
+    for (int li = 0; li < p.num_of_list_to_search; ++li)
+        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
+            if (p.temporal_layer_index > 0 || li == 0) {
+                uint32_t m = (uint32_t)min(s->ph[li][ri][0].sad, s->ph[li][ri][1].sad);
+                best_sad = min(best_sad, m);
+            } else {
+                for (int sr = 0; sr < 2; ++sr) {
+                    s->ph[1][ri][sr].col = (int16_t)-s->ph[0][ri][sr].col;
+                    s->ph[1][ri][sr].row = (int16_t)-s->ph[0][ri][sr].row;
+                    s->ph[1][ri][sr].sad = s->ph[0][ri][sr].sad;
+                }
+            }
+        }
+    if (p.temporal_layer_index > 0 && best_sad < p.phme_sad_th)
+        for (int li = 0; li < p.num_of_list_to_search; ++li)
+            for (int ri = 1; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
+                if (!s->sr[li][ri].do_ref) continue;
+                uint32_t m = (uint32_t)min(s->ph[li][ri][0].sad, s->ph[li][ri][1].sad);
+                if ((uint32_t)((m - best_sad) * 100) > (uint32_t)(p.phme_sad_pct * best_sad)) s->sr[li][ri].do_ref = 0;
+            }
+}
+
+// get_hme_l0_search_area :1870-1935 (works on a local copy of hme_l0_sa == modify + restore)
+__device__ void hme_l0_area(const StageState *s, const SvtMeParams &p, int li, int ri, uint16_t dist, int16_t *sa_w,
+                            int16_t *sa_h) {
+    SvtMeSearchAreaMinMax a = s->hme_l0_sa;
+    if (p.enable_me_sr_adjustment && p.distance_based_hme_resizing) {
+        uint8_t is_hor = 1, is_ver = 1, is_still = 0;
+        if (p.reduce_hme_l0_sr_th_min && p.reduce_hme_l0_sr_th_max && (li || ri)) {
+            int16_t mvx = s->cx[0][0][0][0][0], mvy = s->cy[0][0][0][0][0];
+            is_ver = (iabs(mvx) < p.reduce_hme_l0_sr_th_min) && (iabs(mvy) > p.reduce_hme_l0_sr_th_max);
+            is_hor = (iabs(mvx) > p.reduce_hme_l0_sr_th_max) && (iabs(mvy) < p.reduce_hme_l0_sr_th_min);
+            is_still = (iabs(mvx) < (p.reduce_hme_l0_sr_th_min * 3)) && (iabs(mvy) < (p.reduce_hme_l0_sr_th_min * 3));
+        }
+        uint8_t xo = is_hor ? 1 : 2, yo = is_ver ? 1 : 2;
+        if (p.enable_me_sr_adjustment == 2 && is_still) xo = yo = 4;
+        a.sa_min.width = (uint16_t)(a.sa_min.width / (xo + ri));
+        a.sa_min.height = (uint16_t)(a.sa_min.height / (yo + ri));
+        a.sa_max.width = (uint16_t)(a.sa_max.width / (xo + ri));
+        a.sa_max.height = (uint16_t)(a.sa_max.height / (yo + ri));
+    }
+    const int factor = scaled_dist(dist);
+    int16_t w = (int16_t)(a.sa_min.width / p.num_hme_sa_w);
+    w = (int16_t)min((((w * factor) + 15) & ~0x0F), (((a.sa_max.width / p.num_hme_sa_w) + 15) & ~0x0F));
+    int16_t h = (int16_t)(a.sa_min.height / p.num_hme_sa_h);
+    h = (int16_t)min((h * factor), a.sa_max.height / p.num_hme_sa_h);
+    *sa_w = w;
+    *sa_h = h;
+}
+
+// hme_level0_b64 :1976-2106. first_only: plan (list0, ref0) only; skip_first: everything else.
+__device__ void plan_l0(StageState *s, const DevJob &J, bool first_only, bool skip_first) {
+    const SvtMeParams &p = J.prm;
+    s->n_jobs = 0;
+    for (int li = 0; li < p.num_of_list_to_search; ++li)
+        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
+            const bool first = (li == 0 && ri == 0);
+            if ((first_only && !first) || (skip_first && first)) continue;
+            if (p.me_early_exit_th && s->zz[li][ri] < (p.me_early_exit_th >> 2)) {
+                set_quadrants(s, 0, li, ri, 0, 0, 0);
+                continue;
+            }
+            if (p.prev_me_stage_based_exit_th) {
+                int sr = s->ph[li][ri][0].sad <= s->ph[li][ri][1].sad ? 0 : 1;
+                if (s->performed_phme[li][ri][sr] && s->ph[li][ri][sr].sad < (p.prev_me_stage_based_exit_th >> 4)) {
+                    set_quadrants(s, 0, li, ri, s->ph[li][ri][sr].col, s->ph[li][ri][sr].row, s->ph[li][ri][sr].sad);
+                    continue;
+                }
+            }
+            if (!s->sr[li][ri].do_ref) {
+                set_quadrants(s, 0, li, ri, 0, 0, MAXU32);
+                continue;
+            }
+            if (!(p.temporal_layer_index > 0 || li == 0)) continue;
+            const DevPlane &pl = J.ref[li][ri].lvl[2];
+            int16_t sa_w0 = 0, sa_h0 = 0;
+            hme_l0_area(s, p, li, ri, ref_dist(p, li, ri), &sa_w0, &sa_h0);
+            const int16_t org_x = (int16_t)s->org_x >> 2, org_y = (int16_t)s->org_y >> 2;
+            for (int sh = 0; sh < p.num_hme_sa_h; ++sh)
+                for (int sw = 0; sw < p.num_hme_sa_w; ++sw) {
+                    int16_t w = (int16_t)((sa_w0 + 7) & ~0x07), h = sa_h0;
+                    int16_t ox = (int16_t)(-(int16_t)((w * p.num_hme_sa_w) >> 1) + (int16_t)(w * sw));
+                    int16_t oy = (int16_t)(-(int16_t)((sa_h0 * p.num_hme_sa_h) >> 1) + (int16_t)(sa_h0 * sh));
+                    clip_hme(org_x, org_y, (int16_t)pl.width, (int16_t)pl.height, 15, 15, w, h, ox, oy);
+                    add_job(s, pl, pl.org_x + org_x + ox, pl.org_y + org_y + oy, w, h, 0, li, ri, sw, sh, ox, oy);
+                }
+        }
+}
+
+__device__ void post_level_jobs(StageState *s, const SvtMeParams &p, int lvl, int scale) {
+    const bool full = p.hme_search_method == 1;
+    for (int n = 0; n < s->n_jobs; ++n) {
+        const JobMeta &m = s->meta[n];
+        const unsigned long long k = s->jobs[n].key;
+        s->lsad[lvl][m.li][m.ri][m.a][m.b] = (k >> 32) * (full ? 1 : 2);
+        s->cx[lvl][m.li][m.ri][m.a][m.b] = (int16_t)((int16_t)((int16_t)(k & 0xffff) + m.ox) * scale);
+        s->cy[lvl][m.li][m.ri][m.a][m.b] = (int16_t)((int16_t)((int16_t)((k >> 16) & 0xffff) + m.oy) * scale);
+    }
+}
+
+// worst-quadrant replacement by the pre-HME result (:2073-2101, get_worst_quadrant :1939-1971)
+__device__ void post_l0_prehme(StageState *s, const SvtMeParams &p) {
+    if (!p.prehme_enable) return;
+    int last_li = -1, last_ri = -1;
+    for (int n = 0; n < s->n_jobs; ++n) {
+        const int li = s->meta[n].li, ri = s->meta[n].ri;
+        if (li == last_li && ri == last_ri) continue;
+        last_li = li;
+        last_ri = ri;
+        unsigned long long(*q)[2] = s->lsad[0][li][ri];
+        int bw = 0, bh = 0;
+        unsigned long long mx = 0;
+        if (q[0][0] > mx) { mx = q[0][0]; bw = 0; bh = 0; }
+        if (q[1][0] > mx) { mx = q[1][0]; bw = 1; bh = 0; }
+        if (q[0][1] > mx) { mx = q[0][1]; bw = 0; bh = 1; }
+        if (q[1][1] > mx) { bw = 1; bh = 1; }
+        const int sr = s->ph[li][ri][0].sad <= s->ph[li][ri][1].sad ? 0 : 1;
+        if (s->ph[li][ri][sr].sad < q[bw][bh]) {
+            q[bw][bh] = s->ph[li][ri][sr].sad;
+            s->cx[0][li][ri][bw][bh] = s->ph[li][ri][sr].col;
+            s->cy[0][li][ri][bw][bh] = s->ph[li][ri][sr].row;
+        }
+    }
+}
+
+// hme_level1_b64 :2111-2192
+__device__ void plan_l1(StageState *s, const DevJob &J) {
+    const SvtMeParams &p = J.prm;
+    s->n_jobs = 0;
+    for (int li = 0; li < p.num_of_list_to_search; ++li)
+        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
+            if (!(p.temporal_layer_index > 0 || li == 0)) continue;
+            if (p.me_early_exit_th && s->zz[li][ri] < (p.me_early_exit_th >> 2)) {
+                set_quadrants(s, 1, li, ri, 0, 0, 0);
+                continue;
+            }
+            if (!s->sr[li][ri].do_ref) {
+                set_quadrants(s, 1, li, ri, 0, 0, MAXU32);
+                continue;
+            }
+            const DevPlane &pl = J.ref[li][ri].lvl[1];
+            const int16_t org_x = (int16_t)s->org_x >> 1, org_y = (int16_t)s->org_y >> 1;
+            for (int sh = 0; sh < p.num_hme_sa_h; ++sh)
+                for (int sw = 0; sw < p.num_hme_sa_w; ++sw) {
+                    if (p.prev_me_stage_based_exit_th && s->lsad[0][li][ri][sw][sh] < (p.prev_me_stage_based_exit_th >> 5)) {
+                        s->cx[1][li][ri][sw][sh] = s->cx[0][li][ri][sw][sh];
+                        s->cy[1][li][ri][sw][sh] = s->cy[0][li][ri][sw][sh];
+                        s->lsad[1][li][ri][sw][sh] = s->lsad[0][li][ri][sw][sh];
+                        continue;
+                    }
+                    int16_t w = (int16_t)(((int16_t)p.hme_l1_sa.width + 7) & ~0x07), h = (int16_t)p.hme_l1_sa.height;
+                    int16_t ox = (int16_t)(-(w >> 1) + (s->cx[0][li][ri][sw][sh] >> 1));
+                    int16_t oy = (int16_t)(-(h >> 1) + (s->cy[0][li][ri][sw][sh] >> 1));
+                    clip_hme(org_x, org_y, (int16_t)pl.width, (int16_t)pl.height, 31, 31, w, h, ox, oy);
+                    add_job(s, pl, pl.org_x + org_x + ox, pl.org_y + org_y + oy, w, h, 0, li, ri, sw, sh, ox, oy);
+                }
+        }
+}
+
+// hme_level2_b64 :2197-2247 (no do_ref / early-exit test at this level in the reference)
+__device__ void plan_l2(StageState *s, const DevJob &J) {
+    const SvtMeParams &p = J.prm;
+    s->n_jobs = 0;
+    for (int li = 0; li < p.num_of_list_to_search; ++li)
+        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
+            if (!(p.temporal_layer_index > 0 || li == 0)) continue;
+            const DevPlane &pl = J.ref[li][ri].lvl[0];
+            const int16_t org_x = (int16_t)s->org_x, org_y = (int16_t)s->org_y;
+            for (int sh = 0; sh < p.num_hme_sa_h; ++sh)
+                for (int sw = 0; sw < p.num_hme_sa_w; ++sw) {
+                    if (p.prev_me_stage_based_exit_th && s->lsad[1][li][ri][sw][sh] < (p.prev_me_stage_based_exit_th >> 2)) {
+                        s->cx[2][li][ri][sw][sh] = s->cx[1][li][ri][sw][sh];
+                        s->cy[2][li][ri][sw][sh] = s->cy[1][li][ri][sw][sh];
+                        s->lsad[2][li][ri][sw][sh] = s->lsad[1][li][ri][sw][sh];
+                        continue;
+                    }
+                    int16_t w = (int16_t)(((int16_t)p.hme_l2_sa.width + 7) & ~0x07), h = (int16_t)p.hme_l2_sa.height;
+                    int16_t ox = (int16_t)(-(w >> 1) + s->cx[1][li][ri][sw][sh]);
+                    int16_t oy = (int16_t)(-(h >> 1) + s->cy[1][li][ri][sw][sh]);
+                    clip_hme(org_x, org_y, (int16_t)pl.width, (int16_t)pl.height, 63, 63, w, h, ox, oy);
+                    add_job(s, pl, pl.org_x + org_x + ox, pl.org_y + org_y + oy, w, h, 0, li, ri, sw, sh, ox, oy);
+                }
+        }
+}
+
+// set_final_seach_centre_sb :2252-2450 — hsad/centres persist across the (list, ref) loop.
+__device__ void set_final_search_centre(StageState *s, const SvtMeParams &p) {
+    int16_t hx = 0, hy = 0, cx = 0, cy = 0;
+    unsigned long long hsad = 0;
+    for (int li = 0; li < p.num_of_list_to_search; ++li)
+        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
+            if (p.temporal_layer_index > 0 || li == 0) {
+                if (p.enable_hme_flag) {
+                    for (int pass = 0; pass < 3; ++pass) {
+                        const bool on = pass == 0
+                            ? (p.enable_hme_level0_flag && !p.enable_hme_level1_flag && !p.enable_hme_level2_flag)
+                            : pass == 1 ? (p.enable_hme_level1_flag && !p.enable_hme_level2_flag) : p.enable_hme_level2_flag;
+                        if (!on) continue;
+                        hx = s->cx[pass][li][ri][0][0];
+                        hy = s->cy[pass][li][ri][0][0];
+                        hsad = s->lsad[pass][li][ri][0][0];
+                        uint32_t w = 1, h = 0;
+                        while (h < p.num_hme_sa_h) {
+                            while (w < p.num_hme_sa_w) {
+                                if (s->lsad[pass][li][ri][w][h] < hsad) {
+                                    hx = s->cx[pass][li][ri][w][h];
+                                    hy = s->cy[pass][li][ri][w][h];
+                                    hsad = s->lsad[pass][li][ri][w][h];
+                                }
+                                w++;
+                            }
+                            w = 0;
+                            h++;
+                        }
+                    }
+                    cx = hx;
+                    cy = hy;
+                }
+            } else {
+                cx = 0;
+                cy = 0;
+            }
+            s->sr[li][ri].hme_sc_x = cx;
+            s->sr[li][ri].hme_sc_y = cy;
+            s->sr[li][ri].hme_sad = hsad;
+        }
+}
+
+// hme_prune_ref_and_adjust_sr :2547-2588 — loops cover all 2x4 slots incl. unused ones.
+__device__ void hme_prune_ref_and_adjust_sr(StageState *s, const SvtMeParams &p) {
+    const uint16_t th = p.prune_ref_if_hme_sad_dev_bigger_than_th;
+    if (p.enable_me_hme_ref_pruning && th != (uint16_t)~0) {
+        unsigned long long best = ~0ULL;
+        for (int li = 0; li < NL; ++li)
+            for (int ri = 0; ri < NR; ++ri)
+                if (s->sr[li][ri].hme_sad < best) best = s->sr[li][ri].hme_sad;
+        for (int li = 0; li < NL; ++li)
+            for (int ri = 1; ri < NR; ++ri)
+                if ((s->sr[li][ri].hme_sad - best) * 100 > ((unsigned long long)th * best)) s->sr[li][ri].do_ref = 0;
+    }
+    if (p.enable_me_sr_adjustment)
+        for (int li = 0; li < NL; ++li)
+            for (int ri = 0; ri < NR; ++ri) {
+                const RefResult &r = s->sr[li][ri];
+                if (iabs(r.hme_sc_x) <= p.reduce_me_sr_based_on_mv_length_th &&
+                    iabs(r.hme_sc_y) <= p.reduce_me_sr_based_on_mv_length_th && r.hme_sad < p.stationary_hme_sad_abs_th)
+                    s->div[li][ri] = p.stationary_me_sr_divisor;
+                else if (r.hme_sad < p.reduce_me_sr_based_on_hme_sad_abs_th)
+                    s->div[li][ri] = p.me_sr_divisor_for_low_hme_sad;
+            }
+}
+
+// integer_search_b64 :1249-1586, one reference, split at the points where a SAD search is needed.
+// Step A: search-area size before the centre test; emits the two check_00_center SADs if needed.
+__device__ void plan_int_a(StageState *s, const DevJob &J, int li, int ri) {
+    const SvtMeParams &p = J.prm;
+    s->n_jobs = 0;
+    s->c00_needed = 0;
+    s->fp_do = s->sr[li][ri].do_ref != 0;
+    if (!s->fp_do) return;
+    int16_t xc = s->sr[li][ri].hme_sc_x, yc = s->sr[li][ri].hme_sc_y;
+    if (!p.me_early_exit_th && (xc != 0 || yc != 0) && p.is_ref) {
+        // check_00_center :1139-1206: clip the centre, then SAD at (0,0) and at the centre
+        const DevPlane &pl = J.ref[li][ri].lvl[0];
+        const int16_t org_x = (int16_t)s->org_x, org_y = (int16_t)s->org_y;
+        const int16_t W = (int16_t)pl.width, H = (int16_t)pl.height;
+        xc = ((org_x + xc) < -63) ? -63 - org_x : xc;
+        xc = ((org_x + xc) > W - 1) ? xc - ((org_x + xc) - (W - 1)) : xc;
+        yc = ((org_y + yc) < -63) ? -63 - org_y : yc;
+        yc = ((org_y + yc) > H - 1) ? yc - ((org_y + yc) - (H - 1)) : yc;
+        add_job(s, pl, pl.org_x + org_x, pl.org_y + org_y, 1, 1, 0, li, ri, 0, 0, 0, 0);
+        add_job(s, pl, pl.org_x + org_x + xc, pl.org_y + org_y + yc, 1, 1, 0, li, ri, 1, 0, 0, 0);
+        s->c00_needed = 1;
+    }
+    s->fp_xc = xc;
+    s->fp_yc = yc;
+}
+
+// Step B: finish the size logic, initialise the tables, decide on the 8x8-variance probe.
+__device__ void plan_int_b(StageState *s, const DevJob &J, int li, int ri) {
+    const SvtMeParams &p = J.prm;
+    int16_t xc = s->fp_xc, yc = s->fp_yc;
+    int16_t sa_w = (int16_t)p.me_sa.sa_min.width, sa_h = (int16_t)p.me_sa.sa_min.height;
+    const uint16_t dist = scaled_dist(ref_dist(p, li, ri));
+    sa_w = (int16_t)min((int)(sa_w * dist), (int)p.me_sa.sa_max.width);
+    sa_h = (int16_t)min((int)(sa_h * dist), (int)p.me_sa.sa_max.height);
+    // NB: the reference applies the mv-based scaling to the UNCLIPPED hme centre (:1309-1314)
+    if (p.mv_sa_adj_enabled && (!p.mv_sa_adj_nearest_ref_only || ri == 0)) {
+        if (iabs(s->sr[li][ri].hme_sc_x) > p.mv_sa_adj_mv_size_th) sa_w = (int16_t)(sa_w * p.mv_sa_adj_sa_multiplier);
+        if (iabs(s->sr[li][ri].hme_sc_y) > p.mv_sa_adj_mv_size_th) sa_h = (int16_t)(sa_h * p.mv_sa_adj_sa_multiplier);
+    }
+    sa_w = (int16_t)((max(1u, (uint32_t)sa_w / s->div[li][ri]) + 7) & ~0x07u);
+    sa_h = (int16_t)max(3u, (uint32_t)sa_h / s->div[li][ri]);
+    const int16_t h_before = sa_h, w_before = sa_w;
+    unsigned long long best_hme_sad = ~0ULL;
+    if (p.me_early_exit_th) {
+        if (s->zz[li][ri] < (p.me_early_exit_th / 6)) {
+            sa_w = 1;
+            sa_h = 1;
+        }
+    } else {
+        uint8_t accurate = 1;
+        if (s->c00_needed) {
+            const uint32_t zero_sad = (uint32_t)(s->jobs[0].key >> 32) << 1;
+            const uint32_t hme_sad = (uint32_t)(s->jobs[1].key >> 32) << 1;
+            const unsigned long long zero_cost = (uint32_t)(zero_sad << 8), hme_cost = (uint32_t)(hme_sad << 8);
+            const unsigned long long best = min(zero_cost, hme_cost);
+            xc = (best == zero_cost) ? 0 : xc;
+            yc = (best == zero_cost) ? 0 : yc;
+            best_hme_sad = hme_sad;
+            if (xc == 0 && yc == 0) accurate = 0;
+        }
+        if (p.enable_me_sr_adjustment == 2) {
+            if ((accurate && (best_hme_sad < (24 * 24))) || (p.is_ref && s->sr[li][ri].hme_sad < (24 * 24))) sa_h = sa_h / 2;
+            if ((li || ri) && s->best_sad[0][0][0] < 5000 && sa_h == h_before && sa_w == w_before) {
+                sa_h = sa_h >> 1;
+                sa_w = sa_w >> 1;
+            }
+        }
+    }
+    s->fp_xc = xc;
+    s->fp_yc = yc;
+    s->fp_sa_w = sa_w;
+    s->fp_sa_h = sa_h;
+    s->fp_probe = p.me_8x8_var_enabled && (sa_w * sa_h > 24);
+}
+
+// Step C: after the probe — 8x8-variance scaling (:1416-1441) and picture clipping (:1470-1561).
+__device__ void plan_int_c(StageState *s, const DevJob &J) {
+    const SvtMeParams &p = J.prm;
+    int16_t sa_w = (int16_t)s->fp_sa_w, sa_h = (int16_t)s->fp_sa_h;
+    const int16_t xc = s->fp_xc, yc = s->fp_yc;
+    if (s->fp_probe) {
+        const uint32_t mean = (uint32_t)(s->tab.key[0] >> 32) / 64;
+        uint32_t ssq = 0;
+        for (int i = 0; i < 64; ++i) {
+            const int32_t d = (int32_t)(uint32_t)(s->tab.key[21 + i] >> 32) - (int32_t)mean;
+            ssq += (uint32_t)(d * d);
+        }
+        const uint32_t var = ssq / 64;
+        if (var > p.me_sr_mult2_th) {
+            sa_w = (int16_t)((max(1, sa_w * 3 / 2) + 7) & ~0x7);
+            sa_h = (int16_t)max(1, sa_h * 3 / 2);
+        }
+        if (var < p.me_sr_div4_th) {
+            sa_w = (int16_t)((max(1, sa_w >> 2) + 7) & ~0x7);
+            sa_h = (int16_t)max(1, sa_h >> 2);
+            sa_h = (int16_t)max(3, (int)sa_h);
+        } else if (var < p.me_sr_div2_th) {
+            sa_w = (int16_t)((min((int)sa_w, sa_w >> 1) + 7) & ~0x7);
+            sa_h = (int16_t)min((int)sa_h, sa_h >> 1);
+            sa_h = (int16_t)max(3, (int)sa_h);
+        }
+    }
+    const int16_t org_x = (int16_t)s->org_x, org_y = (int16_t)s->org_y;
+    const int16_t W = (int16_t)s->pic_w, H = (int16_t)s->pic_h;
+    int16_t ox = (int16_t)(xc - (sa_w >> 1)), oy = (int16_t)(yc - (sa_h >> 1));
+    ox = ((org_x + ox) < -63) ? -63 - org_x : ox;
+    sa_w = ((org_x + ox) < -63) ? sa_w - (-63 - (org_x + ox)) : sa_w;
+    ox = ((org_x + ox) > W - 1) ? ox - ((org_x + ox) - (W - 1)) : ox;
+    sa_w = ((org_x + ox + sa_w) > W) ? max(1, sa_w - ((org_x + ox + sa_w) - W)) : sa_w;
+    sa_w = (sa_w < 8) ? sa_w : sa_w & ~0x07;
+    oy = ((org_y + oy) < -63) ? -63 - org_y : oy;
+    sa_h = ((org_y + oy) < -63) ? sa_h - (-63 - (org_y + oy)) : sa_h;
+    oy = ((org_y + oy) > H - 1) ? oy - ((org_y + oy) - (H - 1)) : oy;
+    sa_h = (org_y + oy + sa_h > H) ? max(1, sa_h - ((org_y + oy + sa_h) - H)) : sa_h;
+    s->fp_sa_w = sa_w;
+    s->fp_sa_h = sa_h;
+    s->fp_ox = ox;
+    s->fp_oy = oy;
+}
+
+__constant__ uint8_t k_tab8x8[64] = {0,  1,  4,  5,  16, 17, 20, 21, 2,  3,  6,  7,  18, 19, 22, 23,
+                                     8,  9,  12, 13, 24, 25, 28, 29, 10, 11, 14, 15, 26, 27, 30, 31,
+                                     32, 33, 36, 37, 48, 49, 52, 53, 34, 35, 38, 39, 50, 51, 54, 55,
+                                     40, 41, 44, 45, 56, 57, 60, 61, 42, 43, 46, 47, 58, 59, 62, 63};
+__constant__ uint8_t k_z_to_raster[85] = {
+    0,  1,  2,  3,  4,  5,  6,  9,  10, 7,  8,  11, 12, 13, 14, 17, 18, 15, 16, 19, 20, 21, 22, 29, 30, 23, 24, 31, 32,
+    37, 38, 45, 46, 39, 40, 47, 48, 25, 26, 33, 34, 27, 28, 35, 36, 41, 42, 49, 50, 43, 44, 51, 52, 53, 54, 61, 62, 55,
+    56, 63, 64, 69, 70, 77, 78, 71, 72, 79, 80, 57, 58, 65, 66, 59, 60, 67, 68, 73, 74, 81, 82, 75, 76, 83, 84};
+__constant__ uint8_t k_8x8_to_16x16[64] = {5,  5,  6,  6,  7,  7,  8,  8,  5,  5,  6,  6,  7,  7,  8,  8,
+                                           9,  9,  10, 10, 11, 11, 12, 12, 9,  9,  10, 10, 11, 11, 12, 12,
+                                           13, 13, 14, 14, 15, 15, 16, 16, 13, 13, 14, 14, 15, 15, 16, 16,
+                                           17, 17, 18, 18, 19, 19, 20, 20, 17, 17, 18, 18, 19, 19, 20, 20};
+__constant__ uint8_t k_16x16_to_32x32[16] = {1, 1, 2, 2, 1, 1, 2, 2, 3, 3, 4, 4, 3, 3, 4, 4};
+
+// me_prune_ref :1592-1635
+__device__ void me_prune_ref(StageState *s, const SvtMeParams &p) {
+    for (int li = 0; li < p.num_of_list_to_search; ++li)
+        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
+            s->sr[li][ri].hme_sad = 0;
+            if (s->sr[li][ri].do_ref == 0) {
+                s->sr[li][ri].hme_sad = (unsigned long long)SVTME_MAX_SAD_VALUE * 64;
+                continue;
+            }
+            for (int i = 0; i < 64; ++i) s->sr[li][ri].hme_sad += s->best_sad[li][ri][21 + k_tab8x8[i]];
+        }
+    const uint16_t th = p.prune_ref_if_me_sad_dev_bigger_than_th;
+    if (p.enable_me_hme_ref_pruning && th != (uint16_t)~0) {
+        unsigned long long best = ~0ULL;
+        for (int li = 0; li < NL; ++li)
+            for (int ri = 0; ri < NR; ++ri)
+                if (s->sr[li][ri].hme_sad < best) best = s->sr[li][ri].hme_sad;
+        for (int li = 0; li < NL; ++li)
+            for (int ri = 1; ri < NR; ++ri)
+                if ((s->sr[li][ri].hme_sad - best) * 100 > ((unsigned long long)th * best)) s->sr[li][ri].do_ref = 0;
+    }
+}
+
+__device__ __forceinline__ uint8_t cand_byte(unsigned dir, unsigned i0, unsigned i1, unsigned l0, unsigned l1) {
+    return (uint8_t)((dir & 3) | ((i0 & 3) << 2) | ((i1 & 3) << 4) | ((l0 & 1) << 6) | ((l1 & 1) << 7));
+}
+__device__ __forceinline__ bool use_pu(const SvtMeParams &p, uint32_t n) {
+    return p.enable_me_16x16 ? (p.enable_me_8x8 || n < 21) : n < 5;
+}
+
+// construct_me_candidate_array{,_mrp_off,_single_ref} :2602-2905 — one thread per search-order PU n.
+__device__ void construct_candidates(StageState *s, const SvtMeParams &p, uint32_t n, uint8_t *total, uint32_t *mvo,
+                                     uint8_t *cando) {
+    const uint8_t n0 = p.num_of_ref_pic_to_search[0], n1 = p.num_of_ref_pic_to_search[1];
+    uint32_t nlists = p.num_of_list_to_search;
+    const bool use = use_pu(p, n);
+    if (n0 == 1 && n1 == 0) { // _single_ref :2716
+        const uint8_t pu = k_z_to_raster[n];
+        if (use) total[pu] = 1;
+        s->me_distortion[pu] = s->best_sad[0][0][n];
+        if (s->sr[0][0].do_ref == 0) return;
+        if (use) {
+            cando[pu * p.max_cand] = cand_byte(0, 0, 0, 0, 0);
+            mvo[pu * p.max_refs] = s->best_mv[0][0][n];
+        }
+        return;
+    }
+    if (n0 == 1 && n1 == 1) { // _mrp_off :2602
+        const uint8_t pu = k_z_to_raster[n];
+        uint8_t org[2];
+        org[0] = s->sr[0][0].do_ref;
+        org[1] = (nlists == 1) ? 0 : s->sr[1][0].do_ref;
+        if (nlists < 2 || !s->sr[1][0].do_ref) nlists = 1;
+        const uint32_t th = (org[0] && org[1]) ? (uint32_t)p.prune_me_candidates_th : 0;
+        if (use) total[pu] = 1;
+        uint8_t off = 0;
+        uint8_t *cand = use ? &cando[pu * p.max_cand] : nullptr;
+        uint8_t dr[2] = {org[0], org[1]};
+        const uint32_t best = (org[0] && org[1]) ? min(s->best_sad[0][0][n], s->best_sad[1][0][n])
+            : org[0]                             ? s->best_sad[0][0][n]
+                                                 : s->best_sad[1][0][n];
+        s->me_distortion[pu] = best;
+        int min_list = -1;
+        if (p.use_best_unipred_cand_only && dr[0] && dr[1]) min_list = s->best_sad[0][0][n] < s->best_sad[1][0][n] ? 0 : 1;
+        for (int li = 0; (uint32_t)li < nlists && (use || off == 0); ++li) {
+            if (dr[li] == 0) continue;
+            if (th > 0) {
+                uint32_t d = (s->best_sad[li][0][n] - best) * 100;
+                if (d > (best * th)) {
+                    dr[li] = 0;
+                    continue;
+                }
+            }
+            if (min_list != -1 && min_list != li) {
+                if (use) mvo[pu * p.max_refs + (li ? p.max_l0 : 0)] = s->best_mv[li][0][n];
+                continue;
+            }
+            if (use) {
+                cand[off] = cand_byte((unsigned)li, 0, 0, li == 0 ? (unsigned)li : 24, li == 1 ? (unsigned)li : 24);
+                mvo[pu * p.max_refs + (li ? p.max_l0 : 0)] = s->best_mv[li][0][n];
+            }
+            off++;
+        }
+        if (dr[0] && dr[1] && use) {
+            cand[off] = cand_byte(2, 0, 0, 0, 1);
+            total[pu] = (uint8_t)(off + 1);
+        }
+        return;
+    }
+    // general :2768
+    const uint8_t pu = (n > 4) ? k_z_to_raster[n] : (uint8_t)n;
+    uint8_t off = 0;
+    uint8_t *cand = use ? &cando[pu * p.max_cand] : nullptr;
+    uint8_t dr[NL][NR];
+    const uint32_t th = (uint32_t)p.prune_me_candidates_th;
+    uint32_t best = MAXU32;
+    for (int li = 0; li < NL; ++li)
+        for (int ri = 0; ri < NR; ++ri) dr[li][ri] = 0;
+    for (uint32_t li = 0; li < nlists; ++li)
+        for (uint32_t ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
+            dr[li][ri] = s->sr[li][ri].do_ref;
+            if (dr[li][ri] == 0) continue;
+            best = s->best_sad[li][ri][n] < best ? s->best_sad[li][ri][n] : best;
+        }
+    s->me_distortion[pu] = best;
+    for (uint32_t li = 0; li < nlists && (use || off == 0); ++li)
+        for (uint32_t ri = 0; ri < p.num_of_ref_pic_to_search[li] && (use || off == 0); ++ri) {
+            if (dr[li][ri] == 0) continue;
+            if (th > 0) {
+                uint32_t d = (s->best_sad[li][ri][n] - best) * 100;
+                if (d > (best * th)) {
+                    dr[li][ri] = 0;
+                    continue;
+                }
+            }
+            if (use) {
+                cand[off] = cand_byte(li, ri, ri, li == 0 ? li : 24, li == 1 ? li : 24);
+                mvo[pu * p.max_refs + (li ? p.max_l0 : 0) + ri] = s->best_mv[li][ri][n];
+            }
+            off++;
+        }
+    if (nlists == 2 && use) {
+        for (uint32_t a = 0; a < n0; ++a)
+            for (uint32_t b = 0; b < n1; ++b) {
+                if (p.only_l_bwd && (a > 0 || b > 0)) continue;
+                if (dr[0][a] && dr[1][b]) cand[off++] = cand_byte(2, a, b, 0, 1);
+            }
+        if (!p.only_l_bwd) {
+            for (uint32_t a = 1; a < n0; ++a)
+                if (dr[0][0] && dr[0][a]) cand[off++] = cand_byte(2, 0, a, 0, 0);
+            if (n1 == 3 && dr[1][0] && dr[1][2]) cand[off++] = cand_byte(2, 0, 2, 1, 1);
+        }
+    }
+    if (use) total[pu] = off;
+}
+
+// compute_distortion :3034-3077 + perform_gm_detection :2908-3031 (thread 0)
+__device__ void finish_b64(StageState *s, const DevJob &J, uint32_t b64, const uint8_t *cando) {
+    const SvtMeParams &p = J.prm;
+    const uint32_t *d = s->me_distortion;
+    uint32_t d64 = d[0], d32 = 0, d16 = 0, d8 = 0;
+    for (int i = 0; i < 4; ++i) d32 += d[1 + i];
+    for (int i = 0; i < 16; ++i) d16 += d[5 + i];
+    for (int i = 0; i < 64; ++i) d8 += d[21 + i];
+    unsigned long long mean = d8 / 64, ssq = 0;
+    for (int i = 0; i < 64; ++i) {
+        const long long diff = (long long)d[21 + i] - (long long)mean;
+        ssq += (unsigned long long)(diff * diff);
+    }
+    const uint32_t pix = (uint32_t)(s->b64_w * s->b64_h);
+    J.var8[b64] = (uint32_t)(ssq / 64);
+    J.rc_dist[b64] = p.input_resolution_le_480p ? d8 : d16;
+    J.dist64[b64] = (d64 * 4096u) / pix;
+    J.dist32[b64] = (d32 * 4096u) / pix;
+    J.dist16[b64] = (d16 * 4096u) / pix;
+    J.dist8[b64] = (d8 * 4096u) / pix;
+    uint8_t stationary_flag = 0, gm_flag = 0;
+    if (p.gm_enabled) {
+        unsigned long long cnt[NL][NR][2][2];
+        unsigned long long stationary = 0, tot = 0;
+        for (int a = 0; a < NL; ++a)
+            for (int b = 0; b < NR; ++b)
+                for (int c = 0; c < 2; ++c) cnt[a][b][c][0] = cnt[a][b][c][1] = 0;
+        const bool small = p.input_resolution_le_480p;
+        const unsigned count = small ? 64 : 16;
+        for (unsigned i = 0; i < count; ++i) {
+            uint8_t n = (uint8_t)((small ? 21 : 5) + i);
+            if (small) {
+                if (!p.enable_me_8x8) {
+                    if (n >= 21) n = k_8x8_to_16x16[n - 21];
+                    if (!p.enable_me_16x16 && n >= 5) n = k_16x16_to_32x32[n - 5];
+                }
+            } else if (!p.enable_me_16x16 && n >= 5)
+                n = k_16x16_to_32x32[n - 5];
+            const uint8_t c = cando[n * p.max_cand];
+            const unsigned dir = c & 3, i0 = (c >> 2) & 3, i1 = (c >> 4) & 3, l0 = (c >> 6) & 1, l1 = (c >> 7) & 1;
+            const uint32_t li = (dir == 0 || dir == 2) ? l0 : l1, ri = (dir == 0 || dir == 2) ? i0 : i1;
+            const unsigned long long a = p.picture_number, b = p.ref_picture_number[li][ri];
+            int th;
+            if (small) {
+                uint16_t dist = (uint16_t)iabs((int16_t)(max(a, b) - min(a, b)));
+                th = p.gm_use_distance_based_active_th ? max(dist >> 1, 4) : 4;
+            } else {
+                uint16_t dist = (uint16_t)iabs((int16_t)(a - b));
+                th = p.gm_use_distance_based_active_th ? max(dist * 16, 32) : 32;
+            }
+            const uint32_t mv = s->best_mv[li][ri][n];
+            const int mx = (int16_t)(mv & 0xffff) << 2, my = (int16_t)(mv >> 16) << 2;
+            if (mx < -th) cnt[li][ri][0][0]++;
+            else if (mx > th) cnt[li][ri][0][1]++;
+            if (my < -th) cnt[li][ri][1][0]++;
+            else if (my > th) cnt[li][ri][1][1]++;
+            const int sth = small ? 0 : 4;
+            if (iabs(mx) <= sth && iabs(my) <= sth) stationary++;
+            tot++;
+        }
+        if (stationary > ((tot * 5) / 100)) stationary_flag = 1;
+        for (int l = 0; l < NL; ++l)
+            for (int r = 0; r < NR; ++r)
+                for (int c = 0; c < 2; ++c)
+                    for (int k = 0; k < 2; ++k)
+                        if (cnt[l][r][c][k] > (tot / 2)) gm_flag = 1;
+    }
+    J.stationary[b64] = stationary_flag;
+    J.allow_gm[b64] = gm_flag;
+}
+

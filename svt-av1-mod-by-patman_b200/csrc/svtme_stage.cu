@@ -1,1038 +1,262 @@
-// svtme_stage.cu — the open-loop ME stage kernel: one CTA = one 64x64 block (b64) of one picture,
-// all reference pictures, from zz-SAD / pre-HME / HME L0-L2 to the 85-PU full-pel search, the
-// candidate arrays and the per-b64 statistics. Device twin of svt_aom_motion_estimation_b64
-// (Source/Lib/Codec/motion_estimation.c:3146-3223); citations below are into that file.
+// svtme_stage.cu — the open-loop ME stage as a PIPELINE OF WIDE KERNELS over all 64x64 blocks (b64)
+// of all pictures of a batch. Device twin of svt_aom_motion_estimation_b64
+// (Source/Lib/Codec/motion_estimation.c:3146-3223) called for every b64 by me_process.c:174-289.
 //
-// Structure: the scalar control flow of the reference (search-area derivation, edge clipping in
-// int16, early exits, reference pruning) is executed by thread 0 on a state block in shared
-// memory ("plan" / "post" steps); every SAD search it decides on is executed by the whole CTA
-// through the engines in svtme_search.cuh. All branches that surround a CTA-wide call depend only
-// on shared state published before a __syncthreads(), so control flow is uniform.
-#include "svtme_search.cuh"
+// The reference's per-b64 flow alternates scalar decisions (search areas, clipping, pruning) with
+// SAD searches. Run inside ONE CTA per b64 the scalar steps serialise on one thread while the rest
+// of the CTA waits at a barrier (measured: ~45 % of the kernel time). Here the two kinds of work are
+// separate launches over the whole batch:
+//   scalar_kernel<STEP>  one THREAD per b64: plan / post steps on a state block in global memory
+//   engine_kernel        one CTA per b64: executes the round of searches the last plan step posted
+//                        (zz-SAD, pre-HME, HME L0 / L1 / L2) through hme_search_multi
+//   int_kernel           one CTA per (b64, reference): check_00_center, 8x8-variance probe and the
+//                        85-PU full-pel search (integer_search_b64 :1249-1586)
+//   finish_kernel        one CTA per b64: me_prune_ref, candidate arrays, statistics
+// Dependencies between launches are exactly the reference's statement order; b64s never interact.
+#include "svtme_scalar.cuh"
 
-#define NL SVTME_NL
-#define NR SVTME_NR
-#define MAXU32 0xFFFFFFFFu
-#define MAX_JOBS SVTME_MAX_JOBS
-
-struct PreHme {
-    uint16_t sa_w, sa_h;
-    int16_t col, row;
-    unsigned long long sad;
-    uint8_t valid;
+struct WideArgs {
+    const DevJob *jobs;
+    StageState *st;
+    int b64_per_job, n_b64_total;
 };
 
-struct RefResult {
-    int16_t hme_sc_x, hme_sc_y;
-    unsigned long long hme_sad;
-    uint8_t do_ref;
-};
+size_t svtme_stage_state_bytes() { return sizeof(StageState); }
 
-struct JobMeta { // what the post step needs to know about an HJob
-    int8_t li, ri, a, b; // a,b: search region / quadrant indices
-    int16_t ox, oy;      // search-area origin that was applied
-};
+__device__ __forceinline__ void copy_job_to_smem(DevJob *dst, const DevJob *src) {
+    static_assert(sizeof(DevJob) % 4 == 0, "DevJob is copied as 32-bit words");
+    const uint32_t *g = reinterpret_cast<const uint32_t *>(src);
+    uint32_t *d = reinterpret_cast<uint32_t *>(dst);
+    for (int i = threadIdx.x; i < (int)(sizeof(DevJob) / 4); i += blockDim.x) d[i] = __ldg(g + i);
+}
 
-struct StageState {
-    SvtMeSearchAreaMinMax hme_l0_sa;
-    int org_x, org_y, b64_w, b64_h, pic_w, pic_h;
-    int16_t cx[3][NL][NR][2][2], cy[3][NL][NR][2][2];
-    unsigned long long lsad[3][NL][NR][2][2];
-    RefResult sr[NL][NR];
-    uint32_t div[NL][NR];
-    uint32_t zz[NL][NR];
-    PreHme ph[NL][NR][2];
-    uint8_t performed_phme[NL][NR][2];
-    uint32_t best_sad[NL][NR][SVTME_PU_COUNT], best_mv[NL][NR][SVTME_PU_COUNT];
-    uint32_t me_distortion[SVTME_PU_COUNT];
-    FpTables tab;
+__device__ __forceinline__ bool l0_dependent(const SvtMeParams &p) { // :1882-1895
+    return p.enable_me_sr_adjustment && p.distance_based_hme_resizing && p.reduce_hme_l0_sr_th_min &&
+        p.reduce_hme_l0_sr_th_max;
+}
+
+// ---------------------------------------------------------------- scalar steps (one thread per b64)
+enum { S_INIT = 0, S_ZZ, S_PREHME1, S_PREHME2, S_L0A, S_L0B, S_L1, S_L2, S_N };
+
+template <int STEP>
+__global__ void __launch_bounds__(128) scalar_kernel(WideArgs a) {
+    const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= a.n_b64_total) return;
+    const DevJob &J = a.jobs[gid / a.b64_per_job];
+    const uint32_t b64 = (uint32_t)(gid % a.b64_per_job);
+    const SvtMeParams &p = J.prm;
+    StageState *s = &a.st[gid];
+    const bool hme_l0 = p.enable_hme_flag && p.enable_hme_level0_flag;
+    const bool hme_l1 = p.enable_hme_flag && p.enable_hme_level1_flag;
+    const bool hme_l2 = p.enable_hme_flag && p.enable_hme_level2_flag;
+    const bool zz = p.me_early_exit_th || p.me_safe_limit_zz_th;
+    if (STEP == S_INIT) { // the state block was zero-filled by the host (best tables start at 0)
+        s->org_x = (int)(b64 % J.b64_cols) * 64;
+        s->org_y = (int)(b64 / J.b64_cols) * 64;
+        s->pic_w = J.width;
+        s->pic_h = J.height;
+        s->b64_w = min(64, J.width - s->org_x);
+        s->b64_h = min(64, J.height - s->org_y);
+        init_state(s, p);
+        s->n_jobs = 0;
+        if (zz) plan_zz(s, J);
+    } else if (STEP == S_ZZ) {
+        if (zz) post_zz(s, p);
+        s->n_jobs = 0;
+        if (p.prehme_enable) plan_prehme(s, J, 0);
+    } else if (STEP == S_PREHME1) {
+        if (p.prehme_enable) post_prehme_jobs(s, p);
+        s->n_jobs = 0;
+        if (p.prehme_enable && p.num_of_list_to_search > 1) plan_prehme(s, J, 1);
+    } else if (STEP == S_PREHME2) {
+        if (p.prehme_enable) {
+            post_prehme_jobs(s, p);
+            post_prehme_final(s, p);
+        }
+        s->n_jobs = 0;
+        if (hme_l0) plan_l0(s, J, l0_dependent(p), false);
+    } else if (STEP == S_L0A) {
+        if (hme_l0) {
+            post_level_jobs(s, p, 0, 4);
+            post_l0_prehme(s, p);
+        }
+        s->n_jobs = 0;
+        if (hme_l0 && l0_dependent(p)) plan_l0(s, J, false, true);
+    } else if (STEP == S_L0B) {
+        if (hme_l0 && l0_dependent(p)) {
+            post_level_jobs(s, p, 0, 4);
+            post_l0_prehme(s, p);
+        }
+        s->n_jobs = 0;
+        if (hme_l1) plan_l1(s, J);
+    } else if (STEP == S_L1) {
+        if (hme_l1) post_level_jobs(s, p, 1, 2);
+        s->n_jobs = 0;
+        if (hme_l2) plan_l2(s, J);
+    } else if (STEP == S_L2) {
+        if (hme_l2) post_level_jobs(s, p, 2, 1);
+        s->n_jobs = 0;
+        set_final_search_centre(s, p);
+        if (p.enable_hme_flag) hme_prune_ref_and_adjust_sr(s, p);
+    }
+}
+
+// ---------------------------------------------------------------- HME engine launch (one CTA per b64)
+struct EngSmem {
     HJob jobs[MAX_JOBS];
     HPlan plan;
-    JobMeta meta[MAX_JOBS];
-    int n_jobs;
-    // integer-search hand-over between plan steps
-    int fp_do, fp_sa_w, fp_sa_h, fp_ox, fp_oy, fp_probe;
-    int16_t fp_xc, fp_yc;
-    int c00_needed;
-    unsigned long long n_groups_total;
-    unsigned long long work_ops; // sum over executed searches of positions x block_w x rows
-};
-
-__device__ __forceinline__ int iabs(int v) { return v < 0 ? -v : v; }
-__device__ __forceinline__ uint16_t scaled_dist(uint16_t dist) { // svt_aom_get_scaled_picture_distance :1239
-    return (uint16_t)(((dist * 5) / 8) + ((dist % 8) ? 1 : 0));
-}
-__device__ __forceinline__ uint16_t ref_dist(const SvtMeParams &p, int li, int ri) { // get_me_reference :1232
-    long long d = (long long)p.picture_number - (long long)p.ref_picture_number[li][ri];
-    return (uint16_t)(int16_t)(d < 0 ? -d : d);
-}
-
-__device__ void add_job(StageState *s, const DevPlane &pl, int x_tl, int y_tl, int sa_w, int sa_h, int skip, int li,
-                        int ri, int a, int b, int16_t ox, int16_t oy) {
-    const int n = s->n_jobs++;
-    HJob &j = s->jobs[n];
-    // (x_tl, y_tl) already include the plane origin of the REFERENCE geometry; rebase on ours
-    j.ref = pl.base + (size_t)y_tl * pl.stride + x_tl;
-    j.stride = pl.stride;
-    j.sa_w = sa_w;
-    j.sa_h = sa_h;
-    j.skip_even = skip;
-    j.key = HME_KEY_INIT;
-    s->meta[n] = JobMeta{(int8_t)li, (int8_t)ri, (int8_t)a, (int8_t)b, ox, oy};
-}
-
-// Window clipping shared by hme_level_0/1/2 (:820-1113), with the reference's no-op left/top size
-// corrections kept. pad_w/pad_h are the LOGICAL limits (org-1 of the reference's planes, 63 at L2).
-__device__ void clip_hme(int16_t org_x, int16_t org_y, int16_t W, int16_t H, int16_t pad_w, int16_t pad_h,
-                         int16_t &sa_w, int16_t &sa_h, int16_t &ox, int16_t &oy) {
-    if ((org_x + ox) < -pad_w) {
-        ox = -pad_w - org_x;
-        sa_w = sa_w - (-pad_w - (org_x + ox));
-    }
-    if ((org_x + ox) > W - 1) ox = ox - ((org_x + ox) - (W - 1));
-    if ((org_x + ox + sa_w) > W) sa_w = max(1, sa_w - ((org_x + ox + sa_w) - W));
-    sa_w = (sa_w < 8) ? sa_w : sa_w & ~0x07;
-    if ((org_y + oy) < -pad_h) {
-        oy = -pad_h - org_y;
-        sa_h = sa_h - (-pad_h - (org_y + oy));
-    }
-    if ((org_y + oy) > H - 1) oy = oy - ((org_y + oy) - (H - 1));
-    if (org_y + oy + sa_h > H) sa_h = max(1, sa_h - ((org_y + oy + sa_h) - H));
-}
-
-__device__ void set_quadrants(StageState *s, int lvl, int li, int ri, int16_t x, int16_t y, unsigned long long sad) {
-    for (int a = 0; a < 2; ++a)
-        for (int b = 0; b < 2; ++b) {
-            s->cx[lvl][li][ri][a][b] = x;
-            s->cy[lvl][li][ri][a][b] = y;
-            s->lsad[lvl][li][ri][a][b] = sad;
-        }
-}
-
-// ---------------------------------------------------------------- plan / post steps (thread 0)
-__device__ void init_state(StageState *s, const SvtMeParams &p) { // init_me_hme_data :3080-3140
-    for (int li = 0; li < NL; ++li)
-        for (int ri = 0; ri < NR; ++ri) {
-            RefResult &r = s->sr[li][ri];
-            r.hme_sc_x = r.hme_sc_y = 0;
-            r.do_ref = 1;
-            r.hme_sad = MAXU32;
-            s->div[li][ri] = 1;
-            s->zz[li][ri] = MAXU32;
-            for (int k = 0; k < 2; ++k) {
-                PreHme &d = s->ph[li][ri][k];
-                d.sa_w = d.sa_h = 0;
-                d.col = d.row = 0;
-                d.sad = 0;
-                d.valid = 0;
-                s->performed_phme[li][ri][k] = 0;
-            }
-            for (int l = 0; l < 3; ++l) set_quadrants(s, l, li, ri, 0, 0, 0);
-        }
-    s->hme_l0_sa = p.hme_l0_sa;
-}
-
-// zz-SAD jobs: one 1x1 search per reference at MV (0,0) (get_zz_sad :1737-1759)
-__device__ void plan_zz(StageState *s, const DevJob &J) {
-    const SvtMeParams &p = J.prm;
-    s->n_jobs = 0;
-    for (int li = 0; li < p.num_of_list_to_search; ++li)
-        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri)
-            if (p.temporal_layer_index > 0 || li == 0) {
-                const DevPlane &pl = J.ref[li][ri].lvl[0];
-                add_job(s, pl, pl.org_x + s->org_x, pl.org_y + s->org_y, 1, 1, 0, li, ri, 0, 0, 0, 0);
-            }
-}
-
-__device__ void post_zz(StageState *s, const SvtMeParams &p) { // init_zz_sad :2452-2507
-    uint32_t best = MAXU32;
-    for (int n = 0; n < s->n_jobs; ++n) {
-        const JobMeta &m = s->meta[n];
-        uint32_t z = (uint32_t)(s->jobs[n].key >> 32) << 1;
-        z = (z * 64 * 64) / (uint32_t)(s->b64_w * s->b64_h);
-        s->zz[m.li][m.ri] = z;
-        best = min(best, z);
-    }
-    if (p.temporal_layer_index > 0 && best < p.zz_sad_th)
-        for (int li = 0; li < p.num_of_list_to_search; ++li)
-            for (int ri = 1; ri < p.num_of_ref_pic_to_search[li]; ++ri)
-                if ((uint32_t)((s->zz[li][ri] - best) * 100) > (uint32_t)(p.zz_sad_pct * best)) s->sr[li][ri].do_ref = 0;
-    if (p.me_safe_limit_zz_th) {
-        const bool limit = p.hierarchical_levels > 0 && p.num_of_list_to_search == 2 &&
-            p.temporal_layer_index >= p.hierarchical_levels && p.similar_brightness_refs &&
-            s->zz[0][0] < p.me_safe_limit_zz_th && s->zz[1][0] < p.me_safe_limit_zz_th;
-        if (limit)
-            for (int li = 0; li < p.num_of_list_to_search; ++li)
-                for (int ri = 1; ri < p.num_of_ref_pic_to_search[li]; ++ri) s->sr[li][ri].do_ref = 0;
-    }
-}
-
-// check_prehme_early_exit :1763-1788
-__device__ bool prehme_early_exit(StageState *s, const SvtMeParams &p, int li, int ri, int sr) {
-    PreHme &d = s->ph[li][ri][sr];
-    if (p.me_early_exit_th && s->zz[li][ri] < p.me_early_exit_th) {
-        d.col = d.row = 0;
-        d.sad = 0;
-        d.valid = 1;
-        return true;
-    }
-    if (p.prehme_l1_early_exit) {
-        const PreHme &l0 = s->ph[0][ri][sr];
-        if (li == 1 && l0.valid && ((l0.sad < (32 * 32)) || ((iabs(l0.col) < 16) && (iabs(l0.row) < 16)))) {
-            d.col = (int16_t)-l0.col;
-            d.row = (int16_t)-l0.row;
-            d.sad = l0.sad;
-            d.valid = 1;
-            return true;
-        }
-    }
-    return false;
-}
-
-// prehme_b64 (:1791-1866) for one list: decide per (ref, region) and emit jobs (prehme_core :1641)
-__device__ void plan_prehme(StageState *s, const DevJob &J, int li) {
-    const SvtMeParams &p = J.prm;
-    s->n_jobs = 0;
-    if (!(p.temporal_layer_index > 0 || li == 0)) return;
-    for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
-        const uint32_t factor = scaled_dist(ref_dist(p, li, ri));
-        for (int sr = 0; sr < 2; ++sr) {
-            if (prehme_early_exit(s, p, li, ri, sr)) continue;
-            PreHme &d = s->ph[li][ri][sr];
-            if (!s->sr[li][ri].do_ref) {
-                d.col = d.row = 0;
-                d.sad = MAXU32;
-                continue;
-            }
-            d.sa_w = (uint16_t)min(p.prehme_sa_cfg[sr].sa_min.width * factor, (uint32_t)p.prehme_sa_cfg[sr].sa_max.width);
-            d.sa_h = (uint16_t)min(p.prehme_sa_cfg[sr].sa_min.height * factor, (uint32_t)p.prehme_sa_cfg[sr].sa_max.height);
-            const DevPlane &pl = J.ref[li][ri].lvl[2];
-            const int16_t org_x = (int16_t)s->org_x >> 2, org_y = (int16_t)s->org_y >> 2;
-            const int16_t pad_w = 15, pad_h = 15; // sixteenth org (16) - 1
-            const int16_t W = (int16_t)pl.width, H = (int16_t)pl.height;
-            int16_t sa_w = (int16_t)d.sa_w, sa_h = (int16_t)d.sa_h;
-            int16_t ox = -(int16_t)(sa_w >> 1), oy = -(int16_t)(sa_h >> 1);
-            ox = ((org_x + ox) < -pad_w) ? -pad_w - org_x : ox;
-            sa_w = ((org_x + ox) < -pad_w) ? sa_w - (-pad_w - (org_x + ox)) : sa_w;
-            ox = ((org_x + ox) > W - 1) ? ox - ((org_x + ox) - (W - 1)) : ox;
-            sa_w = ((org_x + ox + sa_w) > W) ? max(1, sa_w - ((org_x + ox + sa_w) - W)) : sa_w;
-            oy = ((org_y + oy) < -pad_h) ? -pad_h - org_y : oy;
-            sa_h = ((org_y + oy) < -pad_h) ? sa_h - (-pad_h - (org_y + oy)) : sa_h;
-            oy = ((org_y + oy) > H - 1) ? oy - ((org_y + oy) - (H - 1)) : oy;
-            sa_h = (org_y + oy + sa_h > H) ? max(1, sa_h - ((org_y + oy + sa_h) - H)) : sa_h;
-            add_job(s, pl, pl.org_x + org_x + ox, pl.org_y + org_y + oy, sa_w, sa_h, p.prehme_skip_search_line, li, ri, sr,
-                    0, ox, oy);
-        }
-    }
-}
-
-__device__ void post_prehme_jobs(StageState *s, const SvtMeParams &p) {
-    const bool full = p.hme_search_method == 1;
-    for (int n = 0; n < s->n_jobs; ++n) {
-        const JobMeta &m = s->meta[n];
-        const unsigned long long k = s->jobs[n].key;
-        PreHme &d = s->ph[m.li][m.ri][m.a];
-        d.sad = (k >> 32) * (full ? 1 : 2);
-        d.col = (int16_t)((int16_t)((int16_t)(k & 0xffff) + m.ox) * 4);
-        d.row = (int16_t)((int16_t)((int16_t)((k >> 16) & 0xffff) + m.oy) * 4);
-        d.valid = 1;
-        s->performed_phme[m.li][m.ri][m.a] = 1;
-    }
-}
-
-__device__ void post_prehme_final(StageState *s, const SvtMeParams &p) { // tail of prehme_b64 :1841-1866
-    uint32_t best_sad = MAXU32;
-    for (int li = 0; li < p.num_of_list_to_search; ++li)
-        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
-            if (p.temporal_layer_index > 0 || li == 0) {
-                uint32_t m = (uint32_t)min(s->ph[li][ri][0].sad, s->ph[li][ri][1].sad);
-                best_sad = min(best_sad, m);
-            } else {
-                for (int sr = 0; sr < 2; ++sr) {
-                    s->ph[1][ri][sr].col = (int16_t)-s->ph[0][ri][sr].col;
-                    s->ph[1][ri][sr].row = (int16_t)-s->ph[0][ri][sr].row;
-                    s->ph[1][ri][sr].sad = s->ph[0][ri][sr].sad;
-                }
-            }
-        }
-    if (p.temporal_layer_index > 0 && best_sad < p.phme_sad_th)
-        for (int li = 0; li < p.num_of_list_to_search; ++li)
-            for (int ri = 1; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
-                if (!s->sr[li][ri].do_ref) continue;
-                uint32_t m = (uint32_t)min(s->ph[li][ri][0].sad, s->ph[li][ri][1].sad);
-                if ((uint32_t)((m - best_sad) * 100) > (uint32_t)(p.phme_sad_pct * best_sad)) s->sr[li][ri].do_ref = 0;
-            }
-}
-
-// get_hme_l0_search_area :1870-1935 (works on a local copy of hme_l0_sa == modify + restore)
-__device__ void hme_l0_area(const StageState *s, const SvtMeParams &p, int li, int ri, uint16_t dist, int16_t *sa_w,
-                            int16_t *sa_h) {
-    SvtMeSearchAreaMinMax a = s->hme_l0_sa;
-    if (p.enable_me_sr_adjustment && p.distance_based_hme_resizing) {
-        uint8_t is_hor = 1, is_ver = 1, is_still = 0;
-        if (p.reduce_hme_l0_sr_th_min && p.reduce_hme_l0_sr_th_max && (li || ri)) {
-            int16_t mvx = s->cx[0][0][0][0][0], mvy = s->cy[0][0][0][0][0];
-            is_ver = (iabs(mvx) < p.reduce_hme_l0_sr_th_min) && (iabs(mvy) > p.reduce_hme_l0_sr_th_max);
-            is_hor = (iabs(mvx) > p.reduce_hme_l0_sr_th_max) && (iabs(mvy) < p.reduce_hme_l0_sr_th_min);
-            is_still = (iabs(mvx) < (p.reduce_hme_l0_sr_th_min * 3)) && (iabs(mvy) < (p.reduce_hme_l0_sr_th_min * 3));
-        }
-        uint8_t xo = is_hor ? 1 : 2, yo = is_ver ? 1 : 2;
-        if (p.enable_me_sr_adjustment == 2 && is_still) xo = yo = 4;
-        a.sa_min.width = (uint16_t)(a.sa_min.width / (xo + ri));
-        a.sa_min.height = (uint16_t)(a.sa_min.height / (yo + ri));
-        a.sa_max.width = (uint16_t)(a.sa_max.width / (xo + ri));
-        a.sa_max.height = (uint16_t)(a.sa_max.height / (yo + ri));
-    }
-    const int factor = scaled_dist(dist);
-    int16_t w = (int16_t)(a.sa_min.width / p.num_hme_sa_w);
-    w = (int16_t)min((((w * factor) + 15) & ~0x0F), (((a.sa_max.width / p.num_hme_sa_w) + 15) & ~0x0F));
-    int16_t h = (int16_t)(a.sa_min.height / p.num_hme_sa_h);
-    h = (int16_t)min((h * factor), a.sa_max.height / p.num_hme_sa_h);
-    *sa_w = w;
-    *sa_h = h;
-}
-
-// hme_level0_b64 :1976-2106. first_only: plan (list0, ref0) only; skip_first: everything else.
-__device__ void plan_l0(StageState *s, const DevJob &J, bool first_only, bool skip_first) {
-    const SvtMeParams &p = J.prm;
-    s->n_jobs = 0;
-    for (int li = 0; li < p.num_of_list_to_search; ++li)
-        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
-            const bool first = (li == 0 && ri == 0);
-            if ((first_only && !first) || (skip_first && first)) continue;
-            if (p.me_early_exit_th && s->zz[li][ri] < (p.me_early_exit_th >> 2)) {
-                set_quadrants(s, 0, li, ri, 0, 0, 0);
-                continue;
-            }
-            if (p.prev_me_stage_based_exit_th) {
-                int sr = s->ph[li][ri][0].sad <= s->ph[li][ri][1].sad ? 0 : 1;
-                if (s->performed_phme[li][ri][sr] && s->ph[li][ri][sr].sad < (p.prev_me_stage_based_exit_th >> 4)) {
-                    set_quadrants(s, 0, li, ri, s->ph[li][ri][sr].col, s->ph[li][ri][sr].row, s->ph[li][ri][sr].sad);
-                    continue;
-                }
-            }
-            if (!s->sr[li][ri].do_ref) {
-                set_quadrants(s, 0, li, ri, 0, 0, MAXU32);
-                continue;
-            }
-            if (!(p.temporal_layer_index > 0 || li == 0)) continue;
-            const DevPlane &pl = J.ref[li][ri].lvl[2];
-            int16_t sa_w0 = 0, sa_h0 = 0;
-            hme_l0_area(s, p, li, ri, ref_dist(p, li, ri), &sa_w0, &sa_h0);
-            const int16_t org_x = (int16_t)s->org_x >> 2, org_y = (int16_t)s->org_y >> 2;
-            for (int sh = 0; sh < p.num_hme_sa_h; ++sh)
-                for (int sw = 0; sw < p.num_hme_sa_w; ++sw) {
-                    int16_t w = (int16_t)((sa_w0 + 7) & ~0x07), h = sa_h0;
-                    int16_t ox = (int16_t)(-(int16_t)((w * p.num_hme_sa_w) >> 1) + (int16_t)(w * sw));
-                    int16_t oy = (int16_t)(-(int16_t)((sa_h0 * p.num_hme_sa_h) >> 1) + (int16_t)(sa_h0 * sh));
-                    clip_hme(org_x, org_y, (int16_t)pl.width, (int16_t)pl.height, 15, 15, w, h, ox, oy);
-                    add_job(s, pl, pl.org_x + org_x + ox, pl.org_y + org_y + oy, w, h, 0, li, ri, sw, sh, ox, oy);
-                }
-        }
-}
-
-__device__ void post_level_jobs(StageState *s, const SvtMeParams &p, int lvl, int scale) {
-    const bool full = p.hme_search_method == 1;
-    for (int n = 0; n < s->n_jobs; ++n) {
-        const JobMeta &m = s->meta[n];
-        const unsigned long long k = s->jobs[n].key;
-        s->lsad[lvl][m.li][m.ri][m.a][m.b] = (k >> 32) * (full ? 1 : 2);
-        s->cx[lvl][m.li][m.ri][m.a][m.b] = (int16_t)((int16_t)((int16_t)(k & 0xffff) + m.ox) * scale);
-        s->cy[lvl][m.li][m.ri][m.a][m.b] = (int16_t)((int16_t)((int16_t)((k >> 16) & 0xffff) + m.oy) * scale);
-    }
-}
-
-// worst-quadrant replacement by the pre-HME result (:2073-2101, get_worst_quadrant :1939-1971)
-__device__ void post_l0_prehme(StageState *s, const SvtMeParams &p) {
-    if (!p.prehme_enable) return;
-    int last_li = -1, last_ri = -1;
-    for (int n = 0; n < s->n_jobs; ++n) {
-        const int li = s->meta[n].li, ri = s->meta[n].ri;
-        if (li == last_li && ri == last_ri) continue;
-        last_li = li;
-        last_ri = ri;
-        unsigned long long(*q)[2] = s->lsad[0][li][ri];
-        int bw = 0, bh = 0;
-        unsigned long long mx = 0;
-        if (q[0][0] > mx) { mx = q[0][0]; bw = 0; bh = 0; }
-        if (q[1][0] > mx) { mx = q[1][0]; bw = 1; bh = 0; }
-        if (q[0][1] > mx) { mx = q[0][1]; bw = 0; bh = 1; }
-        if (q[1][1] > mx) { bw = 1; bh = 1; }
-        const int sr = s->ph[li][ri][0].sad <= s->ph[li][ri][1].sad ? 0 : 1;
-        if (s->ph[li][ri][sr].sad < q[bw][bh]) {
-            q[bw][bh] = s->ph[li][ri][sr].sad;
-            s->cx[0][li][ri][bw][bh] = s->ph[li][ri][sr].col;
-            s->cy[0][li][ri][bw][bh] = s->ph[li][ri][sr].row;
-        }
-    }
-}
-
-// hme_level1_b64 :2111-2192
-__device__ void plan_l1(StageState *s, const DevJob &J) {
-    const SvtMeParams &p = J.prm;
-    s->n_jobs = 0;
-    for (int li = 0; li < p.num_of_list_to_search; ++li)
-        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
-            if (!(p.temporal_layer_index > 0 || li == 0)) continue;
-            if (p.me_early_exit_th && s->zz[li][ri] < (p.me_early_exit_th >> 2)) {
-                set_quadrants(s, 1, li, ri, 0, 0, 0);
-                continue;
-            }
-            if (!s->sr[li][ri].do_ref) {
-                set_quadrants(s, 1, li, ri, 0, 0, MAXU32);
-                continue;
-            }
-            const DevPlane &pl = J.ref[li][ri].lvl[1];
-            const int16_t org_x = (int16_t)s->org_x >> 1, org_y = (int16_t)s->org_y >> 1;
-            for (int sh = 0; sh < p.num_hme_sa_h; ++sh)
-                for (int sw = 0; sw < p.num_hme_sa_w; ++sw) {
-                    if (p.prev_me_stage_based_exit_th && s->lsad[0][li][ri][sw][sh] < (p.prev_me_stage_based_exit_th >> 5)) {
-                        s->cx[1][li][ri][sw][sh] = s->cx[0][li][ri][sw][sh];
-                        s->cy[1][li][ri][sw][sh] = s->cy[0][li][ri][sw][sh];
-                        s->lsad[1][li][ri][sw][sh] = s->lsad[0][li][ri][sw][sh];
-                        continue;
-                    }
-                    int16_t w = (int16_t)(((int16_t)p.hme_l1_sa.width + 7) & ~0x07), h = (int16_t)p.hme_l1_sa.height;
-                    int16_t ox = (int16_t)(-(w >> 1) + (s->cx[0][li][ri][sw][sh] >> 1));
-                    int16_t oy = (int16_t)(-(h >> 1) + (s->cy[0][li][ri][sw][sh] >> 1));
-                    clip_hme(org_x, org_y, (int16_t)pl.width, (int16_t)pl.height, 31, 31, w, h, ox, oy);
-                    add_job(s, pl, pl.org_x + org_x + ox, pl.org_y + org_y + oy, w, h, 0, li, ri, sw, sh, ox, oy);
-                }
-        }
-}
-
-// hme_level2_b64 :2197-2247 (no do_ref / early-exit test at this level in the reference)
-__device__ void plan_l2(StageState *s, const DevJob &J) {
-    const SvtMeParams &p = J.prm;
-    s->n_jobs = 0;
-    for (int li = 0; li < p.num_of_list_to_search; ++li)
-        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
-            if (!(p.temporal_layer_index > 0 || li == 0)) continue;
-            const DevPlane &pl = J.ref[li][ri].lvl[0];
-            const int16_t org_x = (int16_t)s->org_x, org_y = (int16_t)s->org_y;
-            for (int sh = 0; sh < p.num_hme_sa_h; ++sh)
-                for (int sw = 0; sw < p.num_hme_sa_w; ++sw) {
-                    if (p.prev_me_stage_based_exit_th && s->lsad[1][li][ri][sw][sh] < (p.prev_me_stage_based_exit_th >> 2)) {
-                        s->cx[2][li][ri][sw][sh] = s->cx[1][li][ri][sw][sh];
-                        s->cy[2][li][ri][sw][sh] = s->cy[1][li][ri][sw][sh];
-                        s->lsad[2][li][ri][sw][sh] = s->lsad[1][li][ri][sw][sh];
-                        continue;
-                    }
-                    int16_t w = (int16_t)(((int16_t)p.hme_l2_sa.width + 7) & ~0x07), h = (int16_t)p.hme_l2_sa.height;
-                    int16_t ox = (int16_t)(-(w >> 1) + s->cx[1][li][ri][sw][sh]);
-                    int16_t oy = (int16_t)(-(h >> 1) + s->cy[1][li][ri][sw][sh]);
-                    clip_hme(org_x, org_y, (int16_t)pl.width, (int16_t)pl.height, 63, 63, w, h, ox, oy);
-                    add_job(s, pl, pl.org_x + org_x + ox, pl.org_y + org_y + oy, w, h, 0, li, ri, sw, sh, ox, oy);
-                }
-        }
-}
-
-// set_final_seach_centre_sb :2252-2450 — hsad/centres persist across the (list, ref) loop.
-__device__ void set_final_search_centre(StageState *s, const SvtMeParams &p) {
-    int16_t hx = 0, hy = 0, cx = 0, cy = 0;
-    unsigned long long hsad = 0;
-    for (int li = 0; li < p.num_of_list_to_search; ++li)
-        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
-            if (p.temporal_layer_index > 0 || li == 0) {
-                if (p.enable_hme_flag) {
-                    for (int pass = 0; pass < 3; ++pass) {
-                        const bool on = pass == 0
-                            ? (p.enable_hme_level0_flag && !p.enable_hme_level1_flag && !p.enable_hme_level2_flag)
-                            : pass == 1 ? (p.enable_hme_level1_flag && !p.enable_hme_level2_flag) : p.enable_hme_level2_flag;
-                        if (!on) continue;
-                        hx = s->cx[pass][li][ri][0][0];
-                        hy = s->cy[pass][li][ri][0][0];
-                        hsad = s->lsad[pass][li][ri][0][0];
-                        uint32_t w = 1, h = 0;
-                        while (h < p.num_hme_sa_h) {
-                            while (w < p.num_hme_sa_w) {
-                                if (s->lsad[pass][li][ri][w][h] < hsad) {
-                                    hx = s->cx[pass][li][ri][w][h];
-                                    hy = s->cy[pass][li][ri][w][h];
-                                    hsad = s->lsad[pass][li][ri][w][h];
-                                }
-                                w++;
-                            }
-                            w = 0;
-                            h++;
-                        }
-                    }
-                    cx = hx;
-                    cy = hy;
-                }
-            } else {
-                cx = 0;
-                cy = 0;
-            }
-            s->sr[li][ri].hme_sc_x = cx;
-            s->sr[li][ri].hme_sc_y = cy;
-            s->sr[li][ri].hme_sad = hsad;
-        }
-}
-
-// hme_prune_ref_and_adjust_sr :2547-2588 — loops cover all 2x4 slots incl. unused ones.
-__device__ void hme_prune_ref_and_adjust_sr(StageState *s, const SvtMeParams &p) {
-    const uint16_t th = p.prune_ref_if_hme_sad_dev_bigger_than_th;
-    if (p.enable_me_hme_ref_pruning && th != (uint16_t)~0) {
-        unsigned long long best = ~0ULL;
-        for (int li = 0; li < NL; ++li)
-            for (int ri = 0; ri < NR; ++ri)
-                if (s->sr[li][ri].hme_sad < best) best = s->sr[li][ri].hme_sad;
-        for (int li = 0; li < NL; ++li)
-            for (int ri = 1; ri < NR; ++ri)
-                if ((s->sr[li][ri].hme_sad - best) * 100 > ((unsigned long long)th * best)) s->sr[li][ri].do_ref = 0;
-    }
-    if (p.enable_me_sr_adjustment)
-        for (int li = 0; li < NL; ++li)
-            for (int ri = 0; ri < NR; ++ri) {
-                const RefResult &r = s->sr[li][ri];
-                if (iabs(r.hme_sc_x) <= p.reduce_me_sr_based_on_mv_length_th &&
-                    iabs(r.hme_sc_y) <= p.reduce_me_sr_based_on_mv_length_th && r.hme_sad < p.stationary_hme_sad_abs_th)
-                    s->div[li][ri] = p.stationary_me_sr_divisor;
-                else if (r.hme_sad < p.reduce_me_sr_based_on_hme_sad_abs_th)
-                    s->div[li][ri] = p.me_sr_divisor_for_low_hme_sad;
-            }
-}
-
-// integer_search_b64 :1249-1586, one reference, split at the points where a SAD search is needed.
-// Step A: search-area size before the centre test; emits the two check_00_center SADs if needed.
-__device__ void plan_int_a(StageState *s, const DevJob &J, int li, int ri) {
-    const SvtMeParams &p = J.prm;
-    s->n_jobs = 0;
-    s->c00_needed = 0;
-    s->fp_do = s->sr[li][ri].do_ref != 0;
-    if (!s->fp_do) return;
-    int16_t xc = s->sr[li][ri].hme_sc_x, yc = s->sr[li][ri].hme_sc_y;
-    if (!p.me_early_exit_th && (xc != 0 || yc != 0) && p.is_ref) {
-        // check_00_center :1139-1206: clip the centre, then SAD at (0,0) and at the centre
-        const DevPlane &pl = J.ref[li][ri].lvl[0];
-        const int16_t org_x = (int16_t)s->org_x, org_y = (int16_t)s->org_y;
-        const int16_t W = (int16_t)pl.width, H = (int16_t)pl.height;
-        xc = ((org_x + xc) < -63) ? -63 - org_x : xc;
-        xc = ((org_x + xc) > W - 1) ? xc - ((org_x + xc) - (W - 1)) : xc;
-        yc = ((org_y + yc) < -63) ? -63 - org_y : yc;
-        yc = ((org_y + yc) > H - 1) ? yc - ((org_y + yc) - (H - 1)) : yc;
-        add_job(s, pl, pl.org_x + org_x, pl.org_y + org_y, 1, 1, 0, li, ri, 0, 0, 0, 0);
-        add_job(s, pl, pl.org_x + org_x + xc, pl.org_y + org_y + yc, 1, 1, 0, li, ri, 1, 0, 0, 0);
-        s->c00_needed = 1;
-    }
-    s->fp_xc = xc;
-    s->fp_yc = yc;
-}
-
-// Step B: finish the size logic, initialise the tables, decide on the 8x8-variance probe.
-__device__ void plan_int_b(StageState *s, const DevJob &J, int li, int ri) {
-    const SvtMeParams &p = J.prm;
-    int16_t xc = s->fp_xc, yc = s->fp_yc;
-    int16_t sa_w = (int16_t)p.me_sa.sa_min.width, sa_h = (int16_t)p.me_sa.sa_min.height;
-    const uint16_t dist = scaled_dist(ref_dist(p, li, ri));
-    sa_w = (int16_t)min((int)(sa_w * dist), (int)p.me_sa.sa_max.width);
-    sa_h = (int16_t)min((int)(sa_h * dist), (int)p.me_sa.sa_max.height);
-    // NB: the reference applies the mv-based scaling to the UNCLIPPED hme centre (:1309-1314)
-    if (p.mv_sa_adj_enabled && (!p.mv_sa_adj_nearest_ref_only || ri == 0)) {
-        if (iabs(s->sr[li][ri].hme_sc_x) > p.mv_sa_adj_mv_size_th) sa_w = (int16_t)(sa_w * p.mv_sa_adj_sa_multiplier);
-        if (iabs(s->sr[li][ri].hme_sc_y) > p.mv_sa_adj_mv_size_th) sa_h = (int16_t)(sa_h * p.mv_sa_adj_sa_multiplier);
-    }
-    sa_w = (int16_t)((max(1u, (uint32_t)sa_w / s->div[li][ri]) + 7) & ~0x07u);
-    sa_h = (int16_t)max(3u, (uint32_t)sa_h / s->div[li][ri]);
-    const int16_t h_before = sa_h, w_before = sa_w;
-    unsigned long long best_hme_sad = ~0ULL;
-    if (p.me_early_exit_th) {
-        if (s->zz[li][ri] < (p.me_early_exit_th / 6)) {
-            sa_w = 1;
-            sa_h = 1;
-        }
-    } else {
-        uint8_t accurate = 1;
-        if (s->c00_needed) {
-            const uint32_t zero_sad = (uint32_t)(s->jobs[0].key >> 32) << 1;
-            const uint32_t hme_sad = (uint32_t)(s->jobs[1].key >> 32) << 1;
-            const unsigned long long zero_cost = (uint32_t)(zero_sad << 8), hme_cost = (uint32_t)(hme_sad << 8);
-            const unsigned long long best = min(zero_cost, hme_cost);
-            xc = (best == zero_cost) ? 0 : xc;
-            yc = (best == zero_cost) ? 0 : yc;
-            best_hme_sad = hme_sad;
-            if (xc == 0 && yc == 0) accurate = 0;
-        }
-        if (p.enable_me_sr_adjustment == 2) {
-            if ((accurate && (best_hme_sad < (24 * 24))) || (p.is_ref && s->sr[li][ri].hme_sad < (24 * 24))) sa_h = sa_h / 2;
-            if ((li || ri) && s->best_sad[0][0][0] < 5000 && sa_h == h_before && sa_w == w_before) {
-                sa_h = sa_h >> 1;
-                sa_w = sa_w >> 1;
-            }
-        }
-    }
-    s->fp_xc = xc;
-    s->fp_yc = yc;
-    s->fp_sa_w = sa_w;
-    s->fp_sa_h = sa_h;
-    s->fp_probe = p.me_8x8_var_enabled && (sa_w * sa_h > 24);
-}
-
-// Step C: after the probe — 8x8-variance scaling (:1416-1441) and picture clipping (:1470-1561).
-__device__ void plan_int_c(StageState *s, const DevJob &J) {
-    const SvtMeParams &p = J.prm;
-    int16_t sa_w = (int16_t)s->fp_sa_w, sa_h = (int16_t)s->fp_sa_h;
-    const int16_t xc = s->fp_xc, yc = s->fp_yc;
-    if (s->fp_probe) {
-        const uint32_t mean = (uint32_t)(s->tab.key[0] >> 32) / 64;
-        uint32_t ssq = 0;
-        for (int i = 0; i < 64; ++i) {
-            const int32_t d = (int32_t)(uint32_t)(s->tab.key[21 + i] >> 32) - (int32_t)mean;
-            ssq += (uint32_t)(d * d);
-        }
-        const uint32_t var = ssq / 64;
-        if (var > p.me_sr_mult2_th) {
-            sa_w = (int16_t)((max(1, sa_w * 3 / 2) + 7) & ~0x7);
-            sa_h = (int16_t)max(1, sa_h * 3 / 2);
-        }
-        if (var < p.me_sr_div4_th) {
-            sa_w = (int16_t)((max(1, sa_w >> 2) + 7) & ~0x7);
-            sa_h = (int16_t)max(1, sa_h >> 2);
-            sa_h = (int16_t)max(3, (int)sa_h);
-        } else if (var < p.me_sr_div2_th) {
-            sa_w = (int16_t)((min((int)sa_w, sa_w >> 1) + 7) & ~0x7);
-            sa_h = (int16_t)min((int)sa_h, sa_h >> 1);
-            sa_h = (int16_t)max(3, (int)sa_h);
-        }
-    }
-    const int16_t org_x = (int16_t)s->org_x, org_y = (int16_t)s->org_y;
-    const int16_t W = (int16_t)s->pic_w, H = (int16_t)s->pic_h;
-    int16_t ox = (int16_t)(xc - (sa_w >> 1)), oy = (int16_t)(yc - (sa_h >> 1));
-    ox = ((org_x + ox) < -63) ? -63 - org_x : ox;
-    sa_w = ((org_x + ox) < -63) ? sa_w - (-63 - (org_x + ox)) : sa_w;
-    ox = ((org_x + ox) > W - 1) ? ox - ((org_x + ox) - (W - 1)) : ox;
-    sa_w = ((org_x + ox + sa_w) > W) ? max(1, sa_w - ((org_x + ox + sa_w) - W)) : sa_w;
-    sa_w = (sa_w < 8) ? sa_w : sa_w & ~0x07;
-    oy = ((org_y + oy) < -63) ? -63 - org_y : oy;
-    sa_h = ((org_y + oy) < -63) ? sa_h - (-63 - (org_y + oy)) : sa_h;
-    oy = ((org_y + oy) > H - 1) ? oy - ((org_y + oy) - (H - 1)) : oy;
-    sa_h = (org_y + oy + sa_h > H) ? max(1, sa_h - ((org_y + oy + sa_h) - H)) : sa_h;
-    s->fp_sa_w = sa_w;
-    s->fp_sa_h = sa_h;
-    s->fp_ox = ox;
-    s->fp_oy = oy;
-}
-
-__constant__ uint8_t k_tab8x8[64] = {0,  1,  4,  5,  16, 17, 20, 21, 2,  3,  6,  7,  18, 19, 22, 23,
-                                     8,  9,  12, 13, 24, 25, 28, 29, 10, 11, 14, 15, 26, 27, 30, 31,
-                                     32, 33, 36, 37, 48, 49, 52, 53, 34, 35, 38, 39, 50, 51, 54, 55,
-                                     40, 41, 44, 45, 56, 57, 60, 61, 42, 43, 46, 47, 58, 59, 62, 63};
-__constant__ uint8_t k_z_to_raster[85] = {
-    0,  1,  2,  3,  4,  5,  6,  9,  10, 7,  8,  11, 12, 13, 14, 17, 18, 15, 16, 19, 20, 21, 22, 29, 30, 23, 24, 31, 32,
-    37, 38, 45, 46, 39, 40, 47, 48, 25, 26, 33, 34, 27, 28, 35, 36, 41, 42, 49, 50, 43, 44, 51, 52, 53, 54, 61, 62, 55,
-    56, 63, 64, 69, 70, 77, 78, 71, 72, 79, 80, 57, 58, 65, 66, 59, 60, 67, 68, 73, 74, 81, 82, 75, 76, 83, 84};
-__constant__ uint8_t k_8x8_to_16x16[64] = {5,  5,  6,  6,  7,  7,  8,  8,  5,  5,  6,  6,  7,  7,  8,  8,
-                                           9,  9,  10, 10, 11, 11, 12, 12, 9,  9,  10, 10, 11, 11, 12, 12,
-                                           13, 13, 14, 14, 15, 15, 16, 16, 13, 13, 14, 14, 15, 15, 16, 16,
-                                           17, 17, 18, 18, 19, 19, 20, 20, 17, 17, 18, 18, 19, 19, 20, 20};
-__constant__ uint8_t k_16x16_to_32x32[16] = {1, 1, 2, 2, 1, 1, 2, 2, 3, 3, 4, 4, 3, 3, 4, 4};
-
-// me_prune_ref :1592-1635
-__device__ void me_prune_ref(StageState *s, const SvtMeParams &p) {
-    for (int li = 0; li < p.num_of_list_to_search; ++li)
-        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
-            s->sr[li][ri].hme_sad = 0;
-            if (s->sr[li][ri].do_ref == 0) {
-                s->sr[li][ri].hme_sad = (unsigned long long)SVTME_MAX_SAD_VALUE * 64;
-                continue;
-            }
-            for (int i = 0; i < 64; ++i) s->sr[li][ri].hme_sad += s->best_sad[li][ri][21 + k_tab8x8[i]];
-        }
-    const uint16_t th = p.prune_ref_if_me_sad_dev_bigger_than_th;
-    if (p.enable_me_hme_ref_pruning && th != (uint16_t)~0) {
-        unsigned long long best = ~0ULL;
-        for (int li = 0; li < NL; ++li)
-            for (int ri = 0; ri < NR; ++ri)
-                if (s->sr[li][ri].hme_sad < best) best = s->sr[li][ri].hme_sad;
-        for (int li = 0; li < NL; ++li)
-            for (int ri = 1; ri < NR; ++ri)
-                if ((s->sr[li][ri].hme_sad - best) * 100 > ((unsigned long long)th * best)) s->sr[li][ri].do_ref = 0;
-    }
-}
-
-__device__ __forceinline__ uint8_t cand_byte(unsigned dir, unsigned i0, unsigned i1, unsigned l0, unsigned l1) {
-    return (uint8_t)((dir & 3) | ((i0 & 3) << 2) | ((i1 & 3) << 4) | ((l0 & 1) << 6) | ((l1 & 1) << 7));
-}
-__device__ __forceinline__ bool use_pu(const SvtMeParams &p, uint32_t n) {
-    return p.enable_me_16x16 ? (p.enable_me_8x8 || n < 21) : n < 5;
-}
-
-// construct_me_candidate_array{,_mrp_off,_single_ref} :2602-2905 — one thread per search-order PU n.
-__device__ void construct_candidates(StageState *s, const SvtMeParams &p, uint32_t n, uint8_t *total, uint32_t *mvo,
-                                     uint8_t *cando) {
-    const uint8_t n0 = p.num_of_ref_pic_to_search[0], n1 = p.num_of_ref_pic_to_search[1];
-    uint32_t nlists = p.num_of_list_to_search;
-    const bool use = use_pu(p, n);
-    if (n0 == 1 && n1 == 0) { // _single_ref :2716
-        const uint8_t pu = k_z_to_raster[n];
-        if (use) total[pu] = 1;
-        s->me_distortion[pu] = s->best_sad[0][0][n];
-        if (s->sr[0][0].do_ref == 0) return;
-        if (use) {
-            cando[pu * p.max_cand] = cand_byte(0, 0, 0, 0, 0);
-            mvo[pu * p.max_refs] = s->best_mv[0][0][n];
-        }
-        return;
-    }
-    if (n0 == 1 && n1 == 1) { // _mrp_off :2602
-        const uint8_t pu = k_z_to_raster[n];
-        uint8_t org[2];
-        org[0] = s->sr[0][0].do_ref;
-        org[1] = (nlists == 1) ? 0 : s->sr[1][0].do_ref;
-        if (nlists < 2 || !s->sr[1][0].do_ref) nlists = 1;
-        const uint32_t th = (org[0] && org[1]) ? (uint32_t)p.prune_me_candidates_th : 0;
-        if (use) total[pu] = 1;
-        uint8_t off = 0;
-        uint8_t *cand = use ? &cando[pu * p.max_cand] : nullptr;
-        uint8_t dr[2] = {org[0], org[1]};
-        const uint32_t best = (org[0] && org[1]) ? min(s->best_sad[0][0][n], s->best_sad[1][0][n])
-            : org[0]                             ? s->best_sad[0][0][n]
-                                                 : s->best_sad[1][0][n];
-        s->me_distortion[pu] = best;
-        int min_list = -1;
-        if (p.use_best_unipred_cand_only && dr[0] && dr[1]) min_list = s->best_sad[0][0][n] < s->best_sad[1][0][n] ? 0 : 1;
-        for (int li = 0; (uint32_t)li < nlists && (use || off == 0); ++li) {
-            if (dr[li] == 0) continue;
-            if (th > 0) {
-                uint32_t d = (s->best_sad[li][0][n] - best) * 100;
-                if (d > (best * th)) {
-                    dr[li] = 0;
-                    continue;
-                }
-            }
-            if (min_list != -1 && min_list != li) {
-                if (use) mvo[pu * p.max_refs + (li ? p.max_l0 : 0)] = s->best_mv[li][0][n];
-                continue;
-            }
-            if (use) {
-                cand[off] = cand_byte((unsigned)li, 0, 0, li == 0 ? (unsigned)li : 24, li == 1 ? (unsigned)li : 24);
-                mvo[pu * p.max_refs + (li ? p.max_l0 : 0)] = s->best_mv[li][0][n];
-            }
-            off++;
-        }
-        if (dr[0] && dr[1] && use) {
-            cand[off] = cand_byte(2, 0, 0, 0, 1);
-            total[pu] = (uint8_t)(off + 1);
-        }
-        return;
-    }
-    // general :2768
-    const uint8_t pu = (n > 4) ? k_z_to_raster[n] : (uint8_t)n;
-    uint8_t off = 0;
-    uint8_t *cand = use ? &cando[pu * p.max_cand] : nullptr;
-    uint8_t dr[NL][NR];
-    const uint32_t th = (uint32_t)p.prune_me_candidates_th;
-    uint32_t best = MAXU32;
-    for (int li = 0; li < NL; ++li)
-        for (int ri = 0; ri < NR; ++ri) dr[li][ri] = 0;
-    for (uint32_t li = 0; li < nlists; ++li)
-        for (uint32_t ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
-            dr[li][ri] = s->sr[li][ri].do_ref;
-            if (dr[li][ri] == 0) continue;
-            best = s->best_sad[li][ri][n] < best ? s->best_sad[li][ri][n] : best;
-        }
-    s->me_distortion[pu] = best;
-    for (uint32_t li = 0; li < nlists && (use || off == 0); ++li)
-        for (uint32_t ri = 0; ri < p.num_of_ref_pic_to_search[li] && (use || off == 0); ++ri) {
-            if (dr[li][ri] == 0) continue;
-            if (th > 0) {
-                uint32_t d = (s->best_sad[li][ri][n] - best) * 100;
-                if (d > (best * th)) {
-                    dr[li][ri] = 0;
-                    continue;
-                }
-            }
-            if (use) {
-                cand[off] = cand_byte(li, ri, ri, li == 0 ? li : 24, li == 1 ? li : 24);
-                mvo[pu * p.max_refs + (li ? p.max_l0 : 0) + ri] = s->best_mv[li][ri][n];
-            }
-            off++;
-        }
-    if (nlists == 2 && use) {
-        for (uint32_t a = 0; a < n0; ++a)
-            for (uint32_t b = 0; b < n1; ++b) {
-                if (p.only_l_bwd && (a > 0 || b > 0)) continue;
-                if (dr[0][a] && dr[1][b]) cand[off++] = cand_byte(2, a, b, 0, 1);
-            }
-        if (!p.only_l_bwd) {
-            for (uint32_t a = 1; a < n0; ++a)
-                if (dr[0][0] && dr[0][a]) cand[off++] = cand_byte(2, 0, a, 0, 0);
-            if (n1 == 3 && dr[1][0] && dr[1][2]) cand[off++] = cand_byte(2, 0, 2, 1, 1);
-        }
-    }
-    if (use) total[pu] = off;
-}
-
-// compute_distortion :3034-3077 + perform_gm_detection :2908-3031 (thread 0)
-__device__ void finish_b64(StageState *s, const DevJob &J, uint32_t b64, const uint8_t *cando) {
-    const SvtMeParams &p = J.prm;
-    const uint32_t *d = s->me_distortion;
-    uint32_t d64 = d[0], d32 = 0, d16 = 0, d8 = 0;
-    for (int i = 0; i < 4; ++i) d32 += d[1 + i];
-    for (int i = 0; i < 16; ++i) d16 += d[5 + i];
-    for (int i = 0; i < 64; ++i) d8 += d[21 + i];
-    unsigned long long mean = d8 / 64, ssq = 0;
-    for (int i = 0; i < 64; ++i) {
-        const long long diff = (long long)d[21 + i] - (long long)mean;
-        ssq += (unsigned long long)(diff * diff);
-    }
-    const uint32_t pix = (uint32_t)(s->b64_w * s->b64_h);
-    J.var8[b64] = (uint32_t)(ssq / 64);
-    J.rc_dist[b64] = p.input_resolution_le_480p ? d8 : d16;
-    J.dist64[b64] = (d64 * 4096u) / pix;
-    J.dist32[b64] = (d32 * 4096u) / pix;
-    J.dist16[b64] = (d16 * 4096u) / pix;
-    J.dist8[b64] = (d8 * 4096u) / pix;
-    uint8_t stationary_flag = 0, gm_flag = 0;
-    if (p.gm_enabled) {
-        unsigned long long cnt[NL][NR][2][2];
-        unsigned long long stationary = 0, tot = 0;
-        for (int a = 0; a < NL; ++a)
-            for (int b = 0; b < NR; ++b)
-                for (int c = 0; c < 2; ++c) cnt[a][b][c][0] = cnt[a][b][c][1] = 0;
-        const bool small = p.input_resolution_le_480p;
-        const unsigned count = small ? 64 : 16;
-        for (unsigned i = 0; i < count; ++i) {
-            uint8_t n = (uint8_t)((small ? 21 : 5) + i);
-            if (small) {
-                if (!p.enable_me_8x8) {
-                    if (n >= 21) n = k_8x8_to_16x16[n - 21];
-                    if (!p.enable_me_16x16 && n >= 5) n = k_16x16_to_32x32[n - 5];
-                }
-            } else if (!p.enable_me_16x16 && n >= 5)
-                n = k_16x16_to_32x32[n - 5];
-            const uint8_t c = cando[n * p.max_cand];
-            const unsigned dir = c & 3, i0 = (c >> 2) & 3, i1 = (c >> 4) & 3, l0 = (c >> 6) & 1, l1 = (c >> 7) & 1;
-            const uint32_t li = (dir == 0 || dir == 2) ? l0 : l1, ri = (dir == 0 || dir == 2) ? i0 : i1;
-            const unsigned long long a = p.picture_number, b = p.ref_picture_number[li][ri];
-            int th;
-            if (small) {
-                uint16_t dist = (uint16_t)iabs((int16_t)(max(a, b) - min(a, b)));
-                th = p.gm_use_distance_based_active_th ? max(dist >> 1, 4) : 4;
-            } else {
-                uint16_t dist = (uint16_t)iabs((int16_t)(a - b));
-                th = p.gm_use_distance_based_active_th ? max(dist * 16, 32) : 32;
-            }
-            const uint32_t mv = s->best_mv[li][ri][n];
-            const int mx = (int16_t)(mv & 0xffff) << 2, my = (int16_t)(mv >> 16) << 2;
-            if (mx < -th) cnt[li][ri][0][0]++;
-            else if (mx > th) cnt[li][ri][0][1]++;
-            if (my < -th) cnt[li][ri][1][0]++;
-            else if (my > th) cnt[li][ri][1][1]++;
-            const int sth = small ? 0 : 4;
-            if (iabs(mx) <= sth && iabs(my) <= sth) stationary++;
-            tot++;
-        }
-        if (stationary > ((tot * 5) / 100)) stationary_flag = 1;
-        for (int l = 0; l < NL; ++l)
-            for (int r = 0; r < NR; ++r)
-                for (int c = 0; c < 2; ++c)
-                    for (int k = 0; k < 2; ++k)
-                        if (cnt[l][r][c][k] > (tot / 2)) gm_flag = 1;
-    }
-    J.stationary[b64] = stationary_flag;
-    J.allow_gm[b64] = gm_flag;
-}
-
-// ---------------------------------------------------------------- the kernel
-struct StageSmem {
-    StageState st;
-    DevJob job; // this picture's job descriptor, copied from global memory once
-    __align__(16) uint8_t src64[64 * 64];
-    __align__(16) uint8_t src32[32 * 32];
-    __align__(16) uint8_t src16[16 * 16];
+    DevPlane cur; // the level of the current picture this round reads its source block from
+    __align__(16) uint8_t src[64 * 64];
     __align__(16) uint8_t arena[SVTME_ARENA_BYTES];
 };
 
-int svtme_stage_smem_bytes() { return (int)sizeof(StageSmem); }
-
-#define T0(stmt)                                                    \
-    do {                                                            \
-        if (threadIdx.x == 0) {                                     \
-            const long long t0_ = clock64();                        \
-            stmt;                                                   \
-            ph[SVTME_PH_SCALAR] += (unsigned long long)(clock64() - t0_); \
-        }                                                           \
-        __syncthreads();                                            \
-    } while (0)
-
-__device__ void run_jobs(StageState *s, const HBlk &blk, uint8_t *arena) {
-    const int n = s->n_jobs; // published by T0
-    hme_search_multi(blk, s->jobs, n, &s->plan, arena);
-    if (threadIdx.x == 0) {
-        s->n_groups_total += s->plan.n_groups;
-        unsigned long long w = 0;
-        for (int j = 0; j < n; ++j) {
-            const int rows = s->jobs[j].skip_even ? s->jobs[j].sa_h / 2 : s->jobs[j].sa_h;
-            w += (unsigned long long)s->jobs[j].sa_w * rows * blk.bw * blk.nrows;
+// level: 0 = 64x64 block, every other row (zz-SAD); 1/2/3 = HME level 0/1/2 block
+__global__ void __launch_bounds__(SVTME_THREADS, SVTME_CTAS_PER_SM) engine_kernel(WideArgs a, int level) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    EngSmem *sm = reinterpret_cast<EngSmem *>(smem_raw);
+    const int gid = blockIdx.x, tid = threadIdx.x;
+    StageState *s = &a.st[gid];
+    const int n = s->n_jobs;
+    if (n == 0) return;
+    const DevJob &J = a.jobs[gid / a.b64_per_job];
+    const bool full = J.prm.hme_search_method == 1;
+    const int b64_w = s->b64_w, b64_h = s->b64_h, org_x = s->org_x, org_y = s->org_y;
+    const int sh = level == 1 ? 2 : (level == 2 ? 1 : 0); // down-scaling of the level
+    const DevPlane &pl = J.cur.lvl[level == 1 ? 2 : (level == 2 ? 1 : 0)];
+    const int side = 64 >> sh; // source block is side x side
+    {   // source block -> shared memory, 16-byte chunks (b64_src_ptr / quarter / sixteenth buffers, me_process.c:189-213)
+        const int cpr = side >> 4;
+        for (int i = tid; i < side * cpr; i += SVTME_THREADS) {
+            const int r = i / cpr, c = i - r * cpr;
+            *reinterpret_cast<uint4 *>(&sm->src[r * side + c * 16]) =
+                *reinterpret_cast<const uint4 *>(pl.at((org_x >> sh) + c * 16, (org_y >> sh) + r));
         }
-        s->work_ops += w;
+    }
+    for (int i = tid; i < n * (int)(sizeof(HJob) / 4); i += SVTME_THREADS)
+        reinterpret_cast<uint32_t *>(sm->jobs)[i] = reinterpret_cast<const uint32_t *>(s->jobs)[i];
+    __syncthreads();
+    const bool sub = level == 0 || !full;
+    const HBlk blk = make_hblk(sm->src, sub ? 2 * side : side, b64_w >> sh, sub ? (b64_h >> (sh + 1)) : (b64_h >> sh), sub ? 2 : 1);
+    hme_search_multi(blk, sm->jobs, n, &sm->plan, sm->arena);
+    unsigned long long w = 0;
+    if (tid < n) {
+        s->jobs[tid].key = sm->jobs[tid].key;
+        const int rows = sm->jobs[tid].skip_even ? sm->jobs[tid].sa_h / 2 : sm->jobs[tid].sa_h;
+        w = (unsigned long long)sm->jobs[tid].sa_w * rows * blk.bw * blk.nrows;
+    }
+    if (tid < 32 && J.work_ops) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) w += __shfl_xor_sync(0xffffffffu, w, o);
+        if (tid == 0 && w) atomicAdd(J.work_ops, w);
     }
 }
 
-__global__ void __launch_bounds__(SVTME_THREADS, SVTME_CTAS_PER_SM) me_stage_kernel(const DevJob *__restrict__ jobs, int b64_per_job) {
+// ---------------------------------------------------------------- integer search (one CTA per b64 x reference)
+struct IntSmem {
+    StageState st; // private scratch copy: only the fields integer_search_b64 reads are filled in
+    HPlan plan;
+    DevJob job;
+    __align__(16) uint8_t src64[64 * 64];
+    __align__(16) uint8_t arena[SVTME_ARENA_BYTES];
+};
+
+#define T0(stmt)                        \
+    do {                                \
+        if (threadIdx.x == 0) { stmt; } \
+        __syncthreads();                \
+    } while (0)
+
+// slots [slot0, slot0 + n_slots) of the 2x4 (list, ref_idx) grid; slot 0 = (list 0, ref 0) runs in a
+// launch of its own because the other references' search areas may depend on its result (:1345-1350)
+__global__ void __launch_bounds__(SVTME_THREADS, SVTME_CTAS_PER_SM) int_kernel(WideArgs a, int slot0, int n_slots) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
-    StageSmem *sm = reinterpret_cast<StageSmem *>(smem_raw);
+    IntSmem *sm = reinterpret_cast<IntSmem *>(smem_raw);
+    const int gid = blockIdx.x / n_slots, slot = slot0 + blockIdx.x % n_slots, tid = threadIdx.x;
+    const int li = slot / NR, ri = slot % NR;
+    const DevJob &Jg = a.jobs[gid / a.b64_per_job];
+    if (li >= Jg.prm.num_of_list_to_search || ri >= Jg.prm.num_of_ref_pic_to_search[li]) return;
+    StageState *g = &a.st[gid];
+    if (!g->sr[li][ri].do_ref) return; // pruned reference: its tables keep the zero fill (:1287-1290)
+    copy_job_to_smem(&sm->job, &Jg);
     StageState *s = &sm->st;
-    const int tid = threadIdx.x;
-    {
-        static_assert(sizeof(DevJob) % 4 == 0, "DevJob is copied as 32-bit words");
-        const uint32_t *gsrc = reinterpret_cast<const uint32_t *>(&jobs[blockIdx.x / b64_per_job]);
-        uint32_t *sdst = reinterpret_cast<uint32_t *>(&sm->job);
-        for (int i = tid; i < (int)(sizeof(DevJob) / 4); i += SVTME_THREADS) sdst[i] = __ldg(gsrc + i);
+    if (tid == 0) {
+        s->org_x = g->org_x; s->org_y = g->org_y;
+        s->b64_w = g->b64_w; s->b64_h = g->b64_h;
+        s->pic_w = g->pic_w; s->pic_h = g->pic_h;
+        s->sr[li][ri] = g->sr[li][ri];
+        s->div[li][ri] = g->div[li][ri];
+        s->zz[li][ri] = g->zz[li][ri];
+        s->best_sad[0][0][0] = g->best_sad[0][0][0];
     }
+    const int org_x = g->org_x, org_y = g->org_y;
     __syncthreads();
     const DevJob &J = sm->job;
-    const uint32_t b64 = blockIdx.x % b64_per_job;
     const SvtMeParams &p = J.prm;
-    long long t_prev = clock64(), t_start = t_prev;
-    unsigned long long ph[SVTME_PHASES];
-#pragma unroll
-    for (int k = 0; k < SVTME_PHASES; ++k) ph[k] = 0;
-#define PHASE(k)                                    \
-    do {                                            \
-        if (tid == 0) {                             \
-            const long long t_now = clock64();      \
-            ph[k] += (unsigned long long)(t_now - t_prev); \
-            t_prev = t_now;                         \
-        }                                           \
-    } while (0)
-
-#define TIMED(slot, call)                                               \
-    do {                                                                \
-        const long long t1_ = clock64();                                \
-        call;                                                           \
-        if (tid == 0) ph[slot] += (unsigned long long)(clock64() - t1_); \
-    } while (0)
-
-    const int org_x = (int)(b64 % J.b64_cols) * 64, org_y = (int)(b64 / J.b64_cols) * 64;
-    if (tid == 0) {
-        s->org_x = org_x;
-        s->org_y = org_y;
-        s->pic_w = J.width;
-        s->pic_h = J.height;
-        s->b64_w = min(64, J.width - org_x);
-        s->b64_h = min(64, J.height - org_y);
-        s->work_ops = 0;
-        s->n_groups_total = 0;
-        init_state(s, p);
-    }
-    // source blocks -> shared memory (b64_src_ptr, quarter_b64_buffer, sixteenth_b64_buffer; me_process.c:189-213)
     {
-        const DevPlane &f = J.cur.lvl[0], &q = J.cur.lvl[1], &x = J.cur.lvl[2];
+        const DevPlane &f = J.cur.lvl[0];
         for (int i = tid; i < 256; i += SVTME_THREADS) { // 64 rows x 4 chunks of 16 bytes
             const int r = i >> 2, c4 = i & 3;
             *reinterpret_cast<uint4 *>(&sm->src64[r * 64 + c4 * 16]) =
                 *reinterpret_cast<const uint4 *>(f.at(org_x + c4 * 16, org_y + r));
         }
-        if (tid < 64) {
-            const int rq = tid >> 1, cq = tid & 1;
-            *reinterpret_cast<uint4 *>(&sm->src32[rq * 32 + cq * 16]) =
-                *reinterpret_cast<const uint4 *>(q.at((org_x >> 1) + cq * 16, (org_y >> 1) + rq));
-        } else if (tid < 80) {
-            const int rs = tid - 64;
-            *reinterpret_cast<uint4 *>(&sm->src16[rs * 16]) =
-                *reinterpret_cast<const uint4 *>(x.at(org_x >> 2, (org_y >> 2) + rs));
-        }
     }
-    for (int i = tid; i < NL * NR * SVTME_PU_COUNT; i += SVTME_THREADS) {
-        (&s->best_sad[0][0][0])[i] = 0;
-        (&s->best_mv[0][0][0])[i] = 0;
+    T0(plan_int_a(s, J, li, ri));
+    unsigned long long work = 0;
+    const bool sub_sad = p.me_search_method == 0;
+    if (s->n_jobs) {
+        const HBlk blk_zz = make_hblk(sm->src64, 128, s->b64_w, s->b64_h >> 1, 2);
+        hme_search_multi(blk_zz, s->jobs, s->n_jobs, &sm->plan, sm->arena);
+        work += (unsigned long long)s->n_jobs * blk_zz.bw * blk_zz.nrows;
+    }
+    T0(plan_int_b(s, J, li, ri));
+    // svt_initialize_buffer_32bits(p_sb_best_sad, 21, 1, MAX_SAD_VALUE) :1368
+    if (tid < SVTME_PU_COUNT) {
+        s->tab.key[tid] = (unsigned long long)SVTME_MAX_SAD_VALUE << 32;
+        s->tab.mv[tid] = 0;
     }
     __syncthreads();
-
-    const int b64_w = s->b64_w, b64_h = s->b64_h;
-    const bool hme_full = p.hme_search_method == 1;
-    const HBlk blk_zz = make_hblk(sm->src64, 128, b64_w, b64_h >> 1, 2);
-    const HBlk blk_l0 = make_hblk(sm->src16, hme_full ? 16 : 32, b64_w >> 2, hme_full ? (b64_h >> 2) : (b64_h >> 3), hme_full ? 1 : 2);
-    const HBlk blk_l1 = make_hblk(sm->src32, hme_full ? 32 : 64, b64_w >> 1, hme_full ? (b64_h >> 1) : (b64_h >> 2), hme_full ? 1 : 2);
-    const HBlk blk_l2 = make_hblk(sm->src64, hme_full ? 64 : 128, b64_w, hme_full ? b64_h : (b64_h >> 1), hme_full ? 1 : 2);
-
-    PHASE(SVTME_PH_SETUP);
-    // ---- hme_b64 :2511-2545
-    if (p.me_early_exit_th || p.me_safe_limit_zz_th) {
-        T0(plan_zz(s, J));
-        TIMED(SVTME_PH_HME_ENGINE, run_jobs(s, blk_zz, sm->arena));
-        T0(post_zz(s, p));
+    const DevPlane &pl = J.ref[li][ri].lvl[0];
+    if (s->fp_probe) {
+        const int xc = s->fp_xc, yc = s->fp_yc;
+        fullpel_probe(sm->src64, pl.at(org_x + xc, org_y + yc), pl.stride, xc, yc, sub_sad, 1, &s->tab);
+        work += 64ull * (sub_sad ? 32 : 64);
     }
-    PHASE(SVTME_PH_ZZ);
-    if (p.prehme_enable) {
-        for (int li = 0; li < p.num_of_list_to_search; ++li) {
-            T0(plan_prehme(s, J, li));
-            TIMED(SVTME_PH_HME_ENGINE, run_jobs(s, blk_l0, sm->arena));
-            T0(post_prehme_jobs(s, p));
-        }
-        T0(post_prehme_final(s, p));
+    T0(plan_int_c(s, J));
+    {
+        const int ox = s->fp_ox, oy = s->fp_oy;
+        fullpel_search(sm->src64, pl.at(org_x + ox, org_y + oy), pl.stride, ox, oy, s->fp_sa_w, s->fp_sa_h, sub_sad, 2,
+                       &s->tab, sm->arena);
+        work += (unsigned long long)s->fp_sa_w * s->fp_sa_h * 64ull * (sub_sad ? 32 : 64);
     }
-    PHASE(SVTME_PH_PREHME);
-    if (p.enable_hme_flag) {
-        if (p.enable_hme_level0_flag) {
-            const bool dependent = p.enable_me_sr_adjustment && p.distance_based_hme_resizing &&
-                p.reduce_hme_l0_sr_th_min && p.reduce_hme_l0_sr_th_max;
-            if (dependent) { // other refs' areas depend on (list0, ref0)'s level-0 vector (:1882-1895)
-                T0(plan_l0(s, J, true, false));
-                TIMED(SVTME_PH_HME_ENGINE, run_jobs(s, blk_l0, sm->arena));
-                T0(post_level_jobs(s, p, 0, 4); post_l0_prehme(s, p));
-            }
-            T0(plan_l0(s, J, false, dependent));
-            TIMED(SVTME_PH_HME_ENGINE, run_jobs(s, blk_l0, sm->arena));
-            T0(post_level_jobs(s, p, 0, 4); post_l0_prehme(s, p));
-        }
-        PHASE(SVTME_PH_L0);
-        if (p.enable_hme_level1_flag) {
-            T0(plan_l1(s, J));
-            TIMED(SVTME_PH_HME_ENGINE, run_jobs(s, blk_l1, sm->arena));
-            T0(post_level_jobs(s, p, 1, 2));
-        }
-        PHASE(SVTME_PH_L1);
-        if (p.enable_hme_level2_flag) {
-            T0(plan_l2(s, J));
-            TIMED(SVTME_PH_HME_ENGINE, run_jobs(s, blk_l2, sm->arena));
-            T0(post_level_jobs(s, p, 2, 1));
-        }
-        PHASE(SVTME_PH_L2);
+    if (tid < SVTME_PU_COUNT) {
+        g->best_sad[li][ri][tid] = (uint32_t)(s->tab.key[tid] >> 32);
+        g->best_mv[li][ri][tid] = s->tab.mv[tid];
     }
-    T0(set_final_search_centre(s, p); if (p.enable_hme_flag) hme_prune_ref_and_adjust_sr(s, p));
-    PHASE(SVTME_PH_CENTRE);
+    if (tid == 0 && J.work_ops) atomicAdd(J.work_ops, work);
+}
 
-    // ---- integer_search_b64 :1249-1586
-    const bool sub_sad = p.me_search_method == 0;
-    for (int li = 0; li < p.num_of_list_to_search; ++li)
-        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
-            T0(plan_int_a(s, J, li, ri));
-            if (!s->fp_do) continue;
-            TIMED(SVTME_PH_HME_ENGINE, run_jobs(s, blk_zz, sm->arena));
-            T0(plan_int_b(s, J, li, ri));
-            // svt_initialize_buffer_32bits(p_sb_best_sad, 21, 1, MAX_SAD_VALUE) :1368
-            if (tid < SVTME_PU_COUNT) {
-                s->tab.key[tid] = (unsigned long long)SVTME_MAX_SAD_VALUE << 32;
-                s->tab.mv[tid] = 0;
-            }
-            __syncthreads();
-            PHASE(SVTME_PH_INT_CHECK);
-            const DevPlane &pl = J.ref[li][ri].lvl[0];
-            if (s->fp_probe) {
-                const int xc = s->fp_xc, yc = s->fp_yc;
-                TIMED(SVTME_PH_FP_ENGINE, fullpel_probe(sm->src64, pl.at(org_x + xc, org_y + yc), pl.stride, xc, yc, sub_sad, 1, &s->tab));
-                if (tid == 0) s->work_ops += 64ull * (sub_sad ? 32 : 64);
-            }
-            T0(plan_int_c(s, J));
-            PHASE(SVTME_PH_INT_PROBE);
-            {
-                const int ox = s->fp_ox, oy = s->fp_oy;
-                TIMED(SVTME_PH_FP_ENGINE, fullpel_search(sm->src64, pl.at(org_x + ox, org_y + oy), pl.stride, ox, oy, s->fp_sa_w,
-                                                         s->fp_sa_h, sub_sad, 2, &s->tab, sm->arena));
-                if (tid == 0) s->work_ops += (unsigned long long)s->fp_sa_w * s->fp_sa_h * 64ull * (sub_sad ? 32 : 64);
-            }
-            if (tid < SVTME_PU_COUNT) {
-                s->best_sad[li][ri][tid] = (uint32_t)(s->tab.key[tid] >> 32);
-                s->best_mv[li][ri][tid] = s->tab.mv[tid];
-            }
-            __syncthreads();
-            PHASE(SVTME_PH_INT_MAIN);
-        }
+// ---------------------------------------------------------------- pruning, candidates, statistics (one CTA per b64)
+struct FinSmem {
+    StageState st;
+    DevJob job;
+};
 
+__global__ void __launch_bounds__(128) finish_kernel(WideArgs a) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    FinSmem *sm = reinterpret_cast<FinSmem *>(smem_raw);
+    const int gid = blockIdx.x, tid = threadIdx.x;
+    const uint32_t b64 = (uint32_t)(gid % a.b64_per_job);
+    copy_job_to_smem(&sm->job, &a.jobs[gid / a.b64_per_job]);
+    {   // whole state block -> shared memory (coalesced), then the reference's scalar tail runs on it
+        const uint32_t *gs = reinterpret_cast<const uint32_t *>(&a.st[gid]);
+        uint32_t *d = reinterpret_cast<uint32_t *>(&sm->st);
+        static_assert(sizeof(StageState) % 4 == 0, "state is copied as 32-bit words");
+        for (int i = tid; i < (int)(sizeof(StageState) / 4); i += blockDim.x) d[i] = gs[i];
+    }
+    __syncthreads();
+    StageState *s = &sm->st;
+    const DevJob &J = sm->job;
+    const SvtMeParams &p = J.prm;
     // ---- pruning, candidates, statistics :3192-3221
     T0(if (p.enable_hme_flag && p.enable_me_hme_ref_pruning) me_prune_ref(s, p));
     uint8_t *total = J.total + (size_t)b64 * J.n_pu;
@@ -1041,20 +265,10 @@ __global__ void __launch_bounds__(SVTME_THREADS, SVTME_CTAS_PER_SM) me_stage_ker
     if (tid < p.max_number_of_pus_per_sb) construct_candidates(s, p, (uint32_t)tid, total, mvo, cando);
     __threadfence_block();
     __syncthreads();
-    if (tid == 0) {
-        finish_b64(s, J, b64, cando);
-        PHASE(SVTME_PH_FINISH);
-        ph[SVTME_PH_TOTAL] = (unsigned long long)(clock64() - t_start);
-        ph[SVTME_PH_HME_GROUPS] = s->n_groups_total;
-        if (J.work_ops) {
-            atomicAdd(J.work_ops, s->work_ops);
-#pragma unroll
-            for (int k = 0; k < SVTME_PHASES; ++k) atomicAdd(J.work_ops + 1 + k, ph[k]);
-        }
-    }
+    if (tid == 0) finish_b64(s, J, b64, cando);
     // deep state for parity checks
     if (J.best_sad)
-        for (int i = tid; i < NL * NR * SVTME_PU_COUNT; i += SVTME_THREADS) {
+        for (int i = tid; i < NL * NR * SVTME_PU_COUNT; i += blockDim.x) {
             J.best_sad[(size_t)b64 * NL * NR * SVTME_PU_COUNT + i] = (&s->best_sad[0][0][0])[i];
             J.best_mv[(size_t)b64 * NL * NR * SVTME_PU_COUNT + i] = (&s->best_mv[0][0][0])[i];
         }
@@ -1068,14 +282,56 @@ __global__ void __launch_bounds__(SVTME_THREADS, SVTME_CTAS_PER_SM) me_stage_ker
     }
 }
 
-void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, cudaStream_t st) {
+// ---------------------------------------------------------------- host: the launch sequence
+// Launch slots (one event after each; names in SVTME_PHASE_NAMES of svtme_common.cuh).
+void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, void *d_states, cudaStream_t st,
+                           cudaEvent_t *ev) {
     static bool configured = false;
     if (!configured) {
-        cudaFuncSetAttribute(me_stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(StageSmem));
+        cudaFuncSetAttribute(engine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EngSmem));
+        cudaFuncSetAttribute(int_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IntSmem));
+        cudaFuncSetAttribute(finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FinSmem));
         configured = true;
     }
-    me_stage_kernel<<<n_jobs * b64_per_job, SVTME_THREADS, sizeof(StageSmem), st>>>(d_jobs, b64_per_job);
-    ++g_svtme_launches;
+    WideArgs a;
+    a.jobs = d_jobs;
+    a.st = reinterpret_cast<StageState *>(d_states);
+    a.b64_per_job = b64_per_job;
+    a.n_b64_total = n_jobs * b64_per_job;
+    const int N = a.n_b64_total, sg = (N + 127) / 128;
+    int slot = 0;
+    auto mark = [&]() {
+        if (ev) cudaEventRecord(ev[slot], st);
+        ++slot;
+    };
+    cudaMemsetAsync(d_states, 0, (size_t)N * sizeof(StageState), st);
+    mark(); // 0: state clear
+    scalar_kernel<S_INIT><<<sg, 128, 0, st>>>(a);
+    engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 0);
+    scalar_kernel<S_ZZ><<<sg, 128, 0, st>>>(a);
+    mark(); // 1: zz-SAD
+    engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1);
+    scalar_kernel<S_PREHME1><<<sg, 128, 0, st>>>(a);
+    engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1);
+    scalar_kernel<S_PREHME2><<<sg, 128, 0, st>>>(a);
+    mark(); // 2: pre-HME
+    engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1);
+    scalar_kernel<S_L0A><<<sg, 128, 0, st>>>(a);
+    engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1);
+    scalar_kernel<S_L0B><<<sg, 128, 0, st>>>(a);
+    mark(); // 3: HME level 0
+    engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 2);
+    scalar_kernel<S_L1><<<sg, 128, 0, st>>>(a);
+    mark(); // 4: HME level 1
+    engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 3);
+    scalar_kernel<S_L2><<<sg, 128, 0, st>>>(a);
+    mark(); // 5: HME level 2 + search centre + HME pruning
+    int_kernel<<<N, SVTME_THREADS, sizeof(IntSmem), st>>>(a, 0, 1);
+    int_kernel<<<N * (NL * NR - 1), SVTME_THREADS, sizeof(IntSmem), st>>>(a, 1, NL * NR - 1);
+    mark(); // 6: integer search
+    finish_kernel<<<N, 128, sizeof(FinSmem), st>>>(a);
+    mark(); // 7: candidates + statistics
+    g_svtme_launches += 19;
 }
 
 // ---------------------------------------------------------------- kernel-test entry points

@@ -114,14 +114,13 @@ class MeSession:
         _check(self.lib.svtme_last_work_ops(self.h, C.byref(v)), self.lib)
         return int(v.value)
 
-    PHASE_NAMES = ("setup", "zz_sad", "prehme", "hme_l0", "hme_l1", "hme_l2", "centre_prune", "check_00",
-                   "probe", "fullpel", "finish", "total", "x_scalar", "x_hme_engine", "x_fp_engine", "n_hme_groups")
+    PHASE_NAMES = ("state_clear", "zz_sad", "prehme", "hme_l0", "hme_l1", "hme_l2_centre", "integer_search", "finish")
 
-    def last_phase_cycles(self):
-        """Per-phase SM cycles of the last launch (thread 0 of every b64 CTA, summed)."""
-        v = (C.c_uint64 * len(self.PHASE_NAMES))()
-        _check(self.lib.svtme_last_phase_cycles(self.h, v, len(self.PHASE_NAMES)), self.lib)
-        return dict(zip(self.PHASE_NAMES, (int(x) for x in v)))
+    def last_phase_ms(self):
+        """Device milliseconds per launch slot of the stage pipeline in the last launch."""
+        v = (C.c_float * len(self.PHASE_NAMES))()
+        _check(self.lib.svtme_last_phase_ms(self.h, v, len(self.PHASE_NAMES)), self.lib)
+        return dict(zip(self.PHASE_NAMES, (float(x) for x in v)))
 
     def last_kernel_ms(self):
         return float(self.lib.svtme_last_kernel_ms(self.h))

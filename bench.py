@@ -211,13 +211,11 @@ def main():
     d2h_bytes = sum(a.nbytes for o in outs for a in o.values())
 
     def step_resident():
-        for f in frames_here:
-            ses.put_picture_device(f, dev.data_ptr() + f * frame_bytes, W)
+        ses.put_pictures(frames_here, [dev.data_ptr() + f * frame_bytes for f in frames_here], W, device=True)
         ses.launch_jobs(jobs)
 
     def step_e2e():
-        for f in frames_here:
-            ses.lib.svtme_put_picture(ses.h, f, host.data_ptr() + f * frame_bytes, W)
+        ses.put_pictures(frames_here, [host.data_ptr() + f * frame_bytes for f in frames_here], W, device=False)
         ses.run_jobs(jobs)
 
     def barrier():

@@ -183,6 +183,14 @@ uint32_t svtme_exported_pu_count(const SvtMeParams *p);
 int svtme_put_picture(SvtMeHandle *h, uint64_t pic_num, const uint8_t *luma, uint32_t stride);
 /* Same, source already in device memory (tightly described by stride). */
 int svtme_put_picture_device(SvtMeHandle *h, uint64_t pic_num, const void *d_luma, uint32_t stride);
+
+/* Batched forms: n pictures, two kernel launches in total (decimation, padding). For device input
+ * with 16-byte aligned rows the decimation kernel reads the caller's buffers directly. The encoder
+ * side is the same loop as above run over a look-ahead window of pictures. */
+int svtme_put_pictures(SvtMeHandle *h, uint32_t n, const uint64_t *picture_numbers, const uint8_t *const *luma,
+                       uint32_t stride);
+int svtme_put_pictures_device(SvtMeHandle *h, uint32_t n, const uint64_t *picture_numbers, const void *const *d_luma,
+                              uint32_t stride);
 /* Copy the padded planes back (level 0 full, 1 quarter, 2 sixteenth) incl. the reference's pads
  * (72/32/16): the CPU stages that still read them (picture statistics, TF) need them. */
 int svtme_get_plane(SvtMeHandle *h, uint64_t pic_num, int level, uint8_t *dst, uint32_t dst_stride,

@@ -11,6 +11,10 @@
 #include "svtme_common.cuh"
 
 static thread_local char g_err[512] = "";
+static int failf(int code, const char *fmt, const char *who) {
+    snprintf(g_err, sizeof(g_err), fmt, who);
+    return code;
+}
 static int fail(int code, const char *what, cudaError_t e = cudaSuccess) {
     if (e != cudaSuccess)
         snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
@@ -62,6 +66,10 @@ struct SvtMeHandle {
     cudaEvent_t ev0, ev1;
     cudaEvent_t ph_ev[SVTME_PHASES];
     void *d_states = nullptr; // per-b64 scratch of the stage pipeline
+    SvtmePutItem *d_put = nullptr, *h_put = nullptr; // descriptors of the last batched pyramid build (device, pinned)
+    uint32_t put_cap = 0;
+    bool put_pending = false;
+    cudaEvent_t put_ev;
     size_t states_bytes = 0;
     float last_ms;
     std::mutex mu;
@@ -117,6 +125,7 @@ extern "C" int svtme_open(int device, uint32_t width, uint32_t height, uint32_t 
     if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
     if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
     for (int k = 0; k < SVTME_PHASES && e == cudaSuccess; ++k) e = cudaEventCreate(&h->ph_ev[k]);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->put_ev, cudaEventDisableTiming);
     if (e != cudaSuccess) { cudaFree(h->pool); delete h; return fail(SVTME_ERR_CUDA, "svtme_open", e); }
     h->slots.resize(capacity);
     for (uint32_t i = 0; i < capacity; ++i) {
@@ -146,6 +155,9 @@ extern "C" void svtme_close(SvtMeHandle *h) {
     cudaEventDestroy(h->ev1);
     for (int k = 0; k < SVTME_PHASES; ++k) cudaEventDestroy(h->ph_ev[k]);
     cudaFree(h->d_states);
+    cudaFree(h->d_put);
+    cudaFreeHost(h->h_put);
+    cudaEventDestroy(h->put_ev);
     if (h->own_stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -166,41 +178,73 @@ static int find_slot(SvtMeHandle *h, uint64_t pic, bool create) {
     return -2;
 }
 
-static int build_pyramid(SvtMeHandle *h, Slot &s) {
-    const DevPlane &f = s.pyr.lvl[0], &q = s.pyr.lvl[1], &x = s.pyr.lvl[2];
-    svtme_launch_pad_plane(f, kPadL[0], kPadR[0], kPadT[0], kPadB[0], h->stream);
-    svtme_launch_downsample(f, q, x, 1, h->stream);
-    svtme_launch_pad_plane(q, kPadL[1], kPadR[1], kPadT[1], kPadB[1], h->stream);
-    svtme_launch_pad_plane(x, kPadL[2], kPadR[2], kPadT[2], kPadB[2], h->stream);
+// n pictures -> pyramids: (host input) n H2D copies, then 2 launches for the whole batch.
+static int put_batch(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const uint8_t *const *luma, uint32_t stride,
+                     bool device_src, const char *who) {
+    if (!h || !pic_nums || !luma || stride < h->width) return failf(SVTME_ERR_INVALID, "%s: bad argument", who);
+    if (n == 0) return SVTME_OK;
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(cudaSetDevice(h->device));
+    if (n > h->put_cap) {
+        cudaFree(h->d_put);
+        cudaFreeHost(h->h_put);
+        h->d_put = h->h_put = nullptr;
+        h->put_cap = 0;
+        CU(cudaMalloc(reinterpret_cast<void **>(&h->d_put), sizeof(SvtmePutItem) * n));
+        CU(cudaMallocHost(reinterpret_cast<void **>(&h->h_put), sizeof(SvtmePutItem) * n));
+        h->put_cap = n;
+    } else if (h->put_pending) {
+        CU(cudaEventSynchronize(h->put_ev)); // the previous batch's descriptors have left the pinned buffer
+    }
+    SvtmePutItem *items = h->h_put;
+    for (uint32_t i = 0; i < n; ++i) {
+        if (!luma[i]) return failf(SVTME_ERR_INVALID, "%s: null picture", who);
+        const int si = find_slot(h, pic_nums[i], true);
+        if (si == -2) return failf(SVTME_ERR_NOMEM, "%s: pyramid ring full (release pictures or raise capacity)", who);
+        Slot &s = h->slots[si];
+        const DevPlane &f = s.pyr.lvl[0];
+        items[i].pyr = s.pyr;
+        items[i].src = nullptr;
+        items[i].src_stride = 0;
+        if (device_src && ((uintptr_t)luma[i] & 15) == 0 && (stride & 15) == 0) {
+            items[i].src = luma[i]; // the decimation kernel reads the caller's buffer and fills level 0 itself
+            items[i].src_stride = (int)stride;
+        } else {
+            // a pageable host buffer makes this copy synchronous w.r.t. the host
+            CU(cudaMemcpy2DAsync(const_cast<uint8_t *>(f.at(0, 0)), f.stride, luma[i], stride, h->width, h->height,
+                                 device_src ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, h->stream));
+        }
+    }
+    CU(cudaMemcpyAsync(h->d_put, items, sizeof(SvtmePutItem) * n, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaEventRecord(h->put_ev, h->stream));
+    h->put_pending = true;
+    SvtmePadSpec ps;
+    for (int l = 0; l < 3; ++l) {
+        ps.l[l] = kPadL[l]; ps.r[l] = kPadR[l]; ps.t[l] = kPadT[l]; ps.b[l] = kPadB[l];
+    }
+    svtme_launch_build_batch(h->d_put, (int)n, items[0].pyr, ps, h->stream);
     CU(cudaGetLastError());
     return SVTME_OK;
 }
 
+extern "C" int svtme_put_pictures(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const uint8_t *const *luma,
+                                  uint32_t stride) {
+    return put_batch(h, n, pic_nums, luma, stride, false, "svtme_put_pictures");
+}
+
+extern "C" int svtme_put_pictures_device(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const void *const *d_luma,
+                                         uint32_t stride) {
+    return put_batch(h, n, pic_nums, reinterpret_cast<const uint8_t *const *>(d_luma), stride, true,
+                     "svtme_put_pictures_device");
+}
+
 extern "C" int svtme_put_picture(SvtMeHandle *h, uint64_t pic_num, const uint8_t *luma, uint32_t stride) {
-    if (!h || !luma || stride < h->width) return fail(SVTME_ERR_INVALID, "svtme_put_picture: bad argument");
-    std::lock_guard<std::mutex> lk(h->mu);
-    CU(cudaSetDevice(h->device));
-    const int si = find_slot(h, pic_num, true);
-    if (si == -2) return fail(SVTME_ERR_NOMEM, "svtme_put_picture: pyramid ring full (release pictures or raise capacity)");
-    Slot &s = h->slots[si];
-    const DevPlane &f = s.pyr.lvl[0];
-    // the caller's buffer may be pageable: the copy is synchronous w.r.t. the host in that case
-    CU(cudaMemcpy2DAsync(const_cast<uint8_t *>(f.at(0, 0)), f.stride, luma, stride, h->width, h->height,
-                         cudaMemcpyHostToDevice, h->stream));
-    return build_pyramid(h, s);
+    return put_batch(h, 1, &pic_num, &luma, stride, false, "svtme_put_picture");
 }
 
 extern "C" int svtme_put_picture_device(SvtMeHandle *h, uint64_t pic_num, const void *d_luma, uint32_t stride) {
-    if (!h || !d_luma || stride < h->width) return fail(SVTME_ERR_INVALID, "svtme_put_picture_device: bad argument");
-    std::lock_guard<std::mutex> lk(h->mu);
-    CU(cudaSetDevice(h->device));
-    const int si = find_slot(h, pic_num, true);
-    if (si == -2) return fail(SVTME_ERR_NOMEM, "svtme_put_picture_device: pyramid ring full");
-    Slot &s = h->slots[si];
-    const DevPlane &f = s.pyr.lvl[0];
-    CU(cudaMemcpy2DAsync(const_cast<uint8_t *>(f.at(0, 0)), f.stride, d_luma, stride, h->width, h->height,
-                         cudaMemcpyDeviceToDevice, h->stream));
-    return build_pyramid(h, s);
+    const uint8_t *p = reinterpret_cast<const uint8_t *>(d_luma);
+    return put_batch(h, 1, &pic_num, &p, stride, true, "svtme_put_picture_device");
 }
 
 extern "C" int svtme_adopt_picture(SvtMeHandle *h, uint64_t pic_num) {

@@ -65,6 +65,17 @@ void svtme_launch_downsample(const DevPlane &full, const DevPlane &quarter, cons
                              int hme_level1, cudaStream_t st);
 void svtme_launch_downsample_generic(const uint8_t *in, int in_stride, int w, int h, uint8_t *out, int out_stride,
                                      int step, cudaStream_t st);
+// batched pyramid build: 2 launches for n pictures
+struct SvtmePutItem {
+    const uint8_t *src; // device luma of the caller, 16-byte aligned rows; null = level 0 already holds the picture
+    int src_stride;
+    DevPyramid pyr;
+};
+struct SvtmePadSpec {
+    int l[3], r[3], t[3], b[3];
+};
+void svtme_launch_build_batch(const SvtmePutItem *d_items, int n, const DevPyramid &geom, const SvtmePadSpec &ps,
+                              cudaStream_t st);
 // stage kernel (svtme_stage.cu)
 // d_states: n_jobs * b64_per_job * svtme_stage_state_bytes() bytes of scratch; ev: SVTME_PHASES events or null
 void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, void *d_states, cudaStream_t st,

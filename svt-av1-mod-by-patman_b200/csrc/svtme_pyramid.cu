@@ -135,6 +135,114 @@ void svtme_launch_downsample(const DevPlane &f, const DevPlane &q, const DevPlan
     ++g_svtme_launches;
 }
 
+// ------------------------------------------------------------------ batched build (n pictures, 2 launches)
+// One launch decimates n pictures (blockIdx.z = picture): the 16x4 patch is read from the caller's
+// luma buffer (or from the level-0 plane when the copy was done by the host->device transfer) and
+// written to the level-0 interior, the quarter and the sixteenth planes. A second launch pads all
+// three levels of all pictures.
+__global__ void __launch_bounds__(256) downsample_batch_kernel(const SvtmePutItem *__restrict__ items) {
+    const SvtmePutItem &it = items[blockIdx.z];
+    const DevPlane &f = it.pyr.lvl[0], &q = it.pyr.lvl[1], &x = it.pyr.lvl[2];
+    const int W = f.width, H = f.height;
+    const int px = blockIdx.x * blockDim.x + threadIdx.x, py = blockIdx.y * blockDim.y + threadIdx.y;
+    const int x0 = px * 16, y0 = py * 4;
+    if (x0 >= W || y0 >= H) return;
+    const bool wide = (x0 + 16 <= W);
+    const uint8_t *src = it.src ? it.src : f.at(0, 0);
+    const int sstride = it.src ? it.src_stride : f.stride;
+    uint32_t r[4][4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const uint8_t *row = src + (size_t)(y0 + k) * sstride + x0;
+        if (wide) {
+            const uint4 v = *reinterpret_cast<const uint4 *>(row);
+            r[k][0] = v.x; r[k][1] = v.y; r[k][2] = v.z; r[k][3] = v.w;
+        } else {
+            const uint2 v = *reinterpret_cast<const uint2 *>(row);
+            r[k][0] = v.x; r[k][1] = v.y; r[k][2] = 0; r[k][3] = 0;
+        }
+        if (it.src) {
+            uint8_t *drow = const_cast<uint8_t *>(f.at(x0, y0 + k));
+            if (wide)
+                *reinterpret_cast<uint4 *>(drow) = make_uint4(r[k][0], r[k][1], r[k][2], r[k][3]);
+            else
+                *reinterpret_cast<uint2 *>(drow) = make_uint2(r[k][0], r[k][1]);
+        }
+    }
+    uint32_t qq[2][2];
+#pragma unroll
+    for (int qr = 0; qr < 2; ++qr) {
+        const uint32_t b0 = box2(r[2 * qr][0], r[2 * qr + 1][0]), b1 = box2(r[2 * qr][1], r[2 * qr + 1][1]);
+        const uint32_t b2 = box2(r[2 * qr][2], r[2 * qr + 1][2]), b3 = box2(r[2 * qr][3], r[2 * qr + 1][3]);
+        qq[qr][0] = (b0 & 0xff) | ((b0 >> 16) << 8) | ((b1 & 0xff) << 16) | ((b1 >> 16) << 24);
+        qq[qr][1] = (b2 & 0xff) | ((b2 >> 16) << 8) | ((b3 & 0xff) << 16) | ((b3 >> 16) << 24);
+    }
+    uint8_t *qrow = const_cast<uint8_t *>(q.at(x0 >> 1, y0 >> 1));
+    if (wide) {
+        *reinterpret_cast<uint2 *>(qrow) = make_uint2(qq[0][0], qq[0][1]);
+        *reinterpret_cast<uint2 *>(qrow + q.stride) = make_uint2(qq[1][0], qq[1][1]);
+    } else {
+        *reinterpret_cast<uint32_t *>(qrow) = qq[0][0];
+        *reinterpret_cast<uint32_t *>(qrow + q.stride) = qq[1][0];
+    }
+    const uint32_t a = box2(qq[0][0], qq[1][0]), b = box2(qq[0][1], qq[1][1]);
+    const uint32_t s4 = (a & 0xff) | ((a >> 16) << 8) | ((b & 0xff) << 16) | ((b >> 16) << 24);
+    uint8_t *srow = const_cast<uint8_t *>(x.at(x0 >> 2, y0 >> 2));
+    if (wide)
+        *reinterpret_cast<uint32_t *>(srow) = s4;
+    else
+        *reinterpret_cast<uint16_t *>(srow) = (uint16_t)s4;
+}
+
+__global__ void __launch_bounds__(256) pad_batch_kernel(const SvtmePutItem *__restrict__ items, SvtmePadSpec ps) {
+    const SvtmePutItem &it = items[blockIdx.z];
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+#pragma unroll 1
+    for (int lvl = 0; lvl < 3; ++lvl) {
+        const DevPlane &p = it.pyr.lvl[lvl];
+        const int W = p.width, H = p.height, pl = ps.l[lvl], pr = ps.r[lvl], pt = ps.t[lvl], pb = ps.b[lvl];
+        const long long full_w = (long long)pl + W + pr;
+        const long long n_top = full_w * pt, n_bot = full_w * pb, n_side = (long long)(pl + pr) * H;
+        int x, y;
+        if (i < n_top) {
+            y = -pt + (int)(i / full_w);
+            x = -pl + (int)(i % full_w);
+        } else if (i - n_top < n_bot) {
+            const long long k = i - n_top;
+            y = H + (int)(k / full_w);
+            x = -pl + (int)(k % full_w);
+        } else if (i - n_top - n_bot < n_side) {
+            const long long k = i - n_top - n_bot;
+            y = (int)(k / (pl + pr));
+            const int c = (int)(k % (pl + pr));
+            x = c < pl ? -pl + c : W + (c - pl);
+        } else {
+            i -= n_top + n_bot + n_side;
+            continue;
+        }
+        const int sx = min(max(x, 0), W - 1), sy = min(max(y, 0), H - 1);
+        uint8_t *org = const_cast<uint8_t *>(p.at(0, 0));
+        org[(long long)y * p.stride + x] = org[(long long)sy * p.stride + sx];
+        return;
+    }
+}
+
+void svtme_launch_build_batch(const SvtmePutItem *d_items, int n, const DevPyramid &geom, const SvtmePadSpec &ps,
+                              cudaStream_t st) {
+    if (n <= 0) return;
+    const DevPlane &f = geom.lvl[0];
+    dim3 blk(32, 8);
+    dim3 grd((f.width + 16 * 32 - 1) / (16 * 32), (f.height + 4 * 8 - 1) / (4 * 8), n);
+    downsample_batch_kernel<<<grd, blk, 0, st>>>(d_items);
+    long long total = 0;
+    for (int l = 0; l < 3; ++l) {
+        const DevPlane &p = geom.lvl[l];
+        total += ((long long)ps.l[l] + p.width + ps.r[l]) * (ps.t[l] + ps.b[l]) + (long long)(ps.l[l] + ps.r[l]) * p.height;
+    }
+    pad_batch_kernel<<<dim3((unsigned)((total + 255) / 256), 1, n), 256, 0, st>>>(d_items, ps);
+    g_svtme_launches += 2;
+}
+
 // Generic svt_aom_downsample_2d (any size / step 2,4,8): one thread per output pixel.
 // Kernel-test ABI only (PictureOperatorTest.cc:225-335 shapes).
 __global__ void __launch_bounds__(256)

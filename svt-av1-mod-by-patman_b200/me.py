@@ -65,6 +65,14 @@ class MeSession:
     def release_picture(self, pic_num):
         _check(self.lib.svtme_release_picture(self.h, pic_num), self.lib)
 
+    def put_pictures(self, picture_numbers, ptrs, stride, device=False):
+        """Batched pyramid build: ptrs = host (or device) addresses of the luma planes."""
+        n = len(picture_numbers)
+        nums = (C.c_uint64 * n)(*picture_numbers)
+        arr = (C.c_void_p * n)(*ptrs)
+        fn = self.lib.svtme_put_pictures_device if device else self.lib.svtme_put_pictures
+        _check(fn(self.h, n, nums, arr, stride), self.lib)
+
     def get_plane(self, pic_num, level, pad=None):
         pad = (72, 32, 16)[level] if pad is None else pad
         w, h = self.width >> level, self.height >> level

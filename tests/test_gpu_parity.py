@@ -68,6 +68,33 @@ def test_pyramid_sizes_vs_oracle(size):
             assert np.array_equal(pyr.plane(lvl)[:, :got.shape[1]], got), lvl
 
 
+@pytest.mark.parametrize("size", [(856, 480), (328, 200)])
+def test_batched_pyramid_build_host_and_device_sources(size):
+    """svtme_put_pictures / svtme_put_pictures_device (2 launches per batch; aligned device rows are
+    read in place, misaligned ones go through a copy) == the oracle pyramid of every picture."""
+    import torch
+    W, H = size
+    n = 3
+    imgs = U.random_frames(W, H, n, seed=H)
+    want = [U.CpuPyramid("orc", imgs[i], i) for i in range(n)]
+    with me.MeSession(0, W, H, capacity=3 * n) as ses:
+        host = np.ascontiguousarray(imgs)
+        ses.put_pictures(list(range(n)), [host[i].ctypes.data for i in range(n)], W, device=False)
+        stride = (W + 15) // 16 * 16  # W % 16 != 0 for 856 / 328: pad the rows to keep them aligned
+        dev = torch.zeros((n, H, stride), dtype=torch.uint8, device="cuda")
+        dev[:, :, :W] = torch.from_numpy(host).cuda()
+        ses.put_pictures([10 + i for i in range(n)], [dev[i].data_ptr() for i in range(n)], stride, device=True)
+        mis = torch.zeros((n, H, stride + 3), dtype=torch.uint8, device="cuda")  # odd stride: copy path
+        mis[:, :, :W] = torch.from_numpy(host).cuda()
+        ses.put_pictures([20 + i for i in range(n)], [mis[i].data_ptr() for i in range(n)], stride + 3, device=True)
+        torch.cuda.synchronize()
+        for base in (0, 10, 20):
+            for i in range(n):
+                for lvl in range(3):
+                    got = ses.get_plane(base + i, lvl)
+                    assert np.array_equal(want[i].plane(lvl)[:, :got.shape[1]], got), (base, i, lvl)
+
+
 @pytest.mark.parametrize("preset,tl,refs,cur", [
     (8, 3, {(0, 0): 2, (0, 1): 1, (0, 2): 0, (1, 0): 4, (1, 1): 5}, 3),
     (4, 2, {(0, 0): 2, (0, 1): 1, (0, 2): 0, (0, 3): 0, (1, 0): 4, (1, 1): 5, (1, 2): 6}, 3),

@@ -132,7 +132,8 @@ struct HGeo {
     int x0, y0;          // tile origin inside the job's search area
     int xt_n, n_items, G, skip_even, variant;
     int ref_off;         // byte offset of the tile origin from the job's ref pointer
-    int rows, cpr;       // staged rows, 16-byte chunks staged per copy row
+    int rows, cpr;       // staged rows (padded to whole item tiles), 16-byte chunks staged per row
+    int rows_real;       // rows that exist in the window; staged rows beyond repeat the last one
     int stage_units;     // rows * cpr
     int scan_n;          // positions whose SAD is summed over sub-blocks in the SAD buffer (nb > 1)
     uint32_t mg_xt, mg_cpr, mg_wb;
@@ -152,150 +153,189 @@ struct HPlan {           // shared-memory scratch of one round
     int n_groups;
 };
 
-struct SrcRegs {         // one 16x8 source sub-block in registers
+struct SrcRegs {         // one full 16x8 source sub-block in registers (fast path only)
     uint32_t s[8][4];
-    uint32_t msk[4];
-    int cached_b, rows_here;
+    int cached_b;
 };
 
 __device__ __forceinline__ void load_src_regs(const HBlk &blk, int b, int bxi, int byi, SrcRegs &sr) {
     sr.cached_b = b;
-    sr.rows_here = min(8, blk.nrows - 8 * byi);
-    const int vb = min(16, blk.bw - 16 * bxi);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int n = min(max(vb - 4 * i, 0), 4);
-        sr.msk[i] = n >= 4 ? ~0u : ((1u << (8 * n)) - 1u);
-    }
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
-        if (r < sr.rows_here) {
-            const uint8_t *sp = blk.src + (size_t)(8 * byi + r) * blk.src_pitch + 16 * bxi;
-            if (vb == 16) {
-                const uint4 v = *reinterpret_cast<const uint4 *>(sp);
-                sr.s[r][0] = v.x; sr.s[r][1] = v.y; sr.s[r][2] = v.z; sr.s[r][3] = v.w;
-            } else {
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    sr.s[r][i] = sr.msk[i] ? (*reinterpret_cast<const uint32_t *>(sp + 4 * i) & sr.msk[i]) : 0u;
-            }
-        }
+        const uint4 v = *reinterpret_cast<const uint4 *>(blk.src + (size_t)(8 * byi + r) * blk.src_pitch + 16 * bxi);
+        sr.s[r][0] = v.x; sr.s[r][1] = v.y; sr.s[r][2] = v.z; sr.s[r][3] = v.w;
     }
 }
 
+// The fields of HGeo a work item needs, held in registers while a thread stays inside one job.
+struct ItemGeo {
+    uint32_t arena_off, sad_off;
+    int pitch, xt_n, sa_w, bh, y0, skip_even, variant;
+    uint32_t mg_xt;
+};
+__device__ __forceinline__ void load_item_geo(const HGeo &g, ItemGeo &ig) {
+    ig.arena_off = g.arena_off; ig.sad_off = g.sad_off;
+    ig.pitch = g.m << 4; ig.xt_n = g.xt_n; ig.sa_w = g.sa_w; ig.bh = g.bh; ig.y0 = g.y0;
+    ig.skip_even = g.skip_even; ig.variant = g.variant; ig.mg_xt = g.mg_xt;
+}
+
+// Result sink of one position. Single-sub-block blocks (<= 16x8, SAD < 2^15) keep a 32-bit running
+// key  sad << 17 | (y * sa_w + x)  (tile-local raster index < 2^16); larger blocks add their
+// sub-block SAD into the per-position buffer.
+__device__ __forceinline__ void hme_emit(bool single, uint32_t sad, int y, int x, const ItemGeo &ig, uint8_t *arena,
+                                         uint32_t &best32) {
+    const uint32_t idx = (uint32_t)(y * ig.sa_w + x);
+    if (single)
+        best32 = min(best32, (sad << 17) | idx);
+    else
+        atomicAdd(reinterpret_cast<uint32_t *>(arena + ig.sad_off) + idx, sad);
+}
+
 // One work item = G same-phase x-positions times TY y-positions (spaced row_step apart, so that
-// they share reference rows) against one 16x8 source sub-block. The window is staged ONCE,
-// byte-aligned to the search origin; phase c = x & 3 is applied in registers with funnel shifts
-// (G+4 SHF per reference row, amortised over 4*G*TY VABSDIFF4).
-template <int G, int TY, bool MASKED>
-__device__ __forceinline__ void hme_item(const HBlk &blk, const HGeo &g, uint8_t *arena, int it, SrcRegs &sr,
-                                         unsigned long long &best) {
-    const int nb = blk.nb, nbx = blk.nbx, rs = blk.row_step;
-    int t = nb == 1 ? it : (int)__umulhi((uint32_t)it, blk.mg_nb);
-    const int b = it - t * nb;
-    const int c = t & 3;
-    t >>= 2;
-    const int xt_n = g.xt_n;
-    const int yt = xt_n == 1 ? t : (int)__umulhi((uint32_t)t, g.mg_xt);
-    const int xt = t - yt * xt_n;
-    const int byi = nbx == 1 ? b : (int)__umulhi((uint32_t)b, blk.mg_nbx);
-    const int bxi = b - byi * nbx;
-    if (b != sr.cached_b) load_src_regs(blk, b, bxi, byi, sr);
-    const int yb = (yt & (rs - 1)) + (yt >> (rs - 1)) * TY * rs; // rs is 1 or 2
+// they share reference rows) against one FULL 16x8 source sub-block held in registers. The window
+// is staged once, byte-aligned to the search origin; phase c = x & 3 is applied in registers with
+// funnel shifts (G+4 SHF per reference row, amortised over 4*G*TY VABSDIFF4). No predicates in
+// the row loop: staging pads the window to whole y-tiles (clamped rows).
+template <int G, int TY>
+__device__ __forceinline__ void hme_item_fast(const HBlk &blk, const ItemGeo &ig, uint8_t *arena, int c, int xt, int yb,
+                                              int bxi, int byi, const SrcRegs &sr, uint32_t &best32) {
+    const int rs = blk.row_step;
     uint32_t acc[TY][G];
 #pragma unroll
     for (int ty = 0; ty < TY; ++ty)
 #pragma unroll
         for (int j = 0; j < G; ++j) acc[ty][j] = 0;
-    const int pitch = g.m << 4;
-    const uint8_t *base = arena + g.arena_off + 4 * (xt * G + 4 * bxi);
+    const uint8_t *base = arena + ig.arena_off + 4 * (xt * G + 4 * bxi);
     const uint32_t sh = 8 * c;
     const int row0 = yb + 8 * byi * rs;
 #pragma unroll
     for (int rho = 0; rho < TY + 7; ++rho) {
         const int row = row0 + rho * rs;
-        if (rho < sr.rows_here + TY - 1 && row < g.rows) {
-            const uint8_t *rp = base + row * pitch + ((row >> 3) << 4);
-            uint32_t w[G + 5];
-            if (G == 2) {
+        const uint8_t *rp = base + row * ig.pitch + ((row >> 3) << 4);
+        uint32_t w[G + 5];
+        if (G == 2) {
 #pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    const uint2 v = *reinterpret_cast<const uint2 *>(rp + 8 * k);
-                    w[2 * k] = v.x; w[2 * k + 1] = v.y;
-                }
-            } else {
-#pragma unroll
-                for (int k = 0; k < (G + 4) / 4; ++k) {
-                    const uint4 v = *reinterpret_cast<const uint4 *>(rp + 16 * k);
-                    w[4 * k] = v.x; w[4 * k + 1] = v.y; w[4 * k + 2] = v.z; w[4 * k + 3] = v.w;
-                }
+            for (int k = 0; k < 3; ++k) {
+                const uint2 v = *reinterpret_cast<const uint2 *>(rp + 8 * k);
+                w[2 * k] = v.x; w[2 * k + 1] = v.y;
             }
-            w[G + 4] = *reinterpret_cast<const uint32_t *>(rp + 4 * (G + 4));
+        } else {
 #pragma unroll
-            for (int i = 0; i < G + 4; ++i) w[i] = __funnelshift_r(w[i], w[i + 1], sh);
+            for (int k = 0; k < (G + 4) / 4; ++k) {
+                const uint4 v = *reinterpret_cast<const uint4 *>(rp + 16 * k);
+                w[4 * k] = v.x; w[4 * k + 1] = v.y; w[4 * k + 2] = v.z; w[4 * k + 3] = v.w;
+            }
+        }
+        w[G + 4] = *reinterpret_cast<const uint32_t *>(rp + 4 * (G + 4));
 #pragma unroll
-            for (int ty = 0; ty < TY; ++ty) {
-                const int r = rho - ty;
-                if (r >= 0 && r < 8) {
-                    if (r < sr.rows_here) {
+        for (int i = 0; i < G + 4; ++i) w[i] = __funnelshift_r(w[i], w[i + 1], sh);
 #pragma unroll
-                        for (int j = 0; j < G; ++j)
+        for (int ty = 0; ty < TY; ++ty) {
+            const int r = rho - ty;
+            if (r >= 0 && r < 8) {
 #pragma unroll
-                            for (int i = 0; i < 4; ++i)
-                                acc[ty][j] = vsad4(sr.s[r][i], MASKED ? (w[j + i] & sr.msk[i]) : w[j + i], acc[ty][j]);
-                    }
-                }
+                for (int j = 0; j < G; ++j)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) acc[ty][j] = vsad4(sr.s[r][i], w[j + i], acc[ty][j]);
             }
         }
     }
-    uint32_t *sadbuf = reinterpret_cast<uint32_t *>(arena + g.sad_off);
+    const bool single = blk.nb == 1;
 #pragma unroll
     for (int ty = 0; ty < TY; ++ty) {
         const int y = yb + ty * rs;
-        const int yg = g.y0 + y;
-        if (y < g.bh && !(g.skip_even && !(yg & 1))) {
+        if (y < ig.bh && !(ig.skip_even && !((ig.y0 + y) & 1))) {
 #pragma unroll
             for (int j = 0; j < G; ++j) {
                 const int x = xt * 4 * G + 4 * j + c;
-                if (x < g.sa_w) {
-                    if (nb == 1) {
-                        const unsigned long long k =
-                            ((unsigned long long)acc[ty][j] << 32) | ((unsigned)yg << 16) | (unsigned)(g.x0 + x);
-                        best = k < best ? k : best;
-                    } else {
-                        atomicAdd(&sadbuf[y * g.sa_w + x], acc[ty][j]);
-                    }
-                }
+                if (x < ig.sa_w) hme_emit(single, acc[ty][j], y, x, ig, arena, best32);
             }
         }
     }
 }
 
-__device__ __forceinline__ void hme_item_any(const HBlk &blk, const HGeo &g, uint8_t *arena, int it, SrcRegs &sr,
-                                             unsigned long long &best) {
-    // few variants on purpose: the unrolled bodies are large and the kernel must stay I-cache friendly
-    switch (g.variant) {
-    case 0: hme_item<2, 4, false>(blk, g, arena, it, sr, best); break;
-    case 1: hme_item<4, 4, false>(blk, g, arena, it, sr, best); break;
-    case 2: hme_item<8, 2, false>(blk, g, arena, it, sr, best); break;
-    default: hme_item<2, 1, true>(blk, g, arena, it, sr, best); break; // partial block width (rare)
+// Generic item: partial sub-blocks (block height not a multiple of 8 rows, width not a multiple of
+// 16) — edge b64s only. Position by position, source rows read from shared memory, compact code.
+__device__ __noinline__ uint32_t hme_item_slow(const HBlk blk, const ItemGeo ig, uint8_t *arena, int G, int TY, int c, int xt,
+                                               int yb, int bxi, int byi, uint32_t best32) {
+    const int rs = blk.row_step;
+    const int rows_here = min(8, blk.nrows - 8 * byi), vb = min(16, blk.bw - 16 * bxi);
+    uint32_t msk[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int n = min(max(vb - 4 * i, 0), 4);
+        msk[i] = n >= 4 ? ~0u : ((1u << (8 * n)) - 1u);
     }
+    const bool single = blk.nb == 1;
+    const uint32_t sh = 8 * c;
+    for (int ty = 0; ty < TY; ++ty) {
+        const int y = yb + ty * rs;
+        if (y >= ig.bh || (ig.skip_even && !((ig.y0 + y) & 1))) continue;
+        for (int j = 0; j < G; ++j) {
+            const int x = xt * 4 * G + 4 * j + c;
+            if (x >= ig.sa_w) continue;
+            uint32_t acc = 0;
+            for (int r = 0; r < rows_here; ++r) {
+                const int row = y + (8 * byi + r) * rs;
+                const uint32_t *rp = reinterpret_cast<const uint32_t *>(arena + ig.arena_off + row * ig.pitch +
+                                                                        ((row >> 3) << 4) + 4 * (xt * G + j + 4 * bxi));
+                const uint32_t *sp = reinterpret_cast<const uint32_t *>(blk.src + (size_t)(8 * byi + r) * blk.src_pitch + 16 * bxi);
+                uint32_t w[5];
+#pragma unroll
+                for (int i = 0; i < 5; ++i) w[i] = rp[i];
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    if (msk[i]) acc = vsad4(sp[i] & msk[i], __funnelshift_r(w[i], w[i + 1], sh) & msk[i], acc);
+            }
+            hme_emit(single, acc, y, x, ig, arena, best32);
+        }
+    }
+    return best32;
+}
+
+__device__ __forceinline__ void hme_item_any(const HBlk &blk, const ItemGeo &ig, uint8_t *arena, int it, SrcRegs &sr,
+                                             uint32_t &best32) {
+    const int nb = blk.nb, nbx = blk.nbx, rs = blk.row_step;
+    int t = nb == 1 ? it : (int)__umulhi((uint32_t)it, blk.mg_nb);
+    const int b = it - t * nb;
+    const int c = t & 3;
+    t >>= 2;
+    const int yt = ig.xt_n == 1 ? t : (int)__umulhi((uint32_t)t, ig.mg_xt);
+    const int xt = t - yt * ig.xt_n;
+    const int byi = nbx == 1 ? b : (int)__umulhi((uint32_t)b, blk.mg_nbx);
+    const int bxi = b - byi * nbx;
+    const int G = ig.variant == 0 ? 2 : (ig.variant == 1 ? 4 : 8), TY = ig.variant == 2 ? 2 : 4;
+    const int yb = (yt & (rs - 1)) + (yt >> (rs - 1)) * TY * rs; // rs is 1 or 2
+    const bool full = blk.nrows - 8 * byi >= 8 && blk.bw - 16 * bxi >= 16;
+    if (!full) {
+        best32 = hme_item_slow(blk, ig, arena, G, TY, c, xt, yb, bxi, byi, best32);
+        return;
+    }
+    if (b != sr.cached_b) load_src_regs(blk, b, bxi, byi, sr);
+    // few variants on purpose: the unrolled bodies are large and the kernel must stay I-cache friendly
+    if (ig.variant == 0)
+        hme_item_fast<2, 4>(blk, ig, arena, c, xt, yb, bxi, byi, sr, best32);
+    else if (ig.variant == 1)
+        hme_item_fast<4, 4>(blk, ig, arena, c, xt, yb, bxi, byi, sr, best32);
+    else
+        hme_item_fast<8, 2>(blk, ig, arena, c, xt, yb, bxi, byi, sr, best32);
 }
 
 // Tile geometry for a (sub)area of wb x hb positions; g.need = the arena bytes it takes.
 __device__ __forceinline__ void hme_geo(const HBlk &blk, int wb, int hb, int skip_even, HGeo &g) {
-    const bool masked = (blk.bw & 15) != 0;
-    const int G = (wb <= 8 || masked) ? 2 : (wb <= 16 ? 4 : 8);
+    const int G = wb <= 8 ? 2 : (wb <= 16 ? 4 : 8);
+    const int TY = G == 8 ? 2 : 4;
     const int tile_w = 4 * G;
     const int xt_n = (wb + tile_w - 1) / tile_w;
     const int rs = blk.row_step;
-    const int rpp = (hb + rs - 1) / rs; // positions per row-parity class
-    const int TY = masked ? 1 : (G == 8 ? 2 : 4);
-    g.variant = masked ? 3 : (G == 2 ? 0 : (G == 4 ? 1 : 2));
+    const int n_yt = (((hb + rs - 1) / rs) + TY - 1) / TY; // y-tiles per row-parity class
+    g.variant = G == 2 ? 0 : (G == 4 ? 1 : 2);
     const int words = (xt_n - 1) * G + 4 * (blk.nbx - 1) + G + 5;
     const int cpr = (words + 3) >> 2;
-    const int m = cpr | 1; // odd chunk pitch; plus one skew chunk every 8 rows (see hme_item)
-    const int rows = hb + (blk.nrows - 1) * rs;
+    const int m = cpr | 1; // odd chunk pitch; plus one skew chunk every 8 rows (see hme_item_fast)
+    g.rows_real = hb + (blk.nrows - 1) * rs;
+    // rows the (unpredicated) items of the last y-tiles touch: whole tiles of 8-row sub-blocks
+    const int rows = n_yt * TY * rs + (8 * ((blk.nrows + 7) >> 3) - 1) * rs;
     g.copy_bytes = (rows * m + (rows >> 3) + 1) * 16;
     g.m = m;
     g.sa_w = wb;
@@ -303,7 +343,7 @@ __device__ __forceinline__ void hme_geo(const HBlk &blk, int wb, int hb, int ski
     g.x0 = g.y0 = 0;
     g.ref_off = 0;
     g.xt_n = xt_n;
-    g.n_items = rs * ((rpp + TY - 1) / TY) * xt_n * 4 * blk.nb;
+    g.n_items = rs * n_yt * xt_n * 4 * blk.nb;
     g.G = G;
     g.skip_even = skip_even;
     g.rows = rows;
@@ -314,7 +354,7 @@ __device__ __forceinline__ void hme_geo(const HBlk &blk, int wb, int hb, int ski
     g.mg_cpr = magic_div((uint32_t)cpr);
     g.mg_wb = magic_div((uint32_t)wb);
     g.need = (uint32_t)g.copy_bytes + (uint32_t)g.scan_n * 4u;
-    g.big = g.need > SVTME_ARENA_BYTES || g.n_items >= 65536 || g.stage_units >= 65536 || g.scan_n >= 65536;
+    g.big = g.need > SVTME_ARENA_BYTES || g.n_items >= 65536 || g.stage_units >= 65536 || hb * wb >= 65536;
     g.arena_off = 0;
     g.sad_off = (uint32_t)g.copy_bytes;
     g.stage_base = g.item_base = g.scan_base = 0;
@@ -380,8 +420,9 @@ __device__ __noinline__ void hme_points(const HBlk &blk, HJob *jobs, int n) {
 }
 
 // ---- group helpers (separate functions: separate register allocations)
-__device__ __noinline__ void hme_group_stage(const HJob *jobs, const HGeo *geo, const HGroup &G, uint8_t *arena) {
-    constexpr int U = 8; // chunks per thread in flight
+__device__ __noinline__ void hme_group_stage(const HJob *jobs, const HGeo *geo, const HGroup &G_ref, uint8_t *arena) {
+    const HGroup G = G_ref;
+    constexpr int U = 4; // chunks per thread in flight
     const int tid = threadIdx.x;
     int cj = G.j0;
     for (int base = tid; base < G.stage_total; base += U * SVTME_THREADS) {
@@ -395,7 +436,7 @@ __device__ __noinline__ void hme_group_stage(const HJob *jobs, const HGeo *geo, 
                 const HGeo &g = geo[cj];
                 const int il = i - g.stage_base;
                 const int R = (int)__umulhi((uint32_t)il, g.mg_cpr), k = il - R * g.cpr;
-                stage_unit_load(jobs[cj].ref + g.ref_off + (size_t)R * jobs[cj].stride, k, w[u], mis[u]);
+                stage_unit_load(jobs[cj].ref + g.ref_off + (size_t)min(R, g.rows_real - 1) * jobs[cj].stride, k, w[u], mis[u]);
                 dst[u] = stage_dst(arena, g, R, k);
             }
         }
@@ -407,26 +448,49 @@ __device__ __noinline__ void hme_group_stage(const HJob *jobs, const HGeo *geo, 
     for (int i = tid; i < G.scan_total; i += SVTME_THREADS) sadreg[i] = 0;
 }
 
-__device__ __noinline__ void hme_group_items(const HBlk &blk, HJob *jobs, const HGeo *geo, const HGroup &G, uint8_t *arena) {
+// Flush of a 32-bit running key (see hme_emit): lanes flushing the same job combine with one
+// redux.min; the leader rebuilds the 64-bit key  sad << 32 | y << 16 | x  in search-area coordinates.
+__device__ __forceinline__ void flush_key32(HJob *jobs, const HGeo *geo, int j, uint32_t best32) {
+    const unsigned act = __activemask();
+    const unsigned peers = __match_any_sync(act, j);
+    const uint32_t m = __reduce_min_sync(peers, best32);
+    if ((int)(threadIdx.x & 31) == __ffs(peers) - 1 && m != ~0u) {
+        const HGeo &g = geo[j];
+        const uint32_t idx = m & 0x1ffffu;
+        const uint32_t yl = __umulhi(idx, g.mg_wb), xl = idx - yl * (uint32_t)g.sa_w;
+        const unsigned long long key =
+            ((unsigned long long)(m >> 17) << 32) | ((unsigned)(g.y0 + (int)yl) << 16) | (unsigned)(g.x0 + (int)xl);
+        if (key < HME_KEY_INIT) atomicMin(&jobs[j].key, key);
+    }
+}
+
+__device__ __noinline__ void hme_group_items(const HBlk &blk_ref, HJob *jobs, const HGeo *geo, const HGroup &G_ref,
+                                             uint8_t *arena) {
+    const HBlk blk = blk_ref; // registers: the reference points into the caller's local memory
+    const HGroup G = G_ref;
     const int nb = blk.nb;
     SrcRegs sr;
     sr.cached_b = -1;
-    sr.rows_here = 0;
-    unsigned long long best = ~0ULL;
-    int cj = G.j0, bj = -1;
+    ItemGeo ig;
+    uint32_t best32 = ~0u;
+    int cj = G.j0, bj = -1, base = 0, end = 0;
     for (int it = threadIdx.x; it < G.item_total; it += SVTME_THREADS) {
-        while (it >= geo[cj].item_base + geo[cj].n_items) ++cj;
-        if (nb == 1 && cj != bj) {
-            if (bj >= 0) flush_key(jobs, bj, best);
-            best = ~0ULL;
+        if (it >= end) {
+            while (it >= geo[cj].item_base + geo[cj].n_items) ++cj;
+            if (nb == 1 && bj >= 0) flush_key32(jobs, geo, bj, best32);
+            best32 = ~0u;
             bj = cj;
+            load_item_geo(geo[cj], ig);
+            base = geo[cj].item_base;
+            end = base + geo[cj].n_items;
         }
-        hme_item_any(blk, geo[cj], arena, it - geo[cj].item_base, sr, best);
+        hme_item_any(blk, ig, arena, it - base, sr, best32);
     }
-    if (nb == 1 && bj >= 0) flush_key(jobs, bj, best);
+    if (nb == 1 && bj >= 0) flush_key32(jobs, geo, bj, best32);
 }
 
-__device__ __noinline__ void hme_group_scan(HJob *jobs, const HGeo *geo, const HGroup &G, uint8_t *arena) {
+__device__ __noinline__ void hme_group_scan(HJob *jobs, const HGeo *geo, const HGroup &G_ref, uint8_t *arena) {
+    const HGroup G = G_ref;
     const uint32_t *sadreg = reinterpret_cast<const uint32_t *>(arena + geo[G.j0].sad_off);
     unsigned long long best = ~0ULL;
     int cj = G.j0, bj = -1;

@@ -126,6 +126,18 @@ __device__ void init_state(StageState *s, const SvtMeParams &p) { // init_me_hme
     s->hme_l0_sa = p.hme_l0_sa;
 }
 
+// init_me_hme_data on a state block the host has zero-filled: only the non-zero fields.
+__device__ void init_state_zeroed(StageState *s, const SvtMeParams &p) {
+    for (int li = 0; li < NL; ++li)
+        for (int ri = 0; ri < NR; ++ri) {
+            s->sr[li][ri].do_ref = 1;
+            s->sr[li][ri].hme_sad = MAXU32;
+            s->div[li][ri] = 1;
+            s->zz[li][ri] = MAXU32;
+        }
+    s->hme_l0_sa = p.hme_l0_sa;
+}
+
 // zz-SAD jobs: one 1x1 search per reference at MV (0,0) (get_zz_sad :1737-1759)
 __device__ void plan_zz(StageState *s, const DevJob &J) {
     const SvtMeParams &p = J.prm;

@@ -26,7 +26,13 @@
 #define SVTME_CTAS_PER_SM 4
 #endif
 #ifndef SVTME_ARENA_BYTES
-#define SVTME_ARENA_BYTES (32 * 1024)
+#define SVTME_ARENA_BYTES (32 * 1024) // full-pel engine (four phase copies of a 32x16-position tile)
+#endif
+#ifndef SVTME_HME_ARENA_BYTES
+#define SVTME_HME_ARENA_BYTES (32 * 1024) // HME engine: the tallest pre-HME window (8x400, 20.7 KB) plus its wide twin (7.9 KB)
+#endif
+#ifndef SVTME_HME_CTAS_PER_SM
+#define SVTME_HME_CTAS_PER_SM 4
 #endif
 #define SVTME_FP_YL (SVTME_THREADS / 64) // row lanes of the full-pel engine
 
@@ -354,7 +360,7 @@ __device__ __forceinline__ void hme_geo(const HBlk &blk, int wb, int hb, int ski
     g.mg_cpr = magic_div((uint32_t)cpr);
     g.mg_wb = magic_div((uint32_t)wb);
     g.need = (uint32_t)g.copy_bytes + (uint32_t)g.scan_n * 4u;
-    g.big = g.need > SVTME_ARENA_BYTES || g.n_items >= 65536 || g.stage_units >= 65536 || hb * wb >= 65536;
+    g.big = g.need > SVTME_HME_ARENA_BYTES || g.n_items >= 65536 || g.stage_units >= 65536 || hb * wb >= 65536;
     g.arena_off = 0;
     g.sad_off = (uint32_t)g.copy_bytes;
     g.stage_base = g.item_base = g.scan_base = 0;
@@ -603,7 +609,7 @@ __device__ __noinline__ void hme_search_multi(const HBlk &blk, HJob *jobs, int n
                 const uint32_t t = __shfl_up_sync(full, ps, o);
                 if (lane >= o) ps += t;
             }
-            const unsigned brk = __ballot_sync(full, from && (big || ps > SVTME_ARENA_BYTES));
+            const unsigned brk = __ballot_sync(full, from && (big || ps > SVTME_HME_ARENA_BYTES));
             int end = brk ? __ffs(brk) - 1 : n;
             const int first_big = end == start;
             if (first_big) end = start + 1;

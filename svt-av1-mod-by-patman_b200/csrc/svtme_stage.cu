@@ -57,7 +57,7 @@ __global__ void __launch_bounds__(128) scalar_kernel(WideArgs a) {
         s->pic_h = J.height;
         s->b64_w = min(64, J.width - s->org_x);
         s->b64_h = min(64, J.height - s->org_y);
-        init_state(s, p);
+        init_state_zeroed(s, p);
         s->n_jobs = 0;
         if (zz) plan_zz(s, J);
     } else if (STEP == S_ZZ) {
@@ -107,11 +107,11 @@ struct EngSmem {
     HPlan plan;
     DevPlane cur; // the level of the current picture this round reads its source block from
     __align__(16) uint8_t src[64 * 64];
-    __align__(16) uint8_t arena[SVTME_ARENA_BYTES];
+    __align__(16) uint8_t arena[SVTME_HME_ARENA_BYTES];
 };
 
 // level: 0 = 64x64 block, every other row (zz-SAD); 1/2/3 = HME level 0/1/2 block
-__global__ void __launch_bounds__(SVTME_THREADS, SVTME_CTAS_PER_SM) engine_kernel(WideArgs a, int level) {
+__global__ void __launch_bounds__(SVTME_THREADS, SVTME_HME_CTAS_PER_SM) engine_kernel(WideArgs a, int level) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     EngSmem *sm = reinterpret_cast<EngSmem *>(smem_raw);
     const int gid = blockIdx.x, tid = threadIdx.x;
@@ -149,6 +149,21 @@ __global__ void __launch_bounds__(SVTME_THREADS, SVTME_CTAS_PER_SM) engine_kerne
         for (int o = 16; o > 0; o >>= 1) w += __shfl_xor_sync(0xffffffffu, w, o);
         if (tid == 0 && w) atomicAdd(J.work_ops, w);
     }
+}
+
+// ---------------------------------------------------------------- rounds of single-position SADs (zz-SAD)
+// No staging, no shared memory: one warp per job reads source and reference rows straight from
+// global memory (get_zz_sad :1737-1759 -> svt_nxm_sad_kernel on every other row of the 64x64 block).
+__global__ void __launch_bounds__(128) points_kernel(WideArgs a) {
+    const int gid = blockIdx.x;
+    StageState *s = &a.st[gid];
+    const int n = s->n_jobs;
+    if (n == 0) return;
+    const DevJob &J = a.jobs[gid / a.b64_per_job];
+    const DevPlane &pl = J.cur.lvl[0];
+    const HBlk blk = make_hblk(pl.at(s->org_x, s->org_y), 2 * pl.stride, s->b64_w, s->b64_h >> 1, 2);
+    hme_points(blk, s->jobs, n);
+    if (threadIdx.x == 0 && J.work_ops) atomicAdd(J.work_ops, (unsigned long long)n * blk.bw * blk.nrows);
 }
 
 // ---------------------------------------------------------------- integer search (one CTA per b64 x reference)
@@ -307,7 +322,7 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, vo
     cudaMemsetAsync(d_states, 0, (size_t)N * sizeof(StageState), st);
     mark(); // 0: state clear
     scalar_kernel<S_INIT><<<sg, 128, 0, st>>>(a);
-    engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 0);
+    points_kernel<<<N, 128, 0, st>>>(a);
     scalar_kernel<S_ZZ><<<sg, 128, 0, st>>>(a);
     mark(); // 1: zz-SAD
     engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1);

@@ -186,9 +186,9 @@ def main():
 
     import torch
     import torch.distributed as dist
-    if world > 1:
-        dist.init_process_group("nccl", rank=rank, world_size=world)
     torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
     me = importlib.import_module(PKG + ".me")
     shard = importlib.import_module(PKG + ".shard")
     by_picture = args.sharding == "picture" and world > 1

@@ -285,13 +285,13 @@ def main():
                         "d2h_bytes_per_step": d2h_bytes,
                         "frames_per_s": n_streams * F / (ms_e2e / args.steps * 1e-3), "ms_per_step": ms_e2e / args.steps},
                 "gpu_launches": int(launches),
-                "roofline": {"bound": "int_alu", "kernel": "me_stage_kernel", "achieved": int_achieved, "peak": int_peak,
+                "roofline": {"bound": "int_alu", "kernel": "stage pipeline (19 launches: scalar/points/engine/int/finish kernels)", "achieved": int_achieved, "peak": int_peak,
                              "unit": "Tbyte-SAD/s", "frac": int_achieved / int_peak if int_peak else None, "traffic": None,
                              "peak_source": "VABSDIFF4.U8.ACC issue rate measured live in this run (%.0f Ginst/s x 4 bytes)" % vsad,
                              "work_byte_ops_per_launch": work_ops, "kernel_ms": kernel_ms,
                              "kernel_share_of_step": kernel_ms / ms_step,
                              "phase_ms": {k: round(v, 3) for k, v in phases.items()}},
-                "roofline_hbm": {"bound": "hbm", "kernel": "me_stage_kernel", "achieved": alg_bytes / (kernel_ms * 1e-3) / 1e9,
+                "roofline_hbm": {"bound": "hbm", "kernel": "stage pipeline", "achieved": alg_bytes / (kernel_ms * 1e-3) / 1e9,
                                  "peak": hbm_peak, "unit": "GB/s", "frac": alg_bytes / (kernel_ms * 1e-3) / 1e9 / hbm_peak,
                                  "traffic": None, "peak_source": hbm_src},
                 "cpu_baseline": {"value": cpu["sbs_per_s"], "unit": "SB/s", "cores": threads, "kind": cpu["kind"],

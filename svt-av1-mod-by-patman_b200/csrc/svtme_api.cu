@@ -297,6 +297,25 @@ extern "C" int svtme_sync(SvtMeHandle *h) {
     return SVTME_OK;
 }
 
+// Upper bound of the full-pel search area of a picture (integer_search_b64 :1298-1320,1416-1441):
+// min(sa_min * dist, sa_max), optional mv-based multiplier, width rounded up to 8, height >= 3,
+// optional x1.5 of the 8x8-variance probe. Divisors only shrink it.
+static bool areas_are_small(const SvtMeParams &p) {
+    uint32_t w = p.me_sa.sa_max.width, hgt = p.me_sa.sa_max.height;
+    if (p.mv_sa_adj_enabled) {
+        const uint32_t mult = p.mv_sa_adj_sa_multiplier ? p.mv_sa_adj_sa_multiplier : 1;
+        w *= mult;
+        hgt *= mult;
+    }
+    w = ((w ? w : 1u) + 7u) & ~7u;
+    hgt = hgt < 3 ? 3 : hgt;
+    if (p.me_8x8_var_enabled && p.me_sr_mult2_th != 0xFFFFFFFFu) {
+        w = ((w * 3 / 2) + 7u) & ~7u;
+        hgt = hgt * 3 / 2;
+    }
+    return w * hgt <= (uint32_t)svtme_fp_direct_max();
+}
+
 // ---- result buffers: per job one packed record, same order on device and in the pinned mirror
 struct OutLayout {
     size_t total, mv, cand, d64, d32, d16, d8, var8, rc, stat, gm, work, bsad, bmv, sc, hsad, doref, end;
@@ -411,7 +430,9 @@ extern "C" int svtme_launch_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint3
             h->states_bytes = need;
         }
     }
-    svtme_launch_me_stage(h->d_jobs, (int)n, (int)h->n_b64, h->d_states, h->stream, h->ph_ev);
+    bool small_areas = true;
+    for (uint32_t i = 0; i < n; ++i) small_areas = small_areas && areas_are_small(jobs[i].params);
+    svtme_launch_me_stage(h->d_jobs, (int)n, (int)h->n_b64, h->d_states, h->stream, h->ph_ev, small_areas);
     CU(cudaGetLastError());
     CU(cudaEventRecord(h->ev1, h->stream));
     return SVTME_OK;

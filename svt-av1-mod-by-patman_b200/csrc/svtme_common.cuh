@@ -78,8 +78,10 @@ void svtme_launch_build_batch(const SvtmePutItem *d_items, int n, const DevPyram
                               cudaStream_t st);
 // stage kernel (svtme_stage.cu)
 // d_states: n_jobs * b64_per_job * svtme_stage_state_bytes() bytes of scratch; ev: SVTME_PHASES events or null
+// small_areas: every full-pel search area of the batch is at most svtme_fp_direct_max() positions
 void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, void *d_states, cudaStream_t st,
-                           cudaEvent_t *ev);
+                           cudaEvent_t *ev, bool small_areas);
+int svtme_fp_direct_max();
 size_t svtme_stage_state_bytes();
 // kernel-test entry points (svtme_stage.cu)
 void svtme_launch_sad_loop_test(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride,

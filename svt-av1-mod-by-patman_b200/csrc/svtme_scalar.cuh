@@ -46,10 +46,27 @@ struct StageState {
     JobMeta meta[MAX_JOBS];
     int n_jobs;
     // integer-search hand-over between plan steps
-    int fp_do, fp_sa_w, fp_sa_h, fp_ox, fp_oy, fp_probe;
+    int fp_do, fp_sa_w, fp_sa_h, fp_ox, fp_oy, fp_probe, fp_phase;
     int16_t fp_xc, fp_yc;
     int c00_needed;
     unsigned long long work_ops; // sum over executed searches of positions x block_w x rows
+};
+
+// The slice of the state integer_search_b64 works on for ONE reference (int_kernel keeps it in
+// shared memory). Member names match StageState so that the plan_int_* steps compile for both.
+struct IntState {
+    int org_x, org_y, b64_w, b64_h, pic_w, pic_h;
+    RefResult sr[NL][NR];
+    uint32_t div[NL][NR];
+    uint32_t zz[NL][NR];
+    uint32_t best_sad[1][1][1]; // p_sb_best_sad of (list 0, ref 0), 64x64 PU (:1345)
+    FpTables tab;
+    HJob jobs[2];
+    JobMeta meta[2];
+    int n_jobs;
+    int fp_do, fp_sa_w, fp_sa_h, fp_ox, fp_oy, fp_probe, fp_phase;
+    int16_t fp_xc, fp_yc;
+    int c00_needed;
 };
 
 __device__ __forceinline__ int iabs(int v) { return v < 0 ? -v : v; }
@@ -61,7 +78,8 @@ __device__ __forceinline__ uint16_t ref_dist(const SvtMeParams &p, int li, int r
     return (uint16_t)(int16_t)(d < 0 ? -d : d);
 }
 
-__device__ void add_job(StageState *s, const DevPlane &pl, int x_tl, int y_tl, int sa_w, int sa_h, int skip, int li,
+template <class S>
+__device__ void add_job(S *s, const DevPlane &pl, int x_tl, int y_tl, int sa_w, int sa_h, int skip, int li,
                         int ri, int a, int b, int16_t ox, int16_t oy) {
     const int n = s->n_jobs++;
     HJob &j = s->jobs[n];
@@ -502,7 +520,8 @@ __device__ void hme_prune_ref_and_adjust_sr(StageState *s, const SvtMeParams &p)
 
 // integer_search_b64 :1249-1586, one reference, split at the points where a SAD search is needed.
 // Step A: search-area size before the centre test; emits the two check_00_center SADs if needed.
-__device__ void plan_int_a(StageState *s, const DevJob &J, int li, int ri) {
+template <class S>
+__device__ void plan_int_a(S *s, const DevJob &J, int li, int ri) {
     const SvtMeParams &p = J.prm;
     s->n_jobs = 0;
     s->c00_needed = 0;
@@ -527,7 +546,8 @@ __device__ void plan_int_a(StageState *s, const DevJob &J, int li, int ri) {
 }
 
 // Step B: finish the size logic, initialise the tables, decide on the 8x8-variance probe.
-__device__ void plan_int_b(StageState *s, const DevJob &J, int li, int ri) {
+template <class S>
+__device__ void plan_int_b(S *s, const DevJob &J, int li, int ri) {
     const SvtMeParams &p = J.prm;
     int16_t xc = s->fp_xc, yc = s->fp_yc;
     int16_t sa_w = (int16_t)p.me_sa.sa_min.width, sa_h = (int16_t)p.me_sa.sa_min.height;
@@ -576,7 +596,8 @@ __device__ void plan_int_b(StageState *s, const DevJob &J, int li, int ri) {
 }
 
 // Step C: after the probe — 8x8-variance scaling (:1416-1441) and picture clipping (:1470-1561).
-__device__ void plan_int_c(StageState *s, const DevJob &J) {
+template <class S>
+__device__ void plan_int_c(S *s, const DevJob &J) {
     const SvtMeParams &p = J.prm;
     int16_t sa_w = (int16_t)s->fp_sa_w, sa_h = (int16_t)s->fp_sa_h;
     const int16_t xc = s->fp_xc, yc = s->fp_yc;

@@ -31,10 +31,16 @@
 #ifndef SVTME_HME_ARENA_BYTES
 #define SVTME_HME_ARENA_BYTES (32 * 1024) // HME engine: the tallest pre-HME window (8x400, 20.7 KB) plus its wide twin (7.9 KB)
 #endif
+#ifndef SVTME_INT_SMALL_CTAS_PER_SM
+#define SVTME_INT_SMALL_CTAS_PER_SM 6
+#endif
 #ifndef SVTME_HME_CTAS_PER_SM
 #define SVTME_HME_CTAS_PER_SM 4
 #endif
 #define SVTME_FP_YL (SVTME_THREADS / 64) // row lanes of the full-pel engine
+#ifndef SVTME_FP_DIRECT_MAX
+#define SVTME_FP_DIRECT_MAX 96 // search areas up to this many positions skip the shared-memory staging
+#endif
 
 __device__ __forceinline__ uint32_t vsad4(uint32_t a, uint32_t b, uint32_t acc) {
     uint32_t r;
@@ -740,7 +746,10 @@ __device__ __forceinline__ void fp_butterfly(uint32_t (&v)[G], int b, int &joff3
     v64 = v[0];
 }
 
-template <int G>
+// DIRECT: no staging — `arena` is the GLOBAL address of the tile's top-left reference pixel and `m` the
+// plane stride; each row's words are read with scalar loads (L1-resident for the small windows this
+// mode is used for) and shifted to the thread's byte phase in registers.
+template <int G, bool DIRECT>
 __device__ __noinline__ void fp_tile(const uint8_t *src64, const uint8_t *arena, int copy_bytes, int m, int tw, int th,
                                         bool sub_sad, FpTables *tab) {
     const int tid = threadIdx.x, b = tid & 15, c = (tid >> 4) & 3, yl = tid >> 6;
@@ -768,8 +777,19 @@ __device__ __noinline__ void fp_tile(const uint8_t *src64, const uint8_t *arena,
 #pragma unroll
                 for (int r = 0; r < 8; ++r) {
                     const int R = y + 16 * by + 2 * r + par;
-                    const uint8_t *rp = base + ((size_t)(R * m + 4 * (R >> 4)) << 4);
                     uint32_t w[G + 4];
+                    if (DIRECT) {
+                        const uintptr_t ai = reinterpret_cast<uintptr_t>(arena + (size_t)R * m + 4 * q0 + c);
+                        const uint32_t *al = reinterpret_cast<const uint32_t *>(ai & ~(uintptr_t)3);
+                        const uint32_t sh = (uint32_t)(ai & 3) * 8;
+                        uint32_t t[G + 5];
+#pragma unroll
+                        for (int k = 0; k < G + 4; ++k) t[k] = __ldg(al + k);
+                        t[G + 4] = sh ? __ldg(al + G + 4) : 0u;
+#pragma unroll
+                        for (int k = 0; k < G + 4; ++k) w[k] = __funnelshift_r(t[k], t[k + 1], sh);
+                    } else {
+                    const uint8_t *rp = base + ((size_t)(R * m + 4 * (R >> 4)) << 4);
                     if (G == 2) {
 #pragma unroll
                         for (int k = 0; k < 3; ++k) {
@@ -785,6 +805,7 @@ __device__ __noinline__ void fp_tile(const uint8_t *src64, const uint8_t *arena,
                             if (4 * k + 2 < G + 4) w[4 * k + 2] = v.z;
                             if (4 * k + 3 < G + 4) w[4 * k + 3] = v.w;
                         }
+                    }
                     }
                     const int kb = (r >= 4) ? 2 : 0; // 8x8 row half
 #pragma unroll
@@ -860,6 +881,9 @@ __device__ __noinline__ void fullpel_search(const uint8_t *src64, const uint8_t 
                                int sa_h, bool sub_sad, uint32_t order_base, FpTables *tab, uint8_t *arena) {
     if (sa_w <= 0 || sa_h <= 0) return;
     const int G = sa_w <= 8 ? 2 : (sa_w <= 16 ? 4 : 8);
+    // small areas (the 8x3 .. 16x5 windows of the fast presets): staging four copies of a 71x66 window
+    // for a few dozen positions costs more than the search; read the reference through L1 instead
+    const bool direct = arena == nullptr || sa_w * sa_h <= SVTME_FP_DIRECT_MAX;
     const int last_row = sub_sad ? 62 : 63; // last block row that is read
     for (int ty0 = 0; ty0 < sa_h; ty0 += FP_TH) {
         const int th = min(FP_TH, sa_h - ty0);
@@ -872,16 +896,24 @@ __device__ __noinline__ void fullpel_search(const uint8_t *src64, const uint8_t 
             const int rows = ((th + SVTME_FP_YL - 1) / SVTME_FP_YL) * SVTME_FP_YL + last_row;
             const int copy_chunks = rows * m + 4 * ((rows - 1) >> 4) + 4;
             const int copy_bytes = copy_chunks * 16;
+            const uint8_t *tile0 = ref0 + (size_t)ty0 * ref_stride + tx0;
             __syncthreads();
-            stage_window4(arena, ref0 + (size_t)ty0 * ref_stride + tx0, ref_stride, rows, m, 4, copy_bytes, words);
+            if (!direct) stage_window4(arena, tile0, ref_stride, rows, m, 4, copy_bytes, words);
             for (int i = threadIdx.x; i < SVTME_PU_COUNT; i += SVTME_THREADS) tab->tile_best[i] = ~0u;
             __syncthreads();
-            if (G == 2)
-                fp_tile<2>(src64, arena, copy_bytes, m, tw, th, sub_sad, tab);
+            if (direct) {
+                if (G == 2)
+                    fp_tile<2, true>(src64, tile0, 0, ref_stride, tw, th, sub_sad, tab);
+                else if (G == 4)
+                    fp_tile<4, true>(src64, tile0, 0, ref_stride, tw, th, sub_sad, tab);
+                else
+                    fp_tile<8, true>(src64, tile0, 0, ref_stride, tw, th, sub_sad, tab);
+            } else if (G == 2)
+                fp_tile<2, false>(src64, arena, copy_bytes, m, tw, th, sub_sad, tab);
             else if (G == 4)
-                fp_tile<4>(src64, arena, copy_bytes, m, tw, th, sub_sad, tab);
+                fp_tile<4, false>(src64, arena, copy_bytes, m, tw, th, sub_sad, tab);
             else
-                fp_tile<8>(src64, arena, copy_bytes, m, tw, th, sub_sad, tab);
+                fp_tile<8, false>(src64, arena, copy_bytes, m, tw, th, sub_sad, tab);
             __syncthreads();
             if (threadIdx.x < SVTME_PU_COUNT) {
                 const uint32_t k = tab->tile_best[threadIdx.x];

@@ -22,6 +22,7 @@ struct WideArgs {
 };
 
 size_t svtme_stage_state_bytes() { return sizeof(StageState); }
+int svtme_fp_direct_max() { return SVTME_FP_DIRECT_MAX; }
 
 __device__ __forceinline__ void copy_job_to_smem(DevJob *dst, const DevJob *src) {
     static_assert(sizeof(DevJob) % 4 == 0, "DevJob is copied as 32-bit words");
@@ -167,12 +168,15 @@ __global__ void __launch_bounds__(128) points_kernel(WideArgs a) {
 }
 
 // ---------------------------------------------------------------- integer search (one CTA per b64 x reference)
+// SMALL: every search area of the batch is small enough for the unstaged full-pel path (decided on
+// the host from the parameters; a larger area would still be searched correctly, only slower), so
+// the CTA needs no arena: ~7 KB of shared memory, more CTAs per SM.
+template <bool SMALL>
 struct IntSmem {
-    StageState st; // private scratch copy: only the fields integer_search_b64 reads are filled in
-    HPlan plan;
+    IntState st;
     DevJob job;
     __align__(16) uint8_t src64[64 * 64];
-    __align__(16) uint8_t arena[SVTME_ARENA_BYTES];
+    __align__(16) uint8_t arena[SMALL ? 16 : SVTME_ARENA_BYTES];
 };
 
 #define T0(stmt)                        \
@@ -183,9 +187,11 @@ struct IntSmem {
 
 // slots [slot0, slot0 + n_slots) of the 2x4 (list, ref_idx) grid; slot 0 = (list 0, ref 0) runs in a
 // launch of its own because the other references' search areas may depend on its result (:1345-1350)
-__global__ void __launch_bounds__(SVTME_THREADS, SVTME_CTAS_PER_SM) int_kernel(WideArgs a, int slot0, int n_slots) {
+template <bool SMALL>
+__global__ void __launch_bounds__(SVTME_THREADS, SMALL ? SVTME_INT_SMALL_CTAS_PER_SM : SVTME_CTAS_PER_SM)
+    int_kernel(WideArgs a, int slot0, int n_slots) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
-    IntSmem *sm = reinterpret_cast<IntSmem *>(smem_raw);
+    IntSmem<SMALL> *sm = reinterpret_cast<IntSmem<SMALL> *>(smem_raw);
     const int gid = blockIdx.x / n_slots, slot = slot0 + blockIdx.x % n_slots, tid = threadIdx.x;
     const int li = slot / NR, ri = slot % NR;
     const DevJob &Jg = a.jobs[gid / a.b64_per_job];
@@ -193,7 +199,7 @@ __global__ void __launch_bounds__(SVTME_THREADS, SVTME_CTAS_PER_SM) int_kernel(W
     StageState *g = &a.st[gid];
     if (!g->sr[li][ri].do_ref) return; // pruned reference: its tables keep the zero fill (:1287-1290)
     copy_job_to_smem(&sm->job, &Jg);
-    StageState *s = &sm->st;
+    IntState *s = &sm->st;
     if (tid == 0) {
         s->org_x = g->org_x; s->org_y = g->org_y;
         s->b64_w = g->b64_w; s->b64_h = g->b64_h;
@@ -204,6 +210,11 @@ __global__ void __launch_bounds__(SVTME_THREADS, SVTME_CTAS_PER_SM) int_kernel(W
         s->best_sad[0][0][0] = g->best_sad[0][0][0];
     }
     const int org_x = g->org_x, org_y = g->org_y;
+    // svt_initialize_buffer_32bits(p_sb_best_sad, 21, 1, MAX_SAD_VALUE) :1368
+    if (tid < SVTME_PU_COUNT) {
+        s->tab.key[tid] = (unsigned long long)SVTME_MAX_SAD_VALUE << 32;
+        s->tab.mv[tid] = 0;
+    }
     __syncthreads();
     const DevJob &J = sm->job;
     const SvtMeParams &p = J.prm;
@@ -215,32 +226,40 @@ __global__ void __launch_bounds__(SVTME_THREADS, SVTME_CTAS_PER_SM) int_kernel(W
                 *reinterpret_cast<const uint4 *>(f.at(org_x + c4 * 16, org_y + r));
         }
     }
-    T0(plan_int_a(s, J, li, ri));
+    // The three scalar steps run back to back on thread 0 whenever no search separates them
+    // (no check_00_center, no 8x8-variance probe): one serial section instead of three.
+    T0(plan_int_a(s, J, li, ri); s->fp_phase = 0;
+       if (!s->n_jobs) {
+           plan_int_b(s, J, li, ri);
+           s->fp_phase = 1;
+           if (!s->fp_probe) {
+               plan_int_c(s, J);
+               s->fp_phase = 2;
+           }
+       });
     unsigned long long work = 0;
     const bool sub_sad = p.me_search_method == 0;
-    if (s->n_jobs) {
-        const HBlk blk_zz = make_hblk(sm->src64, 128, s->b64_w, s->b64_h >> 1, 2);
-        hme_search_multi(blk_zz, s->jobs, s->n_jobs, &sm->plan, sm->arena);
-        work += (unsigned long long)s->n_jobs * blk_zz.bw * blk_zz.nrows;
-    }
-    T0(plan_int_b(s, J, li, ri));
-    // svt_initialize_buffer_32bits(p_sb_best_sad, 21, 1, MAX_SAD_VALUE) :1368
-    if (tid < SVTME_PU_COUNT) {
-        s->tab.key[tid] = (unsigned long long)SVTME_MAX_SAD_VALUE << 32;
-        s->tab.mv[tid] = 0;
-    }
-    __syncthreads();
     const DevPlane &pl = J.ref[li][ri].lvl[0];
-    if (s->fp_probe) {
+    if (s->fp_phase == 0) { // check_00_center: two single-position SADs
+        const HBlk blk_zz = make_hblk(sm->src64, 128, s->b64_w, s->b64_h >> 1, 2);
+        hme_points(blk_zz, s->jobs, s->n_jobs);
+        work += (unsigned long long)s->n_jobs * blk_zz.bw * blk_zz.nrows;
+        T0(plan_int_b(s, J, li, ri); s->fp_phase = 1;
+           if (!s->fp_probe) {
+               plan_int_c(s, J);
+               s->fp_phase = 2;
+           });
+    }
+    if (s->fp_phase == 1) {
         const int xc = s->fp_xc, yc = s->fp_yc;
         fullpel_probe(sm->src64, pl.at(org_x + xc, org_y + yc), pl.stride, xc, yc, sub_sad, 1, &s->tab);
         work += 64ull * (sub_sad ? 32 : 64);
+        T0(plan_int_c(s, J));
     }
-    T0(plan_int_c(s, J));
     {
         const int ox = s->fp_ox, oy = s->fp_oy;
         fullpel_search(sm->src64, pl.at(org_x + ox, org_y + oy), pl.stride, ox, oy, s->fp_sa_w, s->fp_sa_h, sub_sad, 2,
-                       &s->tab, sm->arena);
+                       &s->tab, SMALL ? nullptr : sm->arena);
         work += (unsigned long long)s->fp_sa_w * s->fp_sa_h * 64ull * (sub_sad ? 32 : 64);
     }
     if (tid < SVTME_PU_COUNT) {
@@ -300,11 +319,12 @@ __global__ void __launch_bounds__(128) finish_kernel(WideArgs a) {
 // ---------------------------------------------------------------- host: the launch sequence
 // Launch slots (one event after each; names in SVTME_PHASE_NAMES of svtme_common.cuh).
 void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, void *d_states, cudaStream_t st,
-                           cudaEvent_t *ev) {
+                           cudaEvent_t *ev, bool small_areas) {
     static bool configured = false;
     if (!configured) {
         cudaFuncSetAttribute(engine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EngSmem));
-        cudaFuncSetAttribute(int_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IntSmem));
+        cudaFuncSetAttribute(int_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IntSmem<false>));
+        cudaFuncSetAttribute(int_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IntSmem<true>));
         cudaFuncSetAttribute(finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FinSmem));
         configured = true;
     }
@@ -341,8 +361,13 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, vo
     engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 3);
     scalar_kernel<S_L2><<<sg, 128, 0, st>>>(a);
     mark(); // 5: HME level 2 + search centre + HME pruning
-    int_kernel<<<N, SVTME_THREADS, sizeof(IntSmem), st>>>(a, 0, 1);
-    int_kernel<<<N * (NL * NR - 1), SVTME_THREADS, sizeof(IntSmem), st>>>(a, 1, NL * NR - 1);
+    if (small_areas) {
+        int_kernel<true><<<N, SVTME_THREADS, sizeof(IntSmem<true>), st>>>(a, 0, 1);
+        int_kernel<true><<<N * (NL * NR - 1), SVTME_THREADS, sizeof(IntSmem<true>), st>>>(a, 1, NL * NR - 1);
+    } else {
+        int_kernel<false><<<N, SVTME_THREADS, sizeof(IntSmem<false>), st>>>(a, 0, 1);
+        int_kernel<false><<<N * (NL * NR - 1), SVTME_THREADS, sizeof(IntSmem<false>), st>>>(a, 1, NL * NR - 1);
+    }
     mark(); // 6: integer search
     finish_kernel<<<N, 128, sizeof(FinSmem), st>>>(a);
     mark(); // 7: candidates + statistics

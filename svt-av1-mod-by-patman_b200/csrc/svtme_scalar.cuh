@@ -214,9 +214,9 @@ __device__ bool prehme_early_exit(StageState *s, const SvtMeParams &p, int li, i
 }
 
 // prehme_b64 (:1791-1866) for one list: decide per (ref, region) and emit jobs (prehme_core :1641)
-__device__ void plan_prehme(StageState *s, const DevJob &J, int li) {
+__device__ void plan_prehme(StageState *s, const DevJob &J, int li, bool append = false) {
     const SvtMeParams &p = J.prm;
-    s->n_jobs = 0;
+    if (!append) s->n_jobs = 0;
     if (!(p.temporal_layer_index > 0 || li == 0)) return;
     for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
         const uint32_t factor = scaled_dist(ref_dist(p, li, ri));

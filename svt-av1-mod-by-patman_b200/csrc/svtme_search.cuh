@@ -32,7 +32,7 @@
 #define SVTME_HME_ARENA_BYTES (32 * 1024) // HME engine: the tallest pre-HME window (8x400, 20.7 KB) plus its wide twin (7.9 KB)
 #endif
 #ifndef SVTME_INT_SMALL_CTAS_PER_SM
-#define SVTME_INT_SMALL_CTAS_PER_SM 6
+#define SVTME_INT_SMALL_CTAS_PER_SM 8
 #endif
 #ifndef SVTME_HME_CTAS_PER_SM
 #define SVTME_HME_CTAS_PER_SM 4

@@ -64,11 +64,16 @@ __global__ void __launch_bounds__(128) scalar_kernel(WideArgs a) {
     } else if (STEP == S_ZZ) {
         if (zz) post_zz(s, p);
         s->n_jobs = 0;
-        if (p.prehme_enable) plan_prehme(s, J, 0);
+        if (p.prehme_enable) {
+            plan_prehme(s, J, 0);
+            // list 1 depends on list 0 only through prehme_l1_early_exit (:1763-1788): otherwise both
+            // lists are one round
+            if (p.num_of_list_to_search > 1 && !p.prehme_l1_early_exit) plan_prehme(s, J, 1, true);
+        }
     } else if (STEP == S_PREHME1) {
         if (p.prehme_enable) post_prehme_jobs(s, p);
         s->n_jobs = 0;
-        if (p.prehme_enable && p.num_of_list_to_search > 1) plan_prehme(s, J, 1);
+        if (p.prehme_enable && p.num_of_list_to_search > 1 && p.prehme_l1_early_exit) plan_prehme(s, J, 1);
     } else if (STEP == S_PREHME2) {
         if (p.prehme_enable) {
             post_prehme_jobs(s, p);

@@ -430,9 +430,16 @@ extern "C" int svtme_launch_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint3
             h->states_bytes = need;
         }
     }
-    bool small_areas = true;
-    for (uint32_t i = 0; i < n; ++i) small_areas = small_areas && areas_are_small(jobs[i].params);
-    svtme_launch_me_stage(h->d_jobs, (int)n, (int)h->n_b64, h->d_states, h->stream, h->ph_ev, small_areas);
+    SvtmeStageFlags flags = {};
+    flags.small_areas = true;
+    for (uint32_t i = 0; i < n; ++i) {
+        const SvtmeStageFlags f = svtme_stage_flags(jobs[i].params);
+        flags.small_areas = flags.small_areas && areas_are_small(jobs[i].params);
+        flags.zz |= f.zz; flags.prehme |= f.prehme; flags.prehme_l1_round |= f.prehme_l1_round;
+        flags.hme_l0 |= f.hme_l0; flags.hme_l0_round_b |= f.hme_l0_round_b;
+        flags.hme_l1 |= f.hme_l1; flags.hme_l2 |= f.hme_l2;
+    }
+    svtme_launch_me_stage(h->d_jobs, (int)n, (int)h->n_b64, h->d_states, h->stream, h->ph_ev, flags);
     CU(cudaGetLastError());
     CU(cudaEventRecord(h->ev1, h->stream));
     return SVTME_OK;

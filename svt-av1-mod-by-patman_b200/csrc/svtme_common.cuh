@@ -78,9 +78,14 @@ void svtme_launch_build_batch(const SvtmePutItem *d_items, int n, const DevPyram
                               cudaStream_t st);
 // stage kernel (svtme_stage.cu)
 // d_states: n_jobs * b64_per_job * svtme_stage_state_bytes() bytes of scratch; ev: SVTME_PHASES events or null
-// small_areas: every full-pel search area of the batch is at most svtme_fp_direct_max() positions
+// What the pictures of a batch need, so that launches no picture uses are skipped.
+struct SvtmeStageFlags {
+    bool small_areas;     // every full-pel search area is at most svtme_fp_direct_max() positions
+    bool zz, prehme, prehme_l1_round, hme_l0, hme_l0_round_b, hme_l1, hme_l2;
+};
+SvtmeStageFlags svtme_stage_flags(const SvtMeParams &p);
 void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, void *d_states, cudaStream_t st,
-                           cudaEvent_t *ev, bool small_areas);
+                           cudaEvent_t *ev, const SvtmeStageFlags &f);
 int svtme_fp_direct_max();
 size_t svtme_stage_state_bytes();
 // kernel-test entry points (svtme_stage.cu)

@@ -194,35 +194,60 @@ __global__ void __launch_bounds__(256) downsample_batch_kernel(const SvtmePutIte
         *reinterpret_cast<uint16_t *>(srow) = (uint16_t)s4;
 }
 
+// Padding of all three levels of n pictures in one launch: one thread per aligned 4-byte word that
+// holds at least one pad byte (words are counted from the left edge of the padded row; a word that
+// straddles the right picture edge rewrites its interior bytes with their own values). Every byte is
+// the clamped interior pixel, read from interior bytes only, so there is no ordering between threads.
+__device__ __forceinline__ int pad_words_per_level(int W, int H, int pl, int pr, int pt, int pb, int &fw4, int &wi0) {
+    fw4 = (pl + W + pr + 3) >> 2;
+    wi0 = (pl + W) >> 2;
+    return fw4 * (pt + pb) + ((pl >> 2) + (fw4 - wi0)) * H;
+}
+
 __global__ void __launch_bounds__(256) pad_batch_kernel(const SvtmePutItem *__restrict__ items, SvtmePadSpec ps) {
     const SvtmePutItem &it = items[blockIdx.z];
-    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    int i = (int)(blockIdx.x * blockDim.x + threadIdx.x);
 #pragma unroll 1
     for (int lvl = 0; lvl < 3; ++lvl) {
         const DevPlane &p = it.pyr.lvl[lvl];
         const int W = p.width, H = p.height, pl = ps.l[lvl], pr = ps.r[lvl], pt = ps.t[lvl], pb = ps.b[lvl];
-        const long long full_w = (long long)pl + W + pr;
-        const long long n_top = full_w * pt, n_bot = full_w * pb, n_side = (long long)(pl + pr) * H;
-        int x, y;
-        if (i < n_top) {
-            y = -pt + (int)(i / full_w);
-            x = -pl + (int)(i % full_w);
-        } else if (i - n_top < n_bot) {
-            const long long k = i - n_top;
-            y = H + (int)(k / full_w);
-            x = -pl + (int)(k % full_w);
-        } else if (i - n_top - n_bot < n_side) {
-            const long long k = i - n_top - n_bot;
-            y = (int)(k / (pl + pr));
-            const int c = (int)(k % (pl + pr));
-            x = c < pl ? -pl + c : W + (c - pl);
-        } else {
-            i -= n_top + n_bot + n_side;
+        int fw4, wi0;
+        const int n_lvl = pad_words_per_level(W, H, pl, pr, pt, pb, fw4, wi0);
+        if (i >= n_lvl) {
+            i -= n_lvl;
             continue;
         }
-        const int sx = min(max(x, 0), W - 1), sy = min(max(y, 0), H - 1);
+        const int n_top = fw4 * pt, n_bot = fw4 * pb, side4 = (pl >> 2) + (fw4 - wi0);
+        int wi, y;
+        if (i < n_top) {
+            const int r = i / fw4;
+            y = -pt + r;
+            wi = i - r * fw4;
+        } else if (i - n_top < n_bot) {
+            const int k = i - n_top, r = k / fw4;
+            y = H + r;
+            wi = k - r * fw4;
+        } else {
+            const int k = i - n_top - n_bot, r = k / side4, c = k - r * side4;
+            y = r;
+            wi = c < (pl >> 2) ? c : wi0 + (c - (pl >> 2));
+        }
+        const int x = -pl + 4 * wi;
         uint8_t *org = const_cast<uint8_t *>(p.at(0, 0));
-        org[(long long)y * p.stride + x] = org[(long long)sy * p.stride + sx];
+        const uint8_t *srow = org + (long long)min(max(y, 0), H - 1) * p.stride;
+        uint32_t v;
+        if (x + 3 < 0)
+            v = srow[0] * 0x01010101u;
+        else if (x >= W)
+            v = srow[W - 1] * 0x01010101u;
+        else if (x >= 0 && x + 3 < W)
+            v = *reinterpret_cast<const uint32_t *>(srow + x);
+        else {
+            v = 0;
+#pragma unroll
+            for (int b = 0; b < 4; ++b) v |= (uint32_t)srow[min(max(x + b, 0), W - 1)] << (8 * b);
+        }
+        *reinterpret_cast<uint32_t *>(org + (long long)y * p.stride + x) = v;
         return;
     }
 }
@@ -237,7 +262,8 @@ void svtme_launch_build_batch(const SvtmePutItem *d_items, int n, const DevPyram
     long long total = 0;
     for (int l = 0; l < 3; ++l) {
         const DevPlane &p = geom.lvl[l];
-        total += ((long long)ps.l[l] + p.width + ps.r[l]) * (ps.t[l] + ps.b[l]) + (long long)(ps.l[l] + ps.r[l]) * p.height;
+        const int fw4 = (ps.l[l] + p.width + ps.r[l] + 3) >> 2, wi0 = (ps.l[l] + p.width) >> 2;
+        total += (long long)fw4 * (ps.t[l] + ps.b[l]) + (long long)((ps.l[l] >> 2) + (fw4 - wi0)) * p.height;
     }
     pad_batch_kernel<<<dim3((unsigned)((total + 255) / 256), 1, n), 256, 0, st>>>(d_items, ps);
     g_svtme_launches += 2;

@@ -413,6 +413,23 @@ __device__ __noinline__ void hme_points(const HBlk &blk, HJob *jobs, int n) {
     for (int j = warp; j < n; j += SVTME_THREADS / 32) {
         const HJob &job = jobs[j];
         uint32_t acc = 0;
+        const size_t rstep = (size_t)blk.row_step * job.stride;
+        if (blk.bw == 64 && blk.nrows <= 32 &&
+            ((reinterpret_cast<uintptr_t>(blk.src) | reinterpret_cast<uintptr_t>(job.ref) | (uintptr_t)blk.src_pitch | rstep) & 15) == 0) {
+            // aligned 64-wide block (zz-SAD): one lane per row, four 16-byte loads from each side
+            if (lane < blk.nrows) {
+                const uint4 *sp = reinterpret_cast<const uint4 *>(blk.src + (size_t)lane * blk.src_pitch);
+                const uint4 *rp = reinterpret_cast<const uint4 *>(job.ref + (size_t)lane * rstep);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const uint4 a = sp[k], b = __ldg(rp + k);
+                    acc = vsad4(a.x, b.x, acc);
+                    acc = vsad4(a.y, b.y, acc);
+                    acc = vsad4(a.z, b.z, acc);
+                    acc = vsad4(a.w, b.w, acc);
+                }
+            }
+        } else
         for (int i = lane; i < items; i += 32) {
             const int r = (int)__umulhi((uint32_t)i, mg_wc), cw = i - r * wcols;
             const int nbytes = min(4, blk.bw - 4 * cw);

@@ -31,7 +31,7 @@ __device__ __forceinline__ void copy_job_to_smem(DevJob *dst, const DevJob *src)
     for (int i = threadIdx.x; i < (int)(sizeof(DevJob) / 4); i += blockDim.x) d[i] = __ldg(g + i);
 }
 
-__device__ __forceinline__ bool l0_dependent(const SvtMeParams &p) { // :1882-1895
+__host__ __device__ __forceinline__ bool l0_dependent(const SvtMeParams &p) { // :1882-1895
     return p.enable_me_sr_adjustment && p.distance_based_hme_resizing && p.reduce_hme_l0_sr_th_min &&
         p.reduce_hme_l0_sr_th_max;
 }
@@ -323,8 +323,21 @@ __global__ void __launch_bounds__(128) finish_kernel(WideArgs a) {
 
 // ---------------------------------------------------------------- host: the launch sequence
 // Launch slots (one event after each; names in SVTME_PHASE_NAMES of svtme_common.cuh).
+SvtmeStageFlags svtme_stage_flags(const SvtMeParams &p) {
+    SvtmeStageFlags f;
+    f.small_areas = false; // filled in by the caller (svtme_api.cu)
+    f.zz = p.me_early_exit_th || p.me_safe_limit_zz_th;
+    f.prehme = p.prehme_enable != 0;
+    f.prehme_l1_round = f.prehme && p.num_of_list_to_search > 1 && p.prehme_l1_early_exit;
+    f.hme_l0 = p.enable_hme_flag && p.enable_hme_level0_flag;
+    f.hme_l0_round_b = f.hme_l0 && l0_dependent(p);
+    f.hme_l1 = p.enable_hme_flag && p.enable_hme_level1_flag;
+    f.hme_l2 = p.enable_hme_flag && p.enable_hme_level2_flag;
+    return f;
+}
+
 void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, void *d_states, cudaStream_t st,
-                           cudaEvent_t *ev, bool small_areas) {
+                           cudaEvent_t *ev, const SvtmeStageFlags &f) {
     static bool configured = false;
     if (!configured) {
         cudaFuncSetAttribute(engine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EngSmem));
@@ -346,27 +359,30 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, vo
     };
     cudaMemsetAsync(d_states, 0, (size_t)N * sizeof(StageState), st);
     mark(); // 0: state clear
+    int launches = 0;
+    // scalar steps always run (they also carry the bookkeeping of disabled phases); engine launches
+    // that no picture of the batch needs are skipped
     scalar_kernel<S_INIT><<<sg, 128, 0, st>>>(a);
-    points_kernel<<<N, 128, 0, st>>>(a);
+    if (f.zz) points_kernel<<<N, 128, 0, st>>>(a), ++launches;
     scalar_kernel<S_ZZ><<<sg, 128, 0, st>>>(a);
     mark(); // 1: zz-SAD
-    engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1);
+    if (f.prehme) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1), ++launches;
     scalar_kernel<S_PREHME1><<<sg, 128, 0, st>>>(a);
-    engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1);
+    if (f.prehme_l1_round) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1), ++launches;
     scalar_kernel<S_PREHME2><<<sg, 128, 0, st>>>(a);
     mark(); // 2: pre-HME
-    engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1);
+    if (f.hme_l0) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1), ++launches;
     scalar_kernel<S_L0A><<<sg, 128, 0, st>>>(a);
-    engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1);
+    if (f.hme_l0_round_b) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1), ++launches;
     scalar_kernel<S_L0B><<<sg, 128, 0, st>>>(a);
     mark(); // 3: HME level 0
-    engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 2);
+    if (f.hme_l1) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 2), ++launches;
     scalar_kernel<S_L1><<<sg, 128, 0, st>>>(a);
     mark(); // 4: HME level 1
-    engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 3);
+    if (f.hme_l2) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 3), ++launches;
     scalar_kernel<S_L2><<<sg, 128, 0, st>>>(a);
     mark(); // 5: HME level 2 + search centre + HME pruning
-    if (small_areas) {
+    if (f.small_areas) {
         int_kernel<true><<<N, SVTME_THREADS, sizeof(IntSmem<true>), st>>>(a, 0, 1);
         int_kernel<true><<<N * (NL * NR - 1), SVTME_THREADS, sizeof(IntSmem<true>), st>>>(a, 1, NL * NR - 1);
     } else {
@@ -376,7 +392,7 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, vo
     mark(); // 6: integer search
     finish_kernel<<<N, 128, sizeof(FinSmem), st>>>(a);
     mark(); // 7: candidates + statistics
-    g_svtme_launches += 19;
+    g_svtme_launches += 8 + 2 + 1 + launches;
 }
 
 // ---------------------------------------------------------------- kernel-test entry points

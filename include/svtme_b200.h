@@ -235,6 +235,8 @@ int svtme_last_work_ops(SvtMeHandle *h, uint64_t *ops);
  * 7 ME pruning + candidates + statistics. */
 #define SVTME_PHASES 8
 int svtme_last_phase_ms(SvtMeHandle *h, float *ms, uint32_t n);
+/* Algorithmic SAD byte-ops (positions x block pixels compared) per launch slot, same slots. */
+int svtme_last_phase_work(SvtMeHandle *h, uint64_t *ops, uint32_t n);
 /* Measured issue rate (Ginst/s, whole GPU) of VABSDIFF4.U8.ACC, 4 byte-SADs per instruction: the
  * integer-SAD roofline denominator (not part of MEASURED_PEAKS.json). */
 double svtme_measure_vabsdiff4_ginst_per_s(void);

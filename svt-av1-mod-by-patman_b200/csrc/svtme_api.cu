@@ -330,7 +330,7 @@ static OutLayout out_layout(uint32_t n_b64, uint32_t n_pu, const SvtMeParams &p,
     L.d64 = take((size_t)n_b64 * 4); L.d32 = take((size_t)n_b64 * 4); L.d16 = take((size_t)n_b64 * 4);
     L.d8 = take((size_t)n_b64 * 4); L.var8 = take((size_t)n_b64 * 4); L.rc = take((size_t)n_b64 * 4);
     L.stat = take(n_b64); L.gm = take(n_b64);
-    L.work = take(8);
+    L.work = take(8 * SVTME_PHASES); // per launch slot
     if (deep) {
         L.bsad = take((size_t)n_b64 * 2 * 4 * 85 * 4); L.bmv = take((size_t)n_b64 * 2 * 4 * 85 * 4);
         L.sc = take((size_t)n_b64 * 2 * 4 * 2 * 2); L.hsad = take((size_t)n_b64 * 2 * 4 * 8); L.doref = take((size_t)n_b64 * 2 * 4);
@@ -528,12 +528,28 @@ extern "C" int svtme_last_work_ops(SvtMeHandle *h, uint64_t *ops) {
     CU(cudaStreamSynchronize(h->stream));
     uint64_t sum = 0;
     for (size_t o : h->work_off) {
-        unsigned long long v = 0;
-        CU(cudaMemcpy(&v, h->ob.dev + o, 8, cudaMemcpyDeviceToHost));
-        sum += v;
+        unsigned long long v[SVTME_PHASES];
+        CU(cudaMemcpy(v, h->ob.dev + o, sizeof(v), cudaMemcpyDeviceToHost));
+        for (int k = 0; k < SVTME_PHASES; ++k) sum += v[k];
     }
     *ops = sum;
     cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+    return SVTME_OK;
+}
+
+// Algorithmic SAD byte-ops per launch slot (same slots as svtme_last_phase_ms) of the last launch.
+extern "C" int svtme_last_phase_work(SvtMeHandle *h, uint64_t *ops, uint32_t n) {
+    if (!h || !ops) return fail(SVTME_ERR_INVALID, "svtme_last_phase_work: bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    if (n > SVTME_PHASES) n = SVTME_PHASES;
+    for (uint32_t k = 0; k < n; ++k) ops[k] = 0;
+    for (size_t o : h->work_off) {
+        unsigned long long v[SVTME_PHASES];
+        CU(cudaMemcpy(v, h->ob.dev + o, sizeof(v), cudaMemcpyDeviceToHost));
+        for (uint32_t k = 0; k < n; ++k) ops[k] += v[k];
+    }
     return SVTME_OK;
 }
 

@@ -50,7 +50,7 @@ struct DevJob {
     int16_t *hme_sc;
     unsigned long long *hme_sad;
     uint8_t *do_ref;
-    unsigned long long *work_ops; // [0] algorithmic SAD byte-ops executed for this picture (roofline numerator)
+    unsigned long long *work_ops; // [SVTME_PHASES], per launch slot: algorithmic SAD byte-ops executed for this picture (roofline numerator)
 };
 
 // launch slots of the stage pipeline (svtme_stage.cu), timed with one CUDA event after each

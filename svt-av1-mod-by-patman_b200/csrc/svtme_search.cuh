@@ -165,20 +165,6 @@ struct HPlan {           // shared-memory scratch of one round
     int n_groups;
 };
 
-struct SrcRegs {         // one full 16x8 source sub-block in registers (fast path only)
-    uint32_t s[8][4];
-    int cached_b;
-};
-
-__device__ __forceinline__ void load_src_regs(const HBlk &blk, int b, int bxi, int byi, SrcRegs &sr) {
-    sr.cached_b = b;
-#pragma unroll
-    for (int r = 0; r < 8; ++r) {
-        const uint4 v = *reinterpret_cast<const uint4 *>(blk.src + (size_t)(8 * byi + r) * blk.src_pitch + 16 * bxi);
-        sr.s[r][0] = v.x; sr.s[r][1] = v.y; sr.s[r][2] = v.z; sr.s[r][3] = v.w;
-    }
-}
-
 // The fields of HGeo a work item needs, held in registers while a thread stays inside one job.
 struct ItemGeo {
     uint32_t arena_off, sad_off;
@@ -210,7 +196,7 @@ __device__ __forceinline__ void hme_emit(bool single, uint32_t sad, int y, int x
 // the row loop: staging pads the window to whole y-tiles (clamped rows).
 template <int G, int TY>
 __device__ __forceinline__ void hme_item_fast(const HBlk &blk, const ItemGeo &ig, uint8_t *arena, int c, int xt, int yb,
-                                              int bxi, int byi, const SrcRegs &sr, uint32_t &best32) {
+                                              int bxi, int byi, uint32_t &best32) {
     const int rs = blk.row_step;
     uint32_t acc[TY][G];
 #pragma unroll
@@ -218,10 +204,19 @@ __device__ __forceinline__ void hme_item_fast(const HBlk &blk, const ItemGeo &ig
 #pragma unroll
         for (int j = 0; j < G; ++j) acc[ty][j] = 0;
     const uint8_t *base = arena + ig.arena_off + 4 * (xt * G + 4 * bxi);
+    const uint8_t *sp = blk.src + (size_t)(8 * byi) * blk.src_pitch + 16 * bxi;
     const uint32_t sh = 8 * c;
     const int row0 = yb + 8 * byi * rs;
+    // sliding window of the TY source rows in use: reference row rho meets source row rho - ty at
+    // y-position ty. Source rows come from shared memory as warp-wide broadcasts (every lane of an
+    // item group reads the same address), which keeps the register budget at TY*4 instead of 32.
+    uint32_t sw[TY][4];
 #pragma unroll
     for (int rho = 0; rho < TY + 7; ++rho) {
+        if (rho < 8) {
+            const uint4 v = *reinterpret_cast<const uint4 *>(sp + rho * blk.src_pitch);
+            sw[rho % TY][0] = v.x; sw[rho % TY][1] = v.y; sw[rho % TY][2] = v.z; sw[rho % TY][3] = v.w;
+        }
         const int row = row0 + rho * rs;
         const uint8_t *rp = base + row * ig.pitch + ((row >> 3) << 4);
         uint32_t w[G + 5];
@@ -248,7 +243,7 @@ __device__ __forceinline__ void hme_item_fast(const HBlk &blk, const ItemGeo &ig
 #pragma unroll
                 for (int j = 0; j < G; ++j)
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) acc[ty][j] = vsad4(sr.s[r][i], w[j + i], acc[ty][j]);
+                    for (int i = 0; i < 4; ++i) acc[ty][j] = vsad4(sw[r % TY][i], w[j + i], acc[ty][j]);
             }
         }
     }
@@ -305,8 +300,7 @@ __device__ __noinline__ uint32_t hme_item_slow(const HBlk blk, const ItemGeo ig,
     return best32;
 }
 
-__device__ __forceinline__ void hme_item_any(const HBlk &blk, const ItemGeo &ig, uint8_t *arena, int it, SrcRegs &sr,
-                                             uint32_t &best32) {
+__device__ __forceinline__ void hme_item_any(const HBlk &blk, const ItemGeo &ig, uint8_t *arena, int it, uint32_t &best32) {
     const int nb = blk.nb, nbx = blk.nbx, rs = blk.row_step;
     int t = nb == 1 ? it : (int)__umulhi((uint32_t)it, blk.mg_nb);
     const int b = it - t * nb;
@@ -323,14 +317,13 @@ __device__ __forceinline__ void hme_item_any(const HBlk &blk, const ItemGeo &ig,
         best32 = hme_item_slow(blk, ig, arena, G, TY, c, xt, yb, bxi, byi, best32);
         return;
     }
-    if (b != sr.cached_b) load_src_regs(blk, b, bxi, byi, sr);
     // few variants on purpose: the unrolled bodies are large and the kernel must stay I-cache friendly
     if (ig.variant == 0)
-        hme_item_fast<2, 4>(blk, ig, arena, c, xt, yb, bxi, byi, sr, best32);
+        hme_item_fast<2, 4>(blk, ig, arena, c, xt, yb, bxi, byi, best32);
     else if (ig.variant == 1)
-        hme_item_fast<4, 4>(blk, ig, arena, c, xt, yb, bxi, byi, sr, best32);
+        hme_item_fast<4, 4>(blk, ig, arena, c, xt, yb, bxi, byi, best32);
     else
-        hme_item_fast<8, 2>(blk, ig, arena, c, xt, yb, bxi, byi, sr, best32);
+        hme_item_fast<8, 2>(blk, ig, arena, c, xt, yb, bxi, byi, best32);
 }
 
 // Tile geometry for a (sub)area of wb x hb positions; g.need = the arena bytes it takes.
@@ -498,8 +491,6 @@ __device__ __noinline__ void hme_group_items(const HBlk &blk_ref, HJob *jobs, co
     const HBlk blk = blk_ref; // registers: the reference points into the caller's local memory
     const HGroup G = G_ref;
     const int nb = blk.nb;
-    SrcRegs sr;
-    sr.cached_b = -1;
     ItemGeo ig;
     uint32_t best32 = ~0u;
     int cj = G.j0, bj = -1, base = 0, end = 0;
@@ -513,7 +504,7 @@ __device__ __noinline__ void hme_group_items(const HBlk &blk_ref, HJob *jobs, co
             base = geo[cj].item_base;
             end = base + geo[cj].n_items;
         }
-        hme_item_any(blk, ig, arena, it - base, sr, best32);
+        hme_item_any(blk, ig, arena, it - base, best32);
     }
     if (nb == 1 && bj >= 0) flush_key32(jobs, geo, bj, best32);
 }

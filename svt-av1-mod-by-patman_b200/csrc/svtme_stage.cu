@@ -117,7 +117,7 @@ struct EngSmem {
 };
 
 // level: 0 = 64x64 block, every other row (zz-SAD); 1/2/3 = HME level 0/1/2 block
-__global__ void __launch_bounds__(SVTME_THREADS, SVTME_HME_CTAS_PER_SM) engine_kernel(WideArgs a, int level) {
+__global__ void __launch_bounds__(SVTME_THREADS, SVTME_HME_CTAS_PER_SM) engine_kernel(WideArgs a, int level, int wslot) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     EngSmem *sm = reinterpret_cast<EngSmem *>(smem_raw);
     const int gid = blockIdx.x, tid = threadIdx.x;
@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(SVTME_THREADS, SVTME_HME_CTAS_PER_SM) engine_k
     if (tid < 32 && J.work_ops) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) w += __shfl_xor_sync(0xffffffffu, w, o);
-        if (tid == 0 && w) atomicAdd(J.work_ops, w);
+        if (tid == 0 && w) atomicAdd(J.work_ops + wslot, w);
     }
 }
 
@@ -169,7 +169,7 @@ __global__ void __launch_bounds__(128) points_kernel(WideArgs a) {
     const DevPlane &pl = J.cur.lvl[0];
     const HBlk blk = make_hblk(pl.at(s->org_x, s->org_y), 2 * pl.stride, s->b64_w, s->b64_h >> 1, 2);
     hme_points(blk, s->jobs, n);
-    if (threadIdx.x == 0 && J.work_ops) atomicAdd(J.work_ops, (unsigned long long)n * blk.bw * blk.nrows);
+    if (threadIdx.x == 0 && J.work_ops) atomicAdd(J.work_ops + 1, (unsigned long long)n * blk.bw * blk.nrows);
 }
 
 // ---------------------------------------------------------------- integer search (one CTA per b64 x reference)
@@ -271,7 +271,7 @@ __global__ void __launch_bounds__(SVTME_THREADS, SMALL ? SVTME_INT_SMALL_CTAS_PE
         g->best_sad[li][ri][tid] = (uint32_t)(s->tab.key[tid] >> 32);
         g->best_mv[li][ri][tid] = s->tab.mv[tid];
     }
-    if (tid == 0 && J.work_ops) atomicAdd(J.work_ops, work);
+    if (tid == 0 && J.work_ops) atomicAdd(J.work_ops + 6, work);
 }
 
 // ---------------------------------------------------------------- pruning, candidates, statistics (one CTA per b64)
@@ -366,20 +366,20 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, vo
     if (f.zz) points_kernel<<<N, 128, 0, st>>>(a), ++launches;
     scalar_kernel<S_ZZ><<<sg, 128, 0, st>>>(a);
     mark(); // 1: zz-SAD
-    if (f.prehme) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1), ++launches;
+    if (f.prehme) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1, 2), ++launches;
     scalar_kernel<S_PREHME1><<<sg, 128, 0, st>>>(a);
-    if (f.prehme_l1_round) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1), ++launches;
+    if (f.prehme_l1_round) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1, 2), ++launches;
     scalar_kernel<S_PREHME2><<<sg, 128, 0, st>>>(a);
     mark(); // 2: pre-HME
-    if (f.hme_l0) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1), ++launches;
+    if (f.hme_l0) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1, 3), ++launches;
     scalar_kernel<S_L0A><<<sg, 128, 0, st>>>(a);
-    if (f.hme_l0_round_b) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1), ++launches;
+    if (f.hme_l0_round_b) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1, 3), ++launches;
     scalar_kernel<S_L0B><<<sg, 128, 0, st>>>(a);
     mark(); // 3: HME level 0
-    if (f.hme_l1) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 2), ++launches;
+    if (f.hme_l1) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 2, 4), ++launches;
     scalar_kernel<S_L1><<<sg, 128, 0, st>>>(a);
     mark(); // 4: HME level 1
-    if (f.hme_l2) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 3), ++launches;
+    if (f.hme_l2) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 3, 5), ++launches;
     scalar_kernel<S_L2><<<sg, 128, 0, st>>>(a);
     mark(); // 5: HME level 2 + search centre + HME pruning
     if (f.small_areas) {

@@ -130,6 +130,12 @@ class MeSession:
         _check(self.lib.svtme_last_phase_ms(self.h, v, len(self.PHASE_NAMES)), self.lib)
         return dict(zip(self.PHASE_NAMES, (float(x) for x in v)))
 
+    def last_phase_work(self):
+        """Algorithmic SAD byte-ops per launch slot of the stage pipeline in the last launch."""
+        v = (C.c_uint64 * len(self.PHASE_NAMES))()
+        _check(self.lib.svtme_last_phase_work(self.h, v, len(self.PHASE_NAMES)), self.lib)
+        return dict(zip(self.PHASE_NAMES, (int(x) for x in v)))
+
     def last_kernel_ms(self):
         return float(self.lib.svtme_last_kernel_ms(self.h))
 

@@ -98,6 +98,10 @@ __device__ __noinline__ void stage_window4(uint8_t *arena, const uint8_t *__rest
 // HME engine
 // ------------------------------------------------------------------------------------------------
 #define SVTME_MAX_JOBS 32
+#define HME_NT ((int)blockDim.x) // the HME engine adapts to the CTA size of its kernel
+#ifndef SVTME_HME_THREADS
+#define SVTME_HME_THREADS 128
+#endif
 
 __device__ __forceinline__ uint32_t magic_div(uint32_t d) { return 0xFFFFFFFFu / d + 1u; } // exact for n < 2^16
 
@@ -403,7 +407,7 @@ __device__ __noinline__ void hme_points(const HBlk &blk, HJob *jobs, int n) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int wcols = (blk.bw + 3) >> 2, items = blk.nrows * wcols;
     const uint32_t mg_wc = magic_div((uint32_t)wcols);
-    for (int j = warp; j < n; j += SVTME_THREADS / 32) {
+    for (int j = warp; j < n; j += (HME_NT >> 5)) {
         const HJob &job = jobs[j];
         uint32_t acc = 0;
         const size_t rstep = (size_t)blk.row_step * job.stride;
@@ -447,12 +451,12 @@ __device__ __noinline__ void hme_group_stage(const HJob *jobs, const HGeo *geo, 
     constexpr int U = 4; // chunks per thread in flight
     const int tid = threadIdx.x;
     int cj = G.j0;
-    for (int base = tid; base < G.stage_total; base += U * SVTME_THREADS) {
+    for (int base = tid; base < G.stage_total; base += U * HME_NT) {
         uint32_t w[U][5], mis[U];
         uint8_t *dst[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const int i = base + u * SVTME_THREADS;
+            const int i = base + u * HME_NT;
             if (i < G.stage_total) {
                 while (i >= geo[cj].stage_base + geo[cj].stage_units) ++cj;
                 const HGeo &g = geo[cj];
@@ -464,10 +468,10 @@ __device__ __noinline__ void hme_group_stage(const HJob *jobs, const HGeo *geo, 
         }
 #pragma unroll
         for (int u = 0; u < U; ++u)
-            if (base + u * SVTME_THREADS < G.stage_total) stage_unit_store(dst[u], w[u], mis[u]);
+            if (base + u * HME_NT < G.stage_total) stage_unit_store(dst[u], w[u], mis[u]);
     }
     uint32_t *sadreg = reinterpret_cast<uint32_t *>(arena + geo[G.j0].sad_off);
-    for (int i = tid; i < G.scan_total; i += SVTME_THREADS) sadreg[i] = 0;
+    for (int i = tid; i < G.scan_total; i += HME_NT) sadreg[i] = 0;
 }
 
 // Flush of a 32-bit running key (see hme_emit): lanes flushing the same job combine with one
@@ -494,7 +498,7 @@ __device__ __noinline__ void hme_group_items(const HBlk &blk_ref, HJob *jobs, co
     ItemGeo ig;
     uint32_t best32 = ~0u;
     int cj = G.j0, bj = -1, base = 0, end = 0;
-    for (int it = threadIdx.x; it < G.item_total; it += SVTME_THREADS) {
+    for (int it = threadIdx.x; it < G.item_total; it += HME_NT) {
         if (it >= end) {
             while (it >= geo[cj].item_base + geo[cj].n_items) ++cj;
             if (nb == 1 && bj >= 0) flush_key32(jobs, geo, bj, best32);
@@ -514,7 +518,7 @@ __device__ __noinline__ void hme_group_scan(HJob *jobs, const HGeo *geo, const H
     const uint32_t *sadreg = reinterpret_cast<const uint32_t *>(arena + geo[G.j0].sad_off);
     unsigned long long best = ~0ULL;
     int cj = G.j0, bj = -1;
-    for (int i = threadIdx.x; i < G.scan_total; i += SVTME_THREADS) {
+    for (int i = threadIdx.x; i < G.scan_total; i += HME_NT) {
         while (i >= geo[cj].scan_base + geo[cj].scan_n) ++cj;
         if (cj != bj) {
             if (bj >= 0) flush_key(jobs, bj, best);

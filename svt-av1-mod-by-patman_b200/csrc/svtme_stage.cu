@@ -117,7 +117,7 @@ struct EngSmem {
 };
 
 // level: 0 = 64x64 block, every other row (zz-SAD); 1/2/3 = HME level 0/1/2 block
-__global__ void __launch_bounds__(SVTME_THREADS, SVTME_HME_CTAS_PER_SM) engine_kernel(WideArgs a, int level, int wslot) {
+__global__ void __launch_bounds__(SVTME_HME_THREADS, SVTME_HME_CTAS_PER_SM) engine_kernel(WideArgs a, int level, int wslot) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     EngSmem *sm = reinterpret_cast<EngSmem *>(smem_raw);
     const int gid = blockIdx.x, tid = threadIdx.x;
@@ -132,13 +132,13 @@ __global__ void __launch_bounds__(SVTME_THREADS, SVTME_HME_CTAS_PER_SM) engine_k
     const int side = 64 >> sh; // source block is side x side
     {   // source block -> shared memory, 16-byte chunks (b64_src_ptr / quarter / sixteenth buffers, me_process.c:189-213)
         const int cpr = side >> 4;
-        for (int i = tid; i < side * cpr; i += SVTME_THREADS) {
+        for (int i = tid; i < side * cpr; i += SVTME_HME_THREADS) {
             const int r = i / cpr, c = i - r * cpr;
             *reinterpret_cast<uint4 *>(&sm->src[r * side + c * 16]) =
                 *reinterpret_cast<const uint4 *>(pl.at((org_x >> sh) + c * 16, (org_y >> sh) + r));
         }
     }
-    for (int i = tid; i < n * (int)(sizeof(HJob) / 4); i += SVTME_THREADS)
+    for (int i = tid; i < n * (int)(sizeof(HJob) / 4); i += SVTME_HME_THREADS)
         reinterpret_cast<uint32_t *>(sm->jobs)[i] = reinterpret_cast<const uint32_t *>(s->jobs)[i];
     __syncthreads();
     const bool sub = level == 0 || !full;
@@ -366,20 +366,20 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, vo
     if (f.zz) points_kernel<<<N, 128, 0, st>>>(a), ++launches;
     scalar_kernel<S_ZZ><<<sg, 128, 0, st>>>(a);
     mark(); // 1: zz-SAD
-    if (f.prehme) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1, 2), ++launches;
+    if (f.prehme) engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 2), ++launches;
     scalar_kernel<S_PREHME1><<<sg, 128, 0, st>>>(a);
-    if (f.prehme_l1_round) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1, 2), ++launches;
+    if (f.prehme_l1_round) engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 2), ++launches;
     scalar_kernel<S_PREHME2><<<sg, 128, 0, st>>>(a);
     mark(); // 2: pre-HME
-    if (f.hme_l0) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1, 3), ++launches;
+    if (f.hme_l0) engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 3), ++launches;
     scalar_kernel<S_L0A><<<sg, 128, 0, st>>>(a);
-    if (f.hme_l0_round_b) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 1, 3), ++launches;
+    if (f.hme_l0_round_b) engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 3), ++launches;
     scalar_kernel<S_L0B><<<sg, 128, 0, st>>>(a);
     mark(); // 3: HME level 0
-    if (f.hme_l1) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 2, 4), ++launches;
+    if (f.hme_l1) engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 2, 4), ++launches;
     scalar_kernel<S_L1><<<sg, 128, 0, st>>>(a);
     mark(); // 4: HME level 1
-    if (f.hme_l2) engine_kernel<<<N, SVTME_THREADS, sizeof(EngSmem), st>>>(a, 3, 5), ++launches;
+    if (f.hme_l2) engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 3, 5), ++launches;
     scalar_kernel<S_L2><<<sg, 128, 0, st>>>(a);
     mark(); // 5: HME level 2 + search centre + HME pruning
     if (f.small_areas) {

@@ -432,14 +432,16 @@ extern "C" int svtme_launch_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint3
     }
     SvtmeStageFlags flags = {};
     flags.small_areas = true;
+    flags.prehme_strip = true;
     for (uint32_t i = 0; i < n; ++i) {
+        flags.prehme_strip = flags.prehme_strip && jobs[i].params.hme_search_method != 1;
         const SvtmeStageFlags f = svtme_stage_flags(jobs[i].params);
         flags.small_areas = flags.small_areas && areas_are_small(jobs[i].params);
         flags.zz |= f.zz; flags.prehme |= f.prehme; flags.prehme_l1_round |= f.prehme_l1_round;
         flags.hme_l0 |= f.hme_l0; flags.hme_l0_round_b |= f.hme_l0_round_b;
         flags.hme_l1 |= f.hme_l1; flags.hme_l2 |= f.hme_l2;
     }
-    svtme_launch_me_stage(h->d_jobs, (int)n, (int)h->n_b64, h->d_states, h->stream, h->ph_ev, flags);
+    svtme_launch_me_stage(h->d_jobs, (int)n, (int)h->b64_cols, (int)h->b64_rows, h->d_states, h->stream, h->ph_ev, flags);
     CU(cudaGetLastError());
     CU(cudaEventRecord(h->ev1, h->stream));
     return SVTME_OK;

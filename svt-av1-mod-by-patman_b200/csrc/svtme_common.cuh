@@ -82,9 +82,11 @@ void svtme_launch_build_batch(const SvtmePutItem *d_items, int n, const DevPyram
 struct SvtmeStageFlags {
     bool small_areas;     // every full-pel search area is at most svtme_fp_direct_max() positions
     bool zz, prehme, prehme_l1_round, hme_l0, hme_l0_round_b, hme_l1, hme_l2;
+    bool prehme_strip;    // pre-HME runs in strip mode (one CTA per b64 column / row and reference): every
+                          // picture of the batch uses the sub-sampled SAD (16x8 source block = one sub-block)
 };
 SvtmeStageFlags svtme_stage_flags(const SvtMeParams &p);
-void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, void *d_states, cudaStream_t st,
+void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b64_rows, void *d_states, cudaStream_t st,
                            cudaEvent_t *ev, const SvtmeStageFlags &f);
 int svtme_fp_direct_max();
 size_t svtme_stage_state_bytes();

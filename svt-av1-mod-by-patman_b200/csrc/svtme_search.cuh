@@ -156,6 +156,7 @@ struct HGeo {
     uint32_t need;       // arena bytes (copies + SAD buffer)
     int big;             // does not fit as a whole: tiled single-job path
     int stage_base, item_base, scan_base; // prefix sums inside the group
+    int row_off, x_shift; // strip mode (strip_kernel): rows above / bytes left of the window in the shared strip's tiling
 };
 
 struct HGroup {
@@ -173,12 +174,14 @@ struct HPlan {           // shared-memory scratch of one round
 struct ItemGeo {
     uint32_t arena_off, sad_off;
     int pitch, xt_n, sa_w, bh, y0, skip_even, variant;
+    int row_off, x_shift; // window origin inside a SHARED strip (0 when the job staged its own window)
     uint32_t mg_xt;
 };
 __device__ __forceinline__ void load_item_geo(const HGeo &g, ItemGeo &ig) {
     ig.arena_off = g.arena_off; ig.sad_off = g.sad_off;
     ig.pitch = g.m << 4; ig.xt_n = g.xt_n; ig.sa_w = g.sa_w; ig.bh = g.bh; ig.y0 = g.y0;
     ig.skip_even = g.skip_even; ig.variant = g.variant; ig.mg_xt = g.mg_xt;
+    ig.row_off = g.row_off; ig.x_shift = g.x_shift;
 }
 
 // Result sink of one position. Single-sub-block blocks (<= 16x8, SAD < 2^15) keep a 32-bit running
@@ -210,7 +213,7 @@ __device__ __forceinline__ void hme_item_fast(const HBlk &blk, const ItemGeo &ig
     const uint8_t *base = arena + ig.arena_off + 4 * (xt * G + 4 * bxi);
     const uint8_t *sp = blk.src + (size_t)(8 * byi) * blk.src_pitch + 16 * bxi;
     const uint32_t sh = 8 * c;
-    const int row0 = yb + 8 * byi * rs;
+    const int row0 = ig.row_off + yb + 8 * byi * rs;
     // sliding window of the TY source rows in use: reference row rho meets source row rho - ty at
     // y-position ty. Source rows come from shared memory as warp-wide broadcasts (every lane of an
     // item group reads the same address), which keeps the register budget at TY*4 instead of 32.
@@ -258,17 +261,19 @@ __device__ __forceinline__ void hme_item_fast(const HBlk &blk, const ItemGeo &ig
         if (y < ig.bh && !(ig.skip_even && !((ig.y0 + y) & 1))) {
 #pragma unroll
             for (int j = 0; j < G; ++j) {
-                const int x = xt * 4 * G + 4 * j + c;
-                if (x < ig.sa_w) hme_emit(single, acc[ty][j], y, x, ig, arena, best32);
+                const int x = xt * 4 * G + 4 * j + c - ig.x_shift;
+                if ((unsigned)x < (unsigned)ig.sa_w) hme_emit(single, acc[ty][j], y, x, ig, arena, best32);
             }
         }
     }
 }
 
 // Generic item: partial sub-blocks (block height not a multiple of 8 rows, width not a multiple of
-// 16) — edge b64s only. Position by position, source rows read from shared memory, compact code.
-__device__ __noinline__ uint32_t hme_item_slow(const HBlk blk, const ItemGeo ig, uint8_t *arena, int G, int TY, int c, int xt,
-                                               int yb, int bxi, int byi, uint32_t best32) {
+// 16) — edge b64s only. Same tile shape and loads as the fast item, but rolled loops over the y-positions
+// and the rows that exist (compact code), and byte masks when the sub-block is narrower than 16.
+template <int G>
+__device__ __forceinline__ void hme_slow_body(const HBlk &blk, const ItemGeo &ig, uint8_t *arena, int TY, int c, int xt, int yb,
+                                              int bxi, int byi, uint32_t &best32) {
     const int rs = blk.row_step;
     const int rows_here = min(8, blk.nrows - 8 * byi), vb = min(16, blk.bw - 16 * bxi);
     uint32_t msk[4];
@@ -277,33 +282,73 @@ __device__ __noinline__ uint32_t hme_item_slow(const HBlk blk, const ItemGeo ig,
         const int n = min(max(vb - 4 * i, 0), 4);
         msk[i] = n >= 4 ? ~0u : ((1u << (8 * n)) - 1u);
     }
-    const bool single = blk.nb == 1;
+    const bool single = blk.nb == 1, narrow = vb < 16;
     const uint32_t sh = 8 * c;
+    const uint8_t *base = arena + ig.arena_off + 4 * (xt * G + 4 * bxi);
+    const uint8_t *sp = blk.src + (size_t)(8 * byi) * blk.src_pitch + 16 * bxi;
     for (int ty = 0; ty < TY; ++ty) {
         const int y = yb + ty * rs;
         if (y >= ig.bh || (ig.skip_even && !((ig.y0 + y) & 1))) continue;
-        for (int j = 0; j < G; ++j) {
-            const int x = xt * 4 * G + 4 * j + c;
-            if (x >= ig.sa_w) continue;
-            uint32_t acc = 0;
-            for (int r = 0; r < rows_here; ++r) {
-                const int row = y + (8 * byi + r) * rs;
-                const uint32_t *rp = reinterpret_cast<const uint32_t *>(arena + ig.arena_off + row * ig.pitch +
-                                                                        ((row >> 3) << 4) + 4 * (xt * G + j + 4 * bxi));
-                const uint32_t *sp = reinterpret_cast<const uint32_t *>(blk.src + (size_t)(8 * byi + r) * blk.src_pitch + 16 * bxi);
-                uint32_t w[5];
+        uint32_t acc[G];
 #pragma unroll
-                for (int i = 0; i < 5; ++i) w[i] = rp[i];
+        for (int j = 0; j < G; ++j) acc[j] = 0;
+#pragma unroll 1
+        for (int r = 0; r < rows_here; ++r) {
+            const int row = ig.row_off + y + (8 * byi + r) * rs;
+            const uint8_t *rp = base + row * ig.pitch + ((row >> 3) << 4);
+            uint32_t w[G + 5];
+            if (G == 2) {
 #pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    if (msk[i]) acc = vsad4(sp[i] & msk[i], __funnelshift_r(w[i], w[i + 1], sh) & msk[i], acc);
+                for (int k = 0; k < 3; ++k) {
+                    const uint2 v = *reinterpret_cast<const uint2 *>(rp + 8 * k);
+                    w[2 * k] = v.x; w[2 * k + 1] = v.y;
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < (G + 4) / 4; ++k) {
+                    const uint4 v = *reinterpret_cast<const uint4 *>(rp + 16 * k);
+                    w[4 * k] = v.x; w[4 * k + 1] = v.y; w[4 * k + 2] = v.z; w[4 * k + 3] = v.w;
+                }
             }
-            hme_emit(single, acc, y, x, ig, arena, best32);
+            w[G + 4] = *reinterpret_cast<const uint32_t *>(rp + 4 * (G + 4));
+#pragma unroll
+            for (int i = 0; i < G + 4; ++i) w[i] = __funnelshift_r(w[i], w[i + 1], sh);
+            const uint4 sv = *reinterpret_cast<const uint4 *>(sp + r * blk.src_pitch);
+            uint32_t s[4] = {sv.x, sv.y, sv.z, sv.w};
+            if (narrow) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) s[i] &= msk[i];
+#pragma unroll
+                for (int j = 0; j < G; ++j)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) acc[j] = vsad4(s[i], w[j + i] & msk[i], acc[j]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < G; ++j)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) acc[j] = vsad4(s[i], w[j + i], acc[j]);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < G; ++j) {
+            const int x = xt * 4 * G + 4 * j + c - ig.x_shift;
+            if ((unsigned)x < (unsigned)ig.sa_w) hme_emit(single, acc[j], y, x, ig, arena, best32);
         }
     }
+}
+
+__device__ __noinline__ uint32_t hme_item_slow(const HBlk blk, const ItemGeo ig, uint8_t *arena, int G, int TY, int c, int xt,
+                                               int yb, int bxi, int byi, uint32_t best32) {
+    if (G == 2)
+        hme_slow_body<2>(blk, ig, arena, TY, c, xt, yb, bxi, byi, best32);
+    else if (G == 4)
+        hme_slow_body<4>(blk, ig, arena, TY, c, xt, yb, bxi, byi, best32);
+    else
+        hme_slow_body<8>(blk, ig, arena, TY, c, xt, yb, bxi, byi, best32);
     return best32;
 }
 
+template <bool STRIP>
 __device__ __forceinline__ void hme_item_any(const HBlk &blk, const ItemGeo &ig, uint8_t *arena, int it, uint32_t &best32) {
     const int nb = blk.nb, nbx = blk.nbx, rs = blk.row_step;
     int t = nb == 1 ? it : (int)__umulhi((uint32_t)it, blk.mg_nb);
@@ -314,7 +359,8 @@ __device__ __forceinline__ void hme_item_any(const HBlk &blk, const ItemGeo &ig,
     const int xt = t - yt * ig.xt_n;
     const int byi = nbx == 1 ? b : (int)__umulhi((uint32_t)b, blk.mg_nbx);
     const int bxi = b - byi * nbx;
-    const int G = ig.variant == 0 ? 2 : (ig.variant == 1 ? 4 : 8), TY = ig.variant == 2 ? 2 : 4;
+    const int G = (ig.variant == 0 || ig.variant == 3) ? 2 : (ig.variant == 1 ? 4 : 8);
+    const int TY = ig.variant == 2 ? 2 : (ig.variant == 3 ? 8 : 4);
     const int yb = (yt & (rs - 1)) + (yt >> (rs - 1)) * TY * rs; // rs is 1 or 2
     const bool full = blk.nrows - 8 * byi >= 8 && blk.bw - 16 * bxi >= 16;
     if (!full) {
@@ -326,8 +372,10 @@ __device__ __forceinline__ void hme_item_any(const HBlk &blk, const ItemGeo &ig,
         hme_item_fast<2, 4>(blk, ig, arena, c, xt, yb, bxi, byi, best32);
     else if (ig.variant == 1)
         hme_item_fast<4, 4>(blk, ig, arena, c, xt, yb, bxi, byi, best32);
-    else
+    else if (!STRIP || ig.variant == 2)
         hme_item_fast<8, 2>(blk, ig, arena, c, xt, yb, bxi, byi, best32);
+    else // tall narrow windows, chosen only where a CTA has enough items to stay balanced (strip mode)
+        hme_item_fast<2, 8>(blk, ig, arena, c, xt, yb, bxi, byi, best32);
 }
 
 // Tile geometry for a (sub)area of wb x hb positions; g.need = the arena bytes it takes.
@@ -367,6 +415,7 @@ __device__ __forceinline__ void hme_geo(const HBlk &blk, int wb, int hb, int ski
     g.arena_off = 0;
     g.sad_off = (uint32_t)g.copy_bytes;
     g.stage_base = g.item_base = g.scan_base = 0;
+    g.row_off = g.x_shift = 0;
 }
 
 // Stage one 16-byte chunk of a window row: five aligned global words -> byte-aligned chunk.
@@ -508,9 +557,47 @@ __device__ __noinline__ void hme_group_items(const HBlk &blk_ref, HJob *jobs, co
             base = geo[cj].item_base;
             end = base + geo[cj].n_items;
         }
-        hme_item_any(blk, ig, arena, it - base, best32);
+        hme_item_any<false>(blk, ig, arena, it - base, best32);
     }
     if (nb == 1 && bj >= 0) flush_key32(jobs, geo, bj, best32);
+}
+
+// Strip mode (strip_kernel): the jobs [j0, j1) are windows of DIFFERENT source blocks inside ONE staged
+// strip of the reference plane (a column or a row of b64s searches almost the same pixels). Every job
+// is a single 16x8 sub-block (nb == 1); geo[j] places its window in the strip (row_off, x_shift,
+// arena_off) and sj[j] is its source block.
+struct StripJob {
+    const uint8_t *src; // shared memory
+    int bw, nrows;
+};
+__device__ __noinline__ void strip_group_items(const StripJob *sj, int src_pitch, int row_step, HJob *jobs, const HGeo *geo,
+                                               int j0, int item_total, uint8_t *arena) {
+    ItemGeo ig;
+    HBlk blk;
+    blk.src = nullptr;
+    blk.src_pitch = src_pitch;
+    blk.row_step = row_step;
+    blk.bw = blk.nrows = 0;
+    blk.nbx = blk.nb = 1;
+    blk.mg_nb = blk.mg_nbx = 0;
+    uint32_t best32 = ~0u;
+    int cj = j0, bj = -1, base = 0, end = 0;
+    for (int it = threadIdx.x; it < item_total; it += HME_NT) {
+        if (it >= end) {
+            while (it >= geo[cj].item_base + geo[cj].n_items) ++cj;
+            if (bj >= 0) flush_key32(jobs, geo, bj, best32);
+            best32 = ~0u;
+            bj = cj;
+            load_item_geo(geo[cj], ig);
+            base = geo[cj].item_base;
+            end = base + geo[cj].n_items;
+            blk.src = sj[cj].src;
+            blk.bw = sj[cj].bw;
+            blk.nrows = sj[cj].nrows;
+        }
+        hme_item_any<true>(blk, ig, arena, it - base, best32);
+    }
+    if (bj >= 0) flush_key32(jobs, geo, bj, best32);
 }
 
 __device__ __noinline__ void hme_group_scan(HJob *jobs, const HGeo *geo, const HGroup &G_ref, uint8_t *arena) {

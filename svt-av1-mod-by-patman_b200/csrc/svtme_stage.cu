@@ -13,6 +13,7 @@
 //                        85-PU full-pel search (integer_search_b64 :1249-1586)
 //   finish_kernel        one CTA per b64: me_prune_ref, candidate arrays, statistics
 // Dependencies between launches are exactly the reference's statement order; b64s never interact.
+#include <cstdlib>
 #include "svtme_scalar.cuh"
 
 struct WideArgs {
@@ -149,6 +150,204 @@ __global__ void __launch_bounds__(SVTME_HME_THREADS, SVTME_HME_CTAS_PER_SM) engi
         s->jobs[tid].key = sm->jobs[tid].key;
         const int rows = sm->jobs[tid].skip_even ? sm->jobs[tid].sa_h / 2 : sm->jobs[tid].sa_h;
         w = (unsigned long long)sm->jobs[tid].sa_w * rows * blk.bw * blk.nrows;
+    }
+    if (tid < 32 && J.work_ops) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) w += __shfl_xor_sync(0xffffffffu, w, o);
+        if (tid == 0 && w) atomicAdd(J.work_ops + wslot, w);
+    }
+}
+
+// ---------------------------------------------------------------- pre-HME in strip mode
+// The two pre-HME windows of a b64 (prehme_core :1641) are a tall 8-wide column and a flat, wide row
+// around the block; the b64s of one column (one row) of the picture therefore search almost the same
+// pixels of the sixteenth plane. strip_kernel gives ONE CTA a line segment of up to STRIP_SEG b64s for
+// one (list, reference, region): it stages the union of their windows once and runs all their search
+// items as one flattened list (thousands of items per barrier instead of a few hundred, staging
+// amortised over the segment). Regions with index 0 are grouped along columns, index 1 along rows —
+// a choice that only affects speed: any set of windows is handled, the segment is split until the
+// union fits the arena, and a single window larger than the arena takes the tiled path.
+#define STRIP_SEG 32
+struct StripSmem {
+    HJob jobs[STRIP_SEG];
+    HPlan plan;                 // plan.geo[j]: window j inside the strip
+    StripJob sj[STRIP_SEG];
+    int gidx[STRIP_SEG], jidx[STRIP_SEG], sx[STRIP_SEG], sy[STRIP_SEG];
+    HJob strip_job;             // the strip itself, as the one staging job
+    HGeo strip_geo;
+    int n, next, item_total, fits;
+    __align__(16) uint8_t src[STRIP_SEG][16 * 16];
+    __align__(16) uint8_t arena[SVTME_HME_ARENA_BYTES];
+};
+
+__device__ __forceinline__ int warp_min(int v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ int warp_max(int v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+__global__ void __launch_bounds__(SVTME_HME_THREADS, SVTME_HME_CTAS_PER_SM)
+    strip_kernel(WideArgs a, int cols, int rows, int wslot, int arena_limit) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    StripSmem *sm = reinterpret_cast<StripSmem *>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int segs_v = (rows + STRIP_SEG - 1) / STRIP_SEG, segs_h = (cols + STRIP_SEG - 1) / STRIP_SEG;
+    const int n_col_tasks = cols * segs_v, per_slot = n_col_tasks + rows * segs_h;
+    int t = blockIdx.x;
+    const int task = t % per_slot;
+    t /= per_slot;
+    const int slot = t % (NL * NR), pic = t / (NL * NR);
+    const int li = slot / NR, ri = slot % NR;
+    const DevJob &J = a.jobs[pic];
+    if (li >= J.prm.num_of_list_to_search || ri >= (int)J.prm.num_of_ref_pic_to_search[li]) return;
+    int region, bx0, by0, len, step;
+    if (task < n_col_tasks) {
+        region = 0; bx0 = task / segs_v; by0 = (task % segs_v) * STRIP_SEG; len = min(STRIP_SEG, rows - by0); step = cols;
+    } else {
+        const int u = task - n_col_tasks;
+        region = 1; by0 = u / segs_h; bx0 = (u % segs_h) * STRIP_SEG; len = min(STRIP_SEG, cols - bx0); step = 1;
+    }
+    const int g0 = pic * a.b64_per_job + by0 * cols + bx0;
+    // ---- the segment's jobs of this (list, reference, region), compacted (warp 0, lane <-> b64)
+    if (warp == 0) {
+        int found = -1;
+        StageState *s = nullptr;
+        if (lane < len) {
+            s = &a.st[g0 + lane * step];
+            const int nj = s->n_jobs;
+            for (int k = 0; k < nj; ++k) {
+                const JobMeta m = s->meta[k];
+                if (m.li == li && m.ri == ri && m.a == region) { found = k; break; }
+            }
+        }
+        const unsigned bal = __ballot_sync(0xffffffffu, found >= 0);
+        const int pos = __popc(bal & ((1u << lane) - 1u));
+        if (found >= 0) {
+            sm->jobs[pos] = s->jobs[found];
+            sm->gidx[pos] = g0 + lane * step;
+            sm->jidx[pos] = found;
+            sm->sj[pos] = StripJob{sm->src[pos], s->b64_w >> 2, s->b64_h >> 3};
+            sm->sx[pos] = s->org_x >> 2;
+            sm->sy[pos] = s->org_y >> 2;
+        }
+        if (lane == 0) sm->n = __popc(bal);
+    }
+    __syncthreads();
+    const int n = sm->n;
+    if (n == 0) return;
+    {   // sixteenth source blocks (me_process.c:205-213), all 16 rows; the sub-sampled SAD reads every other one
+        const DevPlane &cur = J.cur.lvl[2];
+        for (int i = tid; i < n * 16; i += SVTME_HME_THREADS) {
+            const int k = i >> 4, r = i & 15;
+            *reinterpret_cast<uint4 *>(&sm->src[k][r * 16]) = *reinterpret_cast<const uint4 *>(cur.at(sm->sx[k], sm->sy[k] + r));
+        }
+    }
+    const DevPlane &rp = J.ref[li][ri].lvl[2];
+    const int rs = 2, src_pitch = 32; // SUB_SAD_SEARCH (the host selects strip mode only then)
+    int ra = 0;
+    while (ra < n) {
+        if (warp == 0) {
+            const HJob jb = sm->jobs[min(lane, n - 1)];
+            const int nrows_j = max(sm->sj[min(lane, n - 1)].nrows, 1);
+            const ptrdiff_t off = jb.ref - rp.base;
+            const int y_tl = (int)(off / rp.stride), x_tl = (int)(off - (ptrdiff_t)y_tl * rp.stride);
+            const bool live = jb.sa_w > 0 && jb.sa_h > 0;
+            const int G = jb.sa_w <= 8 ? 2 : (jb.sa_w <= 16 ? 4 : 8);
+            const int ny = (jb.sa_h + rs - 1) / rs;
+            const int TY = G == 8 ? 2 : ((G == 2 && ny >= 16) ? 8 : 4);
+            const int n_yt = (ny + TY - 1) / TY;
+            int rb = n, x0, y0, xs, xo, xt_n, dy, rows_s, rows_real, words, bytes, cpr, m;
+            for (;;) {
+                const bool in = lane >= ra && lane < rb;
+                x0 = warp_min(in ? x_tl : 0x7fffffff);
+                y0 = warp_min(in ? y_tl : 0x7fffffff);
+                const int dx = x_tl - x0;
+                dy = y_tl - y0;
+                xs = dx & ~(4 * G - 1);
+                xo = dx - xs;
+                xt_n = (xo + jb.sa_w + 4 * G - 1) / (4 * G);
+                rows_s = warp_max(in ? dy + n_yt * TY * rs + 7 * rs : 0);
+                rows_real = warp_max(in ? dy + jb.sa_h + (nrows_j - 1) * rs : 1);
+                words = warp_max(in ? (xs >> 2) + xt_n * G + 5 : 0);
+                cpr = (words + 3) >> 2;
+                m = cpr | 1;
+                bytes = (rows_s * m + (rows_s >> 3) + 1) * 16;
+                if (bytes <= arena_limit || rb - ra == 1) break;
+                rb = ra + (rb - ra + 1) / 2;
+            }
+            const bool in = lane >= ra && lane < rb;
+            const int n_items = (in && live) ? rs * n_yt * xt_n * 4 : 0;
+            int ps = n_items;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, ps, o);
+                if (lane >= o) ps += v;
+            }
+            const int total = __shfl_sync(0xffffffffu, ps, 31);
+            if (in) {
+                HGeo &g = sm->plan.geo[lane];
+                g.arena_off = (uint32_t)xs;
+                g.sad_off = 0;
+                g.copy_bytes = bytes;
+                g.m = m;
+                g.sa_w = jb.sa_w;
+                g.bh = jb.sa_h;
+                g.x0 = g.y0 = 0;
+                g.xt_n = xt_n;
+                g.n_items = n_items;
+                g.G = G;
+                g.skip_even = jb.skip_even;
+                g.variant = G == 2 ? (TY == 8 ? 3 : 0) : (G == 4 ? 1 : 2);
+                g.mg_xt = magic_div((uint32_t)max(xt_n, 1));
+                g.mg_wb = magic_div((uint32_t)max(jb.sa_w, 1));
+                g.item_base = ps - n_items;
+                g.row_off = dy;
+                g.x_shift = xo;
+            }
+            if (lane == 0) {
+                sm->strip_job.ref = rp.base + (size_t)y0 * rp.stride + x0;
+                sm->strip_job.stride = rp.stride;
+                HGeo &g = sm->strip_geo;
+                g.arena_off = 0;
+                g.sad_off = 0;
+                g.ref_off = 0;
+                g.m = m;
+                g.cpr = cpr;
+                g.mg_cpr = magic_div((uint32_t)cpr);
+                g.rows = rows_s;
+                g.rows_real = rows_real;
+                g.stage_base = 0;
+                g.stage_units = rows_s * cpr;
+                sm->next = rb;
+                sm->item_total = total;
+                sm->fits = bytes <= arena_limit;
+            }
+        }
+        __syncthreads();
+        if (sm->fits) {
+            if (sm->item_total > 0) {
+                const HGroup SG = HGroup{0, 1, 0, sm->strip_geo.stage_units, 0, 0};
+                hme_group_stage(&sm->strip_job, &sm->strip_geo, SG, sm->arena);
+                __syncthreads();
+                strip_group_items(sm->sj, src_pitch, rs, sm->jobs, sm->plan.geo, ra, sm->item_total, sm->arena);
+            }
+        } else { // one window larger than the arena: tiled like any big HME job
+            const HBlk blk = make_hblk(sm->sj[ra].src, src_pitch, sm->sj[ra].bw, sm->sj[ra].nrows, rs);
+            hme_search_tiled(blk, sm->jobs, ra, &sm->plan, sm->arena);
+        }
+        __syncthreads();
+        ra = sm->next;
+    }
+    unsigned long long w = 0;
+    if (tid < n) {
+        a.st[sm->gidx[tid]].jobs[sm->jidx[tid]].key = sm->jobs[tid].key;
+        const int rws = sm->jobs[tid].skip_even ? sm->jobs[tid].sa_h / 2 : sm->jobs[tid].sa_h;
+        w = (unsigned long long)sm->jobs[tid].sa_w * rws * sm->sj[tid].bw * sm->sj[tid].nrows;
     }
     if (tid < 32 && J.work_ops) {
 #pragma unroll
@@ -322,6 +521,15 @@ __global__ void __launch_bounds__(128) finish_kernel(WideArgs a) {
 }
 
 // ---------------------------------------------------------------- host: the launch sequence
+// Arena bytes strip_kernel may fill; lowered only by tests (SVTME_STRIP_ARENA_LIMIT in the environment,
+// read once) to exercise the segment-splitting and tiled paths with ordinary pictures.
+static int strip_arena_limit_from_env() {
+    const char *e = getenv("SVTME_STRIP_ARENA_LIMIT");
+    const int v = e ? atoi(e) : 0;
+    return (v >= 1024 && v <= SVTME_HME_ARENA_BYTES) ? v : SVTME_HME_ARENA_BYTES;
+}
+static const int g_strip_arena_limit = strip_arena_limit_from_env();
+
 // Launch slots (one event after each; names in SVTME_PHASE_NAMES of svtme_common.cuh).
 SvtmeStageFlags svtme_stage_flags(const SvtMeParams &p) {
     SvtmeStageFlags f;
@@ -336,11 +544,13 @@ SvtmeStageFlags svtme_stage_flags(const SvtMeParams &p) {
     return f;
 }
 
-void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, void *d_states, cudaStream_t st,
+void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b64_rows, void *d_states, cudaStream_t st,
                            cudaEvent_t *ev, const SvtmeStageFlags &f) {
+    const int b64_per_job = b64_cols * b64_rows;
     static bool configured = false;
     if (!configured) {
         cudaFuncSetAttribute(engine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EngSmem));
+        cudaFuncSetAttribute(strip_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(StripSmem));
         cudaFuncSetAttribute(int_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IntSmem<false>));
         cudaFuncSetAttribute(int_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IntSmem<true>));
         cudaFuncSetAttribute(finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FinSmem));
@@ -366,9 +576,19 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_per_job, vo
     if (f.zz) points_kernel<<<N, 128, 0, st>>>(a), ++launches;
     scalar_kernel<S_ZZ><<<sg, 128, 0, st>>>(a);
     mark(); // 1: zz-SAD
-    if (f.prehme) engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 2), ++launches;
+    // pre-HME rounds: strip mode when every picture uses the sub-sampled SAD, else one CTA per b64
+    const int strip_tasks = n_jobs * NL * NR *
+        (b64_cols * ((b64_rows + STRIP_SEG - 1) / STRIP_SEG) + b64_rows * ((b64_cols + STRIP_SEG - 1) / STRIP_SEG));
+    auto prehme_round = [&]() {
+        if (f.prehme_strip)
+            strip_kernel<<<strip_tasks, SVTME_HME_THREADS, sizeof(StripSmem), st>>>(a, b64_cols, b64_rows, 2, g_strip_arena_limit);
+        else
+            engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 2);
+        ++launches;
+    };
+    if (f.prehme) prehme_round();
     scalar_kernel<S_PREHME1><<<sg, 128, 0, st>>>(a);
-    if (f.prehme_l1_round) engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 2), ++launches;
+    if (f.prehme_l1_round) prehme_round();
     scalar_kernel<S_PREHME2><<<sg, 128, 0, st>>>(a);
     mark(); // 2: pre-HME
     if (f.hme_l0) engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 3), ++launches;

@@ -55,11 +55,36 @@ def build_specs(abi, gop, wl, derive_fn):
 
 
 class ClockSampler(threading.Thread):
+    """SM clock + throttle reasons sampled DURING the timed region (NVML in-process, ~2 ms per sample;
+    nvidia-smi subprocess as the fallback)."""
+
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.rows, self.stop_flag = index, [], False
+        self.nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nvml = pynvml
+            self.dev = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_sm = int(pynvml.nvmlDeviceGetMaxClockInfo(self.dev, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nvml = None
 
     def run(self):
+        if self.nvml is not None:
+            n = self.nvml
+            bits = [("hw_slowdown", n.nvmlClocksThrottleReasonHwSlowdown), ("hw_thermal_slowdown", n.nvmlClocksThrottleReasonHwThermalSlowdown),
+                    ("sw_thermal_slowdown", n.nvmlClocksThrottleReasonSwThermalSlowdown), ("sw_power_cap", n.nvmlClocksThrottleReasonSwPowerCap)]
+            while not self.stop_flag:
+                try:
+                    sm = int(n.nvmlDeviceGetClockInfo(self.dev, n.NVML_CLOCK_SM))
+                    r = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.dev))
+                    self.rows.append([str(sm), str(self.max_sm)] + ["Active" if r & b else "Not Active" for _, b in bits])
+                except Exception:
+                    pass
+                time.sleep(0.01)
+            return
         q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
         while not self.stop_flag:
@@ -79,7 +104,7 @@ class ClockSampler(threading.Thread):
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": int(self.rows[0][1]) if self.rows[0][1].isdigit() else None,
-                "reasons": reasons, "samples": len(self.rows)}
+                "reasons": reasons, "samples": len(self.rows), "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
 def cpu_reference_run(wl, specs, seq, n_pictures, threads, min_seconds=10.0):
@@ -132,6 +157,9 @@ def main():
     ap.add_argument("--sharding", default="stream", choices=["stream", "picture"],
                     help="N>1: 'stream' = one independent stream per rank (weak scaling, BASELINE configs[4]); "
                          "'picture' = ONE stream, pictures dealt round-robin to the ranks (strong scaling, configs[3])")
+    ap.add_argument("--e2e-chunks", default="4,12,16", help="pictures per chunk of the pipelined end-to-end run "
+                    "(decode order; the last value repeats)")
+    ap.add_argument("--e2e-depth", type=int, default=2, help="chunks in flight before the oldest one is collected")
     ap.add_argument("--cpu-pictures", type=int, default=16, help="pictures in the bounded CPU sample")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="repeat the CPU sample for about this long")
     args = ap.parse_args()
@@ -214,9 +242,34 @@ def main():
         ses.put_pictures(frames_here, [dev.data_ptr() + f * frame_bytes for f in frames_here], W, device=True)
         ses.launch_jobs(jobs)
 
+    # e2e: the look-ahead window is processed in decode order, chunk by chunk, through the queued form
+    # of the C ABI: upload of chunk k+1 / pipeline of chunk k / download of chunk k-1 overlap. Every
+    # frame is uploaded exactly once per step, right before the first chunk that needs it.
+    sizes = [int(x) for x in args.e2e_chunks.split(",") if x]
+    chunks, pos, have = [], 0, set()
+    while pos < len(specs):
+        n = sizes[min(len(chunks), len(sizes) - 1)]
+        part = specs[pos:pos + n]
+        pos += n
+        need = []
+        for _, cur, refs in part:
+            for f in [cur] + list(refs.values()):
+                if f not in have:
+                    have.add(f)
+                    need.append(f)
+        cj, co = ses.make_jobs(part, deep=False)
+        chunks.append((need, [host.data_ptr() + f * frame_bytes for f in need], cj, co))
+    e2e_frames = len(have)
+
     def step_e2e():
-        ses.put_pictures(frames_here, [host.data_ptr() + f * frame_bytes for f in frames_here], W, device=False)
-        ses.run_jobs(jobs)
+        for c, (need, ptrs, cj, _) in enumerate(chunks):
+            if need:
+                ses.put_pictures(need, ptrs, W, device=False)
+            ses.submit_jobs(cj)
+            if c >= args.e2e_depth:
+                ses.collect_jobs(chunks[c - args.e2e_depth][2])
+        for c in range(max(0, len(chunks) - args.e2e_depth), len(chunks)):
+            ses.collect_jobs(chunks[c][2])
 
     def barrier():
         torch.cuda.synchronize()
@@ -293,7 +346,9 @@ def main():
                 "scaling": "strong" if by_picture else "weak",
                 "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": config,
                 "frames_per_s": n_streams * F / (ms_step * 1e-3),
-                "e2e": {"value": e2e_val, "unit": "SB/s", "h2d_bytes_per_step": len(frames_here) * frame_bytes,
+                "e2e": {"value": e2e_val, "unit": "SB/s", "h2d_bytes_per_step": e2e_frames * frame_bytes,
+                        "api": "svtme_put_pictures (pinned host luma) + svtme_submit_pictures / svtme_collect_results (results "
+                               "in host SvtMeOut arrays), chunks of %s pictures, %d in flight" % (args.e2e_chunks, args.e2e_depth),
                         "d2h_bytes_per_step": d2h_bytes,
                         "frames_per_s": n_streams * F / (ms_e2e / args.steps * 1e-3), "ms_per_step": ms_e2e / args.steps},
                 "gpu_launches": int(launches),

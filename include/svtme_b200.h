@@ -218,6 +218,17 @@ int svtme_run_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n);
 /* Device-only part of the batched form (no D2H); svtme_fetch_results completes it. */
 int svtme_launch_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n);
 int svtme_fetch_results(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n);
+/* Queued (pipelined) form of the batched call, for a look-ahead window processed mini-GOP by mini-GOP:
+ * svtme_submit_pictures enqueues the batch and its result download and returns; several batches may be
+ * in flight. svtme_collect_results blocks until the OLDEST submitted batch is complete and fills its
+ * SvtMeOut arrays (jobs/n must describe that batch). Host pictures given to svtme_put_pictures travel on
+ * an upload stream of their own, so with   put(k+1); submit(k+1); collect(k)   the upload of batch k+1,
+ * the pipeline of batch k and the download of batch k-1 overlap. No reference counterpart: the
+ * reference's ME threads consume pictures one at a time from the picture-decision FIFO
+ * (me_process.c:97-124); this is that FIFO at batch granularity. */
+int svtme_submit_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n);
+int svtme_collect_results(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n);
+uint32_t svtme_pending_batches(SvtMeHandle *h);
 int svtme_sync(SvtMeHandle *h);
 /* CUDA-event time (ms) of the ME kernel launches of the last svtme_launch_pictures call, and
  * the number of kernels this library has launched so far. */

@@ -177,6 +177,9 @@ def load_library():
         "svtme_run_pictures": (C.c_int, [vp, P(SvtMeJob), u32]),
         "svtme_launch_pictures": (C.c_int, [vp, P(SvtMeJob), u32]),
         "svtme_fetch_results": (C.c_int, [vp, P(SvtMeJob), u32]),
+        "svtme_submit_pictures": (C.c_int, [vp, P(SvtMeJob), u32]),
+        "svtme_collect_results": (C.c_int, [vp, P(SvtMeJob), u32]),
+        "svtme_pending_batches": (u32, [vp]),
         "svtme_sync": (C.c_int, [vp]),
         "svtme_last_kernel_ms": (C.c_float, [vp]),
         "svtme_launch_count": (u64, []),

@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <deque>
 #include <map>
 #include <mutex>
 #include <vector>
@@ -35,11 +36,16 @@ extern "C" uint32_t svtme_sizeof_out(void) { return (uint32_t)sizeof(SvtMeOut); 
 extern "C" uint32_t svtme_sizeof_job(void) { return (uint32_t)sizeof(SvtMeJob); }
 extern "C" uint32_t svtme_sizeof_derive_input(void) { return (uint32_t)sizeof(SvtMeDeriveInput); }
 
+#define SVTME_LAUNCH_EV_RING 64
 struct Slot {
     DevPyramid pyr;
     uint64_t pic_num;
     bool used;
+    bool build_unread;  // a pyramid build wrote the slot and no launch has read it since
+    uint64_t last_reader; // sequence number of the newest launch that reads this pyramid (an upload into the slot waits for it); 0 = none
 };
+
+static inline size_t up16(size_t v) { return (v + 15) & ~(size_t)15; }
 
 struct OutBuffers { // device + pinned host staging for one batch of jobs
     size_t bytes = 0;
@@ -47,33 +53,82 @@ struct OutBuffers { // device + pinned host staging for one batch of jobs
     uint8_t *host = nullptr;
 };
 
+// One launch of the stage pipeline: its job array, result buffers and events. The handle owns one
+// Batch for the synchronous launch/fetch pair and a pool of them for the queued (pipelined) form,
+// where several launches are in flight and results come back in submission order.
+struct Batch {
+    DevJob *d_jobs = nullptr;
+    DevJob *h_jobs = nullptr; // pinned
+    uint32_t jobs_cap = 0;
+    OutBuffers ob;
+    std::vector<size_t> work_off; // offsets of the per-job work counters
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, jobs_ev = nullptr, done_ev = nullptr;
+    cudaEvent_t ph_ev[SVTME_PHASES] = {};
+    bool jobs_pending = false; // h_jobs may still be on its way to the device
+    uint32_t n = 0;
+    size_t total = 0;
+    uint64_t seq = 0;
+};
+
+#define SVTME_PUT_RING 4
+struct PutRing { // descriptors of one batched pyramid build (device, pinned) + "copied" event
+    SvtmePutItem *d = nullptr, *h = nullptr;
+    uint32_t cap = 0;
+    bool pending = false;
+    cudaEvent_t ev = nullptr;
+};
+
 struct SvtMeHandle {
     int device;
     uint32_t width, height, b64_cols, b64_rows, n_b64;
     cudaStream_t stream;
     bool own_stream;
-    std::vector<size_t> work_off; // offsets of the per-job work counters of the last launch
+    cudaStream_t h2d_stream, d2h_stream; // uploads / result downloads overlap the pipeline of other batches
+    cudaEvent_t h2d_ev, build_ev;
+    cudaEvent_t launch_ev[SVTME_LAUNCH_EV_RING]; // "launch seq is done", indexed seq % ring (Batch objects and their events are recycled)
+    bool build_recorded = false;
     uint8_t *pool; // all planes of all slots
     size_t plane_bytes[3], slot_bytes;
     std::vector<Slot> slots;
     std::map<uint64_t, int> index;
-    uint8_t *stage_host; // pinned upload staging (one luma plane)
-    uint8_t *stage_dev;
-    DevJob *d_jobs;
-    DevJob *h_jobs; // pinned
-    uint32_t jobs_cap;
-    OutBuffers ob;
-    cudaEvent_t ev0, ev1;
-    cudaEvent_t ph_ev[SVTME_PHASES];
+    Batch *sync_batch = nullptr;   // svtme_launch_pictures / svtme_fetch_results
+    Batch *last = nullptr;         // newest launch (measurement getters)
+    std::vector<Batch *> free_batches;
+    std::deque<Batch *> queue;     // submitted, not yet collected (FIFO)
+    uint64_t seq = 0;
     void *d_states = nullptr; // per-b64 scratch of the stage pipeline
-    SvtmePutItem *d_put = nullptr, *h_put = nullptr; // descriptors of the last batched pyramid build (device, pinned)
-    uint32_t put_cap = 0;
-    bool put_pending = false;
-    cudaEvent_t put_ev;
+    PutRing put[SVTME_PUT_RING];
+    uint32_t put_seq = 0;
     size_t states_bytes = 0;
     float last_ms;
     std::mutex mu;
 };
+
+static Batch *batch_new() {
+    Batch *b = new (std::nothrow) Batch();
+    if (!b) return nullptr;
+    cudaError_t e = cudaEventCreate(&b->ev0);
+    if (e == cudaSuccess) e = cudaEventCreate(&b->ev1);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&b->jobs_ev, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&b->done_ev, cudaEventDisableTiming);
+    for (int k = 0; k < SVTME_PHASES && e == cudaSuccess; ++k) e = cudaEventCreate(&b->ph_ev[k]);
+    if (e != cudaSuccess) { delete b; return nullptr; }
+    return b;
+}
+static void batch_free(Batch *b) {
+    if (!b) return;
+    cudaFree(b->d_jobs);
+    cudaFreeHost(b->h_jobs);
+    cudaFree(b->ob.dev);
+    cudaFreeHost(b->ob.host);
+    if (b->ev0) cudaEventDestroy(b->ev0);
+    if (b->ev1) cudaEventDestroy(b->ev1);
+    if (b->jobs_ev) cudaEventDestroy(b->jobs_ev);
+    if (b->done_ev) cudaEventDestroy(b->done_ev);
+    for (int k = 0; k < SVTME_PHASES; ++k)
+        if (b->ph_ev[k]) cudaEventDestroy(b->ph_ev[k]);
+    delete b;
+}
 
 static const int kOrgX[3] = {128, 64, 32}, kOrgY[3] = {72, 32, 16};
 // pads that are actually filled (>= the reference's 72/32/16 and >= every over-read of the kernels)
@@ -112,20 +167,22 @@ extern "C" int svtme_open(int device, uint32_t width, uint32_t height, uint32_t 
         h->slot_bytes += h->plane_bytes[l];
     }
     h->pool = nullptr;
-    h->stage_host = h->stage_dev = nullptr;
-    h->d_jobs = h->h_jobs = nullptr;
-    h->jobs_cap = 0;
     h->last_ms = 0.f;
+    h->h2d_stream = h->d2h_stream = nullptr;
+    h->h2d_ev = h->build_ev = nullptr;
     cudaError_t e = cudaMalloc(&h->pool, h->slot_bytes * capacity);
     if (e != cudaSuccess) { delete h; return fail(SVTME_ERR_NOMEM, "svtme_open: cudaMalloc pyramid pool", e); }
     e = cudaMemset(h->pool, 0, h->slot_bytes * capacity);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
     h->own_stream = true;
-    if (e == cudaSuccess) e = cudaMallocHost(&h->stage_host, (size_t)width * height);
-    if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
-    if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
-    for (int k = 0; k < SVTME_PHASES && e == cudaSuccess; ++k) e = cudaEventCreate(&h->ph_ev[k]);
-    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->put_ev, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->h2d_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->d2h_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->h2d_ev, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->build_ev, cudaEventDisableTiming);
+    for (int k = 0; k < SVTME_PUT_RING && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&h->put[k].ev, cudaEventDisableTiming);
+    for (int k = 0; k < SVTME_LAUNCH_EV_RING; ++k) h->launch_ev[k] = nullptr;
+    for (int k = 0; k < SVTME_LAUNCH_EV_RING && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&h->launch_ev[k], cudaEventDisableTiming);
+    if (e == cudaSuccess && !(h->sync_batch = batch_new())) e = cudaErrorMemoryAllocation;
     if (e != cudaSuccess) { cudaFree(h->pool); delete h; return fail(SVTME_ERR_CUDA, "svtme_open", e); }
     h->slots.resize(capacity);
     for (uint32_t i = 0; i < capacity; ++i) {
@@ -136,6 +193,8 @@ extern "C" int svtme_open(int device, uint32_t width, uint32_t height, uint32_t 
         }
         h->slots[i].used = false;
         h->slots[i].pic_num = 0;
+        h->slots[i].last_reader = 0;
+        h->slots[i].build_unread = false;
     }
     *out = h;
     return SVTME_OK;
@@ -145,19 +204,23 @@ extern "C" void svtme_close(SvtMeHandle *h) {
     if (!h) return;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
+    cudaStreamSynchronize(h->h2d_stream);
+    cudaStreamSynchronize(h->d2h_stream);
     cudaFree(h->pool);
-    cudaFreeHost(h->stage_host);
-    cudaFree(h->d_jobs);
-    cudaFreeHost(h->h_jobs);
-    cudaFree(h->ob.dev);
-    cudaFreeHost(h->ob.host);
-    cudaEventDestroy(h->ev0);
-    cudaEventDestroy(h->ev1);
-    for (int k = 0; k < SVTME_PHASES; ++k) cudaEventDestroy(h->ph_ev[k]);
+    batch_free(h->sync_batch);
+    for (Batch *b : h->free_batches) batch_free(b);
+    for (Batch *b : h->queue) batch_free(b);
     cudaFree(h->d_states);
-    cudaFree(h->d_put);
-    cudaFreeHost(h->h_put);
-    cudaEventDestroy(h->put_ev);
+    for (int k = 0; k < SVTME_PUT_RING; ++k) {
+        cudaFree(h->put[k].d);
+        cudaFreeHost(h->put[k].h);
+        cudaEventDestroy(h->put[k].ev);
+    }
+    cudaEventDestroy(h->h2d_ev);
+    cudaEventDestroy(h->build_ev);
+    for (int k = 0; k < SVTME_LAUNCH_EV_RING; ++k) cudaEventDestroy(h->launch_ev[k]);
+    cudaStreamDestroy(h->h2d_stream);
+    cudaStreamDestroy(h->d2h_stream);
     if (h->own_stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -185,45 +248,70 @@ static int put_batch(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const
     if (n == 0) return SVTME_OK;
     std::lock_guard<std::mutex> lk(h->mu);
     CU(cudaSetDevice(h->device));
-    if (n > h->put_cap) {
-        cudaFree(h->d_put);
-        cudaFreeHost(h->h_put);
-        h->d_put = h->h_put = nullptr;
-        h->put_cap = 0;
-        CU(cudaMalloc(reinterpret_cast<void **>(&h->d_put), sizeof(SvtmePutItem) * n));
-        CU(cudaMallocHost(reinterpret_cast<void **>(&h->h_put), sizeof(SvtmePutItem) * n));
-        h->put_cap = n;
-    } else if (h->put_pending) {
-        CU(cudaEventSynchronize(h->put_ev)); // the previous batch's descriptors have left the pinned buffer
+    PutRing &pr = h->put[h->put_seq++ % SVTME_PUT_RING];
+    if (pr.pending) CU(cudaEventSynchronize(pr.ev)); // this ring entry's descriptors have left the pinned buffer
+    pr.pending = false;
+    if (n > pr.cap) {
+        cudaFree(pr.d);
+        cudaFreeHost(pr.h);
+        pr.d = pr.h = nullptr;
+        pr.cap = 0;
+        CU(cudaMalloc(reinterpret_cast<void **>(&pr.d), up16(sizeof(SvtmePutItem) * n)));
+        CU(cudaMallocHost(reinterpret_cast<void **>(&pr.h), up16(sizeof(SvtmePutItem) * n)));
+        pr.cap = n;
     }
-    SvtmePutItem *items = h->h_put;
+    SvtmePutItem *items = pr.h;
+    // Host pictures travel on the upload stream so that they overlap the ME pipeline of earlier
+    // batches; an upload into a slot must not overtake a launch that still reads the slot's old
+    // content (all launches are in order on the main stream: waiting for the newest reader suffices).
+    uint64_t newest = 0;
+    bool any_copy = false, after_build = false;
     for (uint32_t i = 0; i < n; ++i) {
         if (!luma[i]) return failf(SVTME_ERR_INVALID, "%s: null picture", who);
         const int si = find_slot(h, pic_nums[i], true);
         if (si == -2) return failf(SVTME_ERR_NOMEM, "%s: pyramid ring full (release pictures or raise capacity)", who);
         Slot &s = h->slots[si];
-        const DevPlane &f = s.pyr.lvl[0];
+        if (s.last_reader > newest) newest = s.last_reader;
+        s.last_reader = 0;
+        after_build |= s.build_unread; // re-put before any launch read it: the previous build still writes the slot
+        s.build_unread = true;
         items[i].pyr = s.pyr;
         items[i].src = nullptr;
         items[i].src_stride = 0;
         if (device_src && ((uintptr_t)luma[i] & 15) == 0 && (stride & 15) == 0) {
             items[i].src = luma[i]; // the decimation kernel reads the caller's buffer and fills level 0 itself
             items[i].src_stride = (int)stride;
-        } else {
+        } else
+            any_copy = true;
+    }
+    cudaStream_t cs = device_src ? h->stream : h->h2d_stream;
+    if (any_copy) {
+        // (an event of the ring that has been re-recorded since belongs to a LATER launch: still sufficient)
+        if (!device_src && newest) CU(cudaStreamWaitEvent(cs, h->launch_ev[newest % SVTME_LAUNCH_EV_RING], 0));
+        if (!device_src && after_build && h->build_recorded) CU(cudaStreamWaitEvent(cs, h->build_ev, 0));
+        for (uint32_t i = 0; i < n; ++i) {
+            if (items[i].src) continue;
+            const DevPlane &f = items[i].pyr.lvl[0];
             // a pageable host buffer makes this copy synchronous w.r.t. the host
             CU(cudaMemcpy2DAsync(const_cast<uint8_t *>(f.at(0, 0)), f.stride, luma[i], stride, h->width, h->height,
-                                 device_src ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, h->stream));
+                                 device_src ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, cs));
+        }
+        if (!device_src) {
+            CU(cudaEventRecord(h->h2d_ev, cs));
+            CU(cudaStreamWaitEvent(h->stream, h->h2d_ev, 0));
         }
     }
-    CU(cudaMemcpyAsync(h->d_put, items, sizeof(SvtmePutItem) * n, cudaMemcpyHostToDevice, h->stream));
-    CU(cudaEventRecord(h->put_ev, h->stream));
-    h->put_pending = true;
+    CU(svtme_launch_fetch_from_host(pr.d, items, up16(sizeof(SvtmePutItem) * n), h->stream));
+    CU(cudaEventRecord(pr.ev, h->stream));
+    pr.pending = true;
     SvtmePadSpec ps;
     for (int l = 0; l < 3; ++l) {
         ps.l[l] = kPadL[l]; ps.r[l] = kPadR[l]; ps.t[l] = kPadT[l]; ps.b[l] = kPadB[l];
     }
-    svtme_launch_build_batch(h->d_put, (int)n, items[0].pyr, ps, h->stream);
+    svtme_launch_build_batch(pr.d, (int)n, items[0].pyr, ps, h->stream);
     CU(cudaGetLastError());
+    CU(cudaEventRecord(h->build_ev, h->stream));
+    h->build_recorded = true;
     return SVTME_OK;
 }
 
@@ -260,7 +348,7 @@ extern "C" int svtme_release_picture(SvtMeHandle *h, uint64_t pic_num) {
     std::lock_guard<std::mutex> lk(h->mu);
     auto it = h->index.find(pic_num);
     if (it == h->index.end()) return fail(SVTME_ERR_NOTFOUND, "svtme_release_picture: picture not resident");
-    h->slots[it->second].used = false;
+    h->slots[it->second].used = false; // last_reader stays: the slot's next upload still waits for its readers
     h->index.erase(it);
     return SVTME_OK;
 }
@@ -293,7 +381,9 @@ extern "C" int svtme_get_plane(SvtMeHandle *h, uint64_t pic_num, int level, uint
 extern "C" int svtme_sync(SvtMeHandle *h) {
     if (!h) return fail(SVTME_ERR_INVALID, "svtme_sync: null handle");
     CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->h2d_stream));
     CU(cudaStreamSynchronize(h->stream));
+    CU(cudaStreamSynchronize(h->d2h_stream));
     return SVTME_OK;
 }
 
@@ -351,18 +441,18 @@ static int validate_params(const SvtMeParams &p) {
     return SVTME_OK;
 }
 
-extern "C" int svtme_launch_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n) {
-    if (!h || !jobs || n == 0) return fail(SVTME_ERR_INVALID, "svtme_launch_pictures: bad argument");
-    std::lock_guard<std::mutex> lk(h->mu);
-    CU(cudaSetDevice(h->device));
-    if (n > h->jobs_cap) {
-        cudaFree(h->d_jobs);
-        cudaFreeHost(h->h_jobs);
-        h->d_jobs = h->h_jobs = nullptr;
-        h->jobs_cap = 0;
-        CU(cudaMalloc(&h->d_jobs, sizeof(DevJob) * n));
-        CU(cudaMallocHost(&h->h_jobs, sizeof(DevJob) * n));
-        h->jobs_cap = n;
+// Enqueue the stage pipeline of n pictures on the main stream, results into batch B's device buffer.
+static int launch_into(SvtMeHandle *h, Batch *B, const SvtMeJob *jobs, uint32_t n) {
+    if (B->jobs_pending) CU(cudaEventSynchronize(B->jobs_ev)); // the previous job array has left the pinned buffer
+    B->jobs_pending = false;
+    if (n > B->jobs_cap) {
+        cudaFree(B->d_jobs);
+        cudaFreeHost(B->h_jobs);
+        B->d_jobs = B->h_jobs = nullptr;
+        B->jobs_cap = 0;
+        CU(cudaMalloc(&B->d_jobs, up16(sizeof(DevJob) * n)));
+        CU(cudaMallocHost(&B->h_jobs, up16(sizeof(DevJob) * n)));
+        B->jobs_cap = n;
     }
     size_t total = 0;
     for (uint32_t i = 0; i < n; ++i) {
@@ -370,29 +460,40 @@ extern "C" int svtme_launch_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint3
         if (rc) return rc;
         total += out_layout(h->n_b64, svtme_exported_pu_count(&jobs[i].params), jobs[i].params, wants_deep(jobs[i].out)).end;
     }
-    if (total > h->ob.bytes) {
-        cudaFree(h->ob.dev);
-        cudaFreeHost(h->ob.host);
-        h->ob = OutBuffers();
-        CU(cudaMalloc(&h->ob.dev, total));
-        CU(cudaMallocHost(&h->ob.host, total));
-        h->ob.bytes = total;
+    if (total > B->ob.bytes) {
+        // a queued batch's previous download has been collected before the batch is reused; the
+        // synchronous batch may still be downloading only if the caller never fetched: wait for it
+        CU(cudaStreamSynchronize(h->d2h_stream));
+        CU(cudaStreamSynchronize(h->stream));
+        cudaFree(B->ob.dev);
+        cudaFreeHost(B->ob.host);
+        B->ob = OutBuffers();
+        CU(cudaMalloc(&B->ob.dev, total));
+        CU(cudaMallocHost(&B->ob.host, total));
+        B->ob.bytes = total;
     }
+    B->seq = ++h->seq;
+    B->n = n;
+    B->total = total;
     size_t off = 0;
-    h->work_off.clear();
+    B->work_off.clear();
     for (uint32_t i = 0; i < n; ++i) {
         const SvtMeJob &j = jobs[i];
-        DevJob &d = h->h_jobs[i];
+        DevJob &d = B->h_jobs[i];
         memset(&d, 0, sizeof(d));
         d.prm = j.params;
         const int sc = find_slot(h, j.cur, false);
         if (sc < 0) return fail(SVTME_ERR_NOTFOUND, "svtme_launch_pictures: current picture not resident");
         d.cur = h->slots[sc].pyr;
+        h->slots[sc].last_reader = B->seq;
+        h->slots[sc].build_unread = false;
         for (int li = 0; li < j.params.num_of_list_to_search; ++li)
             for (int ri = 0; ri < j.params.num_of_ref_pic_to_search[li]; ++ri) {
                 const int sr = find_slot(h, j.refs[li][ri], false);
                 if (sr < 0) return fail(SVTME_ERR_NOTFOUND, "svtme_launch_pictures: reference picture not resident");
                 d.ref[li][ri] = h->slots[sr].pyr;
+                h->slots[sr].last_reader = B->seq;
+                h->slots[sr].build_unread = false;
             }
         d.width = (int)h->width;
         d.height = (int)h->height;
@@ -401,7 +502,7 @@ extern "C" int svtme_launch_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint3
         d.n_pu = (int)svtme_exported_pu_count(&j.params);
         const bool deep = wants_deep(j.out);
         const OutLayout L = out_layout(h->n_b64, d.n_pu, j.params, deep);
-        uint8_t *b = h->ob.dev + off;
+        uint8_t *b = B->ob.dev + off;
         d.total = b + L.total;
         d.mv = (uint32_t *)(b + L.mv);
         d.cand = b + L.cand;
@@ -413,16 +514,19 @@ extern "C" int svtme_launch_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint3
             d.best_sad = (uint32_t *)(b + L.bsad); d.best_mv = (uint32_t *)(b + L.bmv);
             d.hme_sc = (int16_t *)(b + L.sc); d.hme_sad = (unsigned long long *)(b + L.hsad); d.do_ref = b + L.doref;
         }
-        h->work_off.push_back(off + L.work);
+        B->work_off.push_back(off + L.work);
         off += L.end;
     }
     // entries the stage never writes (pruned candidates) read as zero, like a fresh MeSbResults
-    CU(cudaMemsetAsync(h->ob.dev, 0, total, h->stream));
-    CU(cudaMemcpyAsync(h->d_jobs, h->h_jobs, sizeof(DevJob) * n, cudaMemcpyHostToDevice, h->stream));
-    CU(cudaEventRecord(h->ev0, h->stream));
+    CU(svtme_launch_zero_fill(B->ob.dev, total, h->stream));
+    CU(svtme_launch_fetch_from_host(B->d_jobs, B->h_jobs, up16(sizeof(DevJob) * n), h->stream));
+    CU(cudaEventRecord(B->jobs_ev, h->stream));
+    B->jobs_pending = true;
+    CU(cudaEventRecord(B->ev0, h->stream));
     {
-        const size_t need = (size_t)n * h->n_b64 * svtme_stage_state_bytes();
+        const size_t need = up16((size_t)n * h->n_b64 * svtme_stage_state_bytes());
         if (need > h->states_bytes) {
+            CU(cudaStreamSynchronize(h->stream)); // earlier launches still use the old scratch
             cudaFree(h->d_states);
             h->d_states = nullptr;
             h->states_bytes = 0;
@@ -441,30 +545,23 @@ extern "C" int svtme_launch_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint3
         flags.hme_l0 |= f.hme_l0; flags.hme_l0_round_b |= f.hme_l0_round_b;
         flags.hme_l1 |= f.hme_l1; flags.hme_l2 |= f.hme_l2;
     }
-    svtme_launch_me_stage(h->d_jobs, (int)n, (int)h->b64_cols, (int)h->b64_rows, h->d_states, h->stream, h->ph_ev, flags);
+    svtme_launch_me_stage(B->d_jobs, (int)n, (int)h->b64_cols, (int)h->b64_rows, h->d_states, h->stream, B->ph_ev, flags);
     CU(cudaGetLastError());
-    CU(cudaEventRecord(h->ev1, h->stream));
+    CU(cudaEventRecord(B->ev1, h->stream));
+    CU(cudaEventRecord(h->launch_ev[B->seq % SVTME_LAUNCH_EV_RING], h->stream));
+    h->last = B;
     return SVTME_OK;
 }
 
-extern "C" int svtme_fetch_results(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n) {
-    if (!h || !jobs || n == 0) return fail(SVTME_ERR_INVALID, "svtme_fetch_results: bad argument");
-    std::lock_guard<std::mutex> lk(h->mu);
-    CU(cudaSetDevice(h->device));
-    size_t total = 0;
-    for (uint32_t i = 0; i < n; ++i)
-        total += out_layout(h->n_b64, svtme_exported_pu_count(&jobs[i].params), jobs[i].params, wants_deep(jobs[i].out)).end;
-    if (total > h->ob.bytes) return fail(SVTME_ERR_INVALID, "svtme_fetch_results: does not match the last launch");
-    CU(cudaMemcpyAsync(h->ob.host, h->ob.dev, total, cudaMemcpyDeviceToHost, h->stream));
-    CU(cudaStreamSynchronize(h->stream));
-    cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+// Scatter batch B's pinned result mirror into the callers' SvtMeOut arrays.
+static int scatter_results(SvtMeHandle *h, const Batch *B, const SvtMeJob *jobs, uint32_t n) {
     size_t off = 0;
     for (uint32_t i = 0; i < n; ++i) {
         const SvtMeJob &j = jobs[i];
         const uint32_t n_pu = svtme_exported_pu_count(&j.params), nb = h->n_b64;
         const bool deep = wants_deep(j.out);
         const OutLayout L = out_layout(nb, n_pu, j.params, deep);
-        const uint8_t *b = h->ob.host + off;
+        const uint8_t *b = B->ob.host + off;
 #define CP(dst, o, bytes) if (j.out.dst) memcpy(j.out.dst, b + (o), (bytes))
         CP(total_me_candidate_index, L.total, (size_t)nb * n_pu);
         CP(me_mv_array, L.mv, (size_t)nb * n_pu * j.params.max_refs * 4);
@@ -483,10 +580,89 @@ extern "C" int svtme_fetch_results(SvtMeHandle *h, const SvtMeJob *jobs, uint32_
     return SVTME_OK;
 }
 
+static size_t results_bytes(const SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n) {
+    size_t total = 0;
+    for (uint32_t i = 0; i < n; ++i)
+        total += out_layout(h->n_b64, svtme_exported_pu_count(&jobs[i].params), jobs[i].params, wants_deep(jobs[i].out)).end;
+    return total;
+}
+
+extern "C" int svtme_launch_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n) {
+    if (!h || !jobs || n == 0) return fail(SVTME_ERR_INVALID, "svtme_launch_pictures: bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(cudaSetDevice(h->device));
+    return launch_into(h, h->sync_batch, jobs, n);
+}
+
+extern "C" int svtme_fetch_results(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n) {
+    if (!h || !jobs || n == 0) return fail(SVTME_ERR_INVALID, "svtme_fetch_results: bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(cudaSetDevice(h->device));
+    Batch *B = h->sync_batch;
+    if (B->n != n || results_bytes(h, jobs, n) != B->total)
+        return fail(SVTME_ERR_INVALID, "svtme_fetch_results: does not match the last svtme_launch_pictures");
+    CU(cudaMemcpyAsync(B->ob.host, B->ob.dev, B->total, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    cudaEventElapsedTime(&h->last_ms, B->ev0, B->ev1);
+    return scatter_results(h, B, jobs, n);
+}
+
 extern "C" int svtme_run_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n) {
     int rc = svtme_launch_pictures(h, jobs, n);
     if (rc) return rc;
     return svtme_fetch_results(h, jobs, n);
+}
+
+// ---- queued form: several batches in flight, results collected in submission order. The download of
+// a batch runs on its own stream as soon as the batch's pipeline is done, i.e. while the next batch
+// computes and the one after that uploads (svtme_put_pictures uses a third stream).
+extern "C" int svtme_submit_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n) {
+    if (!h || !jobs || n == 0) return fail(SVTME_ERR_INVALID, "svtme_submit_pictures: bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(cudaSetDevice(h->device));
+    Batch *B;
+    if (!h->free_batches.empty()) {
+        B = h->free_batches.back();
+        h->free_batches.pop_back();
+    } else if (!(B = batch_new()))
+        return fail(SVTME_ERR_NOMEM, "svtme_submit_pictures: batch allocation");
+    int rc = launch_into(h, B, jobs, n);
+    if (rc) {
+        h->free_batches.push_back(B);
+        return rc;
+    }
+    CU(cudaStreamWaitEvent(h->d2h_stream, B->ev1, 0));
+    CU(cudaMemcpyAsync(B->ob.host, B->ob.dev, B->total, cudaMemcpyDeviceToHost, h->d2h_stream));
+    CU(cudaEventRecord(B->done_ev, h->d2h_stream));
+    h->queue.push_back(B);
+    return SVTME_OK;
+}
+
+extern "C" int svtme_collect_results(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n) {
+    if (!h || !jobs || n == 0) return fail(SVTME_ERR_INVALID, "svtme_collect_results: bad argument");
+    Batch *B;
+    {
+        std::lock_guard<std::mutex> lk(h->mu);
+        CU(cudaSetDevice(h->device));
+        if (h->queue.empty()) return fail(SVTME_ERR_NOTFOUND, "svtme_collect_results: nothing submitted");
+        B = h->queue.front();
+        if (B->n != n || results_bytes(h, jobs, n) != B->total)
+            return fail(SVTME_ERR_INVALID, "svtme_collect_results: jobs do not match the oldest submitted batch");
+        h->queue.pop_front();
+    }
+    // wait and scatter outside the lock: other threads keep submitting
+    cudaError_t e = cudaEventSynchronize(B->done_ev);
+    int rc = e == cudaSuccess ? scatter_results(h, B, jobs, n) : fail(SVTME_ERR_CUDA, "svtme_collect_results", e);
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (e == cudaSuccess) cudaEventElapsedTime(&h->last_ms, B->ev0, B->ev1);
+    h->free_batches.push_back(B);
+    return rc;
+}
+
+extern "C" uint32_t svtme_pending_batches(SvtMeHandle *h) {
+    if (!h) return 0;
+    std::lock_guard<std::mutex> lk(h->mu);
+    return (uint32_t)h->queue.size();
 }
 
 extern "C" int svtme_run_picture(SvtMeHandle *h, const SvtMeParams *params, uint64_t cur,
@@ -529,13 +705,14 @@ extern "C" int svtme_last_work_ops(SvtMeHandle *h, uint64_t *ops) {
     CU(cudaSetDevice(h->device));
     CU(cudaStreamSynchronize(h->stream));
     uint64_t sum = 0;
-    for (size_t o : h->work_off) {
+    if (!h->last) return fail(SVTME_ERR_NOTFOUND, "svtme_last_work_ops: nothing launched");
+    for (size_t o : h->last->work_off) {
         unsigned long long v[SVTME_PHASES];
-        CU(cudaMemcpy(v, h->ob.dev + o, sizeof(v), cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(v, h->last->ob.dev + o, sizeof(v), cudaMemcpyDeviceToHost));
         for (int k = 0; k < SVTME_PHASES; ++k) sum += v[k];
     }
     *ops = sum;
-    cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1);
+    cudaEventElapsedTime(&h->last_ms, h->last->ev0, h->last->ev1);
     return SVTME_OK;
 }
 
@@ -547,9 +724,10 @@ extern "C" int svtme_last_phase_work(SvtMeHandle *h, uint64_t *ops, uint32_t n) 
     CU(cudaStreamSynchronize(h->stream));
     if (n > SVTME_PHASES) n = SVTME_PHASES;
     for (uint32_t k = 0; k < n; ++k) ops[k] = 0;
-    for (size_t o : h->work_off) {
+    if (!h->last) return fail(SVTME_ERR_NOTFOUND, "svtme_last_phase_work: nothing launched");
+    for (size_t o : h->last->work_off) {
         unsigned long long v[SVTME_PHASES];
-        CU(cudaMemcpy(v, h->ob.dev + o, sizeof(v), cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(v, h->last->ob.dev + o, sizeof(v), cudaMemcpyDeviceToHost));
         for (uint32_t k = 0; k < n; ++k) ops[k] += v[k];
     }
     return SVTME_OK;
@@ -563,9 +741,10 @@ extern "C" int svtme_last_phase_ms(SvtMeHandle *h, float *ms, uint32_t n) {
     CU(cudaSetDevice(h->device));
     CU(cudaStreamSynchronize(h->stream));
     if (n > SVTME_PHASES) n = SVTME_PHASES;
+    if (!h->last) return fail(SVTME_ERR_NOTFOUND, "svtme_last_phase_ms: nothing launched");
     for (uint32_t k = 0; k < n; ++k) {
         ms[k] = 0.f;
-        CU(cudaEventElapsedTime(&ms[k], k ? h->ph_ev[k - 1] : h->ev0, h->ph_ev[k]));
+        CU(cudaEventElapsedTime(&ms[k], k ? h->last->ph_ev[k - 1] : h->last->ev0, h->last->ph_ev[k]));
     }
     return SVTME_OK;
 }

@@ -76,6 +76,9 @@ struct SvtmePadSpec {
 };
 void svtme_launch_build_batch(const SvtmePutItem *d_items, int n, const DevPyramid &geom, const SvtmePadSpec &ps,
                               cudaStream_t st);
+// transfers of the main stream that must not queue on a copy engine (svtme_pyramid.cu)
+cudaError_t svtme_launch_fetch_from_host(void *dst, const void *src_pinned, size_t bytes, cudaStream_t st);
+cudaError_t svtme_launch_zero_fill(void *dst, size_t bytes, cudaStream_t st);
 // stage kernel (svtme_stage.cu)
 // d_states: n_jobs * b64_per_job * svtme_stage_state_bytes() bytes of scratch; ev: SVTME_PHASES events or null
 // What the pictures of a batch need, so that launches no picture uses are skipped.

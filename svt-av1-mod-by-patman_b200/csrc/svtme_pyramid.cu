@@ -291,3 +291,39 @@ void svtme_launch_downsample_generic(const uint8_t *in, int is, int w, int h, ui
     downsample_generic_kernel<<<grd, blk, 0, st>>>(in, is, w, h, out, os, step);
     ++g_svtme_launches;
 }
+
+// ---- small transfers without the copy engines
+// The main stream carries only kernels: its job / descriptor arrays are READ from pinned host memory by
+// a kernel, and its buffers are cleared by a kernel. A cudaMemcpyAsync / cudaMemsetAsync here would
+// queue on a copy engine behind the bulk picture uploads of the upload stream (measured: the first
+// pipeline of a look-ahead window then starts only after ALL queued uploads, not after its own).
+__global__ void __launch_bounds__(256) fetch_words_kernel(uint4 *__restrict__ dst, const uint4 *__restrict__ src_host, size_t n16) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x) dst[i] = src_host[i];
+}
+__global__ void __launch_bounds__(256) zero_fill_kernel(uint4 *__restrict__ dst, size_t n16) {
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x) dst[i] = z;
+}
+
+// bytes: multiple of 16; dst 16-byte aligned device memory; src: pinned host memory (its device alias is resolved here)
+cudaError_t svtme_launch_fetch_from_host(void *dst, const void *src_pinned, size_t bytes, cudaStream_t st) {
+    void *alias = nullptr;
+    cudaError_t e = cudaHostGetDevicePointer(&alias, const_cast<void *>(src_pinned), 0);
+    if (e != cudaSuccess) return e;
+    const size_t n16 = bytes / 16;
+    if (!n16) return cudaSuccess;
+    const unsigned blocks = (unsigned)((n16 + 255) / 256 < 148 ? (n16 + 255) / 256 : 148);
+    fetch_words_kernel<<<blocks, 256, 0, st>>>(reinterpret_cast<uint4 *>(dst), reinterpret_cast<const uint4 *>(alias), n16);
+    ++g_svtme_launches;
+    return cudaGetLastError();
+}
+
+cudaError_t svtme_launch_zero_fill(void *dst, size_t bytes, cudaStream_t st) {
+    const size_t n16 = bytes / 16;
+    if (!n16) return cudaSuccess;
+    const size_t want = (n16 + 255) / 256;
+    const unsigned blocks = (unsigned)(want < 148 * 8 ? want : 148 * 8);
+    zero_fill_kernel<<<blocks, 256, 0, st>>>(reinterpret_cast<uint4 *>(dst), n16);
+    ++g_svtme_launches;
+    return cudaGetLastError();
+}

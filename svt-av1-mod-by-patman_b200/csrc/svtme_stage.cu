@@ -567,7 +567,7 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
         if (ev) cudaEventRecord(ev[slot], st);
         ++slot;
     };
-    cudaMemsetAsync(d_states, 0, (size_t)N * sizeof(StageState), st);
+    svtme_launch_zero_fill(d_states, ((size_t)N * sizeof(StageState) + 15) & ~(size_t)15, st); // (the allocation is rounded up likewise)
     mark(); // 0: state clear
     int launches = 0;
     // scalar steps always run (they also carry the bookkeeping of disabled phases); engine launches
@@ -612,7 +612,7 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
     mark(); // 6: integer search
     finish_kernel<<<N, 128, sizeof(FinSmem), st>>>(a);
     mark(); // 7: candidates + statistics
-    g_svtme_launches += 8 + 2 + 1 + launches;
+    g_svtme_launches += 8 + 2 + 1 + launches; // (the state clear counts itself)
 }
 
 // ---------------------------------------------------------------- kernel-test entry points

@@ -111,6 +111,17 @@ class MeSession:
     def fetch_jobs(self, jobs):
         _check(self.lib.svtme_fetch_results(self.h, jobs, len(jobs)), self.lib)
 
+    def submit_jobs(self, jobs):
+        """Queued form: enqueue the batch and its result download; several batches may be in flight."""
+        _check(self.lib.svtme_submit_pictures(self.h, jobs, len(jobs)), self.lib)
+
+    def collect_jobs(self, jobs):
+        """Block until the OLDEST submitted batch is complete; fills the arrays made by make_jobs."""
+        _check(self.lib.svtme_collect_results(self.h, jobs, len(jobs)), self.lib)
+
+    def pending_batches(self):
+        return int(self.lib.svtme_pending_batches(self.h))
+
     def sync(self):
         _check(self.lib.svtme_sync(self.h), self.lib)
 

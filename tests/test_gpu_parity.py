@@ -155,6 +155,49 @@ def test_batched_jobs_equal_single_jobs():
                 assert np.array_equal(single[k], batch[k]), (cur, k)
 
 
+def test_queued_batches_equal_synchronous_runs_and_reuploads_are_ordered():
+    """svtme_submit_pictures / svtme_collect_results: several batches in flight return, in submission
+    order, exactly what the synchronous call returns; a slot re-uploaded with DIFFERENT content while
+    earlier batches that read the old content are still queued must not disturb them (the upload stream
+    waits for the slot's readers)."""
+    W, H = 320, 192
+    seqs = [U.synth_sequence(W, H, 6, seed=s) for s in (11, 12, 13)]
+    d = U.derive_input(8, W, H, temporal_layer_index=1, ref_list0_count_try=1, ref_list1_count_try=1)
+    specs = []
+    for cur in (1, 2, 3, 4):
+        p = U.finish_params(derive(None, d), d, cur, {(0, 0): cur - 1, (1, 0): cur + 1})
+        specs.append((p, cur, {(0, 0): cur - 1, (1, 0): cur + 1}))
+    import torch
+    hosts = [torch.from_numpy(s).pin_memory() for s in seqs]  # pinned: the uploads are truly asynchronous
+    with me.MeSession(0, W, H, capacity=6) as ses:
+        want = []
+        for seq in seqs:
+            for n in range(6):
+                ses.put_picture(n, seq[n])
+            jobs, outs = ses.make_jobs(specs, deep=True)
+            ses.run_jobs(jobs)
+            want.append(outs)
+        queued = []
+        for rnd, hst in enumerate(hosts):  # three rounds back to back, same slots, different pictures
+            ses.put_pictures(list(range(6)), [hst.data_ptr() + n * W * H for n in range(6)], W)
+            a, oa = ses.make_jobs(specs[:2], deep=True)
+            b, ob = ses.make_jobs(specs[2:], deep=True)
+            ses.submit_jobs(a)
+            ses.submit_jobs(b)
+            queued += [(a, oa, rnd, 0), (b, ob, rnd, 2)]
+        assert ses.pending_batches() == 6
+        with pytest.raises(me.SvtMeError):
+            ses.collect_jobs(queued[1][0] if len(queued[1][0]) != len(queued[0][0]) else ses.make_jobs(specs[:1])[0])
+        for jobs, outs, rnd, first in queued:
+            ses.collect_jobs(jobs)
+            for i, o in enumerate(outs):
+                for k in o:
+                    assert np.array_equal(o[k], want[rnd][first + i][k]), (rnd, first + i, k)
+        assert ses.pending_batches() == 0
+        with pytest.raises(me.SvtMeError):
+            ses.collect_jobs(queued[0][0])  # nothing submitted
+
+
 def test_error_behaviour():
     lib = U.product_lib()
     h = C.c_void_p()

@@ -537,10 +537,12 @@ static int launch_into(SvtMeHandle *h, Batch *B, const SvtMeJob *jobs, uint32_t 
     SvtmeStageFlags flags = {};
     flags.small_areas = true;
     flags.prehme_strip = true;
+    flags.refine_small = getenv("SVTME_NO_REFINE_KERNEL") == nullptr; // (tests exercise both paths)
     for (uint32_t i = 0; i < n; ++i) {
         flags.prehme_strip = flags.prehme_strip && jobs[i].params.hme_search_method != 1;
         const SvtmeStageFlags f = svtme_stage_flags(jobs[i].params);
         flags.small_areas = flags.small_areas && areas_are_small(jobs[i].params);
+        flags.refine_small = flags.refine_small && f.refine_small;
         flags.zz |= f.zz; flags.prehme |= f.prehme; flags.prehme_l1_round |= f.prehme_l1_round;
         flags.hme_l0 |= f.hme_l0; flags.hme_l0_round_b |= f.hme_l0_round_b;
         flags.hme_l1 |= f.hme_l1; flags.hme_l2 |= f.hme_l2;

@@ -158,6 +158,141 @@ __global__ void __launch_bounds__(SVTME_HME_THREADS, SVTME_HME_CTAS_PER_SM) engi
     }
 }
 
+// ---------------------------------------------------------------- HME level 1 / 2 refinement, small windows
+// hme_level_1 / hme_level_2 (:923-1113) refine each quadrant centre inside a window of a few dozen
+// positions (8x3 at every preset but M0) with a LARGE block (32x32 of the quarter picture, 64x64 of the
+// full one), up to 32 windows per b64. Here ONE WARP owns one window, no CTA barrier anywhere:
+//   staging : the rows the window touches go to the warp's own shared-memory tile as RAW aligned 16-byte
+//             chunks (LDG.128 -> STS.128, every reference row read once); the window's misalignment is
+//             applied by the readers. (Reading the rows straight through L1 was measured 4x slower:
+//             every load instruction touched 8 cache lines.)
+//   search  : lane = (rq = lane >> 2: block rows rq, rq+8, ...; c = lane & 3: byte phase), positions
+//             x = c and c + 4 of an 8-wide x-tile, REFINE_YT consecutive y per pass. Per (block row, y)
+//             a lane reads BWW+2 words of the staged row, shifts them to its byte phase and feeds
+//             2*BWW VABSDIFF4; the source row (16-byte aligned in the plane) is loaded once per block
+//             row. Row pitch + a 16-byte skew every 8 rows keep the 8 row groups on distinct banks.
+//   argmin  : row-group partial sums meet in a 3-step xor butterfly; the winner is the minimum over
+//             keys sad << 32 | y << 16 | x (first strict minimum in raster order, compute_sad_c.c:73-95).
+// Any sa_w / sa_h works (tiles of 8 x REFINE_YT positions); the host selects this kernel only when
+// every picture of the batch has small refinement windows.
+#define REFINE_YT 3
+template <int BWW> // block width in 32-bit words: 8 = HME level 1, 16 = level 2
+struct RefineCfg {
+    static constexpr int NCH = BWW == 8 ? 4 : 6;                  // 16-byte chunks staged per row: 15 + 8 + 4*BWW + 3 bytes
+    static constexpr int PITCH = BWW == 8 ? 80 : 112;             // bytes
+    static constexpr int ROWS = (BWW == 8 ? 32 : 64) + REFINE_YT; // >= (nrows-1)*row_step + REFINE_YT for both row steps
+    static constexpr int BYTES = ROWS * PITCH + 32;               // + skew + slack for the (shifted-out) last word
+};
+__device__ __forceinline__ int refine_rowoff(int R, int pitch) { return R * pitch + ((R >> 3) & 1) * 16; }
+
+template <int BWW, bool FULLW>
+__device__ __forceinline__ void refine_rows(const uint8_t *__restrict__ src0, int src_pitch, const uint8_t *tile, int boff,
+                                            int rs, int nrows, int kw, int rq, int ny, uint32_t (&acc)[REFINE_YT][2]) {
+    constexpr int PITCH = RefineCfg<BWW>::PITCH;
+    const uint32_t shb = (uint32_t)(boff & 3) * 8;
+    const uint8_t *col = tile + (boff & ~3);
+    for (int r = rq; r < nrows; r += 8) {
+        uint32_t sw[BWW];
+        const uint4 *sp = reinterpret_cast<const uint4 *>(src0 + (size_t)r * src_pitch);
+#pragma unroll
+        for (int k = 0; k < BWW / 4; ++k) {
+            const uint4 v = __ldg(sp + k);
+            sw[4 * k] = v.x; sw[4 * k + 1] = v.y; sw[4 * k + 2] = v.z; sw[4 * k + 3] = v.w;
+        }
+#pragma unroll
+        for (int ty = 0; ty < REFINE_YT; ++ty) {
+            if (ty < ny) {
+                const uint32_t *rp = reinterpret_cast<const uint32_t *>(col + refine_rowoff(ty + r * rs, PITCH));
+                uint32_t t[BWW + 2];
+#pragma unroll
+                for (int k = 0; k < BWW + 2; ++k) t[k] = rp[k];
+#pragma unroll
+                for (int k = 0; k < BWW + 1; ++k) t[k] = __funnelshift_r(t[k], t[k + 1], shb);
+#pragma unroll
+                for (int k = 0; k < BWW; ++k) {
+                    if (FULLW || k < kw) {
+                        acc[ty][0] = vsad4(sw[k], t[k], acc[ty][0]);
+                        acc[ty][1] = vsad4(sw[k], t[k + 1], acc[ty][1]);
+                    }
+                }
+            }
+        }
+    }
+}
+
+template <int BWW>
+__global__ void __launch_bounds__(128) refine_kernel(WideArgs a, int sh, int wslot) {
+    using Cfg = RefineCfg<BWW>;
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const int gid = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    StageState *s = &a.st[gid];
+    const int n = s->n_jobs;
+    if (n == 0) return;
+    uint8_t *tile = smem_raw + warp * Cfg::BYTES;
+    const DevJob &J = a.jobs[gid / a.b64_per_job];
+    const bool full_sad = J.prm.hme_search_method == 1;
+    const int rs = full_sad ? 1 : 2;
+    const DevPlane &cp = J.cur.lvl[sh]; // sh = 1: quarter picture (HME level 1), 0: full picture (level 2)
+    const int bw = s->b64_w >> sh, kw = bw >> 2;
+    const int nrows = full_sad ? (s->b64_h >> sh) : (s->b64_h >> (sh + 1));
+    const uint8_t *src0 = cp.at(s->org_x >> sh, s->org_y >> sh);
+    const int src_pitch = cp.stride * rs;
+    const int c = lane & 3, rq = lane >> 2;
+    unsigned long long work = 0;
+    for (int j = warp; j < n; j += 4) {
+        const uint8_t *ref = s->jobs[j].ref;
+        const int stride = s->jobs[j].stride, sa_w = s->jobs[j].sa_w, sa_h = s->jobs[j].sa_h, skip_even = s->jobs[j].skip_even;
+        if (sa_w <= 0 || sa_h <= 0) continue;
+        unsigned long long best = ~0ULL;
+        for (int y0 = 0; y0 < sa_h; y0 += REFINE_YT) {
+            const int ny = min(REFINE_YT, sa_h - y0);
+            const int rows = (nrows - 1) * rs + ny;
+            for (int x0 = 0; x0 < sa_w; x0 += 8) {
+                const uintptr_t a0 = reinterpret_cast<uintptr_t>(ref + (size_t)y0 * stride + x0);
+                const uint8_t *g = reinterpret_cast<const uint8_t *>(a0 & ~(uintptr_t)15);
+                __syncwarp(); // the previous tile's readers are done
+                for (int u = lane; u < rows * Cfg::NCH; u += 32) {
+                    const int R = u / Cfg::NCH, ch = u - R * Cfg::NCH;
+                    *reinterpret_cast<uint4 *>(tile + refine_rowoff(R, Cfg::PITCH) + 16 * ch) =
+                        __ldg(reinterpret_cast<const uint4 *>(g + (size_t)R * stride) + ch);
+                }
+                __syncwarp();
+                uint32_t acc[REFINE_YT][2];
+#pragma unroll
+                for (int ty = 0; ty < REFINE_YT; ++ty) acc[ty][0] = acc[ty][1] = 0;
+                const int boff = (int)(a0 & 15) + c;
+                if (kw == BWW)
+                    refine_rows<BWW, true>(src0, src_pitch, tile, boff, rs, nrows, kw, rq, ny, acc);
+                else
+                    refine_rows<BWW, false>(src0, src_pitch, tile, boff, rs, nrows, kw, rq, ny, acc);
+#pragma unroll
+                for (int ty = 0; ty < REFINE_YT; ++ty)
+#pragma unroll
+                    for (int xh = 0; xh < 2; ++xh) {
+                        uint32_t v = acc[ty][xh];
+                        v += __shfl_xor_sync(0xffffffffu, v, 4);
+                        v += __shfl_xor_sync(0xffffffffu, v, 8);
+                        v += __shfl_xor_sync(0xffffffffu, v, 16);
+                        const int y = y0 + ty, x = x0 + c + 4 * xh;
+                        const bool ok = ty < ny && x < sa_w && !(skip_even && !(y & 1));
+                        const unsigned long long k = ((unsigned long long)v << 32) | ((unsigned)y << 16) | (unsigned)x;
+                        best = (ok && k < best) ? k : best;
+                    }
+            }
+        }
+#pragma unroll
+        for (int o = 1; o <= 2; o <<= 1) {
+            const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+            best = other < best ? other : best;
+        }
+        if (lane == 0) {
+            if (best < HME_KEY_INIT) s->jobs[j].key = best;
+            work += (unsigned long long)sa_w * (skip_even ? sa_h / 2 : sa_h) * bw * nrows;
+        }
+    }
+    if (lane == 0 && work && J.work_ops) atomicAdd(J.work_ops + wslot, work);
+}
+
 // ---------------------------------------------------------------- pre-HME in strip mode
 // The two pre-HME windows of a b64 (prehme_core :1641) are a tall 8-wide column and a flat, wide row
 // around the block; the b64s of one column (one row) of the picture therefore search almost the same
@@ -541,6 +676,9 @@ SvtmeStageFlags svtme_stage_flags(const SvtMeParams &p) {
     f.hme_l0_round_b = f.hme_l0 && l0_dependent(p);
     f.hme_l1 = p.enable_hme_flag && p.enable_hme_level1_flag;
     f.hme_l2 = p.enable_hme_flag && p.enable_hme_level2_flag;
+    // refinement windows of at most 64 positions (8x3 everywhere but M0) take the warp-per-window kernel
+    f.refine_small = (!f.hme_l1 || ((p.hme_l1_sa.width + 7u) & ~7u) * p.hme_l1_sa.height <= 64u) &&
+        (!f.hme_l2 || ((p.hme_l2_sa.width + 7u) & ~7u) * p.hme_l2_sa.height <= 64u);
     return f;
 }
 
@@ -596,10 +734,22 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
     if (f.hme_l0_round_b) engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 3), ++launches;
     scalar_kernel<S_L0B><<<sg, 128, 0, st>>>(a);
     mark(); // 3: HME level 0
-    if (f.hme_l1) engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 2, 4), ++launches;
+    if (f.hme_l1) {
+        if (f.refine_small)
+            refine_kernel<8><<<N, 128, 4 * RefineCfg<8>::BYTES, st>>>(a, 1, 4);
+        else
+            engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 2, 4);
+        ++launches;
+    }
     scalar_kernel<S_L1><<<sg, 128, 0, st>>>(a);
     mark(); // 4: HME level 1
-    if (f.hme_l2) engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 3, 5), ++launches;
+    if (f.hme_l2) {
+        if (f.refine_small)
+            refine_kernel<16><<<N, 128, 4 * RefineCfg<16>::BYTES, st>>>(a, 0, 5);
+        else
+            engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 3, 5);
+        ++launches;
+    }
     scalar_kernel<S_L2><<<sg, 128, 0, st>>>(a);
     mark(); // 5: HME level 2 + search centre + HME pruning
     if (f.small_areas) {

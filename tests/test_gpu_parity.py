@@ -46,6 +46,20 @@ def test_stage_matches_golden_and_oracle(case):
         assert np.array_equal(orc[k], got[k]), "oracle " + k
 
 
+@pytest.mark.parametrize("case", [c for c in G.STAGE_CASES if c[3] in (4, 8)], ids=lambda c: c[0])
+def test_stage_generic_engine_for_refinement_rounds(case, monkeypatch):
+    """HME level 1 / 2 rounds through the generic staged engine instead of the warp-per-window
+    refinement kernel (the path presets with wide refinement windows take): same golden result."""
+    monkeypatch.setenv("SVTME_NO_REFINE_KERNEL", "1")
+    name, W, H, preset, tl, refs, cur, kw = case
+    seq, d = G.stage_case(*case)
+    p = U.finish_params(derive(None, d), d, cur, refs)
+    got = gpu_stage(seq, p, cur, refs, W, H)
+    want = np.load(os.path.join(GOLD, "stage_%s.npz" % name))
+    for k in want.files:
+        assert np.array_equal(want[k], got[k]), "golden " + k
+
+
 def test_pyramid_matches_golden_and_oracle():
     seq = U.synth_sequence(328, 200, 1, seed=5)
     want = np.load(os.path.join(GOLD, "pyramid.npz"))

@@ -543,6 +543,8 @@ static int launch_into(SvtMeHandle *h, Batch *B, const SvtMeJob *jobs, uint32_t 
         const SvtmeStageFlags f = svtme_stage_flags(jobs[i].params);
         flags.small_areas = flags.small_areas && areas_are_small(jobs[i].params);
         flags.refine_small = flags.refine_small && f.refine_small;
+        flags.int_dependent |= f.int_dependent;
+        for (int li = 0; li < 2; ++li) flags.max_refs[li] = f.max_refs[li] > flags.max_refs[li] ? f.max_refs[li] : flags.max_refs[li];
         flags.zz |= f.zz; flags.prehme |= f.prehme; flags.prehme_l1_round |= f.prehme_l1_round;
         flags.hme_l0 |= f.hme_l0; flags.hme_l0_round_b |= f.hme_l0_round_b;
         flags.hme_l1 |= f.hme_l1; flags.hme_l2 |= f.hme_l2;

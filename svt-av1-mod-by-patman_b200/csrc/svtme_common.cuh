@@ -85,6 +85,8 @@ cudaError_t svtme_launch_zero_fill(void *dst, size_t bytes, cudaStream_t st);
 struct SvtmeStageFlags {
     bool small_areas;     // every full-pel search area is at most svtme_fp_direct_max() positions
     bool zz, prehme, prehme_l1_round, hme_l0, hme_l0_round_b, hme_l1, hme_l2;
+    bool int_dependent;   // some picture derives the other references' full-pel areas from (list 0, ref 0)'s result
+    int max_refs[2];      // references searched per list, maximum over the batch
     bool refine_small;    // HME level 1 / 2 windows are small in every picture: one warp per window, no staging
     bool prehme_strip;    // pre-HME runs in strip mode (one CTA per b64 column / row and reference): every
                           // picture of the batch uses the sub-sampled SAD (16x8 source block = one sub-block)

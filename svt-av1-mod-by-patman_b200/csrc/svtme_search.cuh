@@ -38,6 +38,9 @@
 #define SVTME_HME_CTAS_PER_SM 4
 #endif
 #define SVTME_FP_YL (SVTME_THREADS / 64) // row lanes of the full-pel engine
+#ifndef SVTME_FP_SMALL_ARENA_BYTES
+#define SVTME_FP_SMALL_ARENA_BYTES (10 * 1024) // raw tile of a small full-pel window: up to 78 rows x 128 bytes
+#endif
 #ifndef SVTME_FP_DIRECT_MAX
 #define SVTME_FP_DIRECT_MAX 96 // search areas up to this many positions skip the shared-memory staging
 #endif
@@ -462,13 +465,16 @@ __device__ __noinline__ void hme_points(const HBlk &blk, HJob *jobs, int n) {
         const size_t rstep = (size_t)blk.row_step * job.stride;
         if (blk.bw == 64 && blk.nrows <= 32 &&
             ((reinterpret_cast<uintptr_t>(blk.src) | reinterpret_cast<uintptr_t>(job.ref) | (uintptr_t)blk.src_pitch | rstep) & 15) == 0) {
-            // aligned 64-wide block (zz-SAD): one lane per row, four 16-byte loads from each side
-            if (lane < blk.nrows) {
-                const uint4 *sp = reinterpret_cast<const uint4 *>(blk.src + (size_t)lane * blk.src_pitch);
-                const uint4 *rp = reinterpret_cast<const uint4 *>(job.ref + (size_t)lane * rstep);
+            // aligned 64-wide block (zz-SAD): four lanes per row (one 16-byte chunk each), eight rows per
+            // load instruction -> every cache line is touched once (one lane per row touched 32 lines
+            // per instruction and was bound by the L1 tag rate)
+            const int ch = lane & 3;
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const uint4 a = sp[k], b = __ldg(rp + k);
+            for (int i = 0; i < 4; ++i) {
+                const int r = (lane >> 2) + 8 * i;
+                if (r < blk.nrows) {
+                    const uint4 a = *(reinterpret_cast<const uint4 *>(blk.src + (size_t)r * blk.src_pitch) + ch);
+                    const uint4 b = __ldg(reinterpret_cast<const uint4 *>(job.ref + (size_t)r * rstep) + ch);
                     acc = vsad4(a.x, b.x, acc);
                     acc = vsad4(a.y, b.y, acc);
                     acc = vsad4(a.z, b.z, acc);
@@ -845,10 +851,21 @@ __device__ __forceinline__ void fp_butterfly(uint32_t (&v)[G], int b, int &joff3
     v64 = v[0];
 }
 
-// DIRECT: no staging — `arena` is the GLOBAL address of the tile's top-left reference pixel and `m` the
-// plane stride; each row's words are read with scalar loads (L1-resident for the small windows this
-// mode is used for) and shifted to the thread's byte phase in registers.
-template <int G, bool DIRECT>
+// MODE FP_COPIES: the window was staged as four byte-phase copies (stage_window4), aligned vector loads.
+// MODE FP_RAW   : small windows — the rows were staged as RAW aligned 16-byte chunks (fp_stage_raw): `arena`
+//                 is the tile in shared memory, `m` its row pitch in bytes and `copy_bytes` the byte offset
+//                 of the window inside the first chunk; each row's words are read with scalar LDS and shifted
+//                 to the thread's byte phase in registers. (Reading the rows straight from global memory,
+//                 MODE FP_DIRECT, made every load touch ~8 cache lines: ncu showed l1tex at 85 % of peak.)
+// MODE FP_DIRECT: no staging — `arena` is the GLOBAL address of the tile's top-left reference pixel and `m`
+//                 the plane stride. Fallback only (a window that fits neither arena).
+#define FP_COPIES 0
+#define FP_DIRECT 1
+#define FP_RAW 2
+// 64 bytes of skew per 16 rows (cumulative: rows never overlap): the four block rows of a lane group sit 16 rows
+// apart, a multiple of 128 bytes for every pitch, and would share banks
+__device__ __forceinline__ int fp_raw_rowoff(int R, int pitch) { return R * pitch + (R >> 4) * 64; }
+template <int G, int MODE>
 __device__ __noinline__ void fp_tile(const uint8_t *src64, const uint8_t *arena, int copy_bytes, int m, int tw, int th,
                                         bool sub_sad, FpTables *tab) {
     const int tid = threadIdx.x, b = tid & 15, c = (tid >> 4) & 3, yl = tid >> 6;
@@ -877,7 +894,7 @@ __device__ __noinline__ void fp_tile(const uint8_t *src64, const uint8_t *arena,
                 for (int r = 0; r < 8; ++r) {
                     const int R = y + 16 * by + 2 * r + par;
                     uint32_t w[G + 4];
-                    if (DIRECT) {
+                    if (MODE == FP_DIRECT) {
                         const uintptr_t ai = reinterpret_cast<uintptr_t>(arena + (size_t)R * m + 4 * q0 + c);
                         const uint32_t *al = reinterpret_cast<const uint32_t *>(ai & ~(uintptr_t)3);
                         const uint32_t sh = (uint32_t)(ai & 3) * 8;
@@ -885,6 +902,15 @@ __device__ __noinline__ void fp_tile(const uint8_t *src64, const uint8_t *arena,
 #pragma unroll
                         for (int k = 0; k < G + 4; ++k) t[k] = __ldg(al + k);
                         t[G + 4] = sh ? __ldg(al + G + 4) : 0u;
+#pragma unroll
+                        for (int k = 0; k < G + 4; ++k) w[k] = __funnelshift_r(t[k], t[k + 1], sh);
+                    } else if (MODE == FP_RAW) {
+                        const int off = copy_bytes + 4 * q0 + c; // byte offset inside the staged row
+                        const uint32_t *al = reinterpret_cast<const uint32_t *>(arena + fp_raw_rowoff(R, m) + (off & ~3));
+                        const uint32_t sh = (uint32_t)(off & 3) * 8;
+                        uint32_t t[G + 5];
+#pragma unroll
+                        for (int k = 0; k < G + 5; ++k) t[k] = al[k];
 #pragma unroll
                         for (int k = 0; k < G + 4; ++k) w[k] = __funnelshift_r(t[k], t[k + 1], sh);
                     } else {
@@ -972,17 +998,30 @@ __device__ __noinline__ void fp_tile(const uint8_t *src64, const uint8_t *arena,
     }
 }
 
+// Raw staging for small windows: rows [0, rows) x chunks [0, nch) of the 16-byte aligned region that
+// contains the tile go to shared memory as they are (LDG.128 -> STS.128, every line read once).
+__device__ __forceinline__ void fp_stage_raw(uint8_t *arena, const uint8_t *__restrict__ g16, int gstride, int rows, int nch,
+                                             int pitch) {
+    const int total = rows * nch;
+    const uint32_t mg = 0xFFFFFFFFu / (uint32_t)nch + 1u;
+    for (int i = threadIdx.x; i < total; i += SVTME_THREADS) {
+        const int R = (int)__umulhi((uint32_t)i, mg), ch = i - R * nch;
+        *reinterpret_cast<uint4 *>(arena + fp_raw_rowoff(R, pitch) + 16 * ch) =
+            __ldg(reinterpret_cast<const uint4 *>(g16 + (size_t)R * gstride) + ch);
+    }
+}
+
 // All threads call with identical arguments. ref0: global pointer to the reference pixel under
 // block(0,0) at search position (0,0). (ox, oy): MV of search position (0,0). order_base: rank of
 // position (0,0) in the reference's evaluation order (see FpTables). src64: shared memory, 64x64
-// source block with row stride 64.
+// source block with row stride 64. arena: shared memory of arena_bytes bytes.
 __device__ __noinline__ void fullpel_search(const uint8_t *src64, const uint8_t *ref0, int ref_stride, int ox, int oy, int sa_w,
-                               int sa_h, bool sub_sad, uint32_t order_base, FpTables *tab, uint8_t *arena) {
+                               int sa_h, bool sub_sad, uint32_t order_base, FpTables *tab, uint8_t *arena, int arena_bytes) {
     if (sa_w <= 0 || sa_h <= 0) return;
     const int G = sa_w <= 8 ? 2 : (sa_w <= 16 ? 4 : 8);
-    // small areas (the 8x3 .. 16x5 windows of the fast presets): staging four copies of a 71x66 window
-    // for a few dozen positions costs more than the search; read the reference through L1 instead
-    const bool direct = arena == nullptr || sa_w * sa_h <= SVTME_FP_DIRECT_MAX;
+    // small areas (the 8x3 .. 24x7 windows of the fast presets): staging four copies of a 71x66 window
+    // for a few dozen positions costs more than the search; stage the rows once, raw
+    const bool small = sa_w * sa_h <= SVTME_FP_DIRECT_MAX;
     const int last_row = sub_sad ? 62 : 63; // last block row that is read
     for (int ty0 = 0; ty0 < sa_h; ty0 += FP_TH) {
         const int th = min(FP_TH, sa_h - ty0);
@@ -996,23 +1035,36 @@ __device__ __noinline__ void fullpel_search(const uint8_t *src64, const uint8_t 
             const int copy_chunks = rows * m + 4 * ((rows - 1) >> 4) + 4;
             const int copy_bytes = copy_chunks * 16;
             const uint8_t *tile0 = ref0 + (size_t)ty0 * ref_stride + tx0;
+            // raw tile: bytes [mis, mis + span + 64 + 4) of every row, from the 16-byte aligned address below tile0
+            const int mis = (int)(reinterpret_cast<uintptr_t>(tile0) & 15);
+            const int nch = (mis + span + 64 + 4 + 15) >> 4, pitch = nch * 16;
+            const int mode = (small && fp_raw_rowoff(rows, pitch) + 64 <= arena_bytes) ? FP_RAW
+                : (4 * copy_bytes <= arena_bytes ? FP_COPIES : FP_DIRECT);
             __syncthreads();
-            if (!direct) stage_window4(arena, tile0, ref_stride, rows, m, 4, copy_bytes, words);
+            if (mode == FP_COPIES) stage_window4(arena, tile0, ref_stride, rows, m, 4, copy_bytes, words);
+            if (mode == FP_RAW) fp_stage_raw(arena, tile0 - mis, ref_stride, rows, nch, pitch);
             for (int i = threadIdx.x; i < SVTME_PU_COUNT; i += SVTME_THREADS) tab->tile_best[i] = ~0u;
             __syncthreads();
-            if (direct) {
+            if (mode == FP_DIRECT) {
                 if (G == 2)
-                    fp_tile<2, true>(src64, tile0, 0, ref_stride, tw, th, sub_sad, tab);
+                    fp_tile<2, FP_DIRECT>(src64, tile0, 0, ref_stride, tw, th, sub_sad, tab);
                 else if (G == 4)
-                    fp_tile<4, true>(src64, tile0, 0, ref_stride, tw, th, sub_sad, tab);
+                    fp_tile<4, FP_DIRECT>(src64, tile0, 0, ref_stride, tw, th, sub_sad, tab);
                 else
-                    fp_tile<8, true>(src64, tile0, 0, ref_stride, tw, th, sub_sad, tab);
+                    fp_tile<8, FP_DIRECT>(src64, tile0, 0, ref_stride, tw, th, sub_sad, tab);
+            } else if (mode == FP_RAW) {
+                if (G == 2)
+                    fp_tile<2, FP_RAW>(src64, arena, mis, pitch, tw, th, sub_sad, tab);
+                else if (G == 4)
+                    fp_tile<4, FP_RAW>(src64, arena, mis, pitch, tw, th, sub_sad, tab);
+                else
+                    fp_tile<8, FP_RAW>(src64, arena, mis, pitch, tw, th, sub_sad, tab);
             } else if (G == 2)
-                fp_tile<2, false>(src64, arena, copy_bytes, m, tw, th, sub_sad, tab);
+                fp_tile<2, FP_COPIES>(src64, arena, copy_bytes, m, tw, th, sub_sad, tab);
             else if (G == 4)
-                fp_tile<4, false>(src64, arena, copy_bytes, m, tw, th, sub_sad, tab);
+                fp_tile<4, FP_COPIES>(src64, arena, copy_bytes, m, tw, th, sub_sad, tab);
             else
-                fp_tile<8, false>(src64, arena, copy_bytes, m, tw, th, sub_sad, tab);
+                fp_tile<8, FP_COPIES>(src64, arena, copy_bytes, m, tw, th, sub_sad, tab);
             __syncthreads();
             if (threadIdx.x < SVTME_PU_COUNT) {
                 const uint32_t k = tab->tile_best[threadIdx.x];

@@ -507,15 +507,15 @@ __global__ void __launch_bounds__(128) points_kernel(WideArgs a) {
 }
 
 // ---------------------------------------------------------------- integer search (one CTA per b64 x reference)
-// SMALL: every search area of the batch is small enough for the unstaged full-pel path (decided on
+// SMALL: every search area of the batch is small enough for the raw-staged full-pel path (decided on
 // the host from the parameters; a larger area would still be searched correctly, only slower), so
-// the CTA needs no arena: ~7 KB of shared memory, more CTAs per SM.
+// the CTA needs only a 10 KB arena: more CTAs per SM.
 template <bool SMALL>
 struct IntSmem {
     IntState st;
     DevJob job;
     __align__(16) uint8_t src64[64 * 64];
-    __align__(16) uint8_t arena[SMALL ? 16 : SVTME_ARENA_BYTES];
+    __align__(16) uint8_t arena[SMALL ? SVTME_FP_SMALL_ARENA_BYTES : SVTME_ARENA_BYTES];
 };
 
 #define T0(stmt)                        \
@@ -524,14 +524,19 @@ struct IntSmem {
         __syncthreads();                \
     } while (0)
 
-// slots [slot0, slot0 + n_slots) of the 2x4 (list, ref_idx) grid; slot 0 = (list 0, ref 0) runs in a
-// launch of its own because the other references' search areas may depend on its result (:1345-1350)
+// The (list, ref_idx) slots a launch covers: only those some picture of the batch uses. Slot 0 =
+// (list 0, ref 0) runs in a launch of its own when the other references' search areas may depend on
+// its result (:1345-1350, enable_me_sr_adjustment == 2); otherwise all slots are one launch.
+struct IntSlots {
+    int n;
+    int8_t slot[NL * NR];
+};
 template <bool SMALL>
 __global__ void __launch_bounds__(SVTME_THREADS, SMALL ? SVTME_INT_SMALL_CTAS_PER_SM : SVTME_CTAS_PER_SM)
-    int_kernel(WideArgs a, int slot0, int n_slots) {
+    int_kernel(WideArgs a, IntSlots sl) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     IntSmem<SMALL> *sm = reinterpret_cast<IntSmem<SMALL> *>(smem_raw);
-    const int gid = blockIdx.x / n_slots, slot = slot0 + blockIdx.x % n_slots, tid = threadIdx.x;
+    const int gid = blockIdx.x / sl.n, slot = sl.slot[blockIdx.x % sl.n], tid = threadIdx.x;
     const int li = slot / NR, ri = slot % NR;
     const DevJob &Jg = a.jobs[gid / a.b64_per_job];
     if (li >= Jg.prm.num_of_list_to_search || ri >= Jg.prm.num_of_ref_pic_to_search[li]) return;
@@ -598,7 +603,7 @@ __global__ void __launch_bounds__(SVTME_THREADS, SMALL ? SVTME_INT_SMALL_CTAS_PE
     {
         const int ox = s->fp_ox, oy = s->fp_oy;
         fullpel_search(sm->src64, pl.at(org_x + ox, org_y + oy), pl.stride, ox, oy, s->fp_sa_w, s->fp_sa_h, sub_sad, 2,
-                       &s->tab, SMALL ? nullptr : sm->arena);
+                       &s->tab, sm->arena, (int)sizeof(sm->arena));
         work += (unsigned long long)s->fp_sa_w * s->fp_sa_h * 64ull * (sub_sad ? 32 : 64);
     }
     if (tid < SVTME_PU_COUNT) {
@@ -676,6 +681,9 @@ SvtmeStageFlags svtme_stage_flags(const SvtMeParams &p) {
     f.hme_l0_round_b = f.hme_l0 && l0_dependent(p);
     f.hme_l1 = p.enable_hme_flag && p.enable_hme_level1_flag;
     f.hme_l2 = p.enable_hme_flag && p.enable_hme_level2_flag;
+    f.int_dependent = p.enable_me_sr_adjustment == 2; // plan_int_b reads p_sb_best_sad[0][0][0] (:1345-1350)
+    f.max_refs[0] = (int)p.num_of_ref_pic_to_search[0];
+    f.max_refs[1] = p.num_of_list_to_search > 1 ? (int)p.num_of_ref_pic_to_search[1] : 0;
     // refinement windows of at most 64 positions (8x3 everywhere but M0) take the warp-per-window kernel
     f.refine_small = (!f.hme_l1 || ((p.hme_l1_sa.width + 7u) & ~7u) * p.hme_l1_sa.height <= 64u) &&
         (!f.hme_l2 || ((p.hme_l2_sa.width + 7u) & ~7u) * p.hme_l2_sa.height <= 64u);
@@ -752,17 +760,26 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
     }
     scalar_kernel<S_L2><<<sg, 128, 0, st>>>(a);
     mark(); // 5: HME level 2 + search centre + HME pruning
-    if (f.small_areas) {
-        int_kernel<true><<<N, SVTME_THREADS, sizeof(IntSmem<true>), st>>>(a, 0, 1);
-        int_kernel<true><<<N * (NL * NR - 1), SVTME_THREADS, sizeof(IntSmem<true>), st>>>(a, 1, NL * NR - 1);
-    } else {
-        int_kernel<false><<<N, SVTME_THREADS, sizeof(IntSmem<false>), st>>>(a, 0, 1);
-        int_kernel<false><<<N * (NL * NR - 1), SVTME_THREADS, sizeof(IntSmem<false>), st>>>(a, 1, NL * NR - 1);
+    {
+        IntSlots first = {}, rest = {};
+        for (int li = 0; li < NL; ++li)
+            for (int ri = 0; ri < f.max_refs[li]; ++ri) {
+                IntSlots &t = (f.int_dependent && (li || ri)) ? rest : first;
+                t.slot[t.n++] = (int8_t)(li * NR + ri);
+            }
+        for (const IntSlots *t : {&first, &rest}) {
+            if (!t->n) continue;
+            if (f.small_areas)
+                int_kernel<true><<<N * t->n, SVTME_THREADS, sizeof(IntSmem<true>), st>>>(a, *t);
+            else
+                int_kernel<false><<<N * t->n, SVTME_THREADS, sizeof(IntSmem<false>), st>>>(a, *t);
+            ++launches;
+        }
     }
     mark(); // 6: integer search
     finish_kernel<<<N, 128, sizeof(FinSmem), st>>>(a);
     mark(); // 7: candidates + statistics
-    g_svtme_launches += 8 + 2 + 1 + launches; // (the state clear counts itself)
+    g_svtme_launches += 8 + 1 + launches; // (the state clear counts itself)
 }
 
 // ---------------------------------------------------------------- kernel-test entry points
@@ -819,7 +836,7 @@ __global__ void __launch_bounds__(SVTME_THREADS) fullpel_test_kernel(const uint8
         sm->tab.mv[threadIdx.x] = best_mv[threadIdx.x];
     }
     __syncthreads();
-    fullpel_search(sm->src, ref, ref_stride, ox, oy, sa_w, sa_h, sub_sad != 0, 1, &sm->tab, sm->arena);
+    fullpel_search(sm->src, ref, ref_stride, ox, oy, sa_w, sa_h, sub_sad != 0, 1, &sm->tab, sm->arena, (int)sizeof(sm->arena));
     if (threadIdx.x < SVTME_PU_COUNT) {
         best_sad[threadIdx.x] = (uint32_t)(sm->tab.key[threadIdx.x] >> 32);
         best_mv[threadIdx.x] = sm->tab.mv[threadIdx.x];

@@ -862,9 +862,12 @@ __device__ __forceinline__ void fp_butterfly(uint32_t (&v)[G], int b, int &joff3
 #define FP_COPIES 0
 #define FP_DIRECT 1
 #define FP_RAW 2
-// 64 bytes of skew per 16 rows (cumulative: rows never overlap): the four block rows of a lane group sit 16 rows
-// apart, a multiple of 128 bytes for every pitch, and would share banks
-__device__ __forceinline__ int fp_raw_rowoff(int R, int pitch) { return R * pitch + (R >> 4) * 64; }
+// Row placement of the raw tile. The 16 blocks of a half-warp read the same word column of rows 16*by
+// apart (a multiple of 32 banks for every pitch) and of columns 16*bx bytes apart, two adjacent byte
+// phases each: banks 4*bx + {0,1}. The skew moves the four block rows to bank offsets {0, 2, 16, 18}
+// -> all 32 lanes on distinct banks. Rows stay 8-byte aligned (staging stores 8 bytes at a time) and
+// never overlap (skews are cumulative per 32 rows, 8 < 64).
+__device__ __forceinline__ int fp_raw_rowoff(int R, int pitch) { return R * pitch + ((R >> 4) & 1) * 8 + (R >> 5) * 64; }
 template <int G, int MODE>
 __device__ __noinline__ void fp_tile(const uint8_t *src64, const uint8_t *arena, int copy_bytes, int m, int tw, int th,
                                         bool sub_sad, FpTables *tab) {
@@ -1006,8 +1009,10 @@ __device__ __forceinline__ void fp_stage_raw(uint8_t *arena, const uint8_t *__re
     const uint32_t mg = 0xFFFFFFFFu / (uint32_t)nch + 1u;
     for (int i = threadIdx.x; i < total; i += SVTME_THREADS) {
         const int R = (int)__umulhi((uint32_t)i, mg), ch = i - R * nch;
-        *reinterpret_cast<uint4 *>(arena + fp_raw_rowoff(R, pitch) + 16 * ch) =
-            __ldg(reinterpret_cast<const uint4 *>(g16 + (size_t)R * gstride) + ch);
+        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(g16 + (size_t)R * gstride) + ch);
+        uint2 *d = reinterpret_cast<uint2 *>(arena + fp_raw_rowoff(R, pitch) + 16 * ch);
+        d[0] = make_uint2(v.x, v.y);
+        d[1] = make_uint2(v.z, v.w);
     }
 }
 

@@ -538,6 +538,7 @@ static int launch_into(SvtMeHandle *h, Batch *B, const SvtMeJob *jobs, uint32_t 
     flags.small_areas = true;
     flags.prehme_strip = true;
     flags.refine_small = getenv("SVTME_NO_REFINE_KERNEL") == nullptr; // (tests exercise both paths)
+    flags.l0_strip = getenv("SVTME_NO_L0_STRIP") == nullptr;
     for (uint32_t i = 0; i < n; ++i) {
         flags.prehme_strip = flags.prehme_strip && jobs[i].params.hme_search_method != 1;
         const SvtmeStageFlags f = svtme_stage_flags(jobs[i].params);

@@ -87,6 +87,7 @@ struct SvtmeStageFlags {
     bool zz, prehme, prehme_l1_round, hme_l0, hme_l0_round_b, hme_l1, hme_l2;
     bool int_dependent;   // some picture derives the other references' full-pel areas from (list 0, ref 0)'s result
     int max_refs[2];      // references searched per list, maximum over the batch
+    bool l0_strip;        // HME level 0 in strip mode too (needs prehme_strip's condition; off: one CTA per b64)
     bool refine_small;    // HME level 1 / 2 windows are small in every picture: one warp per window, no staging
     bool prehme_strip;    // pre-HME runs in strip mode (one CTA per b64 column / row and reference): every
                           // picture of the batch uses the sub-sampled SAD (16x8 source block = one sub-block)

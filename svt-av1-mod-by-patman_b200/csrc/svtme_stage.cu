@@ -327,12 +327,15 @@ __device__ __forceinline__ int warp_max(int v) {
 }
 
 __global__ void __launch_bounds__(SVTME_HME_THREADS, SVTME_HME_CTAS_PER_SM)
-    strip_kernel(WideArgs a, int cols, int rows, int wslot, int arena_limit) {
+    strip_kernel(WideArgs a, int cols, int rows, int wslot, int arena_limit, int mode) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     StripSmem *sm = reinterpret_cast<StripSmem *>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int segs_v = (rows + STRIP_SEG - 1) / STRIP_SEG, segs_h = (cols + STRIP_SEG - 1) / STRIP_SEG;
-    const int n_col_tasks = cols * segs_v, per_slot = n_col_tasks + rows * segs_h;
+    // mode 0: pre-HME (region 0 along columns, region 1 along rows); mode 1: HME level 0, the four quadrant
+    // windows of a (list, reference) each along rows (hme_level_0 searches around (0,0): the windows of a
+    // row of b64s are the same rectangle shifted by 16 pixels)
+    const int n_col_tasks = mode == 0 ? cols * segs_v : 0, per_slot = n_col_tasks + (mode == 0 ? 1 : 4) * rows * segs_h;
     int t = blockIdx.x;
     const int task = t % per_slot;
     t /= per_slot;
@@ -344,8 +347,10 @@ __global__ void __launch_bounds__(SVTME_HME_THREADS, SVTME_HME_CTAS_PER_SM)
     if (task < n_col_tasks) {
         region = 0; bx0 = task / segs_v; by0 = (task % segs_v) * STRIP_SEG; len = min(STRIP_SEG, rows - by0); step = cols;
     } else {
-        const int u = task - n_col_tasks;
-        region = 1; by0 = u / segs_h; bx0 = (u % segs_h) * STRIP_SEG; len = min(STRIP_SEG, cols - bx0); step = 1;
+        int u = task - n_col_tasks;
+        region = mode == 0 ? 1 : u / (rows * segs_h);
+        u -= mode == 0 ? 0 : region * (rows * segs_h);
+        by0 = u / segs_h; bx0 = (u % segs_h) * STRIP_SEG; len = min(STRIP_SEG, cols - bx0); step = 1;
     }
     const int g0 = pic * a.b64_per_job + by0 * cols + bx0;
     // ---- the segment's jobs of this (list, reference, region), compacted (warp 0, lane <-> b64)
@@ -357,7 +362,7 @@ __global__ void __launch_bounds__(SVTME_HME_THREADS, SVTME_HME_CTAS_PER_SM)
             const int nj = s->n_jobs;
             for (int k = 0; k < nj; ++k) {
                 const JobMeta m = s->meta[k];
-                if (m.li == li && m.ri == ri && m.a == region) { found = k; break; }
+                if (m.li == li && m.ri == ri && (mode == 0 ? m.a : m.b * 2 + m.a) == region) { found = k; break; }
             }
         }
         const unsigned bal = __ballot_sync(0xffffffffu, found >= 0);
@@ -727,7 +732,7 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
         (b64_cols * ((b64_rows + STRIP_SEG - 1) / STRIP_SEG) + b64_rows * ((b64_cols + STRIP_SEG - 1) / STRIP_SEG));
     auto prehme_round = [&]() {
         if (f.prehme_strip)
-            strip_kernel<<<strip_tasks, SVTME_HME_THREADS, sizeof(StripSmem), st>>>(a, b64_cols, b64_rows, 2, g_strip_arena_limit);
+            strip_kernel<<<strip_tasks, SVTME_HME_THREADS, sizeof(StripSmem), st>>>(a, b64_cols, b64_rows, 2, g_strip_arena_limit, 0);
         else
             engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 2);
         ++launches;
@@ -737,9 +742,17 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
     if (f.prehme_l1_round) prehme_round();
     scalar_kernel<S_PREHME2><<<sg, 128, 0, st>>>(a);
     mark(); // 2: pre-HME
-    if (f.hme_l0) engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 3), ++launches;
+    const int l0_tasks = n_jobs * NL * NR * 4 * b64_rows * ((b64_cols + STRIP_SEG - 1) / STRIP_SEG);
+    auto l0_round = [&]() {
+        if (f.prehme_strip && f.l0_strip)
+            strip_kernel<<<l0_tasks, SVTME_HME_THREADS, sizeof(StripSmem), st>>>(a, b64_cols, b64_rows, 3, g_strip_arena_limit, 1);
+        else
+            engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 3);
+        ++launches;
+    };
+    if (f.hme_l0) l0_round();
     scalar_kernel<S_L0A><<<sg, 128, 0, st>>>(a);
-    if (f.hme_l0_round_b) engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 3), ++launches;
+    if (f.hme_l0_round_b) l0_round();
     scalar_kernel<S_L0B><<<sg, 128, 0, st>>>(a);
     mark(); // 3: HME level 0
     if (f.hme_l1) {

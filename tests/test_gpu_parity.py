@@ -51,6 +51,7 @@ def test_stage_generic_engine_for_refinement_rounds(case, monkeypatch):
     """HME level 1 / 2 rounds through the generic staged engine instead of the warp-per-window
     refinement kernel (the path presets with wide refinement windows take): same golden result."""
     monkeypatch.setenv("SVTME_NO_REFINE_KERNEL", "1")
+    monkeypatch.setenv("SVTME_NO_L0_STRIP", "1")
     name, W, H, preset, tl, refs, cur, kw = case
     seq, d = G.stage_case(*case)
     p = U.finish_params(derive(None, d), d, cur, refs)

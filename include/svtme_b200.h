@@ -229,6 +229,10 @@ int svtme_fetch_results(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n);
 int svtme_submit_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n);
 int svtme_collect_results(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n);
 uint32_t svtme_pending_batches(SvtMeHandle *h);
+/* Timeline aid for the queued form (measurement only): mark an origin on the main stream; after each
+ * svtme_collect_results, ms3 = {pipeline start, pipeline end, download end} of that batch in ms after the mark. */
+int svtme_debug_mark(SvtMeHandle *h);
+int svtme_debug_last_span(SvtMeHandle *h, float *ms3);
 int svtme_sync(SvtMeHandle *h);
 /* CUDA-event time (ms) of the ME kernel launches of the last svtme_launch_pictures call, and
  * the number of kernels this library has launched so far. */

@@ -41,8 +41,7 @@ struct Slot {
     DevPyramid pyr;
     uint64_t pic_num;
     bool used;
-    bool build_unread;  // a pyramid build wrote the slot and no launch has read it since
-    uint64_t last_reader; // sequence number of the newest launch that reads this pyramid (an upload into the slot waits for it); 0 = none
+    uint64_t last_reader[2]; // per compute stream: sequence number of the newest launch that reads this pyramid (a writer of the slot waits for both); 0 = none
 };
 
 static inline size_t up16(size_t v) { return (v + 15) & ~(size_t)15; }
@@ -62,7 +61,7 @@ struct Batch {
     uint32_t jobs_cap = 0;
     OutBuffers ob;
     std::vector<size_t> work_off; // offsets of the per-job work counters
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, jobs_ev = nullptr, done_ev = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, jobs_ev = nullptr, done_ev = nullptr; // done_ev: download complete
     cudaEvent_t ph_ev[SVTME_PHASES] = {};
     bool jobs_pending = false; // h_jobs may still be on its way to the device
     uint32_t n = 0;
@@ -83,7 +82,15 @@ struct SvtMeHandle {
     uint32_t width, height, b64_cols, b64_rows, n_b64;
     cudaStream_t stream;
     bool own_stream;
-    cudaStream_t h2d_stream, d2h_stream; // uploads / result downloads overlap the pipeline of other batches
+    cudaStream_t h2d_stream, d2h_stream; // uploads + pyramid builds / result downloads overlap the pipeline of other batches
+    cudaStream_t stream2;                // second compute stream: queued batches alternate between `stream` and this one, so
+                                         // that the launch tails of one batch are filled by the next (pyramid builds stay on `stream`)
+    bool two_streams = true;
+    cudaEvent_t origin_ev = nullptr; // svtme_debug_mark
+    float span[3] = {0.f, 0.f, 0.f};  // last collected batch: pipeline start / end / download end, ms after the mark
+    uint32_t submit_count = 0;
+    void *d_states2 = nullptr;
+    size_t states_bytes2 = 0;
     cudaEvent_t h2d_ev, build_ev;
     cudaEvent_t launch_ev[SVTME_LAUNCH_EV_RING]; // "launch seq is done", indexed seq % ring (Batch objects and their events are recycled)
     bool build_recorded = false;
@@ -110,7 +117,7 @@ static Batch *batch_new() {
     cudaError_t e = cudaEventCreate(&b->ev0);
     if (e == cudaSuccess) e = cudaEventCreate(&b->ev1);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&b->jobs_ev, cudaEventDisableTiming);
-    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&b->done_ev, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreate(&b->done_ev);
     for (int k = 0; k < SVTME_PHASES && e == cudaSuccess; ++k) e = cudaEventCreate(&b->ph_ev[k]);
     if (e != cudaSuccess) { delete b; return nullptr; }
     return b;
@@ -168,7 +175,8 @@ extern "C" int svtme_open(int device, uint32_t width, uint32_t height, uint32_t 
     }
     h->pool = nullptr;
     h->last_ms = 0.f;
-    h->h2d_stream = h->d2h_stream = nullptr;
+    h->h2d_stream = h->d2h_stream = h->stream2 = nullptr;
+    h->two_streams = getenv("SVTME_SINGLE_STREAM") == nullptr;
     h->h2d_ev = h->build_ev = nullptr;
     cudaError_t e = cudaMalloc(&h->pool, h->slot_bytes * capacity);
     if (e != cudaSuccess) { delete h; return fail(SVTME_ERR_NOMEM, "svtme_open: cudaMalloc pyramid pool", e); }
@@ -177,6 +185,7 @@ extern "C" int svtme_open(int device, uint32_t width, uint32_t height, uint32_t 
     h->own_stream = true;
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->h2d_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->d2h_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->h2d_ev, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->build_ev, cudaEventDisableTiming);
     for (int k = 0; k < SVTME_PUT_RING && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&h->put[k].ev, cudaEventDisableTiming);
@@ -193,8 +202,7 @@ extern "C" int svtme_open(int device, uint32_t width, uint32_t height, uint32_t 
         }
         h->slots[i].used = false;
         h->slots[i].pic_num = 0;
-        h->slots[i].last_reader = 0;
-        h->slots[i].build_unread = false;
+        h->slots[i].last_reader[0] = h->slots[i].last_reader[1] = 0;
     }
     *out = h;
     return SVTME_OK;
@@ -204,9 +212,12 @@ extern "C" void svtme_close(SvtMeHandle *h) {
     if (!h) return;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
+    cudaStreamSynchronize(h->stream2);
     cudaStreamSynchronize(h->h2d_stream);
     cudaStreamSynchronize(h->d2h_stream);
     cudaFree(h->pool);
+    cudaFree(h->d_states2);
+    cudaStreamDestroy(h->stream2);
     batch_free(h->sync_batch);
     for (Batch *b : h->free_batches) batch_free(b);
     for (Batch *b : h->queue) batch_free(b);
@@ -218,6 +229,7 @@ extern "C" void svtme_close(SvtMeHandle *h) {
     }
     cudaEventDestroy(h->h2d_ev);
     cudaEventDestroy(h->build_ev);
+    if (h->origin_ev) cudaEventDestroy(h->origin_ev);
     for (int k = 0; k < SVTME_LAUNCH_EV_RING; ++k) cudaEventDestroy(h->launch_ev[k]);
     cudaStreamDestroy(h->h2d_stream);
     cudaStreamDestroy(h->d2h_stream);
@@ -264,17 +276,17 @@ static int put_batch(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const
     // Host pictures travel on the upload stream so that they overlap the ME pipeline of earlier
     // batches; an upload into a slot must not overtake a launch that still reads the slot's old
     // content (all launches are in order on the main stream: waiting for the newest reader suffices).
-    uint64_t newest = 0;
-    bool any_copy = false, after_build = false;
+    uint64_t newest[2] = {0, 0};
+    bool any_copy = false;
     for (uint32_t i = 0; i < n; ++i) {
         if (!luma[i]) return failf(SVTME_ERR_INVALID, "%s: null picture", who);
         const int si = find_slot(h, pic_nums[i], true);
         if (si == -2) return failf(SVTME_ERR_NOMEM, "%s: pyramid ring full (release pictures or raise capacity)", who);
         Slot &s = h->slots[si];
-        if (s.last_reader > newest) newest = s.last_reader;
-        s.last_reader = 0;
-        after_build |= s.build_unread; // re-put before any launch read it: the previous build still writes the slot
-        s.build_unread = true;
+        for (int k = 0; k < 2; ++k) {
+            if (s.last_reader[k] > newest[k]) newest[k] = s.last_reader[k];
+            s.last_reader[k] = 0;
+        }
         items[i].pyr = s.pyr;
         items[i].src = nullptr;
         items[i].src_stride = 0;
@@ -284,11 +296,18 @@ static int put_batch(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const
         } else
             any_copy = true;
     }
-    cudaStream_t cs = device_src ? h->stream : h->h2d_stream;
+    // Uploads AND pyramid builds run on the upload stream: a build never queues behind the ME pipeline of an
+    // earlier batch. The stream first waits for the newest reader of the slots on each compute stream (an
+    // event of the ring that has been re-recorded since belongs to a LATER launch of the same stream: still
+    // sufficient); launches wait for build_ev.
+    cudaStream_t cs = h->h2d_stream;
+    if (device_src) { // the caller produced the pictures on the handle's stream (svtme_set_stream): keep that order
+        CU(cudaEventRecord(h->h2d_ev, h->stream));
+        CU(cudaStreamWaitEvent(cs, h->h2d_ev, 0));
+    }
+    for (int k = 0; k < 2; ++k)
+        if (newest[k]) CU(cudaStreamWaitEvent(cs, h->launch_ev[newest[k] % SVTME_LAUNCH_EV_RING], 0));
     if (any_copy) {
-        // (an event of the ring that has been re-recorded since belongs to a LATER launch: still sufficient)
-        if (!device_src && newest) CU(cudaStreamWaitEvent(cs, h->launch_ev[newest % SVTME_LAUNCH_EV_RING], 0));
-        if (!device_src && after_build && h->build_recorded) CU(cudaStreamWaitEvent(cs, h->build_ev, 0));
         for (uint32_t i = 0; i < n; ++i) {
             if (items[i].src) continue;
             const DevPlane &f = items[i].pyr.lvl[0];
@@ -296,21 +315,17 @@ static int put_batch(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const
             CU(cudaMemcpy2DAsync(const_cast<uint8_t *>(f.at(0, 0)), f.stride, luma[i], stride, h->width, h->height,
                                  device_src ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, cs));
         }
-        if (!device_src) {
-            CU(cudaEventRecord(h->h2d_ev, cs));
-            CU(cudaStreamWaitEvent(h->stream, h->h2d_ev, 0));
-        }
     }
-    CU(svtme_launch_fetch_from_host(pr.d, items, up16(sizeof(SvtmePutItem) * n), h->stream));
-    CU(cudaEventRecord(pr.ev, h->stream));
+    CU(svtme_launch_fetch_from_host(pr.d, items, up16(sizeof(SvtmePutItem) * n), cs));
+    CU(cudaEventRecord(pr.ev, cs));
     pr.pending = true;
     SvtmePadSpec ps;
     for (int l = 0; l < 3; ++l) {
         ps.l[l] = kPadL[l]; ps.r[l] = kPadR[l]; ps.t[l] = kPadT[l]; ps.b[l] = kPadB[l];
     }
-    svtme_launch_build_batch(pr.d, (int)n, items[0].pyr, ps, h->stream);
+    svtme_launch_build_batch(pr.d, (int)n, items[0].pyr, ps, cs);
     CU(cudaGetLastError());
-    CU(cudaEventRecord(h->build_ev, h->stream));
+    CU(cudaEventRecord(h->build_ev, cs));
     h->build_recorded = true;
     return SVTME_OK;
 }
@@ -372,6 +387,7 @@ extern "C" int svtme_get_plane(SvtMeHandle *h, uint64_t pic_num, int level, uint
     const DevPlane &pl = h->slots[si].pyr.lvl[level];
     if ((int)pad > kPadT[level] || (int)pad > kPadL[level] || dst_stride < pl.width + 2 * pad)
         return fail(SVTME_ERR_INVALID, "svtme_get_plane: pad larger than the resident pad or stride too small");
+    if (h->build_recorded) CU(cudaStreamWaitEvent(h->stream, h->build_ev, 0));
     CU(cudaMemcpy2DAsync(dst, dst_stride, pl.at(-(int)pad, -(int)pad), pl.stride, pl.width + 2 * pad, pl.height + 2 * pad,
                          cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
@@ -383,6 +399,7 @@ extern "C" int svtme_sync(SvtMeHandle *h) {
     CU(cudaSetDevice(h->device));
     CU(cudaStreamSynchronize(h->h2d_stream));
     CU(cudaStreamSynchronize(h->stream));
+    CU(cudaStreamSynchronize(h->stream2));
     CU(cudaStreamSynchronize(h->d2h_stream));
     return SVTME_OK;
 }
@@ -442,7 +459,10 @@ static int validate_params(const SvtMeParams &p) {
 }
 
 // Enqueue the stage pipeline of n pictures on the main stream, results into batch B's device buffer.
-static int launch_into(SvtMeHandle *h, Batch *B, const SvtMeJob *jobs, uint32_t n) {
+static int launch_into(SvtMeHandle *h, Batch *B, const SvtMeJob *jobs, uint32_t n, int si = 0) {
+    cudaStream_t st = si ? h->stream2 : h->stream;
+    void *&d_states = si ? h->d_states2 : h->d_states;
+    size_t &states_bytes = si ? h->states_bytes2 : h->states_bytes;
     if (B->jobs_pending) CU(cudaEventSynchronize(B->jobs_ev)); // the previous job array has left the pinned buffer
     B->jobs_pending = false;
     if (n > B->jobs_cap) {
@@ -465,6 +485,7 @@ static int launch_into(SvtMeHandle *h, Batch *B, const SvtMeJob *jobs, uint32_t 
         // synchronous batch may still be downloading only if the caller never fetched: wait for it
         CU(cudaStreamSynchronize(h->d2h_stream));
         CU(cudaStreamSynchronize(h->stream));
+        CU(cudaStreamSynchronize(h->stream2));
         cudaFree(B->ob.dev);
         cudaFreeHost(B->ob.host);
         B->ob = OutBuffers();
@@ -472,7 +493,9 @@ static int launch_into(SvtMeHandle *h, Batch *B, const SvtMeJob *jobs, uint32_t 
         CU(cudaMallocHost(&B->ob.host, total));
         B->ob.bytes = total;
     }
-    B->seq = ++h->seq;
+    // sequence numbers keep the stream parity: seq % 2 == si (the event ring is indexed by seq)
+    h->seq += 1 + ((h->seq + 1 + si) & 1);
+    B->seq = h->seq;
     B->n = n;
     B->total = total;
     size_t off = 0;
@@ -485,15 +508,13 @@ static int launch_into(SvtMeHandle *h, Batch *B, const SvtMeJob *jobs, uint32_t 
         const int sc = find_slot(h, j.cur, false);
         if (sc < 0) return fail(SVTME_ERR_NOTFOUND, "svtme_launch_pictures: current picture not resident");
         d.cur = h->slots[sc].pyr;
-        h->slots[sc].last_reader = B->seq;
-        h->slots[sc].build_unread = false;
+        h->slots[sc].last_reader[si] = B->seq;
         for (int li = 0; li < j.params.num_of_list_to_search; ++li)
             for (int ri = 0; ri < j.params.num_of_ref_pic_to_search[li]; ++ri) {
                 const int sr = find_slot(h, j.refs[li][ri], false);
                 if (sr < 0) return fail(SVTME_ERR_NOTFOUND, "svtme_launch_pictures: reference picture not resident");
                 d.ref[li][ri] = h->slots[sr].pyr;
-                h->slots[sr].last_reader = B->seq;
-                h->slots[sr].build_unread = false;
+                h->slots[sr].last_reader[si] = B->seq;
             }
         d.width = (int)h->width;
         d.height = (int)h->height;
@@ -518,20 +539,21 @@ static int launch_into(SvtMeHandle *h, Batch *B, const SvtMeJob *jobs, uint32_t 
         off += L.end;
     }
     // entries the stage never writes (pruned candidates) read as zero, like a fresh MeSbResults
-    CU(svtme_launch_zero_fill(B->ob.dev, total, h->stream));
-    CU(svtme_launch_fetch_from_host(B->d_jobs, B->h_jobs, up16(sizeof(DevJob) * n), h->stream));
-    CU(cudaEventRecord(B->jobs_ev, h->stream));
+    if (h->build_recorded) CU(cudaStreamWaitEvent(st, h->build_ev, 0)); // pyramids are built on the upload stream
+    CU(svtme_launch_zero_fill(B->ob.dev, total, st));
+    CU(svtme_launch_fetch_from_host(B->d_jobs, B->h_jobs, up16(sizeof(DevJob) * n), st));
+    CU(cudaEventRecord(B->jobs_ev, st));
     B->jobs_pending = true;
-    CU(cudaEventRecord(B->ev0, h->stream));
+    CU(cudaEventRecord(B->ev0, st));
     {
         const size_t need = up16((size_t)n * h->n_b64 * svtme_stage_state_bytes());
-        if (need > h->states_bytes) {
-            CU(cudaStreamSynchronize(h->stream)); // earlier launches still use the old scratch
-            cudaFree(h->d_states);
-            h->d_states = nullptr;
-            h->states_bytes = 0;
-            CU(cudaMalloc(&h->d_states, need));
-            h->states_bytes = need;
+        if (need > states_bytes) {
+            CU(cudaStreamSynchronize(st)); // earlier launches still use the old scratch
+            cudaFree(d_states);
+            d_states = nullptr;
+            states_bytes = 0;
+            CU(cudaMalloc(&d_states, need));
+            states_bytes = need;
         }
     }
     SvtmeStageFlags flags = {};
@@ -550,23 +572,30 @@ static int launch_into(SvtMeHandle *h, Batch *B, const SvtMeJob *jobs, uint32_t 
         flags.hme_l0 |= f.hme_l0; flags.hme_l0_round_b |= f.hme_l0_round_b;
         flags.hme_l1 |= f.hme_l1; flags.hme_l2 |= f.hme_l2;
     }
-    svtme_launch_me_stage(B->d_jobs, (int)n, (int)h->b64_cols, (int)h->b64_rows, h->d_states, h->stream, B->ph_ev, flags);
+    svtme_launch_me_stage(B->d_jobs, (int)n, (int)h->b64_cols, (int)h->b64_rows, d_states, st, B->ph_ev, flags);
     CU(cudaGetLastError());
-    CU(cudaEventRecord(B->ev1, h->stream));
-    CU(cudaEventRecord(h->launch_ev[B->seq % SVTME_LAUNCH_EV_RING], h->stream));
+    CU(cudaEventRecord(B->ev1, st));
+    CU(cudaEventRecord(h->launch_ev[B->seq % SVTME_LAUNCH_EV_RING], st));
     h->last = B;
     return SVTME_OK;
 }
 
 // Scatter batch B's pinned result mirror into the callers' SvtMeOut arrays.
 static int scatter_results(SvtMeHandle *h, const Batch *B, const SvtMeJob *jobs, uint32_t n) {
+    std::vector<size_t> offs(n);
     size_t off = 0;
     for (uint32_t i = 0; i < n; ++i) {
+        offs[i] = off;
+        off += out_layout(h->n_b64, svtme_exported_pu_count(&jobs[i].params), jobs[i].params, wants_deep(jobs[i].out)).end;
+    }
+    // plain memcpy of ~0.4 MB per picture; a few host threads when the batch is large (one thread moves ~10 GB/s)
+#pragma omp parallel for schedule(static) num_threads(4) if (n >= 4)
+    for (int i = 0; i < (int)n; ++i) {
         const SvtMeJob &j = jobs[i];
         const uint32_t n_pu = svtme_exported_pu_count(&j.params), nb = h->n_b64;
         const bool deep = wants_deep(j.out);
         const OutLayout L = out_layout(nb, n_pu, j.params, deep);
-        const uint8_t *b = B->ob.host + off;
+        const uint8_t *b = B->ob.host + offs[i];
 #define CP(dst, o, bytes) if (j.out.dst) memcpy(j.out.dst, b + (o), (bytes))
         CP(total_me_candidate_index, L.total, (size_t)nb * n_pu);
         CP(me_mv_array, L.mv, (size_t)nb * n_pu * j.params.max_refs * 4);
@@ -580,7 +609,6 @@ static int scatter_results(SvtMeHandle *h, const Batch *B, const SvtMeJob *jobs,
             CP(hme_sc, L.sc, (size_t)nb * 2 * 4 * 2 * 2); CP(hme_sad, L.hsad, (size_t)nb * 2 * 4 * 8); CP(do_ref, L.doref, (size_t)nb * 2 * 4);
         }
 #undef CP
-        off += L.end;
     }
     return SVTME_OK;
 }
@@ -631,7 +659,7 @@ extern "C" int svtme_submit_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint3
         h->free_batches.pop_back();
     } else if (!(B = batch_new()))
         return fail(SVTME_ERR_NOMEM, "svtme_submit_pictures: batch allocation");
-    int rc = launch_into(h, B, jobs, n);
+    int rc = launch_into(h, B, jobs, n, h->two_streams ? (int)(h->submit_count++ & 1) : 0);
     if (rc) {
         h->free_batches.push_back(B);
         return rc;
@@ -660,8 +688,30 @@ extern "C" int svtme_collect_results(SvtMeHandle *h, const SvtMeJob *jobs, uint3
     int rc = e == cudaSuccess ? scatter_results(h, B, jobs, n) : fail(SVTME_ERR_CUDA, "svtme_collect_results", e);
     std::lock_guard<std::mutex> lk(h->mu);
     if (e == cudaSuccess) cudaEventElapsedTime(&h->last_ms, B->ev0, B->ev1);
+    if (e == cudaSuccess && h->origin_ev) {
+        cudaEventElapsedTime(&h->span[0], h->origin_ev, B->ev0);
+        cudaEventElapsedTime(&h->span[1], h->origin_ev, B->ev1);
+        cudaEventElapsedTime(&h->span[2], h->origin_ev, B->done_ev);
+    }
     h->free_batches.push_back(B);
     return rc;
+}
+
+// Timeline aid: svtme_debug_mark records an origin on the main stream; after each svtme_collect_results,
+// svtme_debug_last_span returns when that batch's pipeline started / ended and when its download ended (ms after the mark).
+extern "C" int svtme_debug_mark(SvtMeHandle *h) {
+    if (!h) return fail(SVTME_ERR_INVALID, "svtme_debug_mark: null handle");
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(cudaSetDevice(h->device));
+    if (!h->origin_ev) CU(cudaEventCreate(&h->origin_ev));
+    CU(cudaEventRecord(h->origin_ev, h->stream));
+    return SVTME_OK;
+}
+extern "C" int svtme_debug_last_span(SvtMeHandle *h, float *ms3) {
+    if (!h || !ms3) return fail(SVTME_ERR_INVALID, "svtme_debug_last_span: bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    for (int k = 0; k < 3; ++k) ms3[k] = h->span[k];
+    return SVTME_OK;
 }
 
 extern "C" uint32_t svtme_pending_batches(SvtMeHandle *h) {
@@ -709,6 +759,7 @@ extern "C" int svtme_last_work_ops(SvtMeHandle *h, uint64_t *ops) {
     std::lock_guard<std::mutex> lk(h->mu);
     CU(cudaSetDevice(h->device));
     CU(cudaStreamSynchronize(h->stream));
+    CU(cudaStreamSynchronize(h->stream2));
     uint64_t sum = 0;
     if (!h->last) return fail(SVTME_ERR_NOTFOUND, "svtme_last_work_ops: nothing launched");
     for (size_t o : h->last->work_off) {
@@ -727,6 +778,7 @@ extern "C" int svtme_last_phase_work(SvtMeHandle *h, uint64_t *ops, uint32_t n) 
     std::lock_guard<std::mutex> lk(h->mu);
     CU(cudaSetDevice(h->device));
     CU(cudaStreamSynchronize(h->stream));
+    CU(cudaStreamSynchronize(h->stream2));
     if (n > SVTME_PHASES) n = SVTME_PHASES;
     for (uint32_t k = 0; k < n; ++k) ops[k] = 0;
     if (!h->last) return fail(SVTME_ERR_NOTFOUND, "svtme_last_phase_work: nothing launched");
@@ -745,6 +797,7 @@ extern "C" int svtme_last_phase_ms(SvtMeHandle *h, float *ms, uint32_t n) {
     std::lock_guard<std::mutex> lk(h->mu);
     CU(cudaSetDevice(h->device));
     CU(cudaStreamSynchronize(h->stream));
+    CU(cudaStreamSynchronize(h->stream2));
     if (n > SVTME_PHASES) n = SVTME_PHASES;
     if (!h->last) return fail(SVTME_ERR_NOTFOUND, "svtme_last_phase_ms: nothing launched");
     for (uint32_t k = 0; k < n; ++k) {

@@ -27,9 +27,15 @@ while pos < len(specs):
     cj, co = ses.make_jobs(part)
     chunks.append((need, [host.data_ptr() + f * W * H for f in need], cj, co))
 def step(log):
+    import ctypes as C
+    ses.lib.svtme_debug_mark(ses.h)
     t0 = time.perf_counter()
     def mark(what):
         log.append((what, (time.perf_counter() - t0) * 1e3))
+        if what.startswith("collect"):
+            v = (C.c_float * 3)()
+            ses.lib.svtme_debug_last_span(ses.h, v)
+            log.append(("  gpu[%.2f-%.2f d2h %.2f]" % (v[0], v[1], v[2]), (time.perf_counter() - t0) * 1e3))
     for c, (need, ptrs, cj, _) in enumerate(chunks):
         ses.put_pictures(need, ptrs, W); mark("put%d(%d)" % (c, len(need)))
         ses.submit_jobs(cj); mark("submit%d(%d)" % (c, len(cj)))

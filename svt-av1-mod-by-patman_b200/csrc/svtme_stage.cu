@@ -336,22 +336,35 @@ __global__ void __launch_bounds__(SVTME_HME_THREADS, SVTME_HME_CTAS_PER_SM)
     // windows of a (list, reference) each along rows (hme_level_0 searches around (0,0): the windows of a
     // row of b64s are the same rectangle shifted by 16 pixels)
     const int n_col_tasks = mode == 0 ? cols * segs_v : 0, per_slot = n_col_tasks + (mode == 0 ? 1 : 4) * rows * segs_h;
-    int t = blockIdx.x;
-    const int task = t % per_slot;
-    t /= per_slot;
-    const int slot = t % (NL * NR), pic = t / (NL * NR);
+    // Task order: kind-major, then (list, reference), then picture. CTAs resident on an SM at the same time
+    // then run the same kind of window (same unrolled item body): the bodies are 6-16 KB each and mixed
+    // kinds thrashed the instruction cache (ncu: "no instruction" was the top stall reason).
+    const int n_row_kinds = mode == 0 ? 1 : 4, row_tasks = rows * segs_h;
+    const int n_pics = (int)gridDim.x / (per_slot * NL * NR);
+    int t = blockIdx.x, region, bx0, by0, len, step, slot, pic;
+    const int all_col = n_col_tasks * NL * NR * n_pics;
+    if (t < all_col) {
+        const int task = t % n_col_tasks;
+        t /= n_col_tasks;
+        pic = t % n_pics; slot = t / n_pics;
+        region = 0; bx0 = task / segs_v; by0 = (task % segs_v) * STRIP_SEG; len = min(STRIP_SEG, rows - by0); step = cols;
+    } else if (mode == 0) {
+        t -= all_col;
+        const int u = t % row_tasks;
+        t /= row_tasks;
+        pic = t % n_pics; slot = t / n_pics;
+        region = 1;
+        by0 = u / segs_h; bx0 = (u % segs_h) * STRIP_SEG; len = min(STRIP_SEG, cols - bx0); step = 1;
+    } else { // HME level 0: picture-major (window sizes differ per reference: mixing them balances the tail)
+        const int u = t % row_tasks;
+        t /= row_tasks;
+        region = t % n_row_kinds; t /= n_row_kinds;
+        slot = t % (NL * NR); pic = t / (NL * NR);
+        by0 = u / segs_h; bx0 = (u % segs_h) * STRIP_SEG; len = min(STRIP_SEG, cols - bx0); step = 1;
+    }
     const int li = slot / NR, ri = slot % NR;
     const DevJob &J = a.jobs[pic];
     if (li >= J.prm.num_of_list_to_search || ri >= (int)J.prm.num_of_ref_pic_to_search[li]) return;
-    int region, bx0, by0, len, step;
-    if (task < n_col_tasks) {
-        region = 0; bx0 = task / segs_v; by0 = (task % segs_v) * STRIP_SEG; len = min(STRIP_SEG, rows - by0); step = cols;
-    } else {
-        int u = task - n_col_tasks;
-        region = mode == 0 ? 1 : u / (rows * segs_h);
-        u -= mode == 0 ? 0 : region * (rows * segs_h);
-        by0 = u / segs_h; bx0 = (u % segs_h) * STRIP_SEG; len = min(STRIP_SEG, cols - bx0); step = 1;
-    }
     const int g0 = pic * a.b64_per_job + by0 * cols + bx0;
     // ---- the segment's jobs of this (list, reference, region), compacted (warp 0, lane <-> b64)
     if (warp == 0) {

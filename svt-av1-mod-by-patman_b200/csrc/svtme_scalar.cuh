@@ -655,19 +655,25 @@ __constant__ uint8_t k_8x8_to_16x16[64] = {5,  5,  6,  6,  7,  7,  8,  8,  5,  5
                                            17, 17, 18, 18, 19, 19, 20, 20, 17, 17, 18, 18, 19, 19, 20, 20};
 __constant__ uint8_t k_16x16_to_32x32[16] = {1, 1, 2, 2, 1, 1, 2, 2, 3, 3, 4, 4, 3, 3, 4, 4};
 
-// me_prune_ref :1592-1635
+// me_prune_ref :1592-1635 — called by ALL threads of the CTA (4 warps): one warp per reference sums its 64
+// best 8x8 SADs (the reference walks them in tab8x8 order; a sum does not care), thread 0 prunes.
 __device__ void me_prune_ref(StageState *s, const SvtMeParams &p) {
-    for (int li = 0; li < p.num_of_list_to_search; ++li)
-        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
-            s->sr[li][ri].hme_sad = 0;
-            if (s->sr[li][ri].do_ref == 0) {
-                s->sr[li][ri].hme_sad = (unsigned long long)SVTME_MAX_SAD_VALUE * 64;
-                continue;
-            }
-            for (int i = 0; i < 64; ++i) s->sr[li][ri].hme_sad += s->best_sad[li][ri][21 + k_tab8x8[i]];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    for (int slot = warp; slot < NL * NR; slot += nw) {
+        const int li = slot / NR, ri = slot % NR;
+        if (li >= p.num_of_list_to_search || ri >= (int)p.num_of_ref_pic_to_search[li]) continue;
+        if (s->sr[li][ri].do_ref == 0) {
+            if (lane == 0) s->sr[li][ri].hme_sad = (unsigned long long)SVTME_MAX_SAD_VALUE * 64;
+            continue;
         }
+        unsigned long long v = (unsigned long long)s->best_sad[li][ri][21 + lane] + s->best_sad[li][ri][21 + 32 + lane];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) s->sr[li][ri].hme_sad = v;
+    }
+    __syncthreads();
     const uint16_t th = p.prune_ref_if_me_sad_dev_bigger_than_th;
-    if (p.enable_me_hme_ref_pruning && th != (uint16_t)~0) {
+    if (threadIdx.x == 0 && p.enable_me_hme_ref_pruning && th != (uint16_t)~0) {
         unsigned long long best = ~0ULL;
         for (int li = 0; li < NL; ++li)
             for (int ri = 0; ri < NR; ++ri)
@@ -676,6 +682,7 @@ __device__ void me_prune_ref(StageState *s, const SvtMeParams &p) {
             for (int ri = 1; ri < NR; ++ri)
                 if ((s->sr[li][ri].hme_sad - best) * 100 > ((unsigned long long)th * best)) s->sr[li][ri].do_ref = 0;
     }
+    __syncthreads();
 }
 
 __device__ __forceinline__ uint8_t cand_byte(unsigned dir, unsigned i0, unsigned i1, unsigned l0, unsigned l1) {
@@ -792,18 +799,28 @@ __device__ void construct_candidates(StageState *s, const SvtMeParams &p, uint32
 }
 
 // compute_distortion :3034-3077 + perform_gm_detection :2908-3031 (thread 0)
+// compute_distortion :3034-3077 + perform_gm_detection :2908-3031 — called by the 32 lanes of ONE warp: the
+// sums over the 85 PU distortions are lane-parallel, lane 0 writes (and runs the rare GM histogram).
 __device__ void finish_b64(StageState *s, const DevJob &J, uint32_t b64, const uint8_t *cando) {
     const SvtMeParams &p = J.prm;
     const uint32_t *d = s->me_distortion;
-    uint32_t d64 = d[0], d32 = 0, d16 = 0, d8 = 0;
-    for (int i = 0; i < 4; ++i) d32 += d[1 + i];
-    for (int i = 0; i < 16; ++i) d16 += d[5 + i];
-    for (int i = 0; i < 64; ++i) d8 += d[21 + i];
-    unsigned long long mean = d8 / 64, ssq = 0;
-    for (int i = 0; i < 64; ++i) {
-        const long long diff = (long long)d[21 + i] - (long long)mean;
-        ssq += (unsigned long long)(diff * diff);
+    const int lane = threadIdx.x & 31;
+    const uint32_t d64 = d[0];
+    uint32_t d32 = lane < 4 ? d[1 + lane] : 0u, d16 = lane < 16 ? d[5 + lane] : 0u;
+    const uint32_t e0 = d[21 + lane], e1 = d[21 + 32 + lane];
+    uint32_t d8 = e0 + e1;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        d32 += __shfl_xor_sync(0xffffffffu, d32, o);
+        d16 += __shfl_xor_sync(0xffffffffu, d16, o);
+        d8 += __shfl_xor_sync(0xffffffffu, d8, o);
     }
+    const long long mean = d8 / 64;
+    const long long f0 = (long long)e0 - mean, f1 = (long long)e1 - mean;
+    unsigned long long ssq = (unsigned long long)(f0 * f0) + (unsigned long long)(f1 * f1);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ssq += __shfl_xor_sync(0xffffffffu, ssq, o);
+    if (lane != 0) return;
     const uint32_t pix = (uint32_t)(s->b64_w * s->b64_h);
     J.var8[b64] = (uint32_t)(ssq / 64);
     J.rc_dist[b64] = p.input_resolution_le_480p ? d8 : d16;

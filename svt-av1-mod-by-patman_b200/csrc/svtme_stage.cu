@@ -654,14 +654,14 @@ __global__ void __launch_bounds__(128) finish_kernel(WideArgs a) {
     const DevJob &J = sm->job;
     const SvtMeParams &p = J.prm;
     // ---- pruning, candidates, statistics :3192-3221
-    T0(if (p.enable_hme_flag && p.enable_me_hme_ref_pruning) me_prune_ref(s, p));
+    if (p.enable_hme_flag && p.enable_me_hme_ref_pruning) me_prune_ref(s, p); // (CTA-uniform condition; syncs inside)
     uint8_t *total = J.total + (size_t)b64 * J.n_pu;
     uint32_t *mvo = J.mv + (size_t)b64 * J.n_pu * p.max_refs;
     uint8_t *cando = J.cand + (size_t)b64 * J.n_pu * p.max_cand;
     if (tid < p.max_number_of_pus_per_sb) construct_candidates(s, p, (uint32_t)tid, total, mvo, cando);
     __threadfence_block();
     __syncthreads();
-    if (tid == 0) finish_b64(s, J, b64, cando);
+    if (tid < 32) finish_b64(s, J, b64, cando);
     // deep state for parity checks
     if (J.best_sad)
         for (int i = tid; i < NL * NR * SVTME_PU_COUNT; i += blockDim.x) {

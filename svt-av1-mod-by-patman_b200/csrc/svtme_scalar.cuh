@@ -67,6 +67,7 @@ struct IntState {
     int fp_do, fp_sa_w, fp_sa_h, fp_ox, fp_oy, fp_probe, fp_phase;
     int16_t fp_xc, fp_yc;
     int c00_needed;
+    uint32_t fp_var;
 };
 
 __device__ __forceinline__ int iabs(int v) { return v < 0 ? -v : v; }
@@ -595,6 +596,21 @@ __device__ void plan_int_b(S *s, const DevJob &J, int li, int ri) {
     s->fp_probe = p.me_8x8_var_enabled && (sa_w * sa_h > 24);
 }
 
+// Variance of the 64 best 8x8 SADs after the one-point probe (:1416-1425), by the 32 lanes of one warp:
+// mean = SAD64x64 / 64, sum of squared differences in uint32 arithmetic like the reference (wraps mod 2^32,
+// so the order of the additions does not matter), / 64. Every lane returns the result.
+template <class S>
+__device__ __forceinline__ uint32_t probe_variance(const S *s) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t mean = (uint32_t)(s->tab.key[0] >> 32) / 64;
+    const int32_t d0 = (int32_t)(uint32_t)(s->tab.key[21 + lane] >> 32) - (int32_t)mean;
+    const int32_t d1 = (int32_t)(uint32_t)(s->tab.key[21 + 32 + lane] >> 32) - (int32_t)mean;
+    uint32_t ssq = (uint32_t)(d0 * d0) + (uint32_t)(d1 * d1);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ssq += __shfl_xor_sync(0xffffffffu, ssq, o);
+    return ssq / 64;
+}
+
 // Step C: after the probe — 8x8-variance scaling (:1416-1441) and picture clipping (:1470-1561).
 template <class S>
 __device__ void plan_int_c(S *s, const DevJob &J) {
@@ -602,13 +618,7 @@ __device__ void plan_int_c(S *s, const DevJob &J) {
     int16_t sa_w = (int16_t)s->fp_sa_w, sa_h = (int16_t)s->fp_sa_h;
     const int16_t xc = s->fp_xc, yc = s->fp_yc;
     if (s->fp_probe) {
-        const uint32_t mean = (uint32_t)(s->tab.key[0] >> 32) / 64;
-        uint32_t ssq = 0;
-        for (int i = 0; i < 64; ++i) {
-            const int32_t d = (int32_t)(uint32_t)(s->tab.key[21 + i] >> 32) - (int32_t)mean;
-            ssq += (uint32_t)(d * d);
-        }
-        const uint32_t var = ssq / 64;
+        const uint32_t var = s->fp_var; // variance of the 64 probe 8x8 SADs, computed lane-parallel by the caller (probe_variance)
         if (var > p.me_sr_mult2_th) {
             sa_w = (int16_t)((max(1, sa_w * 3 / 2) + 7) & ~0x7);
             sa_h = (int16_t)max(1, sa_h * 3 / 2);

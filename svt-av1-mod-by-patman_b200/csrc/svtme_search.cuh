@@ -31,13 +31,17 @@
 #ifndef SVTME_HME_ARENA_BYTES
 #define SVTME_HME_ARENA_BYTES (32 * 1024) // HME engine: the tallest pre-HME window (8x400, 20.7 KB) plus its wide twin (7.9 KB)
 #endif
+#ifndef SVTME_INT_SMALL_THREADS
+#define SVTME_INT_SMALL_THREADS 64 // small full-pel areas: one row lane per CTA (a 3-row area wastes no lane), more CTAs in flight
+#endif
 #ifndef SVTME_INT_SMALL_CTAS_PER_SM
-#define SVTME_INT_SMALL_CTAS_PER_SM 8
+#define SVTME_INT_SMALL_CTAS_PER_SM 12
 #endif
 #ifndef SVTME_HME_CTAS_PER_SM
 #define SVTME_HME_CTAS_PER_SM 4
 #endif
-#define SVTME_FP_YL (SVTME_THREADS / 64) // row lanes of the full-pel engine
+#define FP_NT ((int)blockDim.x)   // the full-pel engine adapts to the CTA size of its kernel (64 or 128 threads)
+#define SVTME_FP_YL (FP_NT >> 6) // row lanes of the full-pel engine: 64-thread groups share one row lane
 #ifndef SVTME_FP_SMALL_ARENA_BYTES
 #define SVTME_FP_SMALL_ARENA_BYTES (10 * 1024) // raw tile of a small full-pel window: up to 78 rows x 128 bytes
 #endif
@@ -66,12 +70,12 @@ __device__ __noinline__ void stage_window4(uint8_t *arena, const uint8_t *__rest
     const int total = rows * nwords;
     const uint32_t mg = 0xFFFFFFFFu / (uint32_t)nwords + 1u; // exact for total < 2^16
     constexpr int U = 4;
-    for (int base = threadIdx.x; base < total; base += U * SVTME_THREADS) {
+    for (int base = threadIdx.x; base < total; base += U * FP_NT) {
         uint32_t w0[U], w1[U], w2[U], mis[U];
         uint8_t *dst[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const int i = base + u * SVTME_THREADS;
+            const int i = base + u * FP_NT;
             if (i < total) {
                 const int R = (int)__umulhi((uint32_t)i, mg), kw = i - R * nwords;
                 const uintptr_t ai = reinterpret_cast<uintptr_t>(g + (size_t)R * gstride);
@@ -85,7 +89,7 @@ __device__ __noinline__ void stage_window4(uint8_t *arena, const uint8_t *__rest
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            if (base + u * SVTME_THREADS < total) {
+            if (base + u * FP_NT < total) {
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
                     const uint32_t o = c + mis[u]; // byte offset of phase c inside (w0,w1,w2)
@@ -1007,7 +1011,7 @@ __device__ __forceinline__ void fp_stage_raw(uint8_t *arena, const uint8_t *__re
                                              int pitch) {
     const int total = rows * nch;
     const uint32_t mg = 0xFFFFFFFFu / (uint32_t)nch + 1u;
-    for (int i = threadIdx.x; i < total; i += SVTME_THREADS) {
+    for (int i = threadIdx.x; i < total; i += FP_NT) {
         const int R = (int)__umulhi((uint32_t)i, mg), ch = i - R * nch;
         const uint4 v = __ldg(reinterpret_cast<const uint4 *>(g16 + (size_t)R * gstride) + ch);
         uint2 *d = reinterpret_cast<uint2 *>(arena + fp_raw_rowoff(R, pitch) + 16 * ch);
@@ -1048,7 +1052,7 @@ __device__ __noinline__ void fullpel_search(const uint8_t *src64, const uint8_t 
             __syncthreads();
             if (mode == FP_COPIES) stage_window4(arena, tile0, ref_stride, rows, m, 4, copy_bytes, words);
             if (mode == FP_RAW) fp_stage_raw(arena, tile0 - mis, ref_stride, rows, nch, pitch);
-            for (int i = threadIdx.x; i < SVTME_PU_COUNT; i += SVTME_THREADS) tab->tile_best[i] = ~0u;
+            for (int i = threadIdx.x; i < SVTME_PU_COUNT; i += FP_NT) tab->tile_best[i] = ~0u;
             __syncthreads();
             if (mode == FP_DIRECT) {
                 if (G == 2)
@@ -1071,16 +1075,16 @@ __device__ __noinline__ void fullpel_search(const uint8_t *src64, const uint8_t 
             else
                 fp_tile<8, FP_COPIES>(src64, arena, copy_bytes, m, tw, th, sub_sad, tab);
             __syncthreads();
-            if (threadIdx.x < SVTME_PU_COUNT) {
-                const uint32_t k = tab->tile_best[threadIdx.x];
+            for (int pu = threadIdx.x; pu < SVTME_PU_COUNT; pu += FP_NT) {
+                const uint32_t k = tab->tile_best[pu];
                 if (k != ~0u) {
                     const uint32_t sad = k >> FP_IDX_BITS, idx = k & ((1u << FP_IDX_BITS) - 1);
                     const int gy = ty0 + (int)(idx / FP_TW), gx = tx0 + (int)(idx % FP_TW);
                     const unsigned long long key =
                         ((unsigned long long)sad << 32) | (order_base + (uint32_t)gy * (uint32_t)sa_w + (uint32_t)gx);
-                    if (key < tab->key[threadIdx.x]) {
-                        tab->key[threadIdx.x] = key;
-                        tab->mv[threadIdx.x] = ((uint32_t)(uint16_t)(oy + gy) << 16) | (uint16_t)(ox + gx);
+                    if (key < tab->key[pu]) {
+                        tab->key[pu] = key;
+                        tab->mv[pu] = ((uint32_t)(uint16_t)(oy + gy) << 16) | (uint16_t)(ox + gx);
                     }
                 }
             }
@@ -1096,7 +1100,7 @@ __device__ __noinline__ void fullpel_search(const uint8_t *src64, const uint8_t 
 __device__ __noinline__ void fullpel_probe(const uint8_t *src64, const uint8_t *ref0, int ref_stride, int mvx, int mvy, bool sub_sad,
                               uint32_t order, FpTables *tab) {
     const int tid = threadIdx.x;
-    for (int vt = tid; vt < 256; vt += SVTME_THREADS) { // 256 virtual threads: 64 8x8 blocks x 4 row pairs
+    for (int vt = tid; vt < 256; vt += FP_NT) { // 256 virtual threads: 64 8x8 blocks x 4 row pairs
         const int e = vt >> 2, q = vt & 3;
         const int b = e >> 2, k = e & 3;
         const int bx = ((b >> 2) & 1) * 2 + (b & 1), by = ((b >> 3) & 1) * 2 + ((b >> 1) & 1);
@@ -1131,11 +1135,11 @@ __device__ __noinline__ void fullpel_probe(const uint8_t *src64, const uint8_t *
         tab->tile_best[tid] = sum;
     }
     __syncthreads();
-    if (tid < SVTME_PU_COUNT) {
-        const unsigned long long key = ((unsigned long long)tab->tile_best[tid] << 32) | order;
-        if (key < tab->key[tid]) {
-            tab->key[tid] = key;
-            tab->mv[tid] = ((uint32_t)(uint16_t)mvy << 16) | (uint16_t)mvx;
+    for (int pu = tid; pu < SVTME_PU_COUNT; pu += FP_NT) {
+        const unsigned long long key = ((unsigned long long)tab->tile_best[pu] << 32) | order;
+        if (key < tab->key[pu]) {
+            tab->key[pu] = key;
+            tab->mv[pu] = ((uint32_t)(uint16_t)mvy << 16) | (uint16_t)mvx;
         }
     }
     __syncthreads();

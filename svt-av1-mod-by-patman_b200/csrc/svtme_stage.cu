@@ -41,9 +41,7 @@ __host__ __device__ __forceinline__ bool l0_dependent(const SvtMeParams &p) { //
 enum { S_INIT = 0, S_ZZ, S_PREHME1, S_PREHME2, S_L0A, S_L0B, S_L1, S_L2, S_N };
 
 template <int STEP>
-__global__ void __launch_bounds__(128) scalar_kernel(WideArgs a) {
-    const int gid = blockIdx.x * blockDim.x + threadIdx.x;
-    if (gid >= a.n_b64_total) return;
+__device__ __forceinline__ void scalar_step(const WideArgs &a, int gid) {
     const DevJob &J = a.jobs[gid / a.b64_per_job];
     const uint32_t b64 = (uint32_t)(gid % a.b64_per_job);
     const SvtMeParams &p = J.prm;
@@ -106,6 +104,16 @@ __global__ void __launch_bounds__(128) scalar_kernel(WideArgs a) {
         set_final_search_centre(s, p);
         if (p.enable_hme_flag) hme_prune_ref_and_adjust_sr(s, p);
     }
+}
+
+// Steps [FIRST, LAST] back to back in one launch: used where no search round separates them in this batch
+// (e.g. the two pre-HME post steps when list 1 does not wait for list 0).
+template <int FIRST, int LAST>
+__global__ void __launch_bounds__(128) scalar_kernel(WideArgs a) {
+    const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= a.n_b64_total) return;
+    scalar_step<FIRST>(a, gid);
+    if (LAST != FIRST) scalar_step<LAST>(a, gid);
 }
 
 // ---------------------------------------------------------------- HME engine launch (one CTA per b64)
@@ -550,7 +558,7 @@ struct IntSlots {
     int8_t slot[NL * NR];
 };
 template <bool SMALL>
-__global__ void __launch_bounds__(SVTME_THREADS, SMALL ? SVTME_INT_SMALL_CTAS_PER_SM : SVTME_CTAS_PER_SM)
+__global__ void __launch_bounds__(SMALL ? SVTME_INT_SMALL_THREADS : SVTME_THREADS, SMALL ? SVTME_INT_SMALL_CTAS_PER_SM : SVTME_CTAS_PER_SM)
     int_kernel(WideArgs a, IntSlots sl) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     IntSmem<SMALL> *sm = reinterpret_cast<IntSmem<SMALL> *>(smem_raw);
@@ -573,16 +581,16 @@ __global__ void __launch_bounds__(SVTME_THREADS, SMALL ? SVTME_INT_SMALL_CTAS_PE
     }
     const int org_x = g->org_x, org_y = g->org_y;
     // svt_initialize_buffer_32bits(p_sb_best_sad, 21, 1, MAX_SAD_VALUE) :1368
-    if (tid < SVTME_PU_COUNT) {
-        s->tab.key[tid] = (unsigned long long)SVTME_MAX_SAD_VALUE << 32;
-        s->tab.mv[tid] = 0;
+    for (int pu = tid; pu < SVTME_PU_COUNT; pu += (int)blockDim.x) {
+        s->tab.key[pu] = (unsigned long long)SVTME_MAX_SAD_VALUE << 32;
+        s->tab.mv[pu] = 0;
     }
     __syncthreads();
     const DevJob &J = sm->job;
     const SvtMeParams &p = J.prm;
     {
         const DevPlane &f = J.cur.lvl[0];
-        for (int i = tid; i < 256; i += SVTME_THREADS) { // 64 rows x 4 chunks of 16 bytes
+        for (int i = tid; i < 256; i += (int)blockDim.x) { // 64 rows x 4 chunks of 16 bytes
             const int r = i >> 2, c4 = i & 3;
             *reinterpret_cast<uint4 *>(&sm->src64[r * 64 + c4 * 16]) =
                 *reinterpret_cast<const uint4 *>(f.at(org_x + c4 * 16, org_y + r));
@@ -616,7 +624,14 @@ __global__ void __launch_bounds__(SVTME_THREADS, SMALL ? SVTME_INT_SMALL_CTAS_PE
         const int xc = s->fp_xc, yc = s->fp_yc;
         fullpel_probe(sm->src64, pl.at(org_x + xc, org_y + yc), pl.stride, xc, yc, sub_sad, 1, &s->tab);
         work += 64ull * (sub_sad ? 32 : 64);
-        T0(plan_int_c(s, J));
+        if (tid < 32) {
+            const uint32_t var = probe_variance(s);
+            if (tid == 0) {
+                s->fp_var = var;
+                plan_int_c(s, J);
+            }
+        }
+        __syncthreads();
     }
     {
         const int ox = s->fp_ox, oy = s->fp_oy;
@@ -624,9 +639,9 @@ __global__ void __launch_bounds__(SVTME_THREADS, SMALL ? SVTME_INT_SMALL_CTAS_PE
                        &s->tab, sm->arena, (int)sizeof(sm->arena));
         work += (unsigned long long)s->fp_sa_w * s->fp_sa_h * 64ull * (sub_sad ? 32 : 64);
     }
-    if (tid < SVTME_PU_COUNT) {
-        g->best_sad[li][ri][tid] = (uint32_t)(s->tab.key[tid] >> 32);
-        g->best_mv[li][ri][tid] = s->tab.mv[tid];
+    for (int pu = tid; pu < SVTME_PU_COUNT; pu += (int)blockDim.x) {
+        g->best_sad[li][ri][pu] = (uint32_t)(s->tab.key[pu] >> 32);
+        g->best_mv[li][ri][pu] = s->tab.mv[pu];
     }
     if (tid == 0 && J.work_ops) atomicAdd(J.work_ops + 6, work);
 }
@@ -736,9 +751,9 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
     int launches = 0;
     // scalar steps always run (they also carry the bookkeeping of disabled phases); engine launches
     // that no picture of the batch needs are skipped
-    scalar_kernel<S_INIT><<<sg, 128, 0, st>>>(a);
+    scalar_kernel<S_INIT, S_INIT><<<sg, 128, 0, st>>>(a);
     if (f.zz) points_kernel<<<N, 128, 0, st>>>(a), ++launches;
-    scalar_kernel<S_ZZ><<<sg, 128, 0, st>>>(a);
+    scalar_kernel<S_ZZ, S_ZZ><<<sg, 128, 0, st>>>(a);
     mark(); // 1: zz-SAD
     // pre-HME rounds: strip mode when every picture uses the sub-sampled SAD, else one CTA per b64
     const int strip_tasks = n_jobs * NL * NR *
@@ -751,9 +766,13 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
         ++launches;
     };
     if (f.prehme) prehme_round();
-    scalar_kernel<S_PREHME1><<<sg, 128, 0, st>>>(a);
-    if (f.prehme_l1_round) prehme_round();
-    scalar_kernel<S_PREHME2><<<sg, 128, 0, st>>>(a);
+    int fused = 0;
+    if (f.prehme_l1_round) {
+        scalar_kernel<S_PREHME1, S_PREHME1><<<sg, 128, 0, st>>>(a);
+        prehme_round();
+        scalar_kernel<S_PREHME2, S_PREHME2><<<sg, 128, 0, st>>>(a);
+    } else
+        scalar_kernel<S_PREHME1, S_PREHME2><<<sg, 128, 0, st>>>(a), ++fused;
     mark(); // 2: pre-HME
     const int l0_tasks = n_jobs * NL * NR * 4 * b64_rows * ((b64_cols + STRIP_SEG - 1) / STRIP_SEG);
     auto l0_round = [&]() {
@@ -764,9 +783,12 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
         ++launches;
     };
     if (f.hme_l0) l0_round();
-    scalar_kernel<S_L0A><<<sg, 128, 0, st>>>(a);
-    if (f.hme_l0_round_b) l0_round();
-    scalar_kernel<S_L0B><<<sg, 128, 0, st>>>(a);
+    if (f.hme_l0_round_b) {
+        scalar_kernel<S_L0A, S_L0A><<<sg, 128, 0, st>>>(a);
+        l0_round();
+        scalar_kernel<S_L0B, S_L0B><<<sg, 128, 0, st>>>(a);
+    } else
+        scalar_kernel<S_L0A, S_L0B><<<sg, 128, 0, st>>>(a), ++fused;
     mark(); // 3: HME level 0
     if (f.hme_l1) {
         if (f.refine_small)
@@ -775,16 +797,19 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
             engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 2, 4);
         ++launches;
     }
-    scalar_kernel<S_L1><<<sg, 128, 0, st>>>(a);
-    mark(); // 4: HME level 1
     if (f.hme_l2) {
+        scalar_kernel<S_L1, S_L1><<<sg, 128, 0, st>>>(a);
+        mark(); // 4: HME level 1
         if (f.refine_small)
             refine_kernel<16><<<N, 128, 4 * RefineCfg<16>::BYTES, st>>>(a, 0, 5);
         else
             engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 3, 5);
         ++launches;
+        scalar_kernel<S_L2, S_L2><<<sg, 128, 0, st>>>(a);
+    } else {
+        mark(); // 4: HME level 1 (its post step runs fused with the search-centre step below)
+        scalar_kernel<S_L1, S_L2><<<sg, 128, 0, st>>>(a), ++fused;
     }
-    scalar_kernel<S_L2><<<sg, 128, 0, st>>>(a);
     mark(); // 5: HME level 2 + search centre + HME pruning
     {
         IntSlots first = {}, rest = {};
@@ -796,7 +821,7 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
         for (const IntSlots *t : {&first, &rest}) {
             if (!t->n) continue;
             if (f.small_areas)
-                int_kernel<true><<<N * t->n, SVTME_THREADS, sizeof(IntSmem<true>), st>>>(a, *t);
+                int_kernel<true><<<N * t->n, SVTME_INT_SMALL_THREADS, sizeof(IntSmem<true>), st>>>(a, *t);
             else
                 int_kernel<false><<<N * t->n, SVTME_THREADS, sizeof(IntSmem<false>), st>>>(a, *t);
             ++launches;
@@ -805,7 +830,7 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
     mark(); // 6: integer search
     finish_kernel<<<N, 128, sizeof(FinSmem), st>>>(a);
     mark(); // 7: candidates + statistics
-    g_svtme_launches += 8 + 1 + launches; // (the state clear counts itself)
+    g_svtme_launches += 8 - fused + 1 + launches; // (the state clear counts itself)
 }
 
 // ---------------------------------------------------------------- kernel-test entry points

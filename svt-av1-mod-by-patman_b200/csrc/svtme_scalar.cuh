@@ -45,6 +45,7 @@ struct StageState {
     HJob jobs[MAX_JOBS];
     JobMeta meta[MAX_JOBS];
     int n_jobs;
+    uint8_t job_idx[NL][NR][4]; // index of the job last posted for (list, ref, 2*b + a): a hint, verified against meta[] by its reader
     // integer-search hand-over between plan steps
     int fp_do, fp_sa_w, fp_sa_h, fp_ox, fp_oy, fp_probe, fp_phase;
     int16_t fp_xc, fp_yc;
@@ -64,6 +65,7 @@ struct IntState {
     HJob jobs[2];
     JobMeta meta[2];
     int n_jobs;
+    uint8_t job_idx[NL][NR][4];
     int fp_do, fp_sa_w, fp_sa_h, fp_ox, fp_oy, fp_probe, fp_phase;
     int16_t fp_xc, fp_yc;
     int c00_needed;
@@ -92,6 +94,7 @@ __device__ void add_job(S *s, const DevPlane &pl, int x_tl, int y_tl, int sa_w, 
     j.skip_even = skip;
     j.key = HME_KEY_INIT;
     s->meta[n] = JobMeta{(int8_t)li, (int8_t)ri, (int8_t)a, (int8_t)b, ox, oy};
+    s->job_idx[li][ri][(2 * b + a) & 3] = (uint8_t)n;
 }
 
 // Window clipping shared by hme_level_0/1/2 (:820-1113), with the reference's no-op left/top size

@@ -366,8 +366,8 @@ __device__ __forceinline__ void hme_item_any(const HBlk &blk, const ItemGeo &ig,
     const int xt = t - yt * ig.xt_n;
     const int byi = nbx == 1 ? b : (int)__umulhi((uint32_t)b, blk.mg_nbx);
     const int bxi = b - byi * nbx;
-    const int G = (ig.variant == 0 || ig.variant == 3) ? 2 : (ig.variant == 1 ? 4 : 8);
-    const int TY = ig.variant == 2 ? 2 : (ig.variant == 3 ? 8 : 4);
+    const int G = (ig.variant == 0 || ig.variant == 3) ? 2 : ((ig.variant == 1 || ig.variant == 4) ? 4 : 8);
+    const int TY = (ig.variant == 2 || ig.variant == 4) ? 2 : (ig.variant == 3 ? 8 : 4);
     const int yb = (yt & (rs - 1)) + (yt >> (rs - 1)) * TY * rs; // rs is 1 or 2
     const bool full = blk.nrows - 8 * byi >= 8 && blk.bw - 16 * bxi >= 16;
     if (!full) {
@@ -381,12 +381,15 @@ __device__ __forceinline__ void hme_item_any(const HBlk &blk, const ItemGeo &ig,
         hme_item_fast<4, 4>(blk, ig, arena, c, xt, yb, bxi, byi, best32);
     else if (!STRIP || ig.variant == 2)
         hme_item_fast<8, 2>(blk, ig, arena, c, xt, yb, bxi, byi, best32);
+    else if (ig.variant == 4) // short 16-wide windows (HME level 0 of near references: 16x4, 16x12 positions)
+        hme_item_fast<4, 2>(blk, ig, arena, c, xt, yb, bxi, byi, best32);
     else // tall narrow windows, chosen only where a CTA has enough items to stay balanced (strip mode)
         hme_item_fast<2, 8>(blk, ig, arena, c, xt, yb, bxi, byi, best32);
 }
 
 // Tile geometry for a (sub)area of wb x hb positions; g.need = the arena bytes it takes.
-__device__ __forceinline__ void hme_geo(const HBlk &blk, int wb, int hb, int skip_even, HGeo &g) {
+__device__ __forceinline__ void hme_geo(const HBlk &blk, int wb, int hb, int skip_even, HGeo &g,
+                                        int arena_bytes = SVTME_HME_ARENA_BYTES) {
     const int G = wb <= 8 ? 2 : (wb <= 16 ? 4 : 8);
     const int TY = G == 8 ? 2 : 4;
     const int tile_w = 4 * G;
@@ -418,7 +421,7 @@ __device__ __forceinline__ void hme_geo(const HBlk &blk, int wb, int hb, int ski
     g.mg_cpr = magic_div((uint32_t)cpr);
     g.mg_wb = magic_div((uint32_t)wb);
     g.need = (uint32_t)g.copy_bytes + (uint32_t)g.scan_n * 4u;
-    g.big = g.need > SVTME_HME_ARENA_BYTES || g.n_items >= 65536 || g.stage_units >= 65536 || hb * wb >= 65536;
+    g.big = g.need > (uint32_t)arena_bytes || g.n_items >= 65536 || g.stage_units >= 65536 || hb * wb >= 65536;
     g.arena_off = 0;
     g.sad_off = (uint32_t)g.copy_bytes;
     g.stage_base = g.item_base = g.scan_base = 0;
@@ -636,14 +639,15 @@ __device__ __noinline__ void hme_group_scan(HJob *jobs, const HGeo *geo, const H
 // One svt_sad_loop_kernel too large for the arena as a whole: its search area is tiled (row bands,
 // then columns) and every tile runs through the group helpers as a one-job group.
 // All threads of the CTA call it with identical arguments; jobs[J].key must be HME_KEY_INIT on entry.
-__device__ __noinline__ void hme_search_tiled(const HBlk &blk, HJob *jobs, int J, HPlan *pl, uint8_t *arena) {
+__device__ __noinline__ void hme_search_tiled(const HBlk &blk, HJob *jobs, int J, HPlan *pl, uint8_t *arena,
+                                              int arena_bytes = SVTME_HME_ARENA_BYTES) {
     const HJob &job = jobs[J];
     const int sa_w = job.sa_w, sa_h = job.sa_h;
     if (sa_w <= 0 || sa_h <= 0) return;
     int wt = sa_w, bh = sa_h;
     HGeo g;
     for (;;) {
-        hme_geo(blk, wt, bh, job.skip_even, g);
+        hme_geo(blk, wt, bh, job.skip_even, g, arena_bytes);
         if (!g.big) break;
         const int tile_w = 4 * g.G;
         if (bh > 8) bh = (bh + 1) / 2;
@@ -657,7 +661,7 @@ __device__ __noinline__ void hme_search_tiled(const HBlk &blk, HJob *jobs, int J
             const int hb = min(bh, sa_h - y0);
             __syncthreads(); // previous tile is done with the arena and with pl->geo[J]
             if (threadIdx.x == 0) {
-                hme_geo(blk, wb, hb, job.skip_even, g);
+                hme_geo(blk, wb, hb, job.skip_even, g, arena_bytes);
                 g.x0 = x0;
                 g.y0 = y0;
                 g.ref_off = y0 * job.stride + x0;

@@ -334,8 +334,15 @@ __device__ __forceinline__ int warp_max(int v) {
     return v;
 }
 
-__global__ void __launch_bounds__(SVTME_HME_THREADS, SVTME_HME_CTAS_PER_SM)
-    strip_kernel(WideArgs a, int cols, int rows, int wslot, int arena_limit, int mode) {
+// MODE 1 (HME level 0) has many short tasks (near references search 16x4 .. 16x12 positions): its
+// instantiation trades registers and arena for residency (6 CTAs per SM, L0_STRIP_ARENA bytes of arena)
+// so that the per-task latency chain (state -> job -> source blocks -> plan -> staging) overlaps.
+#define L0_STRIP_ARENA (16 * 1024)
+#define L0_STRIP_CTAS 6
+template <int MODE>
+__global__ void __launch_bounds__(SVTME_HME_THREADS, MODE == 0 ? SVTME_HME_CTAS_PER_SM : L0_STRIP_CTAS)
+    strip_kernel(WideArgs a, int cols, int rows, int wslot, int arena_limit) {
+    constexpr int mode = MODE;
     extern __shared__ __align__(16) uint8_t smem_raw[];
     StripSmem *sm = reinterpret_cast<StripSmem *>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -380,10 +387,12 @@ __global__ void __launch_bounds__(SVTME_HME_THREADS, SVTME_HME_CTAS_PER_SM)
         StageState *s = nullptr;
         if (lane < len) {
             s = &a.st[g0 + lane * step];
-            const int nj = s->n_jobs;
-            for (int k = 0; k < nj; ++k) {
+            // the plan step left the job's index in job_idx (a scan of meta[] here cost up to 20 dependent
+            // global loads with three warps waiting at the barrier below: 19 % of the HME level 0 launch)
+            const int nj = s->n_jobs, k = s->job_idx[li][ri][region];
+            if (k < nj) {
                 const JobMeta m = s->meta[k];
-                if (m.li == li && m.ri == ri && (mode == 0 ? m.a : m.b * 2 + m.a) == region) { found = k; break; }
+                if (m.li == li && m.ri == ri && (mode == 0 ? m.a : m.b * 2 + m.a) == region) found = k;
             }
         }
         const unsigned bal = __ballot_sync(0xffffffffu, found >= 0);
@@ -420,7 +429,9 @@ __global__ void __launch_bounds__(SVTME_HME_THREADS, SVTME_HME_CTAS_PER_SM)
             const bool live = jb.sa_w > 0 && jb.sa_h > 0;
             const int G = jb.sa_w <= 8 ? 2 : (jb.sa_w <= 16 ? 4 : 8);
             const int ny = (jb.sa_h + rs - 1) / rs;
-            const int TY = G == 8 ? 2 : ((G == 2 && ny >= 16) ? 8 : 4);
+            // y-tile: 2 rows for the widest items, 8 for tall narrow windows, and for 16-wide windows 2 where a
+            // 4-row tile would be half empty (ny = 2, 6, 10: the 16x4 / 16x12 / 16x20 windows of HME level 0)
+            const int TY = G == 8 ? 2 : ((G == 2 && ny >= 16) ? 8 : ((G == 4 && (ny & 3) != 0 && (ny & 3) <= 2 && ny <= 12) ? 2 : 4));
             const int n_yt = (ny + TY - 1) / TY;
             int rb = n, x0, y0, xs, xo, xt_n, dy, rows_s, rows_real, words, bytes, cpr, m;
             for (;;) {
@@ -463,7 +474,7 @@ __global__ void __launch_bounds__(SVTME_HME_THREADS, SVTME_HME_CTAS_PER_SM)
                 g.n_items = n_items;
                 g.G = G;
                 g.skip_even = jb.skip_even;
-                g.variant = G == 2 ? (TY == 8 ? 3 : 0) : (G == 4 ? 1 : 2);
+                g.variant = G == 2 ? (TY == 8 ? 3 : 0) : (G == 4 ? (TY == 2 ? 4 : 1) : 2);
                 g.mg_xt = magic_div((uint32_t)max(xt_n, 1));
                 g.mg_wb = magic_div((uint32_t)max(jb.sa_w, 1));
                 g.item_base = ps - n_items;
@@ -499,7 +510,7 @@ __global__ void __launch_bounds__(SVTME_HME_THREADS, SVTME_HME_CTAS_PER_SM)
             }
         } else { // one window larger than the arena: tiled like any big HME job
             const HBlk blk = make_hblk(sm->sj[ra].src, src_pitch, sm->sj[ra].bw, sm->sj[ra].nrows, rs);
-            hme_search_tiled(blk, sm->jobs, ra, &sm->plan, sm->arena);
+            hme_search_tiled(blk, sm->jobs, ra, &sm->plan, sm->arena, arena_limit);
         }
         __syncthreads();
         ra = sm->next;
@@ -729,7 +740,8 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
     static bool configured = false;
     if (!configured) {
         cudaFuncSetAttribute(engine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EngSmem));
-        cudaFuncSetAttribute(strip_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(StripSmem));
+        cudaFuncSetAttribute(strip_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(StripSmem));
+        cudaFuncSetAttribute(strip_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(StripSmem));
         cudaFuncSetAttribute(int_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IntSmem<false>));
         cudaFuncSetAttribute(int_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IntSmem<true>));
         cudaFuncSetAttribute(finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FinSmem));
@@ -760,7 +772,7 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
         (b64_cols * ((b64_rows + STRIP_SEG - 1) / STRIP_SEG) + b64_rows * ((b64_cols + STRIP_SEG - 1) / STRIP_SEG));
     auto prehme_round = [&]() {
         if (f.prehme_strip)
-            strip_kernel<<<strip_tasks, SVTME_HME_THREADS, sizeof(StripSmem), st>>>(a, b64_cols, b64_rows, 2, g_strip_arena_limit, 0);
+            strip_kernel<0><<<strip_tasks, SVTME_HME_THREADS, sizeof(StripSmem), st>>>(a, b64_cols, b64_rows, 2, g_strip_arena_limit);
         else
             engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 2);
         ++launches;
@@ -777,7 +789,12 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
     const int l0_tasks = n_jobs * NL * NR * 4 * b64_rows * ((b64_cols + STRIP_SEG - 1) / STRIP_SEG);
     auto l0_round = [&]() {
         if (f.prehme_strip && f.l0_strip)
-            strip_kernel<<<l0_tasks, SVTME_HME_THREADS, sizeof(StripSmem), st>>>(a, b64_cols, b64_rows, 3, g_strip_arena_limit, 1);
+            {
+            // the arena is the last member of StripSmem: a smaller arena is a smaller dynamic allocation
+            const int lim = g_strip_arena_limit < L0_STRIP_ARENA ? g_strip_arena_limit : L0_STRIP_ARENA;
+            strip_kernel<1><<<l0_tasks, SVTME_HME_THREADS, sizeof(StripSmem) - SVTME_HME_ARENA_BYTES + L0_STRIP_ARENA, st>>>(
+                a, b64_cols, b64_rows, 3, lim);
+        }
         else
             engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 3);
         ++launches;

@@ -45,6 +45,8 @@ struct StageState {
     HJob jobs[MAX_JOBS];
     JobMeta meta[MAX_JOBS];
     int n_jobs;
+    int16_t fp_parked[NL][NR][4]; // integer search parked for the big-arena kernel: search origin (x, y), area (w, h)
+    uint8_t fp_deferred[NL][NR];
     uint8_t job_idx[NL][NR][4]; // index of the job last posted for (list, ref, 2*b + a): a hint, verified against meta[] by its reader
     // integer-search hand-over between plan steps
     int fp_do, fp_sa_w, fp_sa_h, fp_ox, fp_oy, fp_probe, fp_phase;

@@ -564,13 +564,18 @@ struct IntSmem {
 // The (list, ref_idx) slots a launch covers: only those some picture of the batch uses. Slot 0 =
 // (list 0, ref 0) runs in a launch of its own when the other references' search areas may depend on
 // its result (:1345-1350, enable_me_sr_adjustment == 2); otherwise all slots are one launch.
+enum { INT_ALL = 0, INT_DEFER = 1, INT_RESUME = 2 };
 struct IntSlots {
     int n;
     int8_t slot[NL * NR];
 };
 template <bool SMALL>
 __global__ void __launch_bounds__(SMALL ? SVTME_INT_SMALL_THREADS : SVTME_THREADS, SMALL ? SVTME_INT_SMALL_CTAS_PER_SM : SVTME_CTAS_PER_SM)
-    int_kernel(WideArgs a, IntSlots sl) {
+    int_kernel(WideArgs a, IntSlots sl, int mode) {
+    // mode INT_ALL: the whole function. A batch whose areas CAN be large (presets <= 6) still has mostly small
+    // ones (stationary blocks divide the area by 8): the lean kernel runs first in mode INT_DEFER — plan, probe,
+    // and the search if the area turned out small, else it parks tables + area in the state block — and the
+    // big-arena kernel follows in mode INT_RESUME for the parked jobs only.
     extern __shared__ __align__(16) uint8_t smem_raw[];
     IntSmem<SMALL> *sm = reinterpret_cast<IntSmem<SMALL> *>(smem_raw);
     const int gid = blockIdx.x / sl.n, slot = sl.slot[blockIdx.x % sl.n], tid = threadIdx.x;
@@ -579,6 +584,7 @@ __global__ void __launch_bounds__(SMALL ? SVTME_INT_SMALL_THREADS : SVTME_THREAD
     if (li >= Jg.prm.num_of_list_to_search || ri >= Jg.prm.num_of_ref_pic_to_search[li]) return;
     StageState *g = &a.st[gid];
     if (!g->sr[li][ri].do_ref) return; // pruned reference: its tables keep the zero fill (:1287-1290)
+    if (mode == INT_RESUME && !g->fp_deferred[li][ri]) return;
     copy_job_to_smem(&sm->job, &Jg);
     IntState *s = &sm->st;
     if (tid == 0) {
@@ -593,8 +599,15 @@ __global__ void __launch_bounds__(SMALL ? SVTME_INT_SMALL_THREADS : SVTME_THREAD
     const int org_x = g->org_x, org_y = g->org_y;
     // svt_initialize_buffer_32bits(p_sb_best_sad, 21, 1, MAX_SAD_VALUE) :1368
     for (int pu = tid; pu < SVTME_PU_COUNT; pu += (int)blockDim.x) {
-        s->tab.key[pu] = (unsigned long long)SVTME_MAX_SAD_VALUE << 32;
-        s->tab.mv[pu] = 0;
+        // resumed job: the parked entries rank before every search position (order 0), like the probe's did
+        s->tab.key[pu] = (unsigned long long)(mode == INT_RESUME ? g->best_sad[li][ri][pu] : SVTME_MAX_SAD_VALUE) << 32;
+        s->tab.mv[pu] = mode == INT_RESUME ? g->best_mv[li][ri][pu] : 0;
+    }
+    if (mode == INT_RESUME && tid == 0) {
+        s->fp_ox = g->fp_parked[li][ri][0]; s->fp_oy = g->fp_parked[li][ri][1];
+        s->fp_sa_w = g->fp_parked[li][ri][2]; s->fp_sa_h = g->fp_parked[li][ri][3];
+        s->fp_phase = 2;
+        s->n_jobs = 0;
     }
     __syncthreads();
     const DevJob &J = sm->job;
@@ -609,6 +622,7 @@ __global__ void __launch_bounds__(SMALL ? SVTME_INT_SMALL_THREADS : SVTME_THREAD
     }
     // The three scalar steps run back to back on thread 0 whenever no search separates them
     // (no check_00_center, no 8x8-variance probe): one serial section instead of three.
+    if (mode != INT_RESUME)
     T0(plan_int_a(s, J, li, ri); s->fp_phase = 0;
        if (!s->n_jobs) {
            plan_int_b(s, J, li, ri);
@@ -644,11 +658,16 @@ __global__ void __launch_bounds__(SMALL ? SVTME_INT_SMALL_THREADS : SVTME_THREAD
         }
         __syncthreads();
     }
-    {
+    const bool park = mode == INT_DEFER && s->fp_sa_w * s->fp_sa_h > SVTME_FP_DIRECT_MAX;
+    if (!park) {
         const int ox = s->fp_ox, oy = s->fp_oy;
         fullpel_search(sm->src64, pl.at(org_x + ox, org_y + oy), pl.stride, ox, oy, s->fp_sa_w, s->fp_sa_h, sub_sad, 2,
                        &s->tab, sm->arena, (int)sizeof(sm->arena));
         work += (unsigned long long)s->fp_sa_w * s->fp_sa_h * 64ull * (sub_sad ? 32 : 64);
+    } else if (tid == 0) {
+        g->fp_parked[li][ri][0] = (int16_t)s->fp_ox; g->fp_parked[li][ri][1] = (int16_t)s->fp_oy;
+        g->fp_parked[li][ri][2] = (int16_t)s->fp_sa_w; g->fp_parked[li][ri][3] = (int16_t)s->fp_sa_h;
+        g->fp_deferred[li][ri] = 1;
     }
     for (int pu = tid; pu < SVTME_PU_COUNT; pu += (int)blockDim.x) {
         g->best_sad[li][ri][pu] = (uint32_t)(s->tab.key[pu] >> 32);
@@ -837,11 +856,12 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
             }
         for (const IntSlots *t : {&first, &rest}) {
             if (!t->n) continue;
-            if (f.small_areas)
-                int_kernel<true><<<N * t->n, SVTME_INT_SMALL_THREADS, sizeof(IntSmem<true>), st>>>(a, *t);
-            else
-                int_kernel<false><<<N * t->n, SVTME_THREADS, sizeof(IntSmem<false>), st>>>(a, *t);
+            int_kernel<true><<<N * t->n, SVTME_INT_SMALL_THREADS, sizeof(IntSmem<true>), st>>>(a, *t, f.small_areas ? INT_ALL : INT_DEFER);
             ++launches;
+            if (!f.small_areas) {
+                int_kernel<false><<<N * t->n, SVTME_THREADS, sizeof(IntSmem<false>), st>>>(a, *t, INT_RESUME);
+                ++launches;
+            }
         }
     }
     mark(); // 6: integer search

@@ -61,6 +61,37 @@ def test_stage_generic_engine_for_refinement_rounds(case, monkeypatch):
         assert np.array_equal(want[k], got[k]), "golden " + k
 
 
+def test_strip_mode_segment_splitting_and_tiled_windows():
+    """SVTME_STRIP_ARENA_LIMIT (read once when the library loads, hence a child process) shrinks the arena
+    the strip kernels may fill: segments are halved until their union fits and single windows larger than
+    the limit take the tiled path. Results must not change."""
+    import subprocess
+    code = r"""
+import os, sys, ctypes as C, importlib, numpy as np
+sys.path.insert(0, %r); sys.path.insert(0, %r); sys.path.insert(0, %r)
+import _util as U, make_golden as G
+me = importlib.import_module(U.PKG + ".me")
+for case in [c for c in G.STAGE_CASES if c[3] in (4, 8)]:
+    name, W, H, preset, tl, refs, cur, kw = case
+    seq, d = G.stage_case(*case)
+    p = U.abi.SvtMeParams()
+    assert U.product_lib().svtme_derive_params(C.byref(d), C.byref(p)) == 0
+    p = U.finish_params(p, d, cur, refs)
+    with me.MeSession(0, W, H, capacity=len(set(refs.values())) + 1) as ses:
+        for n in set(refs.values()) | {cur}:
+            ses.put_picture(n, seq[n])
+        got = ses.run_picture(p, cur, refs, deep=True)
+    want = np.load(os.path.join(%r, "stage_%%s.npz" %% name))
+    for k in want.files:
+        assert np.array_equal(want[k], got[k]), (name, k)
+print("ok")
+""" % (os.path.dirname(os.path.abspath(__file__)), GOLD, os.path.dirname(os.path.dirname(os.path.abspath(__file__))), GOLD)
+    for limit in ("1024", "4096"):
+        env = dict(os.environ, SVTME_STRIP_ARENA_LIMIT=limit)
+        r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0 and "ok" in r.stdout, (limit, r.stdout[-500:], r.stderr[-2000:])
+
+
 def test_pyramid_matches_golden_and_oracle():
     seq = U.synth_sequence(328, 200, 1, seed=5)
     want = np.load(os.path.join(GOLD, "pyramid.npz"))

@@ -569,24 +569,15 @@ struct IntSlots {
     int n;
     int8_t slot[NL * NR];
 };
+// integer_search_b64 for ONE (list, reference) of the CTA's b64; the source block and the job descriptor are
+// already in shared memory. All threads call with identical arguments.
 template <bool SMALL>
-__global__ void __launch_bounds__(SMALL ? SVTME_INT_SMALL_THREADS : SVTME_THREADS, SMALL ? SVTME_INT_SMALL_CTAS_PER_SM : SVTME_CTAS_PER_SM)
-    int_kernel(WideArgs a, IntSlots sl, int mode) {
-    // mode INT_ALL: the whole function. A batch whose areas CAN be large (presets <= 6) still has mostly small
-    // ones (stationary blocks divide the area by 8): the lean kernel runs first in mode INT_DEFER — plan, probe,
-    // and the search if the area turned out small, else it parks tables + area in the state block — and the
-    // big-arena kernel follows in mode INT_RESUME for the parked jobs only.
-    extern __shared__ __align__(16) uint8_t smem_raw[];
-    IntSmem<SMALL> *sm = reinterpret_cast<IntSmem<SMALL> *>(smem_raw);
-    const int gid = blockIdx.x / sl.n, slot = sl.slot[blockIdx.x % sl.n], tid = threadIdx.x;
-    const int li = slot / NR, ri = slot % NR;
-    const DevJob &Jg = a.jobs[gid / a.b64_per_job];
-    if (li >= Jg.prm.num_of_list_to_search || ri >= Jg.prm.num_of_ref_pic_to_search[li]) return;
-    StageState *g = &a.st[gid];
-    if (!g->sr[li][ri].do_ref) return; // pruned reference: its tables keep the zero fill (:1287-1290)
-    if (mode == INT_RESUME && !g->fp_deferred[li][ri]) return;
-    copy_job_to_smem(&sm->job, &Jg);
+__device__ __forceinline__ void int_one_ref(IntSmem<SMALL> *sm, StageState *g, int li, int ri, int mode, unsigned long long &work) {
+    const int tid = threadIdx.x;
     IntState *s = &sm->st;
+    const DevJob &J = sm->job;
+    const SvtMeParams &p = J.prm;
+    __syncthreads(); // the previous reference of this CTA is done with the state and the tables
     if (tid == 0) {
         s->org_x = g->org_x; s->org_y = g->org_y;
         s->b64_w = g->b64_w; s->b64_h = g->b64_h;
@@ -595,6 +586,12 @@ __global__ void __launch_bounds__(SMALL ? SVTME_INT_SMALL_THREADS : SVTME_THREAD
         s->div[li][ri] = g->div[li][ri];
         s->zz[li][ri] = g->zz[li][ri];
         s->best_sad[0][0][0] = g->best_sad[0][0][0];
+        if (mode == INT_RESUME) {
+            s->fp_ox = g->fp_parked[li][ri][0]; s->fp_oy = g->fp_parked[li][ri][1];
+            s->fp_sa_w = g->fp_parked[li][ri][2]; s->fp_sa_h = g->fp_parked[li][ri][3];
+            s->fp_phase = 2;
+            s->n_jobs = 0;
+        }
     }
     const int org_x = g->org_x, org_y = g->org_y;
     // svt_initialize_buffer_32bits(p_sb_best_sad, 21, 1, MAX_SAD_VALUE) :1368
@@ -603,23 +600,7 @@ __global__ void __launch_bounds__(SMALL ? SVTME_INT_SMALL_THREADS : SVTME_THREAD
         s->tab.key[pu] = (unsigned long long)(mode == INT_RESUME ? g->best_sad[li][ri][pu] : SVTME_MAX_SAD_VALUE) << 32;
         s->tab.mv[pu] = mode == INT_RESUME ? g->best_mv[li][ri][pu] : 0;
     }
-    if (mode == INT_RESUME && tid == 0) {
-        s->fp_ox = g->fp_parked[li][ri][0]; s->fp_oy = g->fp_parked[li][ri][1];
-        s->fp_sa_w = g->fp_parked[li][ri][2]; s->fp_sa_h = g->fp_parked[li][ri][3];
-        s->fp_phase = 2;
-        s->n_jobs = 0;
-    }
     __syncthreads();
-    const DevJob &J = sm->job;
-    const SvtMeParams &p = J.prm;
-    {
-        const DevPlane &f = J.cur.lvl[0];
-        for (int i = tid; i < 256; i += (int)blockDim.x) { // 64 rows x 4 chunks of 16 bytes
-            const int r = i >> 2, c4 = i & 3;
-            *reinterpret_cast<uint4 *>(&sm->src64[r * 64 + c4 * 16]) =
-                *reinterpret_cast<const uint4 *>(f.at(org_x + c4 * 16, org_y + r));
-        }
-    }
     // The three scalar steps run back to back on thread 0 whenever no search separates them
     // (no check_00_center, no 8x8-variance probe): one serial section instead of three.
     if (mode != INT_RESUME)
@@ -632,7 +613,6 @@ __global__ void __launch_bounds__(SMALL ? SVTME_INT_SMALL_THREADS : SVTME_THREAD
                s->fp_phase = 2;
            }
        });
-    unsigned long long work = 0;
     const bool sub_sad = p.me_search_method == 0;
     const DevPlane &pl = J.ref[li][ri].lvl[0];
     if (s->fp_phase == 0) { // check_00_center: two single-position SADs
@@ -645,6 +625,9 @@ __global__ void __launch_bounds__(SMALL ? SVTME_INT_SMALL_THREADS : SVTME_THREAD
                s->fp_phase = 2;
            });
     }
+#ifdef SVTME_EXP_SKIP_PROBE // timing experiment only
+    if (s->fp_phase == 1) { T0(s->fp_var = 0; plan_int_c(s, J)); s->fp_phase = 2; }
+#endif
     if (s->fp_phase == 1) {
         const int xc = s->fp_xc, yc = s->fp_yc;
         fullpel_probe(sm->src64, pl.at(org_x + xc, org_y + yc), pl.stride, xc, yc, sub_sad, 1, &s->tab);
@@ -659,7 +642,11 @@ __global__ void __launch_bounds__(SMALL ? SVTME_INT_SMALL_THREADS : SVTME_THREAD
         __syncthreads();
     }
     const bool park = mode == INT_DEFER && s->fp_sa_w * s->fp_sa_h > SVTME_FP_DIRECT_MAX;
+#ifdef SVTME_EXP_SKIP_SEARCH // timing experiment only (tools/build_variant.sh): results are wrong
+    if (false) {
+#else
     if (!park) {
+#endif
         const int ox = s->fp_ox, oy = s->fp_oy;
         fullpel_search(sm->src64, pl.at(org_x + ox, org_y + oy), pl.stride, ox, oy, s->fp_sa_w, s->fp_sa_h, sub_sad, 2,
                        &s->tab, sm->arena, (int)sizeof(sm->arena));
@@ -673,7 +660,46 @@ __global__ void __launch_bounds__(SMALL ? SVTME_INT_SMALL_THREADS : SVTME_THREAD
         g->best_sad[li][ri][pu] = (uint32_t)(s->tab.key[pu] >> 32);
         g->best_mv[li][ri][pu] = s->tab.mv[pu];
     }
-    if (tid == 0 && J.work_ops) atomicAdd(J.work_ops + 6, work);
+}
+
+// One CTA per b64: job descriptor and source block go to shared memory once, then the references of the
+// launch's slot list run one after the other (slot order = the reference's loop order, so a reference that
+// depends on (list 0, ref 0)'s result, :1345-1350, finds it in the state block).
+template <bool SMALL>
+__global__ void __launch_bounds__(SMALL ? SVTME_INT_SMALL_THREADS : SVTME_THREADS, SMALL ? SVTME_INT_SMALL_CTAS_PER_SM : SVTME_CTAS_PER_SM)
+    int_kernel(WideArgs a, IntSlots sl, int mode) {
+    // mode INT_ALL: the whole function. A batch whose areas CAN be large (presets <= 6) still has mostly small
+    // ones (stationary blocks divide the area by 8): the lean kernel runs first in mode INT_DEFER — plan, probe,
+    // and the search if the area turned out small, else it parks tables + area in the state block — and the
+    // big-arena kernel follows in mode INT_RESUME for the parked jobs only.
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    IntSmem<SMALL> *sm = reinterpret_cast<IntSmem<SMALL> *>(smem_raw);
+    const int gid = blockIdx.x, tid = threadIdx.x;
+    const DevJob &Jg = a.jobs[gid / a.b64_per_job];
+    StageState *g = &a.st[gid];
+    unsigned todo = 0; // bit per slot of the list
+    for (int k = 0; k < sl.n; ++k) {
+        const int li = sl.slot[k] / NR, ri = sl.slot[k] % NR;
+        if (li >= Jg.prm.num_of_list_to_search || ri >= Jg.prm.num_of_ref_pic_to_search[li]) continue;
+        if (!g->sr[li][ri].do_ref) continue; // pruned reference: its tables keep the zero fill (:1287-1290)
+        if (mode == INT_RESUME && !g->fp_deferred[li][ri]) continue;
+        todo |= 1u << k;
+    }
+    if (!todo) return;
+    copy_job_to_smem(&sm->job, &Jg);
+    {
+        const DevPlane &f = Jg.cur.lvl[0];
+        const int org_x = g->org_x, org_y = g->org_y;
+        for (int i = tid; i < 256; i += (int)blockDim.x) { // 64 rows x 4 chunks of 16 bytes
+            const int r = i >> 2, c4 = i & 3;
+            *reinterpret_cast<uint4 *>(&sm->src64[r * 64 + c4 * 16]) =
+                *reinterpret_cast<const uint4 *>(f.at(org_x + c4 * 16, org_y + r));
+        }
+    }
+    unsigned long long work = 0;
+    for (int k = 0; k < sl.n; ++k)
+        if (todo >> k & 1) int_one_ref<SMALL>(sm, g, sl.slot[k] / NR, sl.slot[k] % NR, mode, work);
+    if (tid == 0 && Jg.work_ops) atomicAdd(Jg.work_ops + 6, work);
 }
 
 // ---------------------------------------------------------------- pruning, candidates, statistics (one CTA per b64)
@@ -848,18 +874,21 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
     }
     mark(); // 5: HME level 2 + search centre + HME pruning
     {
-        IntSlots first = {}, rest = {};
+        // all references of a b64 in one CTA, in the reference's loop order (which also serves the dependence of
+        // the other references on (list 0, ref 0), :1345-1350)
+        // With parked searches the dependence needs (list 0, ref 0) complete before the others plan: two rounds.
+        IntSlots round[2] = {};
         for (int li = 0; li < NL; ++li)
             for (int ri = 0; ri < f.max_refs[li]; ++ri) {
-                IntSlots &t = (f.int_dependent && (li || ri)) ? rest : first;
+                IntSlots &t = round[(f.int_dependent && !f.small_areas && (li || ri)) ? 1 : 0];
                 t.slot[t.n++] = (int8_t)(li * NR + ri);
             }
-        for (const IntSlots *t : {&first, &rest}) {
-            if (!t->n) continue;
-            int_kernel<true><<<N * t->n, SVTME_INT_SMALL_THREADS, sizeof(IntSmem<true>), st>>>(a, *t, f.small_areas ? INT_ALL : INT_DEFER);
+        for (const IntSlots &t : round) {
+            if (!t.n) continue;
+            int_kernel<true><<<N, SVTME_INT_SMALL_THREADS, sizeof(IntSmem<true>), st>>>(a, t, f.small_areas ? INT_ALL : INT_DEFER);
             ++launches;
             if (!f.small_areas) {
-                int_kernel<false><<<N * t->n, SVTME_THREADS, sizeof(IntSmem<false>), st>>>(a, *t, INT_RESUME);
+                int_kernel<false><<<N, SVTME_THREADS, sizeof(IntSmem<false>), st>>>(a, t, INT_RESUME);
                 ++launches;
             }
         }

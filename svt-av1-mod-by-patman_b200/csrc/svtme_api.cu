@@ -37,11 +37,12 @@ extern "C" uint32_t svtme_sizeof_job(void) { return (uint32_t)sizeof(SvtMeJob); 
 extern "C" uint32_t svtme_sizeof_derive_input(void) { return (uint32_t)sizeof(SvtMeDeriveInput); }
 
 #define SVTME_LAUNCH_EV_RING 64
+#define SVTME_NS 4 // compute streams at most (the event ring is indexed by launch sequence number, seq % SVTME_NS = stream)
 struct Slot {
     DevPyramid pyr;
     uint64_t pic_num;
     bool used;
-    uint64_t last_reader[2]; // per compute stream: sequence number of the newest launch that reads this pyramid (a writer of the slot waits for both); 0 = none
+    uint64_t last_reader[SVTME_NS]; // per compute stream: sequence number of the newest launch that reads this pyramid (a writer of the slot waits for both); 0 = none
 };
 
 static inline size_t up16(size_t v) { return (v + 15) & ~(size_t)15; }
@@ -83,14 +84,14 @@ struct SvtMeHandle {
     cudaStream_t stream;
     bool own_stream;
     cudaStream_t h2d_stream, d2h_stream; // uploads + pyramid builds / result downloads overlap the pipeline of other batches
-    cudaStream_t stream2;                // second compute stream: queued batches alternate between `stream` and this one, so
-                                         // that the launch tails of one batch are filled by the next (pyramid builds stay on `stream`)
-    bool two_streams = true;
+    cudaStream_t xstream[SVTME_NS];      // extra compute streams ([0] unused = `stream`): queued batches rotate over n_streams
+                                         // of them, so that the launch tails of one batch are filled by the next ones
+    int n_streams = 2;
     cudaEvent_t origin_ev = nullptr; // svtme_debug_mark
     float span[3] = {0.f, 0.f, 0.f};  // last collected batch: pipeline start / end / download end, ms after the mark
     uint32_t submit_count = 0;
-    void *d_states2 = nullptr;
-    size_t states_bytes2 = 0;
+    void *x_states[SVTME_NS] = {};      // per extra compute stream: its own per-b64 scratch
+    size_t x_states_bytes[SVTME_NS] = {};
     cudaEvent_t h2d_ev, build_ev;
     cudaEvent_t launch_ev[SVTME_LAUNCH_EV_RING]; // "launch seq is done", indexed seq % ring (Batch objects and their events are recycled)
     bool build_recorded = false;
@@ -175,8 +176,13 @@ extern "C" int svtme_open(int device, uint32_t width, uint32_t height, uint32_t 
     }
     h->pool = nullptr;
     h->last_ms = 0.f;
-    h->h2d_stream = h->d2h_stream = h->stream2 = nullptr;
-    h->two_streams = getenv("SVTME_SINGLE_STREAM") == nullptr;
+    h->h2d_stream = h->d2h_stream = nullptr;
+    for (int k = 0; k < SVTME_NS; ++k) h->xstream[k] = nullptr;
+    {
+        const char *ev = getenv("SVTME_COMPUTE_STREAMS");
+        const int v = ev ? atoi(ev) : 2;
+        h->n_streams = getenv("SVTME_SINGLE_STREAM") ? 1 : (v >= 1 && v <= SVTME_NS ? v : 2);
+    }
     h->h2d_ev = h->build_ev = nullptr;
     cudaError_t e = cudaMalloc(&h->pool, h->slot_bytes * capacity);
     if (e != cudaSuccess) { delete h; return fail(SVTME_ERR_NOMEM, "svtme_open: cudaMalloc pyramid pool", e); }
@@ -185,7 +191,7 @@ extern "C" int svtme_open(int device, uint32_t width, uint32_t height, uint32_t 
     h->own_stream = true;
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->h2d_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->d2h_stream, cudaStreamNonBlocking);
-    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking);
+    for (int k = 1; k < SVTME_NS && e == cudaSuccess; ++k) e = cudaStreamCreateWithFlags(&h->xstream[k], cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->h2d_ev, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->build_ev, cudaEventDisableTiming);
     for (int k = 0; k < SVTME_PUT_RING && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&h->put[k].ev, cudaEventDisableTiming);
@@ -202,7 +208,7 @@ extern "C" int svtme_open(int device, uint32_t width, uint32_t height, uint32_t 
         }
         h->slots[i].used = false;
         h->slots[i].pic_num = 0;
-        h->slots[i].last_reader[0] = h->slots[i].last_reader[1] = 0;
+        for (int k = 0; k < SVTME_NS; ++k) h->slots[i].last_reader[k] = 0;
     }
     *out = h;
     return SVTME_OK;
@@ -212,12 +218,14 @@ extern "C" void svtme_close(SvtMeHandle *h) {
     if (!h) return;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
-    cudaStreamSynchronize(h->stream2);
+    for (int k = 1; k < SVTME_NS; ++k) cudaStreamSynchronize(h->xstream[k]);
     cudaStreamSynchronize(h->h2d_stream);
     cudaStreamSynchronize(h->d2h_stream);
     cudaFree(h->pool);
-    cudaFree(h->d_states2);
-    cudaStreamDestroy(h->stream2);
+    for (int k = 1; k < SVTME_NS; ++k) {
+        cudaFree(h->x_states[k]);
+        cudaStreamDestroy(h->xstream[k]);
+    }
     batch_free(h->sync_batch);
     for (Batch *b : h->free_batches) batch_free(b);
     for (Batch *b : h->queue) batch_free(b);
@@ -276,14 +284,14 @@ static int put_batch(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const
     // Host pictures travel on the upload stream so that they overlap the ME pipeline of earlier
     // batches; an upload into a slot must not overtake a launch that still reads the slot's old
     // content (all launches are in order on the main stream: waiting for the newest reader suffices).
-    uint64_t newest[2] = {0, 0};
+    uint64_t newest[SVTME_NS] = {};
     bool any_copy = false;
     for (uint32_t i = 0; i < n; ++i) {
         if (!luma[i]) return failf(SVTME_ERR_INVALID, "%s: null picture", who);
         const int si = find_slot(h, pic_nums[i], true);
         if (si == -2) return failf(SVTME_ERR_NOMEM, "%s: pyramid ring full (release pictures or raise capacity)", who);
         Slot &s = h->slots[si];
-        for (int k = 0; k < 2; ++k) {
+        for (int k = 0; k < SVTME_NS; ++k) {
             if (s.last_reader[k] > newest[k]) newest[k] = s.last_reader[k];
             s.last_reader[k] = 0;
         }
@@ -305,7 +313,7 @@ static int put_batch(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const
         CU(cudaEventRecord(h->h2d_ev, h->stream));
         CU(cudaStreamWaitEvent(cs, h->h2d_ev, 0));
     }
-    for (int k = 0; k < 2; ++k)
+    for (int k = 0; k < SVTME_NS; ++k)
         if (newest[k]) CU(cudaStreamWaitEvent(cs, h->launch_ev[newest[k] % SVTME_LAUNCH_EV_RING], 0));
     if (any_copy) {
         for (uint32_t i = 0; i < n; ++i) {
@@ -399,7 +407,7 @@ extern "C" int svtme_sync(SvtMeHandle *h) {
     CU(cudaSetDevice(h->device));
     CU(cudaStreamSynchronize(h->h2d_stream));
     CU(cudaStreamSynchronize(h->stream));
-    CU(cudaStreamSynchronize(h->stream2));
+    for (int k = 1; k < SVTME_NS; ++k) CU(cudaStreamSynchronize(h->xstream[k]));
     CU(cudaStreamSynchronize(h->d2h_stream));
     return SVTME_OK;
 }
@@ -460,9 +468,9 @@ static int validate_params(const SvtMeParams &p) {
 
 // Enqueue the stage pipeline of n pictures on the main stream, results into batch B's device buffer.
 static int launch_into(SvtMeHandle *h, Batch *B, const SvtMeJob *jobs, uint32_t n, int si = 0) {
-    cudaStream_t st = si ? h->stream2 : h->stream;
-    void *&d_states = si ? h->d_states2 : h->d_states;
-    size_t &states_bytes = si ? h->states_bytes2 : h->states_bytes;
+    cudaStream_t st = si ? h->xstream[si] : h->stream;
+    void *&d_states = si ? h->x_states[si] : h->d_states;
+    size_t &states_bytes = si ? h->x_states_bytes[si] : h->states_bytes;
     if (B->jobs_pending) CU(cudaEventSynchronize(B->jobs_ev)); // the previous job array has left the pinned buffer
     B->jobs_pending = false;
     if (n > B->jobs_cap) {
@@ -485,7 +493,7 @@ static int launch_into(SvtMeHandle *h, Batch *B, const SvtMeJob *jobs, uint32_t 
         // synchronous batch may still be downloading only if the caller never fetched: wait for it
         CU(cudaStreamSynchronize(h->d2h_stream));
         CU(cudaStreamSynchronize(h->stream));
-        CU(cudaStreamSynchronize(h->stream2));
+        for (int k = 1; k < SVTME_NS; ++k) CU(cudaStreamSynchronize(h->xstream[k]));
         cudaFree(B->ob.dev);
         cudaFreeHost(B->ob.host);
         B->ob = OutBuffers();
@@ -493,8 +501,8 @@ static int launch_into(SvtMeHandle *h, Batch *B, const SvtMeJob *jobs, uint32_t 
         CU(cudaMallocHost(&B->ob.host, total));
         B->ob.bytes = total;
     }
-    // sequence numbers keep the stream parity: seq % 2 == si (the event ring is indexed by seq)
-    h->seq += 1 + ((h->seq + 1 + si) & 1);
+    // sequence numbers name their stream: seq % SVTME_NS == si (the event ring is indexed by seq)
+    do ++h->seq; while ((int)(h->seq % SVTME_NS) != si);
     B->seq = h->seq;
     B->n = n;
     B->total = total;
@@ -659,7 +667,7 @@ extern "C" int svtme_submit_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint3
         h->free_batches.pop_back();
     } else if (!(B = batch_new()))
         return fail(SVTME_ERR_NOMEM, "svtme_submit_pictures: batch allocation");
-    int rc = launch_into(h, B, jobs, n, h->two_streams ? (int)(h->submit_count++ & 1) : 0);
+    int rc = launch_into(h, B, jobs, n, (int)(h->submit_count++ % (uint32_t)h->n_streams));
     if (rc) {
         h->free_batches.push_back(B);
         return rc;
@@ -759,7 +767,7 @@ extern "C" int svtme_last_work_ops(SvtMeHandle *h, uint64_t *ops) {
     std::lock_guard<std::mutex> lk(h->mu);
     CU(cudaSetDevice(h->device));
     CU(cudaStreamSynchronize(h->stream));
-    CU(cudaStreamSynchronize(h->stream2));
+    for (int k = 1; k < SVTME_NS; ++k) CU(cudaStreamSynchronize(h->xstream[k]));
     uint64_t sum = 0;
     if (!h->last) return fail(SVTME_ERR_NOTFOUND, "svtme_last_work_ops: nothing launched");
     for (size_t o : h->last->work_off) {
@@ -778,7 +786,7 @@ extern "C" int svtme_last_phase_work(SvtMeHandle *h, uint64_t *ops, uint32_t n) 
     std::lock_guard<std::mutex> lk(h->mu);
     CU(cudaSetDevice(h->device));
     CU(cudaStreamSynchronize(h->stream));
-    CU(cudaStreamSynchronize(h->stream2));
+    for (int k = 1; k < SVTME_NS; ++k) CU(cudaStreamSynchronize(h->xstream[k]));
     if (n > SVTME_PHASES) n = SVTME_PHASES;
     for (uint32_t k = 0; k < n; ++k) ops[k] = 0;
     if (!h->last) return fail(SVTME_ERR_NOTFOUND, "svtme_last_phase_work: nothing launched");
@@ -797,7 +805,7 @@ extern "C" int svtme_last_phase_ms(SvtMeHandle *h, float *ms, uint32_t n) {
     std::lock_guard<std::mutex> lk(h->mu);
     CU(cudaSetDevice(h->device));
     CU(cudaStreamSynchronize(h->stream));
-    CU(cudaStreamSynchronize(h->stream2));
+    for (int k = 1; k < SVTME_NS; ++k) CU(cudaStreamSynchronize(h->xstream[k]));
     if (n > SVTME_PHASES) n = SVTME_PHASES;
     if (!h->last) return fail(SVTME_ERR_NOTFOUND, "svtme_last_phase_ms: nothing launched");
     for (uint32_t k = 0; k < n; ++k) {

@@ -157,6 +157,10 @@ def main():
     ap.add_argument("--sharding", default="stream", choices=["stream", "picture"],
                     help="N>1: 'stream' = one independent stream per rank (weak scaling, BASELINE configs[4]); "
                          "'picture' = ONE stream, pictures dealt round-robin to the ranks (strong scaling, configs[3])")
+    ap.add_argument("--pyramids", default="rebuild", choices=["rebuild", "nccl"],
+                    help="--sharding picture: 'rebuild' = every GPU builds the pyramids it needs from the frames; 'nccl' = "
+                         "picture p is uploaded and built on GPU p %% N only and sent (NCCL over NVLink) "
+                         "into the ring slots of the GPUs that reference it")
     ap.add_argument("--e2e-chunks", default="4,12,16", help="pictures per chunk of the pipelined end-to-end run "
                     "(decode order; the last value repeats)")
     ap.add_argument("--e2e-depth", type=int, default=2, help="chunks in flight before the oldest one is collected")
@@ -175,7 +179,9 @@ def main():
               "b64_per_frame": n_b64, "me_pictures_per_step": F - 1, "pyramids_per_step": F,
               "l2": "inputs larger than L2: each step touches %.0f MB of frames+pyramids (L2 126 MB)" % (F * W * H * 2.7 / 1e6),
               "sharding": "one independent stream per GPU (weak)" if args.sharding == "stream" else
-                          "one stream, pictures round-robin over GPUs in decode order, each GPU builds the pyramids it needs (strong)"}
+                          "one stream, pictures round-robin over GPUs in decode order, " +
+                          ("each GPU builds the pyramids it needs (strong)" if args.pyramids == "rebuild" else
+                           "picture p built on GPU p % N and sent over NCCL/NVLink to the GPUs that reference it (strong)")}
     abi = importlib.import_module(PKG + ".abi")
     gop = importlib.import_module(PKG + ".gop")
     synth = importlib.import_module(PKG + ".synth")
@@ -228,9 +234,14 @@ def main():
     torch.cuda.set_stream(stream)
     ses.set_stream(stream.cuda_stream)
     specs = build_specs(abi, gop, wl, ses.derive_params)
+    share = None
     if by_picture:
         mine = shard.rank_plan(len(specs), world, rank)
         frames_here = shard.pictures_for(specs, mine)
+        if args.pyramids == "nccl":
+            needed = [shard.pictures_for(specs, shard.rank_plan(len(specs), world, r)) for r in range(world)]
+            wanted = sorted({p for need in needed for p in need})
+            share = dict(plan=shard.sharing_plan(needed, world), owned=[p for p in wanted if shard.pyramid_owner(p, world) == rank])
         specs = [specs[i] for i in mine]
     else:
         frames_here = list(range(F))
@@ -238,8 +249,19 @@ def main():
     frame_bytes = W * H
     d2h_bytes = sum(a.nbytes for o in outs for a in o.values())
 
+    def put_shared(base_ptr, device):
+        """Owners upload + build, then every pyramid another GPU references is broadcast into its ring slot there."""
+        ses.put_pictures(share["owned"], [base_ptr + f * frame_bytes for f in share["owned"]], W, device=device)
+        ses.sync()  # the builds run on the library's upload stream; the collective must see them done
+        if "slot_bytes" not in share:
+            share["slot_bytes"] = sum(ses.plane_device_ptr(share["owned"][0], l)[1] for l in range(3))
+        share["moved"] = shard.share_pyramids(ses, share["plan"], rank, dist, torch, share["slot_bytes"], share.setdefault("cache", {}))
+
     def step_resident():
-        ses.put_pictures(frames_here, [dev.data_ptr() + f * frame_bytes for f in frames_here], W, device=True)
+        if share:
+            put_shared(dev.data_ptr(), True)
+        else:
+            ses.put_pictures(frames_here, [dev.data_ptr() + f * frame_bytes for f in frames_here], W, device=True)
         ses.launch_jobs(jobs)
 
     # e2e: the look-ahead window is processed in decode order, chunk by chunk, through the queued form
@@ -259,9 +281,32 @@ def main():
                     need.append(f)
         cj, co = ses.make_jobs(part, deep=False)
         chunks.append((need, [host.data_ptr() + f * frame_bytes for f in need], cj, co))
-    e2e_frames = len(have)
+    e2e_frames = len(share["owned"]) if share else len(have)
+    sharing_info = None
+    if share:
+        # one-time check outside the timed region: a pyramid received over NCCL equals the one built locally
+        put_shared(dev.data_ptr(), True)
+        torch.cuda.synchronize()
+        foreign = [p for p in frames_here if shard.pyramid_owner(p, world) != rank][:3]
+        with me.MeSession(local_rank, W, H, capacity=1) as chk:
+            for pnum in foreign:
+                chk.put_picture_device(pnum, dev.data_ptr() + pnum * frame_bytes, W)
+                for lvl in range(3):
+                    if not np.array_equal(chk.get_plane(pnum, lvl), ses.get_plane(pnum, lvl)):
+                        raise RuntimeError("rank %d: pyramid of picture %d (level %d) received over NCCL differs from a local build"
+                                           % (rank, pnum, lvl))
+                chk.release_picture(pnum)
+        sharing_info = {"collective": "ncclSend/ncclRecv of the three padded planes of a ring slot, one NCCL group per step (torch.distributed.batch_isend_irecv, in place)",
+                        "pictures_shared_per_step": len(share["plan"]), "bytes_per_step": int(share["moved"]),
+                        "pictures_built_here": len(share["owned"]), "verified_against_local_build": foreign}
+
+    def step_e2e_shared():
+        put_shared(host.data_ptr(), False)
+        ses.run_jobs(jobs)
 
     def step_e2e():
+        if share:
+            return step_e2e_shared()
         for c, (need, ptrs, cj, _) in enumerate(chunks):
             if need:
                 ses.put_pictures(need, ptrs, W, device=False)
@@ -352,6 +397,7 @@ def main():
                         "d2h_bytes_per_step": d2h_bytes,
                         "frames_per_s": n_streams * F / (ms_e2e / args.steps * 1e-3), "ms_per_step": ms_e2e / args.steps},
                 "gpu_launches": int(launches),
+                **({"pyramid_sharing": sharing_info} if sharing_info else {}),
                 # the dominant launch slot of the pipeline (at every preset measured: the pre-HME round =
                 # one engine_kernel launch + its two scalar steps); the whole pipeline is given next to it
                 "roofline": {"bound": "int_alu", "kernel": "engine_kernel, launch slot '%s' (%.0f%% of the pipeline time)"

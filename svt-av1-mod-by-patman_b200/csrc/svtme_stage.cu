@@ -337,8 +337,12 @@ __device__ __forceinline__ int warp_max(int v) {
 // MODE 1 (HME level 0) has many short tasks (near references search 16x4 .. 16x12 positions): its
 // instantiation trades registers and arena for residency (6 CTAs per SM, L0_STRIP_ARENA bytes of arena)
 // so that the per-task latency chain (state -> job -> source blocks -> plan -> staging) overlaps.
+#ifndef L0_STRIP_ARENA
 #define L0_STRIP_ARENA (16 * 1024)
+#endif
+#ifndef L0_STRIP_CTAS
 #define L0_STRIP_CTAS 6
+#endif
 template <int MODE>
 __global__ void __launch_bounds__(SVTME_HME_THREADS, MODE == 0 ? SVTME_HME_CTAS_PER_SM : L0_STRIP_CTAS)
     strip_kernel(WideArgs a, int cols, int rows, int wslot, int arena_limit) {

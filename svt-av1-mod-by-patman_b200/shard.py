@@ -1,4 +1,5 @@
-"""Multi-GPU host logic: one process per GPU, pictures (or streams) sharded, no data-path collective.
+"""Multi-GPU host logic: one process per GPU, pictures (or streams) sharded; the only data-path collective is
+the optional broadcast of source-picture pyramids between GPUs (share_pyramids).
 
 A PAME job needs only SOURCE-picture pyramids (Source/Lib/Codec/me_process.c:248-262 resolves
 `ref_pa_pic_ptr_array` to pa-reference objects, never to reconstructed pictures), so every non-intra
@@ -75,3 +76,66 @@ def max_over_ranks(value_ms: float, dist=None, device=None) -> float:
     t = torch.tensor([float(value_ms)], dtype=torch.float64, device=device or "cpu")
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
+
+
+# ---------------------------------------------------------------- pyramids shared over NVLink
+def pyramid_owner(picture_number: int, world_size: int) -> int:
+    """The rank that uploads picture `picture_number` and builds its pyramid: picture % world_size."""
+    return int(picture_number) % int(world_size)
+
+
+def sharing_plan(needed_by_rank: Sequence[Sequence[int]], world_size: int) -> List[Tuple[int, int, List[int]]]:
+    """needed_by_rank[r] = pictures whose pyramids rank r must hold. Returns, in picture order, the
+    broadcasts to run: (picture, owner rank, ranks that need it besides the owner). Pictures nobody but the
+    owner needs are left out. Every rank computes the same plan (collectives must be issued in one order)."""
+    plan = []
+    for pic in sorted({p for need in needed_by_rank for p in need}):
+        owner = pyramid_owner(pic, world_size)
+        users = [r for r in range(world_size) if r != owner and pic in set(needed_by_rank[r])]
+        if users:
+            plan.append((pic, owner, users))
+    return plan
+
+
+class _DeviceBytes:
+    """A span of device memory as a CUDA-array-interface object (torch.as_tensor aliases it, no copy)."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+
+
+def share_pyramids(ses, plan, rank: int, dist, torch, slot_bytes: int, cache=None):
+    """Run the transfers of `plan` (sharing_plan) on the initialised NCCL group: the owner's pyramid (the three
+    padded planes of one ring slot, contiguous in HBM) goes straight into the slot the referencing ranks adopted
+    for the picture — point-to-point `ncclSend` / `ncclRecv` over NVLink / NVSwitch, all pictures of the step in ONE
+    NCCL group (one launch; 60 separate broadcasts cost 2 ms of launch latency at 1080p), no host copy, no
+    rebuild. The caller orders this after the owners' pyramid builds (ses.sync()); the transfers are enqueued
+    behind the current torch stream and the launches that follow wait for them. `cache` (a dict the caller keeps
+    while the pictures stay resident) remembers the slot tensors: a ring slot does not move. Returns the bytes
+    this rank sent + received."""
+    ops, moved = [], 0
+    cache = {} if cache is None else cache
+    for pic, owner, users in plan:
+        if rank != owner and rank not in users:
+            continue
+        t = cache.get(pic)
+        if t is None:
+            if rank != owner:
+                ses.adopt_picture(pic)
+            p0, n0 = ses.plane_device_ptr(pic, 0)
+            p1, n1 = ses.plane_device_ptr(pic, 1)
+            p2, n2 = ses.plane_device_ptr(pic, 2)
+            if p1 != p0 + n0 or p2 != p1 + n1 or n0 + n1 + n2 != int(slot_bytes):
+                raise RuntimeError("pyramid planes of a slot are expected to be contiguous")
+            t = cache[pic] = torch.as_tensor(_DeviceBytes(p0, slot_bytes), device="cuda")
+        if rank == owner:
+            for u in users:
+                ops.append(dist.P2POp(dist.isend, t, u))
+                moved += slot_bytes
+        else:
+            ops.append(dist.P2POp(dist.irecv, t, owner))
+            moved += slot_bytes
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+    return moved

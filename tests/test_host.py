@@ -2,6 +2,7 @@
 svt_aom_sig_deriv_me (golden grid), ABI symbol export, struct layout, error behaviour."""
 import ctypes as C
 import gzip
+import importlib
 import json
 import os
 import re
@@ -76,3 +77,24 @@ def test_synth_sequence_is_deterministic():
     a = U.synth_sequence(128, 64, 3, seed=4)
     b = U.synth_sequence(128, 64, 3, seed=4)
     assert np.array_equal(a, b) and a.dtype == np.uint8 and a.shape == (3, 64, 128)
+
+
+def test_pyramid_sharing_plan():
+    """Picture p is built on rank p % N; a broadcast is planned for every picture another rank references,
+    in one global order (every rank must issue the same collectives)."""
+    shard = importlib.import_module(U.PKG + ".shard")
+    gop = importlib.import_module(U.PKG + ".gop")
+    jobs = gop.ra_jobs(33, 5, 3, 2)
+    specs = [(None, j.picture_number, j.refs) for j in jobs]
+    for world in (2, 4, 8):
+        needed = [shard.pictures_for(specs, shard.rank_plan(len(specs), world, r)) for r in range(world)]
+        plan = shard.sharing_plan(needed, world)
+        assert [p for p, _, _ in plan] == sorted(p for p, _, _ in plan)
+        for pic, owner, users in plan:
+            assert owner == pic % world and owner not in users and users
+            for r in users:
+                assert pic in needed[r]
+        planned = {p: set(u) for p, _, u in plan}
+        for r in range(world):  # everything a rank needs is either its own build or comes by broadcast
+            for pic in needed[r]:
+                assert pic % world == r or r in planned[pic]

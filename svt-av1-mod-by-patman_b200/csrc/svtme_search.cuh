@@ -887,11 +887,16 @@ __device__ __noinline__ void fp_tile(const uint8_t *src64, const uint8_t *arena,
     for (int pass = 0; pass < npass; ++pass) {
         const int y = SVTME_FP_YL * pass + yl;
         for (int xt = 0; xt < xt_n; ++xt) {
+            // Positions outside the tile (x >= tw, y >= th) still read staged memory; their 8x8 accumulators start
+            // at 2^18, above every real 8x8 / 16x16 SAD, so their keys lose every minimum without a select per key.
+            const uint32_t yvalid = y < th;
             uint32_t acc[G][4];
 #pragma unroll
-            for (int j = 0; j < G; ++j)
+            for (int j = 0; j < G; ++j) {
+                const uint32_t init = (yvalid && xt * 4 * G + 4 * j + c < tw) ? 0u : (1u << 18);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) acc[j][k] = 0;
+                for (int k = 0; k < 4; ++k) acc[j][k] = init;
+            }
             for (int par = 0; par < npar; ++par) {
                 uint32_t s[8][4];
 #pragma unroll
@@ -953,23 +958,17 @@ __device__ __noinline__ void fp_tile(const uint8_t *src64, const uint8_t *arena,
                     }
                 }
             }
-            const uint32_t yvalid = y < th;
+            // keys carry the SAD as accumulated (under SUB_SAD_SEARCH the doubling is applied when the tile's minima
+            // are merged: x2 keeps the order): one multiply-add and one min per PU and position
             uint32_t v16[G];
 #pragma unroll
             for (int j = 0; j < G; ++j) {
-                const int x = xt * 4 * G + 4 * j + c;
-                const bool ok = yvalid && x < tw;
-                const uint32_t idx = (uint32_t)(y * FP_TW + x);
-                uint32_t sum = 0;
+                const uint32_t idx = (uint32_t)(y * FP_TW + xt * 4 * G + 4 * j + c);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const uint32_t sad = sub_sad ? acc[j][k] << 1 : acc[j][k];
-                    sum += sad;
-                    const uint32_t key = ok ? ((sad << FP_IDX_BITS) | idx) : ~0u;
-                    k8[k] = min(k8[k], key);
-                }
+                for (int k = 0; k < 4; ++k) k8[k] = min(k8[k], acc[j][k] * (1u << FP_IDX_BITS) + idx);
+                const uint32_t sum = (acc[j][0] + acc[j][1]) + (acc[j][2] + acc[j][3]);
                 v16[j] = sum;
-                k16 = min(k16, ok ? ((sum << FP_IDX_BITS) | idx) : ~0u);
+                k16 = min(k16, sum * (1u << FP_IDX_BITS) + idx);
             }
             int joff32, n32, joff64;
             uint32_t v32[G], v64;
@@ -1082,7 +1081,7 @@ __device__ __noinline__ void fullpel_search(const uint8_t *src64, const uint8_t 
             for (int pu = threadIdx.x; pu < SVTME_PU_COUNT; pu += FP_NT) {
                 const uint32_t k = tab->tile_best[pu];
                 if (k != ~0u) {
-                    const uint32_t sad = k >> FP_IDX_BITS, idx = k & ((1u << FP_IDX_BITS) - 1);
+                    const uint32_t sad = (k >> FP_IDX_BITS) << (sub_sad ? 1 : 0), idx = k & ((1u << FP_IDX_BITS) - 1);
                     const int gy = ty0 + (int)(idx / FP_TW), gx = tx0 + (int)(idx % FP_TW);
                     const unsigned long long key =
                         ((unsigned long long)sad << 32) | (order_base + (uint32_t)gy * (uint32_t)sa_w + (uint32_t)gx);

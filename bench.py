@@ -40,6 +40,13 @@ WORKLOADS = {
 }
 
 
+# search kernel of each launch slot of the stage pipeline (svtme_stage.cu) for SUB_SAD_SEARCH presets with small
+# HME refinement windows, i.e. every workload of this file
+SLOT_KERNELS = {"zz_sad": "points_kernel", "prehme": "strip_kernel<0>", "hme_l0": "strip_kernel<1>", "hme_l1": "refine_kernel<8>",
+                "hme_l2_centre": "refine_kernel<16>", "integer_search": "int_kernel<true> (+ int_kernel<false> for parked areas)",
+                "finish": "finish_kernel"}
+
+
 def build_specs(abi, gop, wl, derive_fn):
     """(params, cur, refs) per non-intra picture, decode order."""
     U = importlib.import_module(PKG + ".me")
@@ -398,10 +405,10 @@ def main():
                         "frames_per_s": n_streams * F / (ms_e2e / args.steps * 1e-3), "ms_per_step": ms_e2e / args.steps},
                 "gpu_launches": int(launches),
                 **({"pyramid_sharing": sharing_info} if sharing_info else {}),
-                # the dominant launch slot of the pipeline (at every preset measured: the pre-HME round =
-                # one engine_kernel launch + its two scalar steps); the whole pipeline is given next to it
-                "roofline": {"bound": "int_alu", "kernel": "engine_kernel, launch slot '%s' (%.0f%% of the pipeline time)"
-                                                           % (dom, 100 * phases[dom] / max(kernel_ms, 1e-9)),
+                # the dominant launch slot of the pipeline (its search kernel + the scalar plan/post step(s) timed with
+                # it); the whole pipeline is given next to it
+                "roofline": {"bound": "int_alu", "kernel": "%s, launch slot '%s' (%.0f%% of the pipeline time)"
+                                                           % (SLOT_KERNELS.get(dom, "stage pipeline"), dom, 100 * phases[dom] / max(kernel_ms, 1e-9)),
                              "achieved": dom_achieved, "peak": int_peak, "unit": "Tbyte-SAD/s",
                              "frac": dom_achieved / int_peak if int_peak else None, "traffic": traffic,
                              "traffic_source": traffic_src,

@@ -41,7 +41,6 @@ struct StageState {
     uint8_t performed_phme[NL][NR][2];
     uint32_t best_sad[NL][NR][SVTME_PU_COUNT], best_mv[NL][NR][SVTME_PU_COUNT];
     uint32_t me_distortion[SVTME_PU_COUNT];
-    FpTables tab;
     HJob jobs[MAX_JOBS];
     JobMeta meta[MAX_JOBS];
     int n_jobs;
@@ -52,7 +51,6 @@ struct StageState {
     int fp_do, fp_sa_w, fp_sa_h, fp_ox, fp_oy, fp_probe, fp_phase;
     int16_t fp_xc, fp_yc;
     int c00_needed;
-    unsigned long long work_ops; // sum over executed searches of positions x block_w x rows
 };
 
 // The slice of the state integer_search_b64 works on for ONE reference (int_kernel keeps it in

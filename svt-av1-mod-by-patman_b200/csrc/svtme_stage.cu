@@ -228,8 +228,11 @@ __device__ __forceinline__ void refine_rows(const uint8_t *__restrict__ src0, in
     }
 }
 
+#ifndef REFINE_CTAS_PER_SM
+#define REFINE_CTAS_PER_SM 8
+#endif
 template <int BWW>
-__global__ void __launch_bounds__(128) refine_kernel(WideArgs a, int sh, int wslot) {
+__global__ void __launch_bounds__(128, REFINE_CTAS_PER_SM) refine_kernel(WideArgs a, int sh, int wslot) {
     using Cfg = RefineCfg<BWW>;
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const int gid = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;

@@ -35,7 +35,9 @@ WORKLOADS = {
     # configs[1] of BASELINE.json: 1080p 8-bit, preset 8, 60 frames, refs 3+2 (mrp 9), 5 hierarchical levels
     "1080p_p8": dict(width=1920, height=1080, preset=8, frames=60, levels=5, n_l0=3, n_l1=2),
     # configs[2]: 4K (the ME stage sees the 8 MSBs of 10-bit input), preset 4, 120 frames, refs 4+3
-    "4k_p4": dict(width=3840, height=2160, preset=4, frames=120, levels=5, n_l0=4, n_l1=3),
+    # source depth 10: 16-bit samples = the 8-bit pattern << 2 plus two random LSBs; the boundary takes them as they are
+    # (svtme_put_pictures_10bit) and the planes hold sample >> 2, like the reference's 8-bit ME buffer
+    "4k_p4": dict(width=3840, height=2160, preset=4, frames=120, levels=5, n_l0=4, n_l1=3, bits=10),
     "small": dict(width=640, height=360, preset=8, frames=12, levels=3, n_l0=2, n_l1=1),
 }
 
@@ -180,9 +182,10 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     W, H, F = wl["width"], wl["height"], wl["frames"]
     n_b64 = ((W + 63) // 64) * ((H + 63) // 64)
-    config = {"workload": "%s: %dx%d 8-bit luma, preset %d, %d frames, refs %d+%d, %d hierarchical levels, synthetic "
-                          "translating texture + moving rectangles + noise" % (args.workload, W, H, wl["preset"], F, wl["n_l0"],
-                                                                             wl["n_l1"], wl["levels"]),
+    depth_txt = "10-bit source (16-bit samples, ME planes = sample >> 2)" if wl.get("bits") == 10 else "8-bit luma"
+    config = {"workload": "%s: %dx%d %s, preset %d, %d frames, refs %d+%d, %d hierarchical levels, synthetic "
+                          "translating texture + moving rectangles + noise" % (args.workload, W, H, depth_txt, wl["preset"], F,
+                                                                             wl["n_l0"], wl["n_l1"], wl["levels"]),
               "b64_per_frame": n_b64, "me_pictures_per_step": F - 1, "pyramids_per_step": F,
               "l2": "inputs larger than L2: each step touches %.0f MB of frames+pyramids (L2 126 MB)" % (F * W * H * 2.7 / 1e6),
               "sharding": "one independent stream per GPU (weak)" if args.sharding == "stream" else
@@ -234,7 +237,13 @@ def main():
     shard = importlib.import_module(PKG + ".shard")
     by_picture = args.sharding == "picture" and world > 1
     seq = synth.synth_sequence(W, H, F, seed=1 if by_picture else 1 + rank)
-    host = torch.from_numpy(seq).pin_memory()
+    bits = wl.get("bits", 8)
+    if bits == 10:
+        lsb = np.random.default_rng(100 + rank).integers(0, 4, size=seq.shape, dtype=np.uint16)
+        host = torch.from_numpy((seq.astype(np.uint16) << 2) | lsb).pin_memory()
+        del lsb
+    else:
+        host = torch.from_numpy(seq).pin_memory()
     dev = host.to("cuda", non_blocking=False)
     ses = me.MeSession(local_rank, W, H, capacity=F)
     stream = torch.cuda.Stream()  # a non-default stream: the library treats NULL as "use the private stream"
@@ -253,12 +262,12 @@ def main():
     else:
         frames_here = list(range(F))
     jobs, outs = ses.make_jobs(specs, deep=False)
-    frame_bytes = W * H
+    frame_bytes = W * H * (2 if bits == 10 else 1)
     d2h_bytes = sum(a.nbytes for o in outs for a in o.values())
 
     def put_shared(base_ptr, device):
         """Owners upload + build, then every pyramid another GPU references is broadcast into its ring slot there."""
-        ses.put_pictures(share["owned"], [base_ptr + f * frame_bytes for f in share["owned"]], W, device=device)
+        ses.put_pictures(share["owned"], [base_ptr + f * frame_bytes for f in share["owned"]], W, device=device, bits=bits)
         ses.sync()  # the builds run on the library's upload stream; the collective must see them done
         if "slot_bytes" not in share:
             share["slot_bytes"] = sum(ses.plane_device_ptr(share["owned"][0], l)[1] for l in range(3))
@@ -268,7 +277,7 @@ def main():
         if share:
             put_shared(dev.data_ptr(), True)
         else:
-            ses.put_pictures(frames_here, [dev.data_ptr() + f * frame_bytes for f in frames_here], W, device=True)
+            ses.put_pictures(frames_here, [dev.data_ptr() + f * frame_bytes for f in frames_here], W, device=True, bits=bits)
         ses.launch_jobs(jobs)
 
     # e2e: the look-ahead window is processed in decode order, chunk by chunk, through the queued form
@@ -297,7 +306,7 @@ def main():
         foreign = [p for p in frames_here if shard.pyramid_owner(p, world) != rank][:3]
         with me.MeSession(local_rank, W, H, capacity=1) as chk:
             for pnum in foreign:
-                chk.put_picture_device(pnum, dev.data_ptr() + pnum * frame_bytes, W)
+                chk.put_pictures([pnum], [dev.data_ptr() + pnum * frame_bytes], W, device=True, bits=bits)
                 for lvl in range(3):
                     if not np.array_equal(chk.get_plane(pnum, lvl), ses.get_plane(pnum, lvl)):
                         raise RuntimeError("rank %d: pyramid of picture %d (level %d) received over NCCL differs from a local build"
@@ -316,7 +325,7 @@ def main():
             return step_e2e_shared()
         for c, (need, ptrs, cj, _) in enumerate(chunks):
             if need:
-                ses.put_pictures(need, ptrs, W, device=False)
+                ses.put_pictures(need, ptrs, W, device=False, bits=bits)
             ses.submit_jobs(cj)
             if c >= args.e2e_depth:
                 ses.collect_jobs(chunks[c - args.e2e_depth][2])
@@ -399,7 +408,7 @@ def main():
                 "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": config,
                 "frames_per_s": n_streams * F / (ms_step * 1e-3),
                 "e2e": {"value": e2e_val, "unit": "SB/s", "h2d_bytes_per_step": e2e_frames * frame_bytes,
-                        "api": "svtme_put_pictures (pinned host luma) + svtme_submit_pictures / svtme_collect_results (results "
+                        "api": ("svtme_put_pictures_10bit (pinned host 16-bit luma)" if bits == 10 else "svtme_put_pictures (pinned host luma)") + " + svtme_submit_pictures / svtme_collect_results (results "
                                "in host SvtMeOut arrays), chunks of %s pictures, %d in flight" % (args.e2e_chunks, args.e2e_depth),
                         "d2h_bytes_per_step": d2h_bytes,
                         "frames_per_s": n_streams * F / (ms_e2e / args.steps * 1e-3), "ms_per_step": ms_e2e / args.steps},

@@ -191,6 +191,13 @@ int svtme_put_pictures(SvtMeHandle *h, uint32_t n, const uint64_t *picture_numbe
                        uint32_t stride);
 int svtme_put_pictures_device(SvtMeHandle *h, uint32_t n, const uint64_t *picture_numbers, const void *const *d_luma,
                               uint32_t stride);
+/* 10-bit sources: 16-bit samples, stride in SAMPLES. The ME planes get (uint8_t)(sample >> 2), i.e. the 8-bit buffer
+ * svt_aom_un_pack2d -> svt_enc_msb_un_pack2_d (Codec/pic_operators.c:228-244, C_DEFAULT/pack_unpack_c.c:202-218) fills
+ * and that input_padded_pic->buffer_y aliases for 10-bit encodes; the conversion is fused into the decimation kernel. */
+int svtme_put_pictures_10bit(SvtMeHandle *h, uint32_t n, const uint64_t *picture_numbers, const uint16_t *const *luma16,
+                             uint32_t stride_samples);
+int svtme_put_pictures_10bit_device(SvtMeHandle *h, uint32_t n, const uint64_t *picture_numbers, const void *const *d_luma16,
+                                    uint32_t stride_samples);
 /* Copy the padded planes back (level 0 full, 1 quarter, 2 sixteenth) incl. the reference's pads
  * (72/32/16): the CPU stages that still read them (picture statistics, TF) need them. */
 int svtme_get_plane(SvtMeHandle *h, uint64_t pic_num, int level, uint8_t *dst, uint32_t dst_stride,

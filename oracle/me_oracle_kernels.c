@@ -297,3 +297,12 @@ void orc_pyramid_free(OrcPyramid *pyr) {
     free(pyr->sixteenth.buffer_y);
     memset(pyr, 0, sizeof(*pyr));
 }
+
+/* 10-bit source -> the 8-bit plane the open-loop ME reads. Follows svt_enc_msb_un_pack2_d,
+ * Source/Lib/C_DEFAULT/pack_unpack_c.c:202-218 (called through svt_aom_un_pack2d, Codec/pic_operators.c:228-244):
+ * out = (uint8_t)(sample >> 2). */
+void orc_unpack_msb(const uint16_t *in16, uint32_t in_stride, uint8_t *out8, uint32_t out8_stride, uint32_t width,
+                    uint32_t height) {
+    for (uint32_t j = 0; j < height; ++j)
+        for (uint32_t k = 0; k < width; ++k) out8[k + (size_t)j * out8_stride] = (uint8_t)(in16[k + (size_t)j * in_stride] >> 2);
+}

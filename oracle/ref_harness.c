@@ -30,6 +30,7 @@
 #include "enc_mode_config.h"
 #include "compute_sad_c.h"
 #include "me_sad_calculation.h"
+#include "pack_unpack_c.h"
 
 #include "svtme_b200.h"
 
@@ -76,6 +77,7 @@ int ref_set_simd(int simd) {
     svt_nxm_sad_kernel                         = svt_nxm_sad_kernel_helper_c;
     svt_nxm_sad_kernel_sub_sampled             = svt_nxm_sad_kernel_helper_c;
     downsample_2d                              = svt_aom_downsample_2d_c;
+    svt_aom_un_pack2d_16_bit_src_mul4          = svt_enc_msb_un_pack2_d; /* common_dsp_rtcd.c:518, C entry */
 #ifdef REF_HAVE_AVX2
     if (simd && __builtin_cpu_supports("avx2")) {
         svt_sad_loop_kernel                       = svt_sad_loop_kernel_avx2_intrin;
@@ -390,6 +392,13 @@ int ref_me_picture(const SvtMeParams *p, const RefPyramid *cur, const RefPyramid
 }
 
 int ref_simd_level(void) { return g_simd; }
+
+/* 10-bit source -> the 8-bit plane ME reads: svt_aom_un_pack2d (Codec/pic_operators.c:228-244) with no 2-bit plane. */
+void ref_unpack_msb(const uint16_t *in16, uint32_t in_stride, uint8_t *out8, uint32_t out8_stride, uint32_t width,
+                    uint32_t height) {
+    if (g_simd < 0) ref_set_simd(0);
+    svt_aom_un_pack2d((uint16_t *)in16, in_stride, out8, out8_stride, NULL, 0, width, height);
+}
 unsigned ref_sizeof_params(void) { return (unsigned)sizeof(SvtMeParams); }
 unsigned ref_sizeof_derive_input(void) { return (unsigned)sizeof(SvtMeDeriveInput); }
 unsigned ref_sizeof_out(void) { return (unsigned)sizeof(SvtMeOut); }

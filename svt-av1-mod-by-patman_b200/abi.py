@@ -169,6 +169,8 @@ def load_library():
         "svtme_put_picture_device": (C.c_int, [vp, u64, vp, u32]),
         "svtme_put_pictures": (C.c_int, [vp, u32, P(u64), P(vp), u32]),
         "svtme_put_pictures_device": (C.c_int, [vp, u32, P(u64), P(vp), u32]),
+        "svtme_put_pictures_10bit": (C.c_int, [vp, u32, P(u64), P(vp), u32]),
+        "svtme_put_pictures_10bit_device": (C.c_int, [vp, u32, P(u64), P(vp), u32]),
         "svtme_get_plane": (C.c_int, [vp, u64, C.c_int, vp, u32, u32]),
         "svtme_release_picture": (C.c_int, [vp, u64]),
         "svtme_plane_device_ptr": (C.c_int, [vp, u64, C.c_int, P(vp), P(C.c_size_t)]),

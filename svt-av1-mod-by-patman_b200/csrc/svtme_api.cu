@@ -95,6 +95,8 @@ struct SvtMeHandle {
     cudaEvent_t h2d_ev, build_ev;
     cudaEvent_t launch_ev[SVTME_LAUNCH_EV_RING]; // "launch seq is done", indexed seq % ring (Batch objects and their events are recycled)
     bool build_recorded = false;
+    uint8_t *u16_stage = nullptr; // 16-bit input pictures of the batched build in flight (svtme_put_pictures_10bit)
+    size_t u16_bytes = 0;
     uint8_t *pool; // all planes of all slots
     size_t plane_bytes[3], slot_bytes;
     std::vector<Slot> slots;
@@ -262,9 +264,13 @@ static int find_slot(SvtMeHandle *h, uint64_t pic, bool create) {
 }
 
 // n pictures -> pyramids: (host input) n H2D copies, then 2 launches for the whole batch.
+// bits = 8: `stride` bytes between rows of one-byte samples. bits = 10: 16-bit samples (10 significant bits), `stride` in
+// SAMPLES; the planes get (uint8_t)(sample >> 2), what svt_aom_un_pack2d (pic_operators.c:228-244) leaves in the 8-bit
+// buffer that ME reads.
 static int put_batch(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const uint8_t *const *luma, uint32_t stride,
-                     bool device_src, const char *who) {
+                     bool device_src, const char *who, int bits = 8) {
     if (!h || !pic_nums || !luma || stride < h->width) return failf(SVTME_ERR_INVALID, "%s: bad argument", who);
+    const uint32_t stride_bytes = bits == 10 ? stride * 2u : stride;
     if (n == 0) return SVTME_OK;
     std::lock_guard<std::mutex> lk(h->mu);
     CU(cudaSetDevice(h->device));
@@ -298,11 +304,23 @@ static int put_batch(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const
         items[i].pyr = s.pyr;
         items[i].src = nullptr;
         items[i].src_stride = 0;
-        if (device_src && ((uintptr_t)luma[i] & 15) == 0 && (stride & 15) == 0) {
+        items[i].src_bits = bits;
+        if (device_src && ((uintptr_t)luma[i] & 15) == 0 && (stride_bytes & 15) == 0) {
             items[i].src = luma[i]; // the decimation kernel reads the caller's buffer and fills level 0 itself
-            items[i].src_stride = (int)stride;
+            items[i].src_stride = (int)stride_bytes;
         } else
             any_copy = true;
+    }
+    if (bits == 10 && any_copy) { // 16-bit pictures are copied to a staging area the decimation kernel converts from
+        const size_t need = (size_t)n * h->width * 2 * h->height;
+        if (need > h->u16_bytes) {
+            CU(cudaStreamSynchronize(h->h2d_stream)); // an earlier build may still read the old staging area
+            cudaFree(h->u16_stage);
+            h->u16_stage = nullptr;
+            h->u16_bytes = 0;
+            CU(cudaMalloc(&h->u16_stage, need));
+            h->u16_bytes = need;
+        }
     }
     // Uploads AND pyramid builds run on the upload stream: a build never queues behind the ME pipeline of an
     // earlier batch. The stream first waits for the newest reader of the slots on each compute stream (an
@@ -320,8 +338,15 @@ static int put_batch(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const
             if (items[i].src) continue;
             const DevPlane &f = items[i].pyr.lvl[0];
             // a pageable host buffer makes this copy synchronous w.r.t. the host
-            CU(cudaMemcpy2DAsync(const_cast<uint8_t *>(f.at(0, 0)), f.stride, luma[i], stride, h->width, h->height,
-                                 device_src ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, cs));
+            if (bits == 10) { // (in-order on this stream after the previous batch's conversion: the staging area is free)
+                uint8_t *dst = h->u16_stage + (size_t)i * h->width * 2 * h->height;
+                CU(cudaMemcpy2DAsync(dst, (size_t)h->width * 2, luma[i], stride_bytes, (size_t)h->width * 2, h->height,
+                                     device_src ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, cs));
+                items[i].src = dst;
+                items[i].src_stride = (int)h->width * 2;
+            } else
+                CU(cudaMemcpy2DAsync(const_cast<uint8_t *>(f.at(0, 0)), f.stride, luma[i], stride, h->width, h->height,
+                                     device_src ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, cs));
         }
     }
     CU(svtme_launch_fetch_from_host(pr.d, items, up16(sizeof(SvtmePutItem) * n), cs));
@@ -347,6 +372,18 @@ extern "C" int svtme_put_pictures_device(SvtMeHandle *h, uint32_t n, const uint6
                                          uint32_t stride) {
     return put_batch(h, n, pic_nums, reinterpret_cast<const uint8_t *const *>(d_luma), stride, true,
                      "svtme_put_pictures_device");
+}
+
+extern "C" int svtme_put_pictures_10bit(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const uint16_t *const *luma16,
+                                        uint32_t stride_samples) {
+    return put_batch(h, n, pic_nums, reinterpret_cast<const uint8_t *const *>(luma16), stride_samples, false,
+                     "svtme_put_pictures_10bit", 10);
+}
+
+extern "C" int svtme_put_pictures_10bit_device(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const void *const *d_luma16,
+                                               uint32_t stride_samples) {
+    return put_batch(h, n, pic_nums, reinterpret_cast<const uint8_t *const *>(d_luma16), stride_samples, true,
+                     "svtme_put_pictures_10bit_device", 10);
 }
 
 extern "C" int svtme_put_picture(SvtMeHandle *h, uint64_t pic_num, const uint8_t *luma, uint32_t stride) {

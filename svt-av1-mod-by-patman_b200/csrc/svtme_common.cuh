@@ -68,7 +68,8 @@ void svtme_launch_downsample_generic(const uint8_t *in, int in_stride, int w, in
 // batched pyramid build: 2 launches for n pictures
 struct SvtmePutItem {
     const uint8_t *src; // device luma of the caller, 16-byte aligned rows; null = level 0 already holds the picture
-    int src_stride;
+    int src_stride;     // bytes
+    int src_bits;       // 8: one byte per sample; 10: 16-bit samples, level 0 = sample >> 2 (svt_enc_msb_un_pack2_d, pack_unpack_c.c:202)
     DevPyramid pyr;
 };
 struct SvtmePadSpec {

@@ -152,7 +152,20 @@ __global__ void __launch_bounds__(256) downsample_batch_kernel(const SvtmePutIte
     const int sstride = it.src ? it.src_stride : f.stride;
     uint32_t r[4][4];
 #pragma unroll
+    const bool ten = it.src && it.src_bits == 10;
     for (int k = 0; k < 4; ++k) {
+        if (ten) { // 16-bit samples: the 8 MSBs of the 10 go to the ME planes, (uint8_t)(sample >> 2)
+            const uint4 *row16 = reinterpret_cast<const uint4 *>(src + (size_t)(y0 + k) * sstride + 2 * x0);
+            const uint4 a = row16[0];
+            r[k][0] = __byte_perm(a.x >> 2, a.y >> 2, 0x6420);
+            r[k][1] = __byte_perm(a.z >> 2, a.w >> 2, 0x6420);
+            r[k][2] = r[k][3] = 0;
+            if (wide) {
+                const uint4 b = row16[1];
+                r[k][2] = __byte_perm(b.x >> 2, b.y >> 2, 0x6420);
+                r[k][3] = __byte_perm(b.z >> 2, b.w >> 2, 0x6420);
+            }
+        } else {
         const uint8_t *row = src + (size_t)(y0 + k) * sstride + x0;
         if (wide) {
             const uint4 v = *reinterpret_cast<const uint4 *>(row);
@@ -160,6 +173,7 @@ __global__ void __launch_bounds__(256) downsample_batch_kernel(const SvtmePutIte
         } else {
             const uint2 v = *reinterpret_cast<const uint2 *>(row);
             r[k][0] = v.x; r[k][1] = v.y; r[k][2] = 0; r[k][3] = 0;
+        }
         }
         if (it.src) {
             uint8_t *drow = const_cast<uint8_t *>(f.at(x0, y0 + k));

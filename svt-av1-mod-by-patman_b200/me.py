@@ -65,12 +65,16 @@ class MeSession:
     def release_picture(self, pic_num):
         _check(self.lib.svtme_release_picture(self.h, pic_num), self.lib)
 
-    def put_pictures(self, picture_numbers, ptrs, stride, device=False):
-        """Batched pyramid build: ptrs = host (or device) addresses of the luma planes."""
+    def put_pictures(self, picture_numbers, ptrs, stride, device=False, bits=8):
+        """Batched pyramid build: ptrs = host (or device) addresses of the luma planes. bits=10: 16-bit samples,
+        stride in samples; the ME planes get sample >> 2."""
         n = len(picture_numbers)
         nums = (C.c_uint64 * n)(*picture_numbers)
         arr = (C.c_void_p * n)(*ptrs)
-        fn = self.lib.svtme_put_pictures_device if device else self.lib.svtme_put_pictures
+        if bits == 10:
+            fn = self.lib.svtme_put_pictures_10bit_device if device else self.lib.svtme_put_pictures_10bit
+        else:
+            fn = self.lib.svtme_put_pictures_device if device else self.lib.svtme_put_pictures
         _check(fn(self.h, n, nums, arr, stride), self.lib)
 
     def get_plane(self, pic_num, level, pad=None):

@@ -92,6 +92,34 @@ print("ok")
         assert r.returncode == 0 and "ok" in r.stdout, (limit, r.stdout[-500:], r.stderr[-2000:])
 
 
+def test_10bit_sources_give_the_msb_pyramid():
+    """svtme_put_pictures_10bit (host and device sources, aligned and odd strides): all three planes incl. pads equal
+    the pyramid of (sample >> 2), which is what the oracle's unpack + pyramid give."""
+    import torch
+    W, H = 328, 200
+    rng = np.random.default_rng(17)
+    orc = U.oracle_lib()
+    for stride in (W, W + 8, W + 3):
+        src = rng.integers(0, 1024, size=(2, H, stride), dtype=np.uint16)
+        src[1] |= rng.integers(0, 64, size=(H, stride), dtype=np.uint16) << 10  # junk above bit 9 wraps like the reference's cast
+        msb = np.zeros((2, H, W), dtype=np.uint8)
+        for n in range(2):
+            orc.orc_unpack_msb(src[n].ctypes.data_as(C.c_void_p), C.c_uint32(stride), msb[n].ctypes.data_as(C.c_void_p), C.c_uint32(W),
+                               C.c_uint32(W), C.c_uint32(H))
+        dev = torch.from_numpy(src).cuda()
+        with me.MeSession(0, W, H, capacity=6) as ses:
+            ses.put_pictures([0, 1], [src[0].ctypes.data, src[1].ctypes.data], stride, bits=10)
+            ses.put_pictures([2, 3], [dev[0].data_ptr(), dev[1].data_ptr()], stride, device=True, bits=10)
+            ses.put_pictures([4, 5], [msb[0].ctypes.data, msb[1].ctypes.data], W)
+            for n in range(2):
+                pyr = U.CpuPyramid("orc", msb[n], n)
+                for lvl in range(3):
+                    want = ses.get_plane(4 + n, lvl)
+                    assert np.array_equal(ses.get_plane(n, lvl), want), (stride, n, lvl, "host")
+                    assert np.array_equal(ses.get_plane(2 + n, lvl), want), (stride, n, lvl, "device")
+                    assert np.array_equal(pyr.plane(lvl)[:, :want.shape[1]], want), (stride, n, lvl, "oracle")
+
+
 def test_pyramid_matches_golden_and_oracle():
     seq = U.synth_sequence(328, 200, 1, seed=5)
     want = np.load(os.path.join(GOLD, "pyramid.npz"))

@@ -124,3 +124,24 @@ def test_oracle_kernels_match_reference_c():
                                  out.ctypes.data_as(C.c_void_p), C.c_uint32(out.shape[1]), C.c_uint32(step))
                 o.append(out)
             assert np.array_equal(o[0], o[1]), (w, h, step)
+
+
+def test_unpack_msb_oracle_vs_reference():
+    """10-bit source -> 8-bit ME plane: the restatement against svt_aom_un_pack2d of the compiled reference, on
+    sizes that take both of its branches (multiple-of-4 width with even height, and not) and on values with the
+    upper six bits set (the cast to uint8_t wraps)."""
+    ref, orc = U.ref_lib(), U.oracle_lib()
+    if ref is None:
+        pytest.skip("compiled reference (oracle/_ref) not available")
+    rng = np.random.default_rng(3)
+    for (w, h) in [(64, 64), (136, 72), (35, 21), (66, 33)]:
+        for hi in (1024, 65536):
+            src = rng.integers(0, hi, size=(h, w + 5), dtype=np.uint16)
+            a = np.zeros((h, w + 3), dtype=np.uint8)
+            b = np.zeros((h, w + 3), dtype=np.uint8)
+            ref.ref_unpack_msb(src.ctypes.data_as(C.c_void_p), C.c_uint32(w + 5), a.ctypes.data_as(C.c_void_p), C.c_uint32(w + 3),
+                               C.c_uint32(w), C.c_uint32(h))
+            orc.orc_unpack_msb(src.ctypes.data_as(C.c_void_p), C.c_uint32(w + 5), b.ctypes.data_as(C.c_void_p), C.c_uint32(w + 3),
+                               C.c_uint32(w), C.c_uint32(h))
+            assert np.array_equal(a, b), (w, h, hi)
+            assert np.array_equal(b[:, :w], (src[:, :w] >> 2).astype(np.uint8))

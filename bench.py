@@ -38,6 +38,8 @@ WORKLOADS = {
     # source depth 10: 16-bit samples = the 8-bit pattern << 2 plus two random LSBs; the boundary takes them as they are
     # (svtme_put_pictures_10bit) and the planes hold sample >> 2, like the reference's 8-bit ME buffer
     "4k_p4": dict(width=3840, height=2160, preset=4, frames=120, levels=5, n_l0=4, n_l1=3, bits=10),
+    # configs[3]: 8K 10-bit, preset 6, mini-GOP 16 (4 hierarchical levels), refs 3+2; meant for --sharding picture on 8 GPUs
+    "8k_p6": dict(width=7680, height=4320, preset=6, frames=33, levels=4, n_l0=3, n_l1=2, bits=10),
     "small": dict(width=640, height=360, preset=8, frames=12, levels=3, n_l0=2, n_l1=1),
 }
 

@@ -29,6 +29,11 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# One process per GPU shares the host cores: the library's result scatter gets cores / (2 x ranks) threads (1..4) and
+# idle OpenMP workers sleep instead of spinning (both read when the libraries load, i.e. before `import torch`).
+_world = int(os.environ.get("WORLD_SIZE", "1"))
+os.environ.setdefault("SVTME_SCATTER_THREADS", str(max(1, min(4, (os.cpu_count() or 1) // (2 * _world)))))
+os.environ.setdefault("OMP_WAIT_POLICY", "passive")
 PKG = "svt-av1-mod-by-patman_b200"
 
 WORKLOADS = {
@@ -360,7 +365,8 @@ def main():
     torch.cuda.synchronize()
     launches0 = me.launch_count()
     sampler = ClockSampler(local_rank)
-    sampler.start()
+    if rank == 0:  # only rank 0 reports; the other ranks keep their core
+        sampler.start()
     ms_total = timed(step_resident, args.steps)
     launches = me.launch_count() - launches0
     # dominant kernel: the stage kernel of the last step (CUDA events inside the library, same stream)
@@ -372,7 +378,8 @@ def main():
         step_e2e()
     ms_e2e = timed(step_e2e, args.steps)
     sampler.stop_flag = True
-    sampler.join(timeout=2)
+    if rank == 0:
+        sampler.join(timeout=2)
     ms_step = ms_total / args.steps
     sbs_step = (F - 1) * n_b64          # b64 of one whole stream
     n_streams = 1 if by_picture else world

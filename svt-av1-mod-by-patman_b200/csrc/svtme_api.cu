@@ -633,8 +633,14 @@ static int scatter_results(SvtMeHandle *h, const Batch *B, const SvtMeJob *jobs,
         offs[i] = off;
         off += out_layout(h->n_b64, svtme_exported_pu_count(&jobs[i].params), jobs[i].params, wants_deep(jobs[i].out)).end;
     }
-    // plain memcpy of ~0.4 MB per picture; a few host threads when the batch is large (one thread moves ~10 GB/s)
-#pragma omp parallel for schedule(static) num_threads(4) if (n >= 4)
+    // plain memcpy of ~0.4 MB per picture; a few host threads when the batch is large (one thread moves ~10 GB/s).
+    // SVTME_SCATTER_THREADS (1..8, default 4) lets a host that runs one process per GPU keep its cores.
+    static const int scatter_threads = [] {
+        const char *e = getenv("SVTME_SCATTER_THREADS");
+        const int v = e ? atoi(e) : 4;
+        return v < 1 ? 1 : (v > 8 ? 8 : v);
+    }();
+#pragma omp parallel for schedule(static) num_threads(scatter_threads) if (n >= 4 && scatter_threads > 1)
     for (int i = 0; i < (int)n; ++i) {
         const SvtMeJob &j = jobs[i];
         const uint32_t n_pu = svtme_exported_pu_count(&j.params), nb = h->n_b64;

@@ -192,6 +192,29 @@ def test_stage_edges_and_ragged_sizes_vs_oracle(preset, tl, refs, cur):
             assert np.array_equal(orc[k], got[k]), (W, H, k)
 
 
+def test_dependent_references_with_small_areas_vs_oracle():
+    """enable_me_sr_adjustment == 2 makes the full-pel area of every other reference depend on the 64x64 result of
+    (list 0, ref 0) (motion_estimation.c:1345-1350). With small areas all references of a b64 run in ONE CTA of the
+    lean kernel, in the reference's loop order; with large areas the two-round path is taken. Both against the oracle
+    (the parameter set with the small area is synthetic: the rtc screen-content preset with its full-pel area cut to
+    preset 8's)."""
+    W, H = 472, 312
+    refs, cur = {(0, 0): 2, (0, 1): 1, (0, 2): 0, (1, 0): 4, (1, 1): 5}, 3
+    seq = U.synth_sequence(W, H, 7, seed=31, motion=(5, -3), noise=3.0)
+    pyr = {n: U.CpuPyramid("orc", seq[n], n) for n in set(refs.values()) | {cur}}
+    for small in (True, False):
+        d = U.derive_input(10, W, H, temporal_layer_index=2, ref_list0_count_try=3, ref_list1_count_try=2, ref_count_used_list0=3,
+                           ref_count_used_list1=2, rtc_tune=1, sc_class1=1)
+        p = U.finish_params(derive(None, d), d, cur, refs)
+        assert p.enable_me_sr_adjustment == 2
+        if small:
+            p.me_sa.sa_min.width, p.me_sa.sa_min.height, p.me_sa.sa_max.width, p.me_sa.sa_max.height = 9, 3, 9, 5
+        got = gpu_stage(seq, p, cur, refs, W, H)
+        orc = U.cpu_me_picture("orc", p, pyr[cur], {k: pyr[v] for k, v in refs.items()})
+        for k in orc:
+            assert np.array_equal(orc[k], got[k]), (small, k)
+
+
 def test_stage_flat_and_random_pictures_tie_breaks():
     """All-equal pictures make every position tie (first-in-raster-order must win); i.i.d. random
     pictures give non-trivial minima everywhere (SadTest RANDOM pattern)."""

@@ -124,43 +124,67 @@ class ClockSampler(threading.Thread):
 
 
 def cpu_reference_run(wl, specs, seq, n_pictures, threads, min_seconds=10.0):
-    """ME of the first n_pictures jobs on the host: compiled reference (AVX2) if present, else the
-    oracle port. b64 rows are spread over `threads` host threads (ctypes releases the GIL)."""
+    """ME of the first n_pictures jobs (+ the pyramids of the frames they touch) on the host: the compiled reference with
+    its AVX2 kernels if oracle/_ref is present, else the oracle port. Threading is native (oracle/mt_pool.h): a pthread
+    pool pulls (picture, b64-row) tasks from one queue — the reference's own ME-thread / segment scheme — and builds
+    the pyramids one picture per task. Returns throughput, the 1-thread time of the same sample (parallel efficiency)
+    and the result arrays of the sample (for the bit-exactness check against the GPU outputs)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import _util as U  # oracle drivers: CPU-baseline leg only
-    ref = U.ref_lib()
-    which, kind = ("ref", "reference") if ref is not None else ("orc", "port")
-    simd = ref.ref_set_simd(1) if ref is not None else 0
-    lib = ref if ref is not None else U.oracle_lib()
+    which = U.best_cpu_checker()
+    kind = "reference" if which == "ref" else "port"
+    simd = "avx2" if (which == "ref" and U.ref_lib().ref_simd_level() == 1) else "c"
     jobs = specs[:n_pictures]
-    need = set()
-    for p, cur, refs in jobs:
-        need.add(cur)
-        need.update(refs.values())
-    t0 = time.perf_counter()
-    pyr = {n: U.CpuPyramid(which, seq[n], n) for n in sorted(need)}
-    t_pyr = time.perf_counter() - t0
-    n_rows = (wl["height"] + 63) // 64
-    t0 = time.perf_counter()
+    need = sorted({n for _, cur, refs in jobs for n in [cur] + list(refs.values())})
+    frames = {n: seq[n] for n in need}
+    n_b64 = ((wl["width"] + 63) // 64) * ((wl["height"] + 63) // 64)
+    pyrs = U.CpuPyramidSet(which).build(frames, threads)  # allocates the planes (untimed, like the encoder's buffer pools)
+    cj, outs = U.cpu_mt_jobs(which, jobs, pyrs, n_b64)
+
+    def one_pass(nthreads):
+        t0 = time.perf_counter()
+        pyrs.build(frames, nthreads)
+        t1 = time.perf_counter()
+        U.cpu_me_pictures_mt(which, cj, nthreads)
+        return t1 - t0, time.perf_counter() - t1
+
+    one_pass(threads)  # warm-up
+    t_pyr = t_me = 0.0
     reps = 0
+    t_begin = time.perf_counter()
     while True:
-        for p, cur, refs in jobs:
-            chunks = [(r * n_rows // threads, (r + 1) * n_rows // threads) for r in range(threads)]
-            ths = [threading.Thread(target=U.cpu_me_picture, args=(which, p, pyr[cur], {k: pyr[v] for k, v in refs.items()}),
-                                    kwargs=dict(deep=False, rows=c)) for c in chunks if c[1] > c[0]]
-            for t in ths:
-                t.start()
-            for t in ths:
-                t.join()
-        reps += 1
-        if time.perf_counter() - t0 >= min_seconds:
+        a, b = one_pass(threads)
+        t_pyr, t_me, reps = t_pyr + a, t_me + b, reps + 1
+        if time.perf_counter() - t_begin >= min_seconds:
             break
-    t_me = (time.perf_counter() - t0) / reps
-    n_b64 = ((wl["width"] + 63) // 64) * n_rows
-    # pyramid cost is charged per ME'd picture like on the GPU side (one pyramid per frame)
-    per_pic = t_me / len(jobs) + t_pyr / len(pyr)
-    return dict(sbs_per_s=n_b64 / per_pic, fps=1.0 / per_pic, kind=kind, simd="avx2" if simd else "c",
-                seconds=t_me * reps + t_pyr, pictures=len(jobs), reps=reps)
+    t_pyr, t_me = t_pyr / reps, t_me / reps
+    p1, m1 = one_pass(1) if threads > 1 else (t_pyr, t_me)
+    one_pass(threads)  # leave the multi-threaded results in `outs` (identical anyway)
+    # pyramid cost is charged per ME'd picture like on the GPU side (one pyramid per frame of the sequence)
+    per_pic = t_me / len(jobs) + t_pyr / len(need)
+    per_pic_1 = m1 / len(jobs) + p1 / len(need)
+    return dict(sbs_per_s=n_b64 / per_pic, fps=1.0 / per_pic, kind=kind, simd=simd, seconds=time.perf_counter() - t_begin,
+                pictures=len(jobs), pyramids=len(need), reps=reps, threads=threads, sbs_per_s_1thread=n_b64 / per_pic_1,
+                parallel_efficiency=per_pic_1 / (threads * per_pic), outs=outs, keep=(pyrs, cj))
+
+
+def cpu_sample_text(cpu):
+    return ("first %d ME pictures of the workload + the %d pyramids they touch, %d passes in %.1f s, %s kernels, %d native "
+            "threads pulling (picture, b64-row) tasks from one queue; 1 thread: %.0f SB/s -> parallel efficiency %.2f"
+            % (cpu["pictures"], cpu["pyramids"], cpu["reps"], cpu["seconds"], cpu["simd"], cpu["threads"], cpu["sbs_per_s_1thread"],
+               cpu["parallel_efficiency"]))
+
+
+def compare_outputs(cpu_outs, gpu_outs_list):
+    """Bit-exactness of the GPU result arrays against the CPU sample. gpu_outs_list: [(label, [arrays per picture])]."""
+    arrays, bad = 0, []
+    for label, gouts in gpu_outs_list:
+        for i, want in enumerate(cpu_outs):
+            for k, w in want.items():
+                arrays += 1
+                if not np.array_equal(w, gouts[i][k]):
+                    bad.append("%s picture#%d %s" % (label, i, k))
+    return arrays, bad
 
 
 def main():
@@ -180,7 +204,7 @@ def main():
     ap.add_argument("--e2e-chunks", default="4,12,16", help="pictures per chunk of the pipelined end-to-end run "
                     "(decode order; the last value repeats)")
     ap.add_argument("--e2e-depth", type=int, default=2, help="chunks in flight before the oldest one is collected")
-    ap.add_argument("--cpu-pictures", type=int, default=16, help="pictures in the bounded CPU sample")
+    ap.add_argument("--cpu-pictures", type=int, default=0, help="pictures in the bounded CPU sample (0: 16 at 1080p, 8 at 4K, 4 at 8K)")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="repeat the CPU sample for about this long")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
@@ -203,24 +227,36 @@ def main():
     gop = importlib.import_module(PKG + ".gop")
     synth = importlib.import_module(PKG + ".synth")
     threads = os.cpu_count() or 1
+    cpu_pictures = args.cpu_pictures or (16 if W * H <= 1920 * 1088 else (8 if W * H <= 3840 * 2160 else 4))
 
     if args.impl == "reference":
         if rank != 0:
             return 0
-        # parameters from the product's host-side derivation (validated == reference's in tests)
-        lib = abi.load_library()
+        # parameters from the reference's own svt_aom_sig_deriv_me (oracle/_ref); only the oracle-port fallback (no compiled
+        # reference on this machine) has to borrow the product's host-side derivation, which loads the product library
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import _util as U
+        if U.best_cpu_checker() == "ref":
+            rl = U.ref_lib()
 
-        def derive(d):
-            p = abi.SvtMeParams()
-            assert lib.svtme_derive_params(C.byref(d), C.byref(p)) == 0
-            return p
+            def derive(d):
+                p = abi.SvtMeParams()
+                assert rl.ref_derive_params(C.byref(d), C.byref(p)) == 0
+                return p
+        else:
+            lib = abi.load_library()
+
+            def derive(d):
+                p = abi.SvtMeParams()
+                assert lib.svtme_derive_params(C.byref(d), C.byref(p)) == 0
+                return p
         specs = build_specs(abi, gop, wl, derive)
         seq = synth.synth_sequence(W, H, F, seed=1)
         res = None
         times = []
         for i in range(args.warmup + args.steps):
             t0 = time.perf_counter()
-            res = cpu_reference_run(wl, specs, seq, args.cpu_pictures, threads, args.cpu_seconds)
+            res = cpu_reference_run(wl, specs, seq, cpu_pictures, threads, args.cpu_seconds)
             if i >= args.warmup:
                 times.append((time.perf_counter() - t0, res["sbs_per_s"]))
         val = float(np.mean([v for _, v in times])) if times else res["sbs_per_s"]
@@ -229,14 +265,15 @@ def main():
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": config,
                 "frames_per_s": val / n_b64,
                 "cpu_baseline": {"value": val, "unit": "SB/s", "cores": threads, "kind": res["kind"],
-                                 "sample": "first %d ME pictures (+ their pyramids) of the workload, repeated %dx (%.1f s), %s kernels, %d threads over b64 rows"
-                                           % (res["pictures"], res["reps"], res["seconds"], res["simd"], threads)},
+                                 "parallel_efficiency": res["parallel_efficiency"], "value_1thread": res["sbs_per_s_1thread"],
+                                 "sample": cpu_sample_text(res)},
                 "e2e": {"value": val, "unit": "SB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         print(json.dumps(line))
         return 0
 
     import torch
     import torch.distributed as dist
+    exit_code = 0
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
@@ -410,7 +447,17 @@ def main():
         # algorithmic HBM bytes of the stage kernel: every job reads its own pyramid and those of its
         # distinct references once (1 + 1/4 + 1/16 bytes per pixel) and writes its result tables
         alg_bytes = sum((1 + len(set(refs.values()))) * W * H * 1.3125 for _, _, refs in specs) + d2h_bytes
-        cpu = cpu_reference_run(wl, specs, seq, args.cpu_pictures, threads, args.cpu_seconds)
+        cpu = cpu_reference_run(wl, specs, seq, cpu_pictures, threads, args.cpu_seconds)
+        # bit-exactness of THIS run's GPU results against the reference outputs of the CPU sample: the arrays the
+        # end-to-end steps left in the callers' SvtMeOut buffers, and the device-resident launch fetched now
+        ses.fetch_jobs(jobs)
+        e2e_outs = outs if share else [o for c in chunks for o in c[3]]
+        n_arrays, bad = compare_outputs(cpu["outs"], [("e2e", e2e_outs), ("resident", outs)])
+        parity = {"pictures": len(cpu["outs"]), "arrays": n_arrays, "bit_exact": not bad, "against": "oracle/_ref (compiled "
+                  "reference, %s kernels)" % cpu["simd"] if cpu["kind"] == "reference" else "oracle port",
+                  "compared": "all SvtMeOut arrays of the sample's pictures, end-to-end and device-resident runs"}
+        if bad:
+            parity["mismatches"] = bad[:8]
         line = {"metric": "open-loop ME SBs/sec", "value": value, "unit": "SB/s", "n_gpus": world, "steps": args.steps,
                 "warmup": max(3, args.warmup), "ms_per_step": ms_step, "higher_is_better": True,
                 "scaling": "strong" if by_picture else "weak",
@@ -441,15 +488,18 @@ def main():
                                  "peak": hbm_peak, "unit": "GB/s", "frac": alg_bytes / (kernel_ms * 1e-3) / 1e9 / hbm_peak,
                                  "traffic": None, "peak_source": hbm_src},
                 "cpu_baseline": {"value": cpu["sbs_per_s"], "unit": "SB/s", "cores": threads, "kind": cpu["kind"],
-                                 "frames_per_s": cpu["fps"],
-                                 "sample": "first %d ME pictures (+ pyramids) of the same workload, repeated %dx (%.1f s), %s kernels, %d threads over b64 rows"
-                                           % (cpu["pictures"], cpu["reps"], cpu["seconds"], cpu["simd"], threads)},
+                                 "frames_per_s": cpu["fps"], "parallel_efficiency": cpu["parallel_efficiency"],
+                                 "value_1thread": cpu["sbs_per_s_1thread"], "sample": cpu_sample_text(cpu)},
+                "parity": parity,
                 "clocks": sampler.summary()}
         print(json.dumps(line))
+        if bad:
+            sys.stderr.write("bench: GPU results differ from the reference: %s\n" % ", ".join(bad[:8]))
+            exit_code = 1
     ses.close()
     if world > 1:
         dist.destroy_process_group()
-    return 0
+    return exit_code
 
 
 if __name__ == "__main__":

@@ -9,6 +9,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include "me_oracle.h"
+#include "mt_pool.h"
 
 #define NL SVTME_MAX_LISTS
 #define NR SVTME_MAX_REFS
@@ -983,6 +984,57 @@ int orc_me_picture(const SvtMeParams *p, const OrcPyramid *cur,
                    const OrcPyramid *refs[SVTME_MAX_LISTS][SVTME_MAX_REFS], SvtMeOut *out) {
     return orc_me_picture_rows(p, cur, refs, out, 0, 0xffffffffu);
 }
+
+/* ---- all-cores form for bench.py's CPU arm when oracle/_ref is absent ("port"): (picture, b64-row segment)
+ * tasks on a pthread pool, the reference's ME-thread scheme (me_process.c:97-124, enc_handle.c:443-461,768-805). */
+typedef struct OrcMtJob {
+    SvtMeParams       params;
+    const OrcPyramid *cur;
+    const OrcPyramid *refs[SVTME_MAX_LISTS][SVTME_MAX_REFS];
+    SvtMeOut          out;
+} OrcMtJob;
+typedef struct OrcMeMt {
+    OrcMtJob *jobs;
+    uint32_t  segs_per_pic, seg_rows;
+    int       failed;
+} OrcMeMt;
+static void orc_me_mt_item(void *vctx, uint32_t item, uint32_t thread) {
+    (void)thread;
+    OrcMeMt *m = (OrcMeMt *)vctx;
+    OrcMtJob *j = &m->jobs[item / m->segs_per_pic];
+    const uint32_t seg = item % m->segs_per_pic;
+    if (orc_me_picture_rows(&j->params, j->cur, j->refs, &j->out, seg * m->seg_rows, (seg + 1) * m->seg_rows))
+        __atomic_store_n(&m->failed, 1, __ATOMIC_RELAXED);
+}
+int orc_me_pictures_mt(OrcMtJob *jobs, uint32_t n, uint32_t threads, uint32_t seg_rows) {
+    if (!jobs || !n) return -1;
+    if (seg_rows < 1) seg_rows = 1;
+    const uint32_t bh = (jobs[0].cur->full.height + 63) / 64;
+    OrcMeMt m = {jobs, (bh + seg_rows - 1) / seg_rows, seg_rows, 0};
+    const int rc = mt_run(n * m.segs_per_pic, threads, orc_me_mt_item, &m);
+    return (rc || m.failed) ? -1 : 0;
+}
+typedef struct OrcPyrMt {
+    OrcPyramid *pyr;
+    const uint8_t *const *luma;
+    const uint64_t *nums;
+    uint32_t stride, width, height;
+    int hme_level1, failed;
+} OrcPyrMt;
+static void orc_pyr_mt_item(void *vctx, uint32_t item, uint32_t thread) {
+    (void)thread;
+    OrcPyrMt *m = (OrcPyrMt *)vctx;
+    orc_pyramid_free(&m->pyr[item]);
+    if (orc_pyramid_build(&m->pyr[item], m->luma[item], m->stride, m->width, m->height, m->hme_level1, m->nums[item]))
+        __atomic_store_n(&m->failed, 1, __ATOMIC_RELAXED);
+}
+int orc_pyramids_build_mt(OrcPyramid *pyr, const uint8_t *const *luma, uint32_t stride, uint32_t width, uint32_t height,
+                          int hme_level1, const uint64_t *picture_numbers, uint32_t n, uint32_t threads) {
+    OrcPyrMt m = {pyr, luma, picture_numbers, stride, width, height, hme_level1, 0};
+    const int rc = mt_run(n, threads, orc_pyr_mt_item, &m);
+    return (rc || m.failed) ? -1 : 0;
+}
+unsigned orc_sizeof_mt_job(void) { return (unsigned)sizeof(OrcMtJob); }
 
 unsigned orc_sizeof_params(void) { return (unsigned)sizeof(SvtMeParams); }
 unsigned orc_sizeof_out(void) { return (unsigned)sizeof(SvtMeOut); }

@@ -33,6 +33,7 @@
 #include "pack_unpack_c.h"
 
 #include "svtme_b200.h"
+#include "mt_pool.h"
 
 void svt_aom_get_max_allocated_me_refs(uint8_t ref_count_used_list0, uint8_t ref_count_used_list1,
                                        uint8_t *max_ref_to_alloc, uint8_t *max_cand_to_alloc); /* Codec/pcs.c:90 */
@@ -57,6 +58,8 @@ void svt_ext_sad_calculation_8x8_16x16_avx2_intrin(uint8_t *, uint32_t, uint8_t 
 void svt_ext_sad_calculation_32x32_64x64_sse4_intrin(uint32_t *, uint32_t *, uint32_t *, uint32_t *, uint32_t *,
                                                      uint32_t, uint32_t *);
 uint32_t svt_nxm_sad_kernel_helper_avx2(const uint8_t *, uint32_t, const uint8_t *, uint32_t, uint32_t, uint32_t);
+/* Source/Lib/ASM_AVX2/transforms_intrin_avx2.c:171 (aom_dsp_rtcd.h:837) */
+void svt_aom_downsample_2d_avx2(uint8_t *, uint32_t, uint32_t, uint32_t, uint8_t *, uint32_t, uint32_t);
 
 static void *memcpy_shim(void *d, void const *s, size_t n) { return memcpy(d, s, n); }
 static void memcpy_void(void *d, void const *s, size_t n) { memcpy(d, s, n); }
@@ -86,6 +89,7 @@ int ref_set_simd(int simd) {
         svt_ext_sad_calculation_8x8_16x16         = svt_ext_sad_calculation_8x8_16x16_avx2_intrin;
         svt_nxm_sad_kernel                        = svt_nxm_sad_kernel_helper_avx2;
         svt_nxm_sad_kernel_sub_sampled            = svt_nxm_sad_kernel_helper_avx2;
+        downsample_2d                             = svt_aom_downsample_2d_avx2; /* aom_dsp_rtcd.c:507 */
         g_simd                                    = 1;
         return 1;
     }
@@ -133,13 +137,17 @@ void ref_pyramid_free(RefPyramid *pyr) {
 int ref_pyramid_build(RefPyramid *pyr, const uint8_t *luma, uint32_t stride, uint32_t width, uint32_t height,
                       int hme_level1, uint64_t picture_number) {
     if (g_simd < 0) ref_set_simd(0);
-    memset(pyr, 0, sizeof(*pyr));
-    pyr->picture_number = picture_number;
-    if (plane_alloc(&pyr->full, width, height, 72) || plane_alloc(&pyr->quarter, width >> 1, height >> 1, 32) ||
-        plane_alloc(&pyr->sixteenth, width >> 2, height >> 2, 16)) {
-        ref_pyramid_free(pyr);
-        return -1;
+    const int reuse = pyr->full.buffer_y && pyr->quarter.buffer_y && pyr->sixteenth.buffer_y && pyr->full.width == width &&
+        pyr->full.height == height; /* a recycled pa-reference object: refill in place */
+    if (!reuse) {
+        memset(pyr, 0, sizeof(*pyr));
+        if (plane_alloc(&pyr->full, width, height, 72) || plane_alloc(&pyr->quarter, width >> 1, height >> 1, 32) ||
+            plane_alloc(&pyr->sixteenth, width >> 2, height >> 2, 16)) {
+            ref_pyramid_free(pyr);
+            return -1;
+        }
     }
+    pyr->picture_number = picture_number;
     RefPlane *f = &pyr->full;
     for (uint32_t y = 0; y < height; ++y)
         memcpy(f->buffer_y + (size_t)(f->org_y + y) * f->stride_y + f->org_x, luma + (size_t)y * stride, width);
@@ -287,43 +295,83 @@ int ref_derive_params(const SvtMeDeriveInput *in, SvtMeParams *out) {
     return 0;
 }
 
-/* Whole picture through svt_aom_motion_estimation_b64, single thread, raster b64 order, with
- * the pointer set-up of me_process.c:189-262. rows [row0,row1) of b64s. */
-int ref_me_picture_rows(const SvtMeParams *p, const RefPyramid *cur, const RefPyramid *refs[2][4], SvtMeOut *out,
-                        uint32_t row0, uint32_t row1) {
-    if (g_simd < 0) ref_set_simd(0);
+/* ---- whole pictures through svt_aom_motion_estimation_b64 ----
+ * PicShell: the picture-level objects one ME picture needs (scs / pcs / MeSbResults shells pointing straight
+ * into the caller's SvtMeOut arrays; outputs the caller does not want go to scratch). Shared read-only by the
+ * worker threads: svt_aom_motion_estimation_b64 writes only per-b64 entries (motion_estimation.c:2711,2902,
+ * 3017-3076,3216-3217). ThreadCtx: what an ME thread owns (MeContext, me_process.c:75-88). */
+typedef struct PicShell {
+    const SvtMeParams *p;
+    const RefPyramid  *cur;
+    const RefPyramid *const *refs; /* [2][4] flattened */
+    SvtMeOut          *out;
+    uint32_t           bw, bh, nb, n_pu;
+    SequenceControlSet      *scs;
+    PictureParentControlSet *pcs;
+    MotionEstimationData    *med;
+    MeSbResults             *res;
+    MeSbResults            **resp;
+    B64Geom                 *geom;
+    void                    *scratch[11];
+} PicShell;
+
+typedef struct ThreadCtx {
+    MeContext          *ctx;
+    EbPictureBufferDesc dcur, dref[2][4][3];
+    const PicShell     *bound;
+} ThreadCtx;
+
+static void shell_free(PicShell *s) {
+    free(s->scs); free(s->pcs); free(s->med); free(s->res); free(s->resp); free(s->geom);
+    for (int i = 0; i < 11; ++i) free(s->scratch[i]);
+    memset(s, 0, sizeof(*s));
+}
+
+static int shell_init(PicShell *s, const SvtMeParams *p, const RefPyramid *cur, const RefPyramid *const *refs, SvtMeOut *out) {
+    memset(s, 0, sizeof(*s));
+    s->p = p; s->cur = cur; s->refs = refs; s->out = out;
     const uint32_t W = cur->full.width, H = cur->full.height;
-    const uint32_t bw = (W + 63) / 64, bh = (H + 63) / 64, nb = bw * bh;
-    const uint32_t n_pu = p->enable_me_16x16 ? (p->enable_me_8x8 ? p->max_number_of_pus_per_sb : 21u) : 5u;
-    SequenceControlSet      *scs = (SequenceControlSet *)calloc(1, sizeof(*scs));
-    PictureParentControlSet *pcs = (PictureParentControlSet *)calloc(1, sizeof(*pcs));
-    MeContext               *ctx = (MeContext *)calloc(1, sizeof(*ctx));
-    MotionEstimationData    *med = (MotionEstimationData *)calloc(1, sizeof(*med));
-    MeSbResults             *res = (MeSbResults *)calloc(nb, sizeof(*res));
-    MeSbResults            **resp = (MeSbResults **)calloc(nb, sizeof(*resp));
-    B64Geom                 *geom = (B64Geom *)calloc(nb, sizeof(*geom));
-    uint32_t *d64 = calloc(nb, 4), *d32 = calloc(nb, 4), *d16 = calloc(nb, 4), *d8 = calloc(nb, 4), *var = calloc(nb, 4),
-             *rc = calloc(nb, 4);
-    uint8_t *stat = calloc(nb, 1), *gm = calloc(nb, 1);
-    uint8_t  *tot  = calloc((size_t)nb * n_pu, 1);
-    uint32_t *mvs  = calloc((size_t)nb * n_pu * p->max_refs, 4);
-    uint8_t  *cand = calloc((size_t)nb * n_pu * p->max_cand, 1);
-    if (!scs || !pcs || !ctx || !med || !res || !resp || !geom || !tot || !mvs || !cand) return -1;
+    s->bw = (W + 63) / 64; s->bh = (H + 63) / 64; s->nb = s->bw * s->bh;
+    s->n_pu = p->enable_me_16x16 ? (p->enable_me_8x8 ? p->max_number_of_pus_per_sb : 21u) : 5u;
+    const uint32_t nb = s->nb, n_pu = s->n_pu;
+    s->scs  = (SequenceControlSet *)calloc(1, sizeof(*s->scs));
+    s->pcs  = (PictureParentControlSet *)calloc(1, sizeof(*s->pcs));
+    s->med  = (MotionEstimationData *)calloc(1, sizeof(*s->med));
+    s->res  = (MeSbResults *)calloc(nb, sizeof(*s->res));
+    s->resp = (MeSbResults **)calloc(nb, sizeof(*s->resp));
+    s->geom = (B64Geom *)calloc(nb, sizeof(*s->geom));
+    if (!s->scs || !s->pcs || !s->med || !s->res || !s->resp || !s->geom) { shell_free(s); return -1; }
+    int k = 0, bad = 0;
+#define OUTPTR(field, bytes) ((out->field) ? (void *)(out->field) : (s->scratch[k] = calloc((bytes), 1), bad |= !s->scratch[k], s->scratch[k++]))
+    uint8_t  *tot  = (uint8_t *)OUTPTR(total_me_candidate_index, (size_t)nb * n_pu);
+    uint32_t *mvs  = (uint32_t *)OUTPTR(me_mv_array, (size_t)nb * n_pu * p->max_refs * 4);
+    uint8_t  *cand = (uint8_t *)OUTPTR(me_candidate_array, (size_t)nb * n_pu * p->max_cand);
+    PictureParentControlSet *pcs = s->pcs;
+    pcs->me_64x64_distortion         = (uint32_t *)OUTPTR(me_64x64_distortion, (size_t)nb * 4);
+    pcs->me_32x32_distortion         = (uint32_t *)OUTPTR(me_32x32_distortion, (size_t)nb * 4);
+    pcs->me_16x16_distortion         = (uint32_t *)OUTPTR(me_16x16_distortion, (size_t)nb * 4);
+    pcs->me_8x8_distortion           = (uint32_t *)OUTPTR(me_8x8_distortion, (size_t)nb * 4);
+    pcs->me_8x8_cost_variance        = (uint32_t *)OUTPTR(me_8x8_cost_variance, (size_t)nb * 4);
+    pcs->rc_me_distortion            = (uint32_t *)OUTPTR(rc_me_distortion, (size_t)nb * 4);
+    pcs->stationary_block_present_sb = (uint8_t *)OUTPTR(stationary_block_present_sb, nb);
+    pcs->rc_me_allow_gm              = (uint8_t *)OUTPTR(rc_me_allow_gm, nb);
+#undef OUTPTR
+    if (bad) { shell_free(s); return -1; }
     for (uint32_t b = 0; b < nb; ++b) {
-        res[b].total_me_candidate_index = tot + (size_t)b * n_pu;
-        res[b].me_mv_array              = (MvCandidate *)(mvs + (size_t)b * n_pu * p->max_refs);
-        res[b].me_candidate_array       = (MeCandidate *)(cand + (size_t)b * n_pu * p->max_cand);
-        resp[b]                         = &res[b];
-        uint32_t ox = (b % bw) * 64, oy = (b / bw) * 64;
-        geom[b].org_x = (uint16_t)ox; geom[b].org_y = (uint16_t)oy;
-        geom[b].width = (uint8_t)((W - ox) < 64 ? W - ox : 64);
-        geom[b].height = (uint8_t)((H - oy) < 64 ? H - oy : 64);
+        s->res[b].total_me_candidate_index = tot + (size_t)b * n_pu;
+        s->res[b].me_mv_array              = (MvCandidate *)(mvs + (size_t)b * n_pu * p->max_refs);
+        s->res[b].me_candidate_array       = (MeCandidate *)(cand + (size_t)b * n_pu * p->max_cand);
+        s->resp[b]                         = &s->res[b];
+        uint32_t ox = (b % s->bw) * 64, oy = (b / s->bw) * 64;
+        s->geom[b].org_x = (uint16_t)ox; s->geom[b].org_y = (uint16_t)oy;
+        s->geom[b].width = (uint8_t)((W - ox) < 64 ? W - ox : 64);
+        s->geom[b].height = (uint8_t)((H - oy) < 64 ? H - oy : 64);
     }
-    med->me_results = resp; med->max_cand = p->max_cand; med->max_refs = p->max_refs; med->max_l0 = p->max_l0;
-    scs->input_resolution = p->input_resolution_le_480p ? INPUT_SIZE_480p_RANGE : INPUT_SIZE_1080p_RANGE;
-    scs->mrp_ctrls.only_l_bwd = p->only_l_bwd;
-    scs->static_config.restricted_motion_vector = 0;
-    pcs->scs = scs; pcs->pa_me_data = med; pcs->b64_geom = geom;
+    s->med->me_results = s->resp; s->med->max_cand = p->max_cand; s->med->max_refs = p->max_refs; s->med->max_l0 = p->max_l0;
+    s->scs->input_resolution = p->input_resolution_le_480p ? INPUT_SIZE_480p_RANGE : INPUT_SIZE_1080p_RANGE;
+    s->scs->mrp_ctrls.only_l_bwd = p->only_l_bwd;
+    s->scs->static_config.restricted_motion_vector = 0;
+    pcs->scs = s->scs; pcs->pa_me_data = s->med; pcs->b64_geom = s->geom;
     pcs->picture_number = p->picture_number;
     pcs->aligned_width = (uint16_t)W; pcs->aligned_height = (uint16_t)H;
     pcs->enable_me_8x8 = p->enable_me_8x8; pcs->enable_me_16x16 = p->enable_me_16x16;
@@ -331,23 +379,39 @@ int ref_me_picture_rows(const SvtMeParams *p, const RefPyramid *cur, const RefPy
     pcs->hierarchical_levels = p->hierarchical_levels; pcs->temporal_layer_index = p->temporal_layer_index;
     pcs->similar_brightness_refs = p->similar_brightness_refs;
     pcs->gm_ctrls.enabled = p->gm_enabled; pcs->gm_ctrls.use_distance_based_active_th = p->gm_use_distance_based_active_th;
-    pcs->me_64x64_distortion = d64; pcs->me_32x32_distortion = d32; pcs->me_16x16_distortion = d16;
-    pcs->me_8x8_distortion = d8; pcs->me_8x8_cost_variance = var; pcs->rc_me_distortion = rc;
-    pcs->stationary_block_present_sb = stat; pcs->rc_me_allow_gm = gm;
-    params_to_ctx(p, ctx);
-    EbPictureBufferDesc dcur, dref[2][4][3];
-    to_desc(&cur->full, &dcur);
+    return 0;
+}
+
+/* What me_process.c:219-262 does when an ME thread picks up a picture: per-picture scalars and the
+ * me_ds_ref_array pointers go into the thread's MeContext. */
+static void thread_bind(ThreadCtx *t, const PicShell *s) {
+    if (t->bound == s) return;
+    const SvtMeParams *p = s->p;
+    memset(t->ctx, 0, sizeof(*t->ctx));
+    params_to_ctx(p, t->ctx);
+    to_desc(&s->cur->full, &t->dcur);
     for (int li = 0; li < p->num_of_list_to_search; ++li)
         for (int ri = 0; ri < p->num_of_ref_pic_to_search[li]; ++ri) {
-            to_desc(&refs[li][ri]->full, &dref[li][ri][0]);
-            to_desc(&refs[li][ri]->quarter, &dref[li][ri][1]);
-            to_desc(&refs[li][ri]->sixteenth, &dref[li][ri][2]);
-            ctx->me_ds_ref_array[li][ri].picture_ptr           = &dref[li][ri][0];
-            ctx->me_ds_ref_array[li][ri].quarter_picture_ptr   = &dref[li][ri][1];
-            ctx->me_ds_ref_array[li][ri].sixteenth_picture_ptr = &dref[li][ri][2];
-            ctx->me_ds_ref_array[li][ri].picture_number        = p->ref_picture_number[li][ri];
+            const RefPyramid *r = s->refs[li * 4 + ri];
+            to_desc(&r->full, &t->dref[li][ri][0]);
+            to_desc(&r->quarter, &t->dref[li][ri][1]);
+            to_desc(&r->sixteenth, &t->dref[li][ri][2]);
+            t->ctx->me_ds_ref_array[li][ri].picture_ptr           = &t->dref[li][ri][0];
+            t->ctx->me_ds_ref_array[li][ri].quarter_picture_ptr   = &t->dref[li][ri][1];
+            t->ctx->me_ds_ref_array[li][ri].sixteenth_picture_ptr = &t->dref[li][ri][2];
+            t->ctx->me_ds_ref_array[li][ri].picture_number        = p->ref_picture_number[li][ri];
         }
-    if (row1 > bh) row1 = bh;
+    t->bound = s;
+}
+
+/* The b64 loop of me_process.c:174-289 over b64 rows [row0, row1), with its pointer set-up (:189-213). */
+static void run_rows(ThreadCtx *t, const PicShell *s, uint32_t row0, uint32_t row1) {
+    thread_bind(t, s);
+    MeContext *ctx = t->ctx;
+    SvtMeOut  *out = s->out;
+    const RefPyramid *cur = s->cur;
+    const uint32_t bw = s->bw;
+    if (row1 > s->bh) row1 = s->bh;
     for (uint32_t by = row0; by < row1; ++by)
         for (uint32_t bx = 0; bx < bw; ++bx) {
             const uint32_t b = bx + by * bw, ox = bx * 64, oy = by * 64;
@@ -361,35 +425,118 @@ int ref_me_picture_rows(const SvtMeParams *p, const RefPyramid *cur, const RefPy
             ctx->me_type = ME_OPEN_LOOP;
             /* not part of the reference: clear the tables of refs the block will not search so the
              * deep-state dump is comparable (they are never read before being initialised). */
-            memset(ctx->p_sb_best_sad, 0, sizeof(ctx->p_sb_best_sad));
-            svt_aom_motion_estimation_b64(pcs, b, ox, oy, ctx, &dcur);
+            if (out->p_sb_best_sad) memset(ctx->p_sb_best_sad, 0, sizeof(ctx->p_sb_best_sad));
+            svt_aom_motion_estimation_b64(s->pcs, b, ox, oy, ctx, &t->dcur);
             if (out->p_sb_best_sad) memcpy(out->p_sb_best_sad + (size_t)b * 2 * 4 * 85, ctx->p_sb_best_sad, sizeof(ctx->p_sb_best_sad));
             if (out->p_sb_best_mv) memcpy(out->p_sb_best_mv + (size_t)b * 2 * 4 * 85, ctx->p_sb_best_mv, sizeof(ctx->p_sb_best_mv));
-            for (int li = 0; li < 2; ++li)
-                for (int ri = 0; ri < 4; ++ri) {
-                    const size_t k = ((size_t)b * 2 + li) * 4 + ri;
-                    if (out->hme_sc) { out->hme_sc[2 * k] = ctx->search_results[li][ri].hme_sc_x; out->hme_sc[2 * k + 1] = ctx->search_results[li][ri].hme_sc_y; }
-                    if (out->hme_sad) out->hme_sad[k] = ctx->search_results[li][ri].hme_sad;
-                    if (out->do_ref) out->do_ref[k] = ctx->search_results[li][ri].do_ref;
-                }
+            if (out->hme_sc || out->hme_sad || out->do_ref)
+                for (int li = 0; li < 2; ++li)
+                    for (int ri = 0; ri < 4; ++ri) {
+                        const size_t k = ((size_t)b * 2 + li) * 4 + ri;
+                        if (out->hme_sc) { out->hme_sc[2 * k] = ctx->search_results[li][ri].hme_sc_x; out->hme_sc[2 * k + 1] = ctx->search_results[li][ri].hme_sc_y; }
+                        if (out->hme_sad) out->hme_sad[k] = ctx->search_results[li][ri].hme_sad;
+                        if (out->do_ref) out->do_ref[k] = ctx->search_results[li][ri].do_ref;
+                    }
         }
-    const size_t b0 = (size_t)row0 * bw, b1 = (size_t)row1 * bw;
-#define COPY(dst, src, per, sz) if (out->dst) memcpy(out->dst + b0 * (per), (src) + b0 * (per), (b1 - b0) * (per) * (sz))
-    COPY(total_me_candidate_index, tot, n_pu, 1);
-    COPY(me_mv_array, mvs, (size_t)n_pu * p->max_refs, 4);
-    COPY(me_candidate_array, cand, (size_t)n_pu * p->max_cand, 1);
-    COPY(me_64x64_distortion, d64, 1, 4); COPY(me_32x32_distortion, d32, 1, 4); COPY(me_16x16_distortion, d16, 1, 4);
-    COPY(me_8x8_distortion, d8, 1, 4); COPY(me_8x8_cost_variance, var, 1, 4); COPY(rc_me_distortion, rc, 1, 4);
-    COPY(stationary_block_present_sb, stat, 1, 1); COPY(rc_me_allow_gm, gm, 1, 1);
-#undef COPY
-    free(scs); free(pcs); free(ctx); free(med); free(res); free(resp); free(geom);
-    free(d64); free(d32); free(d16); free(d8); free(var); free(rc); free(stat); free(gm); free(tot); free(mvs); free(cand);
+}
+
+/* Single thread, raster b64 order, rows [row0,row1) of b64s. */
+int ref_me_picture_rows(const SvtMeParams *p, const RefPyramid *cur, const RefPyramid *refs[2][4], SvtMeOut *out,
+                        uint32_t row0, uint32_t row1) {
+    if (g_simd < 0) ref_set_simd(0);
+    PicShell  s;
+    ThreadCtx t;
+    memset(&t, 0, sizeof(t));
+    t.ctx = (MeContext *)calloc(1, sizeof(*t.ctx));
+    if (!t.ctx || shell_init(&s, p, cur, (const RefPyramid *const *)refs, out)) { free(t.ctx); return -1; }
+    run_rows(&t, &s, row0, row1);
+    shell_free(&s);
+    free(t.ctx);
     return 0;
 }
 
 int ref_me_picture(const SvtMeParams *p, const RefPyramid *cur, const RefPyramid *refs[2][4], SvtMeOut *out) {
     return ref_me_picture_rows(p, cur, refs, out, 0, 0xffffffffu);
 }
+
+/* ---- all-cores form (bench.py's reference arm): the reference's own threading scheme — ME threads pulling
+ * (picture, segment) tasks from one queue (me_process.c:97-124; segments enc_handle.c:443-461, here a segment =
+ * seg_rows rows of b64s of one picture) — without the encoder around it. Every thread owns a MeContext like the
+ * reference's ME threads do; results go straight into each job's SvtMeOut arrays. */
+typedef struct RefMtJob {
+    SvtMeParams       params;
+    const RefPyramid *cur;
+    const RefPyramid *refs[2][4];
+    SvtMeOut          out;
+} RefMtJob;
+
+typedef struct MeMt {
+    PicShell  *shells;
+    ThreadCtx *threads;
+    uint32_t   segs_per_pic, seg_rows;
+} MeMt;
+
+static void me_mt_item(void *vctx, uint32_t item, uint32_t thread) {
+    MeMt *m = (MeMt *)vctx;
+    const uint32_t pic = item / m->segs_per_pic, seg = item % m->segs_per_pic;
+    run_rows(&m->threads[thread], &m->shells[pic], seg * m->seg_rows, (seg + 1) * m->seg_rows);
+}
+
+int ref_me_pictures_mt(RefMtJob *jobs, uint32_t n, uint32_t threads, uint32_t seg_rows) {
+    if (g_simd < 0) ref_set_simd(0);
+    if (!jobs || !n) return -1;
+    if (threads < 1) threads = 1;
+    if (seg_rows < 1) seg_rows = 1;
+    MeMt m;
+    m.shells  = (PicShell *)calloc(n, sizeof(PicShell));
+    m.threads = (ThreadCtx *)calloc(threads, sizeof(ThreadCtx));
+    int rc = (!m.shells || !m.threads) ? -1 : 0;
+    uint32_t bh = 0;
+    for (uint32_t i = 0; i < n && !rc; ++i) {
+        rc = shell_init(&m.shells[i], &jobs[i].params, jobs[i].cur, &jobs[i].refs[0][0], &jobs[i].out);
+        if (!rc) {
+            if (i && m.shells[i].bh != bh) rc = -1; /* one picture size per call */
+            bh = m.shells[i].bh;
+        }
+    }
+    for (uint32_t t = 0; t < threads && !rc; ++t)
+        if (!(m.threads[t].ctx = (MeContext *)calloc(1, sizeof(MeContext)))) rc = -1;
+    if (!rc) {
+        m.seg_rows     = seg_rows;
+        m.segs_per_pic = (bh + seg_rows - 1) / seg_rows;
+        rc = mt_run(n * m.segs_per_pic, threads, me_mt_item, &m);
+    }
+    if (m.shells) for (uint32_t i = 0; i < n; ++i) shell_free(&m.shells[i]);
+    if (m.threads) for (uint32_t t = 0; t < threads; ++t) free(m.threads[t].ctx);
+    free(m.shells); free(m.threads);
+    return rc;
+}
+
+/* Pyramids of n pictures on the pool (one task per picture). Planes that are already allocated with the right
+ * size are refilled in place, like the encoder's recycled pa-reference objects. */
+typedef struct PyrMt {
+    RefPyramid *pyr;
+    const uint8_t *const *luma;
+    const uint64_t *nums;
+    uint32_t stride, width, height;
+    int hme_level1, failed;
+} PyrMt;
+
+static void pyr_mt_item(void *vctx, uint32_t item, uint32_t thread) {
+    (void)thread;
+    PyrMt *m = (PyrMt *)vctx;
+    if (ref_pyramid_build(&m->pyr[item], m->luma[item], m->stride, m->width, m->height, m->hme_level1, m->nums[item]))
+        __atomic_store_n(&m->failed, 1, __ATOMIC_RELAXED);
+}
+
+int ref_pyramids_build_mt(RefPyramid *pyr, const uint8_t *const *luma, uint32_t stride, uint32_t width, uint32_t height,
+                          int hme_level1, const uint64_t *picture_numbers, uint32_t n, uint32_t threads) {
+    if (g_simd < 0) ref_set_simd(0);
+    PyrMt m = {pyr, luma, picture_numbers, stride, width, height, hme_level1, 0};
+    int rc = mt_run(n, threads, pyr_mt_item, &m);
+    return (rc || m.failed) ? -1 : 0;
+}
+unsigned ref_sizeof_mt_job(void) { return (unsigned)sizeof(RefMtJob); }
 
 int ref_simd_level(void) { return g_simd; }
 

@@ -232,6 +232,7 @@ extern "C" void svtme_close(SvtMeHandle *h) {
     for (Batch *b : h->free_batches) batch_free(b);
     for (Batch *b : h->queue) batch_free(b);
     cudaFree(h->d_states);
+    cudaFree(h->u16_stage);
     for (int k = 0; k < SVTME_PUT_RING; ++k) {
         cudaFree(h->put[k].d);
         cudaFreeHost(h->put[k].h);
@@ -287,20 +288,47 @@ static int put_batch(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const
         pr.cap = n;
     }
     SvtmePutItem *items = pr.h;
+    // Transactional: everything that can be rejected is checked before the ring is touched (a failure
+    // at picture i > 0 used to leave pictures 0..i-1 indexed with no upload or build enqueued).
+    {
+        size_t fresh = 0, free_slots = 0;
+        for (uint32_t i = 0; i < n; ++i) {
+            if (!luma[i]) return failf(SVTME_ERR_INVALID, "%s: null picture", who);
+            bool seen = h->index.count(pic_nums[i]) != 0;
+            for (uint32_t k = 0; k < i && !seen; ++k) seen = pic_nums[k] == pic_nums[i];
+            fresh += seen ? 0 : 1;
+        }
+        for (const Slot &sl : h->slots) free_slots += sl.used ? 0 : 1;
+        if (fresh > free_slots) return failf(SVTME_ERR_NOMEM, "%s: pyramid ring full (release pictures or raise capacity)", who);
+    }
+    std::vector<int> created, touched;
+    // a CUDA failure further down leaves the ring as it was: new index entries are dropped again
+    struct Rollback {
+        SvtMeHandle *h;
+        std::vector<int> *created;
+        bool armed = true;
+        ~Rollback() {
+            if (!armed) return;
+            for (int si : *created) {
+                h->index.erase(h->slots[si].pic_num);
+                h->slots[si].used = false;
+            }
+        }
+    } rollback{h, &created};
     // Host pictures travel on the upload stream so that they overlap the ME pipeline of earlier
     // batches; an upload into a slot must not overtake a launch that still reads the slot's old
     // content (all launches are in order on the main stream: waiting for the newest reader suffices).
     uint64_t newest[SVTME_NS] = {};
     bool any_copy = false;
     for (uint32_t i = 0; i < n; ++i) {
-        if (!luma[i]) return failf(SVTME_ERR_INVALID, "%s: null picture", who);
+        const bool existed = h->index.count(pic_nums[i]) != 0;
         const int si = find_slot(h, pic_nums[i], true);
-        if (si == -2) return failf(SVTME_ERR_NOMEM, "%s: pyramid ring full (release pictures or raise capacity)", who);
+        if (si < 0) return failf(SVTME_ERR_NOMEM, "%s: pyramid ring full (release pictures or raise capacity)", who);
+        if (!existed) created.push_back(si);
+        touched.push_back(si);
         Slot &s = h->slots[si];
-        for (int k = 0; k < SVTME_NS; ++k) {
-            if (s.last_reader[k] > newest[k]) newest[k] = s.last_reader[k];
-            s.last_reader[k] = 0;
-        }
+        for (int k = 0; k < SVTME_NS; ++k)
+            if (s.last_reader[k] > newest[k]) newest[k] = s.last_reader[k]; // (cleared once the waits below are enqueued)
         items[i].pyr = s.pyr;
         items[i].src = nullptr;
         items[i].src_stride = 0;
@@ -333,6 +361,8 @@ static int put_batch(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const
     }
     for (int k = 0; k < SVTME_NS; ++k)
         if (newest[k]) CU(cudaStreamWaitEvent(cs, h->launch_ev[newest[k] % SVTME_LAUNCH_EV_RING], 0));
+    for (int si : touched) // the writes below are ordered behind every reader now: the slots start a new life
+        for (int k = 0; k < SVTME_NS; ++k) h->slots[si].last_reader[k] = 0;
     if (any_copy) {
         for (uint32_t i = 0; i < n; ++i) {
             if (items[i].src) continue;
@@ -360,6 +390,7 @@ static int put_batch(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const
     CU(cudaGetLastError());
     CU(cudaEventRecord(h->build_ev, cs));
     h->build_recorded = true;
+    rollback.armed = false;
     return SVTME_OK;
 }
 
@@ -537,6 +568,15 @@ static int launch_into(SvtMeHandle *h, Batch *B, const SvtMeJob *jobs, uint32_t 
         CU(cudaMalloc(&B->ob.dev, total));
         CU(cudaMallocHost(&B->ob.host, total));
         B->ob.bytes = total;
+    }
+    // every picture of the batch must be resident: checked before the sequence number and the slots' reader marks move
+    // (a NOTFOUND half-way used to leave last_reader pointing at a launch event that is never recorded)
+    for (uint32_t i = 0; i < n; ++i) {
+        if (find_slot(h, jobs[i].cur, false) < 0) return fail(SVTME_ERR_NOTFOUND, "svtme_launch_pictures: current picture not resident");
+        for (int li = 0; li < jobs[i].params.num_of_list_to_search; ++li)
+            for (int ri = 0; ri < jobs[i].params.num_of_ref_pic_to_search[li]; ++ri)
+                if (find_slot(h, jobs[i].refs[li][ri], false) < 0)
+                    return fail(SVTME_ERR_NOTFOUND, "svtme_launch_pictures: reference picture not resident");
     }
     // sequence numbers name their stream: seq % SVTME_NS == si (the event ring is indexed by seq)
     do ++h->seq; while ((int)(h->seq % SVTME_NS) != si);

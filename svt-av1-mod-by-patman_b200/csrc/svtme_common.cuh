@@ -94,6 +94,7 @@ struct SvtmeStageFlags {
                           // picture of the batch uses the sub-sampled SAD (16x8 source block = one sub-block)
 };
 SvtmeStageFlags svtme_stage_flags(const SvtMeParams &p);
+void svtme_configure_stage_kernels(); // per-device kernel attributes (dynamic shared memory), idempotent
 void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b64_rows, void *d_states, cudaStream_t st,
                            cudaEvent_t *ev, const SvtmeStageFlags &f);
 int svtme_fp_direct_max();

@@ -151,8 +151,8 @@ __global__ void __launch_bounds__(256) downsample_batch_kernel(const SvtmePutIte
     const uint8_t *src = it.src ? it.src : f.at(0, 0);
     const int sstride = it.src ? it.src_stride : f.stride;
     uint32_t r[4][4];
-#pragma unroll
     const bool ten = it.src && it.src_bits == 10;
+#pragma unroll
     for (int k = 0; k < 4; ++k) {
         if (ten) { // 16-bit samples: the 8 MSBs of the 10 go to the ME planes, (uint8_t)(sample >> 2)
             const uint4 *row16 = reinterpret_cast<const uint4 *>(src + (size_t)(y0 + k) * sstride + 2 * x0);

@@ -14,6 +14,7 @@
 //   finish_kernel        one CTA per b64: me_prune_ref, candidate arrays, statistics
 // Dependencies between launches are exactly the reference's statement order; b64s never interact.
 #include <cstdlib>
+#include <mutex>
 #include "svtme_scalar.cuh"
 
 struct WideArgs {
@@ -632,9 +633,6 @@ __device__ __forceinline__ void int_one_ref(IntSmem<SMALL> *sm, StageState *g, i
                s->fp_phase = 2;
            });
     }
-#ifdef SVTME_EXP_SKIP_PROBE // timing experiment only
-    if (s->fp_phase == 1) { T0(s->fp_var = 0; plan_int_c(s, J)); s->fp_phase = 2; }
-#endif
     if (s->fp_phase == 1) {
         const int xc = s->fp_xc, yc = s->fp_yc;
         fullpel_probe(sm->src64, pl.at(org_x + xc, org_y + yc), pl.stride, xc, yc, sub_sad, 1, &s->tab);
@@ -649,11 +647,7 @@ __device__ __forceinline__ void int_one_ref(IntSmem<SMALL> *sm, StageState *g, i
         __syncthreads();
     }
     const bool park = mode == INT_DEFER && s->fp_sa_w * s->fp_sa_h > SVTME_FP_DIRECT_MAX;
-#ifdef SVTME_EXP_SKIP_SEARCH // timing experiment only (tools/build_variant.sh): results are wrong
-    if (false) {
-#else
     if (!park) {
-#endif
         const int ox = s->fp_ox, oy = s->fp_oy;
         fullpel_search(sm->src64, pl.at(org_x + ox, org_y + oy), pl.stride, ox, oy, s->fp_sa_w, s->fp_sa_h, sub_sad, 2,
                        &s->tab, sm->arena, (int)sizeof(sm->arena));
@@ -786,19 +780,28 @@ SvtmeStageFlags svtme_stage_flags(const SvtMeParams &p) {
     return f;
 }
 
+// cudaFuncSetAttribute acts on the CURRENT device: once per device, under a lock (a process may open handles on several
+// GPUs and launch from several ME threads).
+void svtme_configure_stage_kernels() {
+    static std::mutex mu;
+    static bool done[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return;
+    std::lock_guard<std::mutex> lk(mu);
+    if (done[dev]) return;
+    cudaFuncSetAttribute(engine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EngSmem));
+    cudaFuncSetAttribute(strip_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(StripSmem));
+    cudaFuncSetAttribute(strip_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(StripSmem));
+    cudaFuncSetAttribute(int_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IntSmem<false>));
+    cudaFuncSetAttribute(int_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IntSmem<true>));
+    cudaFuncSetAttribute(finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FinSmem));
+    done[dev] = true;
+}
+
 void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b64_rows, void *d_states, cudaStream_t st,
                            cudaEvent_t *ev, const SvtmeStageFlags &f) {
     const int b64_per_job = b64_cols * b64_rows;
-    static bool configured = false;
-    if (!configured) {
-        cudaFuncSetAttribute(engine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EngSmem));
-        cudaFuncSetAttribute(strip_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(StripSmem));
-        cudaFuncSetAttribute(strip_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(StripSmem));
-        cudaFuncSetAttribute(int_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IntSmem<false>));
-        cudaFuncSetAttribute(int_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IntSmem<true>));
-        cudaFuncSetAttribute(finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FinSmem));
-        configured = true;
-    }
+    svtme_configure_stage_kernels();
     WideArgs a;
     a.jobs = d_jobs;
     a.st = reinterpret_cast<StageState *>(d_states);

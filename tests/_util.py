@@ -100,3 +100,81 @@ def ref_params(d, picture_number, ref_numbers):
     p = abi.SvtMeParams()
     assert ref_lib().ref_derive_params(C.byref(d), C.byref(p)) == 0
     return finish_params(p, d, picture_number, ref_numbers)
+
+
+# ---------------------------------------------------------------- all-cores drivers (bench.py's CPU arm, big parity cases)
+class CpuMtJob(C.Structure):  # RefMtJob / OrcMtJob (oracle/ref_harness.c, oracle/me_oracle_stage.c)
+    _fields_ = [("params", abi.SvtMeParams), ("cur", C.POINTER(abi.Pyramid)),
+                ("refs", (C.POINTER(abi.Pyramid) * abi.MAX_REFS) * abi.MAX_LISTS), ("out", abi.SvtMeOut)]
+
+
+class CpuPyramidSet:
+    """Pyramids of several pictures built on a pthread pool; planes are recycled when the set is rebuilt."""
+
+    def __init__(self, which):
+        self.which = which
+        self.lib = oracle_lib() if which == "orc" else ref_lib()
+        self.nums, self.arr = [], None
+
+    def build(self, frames, threads, hme_level1=1):
+        """frames: {picture_number: 2-D uint8 array}, all of one size."""
+        nums = sorted(frames)
+        if nums != self.nums:
+            self.free()
+            self.nums, self.arr = nums, (abi.Pyramid * len(nums))()
+        imgs = [np.ascontiguousarray(frames[n]) for n in nums]
+        h, w = imgs[0].shape
+        ptrs = (C.c_void_p * len(nums))(*[im.ctypes.data for im in imgs])
+        pn = (C.c_uint64 * len(nums))(*nums)
+        fn = getattr(self.lib, self.which + "_pyramids_build_mt")
+        rc = fn(self.arr, ptrs, C.c_uint32(w), C.c_uint32(w), C.c_uint32(h), C.c_int(hme_level1), pn, C.c_uint32(len(nums)),
+                C.c_uint32(threads))
+        assert rc == 0
+        return self
+
+    def __getitem__(self, n):
+        return self.arr[self.nums.index(n)]
+
+    def free(self):
+        if self.arr is not None:
+            for i in range(len(self.nums)):
+                getattr(self.lib, self.which + "_pyramid_free")(C.byref(self.arr[i]))
+        self.nums, self.arr = [], None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def cpu_mt_jobs(which, specs, pyrs, n_b64, deep=False):
+    """specs: [(params, cur, {(list, idx): picture number})]; pyrs: CpuPyramidSet. Returns (job array, [arrays])."""
+    lib = oracle_lib() if which == "orc" else ref_lib()
+    assert getattr(lib, which + "_sizeof_mt_job")() == C.sizeof(CpuMtJob)
+    jobs = (CpuMtJob * len(specs))()
+    outs = []
+    for i, (p, cur, refs) in enumerate(specs):
+        jobs[i].params = p
+        jobs[i].cur = C.pointer(pyrs[cur])
+        for (li, ri), n in refs.items():
+            jobs[i].refs[li][ri] = C.pointer(pyrs[n])
+        out, arrays = abi.alloc_out(n_b64, p, deep=deep)
+        jobs[i].out = out
+        outs.append(arrays)
+    return jobs, outs
+
+
+def cpu_me_pictures_mt(which, jobs, threads, seg_rows=1):
+    lib = oracle_lib() if which == "orc" else ref_lib()
+    rc = getattr(lib, which + "_me_pictures_mt")(jobs, C.c_uint32(len(jobs)), C.c_uint32(threads), C.c_uint32(seg_rows))
+    assert rc == 0
+
+
+def best_cpu_checker():
+    """('ref', lib) when the compiled reference is available (AVX2 kernels on), else ('orc', lib)."""
+    ref = ref_lib()
+    if ref is not None:
+        ref.ref_set_simd(1)
+        return "ref"
+    return "orc"

@@ -310,3 +310,69 @@ def test_error_behaviour():
             ses.run_picture(p, 0, {(0, 0): 5, (1, 0): 6})  # references not resident
         with pytest.raises(me.SvtMeError):
             ses.release_picture(9)
+
+
+def test_put_is_transactional_when_the_ring_fills_up():
+    """a batched put that fails at picture i > 0 (ring full, null picture) must leave no trace: the
+    earlier pictures of the call are NOT resident (a later launch on them reports NOTFOUND instead of running on
+    empty pyramids) and pictures that were resident before stay usable."""
+    W, H = 128, 128
+    imgs = U.random_frames(W, H, 4, seed=3)
+    host = np.ascontiguousarray(imgs)
+    d = U.derive_input(8, W, H)
+    with me.MeSession(0, W, H, capacity=3) as ses:
+        ses.put_pictures([0, 1], [host[0].ctypes.data, host[1].ctypes.data], W)
+        with pytest.raises(me.SvtMeError):  # 2 new pictures, 1 free slot
+            ses.put_pictures([2, 3], [host[2].ctypes.data, host[3].ctypes.data], W)
+        with pytest.raises(me.SvtMeError):  # null picture at i = 1
+            ses.put_pictures([2, 3], [host[2].ctypes.data, None], W)
+        p = U.finish_params(derive(None, d), d, 2, {(0, 0): 0, (1, 0): 1})
+        with pytest.raises(me.SvtMeError):
+            ses.run_picture(p, 2, {(0, 0): 0, (1, 0): 1})  # picture 2 must not be resident
+        ses.put_picture(2, imgs[2])  # the slot is still free
+        got = ses.run_picture(p, 2, {(0, 0): 0, (1, 0): 1}, deep=True)
+        with pytest.raises(me.SvtMeError):
+            ses.run_picture(p, 2, {(0, 0): 0, (1, 0): 3})  # NOTFOUND half-way through a launch ...
+        again = ses.run_picture(p, 2, {(0, 0): 0, (1, 0): 1}, deep=True)  # ... leaves the handle usable
+        ses.put_picture(1, imgs[3])  # re-upload into a slot the failed launch named: no stale reader event
+        ses.put_picture(1, imgs[1])
+        third = ses.run_picture(p, 2, {(0, 0): 0, (1, 0): 1}, deep=True)
+    pyr = {n: U.CpuPyramid("orc", imgs[n], n) for n in range(3)}
+    orc = U.cpu_me_picture("orc", p, pyr[2], {(0, 0): pyr[0], (1, 0): pyr[1]})
+    for k in orc:
+        assert np.array_equal(orc[k], got[k]) and np.array_equal(orc[k], again[k]) and np.array_equal(orc[k], third[k]), k
+
+
+def test_two_handles_from_two_threads_and_on_two_devices():
+    """The reference is ONE process with many ME threads: handles opened on different devices (when the box has
+    them; else twice on device 0) and driven from two host threads must each give the single-handle result
+    (kernel attributes are set per device, svtme_configure_stage_kernels)."""
+    import threading
+    import torch
+    ndev = torch.cuda.device_count()
+    W, H = 320, 192
+    seq = U.synth_sequence(W, H, 3, seed=21, motion=(4, 2))
+    d = U.derive_input(4, W, H, temporal_layer_index=1, ref_list0_count_try=1, ref_list1_count_try=1)
+    p = U.finish_params(derive(None, d), d, 1, {(0, 0): 0, (1, 0): 2})
+    want = gpu_stage(seq, p, 1, {(0, 0): 0, (1, 0): 2}, W, H)
+    res, err = {}, []
+
+    def work(dev):
+        try:
+            with me.MeSession(dev % ndev, W, H, capacity=3) as ses:
+                for _ in range(3):
+                    for n in range(3):
+                        ses.put_picture(n, seq[n])
+                    res[dev] = ses.run_picture(p, 1, {(0, 0): 0, (1, 0): 2}, deep=True)
+        except Exception as e:  # noqa: BLE001
+            err.append(repr(e))
+
+    ths = [threading.Thread(target=work, args=(k,)) for k in range(2)]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    assert not err, err
+    for dev in range(2):
+        for k in want:
+            assert np.array_equal(want[k], res[dev][k]), (dev, k)

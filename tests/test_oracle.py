@@ -145,3 +145,44 @@ def test_unpack_msb_oracle_vs_reference():
                                C.c_uint32(w), C.c_uint32(h))
             assert np.array_equal(a, b), (w, h, hi)
             assert np.array_equal(b[:, :w], (src[:, :w] >> 2).astype(np.uint8))
+
+
+@needs_ref
+def test_thread_pool_drivers_equal_the_single_picture_calls():
+    """bench.py's all-cores CPU arm (oracle/mt_pool.h: (picture, b64-row) tasks on a pthread pool; pyramids one
+    picture per task, AVX2 downsample_2d) gives exactly what the single-threaded single-picture calls give, for the
+    compiled reference (C and AVX2 kernels) and for the oracle port — and the pyramids refilled in place equal
+    fresh ones."""
+    W, H = 472, 312
+    seq = U.synth_sequence(W, H, 7, seed=9, motion=(5, -3), noise=2.0)
+    refs = {(0, 0): 2, (0, 1): 1, (0, 2): 0, (1, 0): 4, (1, 1): 5}
+    specs = []
+    for preset, tl, cur in ((8, 3, 3), (4, 2, 3), (6, 0, 6)):
+        r = refs if cur == 3 else {(0, 0): 5, (0, 1): 3, (1, 0): 5, (1, 1): 3}
+        l0, l1 = 1 + max(ri for (li, ri) in r if li == 0), 1 + max(ri for (li, ri) in r if li == 1)
+        d = U.derive_input(preset, W, H, temporal_layer_index=tl, ref_list0_count_try=l0, ref_list1_count_try=l1,
+                           ref_count_used_list0=3, ref_count_used_list1=2)
+        specs.append((U.ref_params(d, cur, r), cur, r))
+    n_b64 = ((W + 63) // 64) * ((H + 63) // 64)
+    single = {n: U.CpuPyramid("orc", seq[n], n) for n in range(7)}
+    want = [U.cpu_me_picture("orc", p, single[cur], {k: single[v] for k, v in r.items()}) for p, cur, r in specs]
+    for which, simd in (("ref", 0), ("ref", 1), ("orc", 0)):
+        if which == "ref":
+            U.ref_lib().ref_set_simd(simd)
+        pyrs = U.CpuPyramidSet(which)
+        for rebuild in range(2):  # the second build refills the planes in place
+            pyrs.build({n: seq[n] for n in range(7)}, 3)
+            for n in range(7):
+                for lvl, name in enumerate(("full", "quarter", "sixteenth")):
+                    pl = getattr(pyrs[n], name)
+                    rows = pl.height + 2 * pl.org_y
+                    got = np.ctypeslib.as_array(C.cast(pl.buffer_y, C.POINTER(C.c_uint8)), shape=(rows, pl.stride_y))
+                    assert np.array_equal(got, single[n].plane(lvl)), (which, simd, n, name)
+        for threads, seg_rows in ((1, 1), (3, 1), (4, 2), (16, 5)):
+            jobs, outs = U.cpu_mt_jobs(which, specs, pyrs, n_b64, deep=True)
+            U.cpu_me_pictures_mt(which, jobs, threads, seg_rows)
+            for w, o in zip(want, outs):
+                for k in w:
+                    assert np.array_equal(w[k], o[k]), (which, simd, threads, seg_rows, k)
+        pyrs.free()
+    U.ref_lib().ref_set_simd(0)

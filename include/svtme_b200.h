@@ -326,6 +326,29 @@ void svt_open_loop_me_fullpel_search_sblock_b200(const uint8_t *src, uint32_t sr
                                                  uint32_t search_area_height, uint8_t sub_sad,
                                                  uint32_t *p_sb_best_sad, uint32_t *p_sb_best_mv);
 
+/* ---------------- allocation-free batched svt_sad_loop_kernel ----------------
+ * NO COUNTERPART IN THE REFERENCE; added for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it). A variant of
+ * svt_sad_loop_kernel_b200 above: n_searches independent searches of one geometry, search i using the block at
+ * d_src + i * src_step and the window whose top-left search position is d_ref + i * ref_step. All pointers are
+ * DEVICE pointers owned by the caller; d_best_sad / d_x_search_center / d_y_search_center are arrays of n_searches
+ * elements with the RTCD meaning per element (best_sad = 0xffffff and x / y untouched when no position beat the
+ * initial best). The reference rows must be readable from 16 bytes before to 4 rows + 256 bytes past the window,
+ * like the wrapper's own staging copy. Asynchronous on `cuda_stream` (a cudaStream_t; NULL = the default stream).
+ * The per-search result keys, the kernel's only scratch memory, live in a static device array of
+ * SVTME_NOALLOC_MAX_SEARCHES entries (64 KB per GPU, held until the process exits): more searches per call are
+ * rejected with SVTME_ERR_INVALID. No cudaMalloc / cudaFree / allocating library call is made. The array is shared
+ * by all calls on a device: calls that overlap on the GPU race (serialise them on one stream); nothing in it has
+ * to be cleared between calls. svtme_noalloc_setup(device) does the once-per-device set-up (device address of the
+ * array, kernel attributes) ahead of time; otherwise the first call on a device does it. */
+#define SVTME_NOALLOC_MAX_SEARCHES 8192
+int svtme_noalloc_setup(int device);
+int svt_sad_loop_kernel_b200_noalloc(void *cuda_stream, uint32_t n_searches, const uint8_t *d_src, uint32_t src_stride,
+                                     size_t src_step, const uint8_t *d_ref, uint32_t ref_stride, size_t ref_step,
+                                     uint32_t block_height, uint32_t block_width, uint32_t src_stride_raw,
+                                     uint8_t skip_search_line, int16_t search_area_width, int16_t search_area_height,
+                                     uint64_t *d_best_sad, int16_t *d_x_search_center, int16_t *d_y_search_center);
+
 #ifdef __cplusplus
 }
 #endif

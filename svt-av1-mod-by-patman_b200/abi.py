@@ -187,6 +187,9 @@ def load_library():
         "svtme_sync": (C.c_int, [vp]),
         "svtme_last_kernel_ms": (C.c_float, [vp]),
         "svtme_launch_count": (u64, []),
+        "svtme_noalloc_setup": (C.c_int, [C.c_int]),
+        "svt_sad_loop_kernel_b200_noalloc": (C.c_int, [vp, u32, vp, u32, C.c_size_t, vp, u32, C.c_size_t, u32, u32, u32, C.c_uint8,
+                                                       C.c_int16, C.c_int16, vp, vp, vp]),
         "svtme_set_stream": (C.c_int, [vp, vp]),
         "svtme_last_work_ops": (C.c_int, [vp, P(u64)]),
         "svtme_last_phase_ms": (C.c_int, [vp, P(C.c_float), C.c_uint32]),

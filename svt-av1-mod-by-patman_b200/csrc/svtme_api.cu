@@ -30,6 +30,7 @@ static int fail(int code, const char *what, cudaError_t e = cudaSuccess) {
     } while (0)
 
 extern "C" const char *svtme_last_error(void) { return g_err; }
+void svtme_set_error(const char *what) { snprintf(g_err, sizeof(g_err), "%s", what); } // for the other translation units
 extern "C" uint64_t svtme_launch_count(void) { return g_svtme_launches; }
 extern "C" uint32_t svtme_sizeof_params(void) { return (uint32_t)sizeof(SvtMeParams); }
 extern "C" uint32_t svtme_sizeof_out(void) { return (uint32_t)sizeof(SvtMeOut); }

@@ -18,7 +18,8 @@ GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 def test_library_exports_every_header_symbol():
     lib = U.product_lib()  # loads csrc/libsvtme_b200.so; no compute calls here
     hdr = open(os.path.join(U.ROOT, "include", "svtme_b200.h")).read()
-    names = set(re.findall(r"\b(svtme_[a-z0-9_]+|svt_[a-z0-9_]+_b200)\s*\(", hdr))
+    names = set(re.findall(r"\b(svtme_[a-z0-9_]+|svt_[a-z0-9_]+_b200(?:_[a-z0-9]+)?)\s*\(", hdr))
+    assert "svt_sad_loop_kernel_b200_noalloc" in names
     assert len(names) >= 25
     for n in sorted(names):
         assert hasattr(lib, n), "symbol missing from libsvtme_b200.so: " + n

@@ -1,0 +1,85 @@
+"""Generates tests/golden/encdump_*.npz from the REAL reference encoder (run in the container, where /root/reference
+exists): oracle/encoder_dump/build_encoder.sh builds SvtAv1EncApp (C-only, stock cmake) from a scratch copy of the
+reference with two hook calls around svt_aom_motion_estimation_b64; this script encodes synthetic clips with
+SVTME_DUMP_DIR set and packs, per ME picture, what the encoder handed to ME (SvtMeParams rebuilt from its MeContext,
+the encoder-level SvtMeDeriveInput, the reference picture numbers) and what ME returned (MeSbResults arrays, per-b64
+pcs arrays, optionally the deep state). The source luma is not stored: it is tests' synth_sequence(seed), and the
+fixture keeps a CRC32 of every plane the encoder's ME actually read.
+
+    python tests/golden/make_encoder_dump.py            # all cases
+"""
+import os
+import subprocess
+import sys
+import tempfile
+import zlib
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+import _encdump as E
+import _util as U
+
+APP = os.path.join(U.ROOT, "oracle", "_ref", "SvtAv1EncApp_dump")
+# name, width, height, frames, preset, deep state, extra encoder arguments
+CASES = [
+    ("360p_p8", 640, 360, 16, 8, True, []),
+    ("360p_p4", 640, 360, 10, 4, False, []),
+    ("1080p_p8", 1920, 1080, 9, 8, False, []),
+]
+ENC_ARGS = ["--fps", "30", "--lp", "1", "--enable-tf", "0", "--scm", "0"]
+
+
+def write_yuv(path, seq):
+    n, h, w = seq.shape
+    chroma = np.full((h // 2) * (w // 2) * 2, 128, np.uint8).tobytes()
+    with open(path, "wb") as f:
+        for i in range(n):
+            f.write(seq[i].tobytes())
+            f.write(chroma)
+
+
+def encode(yuv, w, h, n, preset, extra, ivf, env):
+    cmd = [APP, "-i", yuv, "-w", str(w), "-h", str(h), "-n", str(n), "--preset", str(preset)] + ENC_ARGS + extra + ["-b", ivf]
+    subprocess.run(cmd, check=True, env=dict(os.environ, **env), stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+
+
+def make_case(name, w, h, n, preset, deep, extra):
+    seq = U.synth_sequence(w, h, n, seed=1)
+    with tempfile.TemporaryDirectory() as tmp:
+        yuv, ddir = os.path.join(tmp, "in.yuv"), os.path.join(tmp, "dump")
+        os.mkdir(ddir)
+        write_yuv(yuv, seq)
+        env = {"SVTME_DUMP_DIR": ddir}
+        if deep:
+            env["SVTME_DUMP_DEEP"] = "1"
+        encode(yuv, w, h, n, preset, extra, os.path.join(tmp, "out.ivf"), env)
+        pack = {"meta": np.array([w, h, n, preset, int(deep)], dtype=np.int64)}
+        pics = sorted(int(f[3:9]) for f in os.listdir(ddir) if f.startswith("me_"))
+        pack["pictures"] = np.array(pics, dtype=np.int64)
+        crc = {}
+        for f in os.listdir(ddir):
+            if f.startswith("luma_"):
+                pic = int(f[5:11])
+                plane = E.read_luma(ddir, pic, w, h)
+                assert np.array_equal(plane, seq[pic]), "the encoder's ME input differs from the synthetic frame %d" % pic
+                crc[pic] = zlib.crc32(plane.tobytes())
+        pack["luma_pictures"] = np.array(sorted(crc), dtype=np.int64)
+        pack["luma_crc32"] = np.array([crc[k] for k in sorted(crc)], dtype=np.uint32)
+        for pic in pics:
+            hdr, arrays = E.read_dump(os.path.join(ddir, "me_%06d.bin" % pic))
+            pack["hdr_%d" % pic] = np.frombuffer(bytes(hdr), dtype=np.uint8)
+            for k, a in arrays.items():
+                pack["%s_%d" % (k, pic)] = a
+        out = os.path.join(HERE, "encdump_%s.npz" % name)
+        np.savez_compressed(out, **pack)
+        print(name, "pictures", pics, "->", out, os.path.getsize(out) // 1024, "KiB")
+
+
+if __name__ == "__main__":
+    if not os.path.exists(APP):
+        subprocess.check_call(["bash", os.path.join(U.ROOT, "oracle", "encoder_dump", "build_encoder.sh")])
+    for case in CASES:
+        if len(sys.argv) < 2 or case[0] in sys.argv[1:]:
+            make_case(*case)

@@ -165,6 +165,8 @@ struct HGeo {
     int big;             // does not fit as a whole: tiled single-job path
     int stage_base, item_base, scan_base; // prefix sums inside the group
     int row_off, x_shift; // strip mode (strip_kernel): rows above / bytes left of the window in the shared strip's tiling
+    int n_cols, col_base; // strip mode, streamed windows (strip_columns): columns of this job / prefix sum inside the group
+    int col_chunks;       // ... each column cut into this many y-chunks (balances the CTA: see strip_kernel's planner)
 };
 
 struct HGroup {
@@ -276,6 +278,71 @@ __device__ __forceinline__ void hme_item_fast(const HBlk &blk, const ItemGeo &ig
     }
 }
 
+// Flat wide windows (the W x 3 pre-HME search): ONE item = 32 x-positions of one byte phase (G = 8) times ALL three
+// y-positions, both row parities together. The 17 reference rows the three positions touch are each loaded (3 LDS.128)
+// and shifted (11 SHF) once; an even row meets two source rows (y = 0 and y = 2), an odd row one (y = 1): 768
+// VABSDIFF4 per item, none wasted (the parity-split 2-row tiles computed four y-positions for three). Source rows
+// come from shared memory as they are needed (two live at a time). Full 16x8 sub-blocks only.
+__device__ __forceinline__ void hme_item_wide3(const HBlk &blk, const ItemGeo &ig, uint8_t *arena, int c, int xt, uint32_t &best32) {
+    constexpr int G = 8;
+    uint32_t acc[3][G];
+#pragma unroll
+    for (int y = 0; y < 3; ++y)
+#pragma unroll
+        for (int j = 0; j < G; ++j) acc[y][j] = 0;
+    const uint8_t *base = arena + ig.arena_off + 4 * (xt * G);
+    const uint32_t sh = 8 * c;
+    uint32_t sa[4], sb[4]; // source rows R / 2 and R / 2 - 1
+#pragma unroll
+    for (int i = 0; i < 4; ++i) sa[i] = sb[i] = 0;
+#pragma unroll
+    for (int R = 0; R < 17; ++R) {
+        const int row = ig.row_off + R;
+        const uint8_t *rp = base + row * ig.pitch + ((row >> 3) << 4);
+        uint32_t w[G + 4];
+#pragma unroll
+        for (int k = 0; k < (G + 4) / 4; ++k) {
+            const uint4 v = *reinterpret_cast<const uint4 *>(rp + 16 * k);
+            w[4 * k] = v.x; w[4 * k + 1] = v.y; w[4 * k + 2] = v.z; w[4 * k + 3] = v.w;
+        }
+#pragma unroll
+        for (int i = 0; i < G + 3; ++i) w[i] = __funnelshift_r(w[i], w[i + 1], sh);
+        if ((R & 1) == 0) {
+            if (R > 0) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) sb[i] = sa[i];
+            }
+            if (R < 16) {
+                const uint4 v = *reinterpret_cast<const uint4 *>(blk.src + (R >> 1) * blk.src_pitch);
+                sa[0] = v.x; sa[1] = v.y; sa[2] = v.z; sa[3] = v.w;
+#pragma unroll
+                for (int j = 0; j < G; ++j)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) acc[0][j] = vsad4(sa[i], w[j + i], acc[0][j]); // y = 0, source row R / 2
+            }
+            if (R >= 2) {
+#pragma unroll
+                for (int j = 0; j < G; ++j)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) acc[2][j] = vsad4(sb[i], w[j + i], acc[2][j]); // y = 2, source row R / 2 - 1
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < G; ++j)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) acc[1][j] = vsad4(sa[i], w[j + i], acc[1][j]); // y = 1, source row (R - 1) / 2
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < G; ++j) {
+        const int x = xt * 4 * G + 4 * j + c - ig.x_shift;
+        if ((unsigned)x < (unsigned)ig.sa_w) {
+#pragma unroll
+            for (int y = 0; y < 3; ++y) best32 = min(best32, (acc[y][j] << 17) + (uint32_t)(y * ig.sa_w + x));
+        }
+    }
+}
+
 // Generic item: partial sub-blocks (block height not a multiple of 8 rows, width not a multiple of
 // 16) — edge b64s only. Same tile shape and loads as the fast item, but rolled loops over the y-positions
 // and the rows that exist (compact code), and byte masks when the sub-block is narrower than 16.
@@ -359,6 +426,10 @@ __device__ __noinline__ uint32_t hme_item_slow(const HBlk blk, const ItemGeo ig,
 template <bool STRIP>
 __device__ __forceinline__ void hme_item_any(const HBlk &blk, const ItemGeo &ig, uint8_t *arena, int it, uint32_t &best32) {
     const int nb = blk.nb, nbx = blk.nbx, rs = blk.row_step;
+    if (STRIP && ig.variant == 5) { // flat W x 3 window of a full block: item = (x tile, byte phase), all three y
+        hme_item_wide3(blk, ig, arena, it & 3, it >> 2, best32);
+        return;
+    }
     int t = nb == 1 ? it : (int)__umulhi((uint32_t)it, blk.mg_nb);
     const int b = it - t * nb;
     const int c = t & 3;
@@ -612,6 +683,96 @@ __device__ __noinline__ void strip_group_items(const StripJob *sj, int src_pitch
         hme_item_any<true>(blk, ig, arena, it - base, best32);
     }
     if (bj >= 0) flush_key32(jobs, geo, bj, best32);
+}
+
+// Streamed columns (tall strip windows: the 8 x H pre-HME search, prehme_core :1641). A COLUMN is the positions
+// x = 8 xg + 4 j + c (j = 0, 1), y = p, p + 2, p + 4, ... of one job: same byte phase c, same row parity p. One thread
+// walks down the staged strip once per column: every reference row it loads (6 words) is shifted to phase c (5 SHF)
+// and meets the 8 source rows of the 8 positions in flight — position i = t - r takes source row r at step t — i.e.
+// 64 VABSDIFF4 per step against 16 accumulators held in a ring (slot = step mod 8), one position pair finished per
+// step. The source block stays in 32 registers for the whole column. Against the tiled items (hme_item_fast) this
+// removes the per-item decode, the y-tile padding and most loads / shifts: ~85 % of the issue cycles are VABSDIFF4.
+// The first / last 7 steps of a column carry positions that do not exist (their sums are dropped): 7 / (n + 7) of
+// the column's work. Keys and tie-breaks are those of hme_emit / flush_key32.
+template <bool FULL>
+__device__ __forceinline__ void col_step(int K, const uint32_t (&s)[8][4], uint32_t (&acc)[8][2], const uint32_t (&w)[5], int nrows) {
+    // K = step mod 8, a literal once the caller's step loop is unrolled: every register index below is static
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        if (FULL || r < nrows) { // (nrows < 8 only for the blocks of a ragged bottom picture edge)
+            const int slot = (K - r) & 7;
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) acc[slot][j] = vsad4(s[r][i], w[j + i], acc[slot][j]);
+        }
+    }
+}
+
+template <bool FULL>
+__device__ __forceinline__ uint32_t col_walk(const uint32_t (&s)[8][4], int nrows, const uint8_t *base, int pitch, int R, uint32_t sh,
+                                             uint32_t idx, int idx_step, int T) {
+    uint32_t best32 = ~0u;
+    uint32_t acc[8][2];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k][0] = acc[k][1] = 0;
+    for (int t0 = 0; t0 < T; t0 += 8) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            if (t0 + k < T) {
+                const uint8_t *rp = base + R * pitch + ((R >> 3) << 4);
+                uint32_t raw[6], w[5];
+#pragma unroll
+                for (int q = 0; q < 3; ++q) {
+                    const uint2 v = *reinterpret_cast<const uint2 *>(rp + 8 * q);
+                    raw[2 * q] = v.x; raw[2 * q + 1] = v.y;
+                }
+#pragma unroll
+                for (int q = 0; q < 5; ++q) w[q] = __funnelshift_r(raw[q], raw[q + 1], sh);
+                col_step<FULL>(k, s, acc, w, nrows);
+                const int done = (k + 1) & 7; // the position started 7 steps ago is complete
+                if (t0 + k >= 7) {
+                    best32 = min(best32, (acc[done][0] << 17) + idx);
+                    best32 = min(best32, (acc[done][1] << 17) + idx + 4);
+                }
+                acc[done][0] = acc[done][1] = 0;
+                R += 2;
+                idx += idx_step;
+            }
+        }
+    }
+    return best32;
+}
+
+__device__ __noinline__ void strip_columns(const StripJob *sj, int src_pitch, HJob *jobs, const HGeo *geo, int j0, int col_total,
+                                           uint8_t *arena) {
+    int cj = j0;
+    for (int col = threadIdx.x; col < col_total; col += HME_NT) {
+        while (col >= geo[cj].col_base + geo[cj].n_cols) ++cj;
+        const HGeo &g = geo[cj];
+        const int local = col - g.col_base;
+        const int c = local & 3, p = (local >> 2) & 1, ch = local >> 3, xg = 0; // (streamed windows are 8 wide: one x group)
+        const int sa_w = g.sa_w, n_all = (g.bh - p + 1) >> 1;                   // y = p, p + 2, ... < bh
+        const int i0 = (ch * n_all) / g.col_chunks, n_p = ((ch + 1) * n_all) / g.col_chunks - i0; // this chunk's positions
+        uint32_t best32 = ~0u;
+        if (n_p > 0 && !(g.skip_even && p == 0)) {
+            uint32_t s[8][4];
+            const int nrows = sj[cj].nrows;
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                const uint4 v = *reinterpret_cast<const uint4 *>(sj[cj].src + r * src_pitch);
+                s[r][0] = v.x; s[r][1] = v.y; s[r][2] = v.z; s[r][3] = v.w;
+            }
+            const uint8_t *base = arena + g.arena_off + 8 * xg;
+            const int y0 = p + 2 * i0;
+            const uint32_t idx = (uint32_t)((y0 - 14) * sa_w + 8 * xg + c); // raster index of the position finishing at step t, j = 0
+            if (nrows == 8)
+                best32 = col_walk<true>(s, 8, base, g.m << 4, g.row_off + y0, 8 * c, idx, 2 * sa_w, n_p + 7);
+            else
+                best32 = col_walk<false>(s, nrows, base, g.m << 4, g.row_off + y0, 8 * c, idx, 2 * sa_w, n_p + 7);
+        }
+        flush_key32(jobs, geo, cj, best32);
+    }
 }
 
 __device__ __noinline__ void hme_group_scan(HJob *jobs, const HGeo *geo, const HGroup &G_ref, uint8_t *arena) {

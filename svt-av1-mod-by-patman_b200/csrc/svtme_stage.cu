@@ -315,6 +315,12 @@ __global__ void __launch_bounds__(128, REFINE_CTAS_PER_SM) refine_kernel(WideArg
 // a choice that only affects speed: any set of windows is handled, the segment is split until the
 // union fits the arena, and a single window larger than the arena takes the tiled path.
 #define STRIP_SEG 32
+#ifndef STRIP_STREAM
+#define STRIP_STREAM 1            // tall pre-HME windows as streamed columns (strip_columns); 0: tiled items only
+#endif
+#ifndef STRIP_STREAM_MIN_H
+#define STRIP_STREAM_MIN_H 32     // shorter windows stay tiled: a column spends 7 extra steps on ramp-up / ramp-down
+#endif
 struct StripSmem {
     HJob jobs[STRIP_SEG];
     HPlan plan;                 // plan.geo[j]: window j inside the strip
@@ -322,7 +328,7 @@ struct StripSmem {
     int gidx[STRIP_SEG], jidx[STRIP_SEG], sx[STRIP_SEG], sy[STRIP_SEG];
     HJob strip_job;             // the strip itself, as the one staging job
     HGeo strip_geo;
-    int n, next, item_total, fits;
+    int n, next, item_total, fits, col_total;
     __align__(16) uint8_t src[STRIP_SEG][16 * 16];
     __align__(16) uint8_t arena[SVTME_HME_ARENA_BYTES];
 };
@@ -349,7 +355,7 @@ __device__ __forceinline__ int warp_max(int v) {
 #endif
 template <int MODE>
 __global__ void __launch_bounds__(SVTME_HME_THREADS, MODE == 0 ? SVTME_HME_CTAS_PER_SM : L0_STRIP_CTAS)
-    strip_kernel(WideArgs a, int cols, int rows, int wslot, int arena_limit) {
+    strip_kernel(WideArgs a, int cols, int rows, int wslot, int arena_limit, int stream_min_h) {
     constexpr int mode = MODE;
     extern __shared__ __align__(16) uint8_t smem_raw[];
     StripSmem *sm = reinterpret_cast<StripSmem *>(smem_raw);
@@ -435,6 +441,9 @@ __global__ void __launch_bounds__(SVTME_HME_THREADS, MODE == 0 ? SVTME_HME_CTAS_
             const ptrdiff_t off = jb.ref - rp.base;
             const int y_tl = (int)(off / rp.stride), x_tl = (int)(off - (ptrdiff_t)y_tl * rp.stride);
             const bool live = jb.sa_w > 0 && jb.sa_h > 0;
+            // tall 8-wide windows of full-width blocks are STREAMED (strip_columns); everything else runs as tiled items
+            const bool stream_ok = mode == 0 && STRIP_STREAM && live && jb.sa_w == 8 && jb.sa_h >= stream_min_h &&
+                sm->sj[min(lane, n - 1)].bw == 16;
             const int G = jb.sa_w <= 8 ? 2 : (jb.sa_w <= 16 ? 4 : 8);
             const int ny = (jb.sa_h + rs - 1) / rs;
             // y-tile: 2 rows for the widest items, 8 for tall narrow windows, and for 16-wide windows 2 where a
@@ -442,16 +451,21 @@ __global__ void __launch_bounds__(SVTME_HME_THREADS, MODE == 0 ? SVTME_HME_CTAS_
             const int TY = G == 8 ? 2 : ((G == 2 && ny >= 16) ? 8 : ((G == 4 && (ny & 3) != 0 && (ny & 3) <= 2 && ny <= 12) ? 2 : 4));
             const int n_yt = (ny + TY - 1) / TY;
             int rb = n, x0, y0, xs, xo, xt_n, dy, rows_s, rows_real, words, bytes, cpr, m;
+            bool stream;
             for (;;) {
                 const bool in = lane >= ra && lane < rb;
                 x0 = warp_min(in ? x_tl : 0x7fffffff);
                 y0 = warp_min(in ? y_tl : 0x7fffffff);
                 const int dx = x_tl - x0;
                 dy = y_tl - y0;
-                xs = dx & ~(4 * G - 1);
+                // tile origin: a multiple of the tile width for the narrow tiles; 16 bytes (what the widest loads need) for
+                // the 32-wide ones, so that windows 16 pixels apart (neighbouring b64) all start on a tile boundary
+                xs = dx & ~(min(4 * G, 16) - 1);
                 xo = dx - xs;
+                stream = stream_ok && xo == 0; // (windows of one b64 column start at the same x: always)
                 xt_n = (xo + jb.sa_w + 4 * G - 1) / (4 * G);
-                rows_s = warp_max(in ? dy + n_yt * TY * rs + 7 * rs : 0);
+                // rows the job reads: whole y-tiles of 8-row sub-blocks (items), or the last position's last row (columns)
+                rows_s = warp_max(in ? (stream ? dy + jb.sa_h + 7 * rs : dy + n_yt * TY * rs + 7 * rs) : 0);
                 rows_real = warp_max(in ? dy + jb.sa_h + (nrows_j - 1) * rs : 1);
                 words = warp_max(in ? (xs >> 2) + xt_n * G + 5 : 0);
                 cpr = (words + 3) >> 2;
@@ -461,14 +475,27 @@ __global__ void __launch_bounds__(SVTME_HME_THREADS, MODE == 0 ? SVTME_HME_CTAS_
                 rb = ra + (rb - ra + 1) / 2;
             }
             const bool in = lane >= ra && lane < rb;
-            const int n_items = (in && live) ? rs * n_yt * xt_n * 4 : 0;
-            int ps = n_items;
+            // flat three-row windows of full blocks: one item takes all three y-positions (hme_item_wide3)
+            const bool wide3 = mode == 0 && G == 8 && jb.sa_h == 3 && !jb.skip_even && sm->sj[min(lane, n - 1)].bw == 16 &&
+                sm->sj[min(lane, n - 1)].nrows == 8;
+            const int n_items = (in && live && !stream) ? (wide3 ? xt_n * 4 : rs * n_yt * xt_n * 4) : 0;
+            // Columns: (row parity, byte phase) = 8 per streamed job, one per thread. The jobs that fill whole passes of the
+            // CTA run their columns in one piece; the columns of the r jobs left over are cut into NT / (8 r) y-chunks each,
+            // so that the last pass is short instead of a full column walked by a few lanes (17 b64 rows at 1080p: 16 jobs
+            // in pass one, the 17th as 16 x 8 short chunks) — the other warps would wait for it at the barrier.
+            const unsigned sbal = __ballot_sync(0xffffffffu, in && stream);
+            const int s_idx = __popc(sbal & ((1u << lane) - 1u)), s_tot = __popc(sbal), per_pass = SVTME_HME_THREADS / 8;
+            const int s_full = (s_tot / per_pass) * per_pass;
+            int chunks = 1;
+            if (in && stream && s_idx >= s_full) chunks = max(1, min(per_pass / (s_tot - s_full), (jb.sa_h >> 1) / 8));
+            const int n_cols = (in && stream) ? 8 * chunks : 0;
+            int ps = n_items, pc = n_cols;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
-                const int v = __shfl_up_sync(0xffffffffu, ps, o);
-                if (lane >= o) ps += v;
+                const int v = __shfl_up_sync(0xffffffffu, ps, o), vc = __shfl_up_sync(0xffffffffu, pc, o);
+                if (lane >= o) { ps += v; pc += vc; }
             }
-            const int total = __shfl_sync(0xffffffffu, ps, 31);
+            const int total = __shfl_sync(0xffffffffu, ps, 31), total_c = __shfl_sync(0xffffffffu, pc, 31);
             if (in) {
                 HGeo &g = sm->plan.geo[lane];
                 g.arena_off = (uint32_t)xs;
@@ -482,12 +509,15 @@ __global__ void __launch_bounds__(SVTME_HME_THREADS, MODE == 0 ? SVTME_HME_CTAS_
                 g.n_items = n_items;
                 g.G = G;
                 g.skip_even = jb.skip_even;
-                g.variant = G == 2 ? (TY == 8 ? 3 : 0) : (G == 4 ? (TY == 2 ? 4 : 1) : 2);
+                g.variant = wide3 ? 5 : (G == 2 ? (TY == 8 ? 3 : 0) : (G == 4 ? (TY == 2 ? 4 : 1) : 2));
                 g.mg_xt = magic_div((uint32_t)max(xt_n, 1));
                 g.mg_wb = magic_div((uint32_t)max(jb.sa_w, 1));
                 g.item_base = ps - n_items;
                 g.row_off = dy;
                 g.x_shift = xo;
+                g.n_cols = n_cols;
+                g.col_base = pc - n_cols;
+                g.col_chunks = chunks;
             }
             if (lane == 0) {
                 sm->strip_job.ref = rp.base + (size_t)y0 * rp.stride + x0;
@@ -505,16 +535,18 @@ __global__ void __launch_bounds__(SVTME_HME_THREADS, MODE == 0 ? SVTME_HME_CTAS_
                 g.stage_units = rows_s * cpr;
                 sm->next = rb;
                 sm->item_total = total;
+                sm->col_total = total_c;
                 sm->fits = bytes <= arena_limit;
             }
         }
         __syncthreads();
         if (sm->fits) {
-            if (sm->item_total > 0) {
+            if (sm->item_total > 0 || sm->col_total > 0) {
                 const HGroup SG = HGroup{0, 1, 0, sm->strip_geo.stage_units, 0, 0};
                 hme_group_stage(&sm->strip_job, &sm->strip_geo, SG, sm->arena);
                 __syncthreads();
-                strip_group_items(sm->sj, src_pitch, rs, sm->jobs, sm->plan.geo, ra, sm->item_total, sm->arena);
+                if (sm->col_total > 0) strip_columns(sm->sj, src_pitch, sm->jobs, sm->plan.geo, ra, sm->col_total, sm->arena);
+                if (sm->item_total > 0) strip_group_items(sm->sj, src_pitch, rs, sm->jobs, sm->plan.geo, ra, sm->item_total, sm->arena);
             }
         } else { // one window larger than the arena: tiled like any big HME job
             const HBlk blk = make_hblk(sm->sj[ra].src, src_pitch, sm->sj[ra].bw, sm->sj[ra].nrows, rs);
@@ -759,6 +791,14 @@ static int strip_arena_limit_from_env() {
     return (v >= 1024 && v <= SVTME_HME_ARENA_BYTES) ? v : SVTME_HME_ARENA_BYTES;
 }
 static const int g_strip_arena_limit = strip_arena_limit_from_env();
+// Minimum window height for streamed columns; SVTME_STRIP_STREAM_MIN_H in the environment (read once) lets tests and
+// A/B timings move it (a huge value turns streaming off: every window runs as tiled items).
+static int strip_stream_min_h_from_env() {
+    const char *e = getenv("SVTME_STRIP_STREAM_MIN_H");
+    const int v = e ? atoi(e) : 0;
+    return v > 0 ? v : STRIP_STREAM_MIN_H;
+}
+static const int g_strip_stream_min_h = strip_stream_min_h_from_env();
 
 // Launch slots (one event after each; names in SVTME_PHASE_NAMES of svtme_common.cuh).
 SvtmeStageFlags svtme_stage_flags(const SvtMeParams &p) {
@@ -827,7 +867,7 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
         (b64_cols * ((b64_rows + STRIP_SEG - 1) / STRIP_SEG) + b64_rows * ((b64_cols + STRIP_SEG - 1) / STRIP_SEG));
     auto prehme_round = [&]() {
         if (f.prehme_strip)
-            strip_kernel<0><<<strip_tasks, SVTME_HME_THREADS, sizeof(StripSmem), st>>>(a, b64_cols, b64_rows, 2, g_strip_arena_limit);
+            strip_kernel<0><<<strip_tasks, SVTME_HME_THREADS, sizeof(StripSmem), st>>>(a, b64_cols, b64_rows, 2, g_strip_arena_limit, g_strip_stream_min_h);
         else
             engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 2);
         ++launches;
@@ -848,7 +888,7 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
             // the arena is the last member of StripSmem: a smaller arena is a smaller dynamic allocation
             const int lim = g_strip_arena_limit < L0_STRIP_ARENA ? g_strip_arena_limit : L0_STRIP_ARENA;
             strip_kernel<1><<<l0_tasks, SVTME_HME_THREADS, sizeof(StripSmem) - SVTME_HME_ARENA_BYTES + L0_STRIP_ARENA, st>>>(
-                a, b64_cols, b64_rows, 3, lim);
+                a, b64_cols, b64_rows, 3, lim, 1 << 30);
         }
         else
             engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 3);

@@ -1,0 +1,40 @@
+"""Device-resident step of a bench workload, phase times only (A/B timing of kernel variants selected by environment
+variables that the library reads when it loads). Usage: python tools/prof_phase.py [workload] [steps]"""
+import importlib
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench
+
+PKG = bench.PKG
+abi, gop, synth, me = (importlib.import_module(PKG + "." + m) for m in ("abi", "gop", "synth", "me"))
+import torch
+
+name = sys.argv[1] if len(sys.argv) > 1 else "1080p_p8"
+steps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+wl = bench.WORKLOADS[name]
+W, H, F = wl["width"], wl["height"], wl["frames"]
+seq = synth.synth_sequence(W, H, F, seed=1)
+dev = torch.from_numpy(seq).cuda()
+ses = me.MeSession(0, W, H, capacity=F)
+st = torch.cuda.Stream()
+torch.cuda.set_stream(st)
+ses.set_stream(st.cuda_stream)
+specs = bench.build_specs(abi, gop, wl, ses.derive_params)
+jobs, outs = ses.make_jobs(specs, deep=False)
+tot = None
+for i in range(steps + 2):
+    ses.put_pictures(list(range(F)), [dev.data_ptr() + f * W * H for f in range(F)], W, device=True)
+    ses.launch_jobs(jobs)
+    ph = ses.last_phase_ms()
+    if i >= 2:
+        tot = ph if tot is None else {k: tot[k] + v for k, v in ph.items()}
+work = ses.last_phase_work()
+print(name, {k: round(v / steps, 3) for k, v in tot.items()}, "sum %.3f" % (sum(tot.values()) / steps),
+      "env", {k: v for k, v in os.environ.items() if k.startswith("SVTME_")})
+print("   work G byte-ops", {k: round(v / 1e9, 2) for k, v in work.items() if v})
+ses.close()

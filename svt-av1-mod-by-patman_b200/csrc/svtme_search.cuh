@@ -316,21 +316,21 @@ __device__ __forceinline__ void hme_item_wide3(const HBlk &blk, const ItemGeo &i
                 const uint4 v = *reinterpret_cast<const uint4 *>(blk.src + (R >> 1) * blk.src_pitch);
                 sa[0] = v.x; sa[1] = v.y; sa[2] = v.z; sa[3] = v.w;
 #pragma unroll
-                for (int j = 0; j < G; ++j)
+                for (int i = 0; i < 4; ++i)
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) acc[0][j] = vsad4(sa[i], w[j + i], acc[0][j]); // y = 0, source row R / 2
+                    for (int j = 0; j < G; ++j) acc[0][j] = vsad4(sa[i], w[j + i], acc[0][j]); // y = 0, source row R / 2
             }
             if (R >= 2) {
 #pragma unroll
-                for (int j = 0; j < G; ++j)
+                for (int i = 0; i < 4; ++i)
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) acc[2][j] = vsad4(sb[i], w[j + i], acc[2][j]); // y = 2, source row R / 2 - 1
+                    for (int j = 0; j < G; ++j) acc[2][j] = vsad4(sb[i], w[j + i], acc[2][j]); // y = 2, source row R / 2 - 1
             }
         } else {
 #pragma unroll
-            for (int j = 0; j < G; ++j)
+            for (int i = 0; i < 4; ++i)
 #pragma unroll
-                for (int i = 0; i < 4; ++i) acc[1][j] = vsad4(sa[i], w[j + i], acc[1][j]); // y = 1, source row (R - 1) / 2
+                for (int j = 0; j < G; ++j) acc[1][j] = vsad4(sa[i], w[j + i], acc[1][j]); // y = 1, source row (R - 1) / 2
         }
     }
 #pragma unroll
@@ -697,16 +697,17 @@ __device__ __noinline__ void strip_group_items(const StripJob *sj, int src_pitch
 template <bool FULL>
 __device__ __forceinline__ void col_step(int K, const uint32_t (&s)[8][4], uint32_t (&acc)[8][2], const uint32_t (&w)[5], int nrows) {
     // K = step mod 8, a literal once the caller's step loop is unrolled: every register index below is static
+    // word index outermost: consecutive VABSDIFF4 go to 16 different accumulators (no back-to-back dependent pairs)
 #pragma unroll
-    for (int r = 0; r < 8; ++r) {
-        if (FULL || r < nrows) { // (nrows < 8 only for the blocks of a ragged bottom picture edge)
-            const int slot = (K - r) & 7;
+    for (int i = 0; i < 4; ++i)
 #pragma unroll
-            for (int j = 0; j < 2; ++j)
+        for (int r = 0; r < 8; ++r) {
+            if (FULL || r < nrows) { // (nrows < 8 only for the blocks of a ragged bottom picture edge)
+                const int slot = (K - r) & 7;
 #pragma unroll
-                for (int i = 0; i < 4; ++i) acc[slot][j] = vsad4(s[r][i], w[j + i], acc[slot][j]);
+                for (int j = 0; j < 2; ++j) acc[slot][j] = vsad4(s[r][i], w[j + i], acc[slot][j]);
+            }
         }
-    }
 }
 
 template <bool FULL>

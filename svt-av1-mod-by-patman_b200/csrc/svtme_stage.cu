@@ -329,7 +329,7 @@ struct StripSmem {
     HJob strip_job;             // the strip itself, as the one staging job
     HGeo strip_geo;
     int n, next, item_total, fits, col_total;
-    __align__(16) uint8_t src[STRIP_SEG][16 * 16];
+    __align__(16) uint8_t src[STRIP_SEG][8 * 16]; // the 8 compared rows (every other one) of each 16x16 sixteenth block
     __align__(16) uint8_t arena[SVTME_HME_ARENA_BYTES];
 };
 
@@ -354,7 +354,10 @@ __device__ __forceinline__ int warp_max(int v) {
 #define L0_STRIP_CTAS 6
 #endif
 template <int MODE>
-__global__ void __launch_bounds__(SVTME_HME_THREADS, MODE == 0 ? SVTME_HME_CTAS_PER_SM : L0_STRIP_CTAS)
+#ifndef STRIP0_CTAS
+#define STRIP0_CTAS 5 // measured 4 -> 5: 1080p 1.168 -> 1.147 ms, 4K 14.80 -> 14.49 ms (96 registers: the tiled items spill a little)
+#endif
+__global__ void __launch_bounds__(SVTME_HME_THREADS, MODE == 0 ? STRIP0_CTAS : L0_STRIP_CTAS)
     strip_kernel(WideArgs a, int cols, int rows, int wslot, int arena_limit, int stream_min_h) {
     constexpr int mode = MODE;
     extern __shared__ __align__(16) uint8_t smem_raw[];
@@ -424,22 +427,22 @@ __global__ void __launch_bounds__(SVTME_HME_THREADS, MODE == 0 ? SVTME_HME_CTAS_
     __syncthreads();
     const int n = sm->n;
     if (n == 0) return;
-    {   // sixteenth source blocks (me_process.c:205-213), all 16 rows; the sub-sampled SAD reads every other one
+    {   // sixteenth source blocks (me_process.c:205-213): the sub-sampled SAD reads every other row, only those are kept
         const DevPlane &cur = J.cur.lvl[2];
-        for (int i = tid; i < n * 16; i += SVTME_HME_THREADS) {
-            const int k = i >> 4, r = i & 15;
-            *reinterpret_cast<uint4 *>(&sm->src[k][r * 16]) = *reinterpret_cast<const uint4 *>(cur.at(sm->sx[k], sm->sy[k] + r));
+        for (int i = tid; i < n * 8; i += SVTME_HME_THREADS) {
+            const int k = i >> 3, r = i & 7;
+            *reinterpret_cast<uint4 *>(&sm->src[k][r * 16]) = *reinterpret_cast<const uint4 *>(cur.at(sm->sx[k], sm->sy[k] + 2 * r));
         }
     }
     const DevPlane &rp = J.ref[li][ri].lvl[2];
-    const int rs = 2, src_pitch = 32; // SUB_SAD_SEARCH (the host selects strip mode only then)
+    const int rs = 2, src_pitch = 16; // SUB_SAD_SEARCH (the host selects strip mode only then); compact source rows
     int ra = 0;
     while (ra < n) {
         if (warp == 0) {
             const HJob jb = sm->jobs[min(lane, n - 1)];
             const int nrows_j = max(sm->sj[min(lane, n - 1)].nrows, 1);
-            const ptrdiff_t off = jb.ref - rp.base;
-            const int y_tl = (int)(off / rp.stride), x_tl = (int)(off - (ptrdiff_t)y_tl * rp.stride);
+            const uint32_t off = (uint32_t)(jb.ref - rp.base); // (a plane is far below 4 GB: 32-bit division)
+            const int y_tl = (int)(off / (uint32_t)rp.stride), x_tl = (int)(off - (uint32_t)y_tl * (uint32_t)rp.stride);
             const bool live = jb.sa_w > 0 && jb.sa_h > 0;
             // tall 8-wide windows of full-width blocks are STREAMED (strip_columns); everything else runs as tiled items
             const bool stream_ok = mode == 0 && STRIP_STREAM && live && jb.sa_w == 8 && jb.sa_h >= stream_min_h &&

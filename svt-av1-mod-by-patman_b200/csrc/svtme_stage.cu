@@ -194,18 +194,23 @@ struct RefineCfg {
 };
 __device__ __forceinline__ int refine_rowoff(int R, int pitch) { return R * pitch + ((R >> 3) & 1) * 16; }
 
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src) { // LDGSTS: global -> shared, no registers
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.commit_group;\n cp.async.wait_group 0;" ::: "memory"); }
+
 template <int BWW, bool FULLW>
-__device__ __forceinline__ void refine_rows(const uint8_t *__restrict__ src0, int src_pitch, const uint8_t *tile, int boff,
-                                            int rs, int nrows, int kw, int rq, int ny, uint32_t (&acc)[REFINE_YT][2]) {
+__device__ __forceinline__ void refine_rows(const uint8_t *src0, int src_pitch, const uint8_t *tile, int boff, int rs, int nrows, int kw,
+                                            int rq, int ny, uint32_t (&acc)[REFINE_YT][2]) {
     constexpr int PITCH = RefineCfg<BWW>::PITCH;
     const uint32_t shb = (uint32_t)(boff & 3) * 8;
     const uint8_t *col = tile + (boff & ~3);
     for (int r = rq; r < nrows; r += 8) {
         uint32_t sw[BWW];
-        const uint4 *sp = reinterpret_cast<const uint4 *>(src0 + (size_t)r * src_pitch);
+        const uint4 *sp = reinterpret_cast<const uint4 *>(src0 + r * src_pitch); // shared memory: the four lanes of a row group broadcast
 #pragma unroll
         for (int k = 0; k < BWW / 4; ++k) {
-            const uint4 v = __ldg(sp + k);
+            const uint4 v = sp[k];
             sw[4 * k] = v.x; sw[4 * k + 1] = v.y; sw[4 * k + 2] = v.z; sw[4 * k + 3] = v.w;
         }
 #pragma unroll
@@ -232,28 +237,53 @@ __device__ __forceinline__ void refine_rows(const uint8_t *__restrict__ src0, in
 #ifndef REFINE_CTAS_PER_SM
 #define REFINE_CTAS_PER_SM 8
 #endif
+struct RefineJob { // the fields of an HJob the kernel reads, staged once per CTA
+    const uint8_t *ref;
+    int stride, sa_w, sa_h, skip_even;
+};
+template <int BWW>
+struct RefineSmem {
+    RefineJob jobs[MAX_JOBS];
+    __align__(16) uint8_t src[(BWW == 8 ? 32 : 64) * BWW * 4]; // the compared rows of the source block, pitch BWW * 4 bytes
+    __align__(16) uint8_t tile[4][RefineCfg<BWW>::BYTES];
+};
 template <int BWW>
 __global__ void __launch_bounds__(128, REFINE_CTAS_PER_SM) refine_kernel(WideArgs a, int sh, int wslot) {
     using Cfg = RefineCfg<BWW>;
     extern __shared__ __align__(16) uint8_t smem_raw[];
-    const int gid = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    RefineSmem<BWW> *sm = reinterpret_cast<RefineSmem<BWW> *>(smem_raw);
+    const int gid = blockIdx.x, tid = threadIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     StageState *s = &a.st[gid];
     const int n = s->n_jobs;
     if (n == 0) return;
-    uint8_t *tile = smem_raw + warp * Cfg::BYTES;
+    uint8_t *tile = sm->tile[warp];
     const DevJob &J = a.jobs[gid / a.b64_per_job];
     const bool full_sad = J.prm.hme_search_method == 1;
     const int rs = full_sad ? 1 : 2;
     const DevPlane &cp = J.cur.lvl[sh]; // sh = 1: quarter picture (HME level 1), 0: full picture (level 2)
     const int bw = s->b64_w >> sh, kw = bw >> 2;
     const int nrows = full_sad ? (s->b64_h >> sh) : (s->b64_h >> (sh + 1));
-    const uint8_t *src0 = cp.at(s->org_x >> sh, s->org_y >> sh);
-    const int src_pitch = cp.stride * rs;
+    {   // once per CTA: the job descriptors and the compared rows of the source block go to shared memory (the windows of a
+        // b64 — up to 32 — all use the same block; reading its rows through L1 per window kept l1tex 80 % busy)
+        if (tid < n) {
+            const HJob &hj = s->jobs[tid];
+            sm->jobs[tid] = RefineJob{hj.ref, hj.stride, hj.sa_w, hj.sa_h, hj.skip_even};
+        }
+        const uint8_t *g0 = cp.at(s->org_x >> sh, s->org_y >> sh); // 16-byte aligned: block origins are multiples of 32 >> sh ... of 64 >> sh
+        const size_t gp = (size_t)cp.stride * rs;
+        for (int u = tid; u < nrows * (BWW / 4); u += 128) {
+            const int r = u / (BWW / 4), ch = u - r * (BWW / 4);
+            cp_async16(sm->src + r * (BWW * 4) + 16 * ch, g0 + r * gp + 16 * ch);
+        }
+        cp_async_wait_all();
+    }
+    __syncthreads();
     const int c = lane & 3, rq = lane >> 2;
     unsigned long long work = 0;
     for (int j = warp; j < n; j += 4) {
-        const uint8_t *ref = s->jobs[j].ref;
-        const int stride = s->jobs[j].stride, sa_w = s->jobs[j].sa_w, sa_h = s->jobs[j].sa_h, skip_even = s->jobs[j].skip_even;
+        const RefineJob jb = sm->jobs[j];
+        const uint8_t *ref = jb.ref;
+        const int stride = jb.stride, sa_w = jb.sa_w, sa_h = jb.sa_h, skip_even = jb.skip_even;
         if (sa_w <= 0 || sa_h <= 0) continue;
         unsigned long long best = ~0ULL;
         for (int y0 = 0; y0 < sa_h; y0 += REFINE_YT) {
@@ -263,20 +293,20 @@ __global__ void __launch_bounds__(128, REFINE_CTAS_PER_SM) refine_kernel(WideArg
                 const uintptr_t a0 = reinterpret_cast<uintptr_t>(ref + (size_t)y0 * stride + x0);
                 const uint8_t *g = reinterpret_cast<const uint8_t *>(a0 & ~(uintptr_t)15);
                 __syncwarp(); // the previous tile's readers are done
-                for (int u = lane; u < rows * Cfg::NCH; u += 32) {
+                for (int u = lane; u < rows * Cfg::NCH; u += 32) { // raw aligned 16-byte chunks, asynchronously (LDGSTS)
                     const int R = u / Cfg::NCH, ch = u - R * Cfg::NCH;
-                    *reinterpret_cast<uint4 *>(tile + refine_rowoff(R, Cfg::PITCH) + 16 * ch) =
-                        __ldg(reinterpret_cast<const uint4 *>(g + (size_t)R * stride) + ch);
+                    cp_async16(tile + refine_rowoff(R, Cfg::PITCH) + 16 * ch, g + (size_t)R * stride + 16 * ch);
                 }
+                cp_async_wait_all();
                 __syncwarp();
                 uint32_t acc[REFINE_YT][2];
 #pragma unroll
                 for (int ty = 0; ty < REFINE_YT; ++ty) acc[ty][0] = acc[ty][1] = 0;
                 const int boff = (int)(a0 & 15) + c;
                 if (kw == BWW)
-                    refine_rows<BWW, true>(src0, src_pitch, tile, boff, rs, nrows, kw, rq, ny, acc);
+                    refine_rows<BWW, true>(sm->src, BWW * 4, tile, boff, rs, nrows, kw, rq, ny, acc);
                 else
-                    refine_rows<BWW, false>(src0, src_pitch, tile, boff, rs, nrows, kw, rq, ny, acc);
+                    refine_rows<BWW, false>(sm->src, BWW * 4, tile, boff, rs, nrows, kw, rq, ny, acc);
 #pragma unroll
                 for (int ty = 0; ty < REFINE_YT; ++ty)
 #pragma unroll
@@ -907,7 +937,7 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
     mark(); // 3: HME level 0
     if (f.hme_l1) {
         if (f.refine_small)
-            refine_kernel<8><<<N, 128, 4 * RefineCfg<8>::BYTES, st>>>(a, 1, 4);
+            refine_kernel<8><<<N, 128, sizeof(RefineSmem<8>), st>>>(a, 1, 4);
         else
             engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 2, 4);
         ++launches;
@@ -916,7 +946,7 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
         scalar_kernel<S_L1, S_L1><<<sg, 128, 0, st>>>(a);
         mark(); // 4: HME level 1
         if (f.refine_small)
-            refine_kernel<16><<<N, 128, 4 * RefineCfg<16>::BYTES, st>>>(a, 0, 5);
+            refine_kernel<16><<<N, 128, sizeof(RefineSmem<16>), st>>>(a, 0, 5);
         else
             engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 3, 5);
         ++launches;

@@ -50,6 +50,14 @@
 #define SVTME_FP_DIRECT_MAX 96 // search areas up to this many positions skip the shared-memory staging
 #endif
 
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src) { // LDGSTS: global -> shared, no registers
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async8(void *smem_dst, const void *gmem_src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.commit_group;\n cp.async.wait_group 0;" ::: "memory"); }
+
 __device__ __forceinline__ uint32_t vsad4(uint32_t a, uint32_t b, uint32_t acc) {
     uint32_t r;
     asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(acc));
@@ -1179,11 +1187,13 @@ __device__ __forceinline__ void fp_stage_raw(uint8_t *arena, const uint8_t *__re
     const uint32_t mg = 0xFFFFFFFFu / (uint32_t)nch + 1u;
     for (int i = threadIdx.x; i < total; i += FP_NT) {
         const int R = (int)__umulhi((uint32_t)i, mg), ch = i - R * nch;
-        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(g16 + (size_t)R * gstride) + ch);
-        uint2 *d = reinterpret_cast<uint2 *>(arena + fp_raw_rowoff(R, pitch) + 16 * ch);
-        d[0] = make_uint2(v.x, v.y);
-        d[1] = make_uint2(v.z, v.w);
+        // rows are 8-byte aligned in the tile (fp_raw_rowoff): two 8-byte asynchronous copies per chunk
+        const uint8_t *gsrc = g16 + (size_t)R * gstride + 16 * ch;
+        uint8_t *d = arena + fp_raw_rowoff(R, pitch) + 16 * ch;
+        cp_async8(d, gsrc);
+        cp_async8(d + 8, gsrc + 8);
     }
+    cp_async_wait_all();
 }
 
 // All threads call with identical arguments. ref0: global pointer to the reference pixel under

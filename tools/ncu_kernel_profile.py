@@ -77,9 +77,9 @@ for k, rows in zip(summary, sections):
         if op == "VABSDIFF4":
             chv[c] += e
     if lines_of:
-        name = re.sub(r"[^A-Za-z0-9_]", "", k["kernel"].split("(")[0].replace("void ", ""))
+        name = re.sub(r"[^A-Za-z0-9_]", "", k["kernel"].replace("void ", "").split("(")[0].split("<")[0])
         tmpl = re.search(r"<(\(int\))?(\d+)>|<\(bool\)(\d)>", k["kernel"])
-        cands = [fn for fn in lines_of if name.split("<")[0][:12] in fn]
+        cands = [fn for fn in lines_of if name in fn]
         if tmpl:
             num = tmpl.group(2) or tmpl.group(3)
             cands = [fn for fn in cands if ("ILi%sE" % num) in fn or ("ILb%sE" % num) in fn] or cands

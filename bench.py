@@ -204,6 +204,13 @@ def main():
     ap.add_argument("--e2e-chunks", default="4,12,16", help="pictures per chunk of the pipelined end-to-end run "
                     "(decode order; the last value repeats)")
     ap.add_argument("--e2e-depth", type=int, default=2, help="chunks in flight before the oldest one is collected")
+    ap.add_argument("--e2e-chunks-shared", default="1,2,4", help="--pyramids nccl: pictures PER RANK in each global chunk of the "
+                    "pipelined end-to-end run (the last value repeats)")
+    ap.add_argument("--e2e-source", default="msb8", choices=["msb8", "samples16"],
+                    help="10-bit workloads, end-to-end run: 'msb8' uploads the 8-bit MSB plane the encoder already holds on the host "
+                         "(input_padded_pic->buffer_y, filled by svt_aom_un_pack2d in resource coordination, "
+                         "resource_coordination_process.c:857,1022) — what the reference's ME reads; 'samples16' uploads the "
+                         "16-bit samples and lets the pyramid kernel take the 8 MSBs")
     ap.add_argument("--cpu-pictures", type=int, default=0, help="pictures in the bounded CPU sample (0: 16 at 1080p, 8 at 4K, 4 at 8K)")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="repeat the CPU sample for about this long")
     args = ap.parse_args()
@@ -289,19 +296,22 @@ def main():
     else:
         host = torch.from_numpy(seq).pin_memory()
     dev = host.to("cuda", non_blocking=False)
-    ses = me.MeSession(local_rank, W, H, capacity=F)
+    e2e_bits = 8 if (bits == 10 and args.e2e_source == "msb8") else bits
+    host_e2e = torch.from_numpy(seq).pin_memory() if (bits == 10 and e2e_bits == 8) else host
+    e2e_frame_bytes = W * H * (2 if e2e_bits == 10 else 1)
+    n_slots = -(-F // world) * world if (by_picture and args.pyramids == "nccl") else F  # whole groups of N slots
+    ses = me.MeSession(local_rank, W, H, capacity=n_slots)
     stream = torch.cuda.Stream()  # a non-default stream: the library treats NULL as "use the private stream"
     torch.cuda.set_stream(stream)
     ses.set_stream(stream.cuda_stream)
     specs = build_specs(abi, gop, wl, ses.derive_params)
     share = None
+    all_specs = specs
     if by_picture:
         mine = shard.rank_plan(len(specs), world, rank)
         frames_here = shard.pictures_for(specs, mine)
         if args.pyramids == "nccl":
-            needed = [shard.pictures_for(specs, shard.rank_plan(len(specs), world, r)) for r in range(world)]
-            wanted = sorted({p for need in needed for p in need})
-            share = dict(plan=shard.sharing_plan(needed, world), owned=[p for p in wanted if shard.pyramid_owner(p, world) == rank])
+            share = dict(owned=[p for p in range(F) if shard.pyramid_owner(p, world) == rank])
         specs = [specs[i] for i in mine]
     else:
         frames_here = list(range(F))
@@ -309,13 +319,30 @@ def main():
     frame_bytes = W * H * (2 if bits == 10 else 1)
     d2h_bytes = sum(a.nbytes for o in outs for a in o.values())
 
+    if share:
+        # picture p -> ring slot p on every rank (slots are handed out in order on a fresh handle), built by rank p % N
+        xs = torch.cuda.Stream()  # the exchange stream: NCCL work is ordered against it, never against the host
+        ses.external_write_begin(list(range(n_slots)), xs.cuda_stream)
+        pool_ptr = ses.plane_device_ptr(0, 0)[0]
+        slot_bytes = sum(ses.plane_device_ptr(0, l)[1] for l in range(3))
+        for pnum in (1, n_slots - 1):
+            if ses.plane_device_ptr(pnum, 0)[0] != pool_ptr + pnum * slot_bytes:
+                raise RuntimeError("ring slots are expected in picture order")
+        share.update(xs=xs, pool=pool_ptr, slot_bytes=slot_bytes, cache={}, moved=0)
+
+    def exchange(groups, pictures):
+        """All-gather the slots of `groups` on the exchange stream: after the owners' builds, after the launches that
+        still read those slots; the launches enqueued later wait for it. No host synchronisation."""
+        ses.external_write_begin(pictures, share["xs"].cuda_stream)
+        with torch.cuda.stream(share["xs"]):
+            share["moved"] = shard.all_gather_groups(groups, rank, world, dist, torch, share["pool"], share["slot_bytes"], share["cache"])
+        ses.external_write_end(share["xs"].cuda_stream)
+
     def put_shared(base_ptr, device):
-        """Owners upload + build, then every pyramid another GPU references is broadcast into its ring slot there."""
+        """Owners upload + build, then every group of N slots is all-gathered in place."""
         ses.put_pictures(share["owned"], [base_ptr + f * frame_bytes for f in share["owned"]], W, device=device, bits=bits)
-        ses.sync()  # the builds run on the library's upload stream; the collective must see them done
-        if "slot_bytes" not in share:
-            share["slot_bytes"] = sum(ses.plane_device_ptr(share["owned"][0], l)[1] for l in range(3))
-        share["moved"] = shard.share_pyramids(ses, share["plan"], rank, dist, torch, share["slot_bytes"], share.setdefault("cache", {}))
+        groups = list(range(n_slots // world))
+        exchange(groups, list(range(n_slots)))
 
     def step_resident():
         if share:
@@ -340,8 +367,25 @@ def main():
                     have.add(f)
                     need.append(f)
         cj, co = ses.make_jobs(part, deep=False)
-        chunks.append((need, [host.data_ptr() + f * frame_bytes for f in need], cj, co))
+        chunks.append((need, [host_e2e.data_ptr() + f * e2e_frame_bytes for f in need], cj, co))
     e2e_frames = len(share["owned"]) if share else len(have)
+    chunks_sh = []
+    if share:
+        # pipelined picture-sharded run: GLOBAL chunks in decode order; every rank runs its share of each chunk and all
+        # ranks exchange the same groups of ring slots before it (owners upload + build, one in-place all-gather per group)
+        gsz = [world * int(x) for x in args.e2e_chunks_shared.split(",") if x]
+        pos, have_g = 0, set()
+        while pos < len(all_specs):
+            n = gsz[min(len(chunks_sh), len(gsz) - 1)]
+            idx = range(pos, min(pos + n, len(all_specs)))
+            pos += n
+            pics = [f for i in idx for f in [all_specs[i][1]] + list(all_specs[i][2].values())]
+            groups = [g for g in shard.gather_groups(pics, world) if g not in have_g]
+            have_g.update(groups)
+            part = [all_specs[i] for i in idx if i % world == rank]
+            cj, co = ses.make_jobs(part, deep=False) if part else (None, [])
+            own = [g * world + rank for g in groups if g * world + rank < F]
+            chunks_sh.append((groups, own, [host_e2e.data_ptr() + f * e2e_frame_bytes for f in own], cj, co))
     sharing_info = None
     if share:
         # one-time check outside the timed region: a pyramid received over NCCL equals the one built locally
@@ -356,20 +400,35 @@ def main():
                         raise RuntimeError("rank %d: pyramid of picture %d (level %d) received over NCCL differs from a local build"
                                            % (rank, pnum, lvl))
                 chk.release_picture(pnum)
-        sharing_info = {"collective": "ncclSend/ncclRecv of the three padded planes of a ring slot, one NCCL group per step (torch.distributed.batch_isend_irecv, in place)",
-                        "pictures_shared_per_step": len(share["plan"]), "bytes_per_step": int(share["moved"]),
-                        "pictures_built_here": len(share["owned"]), "verified_against_local_build": foreign}
+        sharing_info = {"collective": "in-place ncclAllGather (torch.distributed.all_gather_into_tensor) over the N consecutive ring slots "
+                                      "of a picture group, one per group, on an exchange stream ordered by events against the builds "
+                                      "and the launches (svtme_external_write_begin / _end): no host synchronisation",
+                        "groups_per_step": n_slots // world, "bytes_received_per_step": int(share["moved"]) if not chunks_sh else
+                        int((world - 1) * share["slot_bytes"] * (n_slots // world)),
+                        "pictures_built_here": len(share["owned"]), "verified_against_local_build": foreign,
+                        "e2e_chunks": [len(c[4]) for c in chunks_sh]}
 
     def step_e2e_shared():
-        put_shared(host.data_ptr(), False)
-        ses.run_jobs(jobs)
+        pending = []
+        for groups, own, ptrs, cj, _ in chunks_sh:
+            if own:
+                ses.put_pictures(own, ptrs, W, device=False, bits=e2e_bits)
+            if groups:
+                exchange(groups, [p for g in groups for p in range(g * world, (g + 1) * world)])
+            if cj is not None:
+                ses.submit_jobs(cj)
+                pending.append(cj)
+            while len(pending) > args.e2e_depth:
+                ses.collect_jobs(pending.pop(0))
+        for cj in pending:
+            ses.collect_jobs(cj)
 
     def step_e2e():
         if share:
             return step_e2e_shared()
         for c, (need, ptrs, cj, _) in enumerate(chunks):
             if need:
-                ses.put_pictures(need, ptrs, W, device=False, bits=bits)
+                ses.put_pictures(need, ptrs, W, device=False, bits=e2e_bits)
             ses.submit_jobs(cj)
             if c >= args.e2e_depth:
                 ses.collect_jobs(chunks[c - args.e2e_depth][2])
@@ -451,7 +510,7 @@ def main():
         # bit-exactness of THIS run's GPU results against the reference outputs of the CPU sample: the arrays the
         # end-to-end steps left in the callers' SvtMeOut buffers, and the device-resident launch fetched now
         ses.fetch_jobs(jobs)
-        e2e_outs = outs if share else [o for c in chunks for o in c[3]]
+        e2e_outs = [o for c in chunks_sh for o in c[4]] if share else [o for c in chunks for o in c[3]]
         n_arrays, bad = compare_outputs(cpu["outs"], [("e2e", e2e_outs), ("resident", outs)])
         parity = {"pictures": len(cpu["outs"]), "arrays": n_arrays, "bit_exact": not bad, "against": "oracle/_ref (compiled "
                   "reference, %s kernels)" % cpu["simd"] if cpu["kind"] == "reference" else "oracle port",
@@ -463,8 +522,10 @@ def main():
                 "scaling": "strong" if by_picture else "weak",
                 "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": config,
                 "frames_per_s": n_streams * F / (ms_step * 1e-3),
-                "e2e": {"value": e2e_val, "unit": "SB/s", "h2d_bytes_per_step": e2e_frames * frame_bytes,
-                        "api": ("svtme_put_pictures_10bit (pinned host 16-bit luma)" if bits == 10 else "svtme_put_pictures (pinned host luma)") + " + svtme_submit_pictures / svtme_collect_results (results "
+                "e2e": {"value": e2e_val, "unit": "SB/s", "h2d_bytes_per_step": e2e_frames * e2e_frame_bytes,
+                        "api": ("svtme_put_pictures_10bit (pinned host 16-bit luma)" if e2e_bits == 10 else
+                                ("svtme_put_pictures (pinned host 8-bit MSB plane of the 10-bit source, the buffer the reference's ME reads)"
+                                 if bits == 10 else "svtme_put_pictures (pinned host luma)")) + " + svtme_submit_pictures / svtme_collect_results (results "
                                "in host SvtMeOut arrays), chunks of %s pictures, %d in flight" % (args.e2e_chunks, args.e2e_depth),
                         "d2h_bytes_per_step": d2h_bytes,
                         "frames_per_s": n_streams * F / (ms_e2e / args.steps * 1e-3), "ms_per_step": ms_e2e / args.steps},

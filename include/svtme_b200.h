@@ -207,6 +207,19 @@ int svtme_release_picture(SvtMeHandle *h, uint64_t pic_num);
 int svtme_plane_device_ptr(SvtMeHandle *h, uint64_t pic_num, int level, void **ptr, size_t *bytes);
 /* Declare a picture resident whose planes were written externally (NCCL recv) */
 int svtme_adopt_picture(SvtMeHandle *h, uint64_t pic_num);
+/* Ordering for pyramids that another GPU writes into / reads from ring slots on the CALLER's stream (NCCL send / recv /
+ * all-gather over NVLink), without host synchronisation. No reference counterpart: the reference shares pa-reference
+ * objects by pointer in host memory (me_process.c:248-262). begin: the pictures get ring slots if they have none and
+ * `cuda_stream` (a cudaStream_t) is made to wait for the pyramid builds enqueued so far and for every launch in flight
+ * that still reads one of those slots. end: everything enqueued on `cuda_stream` so far completes before any later
+ * launch, upload or build of this handle starts. */
+int svtme_external_write_begin(SvtMeHandle *h, uint32_t n, const uint64_t *picture_numbers, void *cuda_stream);
+int svtme_external_write_end(SvtMeHandle *h, void *cuda_stream);
+/* One process driving several GPUs (the reference is one process with a pool of ME threads, enc_handle.c:768-805): copy
+ * the pyramid of pic_num from the handle that built it into a ring slot of a handle on another device
+ * (cudaMemcpyPeerAsync on the destination's upload stream, ordered after the source's builds and the destination's
+ * readers of the slot). Both handles must have been opened for the same picture size. */
+int svtme_share_picture(SvtMeHandle *src, SvtMeHandle *dst, uint64_t pic_num);
 
 /* Open-loop ME of one picture against refs[list][idx] (picture numbers previously put).
  * Replaces the b64 loop of me_process.c:174-289 calling svt_aom_motion_estimation_b64

@@ -175,6 +175,9 @@ def load_library():
         "svtme_release_picture": (C.c_int, [vp, u64]),
         "svtme_plane_device_ptr": (C.c_int, [vp, u64, C.c_int, P(vp), P(C.c_size_t)]),
         "svtme_adopt_picture": (C.c_int, [vp, u64]),
+        "svtme_external_write_begin": (C.c_int, [vp, u32, P(u64), vp]),
+        "svtme_external_write_end": (C.c_int, [vp, vp]),
+        "svtme_share_picture": (C.c_int, [vp, vp, u64]),
         "svtme_run_picture": (C.c_int, [vp, P(SvtMeParams), u64, P((u64 * MAX_REFS) * MAX_LISTS), P(SvtMeOut)]),
         "svtme_run_pictures": (C.c_int, [vp, P(SvtMeJob), u32]),
         "svtme_launch_pictures": (C.c_int, [vp, P(SvtMeJob), u32]),

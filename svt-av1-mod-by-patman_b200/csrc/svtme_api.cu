@@ -94,6 +94,8 @@ struct SvtMeHandle {
     void *x_states[SVTME_NS] = {};      // per extra compute stream: its own per-b64 scratch
     size_t x_states_bytes[SVTME_NS] = {};
     cudaEvent_t h2d_ev, build_ev;
+    cudaEvent_t ext_ev = nullptr;   // svtme_external_write_end / svtme_share_picture: "externally written pyramids are complete"
+    bool ext_recorded = false;
     cudaEvent_t launch_ev[SVTME_LAUNCH_EV_RING]; // "launch seq is done", indexed seq % ring (Batch objects and their events are recycled)
     bool build_recorded = false;
     uint8_t *u16_stage = nullptr; // 16-bit input pictures of the batched build in flight (svtme_put_pictures_10bit)
@@ -197,6 +199,7 @@ extern "C" int svtme_open(int device, uint32_t width, uint32_t height, uint32_t 
     for (int k = 1; k < SVTME_NS && e == cudaSuccess; ++k) e = cudaStreamCreateWithFlags(&h->xstream[k], cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->h2d_ev, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->build_ev, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ext_ev, cudaEventDisableTiming);
     for (int k = 0; k < SVTME_PUT_RING && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&h->put[k].ev, cudaEventDisableTiming);
     for (int k = 0; k < SVTME_LAUNCH_EV_RING; ++k) h->launch_ev[k] = nullptr;
     for (int k = 0; k < SVTME_LAUNCH_EV_RING && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&h->launch_ev[k], cudaEventDisableTiming);
@@ -241,6 +244,7 @@ extern "C" void svtme_close(SvtMeHandle *h) {
     }
     cudaEventDestroy(h->h2d_ev);
     cudaEventDestroy(h->build_ev);
+    if (h->ext_ev) cudaEventDestroy(h->ext_ev);
     if (h->origin_ev) cudaEventDestroy(h->origin_ev);
     for (int k = 0; k < SVTME_LAUNCH_EV_RING; ++k) cudaEventDestroy(h->launch_ev[k]);
     cudaStreamDestroy(h->h2d_stream);
@@ -362,6 +366,7 @@ static int put_batch(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const
     }
     for (int k = 0; k < SVTME_NS; ++k)
         if (newest[k]) CU(cudaStreamWaitEvent(cs, h->launch_ev[newest[k] % SVTME_LAUNCH_EV_RING], 0));
+    if (h->ext_recorded) CU(cudaStreamWaitEvent(cs, h->ext_ev, 0));   // an exchange that reads or writes ring slots is still in flight
     for (int si : touched) // the writes below are ordered behind every reader now: the slots start a new life
         for (int k = 0; k < SVTME_NS; ++k) h->slots[si].last_reader[k] = 0;
     if (any_copy) {
@@ -432,6 +437,89 @@ extern "C" int svtme_adopt_picture(SvtMeHandle *h, uint64_t pic_num) {
     std::lock_guard<std::mutex> lk(h->mu);
     const int si = find_slot(h, pic_num, true);
     if (si == -2) return fail(SVTME_ERR_NOMEM, "svtme_adopt_picture: pyramid ring full");
+    return SVTME_OK;
+}
+
+// ---- pyramids written by someone else (NCCL receive on the caller's stream, peer copy): ordering without host syncs.
+// svtme_external_write_begin: the pictures get ring slots if they have none, and `cuda_stream` is made to wait for
+// (a) the pyramid builds enqueued so far (a sender reads what svtme_put_pictures produced) and (b) every launch in
+// flight that still reads one of those slots (a receiver overwrites them). svtme_external_write_end: everything
+// enqueued on `cuda_stream` up to here must complete before any later launch, build or upload of this handle runs.
+extern "C" int svtme_external_write_begin(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, void *cuda_stream) {
+    if (!h || (n && !pic_nums)) return fail(SVTME_ERR_INVALID, "svtme_external_write_begin: bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(cudaSetDevice(h->device));
+    cudaStream_t cs = (cudaStream_t)cuda_stream;
+    {
+        size_t fresh = 0, free_slots = 0;
+        for (uint32_t i = 0; i < n; ++i) {
+            bool seen = h->index.count(pic_nums[i]) != 0;
+            for (uint32_t k = 0; k < i && !seen; ++k) seen = pic_nums[k] == pic_nums[i];
+            fresh += seen ? 0 : 1;
+        }
+        for (const Slot &sl : h->slots) free_slots += sl.used ? 0 : 1;
+        if (fresh > free_slots) return fail(SVTME_ERR_NOMEM, "svtme_external_write_begin: pyramid ring full");
+    }
+    uint64_t newest[SVTME_NS] = {};
+    std::vector<int> touched;
+    for (uint32_t i = 0; i < n; ++i) {
+        const int si = find_slot(h, pic_nums[i], true);
+        if (si < 0) return fail(SVTME_ERR_NOMEM, "svtme_external_write_begin: pyramid ring full");
+        touched.push_back(si);
+        for (int k = 0; k < SVTME_NS; ++k)
+            if (h->slots[si].last_reader[k] > newest[k]) newest[k] = h->slots[si].last_reader[k];
+    }
+    if (h->build_recorded) CU(cudaStreamWaitEvent(cs, h->build_ev, 0));
+    for (int k = 0; k < SVTME_NS; ++k)
+        if (newest[k]) CU(cudaStreamWaitEvent(cs, h->launch_ev[newest[k] % SVTME_LAUNCH_EV_RING], 0));
+    for (int si : touched)
+        for (int k = 0; k < SVTME_NS; ++k) h->slots[si].last_reader[k] = 0;
+    return SVTME_OK;
+}
+
+extern "C" int svtme_external_write_end(SvtMeHandle *h, void *cuda_stream) {
+    if (!h) return fail(SVTME_ERR_INVALID, "svtme_external_write_end: null handle");
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(cudaSetDevice(h->device));
+    CU(cudaEventRecord(h->ext_ev, (cudaStream_t)cuda_stream));
+    h->ext_recorded = true;
+    return SVTME_OK;
+}
+
+// One process, several GPUs (the reference is ONE process with a pool of ME threads): copy the pyramid of `pic_num`
+// from the handle that built it into a ring slot of a handle on another device — cudaMemcpyPeerAsync over NVLink on
+// the destination's upload stream, ordered after the source's builds and after the destination's launches that still
+// read the slot; the destination's later launches wait for the copy, the source's next upload into the slot too.
+extern "C" int svtme_share_picture(SvtMeHandle *src, SvtMeHandle *dst, uint64_t pic_num) {
+    if (!src || !dst || src == dst) return fail(SVTME_ERR_INVALID, "svtme_share_picture: two different handles are needed");
+    if (src->width != dst->width || src->height != dst->height || src->slot_bytes != dst->slot_bytes)
+        return fail(SVTME_ERR_INVALID, "svtme_share_picture: the handles hold pictures of different sizes");
+    std::mutex &m1 = src < dst ? src->mu : dst->mu, &m2 = src < dst ? dst->mu : src->mu; // fixed lock order
+    std::lock_guard<std::mutex> l1(m1), l2(m2);
+    const int ss = find_slot(src, pic_num, false);
+    if (ss < 0) return fail(SVTME_ERR_NOTFOUND, "svtme_share_picture: picture not resident on the source handle");
+    if (dst->index.count(pic_num) == 0) {
+        bool any_free = false;
+        for (const Slot &sl : dst->slots) any_free |= !sl.used;
+        if (!any_free) return fail(SVTME_ERR_NOMEM, "svtme_share_picture: destination pyramid ring full");
+    }
+    CU(cudaSetDevice(dst->device));
+    const int ds = find_slot(dst, pic_num, true);
+    cudaStream_t cs = dst->h2d_stream;
+    if (src->build_recorded) CU(cudaStreamWaitEvent(cs, src->build_ev, 0));
+    if (src->ext_recorded) CU(cudaStreamWaitEvent(cs, src->ext_ev, 0));
+    Slot &d = dst->slots[ds];
+    for (int k = 0; k < SVTME_NS; ++k) {
+        if (d.last_reader[k]) CU(cudaStreamWaitEvent(cs, dst->launch_ev[d.last_reader[k] % SVTME_LAUNCH_EV_RING], 0));
+        d.last_reader[k] = 0;
+    }
+    CU(cudaMemcpyPeerAsync(d.pyr.lvl[0].base, dst->device, src->slots[ss].pyr.lvl[0].base, src->device, src->slot_bytes, cs));
+    CU(cudaEventRecord(dst->build_ev, cs));
+    dst->build_recorded = true;
+    // the copy READS the source's slot: the source's upload stream (in order with its later uploads) waits for it. (An
+    // event can only be recorded on a stream of its own device, but any stream may wait for any event.)
+    CU(cudaSetDevice(src->device));
+    CU(cudaStreamWaitEvent(src->h2d_stream, dst->build_ev, 0));
     return SVTME_OK;
 }
 
@@ -626,6 +714,7 @@ static int launch_into(SvtMeHandle *h, Batch *B, const SvtMeJob *jobs, uint32_t 
     }
     // entries the stage never writes (pruned candidates) read as zero, like a fresh MeSbResults
     if (h->build_recorded) CU(cudaStreamWaitEvent(st, h->build_ev, 0)); // pyramids are built on the upload stream
+    if (h->ext_recorded) CU(cudaStreamWaitEvent(st, h->ext_ev, 0));     // ... or written by an exchange on the caller's stream
     CU(svtme_launch_zero_fill(B->ob.dev, total, st));
     CU(svtme_launch_fetch_from_host(B->d_jobs, B->h_jobs, up16(sizeof(DevJob) * n), st));
     CU(cudaEventRecord(B->jobs_ev, st));

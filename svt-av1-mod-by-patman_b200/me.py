@@ -92,6 +92,19 @@ class MeSession:
     def adopt_picture(self, pic_num):
         _check(self.lib.svtme_adopt_picture(self.h, pic_num), self.lib)
 
+    def external_write_begin(self, picture_numbers, cuda_stream_ptr):
+        """Ring slots for the pictures + `cuda_stream` waits for pending builds and for launches that still read the slots."""
+        n = len(picture_numbers)
+        _check(self.lib.svtme_external_write_begin(self.h, n, (C.c_uint64 * n)(*picture_numbers), cuda_stream_ptr), self.lib)
+
+    def external_write_end(self, cuda_stream_ptr):
+        """Later launches / uploads wait for everything enqueued on `cuda_stream` so far (the exchange)."""
+        _check(self.lib.svtme_external_write_end(self.h, cuda_stream_ptr), self.lib)
+
+    def share_picture_to(self, other, pic_num):
+        """Peer copy of a pyramid into a handle on another device of the same process."""
+        _check(self.lib.svtme_share_picture(self.h, other.h, pic_num), self.lib)
+
     def make_jobs(self, specs, deep=False):
         """specs: list of (params, cur, {(list, idx): pic_num}). Returns (SvtMeJob array, [arrays])."""
         jobs = (abi.SvtMeJob * len(specs))()

@@ -139,3 +139,38 @@ def share_pyramids(ses, plan, rank: int, dist, torch, slot_bytes: int, cache=Non
         for req in dist.batch_isend_irecv(ops):
             req.wait()
     return moved
+
+
+# ---------------------------------------------------------------- pyramids all-gathered in place (pipelined form)
+def gather_groups(pictures: Sequence[int], world_size: int) -> List[int]:
+    """Picture p lives in ring slot p on every rank and is built by rank p % N: the N pictures of group g =
+    [g N, (g + 1) N) sit in N consecutive slots, one built by each rank, and ONE in-place ncclAllGather over that
+    span gives every rank the whole group. Returns the groups that hold `pictures`, in order of first appearance."""
+    seen, order = set(), []
+    for p in pictures:
+        g = int(p) // world_size
+        if g not in seen:
+            seen.add(g)
+            order.append(g)
+    return order
+
+
+def all_gather_groups(groups: Sequence[int], rank: int, world: int, dist, torch, pool_ptr: int, slot_bytes: int, cache=None,
+                      pool=None) -> int:
+    """In-place all-gather (NCCL over NVLink / NVSwitch) of the ring slots of every group in `groups`, enqueued behind
+    the CURRENT torch stream; the caller brackets the call with MeSession.external_write_begin / _end on that stream,
+    so nothing synchronises with the host. `pool`: a 1-D uint8 tensor that IS the ring (CPU tests with gloo); otherwise
+    the ring is the device memory at pool_ptr. Returns the bytes this rank received."""
+    cache = {} if cache is None else cache
+    moved = 0
+    for g in groups:
+        t = cache.get(g)
+        if t is None:
+            if pool is not None:
+                t = pool[g * world * slot_bytes:(g + 1) * world * slot_bytes]
+            else:
+                t = torch.as_tensor(_DeviceBytes(pool_ptr + g * world * slot_bytes, world * slot_bytes), device="cuda")
+            cache[g] = t
+        dist.all_gather_into_tensor(t, t[rank * slot_bytes:(rank + 1) * slot_bytes])
+        moved += (world - 1) * slot_bytes
+    return moved

@@ -16,6 +16,7 @@ import make_golden as G
 pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 me = importlib.import_module(U.PKG + ".me")
+shard = importlib.import_module(U.PKG + ".shard")
 
 
 def gpu_stage(seq, p, cur, refs, W, H, deep=True):
@@ -376,3 +377,49 @@ def test_two_handles_from_two_threads_and_on_two_devices():
     for dev in range(2):
         for k in want:
             assert np.array_equal(want[k], res[dev][k]), (dev, k)
+
+
+def test_share_picture_between_handles_and_external_writes():
+    """svtme_share_picture (peer copy of a pyramid into another handle's ring: another device when the box has two, else
+    device 0 again) and svtme_external_write_begin / _end (pyramids written on the caller's stream, here a device copy
+    standing in for an NCCL receive): ME on the receiving handle equals ME on the handle that built the pyramids, and the
+    ordering holds without host synchronisation across repeated rounds that overwrite the same slots."""
+    import torch
+    ndev = torch.cuda.device_count()
+    W, H = 320, 192
+    refs, cur = {(0, 0): 0, (1, 0): 2}, 1
+    d = U.derive_input(6, W, H, temporal_layer_index=1, ref_list0_count_try=1, ref_list1_count_try=1)
+    p = U.finish_params(derive(None, d), d, cur, refs)
+    seqs = [U.synth_sequence(W, H, 3, seed=40 + k, motion=(2 + k, -1)) for k in range(3)]
+    with me.MeSession(0, W, H, capacity=3) as a, me.MeSession(1 % ndev, W, H, capacity=3) as b, me.MeSession(0, W, H, capacity=3) as c:
+        xs = torch.cuda.Stream(device=0)
+        for rnd, seq in enumerate(seqs):  # back to back, no host sync in between: slots are overwritten while launches are queued
+            a.put_pictures([0, 1, 2], [np.ascontiguousarray(seq[n]).ctypes.data for n in range(3)], W)
+            ja, oa = a.make_jobs([(p, cur, refs)], deep=True)
+            a.submit_jobs(ja)
+            for n in range(3):
+                a.share_picture_to(b, n)
+            jb, ob = b.make_jobs([(p, cur, refs)], deep=True)
+            b.submit_jobs(jb)
+            # "receive" a's pyramids into c on the caller's stream
+            c.external_write_begin([0, 1, 2], xs.cuda_stream)
+            a.external_write_begin([0, 1, 2], xs.cuda_stream)  # sender side: wait for a's builds
+            with torch.cuda.stream(xs):
+                for n in range(3):
+                    nbytes = sum(a.plane_device_ptr(n, l)[1] for l in range(3))
+                    src = torch.as_tensor(shard._DeviceBytes(a.plane_device_ptr(n, 0)[0], nbytes), device="cuda:0")
+                    dst = torch.as_tensor(shard._DeviceBytes(c.plane_device_ptr(n, 0)[0], nbytes), device="cuda:0")
+                    dst.copy_(src, non_blocking=True)
+            c.external_write_end(xs.cuda_stream)
+            a.external_write_end(xs.cuda_stream)  # a's next upload into these slots waits for the copies that read them
+            jc, oc = c.make_jobs([(p, cur, refs)], deep=True)
+            c.submit_jobs(jc)
+            a.collect_jobs(ja)
+            b.collect_jobs(jb)
+            c.collect_jobs(jc)
+            pyr = {n: U.CpuPyramid("orc", seq[n], n) for n in range(3)}
+            want = U.cpu_me_picture("orc", p, pyr[cur], {k: pyr[v] for k, v in refs.items()})
+            for k in want:
+                assert np.array_equal(want[k], oa[0][k]), (rnd, "builder", k)
+                assert np.array_equal(want[k], ob[0][k]), (rnd, "peer copy", k)
+                assert np.array_equal(want[k], oc[0][k]), (rnd, "external write", k)

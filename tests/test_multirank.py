@@ -118,3 +118,48 @@ def test_two_ranks_gloo_picture_sharding_matches_single_process():
     for i in single:
         for k in single[i]:
             assert np.array_equal(single[i][k], merged[i][k]), (i, k)
+
+
+def _gather_worker(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        slot_bytes, n_slots = 48, 6  # three groups of two pictures; picture p sits in slot p and is built by rank p % 2
+        pool = torch.zeros(n_slots * slot_bytes, dtype=torch.uint8)
+        for p in range(n_slots):
+            if shard.pyramid_owner(p, world) == rank:
+                pool[p * slot_bytes:(p + 1) * slot_bytes] = torch.arange(slot_bytes, dtype=torch.uint8) + 7 * p
+        groups = shard.gather_groups([4, 5, 0, 3], world)  # first-need order: groups 2, 0, 1
+        moved = shard.all_gather_groups(groups, rank, world, dist, torch, 0, slot_bytes, pool=pool)
+        q.put((rank, groups, moved, pool.numpy().copy()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gather_groups_order_and_membership():
+    assert shard.gather_groups([32, 0, 16, 8, 4, 33, 7], 8) == [4, 0, 2, 1]
+    assert shard.gather_groups([], 4) == []
+
+
+@pytest.mark.timeout(300)
+def test_two_ranks_gloo_in_place_all_gather_of_ring_slot_groups():
+    """The pyramid exchange of the pipelined picture-sharded run, on CPU tensors: every rank owns one slot of each
+    group of N consecutive slots; after the in-place all-gather of a group every rank holds all of its slots."""
+    import torch.multiprocessing as mp
+    world, port = 2, _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_gather_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=240) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    want = np.concatenate([(np.arange(48) + 7 * p).astype(np.uint8) for p in range(6)])
+    for rank, groups, moved, pool in got:
+        assert groups == [2, 0, 1] and moved == 3 * 48
+        assert np.array_equal(pool, want), rank

@@ -32,7 +32,7 @@ sys.path.insert(0, ROOT)
 # One process per GPU shares the host cores: the library's result scatter gets cores / (2 x ranks) threads (1..4) and
 # idle OpenMP workers sleep instead of spinning (both read when the libraries load, i.e. before `import torch`).
 _world = int(os.environ.get("WORLD_SIZE", "1"))
-os.environ.setdefault("SVTME_SCATTER_THREADS", str(max(1, min(4, (os.cpu_count() or 1) // (2 * _world)))))
+os.environ.setdefault("SVTME_SCATTER_THREADS", str(max(1, min(8, (os.cpu_count() or 1) // (2 * _world)))))
 os.environ.setdefault("OMP_WAIT_POLICY", "passive")
 PKG = "svt-av1-mod-by-patman_b200"
 
@@ -201,9 +201,8 @@ def main():
                     help="--sharding picture: 'rebuild' = every GPU builds the pyramids it needs from the frames; 'nccl' = "
                          "picture p is uploaded and built on GPU p %% N only and sent (NCCL over NVLink) "
                          "into the ring slots of the GPUs that reference it")
-    ap.add_argument("--e2e-chunks", default="4,12,16", help="pictures per chunk of the pipelined end-to-end run "
-                    "(decode order; the last value repeats)")
-    ap.add_argument("--e2e-depth", type=int, default=2, help="chunks in flight before the oldest one is collected")
+    ap.add_argument("--e2e-chunks", default="32", help="pictures per chunk (batch) of the pipelined end-to-end run "
+                    "(decode order; the last value repeats): one mini-GOP of the look-ahead window per batch")
     ap.add_argument("--e2e-chunks-shared", default="1,2,4", help="--pyramids nccl: pictures PER RANK in each global chunk of the "
                     "pipelined end-to-end run (the last value repeats)")
     ap.add_argument("--e2e-source", default="msb8", choices=["msb8", "samples16"],
@@ -300,7 +299,11 @@ def main():
     host_e2e = torch.from_numpy(seq).pin_memory() if (bits == 10 and e2e_bits == 8) else host
     e2e_frame_bytes = W * H * (2 if e2e_bits == 10 else 1)
     n_slots = -(-F // world) * world if (by_picture and args.pyramids == "nccl") else F  # whole groups of N slots
-    ses = me.MeSession(local_rank, W, H, capacity=n_slots)
+    # streamed end-to-end run: consecutive steps use alternating sets of ring slots (picture numbers offset by ALT), like a
+    # real stream whose new pictures get new pa-reference objects: the next step's uploads do not wait for the launches
+    # that still read the previous step's pictures
+    ALT = 1 << 20
+    ses = me.MeSession(local_rank, W, H, capacity=n_slots if (by_picture and args.pyramids == "nccl") else 2 * F)
     stream = torch.cuda.Stream()  # a non-default stream: the library treats NULL as "use the private stream"
     torch.cuda.set_stream(stream)
     ses.set_stream(stream.cuda_stream)
@@ -367,7 +370,16 @@ def main():
                     have.add(f)
                     need.append(f)
         cj, co = ses.make_jobs(part, deep=False)
-        chunks.append((need, [host_e2e.data_ptr() + f * e2e_frame_bytes for f in need], cj, co))
+        # the same chunk on the alternate slot set: picture numbers + ALT everywhere (distances are unchanged), same outputs
+        alt = []
+        for p0, cur, refs in part:
+            p1 = abi.SvtMeParams.from_buffer_copy(bytes(p0))
+            p1.picture_number = cur + ALT
+            for (li, ri), n_ in refs.items():
+                p1.ref_picture_number[li][ri] = n_ + ALT
+            alt.append((p1, cur + ALT, {k: v + ALT for k, v in refs.items()}))
+        cj_alt, co_alt = ses.make_jobs(alt, deep=False)
+        chunks.append((need, [host_e2e.data_ptr() + f * e2e_frame_bytes for f in need], cj, co, cj_alt, co_alt))
     e2e_frames = len(share["owned"]) if share else len(have)
     chunks_sh = []
     if share:
@@ -408,32 +420,73 @@ def main():
                         "pictures_built_here": len(share["owned"]), "verified_against_local_build": foreign,
                         "e2e_chunks": [len(c[4]) for c in chunks_sh]}
 
-    def step_e2e_shared():
-        pending = []
+    # Results are collected (wait for the download, scatter into the callers' SvtMeOut arrays) by a second host thread, in
+    # submission order, so that the thread that uploads / exchanges / submits never waits for a download: the reference's
+    # ME threads and the downstream process that consumes MotionEstimationResults are different threads too
+    # (me_process.c:304-313 posts to a FIFO). The step ends when the last batch has been collected.
+    import queue
+    collect_q = queue.Queue()
+    collect_err = []
+    # at most two steps' worth of batches in flight: the library recycles its batch objects (device + pinned result
+    # buffers), so nothing is allocated inside a timed region once the warm-up has created that many
+    in_flight = threading.BoundedSemaphore(2 * max(len(chunks_sh) if share else len(chunks), 1))
+
+    def collector():
+        while True:
+            cj = collect_q.get()
+            if cj is None:
+                return
+            try:
+                if not collect_err:
+                    ses.collect_jobs(cj)
+            except Exception as e:  # noqa: BLE001
+                collect_err.append(e)
+            finally:
+                in_flight.release()
+                collect_q.task_done()
+
+    collector_thread = threading.Thread(target=collector, daemon=True)
+    collector_thread.start()
+
+    def finish_step():
+        collect_q.join()
+        if collect_err:
+            raise collect_err[0]
+
+    def step_e2e_shared(drain=True):
         for groups, own, ptrs, cj, _ in chunks_sh:
             if own:
                 ses.put_pictures(own, ptrs, W, device=False, bits=e2e_bits)
             if groups:
                 exchange(groups, [p for g in groups for p in range(g * world, (g + 1) * world)])
             if cj is not None:
+                in_flight.acquire()
                 ses.submit_jobs(cj)
-                pending.append(cj)
-            while len(pending) > args.e2e_depth:
-                ses.collect_jobs(pending.pop(0))
-        for cj in pending:
-            ses.collect_jobs(cj)
+                collect_q.put(cj)
+        if drain:
+            finish_step()
 
-    def step_e2e():
+    def step_e2e(drain=True, alt=False):
         if share:
-            return step_e2e_shared()
-        for c, (need, ptrs, cj, _) in enumerate(chunks):
+            return step_e2e_shared(drain)
+        for c, (need, ptrs, cj, _, cj_alt, _) in enumerate(chunks):
+            if alt:
+                need, cj = [f + ALT for f in need], cj_alt
             if need:
                 ses.put_pictures(need, ptrs, W, device=False, bits=e2e_bits)
+            in_flight.acquire()
             ses.submit_jobs(cj)
-            if c >= args.e2e_depth:
-                ses.collect_jobs(chunks[c - args.e2e_depth][2])
-        for c in range(max(0, len(chunks) - args.e2e_depth), len(chunks)):
-            ses.collect_jobs(chunks[c][2])
+            collect_q.put(cj)
+        if drain:
+            finish_step()
+
+    def steps_e2e_streamed():
+        """K steps as a continuous stream: the next step's uploads and launches are enqueued while the previous step's
+        last batches still compute and download (no drain between steps, like pictures flowing through an encoder's
+        look-ahead); the region ends when every result of every step has been collected."""
+        for k in range(args.steps):
+            step_e2e(drain=False, alt=bool(k & 1))
+        finish_step()
 
     def barrier():
         torch.cuda.synchronize()
@@ -473,6 +526,8 @@ def main():
     for _ in range(max(1, args.warmup)):
         step_e2e()
     ms_e2e = timed(step_e2e, args.steps)
+    steps_e2e_streamed()  # warm-up: creates the batch objects the deeper queue needs
+    ms_e2e_streamed = timed(steps_e2e_streamed, 1)
     sampler.stop_flag = True
     if rank == 0:
         sampler.join(timeout=2)
@@ -511,7 +566,10 @@ def main():
         # end-to-end steps left in the callers' SvtMeOut buffers, and the device-resident launch fetched now
         ses.fetch_jobs(jobs)
         e2e_outs = [o for c in chunks_sh for o in c[4]] if share else [o for c in chunks for o in c[3]]
-        n_arrays, bad = compare_outputs(cpu["outs"], [("e2e", e2e_outs), ("resident", outs)])
+        checks = [("e2e", e2e_outs), ("resident", outs)]
+        if not share and args.steps > 1:
+            checks.append(("e2e streamed (alternate slot set)", [o for c in chunks for o in c[5]]))
+        n_arrays, bad = compare_outputs(cpu["outs"], checks)
         parity = {"pictures": len(cpu["outs"]), "arrays": n_arrays, "bit_exact": not bad, "against": "oracle/_ref (compiled "
                   "reference, %s kernels)" % cpu["simd"] if cpu["kind"] == "reference" else "oracle port",
                   "compared": "all SvtMeOut arrays of the sample's pictures, end-to-end and device-resident runs"}
@@ -522,13 +580,22 @@ def main():
                 "scaling": "strong" if by_picture else "weak",
                 "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": config,
                 "frames_per_s": n_streams * F / (ms_step * 1e-3),
-                "e2e": {"value": e2e_val, "unit": "SB/s", "h2d_bytes_per_step": e2e_frames * e2e_frame_bytes,
+                # headline end-to-end number: the K steps as a continuous stream of look-ahead windows (host buffers in, host
+                # result arrays out, every step's copies inside the timed region); the per-step-drained form is given beside it
+                "e2e": {"value": n_streams * sbs_step / (ms_e2e_streamed / args.steps * 1e-3), "unit": "SB/s",
+                        "h2d_bytes_per_step": e2e_frames * e2e_frame_bytes, "d2h_bytes_per_step": d2h_bytes,
+                        "ms_per_step": ms_e2e_streamed / args.steps,
+                        "frames_per_s": n_streams * F / (ms_e2e_streamed / args.steps * 1e-3),
+                        "mode": "streamed: the %d timed steps are enqueued back to back (consecutive steps use alternating sets of "
+                                "ring slots, like new pictures of a stream), results are collected in order by a second host thread, "
+                                "the region ends when the last result array is filled" % args.steps,
                         "api": ("svtme_put_pictures_10bit (pinned host 16-bit luma)" if e2e_bits == 10 else
                                 ("svtme_put_pictures (pinned host 8-bit MSB plane of the 10-bit source, the buffer the reference's ME reads)"
-                                 if bits == 10 else "svtme_put_pictures (pinned host luma)")) + " + svtme_submit_pictures / svtme_collect_results (results "
-                               "in host SvtMeOut arrays), chunks of %s pictures, %d in flight" % (args.e2e_chunks, args.e2e_depth),
-                        "d2h_bytes_per_step": d2h_bytes,
-                        "frames_per_s": n_streams * F / (ms_e2e / args.steps * 1e-3), "ms_per_step": ms_e2e / args.steps},
+                                 if bits == 10 else "svtme_put_pictures (pinned host luma)")) +
+                               " + svtme_submit_pictures / svtme_collect_results (results in host SvtMeOut arrays), batches of %s pictures"
+                               % (args.e2e_chunks_shared + " per rank" if share else args.e2e_chunks),
+                        "drained": {"value": e2e_val, "unit": "SB/s", "ms_per_step": ms_e2e / args.steps,
+                                    "note": "every step drained (all results collected) before the next one starts"}},
                 "gpu_launches": int(launches),
                 **({"pyramid_sharing": sharing_info} if sharing_info else {}),
                 # the dominant launch slot of the pipeline (its search kernel + the scalar plan/post step(s) timed with
@@ -557,6 +624,7 @@ def main():
         if bad:
             sys.stderr.write("bench: GPU results differ from the reference: %s\n" % ", ".join(bad[:8]))
             exit_code = 1
+    collect_q.put(None)
     ses.close()
     if world > 1:
         dist.destroy_process_group()

@@ -834,10 +834,22 @@ extern "C" int svtme_submit_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint3
     if (!h || !jobs || n == 0) return fail(SVTME_ERR_INVALID, "svtme_submit_pictures: bad argument");
     std::lock_guard<std::mutex> lk(h->mu);
     CU(cudaSetDevice(h->device));
-    Batch *B;
+    // a recycled batch object whose buffers already hold this batch (best fit), else the largest free one (it grows),
+    // else a new one: growing a buffer synchronises the device, which a steady stream of batches must not do
+    Batch *B = nullptr;
     if (!h->free_batches.empty()) {
-        B = h->free_batches.back();
-        h->free_batches.pop_back();
+        const size_t need = results_bytes(h, jobs, n);
+        size_t best = 0;
+        bool fits = false;
+        for (size_t i = 0; i < h->free_batches.size(); ++i) {
+            const Batch *c = h->free_batches[i];
+            const bool ok = c->ob.bytes >= need && c->jobs_cap >= n;
+            const Batch *b = h->free_batches[best];
+            if (ok ? (!fits || c->ob.bytes < b->ob.bytes) : (!fits && c->ob.bytes > b->ob.bytes)) best = i;
+            fits |= ok;
+        }
+        B = h->free_batches[best];
+        h->free_batches.erase(h->free_batches.begin() + (long)best);
     } else if (!(B = batch_new()))
         return fail(SVTME_ERR_NOMEM, "svtme_submit_pictures: batch allocation");
     int rc = launch_into(h, B, jobs, n, (int)(h->submit_count++ % (uint32_t)h->n_streams));

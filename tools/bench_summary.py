@@ -9,8 +9,9 @@ for f in sys.argv[1:]:
         print(f, "no JSON line:", e)
         continue
     r = d.get("roofline", {})
-    print("== %s: %.3f ms/step resident (%.2f M SB/s), e2e %.3f ms, launches %s, parity %s" % (
-        f, d["ms_per_step"], d["value"] / 1e6, d["e2e"].get("ms_per_step", 0), d.get("gpu_launches"), d.get("parity", {}).get("bit_exact")))
+    print("== %s: %.3f ms/step resident (%.2f M SB/s), e2e %.3f ms (streamed %.3f), launches %s, parity %s" % (
+        f, d["ms_per_step"], d["value"] / 1e6, d["e2e"].get("drained", {}).get("ms_per_step", 0), d["e2e"].get("ms_per_step", 0),
+        d.get("gpu_launches"), d.get("parity", {}).get("bit_exact")))
     if r:
         print("   dominant: %s frac %.3f | pipeline frac %.3f (%.3f ms)" % (r["kernel"][:60], r["frac"], r["pipeline"]["frac"], r["pipeline"]["ms"]))
         print("   phase_ms  ", r["phase_ms"])

@@ -25,6 +25,8 @@ st = torch.cuda.Stream()
 torch.cuda.set_stream(st)
 ses.set_stream(st.cuda_stream)
 specs = bench.build_specs(abi, gop, wl, ses.derive_params)
+if len(sys.argv) > 3:  # only the first N ME pictures (small-batch behaviour of the launch chain)
+    specs = specs[:int(sys.argv[3])]
 jobs, outs = ses.make_jobs(specs, deep=False)
 tot = None
 for i in range(steps + 2):

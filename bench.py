@@ -210,6 +210,11 @@ def main():
                          "(input_padded_pic->buffer_y, filled by svt_aom_un_pack2d in resource coordination, "
                          "resource_coordination_process.c:857,1022) — what the reference's ME reads; 'samples16' uploads the "
                          "16-bit samples and lets the pyramid kernel take the 8 MSBs")
+    ap.add_argument("--pin-results", type=int, default=1, help="end-to-end run: 1 = the callers' three big result tables per picture "
+                    "are page-locked (svtme_pin_host_memory) and filled by the download itself; 0 = pageable arrays, filled from "
+                    "the library's pinned mirror by svtme_collect_results")
+    ap.add_argument("--timeline", action="store_true", help="rank 0: after the timed runs, one more drained end-to-end step with host "
+                    "timestamps of every put / exchange / submit / collect and the device spans of every batch (stderr)")
     ap.add_argument("--cpu-pictures", type=int, default=0, help="pictures in the bounded CPU sample (0: 16 at 1080p, 8 at 4K, 4 at 8K)")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="repeat the CPU sample for about this long")
     args = ap.parse_args()
@@ -369,7 +374,7 @@ def main():
                 if f not in have:
                     have.add(f)
                     need.append(f)
-        cj, co = ses.make_jobs(part, deep=False)
+        cj, co = ses.make_jobs(part, deep=False, pin=args.pin_results)
         # the same chunk on the alternate slot set: picture numbers + ALT everywhere (distances are unchanged), same outputs
         alt = []
         for p0, cur, refs in part:
@@ -378,7 +383,7 @@ def main():
             for (li, ri), n_ in refs.items():
                 p1.ref_picture_number[li][ri] = n_ + ALT
             alt.append((p1, cur + ALT, {k: v + ALT for k, v in refs.items()}))
-        cj_alt, co_alt = ses.make_jobs(alt, deep=False)
+        cj_alt, co_alt = ses.make_jobs(alt, deep=False, pin=args.pin_results)
         chunks.append((need, [host_e2e.data_ptr() + f * e2e_frame_bytes for f in need], cj, co, cj_alt, co_alt))
     e2e_frames = len(share["owned"]) if share else len(have)
     chunks_sh = []
@@ -395,7 +400,7 @@ def main():
             groups = [g for g in shard.gather_groups(pics, world) if g not in have_g]
             have_g.update(groups)
             part = [all_specs[i] for i in idx if i % world == rank]
-            cj, co = ses.make_jobs(part, deep=False) if part else (None, [])
+            cj, co = ses.make_jobs(part, deep=False, pin=args.pin_results) if part else (None, [])
             own = [g * world + rank for g in groups if g * world + rank < F]
             chunks_sh.append((groups, own, [host_e2e.data_ptr() + f * e2e_frame_bytes for f in own], cj, co))
     sharing_info = None
@@ -531,6 +536,45 @@ def main():
     sampler.stop_flag = True
     if rank == 0:
         sampler.join(timeout=2)
+    if args.timeline:
+        # one more drained step, instrumented: host time (ms after the step started) at which each call returned, and the
+        # device spans of each batch (pipeline start / end, download end; svtme_debug_last_span) measured from the same mark
+        barrier()
+        lib, spans, tl = ses.lib, [], []
+        lib.svtme_debug_mark(ses.h)
+        t0 = time.perf_counter()
+        stamp = lambda what: tl.append((what, round((time.perf_counter() - t0) * 1e3, 3)))  # noqa: E731
+        seq_c = share and chunks_sh or chunks
+        for c, ch in enumerate(seq_c):
+            if share:
+                groups, own, ptrs, cj = ch[0], ch[1], ch[2], ch[3]
+                if own:
+                    ses.put_pictures(own, ptrs, W, device=False, bits=e2e_bits)
+                    stamp("put%d(%d pics)" % (c, len(own)))
+                if groups:
+                    exchange(groups, [p for g in groups for p in range(g * world, (g + 1) * world)])
+                    stamp("exchange%d(%d groups)" % (c, len(groups)))
+            else:
+                need, ptrs, cj = ch[0], ch[1], ch[2]
+                if need:
+                    ses.put_pictures(need, ptrs, W, device=False, bits=e2e_bits)
+                    stamp("put%d(%d pics)" % (c, len(need)))
+            if cj is not None:
+                ses.submit_jobs(cj)
+                stamp("submit%d(%d jobs)" % (c, len(cj)))
+        for c, ch in enumerate(seq_c):
+            cj = ch[3] if share else ch[2]
+            if cj is None:
+                continue
+            ses.collect_jobs(cj)
+            stamp("collect%d" % c)
+            v = (C.c_float * 3)()
+            lib.svtme_debug_last_span(ses.h, v)
+            spans.append([round(float(x), 3) for x in v])
+        if rank == 0:
+            sys.stderr.write("TIMELINE host(ms): %s\nTIMELINE device spans per batch [pipeline start, pipeline end, download end] (ms): %s\n"
+                             % (tl, spans))
+        barrier()
     ms_step = ms_total / args.steps
     sbs_step = (F - 1) * n_b64          # b64 of one whole stream
     n_streams = 1 if by_picture else world
@@ -592,8 +636,9 @@ def main():
                         "api": ("svtme_put_pictures_10bit (pinned host 16-bit luma)" if e2e_bits == 10 else
                                 ("svtme_put_pictures (pinned host 8-bit MSB plane of the 10-bit source, the buffer the reference's ME reads)"
                                  if bits == 10 else "svtme_put_pictures (pinned host luma)")) +
-                               " + svtme_submit_pictures / svtme_collect_results (results in host SvtMeOut arrays), batches of %s pictures"
-                               % (args.e2e_chunks_shared + " per rank" if share else args.e2e_chunks),
+                               " + svtme_submit_pictures / svtme_collect_results (results in host SvtMeOut arrays%s), batches of %s pictures"
+                               % (", the three big tables page-locked and filled by the download itself" if args.pin_results else "",
+                                  args.e2e_chunks_shared + " per rank" if share else args.e2e_chunks),
                         "drained": {"value": e2e_val, "unit": "SB/s", "ms_per_step": ms_e2e / args.steps,
                                     "note": "every step drained (all results collected) before the next one starts"}},
                 "gpu_launches": int(launches),

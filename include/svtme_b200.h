@@ -249,6 +249,12 @@ int svtme_fetch_results(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n);
 int svtme_submit_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n);
 int svtme_collect_results(SvtMeHandle *h, const SvtMeJob *jobs, uint32_t n);
 uint32_t svtme_pending_batches(SvtMeHandle *h);
+/* Page-lock caller memory in place (cudaHostRegister / cudaHostUnregister). When the three big SvtMeOut tables of a job
+ * (total_me_candidate_index, me_mv_array, me_candidate_array — the MeSbResults arrays of pcs.c:97-119) are page-locked,
+ * the queued form downloads them straight into the caller's arrays: no staging copy, no host-side scatter. Pageable arrays
+ * keep working (they are filled from a pinned mirror by svtme_collect_results). */
+int svtme_pin_host_memory(void *ptr, size_t bytes);
+int svtme_unpin_host_memory(void *ptr);
 /* Timeline aid for the queued form (measurement only): mark an origin on the main stream; after each
  * svtme_collect_results, ms3 = {pipeline start, pipeline end, download end} of that batch in ms after the mark. */
 int svtme_debug_mark(SvtMeHandle *h);

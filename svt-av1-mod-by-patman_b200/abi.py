@@ -185,6 +185,8 @@ def load_library():
         "svtme_submit_pictures": (C.c_int, [vp, P(SvtMeJob), u32]),
         "svtme_collect_results": (C.c_int, [vp, P(SvtMeJob), u32]),
         "svtme_pending_batches": (u32, [vp]),
+        "svtme_pin_host_memory": (C.c_int, [vp, C.c_size_t]),
+        "svtme_unpin_host_memory": (C.c_int, [vp]),
         "svtme_debug_mark": (C.c_int, [vp]),
         "svtme_debug_last_span": (C.c_int, [vp, P(C.c_float)]),
         "svtme_sync": (C.c_int, [vp]),

@@ -63,6 +63,7 @@ struct Batch {
     uint32_t jobs_cap = 0;
     OutBuffers ob;
     std::vector<size_t> work_off; // offsets of the per-job work counters
+    std::vector<uint8_t> direct;  // queued form: job i's three big arrays were downloaded straight into the caller's page-locked arrays
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, jobs_ev = nullptr, done_ev = nullptr; // done_ev: download complete
     cudaEvent_t ph_ev[SVTME_PHASES] = {};
     bool jobs_pending = false; // h_jobs may still be on its way to the device
@@ -778,9 +779,11 @@ static int scatter_results(SvtMeHandle *h, const Batch *B, const SvtMeJob *jobs,
         const OutLayout L = out_layout(nb, n_pu, j.params, deep);
         const uint8_t *b = B->ob.host + offs[i];
 #define CP(dst, o, bytes) if (j.out.dst) memcpy(j.out.dst, b + (o), (bytes))
-        CP(total_me_candidate_index, L.total, (size_t)nb * n_pu);
-        CP(me_mv_array, L.mv, (size_t)nb * n_pu * j.params.max_refs * 4);
-        CP(me_candidate_array, L.cand, (size_t)nb * n_pu * j.params.max_cand);
+        if (!(i < (int)B->direct.size() && B->direct[i])) { // (else: already in place, see svtme_submit_pictures)
+            CP(total_me_candidate_index, L.total, (size_t)nb * n_pu);
+            CP(me_mv_array, L.mv, (size_t)nb * n_pu * j.params.max_refs * 4);
+            CP(me_candidate_array, L.cand, (size_t)nb * n_pu * j.params.max_cand);
+        }
         CP(me_64x64_distortion, L.d64, (size_t)nb * 4); CP(me_32x32_distortion, L.d32, (size_t)nb * 4);
         CP(me_16x16_distortion, L.d16, (size_t)nb * 4); CP(me_8x8_distortion, L.d8, (size_t)nb * 4);
         CP(me_8x8_cost_variance, L.var8, (size_t)nb * 4); CP(rc_me_distortion, L.rc, (size_t)nb * 4);
@@ -858,7 +861,39 @@ extern "C" int svtme_submit_pictures(SvtMeHandle *h, const SvtMeJob *jobs, uint3
         return rc;
     }
     CU(cudaStreamWaitEvent(h->d2h_stream, B->ev1, 0));
-    CU(cudaMemcpyAsync(B->ob.host, B->ob.dev, B->total, cudaMemcpyDeviceToHost, h->d2h_stream));
+    // Download. The three big tables of a job (candidate counts, motion vectors, candidates: 99 % of the bytes) go straight
+    // into the caller's arrays when those are page-locked (cudaMallocHost / svtme_pin_host_memory): no staging copy, no
+    // host-side scatter — at 4K preset 4 the scatter of 1.08 GB per 120-frame step was as long as the ME itself. Everything
+    // else (and every job whose arrays are pageable) travels through the batch's pinned mirror as before.
+    B->direct.assign(n, 0);
+    {
+        size_t off = 0, run0 = 0; // [run0, off): bytes not yet copied to the mirror
+        for (uint32_t i = 0; i < n; ++i) {
+            const SvtMeJob &j = jobs[i];
+            const uint32_t n_pu = svtme_exported_pu_count(&j.params), nb = h->n_b64;
+            const OutLayout L = out_layout(nb, n_pu, j.params, wants_deep(j.out));
+            bool pinned = j.out.total_me_candidate_index && j.out.me_mv_array && j.out.me_candidate_array;
+            const void *big[3] = {j.out.total_me_candidate_index, j.out.me_mv_array, j.out.me_candidate_array};
+            for (int k = 0; k < 3 && pinned; ++k) {
+                cudaPointerAttributes at;
+                if (cudaPointerGetAttributes(&at, big[k]) != cudaSuccess || at.type != cudaMemoryTypeHost) pinned = false;
+            }
+            (void)cudaGetLastError(); // (an unregistered host pointer makes older runtimes report an error: not one of ours)
+            if (pinned) {
+                if (off + L.total > run0)
+                    CU(cudaMemcpyAsync(B->ob.host + run0, B->ob.dev + run0, off + L.total - run0, cudaMemcpyDeviceToHost, h->d2h_stream));
+                const uint8_t *d = B->ob.dev + off;
+                CU(cudaMemcpyAsync(j.out.total_me_candidate_index, d + L.total, (size_t)nb * n_pu, cudaMemcpyDeviceToHost, h->d2h_stream));
+                CU(cudaMemcpyAsync(j.out.me_mv_array, d + L.mv, (size_t)nb * n_pu * j.params.max_refs * 4, cudaMemcpyDeviceToHost, h->d2h_stream));
+                CU(cudaMemcpyAsync(j.out.me_candidate_array, d + L.cand, (size_t)nb * n_pu * j.params.max_cand, cudaMemcpyDeviceToHost,
+                                   h->d2h_stream));
+                B->direct[i] = 1;
+                run0 = off + L.d64; // the mirror run resumes behind the three tables
+            }
+            off += L.end;
+        }
+        if (off > run0) CU(cudaMemcpyAsync(B->ob.host + run0, B->ob.dev + run0, off - run0, cudaMemcpyDeviceToHost, h->d2h_stream));
+    }
     CU(cudaEventRecord(B->done_ev, h->d2h_stream));
     h->queue.push_back(B);
     return SVTME_OK;
@@ -904,6 +939,18 @@ extern "C" int svtme_debug_last_span(SvtMeHandle *h, float *ms3) {
     if (!h || !ms3) return fail(SVTME_ERR_INVALID, "svtme_debug_last_span: bad argument");
     std::lock_guard<std::mutex> lk(h->mu);
     for (int k = 0; k < 3; ++k) ms3[k] = h->span[k];
+    return SVTME_OK;
+}
+
+// Page-lock caller memory in place (cudaHostRegister) so that results can be downloaded straight into it.
+extern "C" int svtme_pin_host_memory(void *ptr, size_t bytes) {
+    if (!ptr || !bytes) return fail(SVTME_ERR_INVALID, "svtme_pin_host_memory: bad argument");
+    CU(cudaHostRegister(ptr, bytes, cudaHostRegisterPortable));
+    return SVTME_OK;
+}
+extern "C" int svtme_unpin_host_memory(void *ptr) {
+    if (!ptr) return fail(SVTME_ERR_INVALID, "svtme_unpin_host_memory: bad argument");
+    CU(cudaHostUnregister(ptr));
     return SVTME_OK;
 }
 

@@ -37,9 +37,12 @@ class MeSession:
         self.width, self.height = width, height
         _check(self.lib.svtme_open(device, width, height, capacity, C.byref(self.h)), self.lib)
         self.n_b64 = int(self.lib.svtme_b64_count(self.h))
+        self._pinned = []
 
     def close(self):
         if self.h:
+            self.lib.svtme_sync(self.h)
+            self.unpin_all()
             self.lib.svtme_close(self.h)
             self.h = C.c_void_p()
 
@@ -105,8 +108,11 @@ class MeSession:
         """Peer copy of a pyramid into a handle on another device of the same process."""
         _check(self.lib.svtme_share_picture(self.h, other.h, pic_num), self.lib)
 
-    def make_jobs(self, specs, deep=False):
-        """specs: list of (params, cur, {(list, idx): pic_num}). Returns (SvtMeJob array, [arrays])."""
+    BIG_TABLES = ("total_me_candidate_index", "me_mv_array", "me_candidate_array")
+
+    def make_jobs(self, specs, deep=False, pin=False):
+        """specs: list of (params, cur, {(list, idx): pic_num}). Returns (SvtMeJob array, [arrays]). pin: page-lock the three
+        big result tables of every job (svtme_pin_host_memory) so that the queued form downloads straight into them."""
         jobs = (abi.SvtMeJob * len(specs))()
         outs = []
         for i, (p, cur, refs) in enumerate(specs):
@@ -115,9 +121,18 @@ class MeSession:
             for (li, ri), n in refs.items():
                 jobs[i].refs[li][ri] = n
             out, arrays = abi.alloc_out(self.n_b64, p, deep=deep)
+            if pin:
+                for name in self.BIG_TABLES:
+                    _check(self.lib.svtme_pin_host_memory(arrays[name].ctypes.data, arrays[name].nbytes), self.lib)
+                    self._pinned.append(arrays[name])
             jobs[i].out = out
             outs.append(arrays)
         return jobs, outs
+
+    def unpin_all(self):
+        for a in self._pinned:
+            self.lib.svtme_unpin_host_memory(a.ctypes.data)
+        self._pinned = []
 
     def run_jobs(self, jobs):
         _check(self.lib.svtme_run_pictures(self.h, jobs, len(jobs)), self.lib)

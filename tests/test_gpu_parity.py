@@ -423,3 +423,38 @@ def test_share_picture_between_handles_and_external_writes():
                 assert np.array_equal(want[k], oa[0][k]), (rnd, "builder", k)
                 assert np.array_equal(want[k], ob[0][k]), (rnd, "peer copy", k)
                 assert np.array_equal(want[k], oc[0][k]), (rnd, "external write", k)
+
+
+def test_queued_results_land_directly_in_page_locked_caller_arrays():
+    """svtme_pin_host_memory: jobs whose three big tables are page-locked get them by direct download, jobs with pageable
+    arrays through the pinned mirror; mixed in one batch, both equal the synchronous run."""
+    W, H = 320, 192
+    seq = U.synth_sequence(W, H, 6, seed=11)
+    d = U.derive_input(4, W, H, temporal_layer_index=1, ref_list0_count_try=1, ref_list1_count_try=1)
+    specs = []
+    for cur in (1, 2, 3, 4):
+        p = U.finish_params(derive(None, d), d, cur, {(0, 0): cur - 1, (1, 0): cur + 1})
+        specs.append((p, cur, {(0, 0): cur - 1, (1, 0): cur + 1}))
+    with me.MeSession(0, W, H, capacity=6) as ses:
+        for n in range(6):
+            ses.put_picture(n, seq[n])
+        jw, want = ses.make_jobs(specs, deep=True)
+        ses.run_jobs(jw)
+        ja, oa = ses.make_jobs(specs[:2], deep=False, pin=True)
+        jb, ob = ses.make_jobs(specs[2:], deep=True, pin=False)
+        jc, oc = ses.make_jobs(specs, deep=True, pin=True)
+        mixed = (U.abi.SvtMeJob * 4)(ja[0], jb[0], ja[1], jb[1])  # pinned / pageable alternating in one batch
+        for rnd in range(2):
+            for o in oa + ob + oc:
+                for a in o.values():
+                    a[...] = 0xAB if a.dtype == np.uint8 else 0
+            ses.submit_jobs(mixed)
+            ses.submit_jobs(jc)
+            ses.collect_jobs(mixed)
+            ses.collect_jobs(jc)
+            for got, w in ((oa[0], want[0]), (ob[0], want[2]), (oa[1], want[1]), (ob[1], want[3])):
+                for k in got:
+                    assert np.array_equal(got[k], w[k]), (rnd, "mixed", k)
+            for got, w in zip(oc, want):
+                for k in got:
+                    assert np.array_equal(got[k], w[k]), (rnd, "all pinned", k)

@@ -203,7 +203,7 @@ def main():
                          "into the ring slots of the GPUs that reference it")
     ap.add_argument("--e2e-chunks", default="32", help="pictures per chunk (batch) of the pipelined end-to-end run "
                     "(decode order; the last value repeats): one mini-GOP of the look-ahead window per batch")
-    ap.add_argument("--e2e-chunks-shared", default="1,2,4", help="--pyramids nccl: pictures PER RANK in each global chunk of the "
+    ap.add_argument("--e2e-chunks-shared", default="4,8,16", help="--pyramids nccl: pictures PER RANK in each global chunk of the "
                     "pipelined end-to-end run (the last value repeats)")
     ap.add_argument("--e2e-source", default="msb8", choices=["msb8", "samples16"],
                     help="10-bit workloads, end-to-end run: 'msb8' uploads the 8-bit MSB plane the encoder already holds on the host "
@@ -308,7 +308,7 @@ def main():
     # real stream whose new pictures get new pa-reference objects: the next step's uploads do not wait for the launches
     # that still read the previous step's pictures
     ALT = 1 << 20
-    ses = me.MeSession(local_rank, W, H, capacity=n_slots if (by_picture and args.pyramids == "nccl") else 2 * F)
+    ses = me.MeSession(local_rank, W, H, capacity=2 * n_slots if (by_picture and args.pyramids == "nccl") else 2 * F)
     stream = torch.cuda.Stream()  # a non-default stream: the library treats NULL as "use the private stream"
     torch.cuda.set_stream(stream)
     ses.set_stream(stream.cuda_stream)
@@ -330,11 +330,12 @@ def main():
     if share:
         # picture p -> ring slot p on every rank (slots are handed out in order on a fresh handle), built by rank p % N
         xs = torch.cuda.Stream()  # the exchange stream: NCCL work is ordered against it, never against the host
-        ses.external_write_begin(list(range(n_slots)), xs.cuda_stream)
+        # (two sets: pictures p and ALT + p, the second one in slots n_slots + p, for consecutive steps of the streamed run)
+        ses.external_write_begin(list(range(n_slots)) + [ALT + p for p in range(n_slots)], xs.cuda_stream)
         pool_ptr = ses.plane_device_ptr(0, 0)[0]
         slot_bytes = sum(ses.plane_device_ptr(0, l)[1] for l in range(3))
-        for pnum in (1, n_slots - 1):
-            if ses.plane_device_ptr(pnum, 0)[0] != pool_ptr + pnum * slot_bytes:
+        for pnum, slot in ((1, 1), (n_slots - 1, n_slots - 1), (ALT, n_slots), (ALT + n_slots - 1, 2 * n_slots - 1)):
+            if ses.plane_device_ptr(pnum, 0)[0] != pool_ptr + slot * slot_bytes:
                 raise RuntimeError("ring slots are expected in picture order")
         share.update(xs=xs, pool=pool_ptr, slot_bytes=slot_bytes, cache={}, moved=0)
 
@@ -401,8 +402,16 @@ def main():
             have_g.update(groups)
             part = [all_specs[i] for i in idx if i % world == rank]
             cj, co = ses.make_jobs(part, deep=False, pin=args.pin_results) if part else (None, [])
+            alt = []
+            for p0, cur, refs in part:
+                p1 = abi.SvtMeParams.from_buffer_copy(bytes(p0))
+                p1.picture_number = cur + ALT
+                for (li, ri), n_ in refs.items():
+                    p1.ref_picture_number[li][ri] = n_ + ALT
+                alt.append((p1, cur + ALT, {k: v + ALT for k, v in refs.items()}))
+            cj_alt, co_alt = ses.make_jobs(alt, deep=False, pin=args.pin_results) if alt else (None, [])
             own = [g * world + rank for g in groups if g * world + rank < F]
-            chunks_sh.append((groups, own, [host_e2e.data_ptr() + f * e2e_frame_bytes for f in own], cj, co))
+            chunks_sh.append((groups, own, [host_e2e.data_ptr() + f * e2e_frame_bytes for f in own], cj, co, cj_alt, co_alt))
     sharing_info = None
     if share:
         # one-time check outside the timed region: a pyramid received over NCCL equals the one built locally
@@ -458,22 +467,24 @@ def main():
         if collect_err:
             raise collect_err[0]
 
-    def step_e2e_shared(drain=True):
-        for groups, own, ptrs, cj, _ in chunks_sh:
+    def step_e2e_shared(drain=True, alt=False):
+        n_groups = n_slots // world
+        for groups, own, ptrs, cj, _, cj_alt, _ in chunks_sh:
+            base = ALT if alt else 0
             if own:
-                ses.put_pictures(own, ptrs, W, device=False, bits=e2e_bits)
+                ses.put_pictures([base + f for f in own], ptrs, W, device=False, bits=e2e_bits)
             if groups:
-                exchange(groups, [p for g in groups for p in range(g * world, (g + 1) * world)])
+                exchange([g + (n_groups if alt else 0) for g in groups], [base + p for g in groups for p in range(g * world, (g + 1) * world)])
             if cj is not None:
                 in_flight.acquire()
-                ses.submit_jobs(cj)
-                collect_q.put(cj)
+                ses.submit_jobs(cj_alt if alt else cj)
+                collect_q.put(cj_alt if alt else cj)
         if drain:
             finish_step()
 
     def step_e2e(drain=True, alt=False):
         if share:
-            return step_e2e_shared(drain)
+            return step_e2e_shared(drain, alt)
         for c, (need, ptrs, cj, _, cj_alt, _) in enumerate(chunks):
             if alt:
                 need, cj = [f + ALT for f in need], cj_alt
@@ -611,8 +622,8 @@ def main():
         ses.fetch_jobs(jobs)
         e2e_outs = [o for c in chunks_sh for o in c[4]] if share else [o for c in chunks for o in c[3]]
         checks = [("e2e", e2e_outs), ("resident", outs)]
-        if not share and args.steps > 1:
-            checks.append(("e2e streamed (alternate slot set)", [o for c in chunks for o in c[5]]))
+        if args.steps > 1:
+            checks.append(("e2e streamed (alternate slot set)", [o for c in (chunks_sh if share else chunks) for o in c[6 if share else 5]]))
         n_arrays, bad = compare_outputs(cpu["outs"], checks)
         parity = {"pictures": len(cpu["outs"]), "arrays": n_arrays, "bit_exact": not bad, "against": "oracle/_ref (compiled "
                   "reference, %s kernels)" % cpu["simd"] if cpu["kind"] == "reference" else "oracle port",

@@ -110,6 +110,8 @@ struct SvtMeHandle {
     std::vector<Batch *> free_batches;
     std::deque<Batch *> queue;     // submitted, not yet collected (FIFO)
     uint64_t seq = 0;
+    size_t max_ob_bytes = 0;   // largest result record / job count any batch has needed so far: batch buffers are (re)sized
+    uint32_t max_jobs = 0;     // to these, so that a steady stream of batches of mixed sizes stops reallocating early
     void *d_states = nullptr; // per-b64 scratch of the stage pipeline
     PutRing put[SVTME_PUT_RING];
     uint32_t put_seq = 0;
@@ -631,14 +633,15 @@ static int launch_into(SvtMeHandle *h, Batch *B, const SvtMeJob *jobs, uint32_t 
     size_t &states_bytes = si ? h->x_states_bytes[si] : h->states_bytes;
     if (B->jobs_pending) CU(cudaEventSynchronize(B->jobs_ev)); // the previous job array has left the pinned buffer
     B->jobs_pending = false;
+    if (n > h->max_jobs) h->max_jobs = n;
     if (n > B->jobs_cap) {
         cudaFree(B->d_jobs);
         cudaFreeHost(B->h_jobs);
         B->d_jobs = B->h_jobs = nullptr;
         B->jobs_cap = 0;
-        CU(cudaMalloc(&B->d_jobs, up16(sizeof(DevJob) * n)));
-        CU(cudaMallocHost(&B->h_jobs, up16(sizeof(DevJob) * n)));
-        B->jobs_cap = n;
+        CU(cudaMalloc(&B->d_jobs, up16(sizeof(DevJob) * h->max_jobs)));
+        CU(cudaMallocHost(&B->h_jobs, up16(sizeof(DevJob) * h->max_jobs)));
+        B->jobs_cap = h->max_jobs;
     }
     size_t total = 0;
     for (uint32_t i = 0; i < n; ++i) {
@@ -655,9 +658,10 @@ static int launch_into(SvtMeHandle *h, Batch *B, const SvtMeJob *jobs, uint32_t 
         cudaFree(B->ob.dev);
         cudaFreeHost(B->ob.host);
         B->ob = OutBuffers();
-        CU(cudaMalloc(&B->ob.dev, total));
-        CU(cudaMallocHost(&B->ob.host, total));
-        B->ob.bytes = total;
+        if (total > h->max_ob_bytes) h->max_ob_bytes = total;
+        CU(cudaMalloc(&B->ob.dev, h->max_ob_bytes));
+        CU(cudaMallocHost(&B->ob.host, h->max_ob_bytes));
+        B->ob.bytes = h->max_ob_bytes;
     }
     // every picture of the batch must be resident: checked before the sequence number and the slots' reader marks move
     // (a NOTFOUND half-way used to leave last_reader pointing at a launch event that is never recorded)

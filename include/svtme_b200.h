@@ -89,7 +89,14 @@ typedef struct SvtMeParams {
     uint16_t mv_sa_adj_mv_size_th, mv_sa_adj_sa_multiplier;
     /* misc MeContext scalars */
     int32_t prune_me_candidates_th;
-    uint8_t use_best_unipred_cand_only, _pad3[3];
+    uint8_t use_best_unipred_cand_only;
+    /* me_ctx->me_type (me_context.h:44-51,459): 0 = the open-loop ME of the PAME tasks (ME_OPEN_LOOP), 1 = ME_MCTF, the
+     * temporal-filter ME of TASK_TFME (temporal_filtering.c:3075): no reference pruning, unscaled picture distance in the
+     * full-pel area (motion_estimation.c:1302), early return after HME when search_results[0][0].hme_sad < tf_me_exit_th
+     * (:3179-3183), no candidate arrays / distortions: its consumers read p_sb_best_sad / p_sb_best_mv and the HME
+     * results (the "deep" SvtMeOut arrays). */
+    uint8_t me_type;
+    uint16_t tf_me_exit_th;               /* me_ctx->tf_me_exit_th = pcs->tf_ctrls.me_exit_th (temporal_filtering.c:3064) */
     uint32_t me_early_exit_th, me_safe_limit_zz_th, prev_me_stage_based_exit_th;
     /* per-picture, me_process.c:219-227 */
     uint8_t num_of_list_to_search;
@@ -133,6 +140,21 @@ typedef struct SvtMeDeriveInput {
     uint8_t ref_count_used_list0, ref_count_used_list1; /* MeSbResults allocation pcs.c:90-95 */
     uint8_t gm_level_enabled, gm_use_distance_based_active_th;
 } SvtMeDeriveInput;
+
+/* Encoder-level inputs of the temporal-filter ME parameters (svt_aom_sig_deriv_me_tf, enc_mode_config.c:829-875;
+ * tf_set_me_hme_params_oq :601-681; TF HME flags :1810-1834; set_hme_search_params_mctf level 0 and the FULL_SAD HME
+ * of create_me_context_and_picture_control, temporal_filtering.c:2730-2749,315). */
+typedef struct SvtMeTfDeriveInput {
+    int32_t enc_mode;
+    uint32_t width, height;      /* luma size -> EbInputResolution */
+    uint32_t qp;                 /* scs->static_config.qp (used when qp_opt) */
+    uint8_t hme_me_level;        /* pcs->tf_ctrls.hme_me_level, 0..4 */
+    uint8_t qp_opt;              /* pcs->tf_ctrls.qp_opt */
+    uint16_t me_exit_th;         /* pcs->tf_ctrls.me_exit_th */
+    uint8_t temporal_layer_index, is_ref; /* of the centre picture (temporal_filtering.c:3049-3052) */
+    uint8_t _pad[2];
+} SvtMeTfDeriveInput;
+int svtme_derive_params_tf(const SvtMeTfDeriveInput *in, SvtMeParams *out);
 
 /* Host-side mirror of svt_aom_sig_deriv_me (enc_mode_config.c:684-823), set_hme_search_params
  * (:141-213), set_me_search_params (:218-353), the HME level flags (:1798-1809) and
@@ -286,6 +308,7 @@ uint32_t svtme_sizeof_params(void);
 uint32_t svtme_sizeof_out(void);
 uint32_t svtme_sizeof_job(void);
 uint32_t svtme_sizeof_derive_input(void);
+uint32_t svtme_sizeof_tf_derive_input(void);
 
 /* ---------------- kernel-test ABI: RTCD signatures (aom_dsp_rtcd.h) ---------------- */
 

@@ -543,7 +543,9 @@ static void integer_search_b64(B64State *s) {
                 continue;
             int16_t  xc = s->sr[li][ri].hme_sc_x, yc = s->sr[li][ri].hme_sc_y;
             int16_t  sa_w = (int16_t)p->me_sa.sa_min.width, sa_h = (int16_t)p->me_sa.sa_min.height;
-            uint16_t dist = scaled_dist(ref_dist(s, li, ri));
+            uint16_t dist = ref_dist(s, li, ri);
+            if (p->me_type != 1) /* :1302: the temporal-filter ME (ME_MCTF) uses the picture distance as it is */
+                dist = scaled_dist(dist);
             sa_w          = (int16_t)IMIN((sa_w * dist), p->me_sa.sa_max.width);
             sa_h          = (int16_t)IMIN((sa_h * dist), p->me_sa.sa_max.height);
             if (p->mv_sa_adj_enabled && (!p->mv_sa_adj_nearest_ref_only || ri == 0)) {
@@ -887,7 +889,8 @@ static void gm_detection(const B64State *s, const B64Out *o, uint32_t b64, SvtMe
 /* svt_aom_motion_estimation_b64 :3146-3223 for one block */
 static void me_b64(B64State *s, uint32_t b64, SvtMeOut *out, B64Out *o) {
     const SvtMeParams *p = s->p;
-    const uint8_t prune_ref = p->enable_hme_flag; /* me_type != ME_MCTF */
+    const int mctf = p->me_type == 1; /* ME_MCTF: the temporal-filter ME (temporal_filtering.c:3075) */
+    const uint8_t prune_ref = p->enable_hme_flag && !mctf; /* :3173 */
     init_state(s);
     /* hme_b64 :2511-2545 */
     if (p->me_early_exit_th || p->me_safe_limit_zz_th)
@@ -900,11 +903,15 @@ static void me_b64(B64State *s, uint32_t b64, SvtMeOut *out, B64Out *o) {
         if (p->enable_hme_level2_flag) hme_level2_b64(s);
     }
     set_final_search_centre(s);
+    if (mctf && s->sr[0][0].hme_sad < p->tf_me_exit_th) /* :3179-3183: the caller sees tf_use_pred_64x64_only_th = ~0 */
+        return;
     if (prune_ref)
         hme_prune_ref_and_adjust_sr(s);
     integer_search_b64(s);
     if (prune_ref && p->enable_me_hme_ref_pruning)
         me_prune_ref(s);
+    if (mctf) /* :3196: no candidate arrays, distortions or GM detection for the temporal filter */
+        return;
     if (p->num_of_ref_pic_to_search[0] == 1 && p->num_of_ref_pic_to_search[1] == 0)
         construct_single_ref(s, o);
     else if (p->num_of_ref_pic_to_search[0] == 1 && p->num_of_ref_pic_to_search[1] == 1)

@@ -46,7 +46,8 @@ static inline void params_to_ctx(const SvtMeParams *p, MeContext *c) {
     c->num_of_ref_pic_to_search[0] = p->num_of_ref_pic_to_search[0];
     c->num_of_ref_pic_to_search[1] = p->num_of_ref_pic_to_search[1];
     c->temporal_layer_index = p->temporal_layer_index; c->is_ref = p->is_ref;
-    c->me_type = ME_OPEN_LOOP;
+    c->me_type = p->me_type == 1 ? ME_MCTF : ME_OPEN_LOOP;
+    c->tf_me_exit_th = p->tf_me_exit_th;
 #undef SA
 }
 
@@ -94,6 +95,8 @@ static inline void ctx_to_params(const MeContext *c, SvtMeParams *p) {
     p->use_best_unipred_cand_only = c->use_best_unipred_cand_only;
     p->me_early_exit_th = c->me_early_exit_th; p->me_safe_limit_zz_th = c->me_safe_limit_zz_th;
     p->prev_me_stage_based_exit_th = c->prev_me_stage_based_exit_th;
+    p->me_type = c->me_type == ME_MCTF ? 1 : 0;
+    p->tf_me_exit_th = c->me_type == ME_MCTF ? c->tf_me_exit_th : 0;
 #undef SA
 }
 

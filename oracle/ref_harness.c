@@ -206,6 +206,47 @@ int ref_derive_params(const SvtMeDeriveInput *in, SvtMeParams *out) {
     return 0;
 }
 
+/* Temporal-filter ME parameters from the reference's own svt_aom_sig_deriv_me_tf (enc_mode_config.c:829), followed by what
+ * produce_temporally_filtered_pic does per block before it calls svt_aom_motion_estimation_b64 (temporal_filtering.c:296,
+ * 315,3046-3074): me_type, FULL_SAD HME, one list / one reference, set_hme_search_params_mctf(ctx, 0). */
+void svt_aom_sig_deriv_me_tf(PictureParentControlSet *pcs, MeContext *me_ctx);
+int ref_derive_params_tf(const SvtMeTfDeriveInput *in, SvtMeParams *out) {
+    SequenceControlSet      *scs = (SequenceControlSet *)calloc(1, sizeof(*scs));
+    PictureParentControlSet *pcs = (PictureParentControlSet *)calloc(1, sizeof(*pcs));
+    MeContext               *ctx = (MeContext *)calloc(1, sizeof(*ctx));
+    if (!scs || !pcs || !ctx) return -1;
+    memset(out, 0, sizeof(*out));
+    EbInputResolution res;
+    svt_aom_derive_input_resolution(&res, in->width * in->height);
+    scs->input_resolution = res;
+    scs->static_config.qp = in->qp;
+    pcs->scs = scs;
+    pcs->enc_mode = (EncMode)in->enc_mode;
+    pcs->tf_ctrls.hme_me_level = in->hme_me_level;
+    pcs->tf_ctrls.qp_opt = in->qp_opt;
+    pcs->tf_ctrls.me_exit_th = in->me_exit_th;
+    /* enc_mode_config.c:1810-1834 */
+    pcs->tf_enable_hme_flag = pcs->tf_enable_hme_level0_flag = 1;
+    pcs->tf_enable_hme_level1_flag = in->hme_me_level <= 2;
+    pcs->tf_enable_hme_level2_flag = in->hme_me_level == 0;
+    svt_aom_sig_deriv_me_tf(pcs, ctx);
+    ctx->me_type = ME_MCTF;
+    ctx->hme_search_method = FULL_SAD_SEARCH;
+    ctx->hme_l0_sa = ctx->hme_l0_sa_default_tf; /* set_hme_search_params_mctf(ctx, 0) */
+    ctx->tf_me_exit_th = pcs->tf_ctrls.me_exit_th;
+    ctx_to_params(ctx, out);
+    out->num_of_list_to_search = 1;
+    out->num_of_ref_pic_to_search[0] = 1;
+    out->temporal_layer_index = in->temporal_layer_index;
+    out->is_ref = in->is_ref;
+    out->max_number_of_pus_per_sb = 85;
+    out->enable_me_8x8 = out->enable_me_16x16 = 1;
+    out->max_refs = out->max_cand = out->max_l0 = 1;
+    out->input_resolution_le_480p = res <= INPUT_SIZE_480p_RANGE;
+    free(scs); free(pcs); free(ctx);
+    return 0;
+}
+
 /* ---- whole pictures through svt_aom_motion_estimation_b64 ----
  * PicShell: the picture-level objects one ME picture needs (scs / pcs / MeSbResults shells pointing straight
  * into the caller's SvtMeOut arrays; outputs the caller does not want go to scratch). Shared read-only by the
@@ -333,7 +374,7 @@ static void run_rows(ThreadCtx *t, const PicShell *s, uint32_t row0, uint32_t ro
             ctx->quarter_b64_buffer_stride = q->stride_y;
             ctx->sixteenth_b64_buffer = x->buffer_y + (size_t)(x->org_y + (oy >> 2)) * x->stride_y + x->org_x + (ox >> 2);
             ctx->sixteenth_b64_buffer_stride = x->stride_y;
-            ctx->me_type = ME_OPEN_LOOP;
+            ctx->me_type = s->p->me_type == 1 ? ME_MCTF : ME_OPEN_LOOP;
             /* not part of the reference: clear the tables of refs the block will not search so the
              * deep-state dump is comparable (they are never read before being initialised). */
             if (out->p_sb_best_sad) memset(ctx->p_sb_best_sad, 0, sizeof(ctx->p_sb_best_sad));

@@ -45,7 +45,7 @@ class SvtMeParams(C.Structure):
         ("mv_sa_adj_enabled", u8), ("mv_sa_adj_nearest_ref_only", u8),
         ("mv_sa_adj_mv_size_th", u16), ("mv_sa_adj_sa_multiplier", u16),
         ("prune_me_candidates_th", i32),
-        ("use_best_unipred_cand_only", u8), ("_pad3", u8 * 3),
+        ("use_best_unipred_cand_only", u8), ("me_type", u8), ("tf_me_exit_th", C.c_uint16),
         ("me_early_exit_th", u32), ("me_safe_limit_zz_th", u32), ("prev_me_stage_based_exit_th", u32),
         ("num_of_list_to_search", u8), ("num_of_ref_pic_to_search", u8 * 2),
         ("temporal_layer_index", u8), ("is_ref", u8),
@@ -80,6 +80,11 @@ class SvtMeDeriveInput(C.Structure):
         ("ref_count_used_list0", u8), ("ref_count_used_list1", u8),
         ("gm_level_enabled", u8), ("gm_use_distance_based_active_th", u8),
     ]
+
+
+class SvtMeTfDeriveInput(C.Structure):  # include/svtme_b200.h
+    _fields_ = [("enc_mode", C.c_int32), ("width", u32), ("height", u32), ("qp", u32), ("hme_me_level", u8), ("qp_opt", u8),
+                ("me_exit_th", C.c_uint16), ("temporal_layer_index", u8), ("is_ref", u8), ("_pad", u8 * 2)]
 
 
 class SvtMeOut(C.Structure):
@@ -160,6 +165,7 @@ def load_library():
     P = C.POINTER
     sigs = {
         "svtme_derive_params": (C.c_int, [P(SvtMeDeriveInput), P(SvtMeParams)]),
+        "svtme_derive_params_tf": (C.c_int, [P(SvtMeTfDeriveInput), P(SvtMeParams)]),
         "svtme_open": (C.c_int, [C.c_int, u32, u32, u32, P(vp)]),
         "svtme_close": (None, [vp]),
         "svtme_last_error": (cp, []),
@@ -204,6 +210,7 @@ def load_library():
         "svtme_sizeof_out": (u32, []),
         "svtme_sizeof_job": (u32, []),
         "svtme_sizeof_derive_input": (u32, []),
+        "svtme_sizeof_tf_derive_input": (u32, []),
     }
     for name, (res, args) in sigs.items():
         fn = getattr(lib, name)
@@ -215,7 +222,7 @@ def load_library():
 
 def check_layout(lib):
     pairs = [("svtme_sizeof_params", SvtMeParams), ("svtme_sizeof_out", SvtMeOut), ("svtme_sizeof_job", SvtMeJob),
-             ("svtme_sizeof_derive_input", SvtMeDeriveInput)]
+             ("svtme_sizeof_derive_input", SvtMeDeriveInput), ("svtme_sizeof_tf_derive_input", SvtMeTfDeriveInput)]
     for fn, st in pairs:
         got, want = getattr(lib, fn)(), C.sizeof(st)
         if got != want:

@@ -250,3 +250,55 @@ extern "C" uint32_t svtme_exported_pu_count(const SvtMeParams *p) {
     if (!p->enable_me_16x16) return 5;
     return p->enable_me_8x8 ? p->max_number_of_pus_per_sb : 21;
 }
+
+
+// ---- temporal-filter ME (ME_MCTF): svt_aom_sig_deriv_me_tf (enc_mode_config.c:829-875), tf_set_me_hme_params_oq
+// (:601-681), TF HME flags (:1810-1834), set_hme_search_params_mctf(ctx, 0) and the FULL_SAD HME search method of
+// create_me_context_and_picture_control (temporal_filtering.c:2730-2749,315), per-block fields (:3046-3065).
+extern "C" int svtme_derive_params_tf(const SvtMeTfDeriveInput *in, SvtMeParams *o) {
+    if (!in || !o || in->hme_me_level > 4 || in->enc_mode < -1 || in->enc_mode > 13) return SVTME_ERR_INVALID;
+    memset(o, 0, sizeof(*o));
+    const int res = input_resolution(in->width * in->height);
+    SvtMeSearchArea l0mn, l0mx, l1, l2, mn, mx;
+    switch (in->hme_me_level) {
+    case 0: l0mn = SA(30, 30); l0mx = SA(60, 60); l1 = SA(16, 16); l2 = SA(16, 16); mn = SA(60, 60); mx = SA(120, 120); break;
+    case 1: l0mn = SA(16, 16); l0mx = SA(32, 32); l1 = SA(16, 16); l2 = SA(16, 16); mn = SA(16, 16); mx = SA(32, 32); break;
+    case 2:
+        if (res <= R360) { l0mn = SA(8, 8); l0mx = SA(8, 8); l1 = SA(8, 8); }
+        else if (res <= R480) { l0mn = SA(8, 8); l0mx = SA(16, 16); l1 = SA(8, 8); }
+        else { l0mn = SA(16, 16); l0mx = SA(32, 32); l1 = SA(16, 16); }
+        l2 = SA(16, 16); mn = SA(8, 8); mx = SA(8, 8);
+        break;
+    case 3: l0mn = SA(8, 8); l0mx = SA(8, 8); l1 = SA(8, 8); l2 = SA(8, 8); mn = SA(8, 8); mx = SA(8, 8); break;
+    default: l0mn = SA(4, 4); l0mx = SA(4, 4); l1 = SA(8, 8); l2 = SA(8, 8); mn = SA(8, 8); mx = SA(8, 8); break;
+    }
+    if (in->qp_opt) {
+        const uint16_t qw = (uint16_t)clip3(250, 1000, (int)((8 * (int)in->qp) - 125));
+        mn.width = (uint16_t)tmax(8, (mn.width * qw) / 1000); mn.height = (uint16_t)tmax(8, (mn.height * qw) / 1000);
+        mx.width = (uint16_t)tmax(8, (mx.width * qw) / 1000); mx.height = (uint16_t)tmax(8, (mx.height * qw) / 1000);
+    }
+    o->num_hme_sa_w = o->num_hme_sa_h = 2;
+    o->hme_l0_sa.sa_min = l0mn; o->hme_l0_sa.sa_max = l0mx; // set_hme_search_params_mctf(ctx, 0): the TF defaults
+    o->hme_l1_sa = l1; o->hme_l2_sa = l2;
+    o->me_sa.sa_min = mn; o->me_sa.sa_max = mx;
+    o->enable_hme_flag = o->enable_hme_level0_flag = 1;
+    o->enable_hme_level1_flag = in->hme_me_level <= 2;
+    o->enable_hme_level2_flag = in->hme_me_level == 0;
+    o->hme_search_method = 1;                          // FULL_SAD_SEARCH, temporal_filtering.c:315
+    o->me_search_method = in->hme_me_level <= 2 ? 1 : 0;
+    o->prune_ref_if_hme_sad_dev_bigger_than_th = o->prune_ref_if_me_sad_dev_bigger_than_th = (uint16_t)~0; // prune level 0
+    o->me_early_exit_th = (in->enc_mode <= 6 || res <= R720) ? 0u : 64u * 64u * 4u;
+    o->prev_me_stage_based_exit_th = (in->enc_mode <= 7 || res <= R720) ? 0u : 64u * 64u * 4u;
+    o->num_of_list_to_search = 1;
+    o->num_of_ref_pic_to_search[0] = 1;
+    o->temporal_layer_index = in->temporal_layer_index;
+    o->is_ref = in->is_ref;
+    o->me_type = 1;
+    o->tf_me_exit_th = in->me_exit_th;
+    o->max_number_of_pus_per_sb = 85;
+    o->enable_me_8x8 = o->enable_me_16x16 = 1; // (the TF reads the tables directly; nothing is exported per PU)
+    o->max_refs = o->max_cand = o->max_l0 = 1;
+    o->input_resolution_le_480p = res <= R480;
+    return SVTME_OK;
+}
+extern "C" uint32_t svtme_sizeof_tf_derive_input(void) { return (uint32_t)sizeof(SvtMeTfDeriveInput); }

@@ -51,6 +51,7 @@ struct StageState {
     int fp_do, fp_sa_w, fp_sa_h, fp_ox, fp_oy, fp_probe, fp_phase;
     int16_t fp_xc, fp_yc;
     int c00_needed;
+    int tf_exit; // ME_MCTF: search_results[0][0].hme_sad < tf_me_exit_th, the function returns after HME (:3179-3183)
 };
 
 // The slice of the state integer_search_b64 works on for ONE reference (int_kernel keeps it in
@@ -555,7 +556,8 @@ __device__ void plan_int_b(S *s, const DevJob &J, int li, int ri) {
     const SvtMeParams &p = J.prm;
     int16_t xc = s->fp_xc, yc = s->fp_yc;
     int16_t sa_w = (int16_t)p.me_sa.sa_min.width, sa_h = (int16_t)p.me_sa.sa_min.height;
-    const uint16_t dist = scaled_dist(ref_dist(p, li, ri));
+    // (:1302: ME_MCTF, the temporal-filter ME, uses the picture distance as it is)
+    const uint16_t dist = p.me_type == 1 ? ref_dist(p, li, ri) : scaled_dist(ref_dist(p, li, ri));
     sa_w = (int16_t)min((int)(sa_w * dist), (int)p.me_sa.sa_max.width);
     sa_h = (int16_t)min((int)(sa_h * dist), (int)p.me_sa.sa_max.height);
     // NB: the reference applies the mv-based scaling to the UNCLIPPED hme centre (:1309-1314)

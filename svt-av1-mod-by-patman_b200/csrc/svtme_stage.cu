@@ -103,7 +103,10 @@ __device__ __forceinline__ void scalar_step(const WideArgs &a, int gid) {
         if (hme_l2) post_level_jobs(s, p, 2, 1);
         s->n_jobs = 0;
         set_final_search_centre(s, p);
-        if (p.enable_hme_flag) hme_prune_ref_and_adjust_sr(s, p);
+        if (p.me_type == 1) // ME_MCTF (:3173-3183): no pruning / area adjustment; early return when the HME SAD is small enough
+            s->tf_exit = s->sr[0][0].hme_sad < p.tf_me_exit_th;
+        else if (p.enable_hme_flag)
+            hme_prune_ref_and_adjust_sr(s, p);
     }
 }
 
@@ -746,7 +749,7 @@ __global__ void __launch_bounds__(SMALL ? SVTME_INT_SMALL_THREADS : SVTME_THREAD
         bool mine = false;
         if (k < sl.n) {
             const int li = sl.slot[k] / NR, ri = sl.slot[k] % NR;
-            mine = li < Jg.prm.num_of_list_to_search && ri < Jg.prm.num_of_ref_pic_to_search[li] && g->sr[li][ri].do_ref &&
+            mine = !g->tf_exit && li < Jg.prm.num_of_list_to_search && ri < Jg.prm.num_of_ref_pic_to_search[li] && g->sr[li][ri].do_ref &&
                 (mode != INT_RESUME || g->fp_deferred[li][ri]); // (pruned reference: its tables keep the zero fill, :1287-1290)
         }
         todo = __ballot_sync(0xffffffffu, mine);
@@ -790,15 +793,18 @@ __global__ void __launch_bounds__(128) finish_kernel(WideArgs a) {
     StageState *s = &sm->st;
     const DevJob &J = sm->job;
     const SvtMeParams &p = J.prm;
-    // ---- pruning, candidates, statistics :3192-3221
-    if (p.enable_hme_flag && p.enable_me_hme_ref_pruning) me_prune_ref(s, p); // (CTA-uniform condition; syncs inside)
-    uint8_t *total = J.total + (size_t)b64 * J.n_pu;
-    uint32_t *mvo = J.mv + (size_t)b64 * J.n_pu * p.max_refs;
-    uint8_t *cando = J.cand + (size_t)b64 * J.n_pu * p.max_cand;
-    if (tid < p.max_number_of_pus_per_sb) construct_candidates(s, p, (uint32_t)tid, total, mvo, cando);
-    __threadfence_block();
-    __syncthreads();
-    if (tid < 32) finish_b64(s, J, b64, cando);
+    // ---- pruning, candidates, statistics :3192-3221 (none of it for ME_MCTF, :3173,3196: the temporal filter reads
+    // p_sb_best_sad / p_sb_best_mv and the HME results, i.e. the deep state below)
+    if (p.me_type != 1) {
+        if (p.enable_hme_flag && p.enable_me_hme_ref_pruning) me_prune_ref(s, p); // (CTA-uniform condition; syncs inside)
+        uint8_t *total = J.total + (size_t)b64 * J.n_pu;
+        uint32_t *mvo = J.mv + (size_t)b64 * J.n_pu * p.max_refs;
+        uint8_t *cando = J.cand + (size_t)b64 * J.n_pu * p.max_cand;
+        if (tid < p.max_number_of_pus_per_sb) construct_candidates(s, p, (uint32_t)tid, total, mvo, cando);
+        __threadfence_block();
+        __syncthreads();
+        if (tid < 32) finish_b64(s, J, b64, cando);
+    }
     // deep state for parity checks
     if (J.best_sad)
         for (int i = tid; i < NL * NR * SVTME_PU_COUNT; i += blockDim.x) {

@@ -368,6 +368,21 @@ void svt_open_loop_me_fullpel_search_sblock_b200(const uint8_t *src, uint32_t sr
                                                  uint32_t search_area_height, uint8_t sub_sad,
                                                  uint32_t *p_sb_best_sad, uint32_t *p_sb_best_mv);
 
+/* Batched form of the above for meaningful timing: n searches of 64x64 blocks in ONE launch, everything in
+ * DEVICE memory. Item i searches the block at d_src + src_offset against the window whose top-left search position is
+ * d_ref + ref_offset (i.e. MV (x_search_area_origin, y_search_area_origin)), search_area_width x search_area_height
+ * positions; d_best_sad / d_best_mv hold n x 85 entries (search order), read-modify-write like p_sb_best_sad / p_sb_best_mv.
+ * The reference rows must be readable from 16 bytes before to 8 rows + 256 bytes past the window (padded planes are).
+ * Asynchronous on cuda_stream. Returns 0 or a negative SVTME_ERR_*. */
+typedef struct SvtMeFullpelItem {
+    uint32_t src_offset, ref_offset;              /* bytes from d_src / d_ref */
+    int16_t x_search_area_origin, y_search_area_origin;
+    uint16_t search_area_width, search_area_height;
+} SvtMeFullpelItem;
+int svt_open_loop_me_fullpel_search_sblock_b200_batch(void *cuda_stream, uint32_t n, const uint8_t *d_src, uint32_t src_stride,
+                                                      const uint8_t *d_ref, uint32_t ref_stride, const SvtMeFullpelItem *d_items,
+                                                      uint8_t sub_sad, uint32_t *d_best_sad, uint32_t *d_best_mv);
+
 /* ---------------- allocation-free batched svt_sad_loop_kernel ----------------
  * NO COUNTERPART IN THE REFERENCE; added for callers that cannot call
  * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it). A variant of

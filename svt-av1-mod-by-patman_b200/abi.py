@@ -82,6 +82,11 @@ class SvtMeDeriveInput(C.Structure):
     ]
 
 
+class SvtMeFullpelItem(C.Structure):  # include/svtme_b200.h
+    _fields_ = [("src_offset", u32), ("ref_offset", u32), ("x_search_area_origin", C.c_int16), ("y_search_area_origin", C.c_int16),
+                ("search_area_width", C.c_uint16), ("search_area_height", C.c_uint16)]
+
+
 class SvtMeTfDeriveInput(C.Structure):  # include/svtme_b200.h
     _fields_ = [("enc_mode", C.c_int32), ("width", u32), ("height", u32), ("qp", u32), ("hme_me_level", u8), ("qp_opt", u8),
                 ("me_exit_th", C.c_uint16), ("temporal_layer_index", u8), ("is_ref", u8), ("_pad", u8 * 2)]
@@ -198,6 +203,7 @@ def load_library():
         "svtme_sync": (C.c_int, [vp]),
         "svtme_last_kernel_ms": (C.c_float, [vp]),
         "svtme_launch_count": (u64, []),
+        "svt_open_loop_me_fullpel_search_sblock_b200_batch": (C.c_int, [vp, u32, vp, u32, vp, u32, vp, C.c_uint8, vp, vp]),
         "svtme_noalloc_setup": (C.c_int, [C.c_int]),
         "svt_sad_loop_kernel_b200_noalloc": (C.c_int, [vp, u32, vp, u32, C.c_size_t, vp, u32, C.c_size_t, u32, u32, u32, C.c_uint8,
                                                        C.c_int16, C.c_int16, vp, vp, vp]),

@@ -106,4 +106,7 @@ void svtme_launch_sad_loop_test(const uint8_t *d_src, int src_stride, const uint
 void svtme_launch_fullpel_test(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride, int ox,
                                int oy, int sa_w, int sa_h, int sub_sad, uint32_t *d_best_sad, uint32_t *d_best_mv,
                                cudaStream_t st);
+cudaError_t svtme_launch_fullpel_batch(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride,
+                                       const SvtMeFullpelItem *d_items, int n, int sub_sad, uint32_t *d_best_sad, uint32_t *d_best_mv,
+                                       cudaStream_t st);
 extern unsigned long long g_svtme_launches;

@@ -1056,3 +1056,55 @@ void svtme_launch_fullpel_test(const uint8_t *d_src, int src_stride, const uint8
                                                                      sub_sad, d_best_sad, d_best_mv);
     ++g_svtme_launches;
 }
+
+
+// ---------------------------------------------------------------- kernel-level batched forms ("*_batch(n, args[])")
+// n full-pel searches of 64x64 blocks in ONE launch, one CTA per item, the same engine as the stage (fullpel_search).
+// Everything is in device memory; the best tables are read-modify-write like p_sb_best_sad / p_sb_best_mv.
+__global__ void __launch_bounds__(SVTME_THREADS, SVTME_CTAS_PER_SM)
+    fullpel_batch_kernel(const uint8_t *src, int src_stride, const uint8_t *ref, int ref_stride, const SvtMeFullpelItem *items,
+                         int sub_sad, uint32_t *best_sad, uint32_t *best_mv) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    TestSmem *sm = reinterpret_cast<TestSmem *>(smem_raw);
+    const SvtMeFullpelItem it = items[blockIdx.x];
+    const uint8_t *s = src + it.src_offset;
+    if (((reinterpret_cast<uintptr_t>(s) | (uintptr_t)src_stride) & 15) == 0) {
+        for (int i = threadIdx.x; i < 256; i += SVTME_THREADS) cp_async16(&sm->src[(i >> 2) * 64 + (i & 3) * 16], s + (size_t)(i >> 2) * src_stride + (i & 3) * 16);
+        cp_async_wait_all();
+    } else
+        for (int i = threadIdx.x; i < 64 * 64; i += SVTME_THREADS) sm->src[i] = s[(size_t)(i >> 6) * src_stride + (i & 63)];
+    uint32_t *bs = best_sad + (size_t)blockIdx.x * SVTME_PU_COUNT, *bm = best_mv + (size_t)blockIdx.x * SVTME_PU_COUNT;
+    if (threadIdx.x < SVTME_PU_COUNT) {
+        sm->tab.key[threadIdx.x] = (unsigned long long)bs[threadIdx.x] << 32; // order 0: existing entries win ties
+        sm->tab.mv[threadIdx.x] = bm[threadIdx.x];
+    }
+    __syncthreads();
+    fullpel_search(sm->src, ref + it.ref_offset, ref_stride, it.x_search_area_origin, it.y_search_area_origin, it.search_area_width,
+                   it.search_area_height, sub_sad != 0, 1, &sm->tab, sm->arena, (int)sizeof(sm->arena));
+    if (threadIdx.x < SVTME_PU_COUNT) {
+        bs[threadIdx.x] = (uint32_t)(sm->tab.key[threadIdx.x] >> 32);
+        bm[threadIdx.x] = sm->tab.mv[threadIdx.x];
+    }
+}
+
+cudaError_t svtme_launch_fullpel_batch(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride,
+                                       const SvtMeFullpelItem *d_items, int n, int sub_sad, uint32_t *d_best_sad, uint32_t *d_best_mv,
+                                       cudaStream_t st) {
+    static std::mutex mu;
+    static bool done[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (dev >= 0 && dev < 64 && !done[dev]) {
+            e = cudaFuncSetAttribute(fullpel_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TestSmem));
+            if (e != cudaSuccess) return e;
+            done[dev] = true;
+        }
+    }
+    fullpel_batch_kernel<<<n, SVTME_THREADS, sizeof(TestSmem), st>>>(d_src, src_stride, d_ref, ref_stride, d_items, sub_sad, d_best_sad,
+                                                                    d_best_mv);
+    ++g_svtme_launches;
+    return cudaGetLastError();
+}

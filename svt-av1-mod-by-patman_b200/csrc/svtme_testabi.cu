@@ -76,6 +76,25 @@ extern "C" void svt_open_loop_me_fullpel_search_sblock_b200(const uint8_t *src, 
     CK(cudaMemcpy(p_sb_best_mv, dmv.p, 85 * 4, cudaMemcpyDeviceToHost));
 }
 
+void svtme_set_error(const char *what); // svtme_api.cu
+extern "C" int svt_open_loop_me_fullpel_search_sblock_b200_batch(void *cuda_stream, uint32_t n, const uint8_t *d_src, uint32_t src_stride,
+                                                                 const uint8_t *d_ref, uint32_t ref_stride,
+                                                                 const SvtMeFullpelItem *d_items, uint8_t sub_sad, uint32_t *d_best_sad,
+                                                                 uint32_t *d_best_mv) {
+    if (n == 0) return SVTME_OK;
+    if (!d_src || !d_ref || !d_items || !d_best_sad || !d_best_mv) {
+        svtme_set_error("svt_open_loop_me_fullpel_search_sblock_b200_batch: null pointer");
+        return SVTME_ERR_INVALID;
+    }
+    const cudaError_t e = svtme_launch_fullpel_batch(d_src, (int)src_stride, d_ref, (int)ref_stride, d_items, (int)n, sub_sad, d_best_sad,
+                                                     d_best_mv, (cudaStream_t)cuda_stream);
+    if (e != cudaSuccess) {
+        svtme_set_error(cudaGetErrorString(e));
+        return SVTME_ERR_CUDA;
+    }
+    return SVTME_OK;
+}
+
 // ---------------------------------------------------------------- small per-call kernels
 __device__ uint32_t sad8xn(const uint8_t *s, int ss, const uint8_t *r, int rs, int rows) {
     uint32_t acc = 0;

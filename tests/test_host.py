@@ -99,3 +99,12 @@ def test_pyramid_sharing_plan():
         for r in range(world):  # everything a rank needs is either its own build or comes by broadcast
             for pic in needed[r]:
                 assert pic % world == r or r in planned[pic]
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/Source"), reason="needs the reference headers (/root/reference)")
+def test_integration_hooks_compile_against_the_reference_headers():
+    """INTEGRATION.md quotes oracle/encoder_dump/svtme_hooks_example.c: it must compile (gcc -fsyntax-only) against the
+    reference's own headers and include/svtme_b200.h."""
+    import subprocess
+    r = subprocess.run(["make", "-s", "-C", os.path.join(U.ROOT, "oracle"), "integration-check"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]

@@ -760,8 +760,9 @@ __device__ __noinline__ void strip_columns(const StripJob *sj, int src_pitch, HJ
         while (col >= geo[cj].col_base + geo[cj].n_cols) ++cj;
         const HGeo &g = geo[cj];
         const int local = col - g.col_base;
-        const int c = local & 3, p = (local >> 2) & 1, ch = local >> 3, xg = 0; // (streamed windows are 8 wide: one x group)
-        const int sa_w = g.sa_w, n_all = (g.bh - p + 1) >> 1;                   // y = p, p + 2, ... < bh
+        const int sa_w = g.sa_w, n_xg = sa_w >> 3;                              // x groups of 8 positions
+        const int c = local & 3, p = (local >> 2) & 1, u = local >> 3, ch = u / n_xg, xg = u - ch * n_xg;
+        const int n_all = (g.bh - p + 1) >> 1;                                  // y = p, p + 2, ... < bh
         const int i0 = (ch * n_all) / g.col_chunks, n_p = ((ch + 1) * n_all) / g.col_chunks - i0; // this chunk's positions
         uint32_t best32 = ~0u;
         if (n_p > 0 && !(g.skip_even && p == 0)) {

@@ -472,10 +472,11 @@ __global__ void __launch_bounds__(SVTME_HME_THREADS, MODE == 0 ? STRIP0_CTAS : L
             const uint32_t off = (uint32_t)(jb.ref - rp.base); // (a plane is far below 4 GB: 32-bit division)
             const int y_tl = (int)(off / (uint32_t)rp.stride), x_tl = (int)(off - (uint32_t)y_tl * (uint32_t)rp.stride);
             const bool live = jb.sa_w > 0 && jb.sa_h > 0;
-            // tall 8-wide windows of full-width blocks are STREAMED (strip_columns); everything else runs as tiled items
-            const bool stream_ok = mode == 0 && STRIP_STREAM && live && jb.sa_w == 8 && jb.sa_h >= stream_min_h &&
+            // tall windows (width a multiple of 8) of full-width blocks are STREAMED (strip_columns: the 8 x H pre-HME windows,
+            // the HME level 0 quadrants of far references); everything else runs as tiled items
+            const bool stream_ok = STRIP_STREAM && live && jb.sa_w >= 8 && (jb.sa_w & 7) == 0 && jb.sa_h >= stream_min_h &&
                 sm->sj[min(lane, n - 1)].bw == 16;
-            const int G = jb.sa_w <= 8 ? 2 : (jb.sa_w <= 16 ? 4 : 8);
+            const int G = (jb.sa_w <= 8 || stream_ok) ? 2 : (jb.sa_w <= 16 ? 4 : 8);
             const int ny = (jb.sa_h + rs - 1) / rs;
             // y-tile: 2 rows for the widest items, 8 for tall narrow windows, and for 16-wide windows 2 where a
             // 4-row tile would be half empty (ny = 2, 6, 10: the 16x4 / 16x12 / 16x20 windows of HME level 0)
@@ -518,8 +519,8 @@ __global__ void __launch_bounds__(SVTME_HME_THREADS, MODE == 0 ? STRIP0_CTAS : L
             const int s_idx = __popc(sbal & ((1u << lane) - 1u)), s_tot = __popc(sbal), per_pass = SVTME_HME_THREADS / 8;
             const int s_full = (s_tot / per_pass) * per_pass;
             int chunks = 1;
-            if (in && stream && s_idx >= s_full) chunks = max(1, min(per_pass / (s_tot - s_full), (jb.sa_h >> 1) / 8));
-            const int n_cols = (in && stream) ? 8 * chunks : 0;
+            if (in && stream && jb.sa_w == 8 && s_idx >= s_full) chunks = max(1, min(per_pass / (s_tot - s_full), (jb.sa_h >> 1) / 8));
+            const int n_cols = (in && stream) ? 8 * (jb.sa_w >> 3) * chunks : 0; // (wider windows give enough units by themselves)
             int ps = n_items, pc = n_cols;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -838,6 +839,16 @@ static int strip_stream_min_h_from_env() {
     return v > 0 ? v : STRIP_STREAM_MIN_H;
 }
 static const int g_strip_stream_min_h = strip_stream_min_h_from_env();
+// HME level 0: streaming its quadrant windows (16 x 4 ... 48 x 48, 2 to 24 positions per column and parity) was measured
+// SLOWER than the tiled items at every threshold (1080p 0.60 -> 0.65-0.66 ms, 4K 11.7 -> 12.2 ms: a column of n positions
+// spends n + 7 steps, and the narrow tile geometry streaming needs makes the 16 KB strips shorter): off unless
+// SVTME_L0_STREAM_MIN_H says otherwise.
+static int l0_stream_min_h_from_env() {
+    const char *e = getenv("SVTME_L0_STREAM_MIN_H");
+    const int v = e ? atoi(e) : 0;
+    return v > 0 ? v : (1 << 30);
+}
+static const int g_l0_stream_min_h = l0_stream_min_h_from_env();
 
 // Launch slots (one event after each; names in SVTME_PHASE_NAMES of svtme_common.cuh).
 SvtmeStageFlags svtme_stage_flags(const SvtMeParams &p) {
@@ -927,7 +938,7 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
             // the arena is the last member of StripSmem: a smaller arena is a smaller dynamic allocation
             const int lim = g_strip_arena_limit < L0_STRIP_ARENA ? g_strip_arena_limit : L0_STRIP_ARENA;
             strip_kernel<1><<<l0_tasks, SVTME_HME_THREADS, sizeof(StripSmem) - SVTME_HME_ARENA_BYTES + L0_STRIP_ARENA, st>>>(
-                a, b64_cols, b64_rows, 3, lim, 1 << 30);
+                a, b64_cols, b64_rows, 3, lim, g_l0_stream_min_h);
         }
         else
             engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 3);

@@ -725,19 +725,31 @@ __device__ __forceinline__ uint32_t col_walk(const uint32_t (&s)[8][4], int nrow
     uint32_t acc[8][2];
 #pragma unroll
     for (int k = 0; k < 8; ++k) acc[k][0] = acc[k][1] = 0;
+    // software pipeline: the row of step t + 1 is loaded while step t computes (the planner stages two rows more than the
+    // last step reads, so the last prefetch stays inside the strip); without it every step began with a wait for its LDS
+    uint32_t nxt[6];
+    {
+        const uint8_t *rp = base + R * pitch + ((R >> 3) << 4);
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            const uint2 v = *reinterpret_cast<const uint2 *>(rp + 8 * q);
+            nxt[2 * q] = v.x; nxt[2 * q + 1] = v.y;
+        }
+    }
     for (int t0 = 0; t0 < T; t0 += 8) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             if (t0 + k < T) {
+                uint32_t w[5];
+#pragma unroll
+                for (int q = 0; q < 5; ++q) w[q] = __funnelshift_r(nxt[q], nxt[q + 1], sh);
+                R += 2;
                 const uint8_t *rp = base + R * pitch + ((R >> 3) << 4);
-                uint32_t raw[6], w[5];
 #pragma unroll
                 for (int q = 0; q < 3; ++q) {
                     const uint2 v = *reinterpret_cast<const uint2 *>(rp + 8 * q);
-                    raw[2 * q] = v.x; raw[2 * q + 1] = v.y;
+                    nxt[2 * q] = v.x; nxt[2 * q + 1] = v.y;
                 }
-#pragma unroll
-                for (int q = 0; q < 5; ++q) w[q] = __funnelshift_r(raw[q], raw[q + 1], sh);
                 col_step<FULL>(k, s, acc, w, nrows);
                 const int done = (k + 1) & 7; // the position started 7 steps ago is complete
                 if (t0 + k >= 7) {
@@ -745,7 +757,6 @@ __device__ __forceinline__ uint32_t col_walk(const uint32_t (&s)[8][4], int nrow
                     best32 = min(best32, (acc[done][1] << 17) + idx + 4);
                 }
                 acc[done][0] = acc[done][1] = 0;
-                R += 2;
                 idx += idx_step;
             }
         }

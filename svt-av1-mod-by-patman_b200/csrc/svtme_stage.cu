@@ -497,7 +497,7 @@ __global__ void __launch_bounds__(SVTME_HME_THREADS, MODE == 0 ? STRIP0_CTAS : L
                 stream = stream_ok && xo == 0; // (windows of one b64 column start at the same x: always)
                 xt_n = (xo + jb.sa_w + 4 * G - 1) / (4 * G);
                 // rows the job reads: whole y-tiles of 8-row sub-blocks (items), or the last position's last row (columns)
-                rows_s = warp_max(in ? (stream ? dy + jb.sa_h + 7 * rs : dy + n_yt * TY * rs + 7 * rs) : 0);
+                rows_s = warp_max(in ? (stream ? dy + jb.sa_h + 8 * rs : dy + n_yt * TY * rs + 7 * rs) : 0); // (+ the prefetched row)
                 rows_real = warp_max(in ? dy + jb.sa_h + (nrows_j - 1) * rs : 1);
                 words = warp_max(in ? (xs >> 2) + xt_n * G + 5 : 0);
                 cpr = (words + 3) >> 2;

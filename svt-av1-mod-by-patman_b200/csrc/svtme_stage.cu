@@ -26,11 +26,18 @@ struct WideArgs {
 size_t svtme_stage_state_bytes() { return sizeof(StageState); }
 int svtme_fp_direct_max() { return SVTME_FP_DIRECT_MAX; }
 
+// global -> shared copy of a whole struct with cp.async (all chunks of the CTA in flight at once: ONE round trip, where the
+// register copy loop paid one per unrolled group of iterations). The caller waits (cp_async_wait_all) and synchronises.
+template <class T>
+__device__ __forceinline__ void async_copy_struct(T *dst, const T *src) {
+    static_assert(sizeof(T) % 8 == 0 && alignof(T) >= 8, "copied as 8-byte chunks");
+    const uint8_t *g = reinterpret_cast<const uint8_t *>(src);
+    uint8_t *d = reinterpret_cast<uint8_t *>(dst);
+    for (int i = threadIdx.x; i < (int)(sizeof(T) / 8); i += blockDim.x) cp_async8(d + 8 * i, g + 8 * i);
+}
 __device__ __forceinline__ void copy_job_to_smem(DevJob *dst, const DevJob *src) {
-    static_assert(sizeof(DevJob) % 4 == 0, "DevJob is copied as 32-bit words");
-    const uint32_t *g = reinterpret_cast<const uint32_t *>(src);
-    uint32_t *d = reinterpret_cast<uint32_t *>(dst);
-    for (int i = threadIdx.x; i < (int)(sizeof(DevJob) / 4); i += blockDim.x) d[i] = __ldg(g + i);
+    async_copy_struct(dst, src);
+    cp_async_wait_all(); // (a __syncthreads of the caller publishes it)
 }
 
 __host__ __device__ __forceinline__ bool l0_dependent(const SvtMeParams &p) { // :1882-1895
@@ -783,13 +790,11 @@ __global__ void __launch_bounds__(128) finish_kernel(WideArgs a) {
     FinSmem *sm = reinterpret_cast<FinSmem *>(smem_raw);
     const int gid = blockIdx.x, tid = threadIdx.x;
     const uint32_t b64 = (uint32_t)(gid % a.b64_per_job);
-    copy_job_to_smem(&sm->job, &a.jobs[gid / a.b64_per_job]);
-    {   // whole state block -> shared memory (coalesced), then the reference's scalar tail runs on it
-        const uint32_t *gs = reinterpret_cast<const uint32_t *>(&a.st[gid]);
-        uint32_t *d = reinterpret_cast<uint32_t *>(&sm->st);
-        static_assert(sizeof(StageState) % 4 == 0, "state is copied as 32-bit words");
-        for (int i = tid; i < (int)(sizeof(StageState) / 4); i += blockDim.x) d[i] = gs[i];
-    }
+    // job descriptor and whole state block -> shared memory (cp.async: one round trip), then the reference's scalar tail
+    // runs on the copy
+    async_copy_struct(&sm->job, &a.jobs[gid / a.b64_per_job]);
+    async_copy_struct(&sm->st, &a.st[gid]);
+    cp_async_wait_all();
     __syncthreads();
     StageState *s = &sm->st;
     const DevJob &J = sm->job;

@@ -493,6 +493,9 @@ def main():
     exit_code = 0
     torch.cuda.set_device(local_rank)
     if world > 1:
+        # the pyramid exchange runs while ME kernels with hundreds of thousands of CTAs are resident: its NCCL kernels must
+        # not queue behind them (high-priority NCCL streams; the exchange stream below is high priority too)
+        os.environ.setdefault("TORCH_NCCL_HIGH_PRIORITY", "1")
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
     me = importlib.import_module(PKG + ".me")
     shard = importlib.import_module(PKG + ".shard")
@@ -535,7 +538,7 @@ def main():
 
     if share:
         # picture p -> ring slot p on every rank (slots are handed out in order on a fresh handle), built by rank p % N
-        xs = torch.cuda.Stream()  # the exchange stream: NCCL work is ordered against it, never against the host
+        xs = torch.cuda.Stream(priority=-1)  # the exchange stream: NCCL work is ordered against it, never against the host
         # (two sets: pictures p and ALT + p, the second one in slots n_slots + p, for consecutive steps of the streamed run)
         ses.external_write_begin(list(range(n_slots)) + [ALT + p for p in range(n_slots)], xs.cuda_stream)
         pool_ptr = ses.plane_device_ptr(0, 0)[0]

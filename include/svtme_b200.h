@@ -300,6 +300,12 @@ int svtme_last_work_ops(SvtMeHandle *h, uint64_t *ops);
 int svtme_last_phase_ms(SvtMeHandle *h, float *ms, uint32_t n);
 /* Algorithmic SAD byte-ops (positions x block pixels compared) per launch slot, same slots. */
 int svtme_last_phase_work(SvtMeHandle *h, uint64_t *ops, uint32_t n);
+/* Profiling aid (no reference counterpart): a slot holds its search launches (the kernels that compute SADs) AND the
+ * one-thread-per-b64 bookkeeping launches between them. With search timing on, every later launch also brackets the
+ * search launches of each slot with their own events; svtme_last_search_ms returns their device milliseconds per slot
+ * (the duration of the search kernels alone; 0 for a slot without one). Off by default (32 more events per launch). */
+int svtme_set_search_timing(SvtMeHandle *h, int on);
+int svtme_last_search_ms(SvtMeHandle *h, float *ms, uint32_t n);
 /* Measured issue rate (Ginst/s, whole GPU) of VABSDIFF4.U8.ACC, 4 byte-SADs per instruction: the
  * integer-SAD roofline denominator (not part of MEASURED_PEAKS.json). */
 double svtme_measure_vabsdiff4_ginst_per_s(void);

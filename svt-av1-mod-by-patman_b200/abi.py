@@ -211,6 +211,8 @@ def load_library():
         "svtme_last_work_ops": (C.c_int, [vp, P(u64)]),
         "svtme_last_phase_ms": (C.c_int, [vp, P(C.c_float), C.c_uint32]),
         "svtme_last_phase_work": (C.c_int, [vp, P(u64), C.c_uint32]),
+        "svtme_set_search_timing": (C.c_int, [vp, C.c_int]),
+        "svtme_last_search_ms": (C.c_int, [vp, P(C.c_float), C.c_uint32]),
         "svtme_measure_vabsdiff4_ginst_per_s": (C.c_double, []),
         "svtme_sizeof_params": (u32, []),
         "svtme_sizeof_out": (u32, []),

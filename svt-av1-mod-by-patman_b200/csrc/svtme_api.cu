@@ -66,6 +66,8 @@ struct Batch {
     std::vector<uint8_t> direct;  // queued form: job i's three big arrays were downloaded straight into the caller's page-locked arrays
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, jobs_ev = nullptr, done_ev = nullptr; // done_ev: download complete
     cudaEvent_t ph_ev[SVTME_PHASES] = {};
+    cudaEvent_t sev[4 * SVTME_PHASES] = {}; // svtme_set_search_timing: brackets around the search launches of each slot (created on first use)
+    uint32_t sev_mask = 0;
     bool jobs_pending = false; // h_jobs may still be on its way to the device
     uint32_t n = 0;
     size_t total = 0;
@@ -90,6 +92,7 @@ struct SvtMeHandle {
                                          // of them, so that the launch tails of one batch are filled by the next ones
     int n_streams = 2;
     cudaEvent_t origin_ev = nullptr; // svtme_debug_mark
+    bool search_timing = false;      // svtme_set_search_timing
     float span[3] = {0.f, 0.f, 0.f};  // last collected batch: pipeline start / end / download end, ms after the mark
     uint32_t submit_count = 0;
     void *x_states[SVTME_NS] = {};      // per extra compute stream: its own per-b64 scratch
@@ -143,6 +146,8 @@ static void batch_free(Batch *b) {
     if (b->done_ev) cudaEventDestroy(b->done_ev);
     for (int k = 0; k < SVTME_PHASES; ++k)
         if (b->ph_ev[k]) cudaEventDestroy(b->ph_ev[k]);
+    for (int k = 0; k < 4 * SVTME_PHASES; ++k)
+        if (b->sev[k]) cudaEventDestroy(b->sev[k]);
     delete b;
 }
 
@@ -752,7 +757,11 @@ static int launch_into(SvtMeHandle *h, Batch *B, const SvtMeJob *jobs, uint32_t 
         flags.hme_l0 |= f.hme_l0; flags.hme_l0_round_b |= f.hme_l0_round_b;
         flags.hme_l1 |= f.hme_l1; flags.hme_l2 |= f.hme_l2;
     }
-    svtme_launch_me_stage(B->d_jobs, (int)n, (int)h->b64_cols, (int)h->b64_rows, d_states, st, B->ph_ev, flags);
+    B->sev_mask = 0;
+    if (h->search_timing && !B->sev[0])
+        for (int k = 0; k < 4 * SVTME_PHASES; ++k) CU(cudaEventCreate(&B->sev[k]));
+    svtme_launch_me_stage(B->d_jobs, (int)n, (int)h->b64_cols, (int)h->b64_rows, d_states, st, B->ph_ev, flags,
+                          h->search_timing ? B->sev : nullptr, &B->sev_mask);
     CU(cudaGetLastError());
     CU(cudaEventRecord(B->ev1, st));
     CU(cudaEventRecord(h->launch_ev[B->seq % SVTME_LAUNCH_EV_RING], st));
@@ -1013,6 +1022,34 @@ extern "C" int svtme_last_work_ops(SvtMeHandle *h, uint64_t *ops) {
     }
     *ops = sum;
     cudaEventElapsedTime(&h->last_ms, h->last->ev0, h->last->ev1);
+    return SVTME_OK;
+}
+
+// Search launches of each slot timed on their own (see svtme_b200.h).
+extern "C" int svtme_set_search_timing(SvtMeHandle *h, int on) {
+    if (!h) return fail(SVTME_ERR_INVALID, "svtme_set_search_timing: null handle");
+    std::lock_guard<std::mutex> lk(h->mu);
+    h->search_timing = on != 0;
+    return SVTME_OK;
+}
+
+extern "C" int svtme_last_search_ms(SvtMeHandle *h, float *ms, uint32_t n) {
+    if (!h || !ms) return fail(SVTME_ERR_INVALID, "svtme_last_search_ms: bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(cudaSetDevice(h->device));
+    CU(cudaStreamSynchronize(h->stream));
+    for (int k = 1; k < SVTME_NS; ++k) CU(cudaStreamSynchronize(h->xstream[k]));
+    if (n > SVTME_PHASES) n = SVTME_PHASES;
+    if (!h->last) return fail(SVTME_ERR_NOTFOUND, "svtme_last_search_ms: nothing launched");
+    for (uint32_t k = 0; k < n; ++k) {
+        ms[k] = 0.f;
+        for (int r = 0; r < 2; ++r)
+            if (h->last->sev_mask >> (2 * k + r) & 1) {
+                float t = 0.f;
+                CU(cudaEventElapsedTime(&t, h->last->sev[(2 * k + r) * 2], h->last->sev[(2 * k + r) * 2 + 1]));
+                ms[k] += t;
+            }
+    }
     return SVTME_OK;
 }
 

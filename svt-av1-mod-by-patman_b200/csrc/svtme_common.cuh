@@ -95,8 +95,10 @@ struct SvtmeStageFlags {
 };
 SvtmeStageFlags svtme_stage_flags(const SvtMeParams &p);
 void svtme_configure_stage_kernels(); // per-device kernel attributes (dynamic shared memory), idempotent
+// sev (optional): 4 * SVTME_PHASES events, [(2 * slot + round) * 2 + {begin, end}] around the search launches of a slot (the
+// scalar bookkeeping launches that share the slot stay outside); *sev_mask: bit 2 * slot + round set for every bracket recorded
 void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b64_rows, void *d_states, cudaStream_t st,
-                           cudaEvent_t *ev, const SvtmeStageFlags &f);
+                           cudaEvent_t *ev, const SvtmeStageFlags &f, cudaEvent_t *sev = nullptr, uint32_t *sev_mask = nullptr);
 int svtme_fp_direct_max();
 size_t svtme_stage_state_bytes();
 // kernel-test entry points (svtme_stage.cu)

@@ -58,6 +58,7 @@ __device__ __forceinline__ void scalar_step(const WideArgs &a, int gid) {
     const bool hme_l1 = p.enable_hme_flag && p.enable_hme_level1_flag;
     const bool hme_l2 = p.enable_hme_flag && p.enable_hme_level2_flag;
     const bool zz = p.me_early_exit_th || p.me_safe_limit_zz_th;
+    if (STEP != S_INIT) prefetch_hot_state(s);
     if (STEP == S_INIT) { // the state block was zero-filled by the host (best tables start at 0)
         s->org_x = (int)(b64 % J.b64_cols) * 64;
         s->org_y = (int)(b64 / J.b64_cols) * 64;
@@ -894,7 +895,7 @@ void svtme_configure_stage_kernels() {
 }
 
 void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b64_rows, void *d_states, cudaStream_t st,
-                           cudaEvent_t *ev, const SvtmeStageFlags &f) {
+                           cudaEvent_t *ev, const SvtmeStageFlags &f, cudaEvent_t *sev, uint32_t *sev_mask) {
     const int b64_per_job = b64_cols * b64_rows;
     svtme_configure_stage_kernels();
     WideArgs a;
@@ -908,36 +909,52 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
         if (ev) cudaEventRecord(ev[slot], st);
         ++slot;
     };
+    // optional: the SEARCH launches of a slot bracketed by their own events (sev[(2 * slot + round) * 2 + {0, 1}]), so that
+    // a kernel's duration can be read without the scalar bookkeeping launches that share its slot
+    uint32_t smask = 0;
+    auto search_begin = [&](int round) {
+        if (sev) cudaEventRecord(sev[(2 * slot + round) * 2], st);
+    };
+    auto search_end = [&](int round) {
+        if (sev) cudaEventRecord(sev[(2 * slot + round) * 2 + 1], st), smask |= 1u << (2 * slot + round);
+    };
     svtme_launch_zero_fill(d_states, ((size_t)N * sizeof(StageState) + 15) & ~(size_t)15, st); // (the allocation is rounded up likewise)
     mark(); // 0: state clear
     int launches = 0;
     // scalar steps always run (they also carry the bookkeeping of disabled phases); engine launches
     // that no picture of the batch needs are skipped
     scalar_kernel<S_INIT, S_INIT><<<sg, 128, 0, st>>>(a);
-    if (f.zz) points_kernel<<<N, 128, 0, st>>>(a), ++launches;
+    if (f.zz) {
+        search_begin(0);
+        points_kernel<<<N, 128, 0, st>>>(a), ++launches;
+        search_end(0);
+    }
     scalar_kernel<S_ZZ, S_ZZ><<<sg, 128, 0, st>>>(a);
     mark(); // 1: zz-SAD
     // pre-HME rounds: strip mode when every picture uses the sub-sampled SAD, else one CTA per b64
     const int strip_tasks = n_jobs * NL * NR *
         (b64_cols * ((b64_rows + STRIP_SEG - 1) / STRIP_SEG) + b64_rows * ((b64_cols + STRIP_SEG - 1) / STRIP_SEG));
-    auto prehme_round = [&]() {
+    auto prehme_round = [&](int round) {
+        search_begin(round);
         if (f.prehme_strip)
             strip_kernel<0><<<strip_tasks, SVTME_HME_THREADS, sizeof(StripSmem), st>>>(a, b64_cols, b64_rows, 2, g_strip_arena_limit, g_strip_stream_min_h);
         else
             engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 2);
         ++launches;
+        search_end(round);
     };
-    if (f.prehme) prehme_round();
+    if (f.prehme) prehme_round(0);
     int fused = 0;
     if (f.prehme_l1_round) {
         scalar_kernel<S_PREHME1, S_PREHME1><<<sg, 128, 0, st>>>(a);
-        prehme_round();
+        prehme_round(1);
         scalar_kernel<S_PREHME2, S_PREHME2><<<sg, 128, 0, st>>>(a);
     } else
         scalar_kernel<S_PREHME1, S_PREHME2><<<sg, 128, 0, st>>>(a), ++fused;
     mark(); // 2: pre-HME
     const int l0_tasks = n_jobs * NL * NR * 4 * b64_rows * ((b64_cols + STRIP_SEG - 1) / STRIP_SEG);
-    auto l0_round = [&]() {
+    auto l0_round = [&](int round) {
+        search_begin(round);
         if (f.prehme_strip && f.l0_strip)
             {
             // the arena is the last member of StripSmem: a smaller arena is a smaller dynamic allocation
@@ -948,30 +965,35 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
         else
             engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 1, 3);
         ++launches;
+        search_end(round);
     };
-    if (f.hme_l0) l0_round();
+    if (f.hme_l0) l0_round(0);
     if (f.hme_l0_round_b) {
         scalar_kernel<S_L0A, S_L0A><<<sg, 128, 0, st>>>(a);
-        l0_round();
+        l0_round(1);
         scalar_kernel<S_L0B, S_L0B><<<sg, 128, 0, st>>>(a);
     } else
         scalar_kernel<S_L0A, S_L0B><<<sg, 128, 0, st>>>(a), ++fused;
     mark(); // 3: HME level 0
     if (f.hme_l1) {
+        search_begin(0);
         if (f.refine_small)
             refine_kernel<8><<<N, 128, sizeof(RefineSmem<8>), st>>>(a, 1, 4);
         else
             engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 2, 4);
         ++launches;
+        search_end(0);
     }
     if (f.hme_l2) {
         scalar_kernel<S_L1, S_L1><<<sg, 128, 0, st>>>(a);
         mark(); // 4: HME level 1
+        search_begin(0);
         if (f.refine_small)
             refine_kernel<16><<<N, 128, sizeof(RefineSmem<16>), st>>>(a, 0, 5);
         else
             engine_kernel<<<N, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(a, 3, 5);
         ++launches;
+        search_end(0);
         scalar_kernel<S_L2, S_L2><<<sg, 128, 0, st>>>(a);
     } else {
         mark(); // 4: HME level 1 (its post step runs fused with the search-centre step below)
@@ -988,6 +1010,7 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
                 IntSlots &t = round[(f.int_dependent && !f.small_areas && (li || ri)) ? 1 : 0];
                 t.slot[t.n++] = (int8_t)(li * NR + ri);
             }
+        search_begin(0);
         for (const IntSlots &t : round) {
             if (!t.n) continue;
             int_kernel<true><<<N, SVTME_INT_SMALL_THREADS, sizeof(IntSmem<true>), st>>>(a, t, f.small_areas ? INT_ALL : INT_DEFER);
@@ -997,10 +1020,14 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
                 ++launches;
             }
         }
+        search_end(0);
     }
     mark(); // 6: integer search
+    search_begin(0);
     finish_kernel<<<N, 128, sizeof(FinSmem), st>>>(a);
+    search_end(0);
     mark(); // 7: candidates + statistics
+    if (sev_mask) *sev_mask = smask;
     g_svtme_launches += 8 - fused + 1 + launches; // (the state clear counts itself)
 }
 

@@ -179,6 +179,16 @@ class MeSession:
         _check(self.lib.svtme_last_phase_work(self.h, v, len(self.PHASE_NAMES)), self.lib)
         return dict(zip(self.PHASE_NAMES, (int(x) for x in v)))
 
+    def set_search_timing(self, on=True):
+        """Later launches also time the search launches of each slot on their own (svtme_last_search_ms)."""
+        _check(self.lib.svtme_set_search_timing(self.h, int(bool(on))), self.lib)
+
+    def last_search_ms(self):
+        """Device milliseconds of the search launches of each slot (no bookkeeping launches) in the last launch."""
+        v = (C.c_float * len(self.PHASE_NAMES))()
+        _check(self.lib.svtme_last_search_ms(self.h, v, len(self.PHASE_NAMES)), self.lib)
+        return dict(zip(self.PHASE_NAMES, (float(x) for x in v)))
+
     def last_kernel_ms(self):
         return float(self.lib.svtme_last_kernel_ms(self.h))
 

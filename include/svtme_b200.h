@@ -243,6 +243,45 @@ int svtme_external_write_end(SvtMeHandle *h, void *cuda_stream);
  * readers of the slot). Both handles must have been opened for the same picture size. */
 int svtme_share_picture(SvtMeHandle *src, SvtMeHandle *dst, uint64_t pic_num);
 
+/* ---- picture statistics of a resident picture --------------------------------------------
+ * Replaces svt_aom_gathering_picture_statistics (Codec/pic_analysis_process.c:1560-1578), which the picture-analysis
+ * kernel calls right after the pyramid build (:2137) on the same two buffers: the padded luma and the 1/16 plane.
+ *   variance  compute_picture_spatial_statistics / compute_block_mean_compute_variance (:307-1378, :1530-1552): per b64
+ *             the means and means of squares of the 64 8x8 blocks (svt_compute_interm_var_four8x8, every other row, for
+ *             BLOCK_MEAN_PREC_SUB — what enc_handle.c:4257 sets — or svt_compute_mean_8x8 / _square_values_8x8 for
+ *             BLOCK_MEAN_PREC_FULL), averaged up to 16x16 / 32x32 / 64x64 with >> 2, variance = (E[x^2] - E[x]^2) >> 16
+ *             as uint16_t in raster-scan order (64x64 = 0, 32x32 = 1..4, 16x16 = 5..20, 8x8 = 21..84); an incomplete b64 at
+ *             the right / bottom edge reads the padding like the reference does. pic_avg_variance = mean of entry 0.
+ *   histogram sub_sample_luma_generate_pixel_intensity_histogram_bins (:1462-1528) on the 1/16 plane: per region 256
+ *             bins that start at 1, every decim-th sample of every decim-th row (decim = 1 with scene-change detection
+ *             on, else 4), bins scaled by 16 * decim^2, average intensity per region, avg_luma over the picture. */
+typedef struct SvtMeStatsParams {
+    uint8_t calc_hist;              /* scs->calc_hist */
+    uint8_t calculate_variance;     /* scs->calculate_variance (off: pic_avg_variance = 0, variance untouched) */
+    uint8_t block_mean_prec_sub;    /* scs->block_mean_calc_prec == BLOCK_MEAN_PREC_SUB (definitions.h:2403-2404) */
+    uint8_t all_block_sizes;        /* enable_adaptive_quantization == 1 || variance_octile (:1110): all 85 entries are
+                                     * written; otherwise only entry 0 (64x64) */
+    uint8_t scene_change_detection; /* static_config.scene_change_detection (:1494) */
+    uint8_t _pad[3];
+    uint32_t regions_per_width, regions_per_height; /* scs->picture_analysis_number_of_regions_per_width / height, 1..4 */
+} SvtMeStatsParams;
+
+typedef struct SvtMeStatsOut {          /* host arrays of the caller; layouts of PictureParentControlSet (pcs.h) */
+    uint16_t *variance;                 /* [b64_count][all_block_sizes ? 85 : 1]: pcs->variance (allocation pcs.c:1306-1313) */
+    uint16_t *pic_avg_variance;         /* 1 */
+    uint32_t *picture_histogram;        /* [4][4][256], index [region x][region y][bin]: pcs->picture_histogram */
+    uint64_t *average_intensity_per_region; /* [4][4]: pcs->average_intensity_per_region (the value is a uint8_t) */
+    uint64_t *avg_luma;                 /* 1: pcs->avg_luma (INVALID_LUMA = 256 when calc_hist is off, :1563) */
+} SvtMeStatsOut;
+/* Synchronous: the arrays are filled on return. The picture must be resident (svtme_put_picture*). */
+int svtme_picture_statistics(SvtMeHandle *h, uint64_t pic_num, const SvtMeStatsParams *params, SvtMeStatsOut *out);
+/* n pictures, one launch sequence, one download (the picture-analysis kernel of the reference handles one picture per
+ * call; a look-ahead window's worth is the batch here). */
+int svtme_pictures_statistics(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const SvtMeStatsParams *params, SvtMeStatsOut *outs);
+/* Profiling aid: device milliseconds of the kernels and of the result download of the last statistics call. */
+int svtme_last_statistics_ms(SvtMeHandle *h, float *kernels_ms, float *download_ms);
+uint32_t svtme_sizeof_stats_params(void);
+
 /* Open-loop ME of one picture against refs[list][idx] (picture numbers previously put).
  * Replaces the b64 loop of me_process.c:174-289 calling svt_aom_motion_estimation_b64
  * (motion_estimation.c:3146). Synchronous: results are in `out` on return. */

@@ -96,6 +96,11 @@ int orc_me_picture_rows(const SvtMeParams *p, const OrcPyramid *cur,
                         const OrcPyramid *refs[SVTME_MAX_LISTS][SVTME_MAX_REFS], SvtMeOut *out,
                         uint32_t row0, uint32_t row1);
 
+/* ---- picture statistics (me_oracle_stats.c) ---- */
+/* svt_aom_gathering_picture_statistics (pic_analysis_process.c:1560) on a built pyramid: variance of the padded luma,
+ * histogram / intensities of the 1/16 plane. `out` arrays as in svtme_picture_statistics. */
+int orc_picture_statistics(const OrcPyramid *pyr, const SvtMeStatsParams *prm, SvtMeStatsOut *out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -8,7 +8,8 @@
  *   svt_aom_sig_deriv_me               Source/Lib/Codec/enc_mode_config.c:684
  *   svt_aom_downsample_filtering_input_picture  Source/Lib/Codec/pic_analysis_process.c:1922
  *   svt_aom_generate_padding           Source/Lib/Codec/pic_operators.c:338
- *   RTCD pointers                      Source/Lib/Codec/aom_dsp_rtcd.h:776,838-854
+ *   svt_aom_gathering_picture_statistics  Source/Lib/Codec/pic_analysis_process.c:1560
+ *   RTCD pointers                      Source/Lib/Codec/aom_dsp_rtcd.h:776,838-860
  */
 #include <stdlib.h>
 #include <string.h>
@@ -31,6 +32,7 @@
 #include "compute_sad_c.h"
 #include "me_sad_calculation.h"
 #include "pack_unpack_c.h"
+#include "compute_mean.h"
 
 #include "svtme_b200.h"
 #include "mt_pool.h"
@@ -80,6 +82,10 @@ int ref_set_simd(int simd) {
     svt_nxm_sad_kernel                         = svt_nxm_sad_kernel_helper_c;
     svt_nxm_sad_kernel_sub_sampled             = svt_nxm_sad_kernel_helper_c;
     downsample_2d                              = svt_aom_downsample_2d_c;
+    svt_compute_mean_8x8                       = svt_compute_mean_c;                /* aom_dsp_rtcd.c:515-518 */
+    svt_compute_mean_square_values_8x8         = svt_compute_mean_squared_values_c;
+    svt_compute_sub_mean_8x8                   = svt_compute_sub_mean_8x8_c;
+    svt_compute_interm_var_four8x8             = svt_compute_interm_var_four8x8_c;
     svt_aom_un_pack2d_16_bit_src_mul4          = svt_enc_msb_un_pack2_d; /* common_dsp_rtcd.c:518, C entry */
 #ifdef REF_HAVE_AVX2
     if (simd && __builtin_cpu_supports("avx2")) {
@@ -90,6 +96,10 @@ int ref_set_simd(int simd) {
         svt_nxm_sad_kernel                        = svt_nxm_sad_kernel_helper_avx2;
         svt_nxm_sad_kernel_sub_sampled            = svt_nxm_sad_kernel_helper_avx2;
         downsample_2d                             = svt_aom_downsample_2d_avx2; /* aom_dsp_rtcd.c:507 */
+        svt_compute_mean_8x8                      = svt_compute_mean8x8_avx2_intrin;
+        svt_compute_mean_square_values_8x8        = svt_compute_mean_of_squared_values8x8_sse2_intrin;
+        svt_compute_sub_mean_8x8                  = svt_compute_sub_mean8x8_sse2_intrin;
+        svt_compute_interm_var_four8x8            = svt_compute_interm_var_four8x8_avx2_intrin;
         g_simd                                    = 1;
         return 1;
     }
@@ -501,3 +511,63 @@ void ref_unpack_msb(const uint16_t *in16, uint32_t in_stride, uint8_t *out8, uin
 unsigned ref_sizeof_params(void) { return (unsigned)sizeof(SvtMeParams); }
 unsigned ref_sizeof_derive_input(void) { return (unsigned)sizeof(SvtMeDeriveInput); }
 unsigned ref_sizeof_out(void) { return (unsigned)sizeof(SvtMeOut); }
+
+/* ---- picture statistics: svt_aom_gathering_picture_statistics (pic_analysis_process.c:1560) on a built pyramid ----
+ * The function takes the sequence and picture control sets; the shells below hold the fields it reads
+ * (scs: calc_hist, calculate_variance, block_mean_calc_prec, the region counts, static_config.scene_change_detection /
+ * enable_adaptive_quantization / variance_octile; pcs: b64_total_count, b64_geom[].org_x/org_y) and the arrays it
+ * writes (variance, picture_histogram, average_intensity_per_region, avg_luma, pic_avg_variance). */
+int ref_picture_statistics(const RefPyramid *pyr, const SvtMeStatsParams *prm, SvtMeStatsOut *out) {
+    if (g_simd < 0) ref_set_simd(0);
+    if (prm->regions_per_width < 1 || prm->regions_per_width > MAX_NUMBER_OF_REGIONS_IN_WIDTH || prm->regions_per_height < 1 ||
+        prm->regions_per_height > MAX_NUMBER_OF_REGIONS_IN_HEIGHT)
+        return -1;
+    SequenceControlSet      *scs = (SequenceControlSet *)calloc(1, sizeof(*scs));
+    PictureParentControlSet *pcs = (PictureParentControlSet *)calloc(1, sizeof(*pcs));
+    if (!scs || !pcs) { free(scs); free(pcs); return -1; }
+    const uint32_t cols = (pyr->full.width + 63) / 64, rows = (pyr->full.height + 63) / 64, n_b64 = cols * rows;
+    const uint32_t n_var = prm->all_block_sizes ? 85 : 1;
+    scs->calc_hist                                      = prm->calc_hist;
+    scs->calculate_variance                             = prm->calculate_variance;
+    scs->block_mean_calc_prec                           = prm->block_mean_prec_sub ? BLOCK_MEAN_PREC_SUB : BLOCK_MEAN_PREC_FULL;
+    scs->picture_analysis_number_of_regions_per_width   = prm->regions_per_width;
+    scs->picture_analysis_number_of_regions_per_height  = prm->regions_per_height;
+    scs->static_config.scene_change_detection           = prm->scene_change_detection;
+    scs->static_config.enable_adaptive_quantization     = prm->all_block_sizes ? 1 : 0;
+    scs->static_config.variance_octile                  = 0;
+    pcs->b64_total_count = (uint16_t)n_b64;
+    pcs->b64_geom        = (B64Geom *)calloc(n_b64, sizeof(B64Geom));
+    pcs->variance        = (uint16_t **)calloc(n_b64, sizeof(uint16_t *));
+    uint16_t *var_rows   = (uint16_t *)calloc((size_t)n_b64 * n_var, sizeof(uint16_t));
+    uint32_t *hist       = (uint32_t *)calloc(4 * 4 * 256, sizeof(uint32_t));
+    uint32_t **hist_y[MAX_NUMBER_OF_REGIONS_IN_WIDTH];
+    uint32_t  *hist_p[MAX_NUMBER_OF_REGIONS_IN_WIDTH][MAX_NUMBER_OF_REGIONS_IN_HEIGHT];
+    int rc = -1;
+    if (pcs->b64_geom && pcs->variance && var_rows && hist) {
+        for (uint32_t b = 0; b < n_b64; ++b) {
+            pcs->b64_geom[b].org_x = (uint16_t)((b % cols) * 64);
+            pcs->b64_geom[b].org_y = (uint16_t)((b / cols) * 64);
+            pcs->variance[b]       = var_rows + (size_t)b * n_var;
+        }
+        for (int x = 0; x < MAX_NUMBER_OF_REGIONS_IN_WIDTH; ++x) {
+            for (int y = 0; y < MAX_NUMBER_OF_REGIONS_IN_HEIGHT; ++y) hist_p[x][y] = hist + ((size_t)x * 4 + y) * 256;
+            hist_y[x] = hist_p[x];
+        }
+        pcs->picture_histogram = hist_y;
+        EbPictureBufferDesc df, ds;
+        to_desc(&pyr->full, &df); to_desc(&pyr->sixteenth, &ds);
+        svt_aom_gathering_picture_statistics(scs, pcs, &df, &ds);
+        if (prm->calculate_variance && out->variance) memcpy(out->variance, var_rows, (size_t)n_b64 * n_var * sizeof(uint16_t));
+        if (out->pic_avg_variance) *out->pic_avg_variance = pcs->pic_avg_variance;
+        if (prm->calc_hist) {
+            if (out->picture_histogram) memcpy(out->picture_histogram, hist, 4 * 4 * 256 * sizeof(uint32_t));
+            if (out->average_intensity_per_region)
+                for (int x = 0; x < 4; ++x)
+                    for (int y = 0; y < 4; ++y) out->average_intensity_per_region[x * 4 + y] = pcs->average_intensity_per_region[x][y];
+        }
+        if (out->avg_luma) *out->avg_luma = pcs->avg_luma;
+        rc = 0;
+    }
+    free(hist); free(var_rows); free(pcs->variance); free(pcs->b64_geom); free(pcs); free(scs);
+    return rc;
+}

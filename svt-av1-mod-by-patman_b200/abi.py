@@ -104,6 +104,33 @@ class SvtMeOut(C.Structure):
     ]
 
 
+class SvtMeStatsParams(C.Structure):  # include/svtme_b200.h
+    _fields_ = [("calc_hist", C.c_uint8), ("calculate_variance", C.c_uint8), ("block_mean_prec_sub", C.c_uint8),
+                ("all_block_sizes", C.c_uint8), ("scene_change_detection", C.c_uint8), ("_pad", C.c_uint8 * 3),
+                ("regions_per_width", u32), ("regions_per_height", u32)]
+
+
+class SvtMeStatsOut(C.Structure):
+    _fields_ = [("variance", C.c_void_p), ("pic_avg_variance", C.c_void_p), ("picture_histogram", C.c_void_p),
+                ("average_intensity_per_region", C.c_void_p), ("avg_luma", C.c_void_p)]
+
+
+def alloc_stats_out(n_b64, params):
+    """Host arrays of one svtme_picture_statistics call (layouts of SvtMeStatsOut) and the struct pointing at them."""
+    import numpy as np
+    arrays = {
+        "variance": np.zeros((n_b64, 85 if params.all_block_sizes else 1), np.uint16),
+        "pic_avg_variance": np.zeros(1, np.uint16),
+        "picture_histogram": np.zeros((4, 4, 256), np.uint32),
+        "average_intensity_per_region": np.zeros((4, 4), np.uint64),
+        "avg_luma": np.zeros(1, np.uint64),
+    }
+    out = SvtMeStatsOut()
+    for name, a in arrays.items():
+        setattr(out, name, a.ctypes.data)
+    return out, arrays
+
+
 class SvtMeJob(C.Structure):
     _fields_ = [("params", SvtMeParams), ("cur", u64), ("refs", (u64 * MAX_REFS) * MAX_LISTS), ("out", SvtMeOut)]
 
@@ -211,6 +238,10 @@ def load_library():
         "svtme_last_work_ops": (C.c_int, [vp, P(u64)]),
         "svtme_last_phase_ms": (C.c_int, [vp, P(C.c_float), C.c_uint32]),
         "svtme_last_phase_work": (C.c_int, [vp, P(u64), C.c_uint32]),
+        "svtme_picture_statistics": (C.c_int, [vp, u64, P(SvtMeStatsParams), P(SvtMeStatsOut)]),
+        "svtme_pictures_statistics": (C.c_int, [vp, u32, P(u64), P(SvtMeStatsParams), P(SvtMeStatsOut)]),
+        "svtme_last_statistics_ms": (C.c_int, [vp, P(C.c_float), P(C.c_float)]),
+        "svtme_sizeof_stats_params": (u32, []),
         "svtme_set_search_timing": (C.c_int, [vp, C.c_int]),
         "svtme_last_search_ms": (C.c_int, [vp, P(C.c_float), C.c_uint32]),
         "svtme_measure_vabsdiff4_ginst_per_s": (C.c_double, []),

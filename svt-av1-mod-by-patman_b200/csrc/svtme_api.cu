@@ -93,6 +93,10 @@ struct SvtMeHandle {
     int n_streams = 2;
     cudaEvent_t origin_ev = nullptr; // svtme_debug_mark
     bool search_timing = false;      // svtme_set_search_timing
+    uint8_t *stats_dev = nullptr;    // svtme_picture_statistics: device scratch and its pinned mirror (created on first use)
+    uint8_t *stats_host = nullptr;
+    size_t stats_cap = 0;
+    cudaEvent_t stats_ev[3] = {}; // before the kernels, after them, after the download (svtme_last_statistics_ms)
     float span[3] = {0.f, 0.f, 0.f};  // last collected batch: pipeline start / end / download end, ms after the mark
     uint32_t submit_count = 0;
     void *x_states[SVTME_NS] = {};      // per extra compute stream: its own per-b64 scratch
@@ -254,6 +258,10 @@ extern "C" void svtme_close(SvtMeHandle *h) {
     cudaEventDestroy(h->build_ev);
     if (h->ext_ev) cudaEventDestroy(h->ext_ev);
     if (h->origin_ev) cudaEventDestroy(h->origin_ev);
+    cudaFree(h->stats_dev);
+    cudaFreeHost(h->stats_host);
+    for (cudaEvent_t e : h->stats_ev)
+        if (e) cudaEventDestroy(e);
     for (int k = 0; k < SVTME_LAUNCH_EV_RING; ++k) cudaEventDestroy(h->launch_ev[k]);
     cudaStreamDestroy(h->h2d_stream);
     cudaStreamDestroy(h->d2h_stream);
@@ -566,6 +574,87 @@ extern "C" int svtme_get_plane(SvtMeHandle *h, uint64_t pic_num, int level, uint
     CU(cudaStreamSynchronize(h->stream));
     return SVTME_OK;
 }
+
+// svt_aom_gathering_picture_statistics (pic_analysis_process.c:1560) of resident pictures; see svtme_b200.h
+extern "C" int svtme_pictures_statistics(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const SvtMeStatsParams *prm, SvtMeStatsOut *outs) {
+    if (!h || !prm || (n && (!pic_nums || !outs))) return fail(SVTME_ERR_INVALID, "svtme_pictures_statistics: null argument");
+    if (prm->calc_hist && (prm->regions_per_width < 1 || prm->regions_per_width > 4 || prm->regions_per_height < 1 || prm->regions_per_height > 4))
+        return fail(SVTME_ERR_INVALID, "svtme_pictures_statistics: 1..4 regions per width / height (MAX_NUMBER_OF_REGIONS_IN_WIDTH / _HEIGHT)");
+    for (uint32_t i = 0; i < n; ++i)
+        if ((prm->calculate_variance && !outs[i].variance) || !outs[i].pic_avg_variance || !outs[i].avg_luma ||
+            (prm->calc_hist && (!outs[i].picture_histogram || !outs[i].average_intensity_per_region)))
+            return fail(SVTME_ERR_INVALID, "svtme_pictures_statistics: an output array the parameters ask for is null");
+    if (!n) return SVTME_OK;
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(cudaSetDevice(h->device));
+    std::vector<int> slot(n);
+    for (uint32_t i = 0; i < n; ++i)
+        if ((slot[i] = find_slot(h, pic_nums[i], false)) < 0) return fail(SVTME_ERR_NOTFOUND, "svtme_pictures_statistics: picture not resident");
+    const int n_b64 = (int)(h->b64_cols * h->b64_rows);
+    const size_t one = svtme_stats_scratch_bytes(n_b64), bytes = one * n;
+    const size_t items_off = (bytes + 255) & ~(size_t)255, host_bytes = items_off + svtme_stats_item_bytes() * n;
+    if (host_bytes > h->stats_cap) { // scratch and its pinned mirror (+ the item array) grow to the largest batch seen
+        CU(cudaStreamSynchronize(h->stream));
+        cudaFree(h->stats_dev);
+        cudaFreeHost(h->stats_host);
+        h->stats_dev = h->stats_host = nullptr;
+        h->stats_cap = 0;
+        CU(cudaMalloc(&h->stats_dev, host_bytes)); // (same layout on both sides: results, then the item array)
+        const cudaError_t e = cudaMallocHost(&h->stats_host, host_bytes);
+        if (e != cudaSuccess) {
+            cudaFree(h->stats_dev);
+            h->stats_dev = nullptr;
+            CU(e);
+        }
+        h->stats_cap = host_bytes;
+    }
+    if (h->build_recorded) CU(cudaStreamWaitEvent(h->stream, h->build_ev, 0));
+    size_t off_hist = 0, off_tail = 0;
+    const size_t n_var = (size_t)n_b64 * (prm->all_block_sizes ? 85 : 1) * sizeof(uint16_t);
+    for (uint32_t i = 0; i < n; ++i) svtme_stats_set_item(h->stats_host + items_off, (int)i, h->slots[slot[i]].pyr);
+    if (!h->stats_ev[0])
+        for (cudaEvent_t &e : h->stats_ev) CU(cudaEventCreate(&e));
+    CU(cudaEventRecord(h->stats_ev[0], h->stream));
+    // the item array goes to the device with one small copy (read through the mapped host pointer it cost every CTA a PCIe round trip)
+    CU(cudaMemcpyAsync(h->stats_dev + items_off, h->stats_host + items_off, svtme_stats_item_bytes() * n, cudaMemcpyHostToDevice, h->stream));
+    g_svtme_launches += svtme_launch_picture_statistics(h->slots[slot[0]].pyr, h->stats_dev + items_off, (int)n, *prm, h->stats_dev, &off_hist,
+                                                        &off_tail, h->stream);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(h->stats_ev[1], h->stream));
+    if (prm->calculate_variance)
+        CU(cudaMemcpyAsync(h->stats_host, h->stats_dev, bytes, cudaMemcpyDeviceToHost, h->stream)); // rows, bins and tails of all n in one copy
+    else
+        for (uint32_t i = 0; i < n; ++i)
+            CU(cudaMemcpyAsync(h->stats_host + one * i + off_hist, h->stats_dev + one * i + off_hist, one - off_hist, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaEventRecord(h->stats_ev[2], h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    for (uint32_t i = 0; i < n; ++i) {
+        const uint8_t *src = h->stats_host + one * i;
+        SvtMeStatsOut &o = outs[i];
+        if (prm->calculate_variance) memcpy(o.variance, src, n_var);
+        if (prm->calc_hist) memcpy(o.picture_histogram, src + off_hist, 16 * 256 * sizeof(uint32_t));
+        unsigned long long avg_int[16], avg_luma = 0;
+        svtme_stats_tail_unpack(src + off_tail, avg_int, &avg_luma, o.pic_avg_variance);
+        if (prm->calc_hist)
+            for (int k = 0; k < 16; ++k) o.average_intensity_per_region[k] = avg_int[k];
+        *o.avg_luma = avg_luma;
+    }
+    return SVTME_OK;
+}
+extern "C" int svtme_picture_statistics(SvtMeHandle *h, uint64_t pic_num, const SvtMeStatsParams *prm, SvtMeStatsOut *out) {
+    if (!out) return fail(SVTME_ERR_INVALID, "svtme_picture_statistics: null argument");
+    return svtme_pictures_statistics(h, 1, &pic_num, prm, out);
+}
+extern "C" int svtme_last_statistics_ms(SvtMeHandle *h, float *kernels_ms, float *download_ms) {
+    if (!h || !kernels_ms || !download_ms) return fail(SVTME_ERR_INVALID, "svtme_last_statistics_ms: null argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->stats_ev[0]) return fail(SVTME_ERR_NOTFOUND, "svtme_last_statistics_ms: no statistics call yet");
+    CU(cudaSetDevice(h->device));
+    CU(cudaEventElapsedTime(kernels_ms, h->stats_ev[0], h->stats_ev[1]));
+    CU(cudaEventElapsedTime(download_ms, h->stats_ev[1], h->stats_ev[2]));
+    return SVTME_OK;
+}
+extern "C" uint32_t svtme_sizeof_stats_params(void) { return (uint32_t)sizeof(SvtMeStatsParams); }
 
 extern "C" int svtme_sync(SvtMeHandle *h) {
     if (!h) return fail(SVTME_ERR_INVALID, "svtme_sync: null handle");

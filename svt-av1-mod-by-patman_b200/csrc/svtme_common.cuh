@@ -111,4 +111,12 @@ void svtme_launch_fullpel_test(const uint8_t *d_src, int src_stride, const uint8
 cudaError_t svtme_launch_fullpel_batch(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride,
                                        const SvtMeFullpelItem *d_items, int n, int sub_sad, uint32_t *d_best_sad, uint32_t *d_best_mv,
                                        cudaStream_t st);
+// picture statistics (svtme_stats.cu)
+size_t svtme_stats_scratch_bytes(int n_b64);
+size_t svtme_stats_item_bytes();
+void svtme_stats_set_item(void *items_host, int i, const DevPyramid &pyr);
+int svtme_launch_picture_statistics(const DevPyramid &geom, const void *items, int n, const SvtMeStatsParams &prm, uint8_t *scratch,
+                                    size_t *off_hist, size_t *off_tail, cudaStream_t st);
+size_t svtme_stats_tail_bytes();
+void svtme_stats_tail_unpack(const void *tail_host, unsigned long long *avg_intensity16, unsigned long long *avg_luma, uint16_t *pic_avg_variance);
 extern unsigned long long g_svtme_launches;

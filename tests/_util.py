@@ -92,6 +92,24 @@ def cpu_me_picture(which, params, cur, refs, deep=True, rows=None):
     return arrays
 
 
+def stats_params(calc_hist=1, calculate_variance=1, prec_sub=1, all_sizes=1, scd=0, regions=(4, 4)):
+    p = abi.SvtMeStatsParams()
+    p.calc_hist, p.calculate_variance, p.block_mean_prec_sub = calc_hist, calculate_variance, prec_sub
+    p.all_block_sizes, p.scene_change_detection = all_sizes, scd
+    p.regions_per_width, p.regions_per_height = regions
+    return p
+
+
+def cpu_picture_statistics(which, pyr, params):
+    """svt_aom_gathering_picture_statistics on a CpuPyramid: the oracle restatement ('orc') or the compiled reference ('ref')."""
+    lib = oracle_lib() if which == "orc" else ref_lib()
+    w, h = pyr.pyr.full.width, pyr.pyr.full.height
+    out, arrays = abi.alloc_stats_out(((w + 63) // 64) * ((h + 63) // 64), params)
+    rc = getattr(lib, which + "_picture_statistics")(C.byref(pyr.pyr), C.byref(params), C.byref(out))
+    assert rc == 0
+    return arrays
+
+
 derive_input, finish_params = me_host.derive_input, me_host.finish_params
 
 

@@ -11,7 +11,7 @@ sys.path.insert(0, os.path.dirname(HERE))
 import _util as U  # noqa: E402
 
 CASES = [((192, 136), dict()), ((192, 136), dict(prec_sub=0)), ((328, 200), dict(all_sizes=0)), ((328, 200), dict(scd=1)),
-         ((128, 64), dict(regions=(1, 1))), ((640, 360), dict(regions=(3, 2), scd=1)), ((640, 360), dict(prec_sub=0, regions=(2, 4))),
+         ((128, 64), dict(regions=(1, 1))), ((264, 136), dict(regions=(3, 2), scd=1)), ((264, 136), dict(prec_sub=0, regions=(2, 4))),
          ((328, 200), dict(calc_hist=0)), ((192, 136), dict(calculate_variance=0))]
 out = {"n_cases": np.int64(len(CASES))}
 assert U.ref_lib() is not None

@@ -143,3 +143,36 @@ EbErrorType svtme_hook_tf_me(SvtMeHandle *svtme, SequenceControlSet *scs, Pictur
     /* per block: hme_sad[b][0][0] < prm.tf_me_exit_th  <=>  the reference returned early and set tf_use_pred_64x64_only_th = ~0 */
     return svtme_run_picture(svtme, &prm, centre->picture_number, refs, &out) == SVTME_OK ? EB_ErrorNone : EB_ErrorInsufficientResources;
 }
+
+/* H6 — picture statistics (Codec/pic_analysis_process.c:2137, right after the pyramid): in place of
+ * svt_aom_gathering_picture_statistics(scs, pcs, input_padded_pic, sixteenth). With it the 1/16 plane no longer has to come
+ * back to the host for this function (H1 keeps the read-back only while the DG detector wants the planes). `var_rows` /
+ * `hist` are flat arrays the patch keeps next to pcs->variance / pcs->picture_histogram (those are arrays of row pointers). */
+EbErrorType svtme_hook_statistics(SvtMeHandle *svtme, const SequenceControlSet *scs, PictureParentControlSet *pcs, uint16_t *var_rows,
+                                  uint32_t *hist /* [4][4][256] */) {
+    SvtMeStatsParams sp;
+    memset(&sp, 0, sizeof(sp));
+    sp.calc_hist              = scs->calc_hist;
+    sp.calculate_variance     = scs->calculate_variance;
+    sp.block_mean_prec_sub    = scs->block_mean_calc_prec == BLOCK_MEAN_PREC_SUB;
+    sp.all_block_sizes        = scs->static_config.enable_adaptive_quantization == 1 || scs->static_config.variance_octile;
+    sp.scene_change_detection = scs->static_config.scene_change_detection != 0;
+    sp.regions_per_width      = scs->picture_analysis_number_of_regions_per_width;
+    sp.regions_per_height     = scs->picture_analysis_number_of_regions_per_height;
+    uint64_t intensity[16];
+    SvtMeStatsOut so;
+    memset(&so, 0, sizeof(so));
+    so.variance = var_rows;  so.pic_avg_variance = &pcs->pic_avg_variance;  so.picture_histogram = hist;
+    so.average_intensity_per_region = intensity;  so.avg_luma = &pcs->avg_luma;
+    if (svtme_picture_statistics(svtme, pcs->picture_number, &sp, &so) != SVTME_OK) return EB_ErrorInsufficientResources;
+    const uint32_t n_var = sp.all_block_sizes ? 85 : 1;
+    if (sp.calculate_variance)
+        for (uint32_t b = 0; b < pcs->b64_total_count; ++b) memcpy(pcs->variance[b], var_rows + (size_t)b * n_var, n_var * sizeof(uint16_t));
+    if (sp.calc_hist)
+        for (uint32_t x = 0; x < sp.regions_per_width; ++x)
+            for (uint32_t y = 0; y < sp.regions_per_height; ++y) {
+                memcpy(pcs->picture_histogram[x][y], hist + ((size_t)x * 4 + y) * 256, 256 * sizeof(uint32_t));
+                pcs->average_intensity_per_region[x][y] = intensity[x * 4 + y];
+            }
+    return EB_ErrorNone;
+}

@@ -278,9 +278,25 @@ int svtme_picture_statistics(SvtMeHandle *h, uint64_t pic_num, const SvtMeStatsP
 /* n pictures, one launch sequence, one download (the picture-analysis kernel of the reference handles one picture per
  * call; a look-ahead window's worth is the batch here). */
 int svtme_pictures_statistics(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const SvtMeStatsParams *params, SvtMeStatsOut *outs);
-/* Profiling aid: device milliseconds of the kernels and of the result download of the last statistics call. */
+/* Profiling aid: device milliseconds of the kernels and of the result download of the last svtme_picture(s)_statistics or
+ * svtme_dg_detector_hme call. */
 int svtme_last_statistics_ms(SvtMeHandle *h, float *kernels_ms, float *download_ms);
 uint32_t svtme_sizeof_stats_params(void);
+
+/* ---- dynamic-GOP detector HME between two resident pictures ---------------------------------
+ * Replaces dg_detector_hme_level0 (Codec/pd_process.c:491-589) over ALL segments of the picture (the reference runs it
+ * per ME segment from the ME kernel's TASK_DG_DETECTOR_HME branch and adds into the same metrics under a mutex): per
+ * b64 one early_hme_b64 (:389-487) = full-SAD svt_sad_loop_kernel of the 16x16 block of the source's 1/16 picture over a
+ * window of 16 x 16 (<= 360p), 64 x 64 (<= 480p) or 128 x 128 positions of `ref_pic`'s 1/16 plane, clipped like HME
+ * level 0; metrics as in DGDetectorMetrics (pcs.h:696-702, without seg_completed). input_resolution = the
+ * EbInputResolution value of ppcs->input_resolution (0 = 240p range ... 6 = 8K range, definitions.h:2086-2094). */
+typedef struct SvtMeDgMetrics {
+    uint64_t tot_dist;       /* sum of the best SADs */
+    uint32_t tot_cplx;       /* b64 whose best SAD exceeds 16 * 16 * 30 */
+    uint32_t tot_active;     /* b64 with a non-zero vector */
+    int32_t sum_in_vectors;  /* vectors pointing towards (+) / away from (-) the picture centre, per component */
+} SvtMeDgMetrics;
+int svtme_dg_detector_hme(SvtMeHandle *h, uint64_t src_pic, uint64_t ref_pic, uint32_t input_resolution, SvtMeDgMetrics *out);
 
 /* Open-loop ME of one picture against refs[list][idx] (picture numbers previously put).
  * Replaces the b64 loop of me_process.c:174-289 calling svt_aom_motion_estimation_b64

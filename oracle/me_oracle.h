@@ -100,6 +100,8 @@ int orc_me_picture_rows(const SvtMeParams *p, const OrcPyramid *cur,
 /* svt_aom_gathering_picture_statistics (pic_analysis_process.c:1560) on a built pyramid: variance of the padded luma,
  * histogram / intensities of the 1/16 plane. `out` arrays as in svtme_picture_statistics. */
 int orc_picture_statistics(const OrcPyramid *pyr, const SvtMeStatsParams *prm, SvtMeStatsOut *out);
+/* dg_detector_hme_level0 (pd_process.c:491) over all segments: src's 16x16 blocks searched in ref's 1/16 plane. */
+int orc_dg_detector_hme(const OrcPyramid *src, const OrcPyramid *ref, uint32_t input_resolution, SvtMeDgMetrics *out);
 
 #ifdef __cplusplus
 }

@@ -119,3 +119,53 @@ int orc_picture_statistics(const OrcPyramid *pyr, const SvtMeStatsParams *prm, S
         *out->pic_avg_variance = 0;
     return 0;
 }
+
+/* ---- dynamic-GOP detector HME: dg_detector_hme_level0 over all segments (pd_process.c:491-589) ----
+ * early_hme_b64 (:389-487): the clipping of hme_level_0 with the pad limits org - 1 = 15 of the reference's 1/16 planes,
+ * one full-SAD svt_sad_loop_kernel, vector x 4. */
+int orc_dg_detector_hme(const OrcPyramid *src, const OrcPyramid *ref, uint32_t input_resolution, SvtMeDgMetrics *out) {
+    const OrcPlane *sp = &src->sixteenth, *rp = &ref->sixteenth;
+    const int16_t S = input_resolution <= 1 ? 16 : (input_resolution <= 2 ? 64 : 128); /* (:497-498) */
+    const uint32_t cols = (src->full.width + 63) / 64, rows = (src->full.height + 63) / 64;
+    memset(out, 0, sizeof(*out));
+    uint64_t best = (uint64_t)~0;
+    int16_t cx = 0, cy = 0; /* sr_center lives across the b64 loop (:501) */
+    for (uint32_t by = 0; by < rows; ++by)
+        for (uint32_t bx = 0; bx < cols; ++bx) {
+            const int16_t org_x = (int16_t)(bx * 64) >> 2, org_y = (int16_t)(by * 64) >> 2;
+            int16_t sa_w = (int16_t)((S + 7) & ~0x07), sa_h = S;
+            const int16_t pad_w = (int16_t)rp->org_x - 1, pad_h = (int16_t)rp->org_y - 1;
+            const int16_t W = (int16_t)rp->width, H = (int16_t)rp->height;
+            int16_t ox = -(int16_t)(sa_w >> 1), oy = -(int16_t)(sa_h >> 1);
+            if ((org_x + ox) < -pad_w) {
+                ox = -pad_w - org_x;
+                sa_w = sa_w - (-pad_w - (org_x + ox));
+            }
+            if ((org_x + ox) > W - 1) ox = ox - ((org_x + ox) - (W - 1));
+            if ((org_x + ox + sa_w) > W) sa_w = (int16_t)((1 > sa_w - ((org_x + ox + sa_w) - W)) ? 1 : sa_w - ((org_x + ox + sa_w) - W));
+            sa_w = (sa_w < 8) ? sa_w : sa_w & ~0x07;
+            if ((org_y + oy) < -pad_h) {
+                oy = -pad_h - org_y;
+                sa_h = sa_h - (-pad_h - (org_y + oy));
+            }
+            if ((org_y + oy) > H - 1) oy = oy - ((org_y + oy) - (H - 1));
+            if (org_y + oy + sa_h > H) sa_h = (int16_t)((1 > sa_h - ((org_y + oy + sa_h) - H)) ? 1 : sa_h - ((org_y + oy + sa_h) - H));
+            uint8_t *s = sp->buffer_y + (size_t)(sp->org_y + org_y) * sp->stride_y + sp->org_x + org_x;
+            uint8_t *r = rp->buffer_y + (size_t)((int)rp->org_y + org_y + oy) * rp->stride_y + (int)rp->org_x + org_x + ox;
+            orc_sad_loop_kernel(s, sp->stride_y, r, rp->stride_y, 16, 16, &best, &cx, &cy, rp->stride_y, 0, sa_w, sa_h);
+            cx = (int16_t)((int16_t)(cx + ox) * 4);
+            cy = (int16_t)((int16_t)(cy + oy) * 4);
+            out->tot_dist += best;
+            out->tot_cplx += best > 16 * 16 * 30;
+            out->tot_active += (cx != 0 || cy != 0);
+            if (by < rows / 2)
+                out->sum_in_vectors += cy > 0 ? -1 : (cy < 0 ? 1 : 0);
+            else if (by > rows / 2)
+                out->sum_in_vectors += cy > 0 ? 1 : (cy < 0 ? -1 : 0);
+            if (bx < cols / 2)
+                out->sum_in_vectors += cx > 0 ? -1 : (cx < 0 ? 1 : 0);
+            else if (bx > cols / 2)
+                out->sum_in_vectors += cx > 0 ? 1 : (cx < 0 ? -1 : 0);
+        }
+    return 0;
+}

@@ -9,6 +9,7 @@
  *   svt_aom_downsample_filtering_input_picture  Source/Lib/Codec/pic_analysis_process.c:1922
  *   svt_aom_generate_padding           Source/Lib/Codec/pic_operators.c:338
  *   svt_aom_gathering_picture_statistics  Source/Lib/Codec/pic_analysis_process.c:1560
+ *   dg_detector_hme_level0             Source/Lib/Codec/pd_process.c:491
  *   RTCD pointers                      Source/Lib/Codec/aom_dsp_rtcd.h:776,838-860
  */
 #include <stdlib.h>
@@ -570,4 +571,42 @@ int ref_picture_statistics(const RefPyramid *pyr, const SvtMeStatsParams *prm, S
     }
     free(hist); free(var_rows); free(pcs->variance); free(pcs->b64_geom); free(pcs); free(scs);
     return rc;
+}
+
+/* ---- dynamic-GOP detector HME: dg_detector_hme_level0 (pd_process.c:491) with ONE segment covering the picture ----
+ * The function takes its pictures from ppcs->pa_ref_pic_wrapper / ppcs->dg_detector->ref_pic->pa_ref_pic_wrapper and adds
+ * into ppcs->dg_detector->metrics under a mutex; the three thread primitives it calls are no-ops here (one thread). */
+EbErrorType svt_block_on_mutex(EbHandle mutex_handle) { (void)mutex_handle; return EB_ErrorNone; }
+EbErrorType svt_release_mutex(EbHandle mutex_handle) { (void)mutex_handle; return EB_ErrorNone; }
+EbErrorType svt_post_semaphore(EbHandle semaphore_handle) { (void)semaphore_handle; return EB_ErrorNone; }
+void dg_detector_hme_level0(struct PictureParentControlSet *ppcs, uint32_t seg_idx); /* pd_process.c:491 */
+
+int ref_dg_detector_hme(const RefPyramid *src, const RefPyramid *ref, uint32_t input_resolution, SvtMeDgMetrics *out) {
+    if (g_simd < 0) ref_set_simd(0);
+    PictureParentControlSet *pcs = (PictureParentControlSet *)calloc(1, sizeof(*pcs)), *rpcs = (PictureParentControlSet *)calloc(1, sizeof(*rpcs));
+    SequenceControlSet      *scs = (SequenceControlSet *)calloc(1, sizeof(*scs));
+    if (!pcs || !rpcs || !scs) { free(pcs); free(rpcs); free(scs); return -1; }
+    EbPictureBufferDesc  ds, dr;
+    EbPaReferenceObject  pa_s, pa_r;
+    EbObjectWrapper      w_s, w_r;
+    DGDetectorSeg        dg;
+    memset(&pa_s, 0, sizeof(pa_s)); memset(&pa_r, 0, sizeof(pa_r)); memset(&w_s, 0, sizeof(w_s)); memset(&w_r, 0, sizeof(w_r));
+    memset(&dg, 0, sizeof(dg));
+    to_desc(&src->sixteenth, &ds); to_desc(&ref->sixteenth, &dr);
+    pa_s.sixteenth_downsampled_picture_ptr = &ds;  pa_r.sixteenth_downsampled_picture_ptr = &dr;
+    w_s.object_ptr = &pa_s;  w_r.object_ptr = &pa_r;
+    pcs->pa_ref_pic_wrapper = &w_s;  rpcs->pa_ref_pic_wrapper = &w_r;
+    dg.ref_pic = rpcs;
+    pcs->dg_detector = &dg;
+    pcs->scs = scs;
+    scs->b64_size = 64;
+    pcs->input_resolution = (EbInputResolution)input_resolution;
+    pcs->aligned_width = (uint16_t)src->full.width;  pcs->aligned_height = (uint16_t)src->full.height;
+    pcs->me_segments_column_count = 1;  pcs->me_segments_row_count = 1;
+    dg_detector_hme_level0(pcs, 0);
+    out->tot_dist = dg.metrics.tot_dist;  out->tot_cplx = dg.metrics.tot_cplx;  out->tot_active = dg.metrics.tot_active;
+    out->sum_in_vectors = dg.metrics.sum_in_vectors;
+    const int done = dg.metrics.seg_completed == 1;
+    free(pcs); free(rpcs); free(scs);
+    return done ? 0 : -1;
 }

@@ -104,6 +104,10 @@ class SvtMeOut(C.Structure):
     ]
 
 
+class SvtMeDgMetrics(C.Structure):  # include/svtme_b200.h
+    _fields_ = [("tot_dist", u64), ("tot_cplx", u32), ("tot_active", u32), ("sum_in_vectors", C.c_int32)]
+
+
 class SvtMeStatsParams(C.Structure):  # include/svtme_b200.h
     _fields_ = [("calc_hist", C.c_uint8), ("calculate_variance", C.c_uint8), ("block_mean_prec_sub", C.c_uint8),
                 ("all_block_sizes", C.c_uint8), ("scene_change_detection", C.c_uint8), ("_pad", C.c_uint8 * 3),
@@ -238,6 +242,7 @@ def load_library():
         "svtme_last_work_ops": (C.c_int, [vp, P(u64)]),
         "svtme_last_phase_ms": (C.c_int, [vp, P(C.c_float), C.c_uint32]),
         "svtme_last_phase_work": (C.c_int, [vp, P(u64), C.c_uint32]),
+        "svtme_dg_detector_hme": (C.c_int, [vp, u64, u64, u32, P(SvtMeDgMetrics)]),
         "svtme_picture_statistics": (C.c_int, [vp, u64, P(SvtMeStatsParams), P(SvtMeStatsOut)]),
         "svtme_pictures_statistics": (C.c_int, [vp, u32, P(u64), P(SvtMeStatsParams), P(SvtMeStatsOut)]),
         "svtme_last_statistics_ms": (C.c_int, [vp, P(C.c_float), P(C.c_float)]),

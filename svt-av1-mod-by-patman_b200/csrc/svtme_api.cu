@@ -96,6 +96,7 @@ struct SvtMeHandle {
     uint8_t *stats_dev = nullptr;    // svtme_picture_statistics: device scratch and its pinned mirror (created on first use)
     uint8_t *stats_host = nullptr;
     size_t stats_cap = 0;
+    void *dg_dev = nullptr, *dg_host = nullptr; // svtme_dg_detector_hme: metric accumulators and their pinned mirror
     cudaEvent_t stats_ev[3] = {}; // before the kernels, after them, after the download (svtme_last_statistics_ms)
     float span[3] = {0.f, 0.f, 0.f};  // last collected batch: pipeline start / end / download end, ms after the mark
     uint32_t submit_count = 0;
@@ -260,6 +261,8 @@ extern "C" void svtme_close(SvtMeHandle *h) {
     if (h->origin_ev) cudaEventDestroy(h->origin_ev);
     cudaFree(h->stats_dev);
     cudaFreeHost(h->stats_host);
+    cudaFree(h->dg_dev);
+    cudaFreeHost(h->dg_host);
     for (cudaEvent_t e : h->stats_ev)
         if (e) cudaEventDestroy(e);
     for (int k = 0; k < SVTME_LAUNCH_EV_RING; ++k) cudaEventDestroy(h->launch_ev[k]);
@@ -572,6 +575,37 @@ extern "C" int svtme_get_plane(SvtMeHandle *h, uint64_t pic_num, int level, uint
     CU(cudaMemcpy2DAsync(dst, dst_stride, pl.at(-(int)pad, -(int)pad), pl.stride, pl.width + 2 * pad, pl.height + 2 * pad,
                          cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
+    return SVTME_OK;
+}
+
+// dg_detector_hme_level0 (pd_process.c:491) between two resident pictures; see svtme_b200.h
+extern "C" int svtme_dg_detector_hme(SvtMeHandle *h, uint64_t src_pic, uint64_t ref_pic, uint32_t input_resolution, SvtMeDgMetrics *out) {
+    if (!h || !out) return fail(SVTME_ERR_INVALID, "svtme_dg_detector_hme: null argument");
+    if (input_resolution > 6) return fail(SVTME_ERR_INVALID, "svtme_dg_detector_hme: input_resolution is an EbInputResolution value (0..6)");
+    std::lock_guard<std::mutex> lk(h->mu);
+    CU(cudaSetDevice(h->device));
+    const int ss = find_slot(h, src_pic, false), sr = find_slot(h, ref_pic, false);
+    if (ss < 0 || sr < 0) return fail(SVTME_ERR_NOTFOUND, "svtme_dg_detector_hme: picture not resident");
+    if (!h->dg_dev) {
+        CU(cudaMalloc(&h->dg_dev, 256));
+        const cudaError_t e = cudaMallocHost(&h->dg_host, 256);
+        if (e != cudaSuccess) {
+            cudaFree(h->dg_dev);
+            h->dg_dev = nullptr;
+            CU(e);
+        }
+    }
+    if (h->build_recorded) CU(cudaStreamWaitEvent(h->stream, h->build_ev, 0));
+    const int sa = input_resolution <= 1 ? 16 : (input_resolution <= 2 ? 64 : 128); // (:497-498)
+    if (!h->stats_ev[0])
+        for (cudaEvent_t &e : h->stats_ev) CU(cudaEventCreate(&e));
+    CU(cudaEventRecord(h->stats_ev[0], h->stream));
+    CU(svtme_launch_dg_hme(h->slots[ss].pyr.lvl[2], h->slots[sr].pyr.lvl[2], (int)h->b64_cols, (int)h->b64_rows, sa, h->dg_dev, h->stream));
+    CU(cudaEventRecord(h->stats_ev[1], h->stream));
+    CU(cudaMemcpyAsync(h->dg_host, h->dg_dev, svtme_dg_acc_bytes(), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaEventRecord(h->stats_ev[2], h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    svtme_dg_acc_unpack(h->dg_host, out);
     return SVTME_OK;
 }
 

@@ -111,6 +111,10 @@ void svtme_launch_fullpel_test(const uint8_t *d_src, int src_stride, const uint8
 cudaError_t svtme_launch_fullpel_batch(const uint8_t *d_src, int src_stride, const uint8_t *d_ref, int ref_stride,
                                        const SvtMeFullpelItem *d_items, int n, int sub_sad, uint32_t *d_best_sad, uint32_t *d_best_mv,
                                        cudaStream_t st);
+// dynamic-GOP detector HME (svtme_stage.cu)
+size_t svtme_dg_acc_bytes();
+void svtme_dg_acc_unpack(const void *host, SvtMeDgMetrics *out);
+cudaError_t svtme_launch_dg_hme(const DevPlane &src16, const DevPlane &ref16, int b64_cols, int b64_rows, int sa, void *acc, cudaStream_t st);
 // picture statistics (svtme_stats.cu)
 size_t svtme_stats_scratch_bytes(int n_b64);
 size_t svtme_stats_item_bytes();

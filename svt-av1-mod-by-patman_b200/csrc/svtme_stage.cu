@@ -878,6 +878,8 @@ SvtmeStageFlags svtme_stage_flags(const SvtMeParams &p) {
 
 // cudaFuncSetAttribute acts on the CURRENT device: once per device, under a lock (a process may open handles on several
 // GPUs and launch from several ME threads).
+struct DgAcc;
+__global__ void dg_hme_kernel(DevPlane src16, DevPlane ref16, int cols, int rows, int sa, DgAcc *acc); // (defined with the DG-detector section below)
 void svtme_configure_stage_kernels() {
     static std::mutex mu;
     static bool done[64] = {};
@@ -886,6 +888,7 @@ void svtme_configure_stage_kernels() {
     std::lock_guard<std::mutex> lk(mu);
     if (done[dev]) return;
     cudaFuncSetAttribute(engine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EngSmem));
+    cudaFuncSetAttribute(dg_hme_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EngSmem));
     cudaFuncSetAttribute(strip_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(StripSmem));
     cudaFuncSetAttribute(strip_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(StripSmem));
     cudaFuncSetAttribute(int_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(IntSmem<false>));
@@ -1029,6 +1032,82 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
     mark(); // 7: candidates + statistics
     if (sev_mask) *sev_mask = smask;
     g_svtme_launches += 8 - fused + 1 + launches; // (the state clear counts itself)
+}
+
+// ---------------------------------------------------------------- dynamic-GOP detector HME
+// dg_detector_hme_level0 (Codec/pd_process.c:491-589): for every b64 of the picture one early_hme_b64 (:389-487) — a
+// full-SAD svt_sad_loop_kernel of the 16x16 block of the 1/16 SOURCE picture over an S x S window of the 1/16 plane of
+// another picture (S = 16 / 64 / 128 by input resolution), clipped like hme_level_0 (block may move 15 px into the pad) —
+// and four running metrics. One CTA per b64, the same engine as every HME round (hme_search_multi: the 128 x 128 window
+// takes its tiled path); the metrics are integer sums, so atomics give the reference's totals whatever the order.
+struct DgAcc { // zero-filled by the host before the launch
+    unsigned long long tot_dist;
+    uint32_t tot_cplx, tot_active;
+    int sum_in_vectors;
+    uint32_t _pad[3]; // 32 bytes: the clear works in 16-byte units
+};
+static_assert(sizeof(DgAcc) % 16 == 0, "svtme_launch_zero_fill clears whole 16-byte units");
+__global__ void __launch_bounds__(SVTME_HME_THREADS, SVTME_HME_CTAS_PER_SM) dg_hme_kernel(DevPlane src16, DevPlane ref16, int cols, int rows,
+                                                                                         int sa, DgAcc *acc) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    EngSmem *sm = reinterpret_cast<EngSmem *>(smem_raw);
+    const int tid = threadIdx.x, bx = blockIdx.x % cols, by = blockIdx.x / cols;
+    const int16_t org_x = (int16_t)((bx * 64) >> 2), org_y = (int16_t)((by * 64) >> 2);
+    for (int i = tid; i < 16; i += SVTME_HME_THREADS) // the 16x16 source block, rows of 16 bytes (16-byte aligned in the plane)
+        *reinterpret_cast<uint4 *>(&sm->src[i * 16]) = *reinterpret_cast<const uint4 *>(src16.at(org_x, org_y + i));
+    if (tid == 0) {
+        int16_t w = (int16_t)((sa + 7) & ~7), h = (int16_t)sa, ox = (int16_t)(-(w >> 1)), oy = (int16_t)(-(h >> 1));
+        clip_hme(org_x, org_y, (int16_t)ref16.width, (int16_t)ref16.height, 15, 15, w, h, ox, oy); // (:408-448: the clipping of hme_level_0)
+        HJob &j = sm->jobs[0];
+        j.ref = ref16.at(org_x + ox, org_y + oy);
+        j.stride = ref16.stride;
+        j.sa_w = w;
+        j.sa_h = h;
+        j.skip_even = 0;
+        j.key = HME_KEY_INIT;
+        sm->cur.org_x = ox; // (scratch: the applied origin, for the metrics below)
+        sm->cur.org_y = oy;
+    }
+    __syncthreads();
+    const HBlk blk = make_hblk(sm->src, 16, 16, 16, 1); // FULL_SAD_SEARCH (:507): every row
+    hme_search_multi(blk, sm->jobs, 1, &sm->plan, sm->arena);
+    if (tid == 0) {
+        const unsigned long long key = sm->jobs[0].key;
+        const unsigned long long sad = key >> 32;
+        const int16_t col = (int16_t)((int16_t)((int16_t)(key & 0xffff) + (int16_t)sm->cur.org_x) * 4);
+        const int16_t row = (int16_t)((int16_t)((int16_t)((key >> 16) & 0xffff) + (int16_t)sm->cur.org_y) * 4);
+        int in = 0; // (:548-577) does the vector point towards the picture centre?
+        if (by < rows / 2)
+            in += row > 0 ? -1 : (row < 0 ? 1 : 0);
+        else if (by > rows / 2)
+            in += row > 0 ? 1 : (row < 0 ? -1 : 0);
+        if (bx < cols / 2)
+            in += col > 0 ? -1 : (col < 0 ? 1 : 0);
+        else if (bx > cols / 2)
+            in += col > 0 ? 1 : (col < 0 ? -1 : 0);
+        atomicAdd(&acc->tot_dist, sad);
+        if (sad > 16 * 16 * 30) atomicAdd(&acc->tot_cplx, 1u);
+        if (col != 0 || row != 0) atomicAdd(&acc->tot_active, 1u);
+        if (in) atomicAdd(&acc->sum_in_vectors, in);
+    }
+}
+
+size_t svtme_dg_acc_bytes() { return sizeof(DgAcc); }
+void svtme_dg_acc_unpack(const void *host, SvtMeDgMetrics *out) {
+    const DgAcc *a = static_cast<const DgAcc *>(host);
+    out->tot_dist = a->tot_dist;
+    out->tot_cplx = a->tot_cplx;
+    out->tot_active = a->tot_active;
+    out->sum_in_vectors = a->sum_in_vectors;
+}
+// acc: 16-byte aligned device scratch of svtme_dg_acc_bytes(); cleared here
+cudaError_t svtme_launch_dg_hme(const DevPlane &src16, const DevPlane &ref16, int b64_cols, int b64_rows, int sa, void *acc, cudaStream_t st) {
+    svtme_configure_stage_kernels();
+    cudaError_t e = svtme_launch_zero_fill(acc, sizeof(DgAcc), st);
+    if (e != cudaSuccess) return e;
+    dg_hme_kernel<<<b64_cols * b64_rows, SVTME_HME_THREADS, sizeof(EngSmem), st>>>(src16, ref16, b64_cols, b64_rows, sa, static_cast<DgAcc *>(acc));
+    ++g_svtme_launches;
+    return cudaGetLastError();
 }
 
 // ---------------------------------------------------------------- kernel-test entry points

@@ -110,6 +110,15 @@ def cpu_picture_statistics(which, pyr, params):
     return arrays
 
 
+def cpu_dg_detector_hme(which, src, ref, input_resolution):
+    """dg_detector_hme_level0 over the whole picture between two CpuPyramids: (tot_dist, tot_cplx, tot_active, sum_in_vectors)."""
+    lib = oracle_lib() if which == "orc" else ref_lib()
+    m = abi.SvtMeDgMetrics()
+    rc = getattr(lib, which + "_dg_detector_hme")(C.byref(src.pyr), C.byref(ref.pyr), C.c_uint32(input_resolution), C.byref(m))
+    assert rc == 0
+    return (int(m.tot_dist), int(m.tot_cplx), int(m.tot_active), int(m.sum_in_vectors))
+
+
 derive_input, finish_params = me_host.derive_input, me_host.finish_params
 
 

@@ -176,3 +176,23 @@ EbErrorType svtme_hook_statistics(SvtMeHandle *svtme, const SequenceControlSet *
             }
     return EB_ErrorNone;
 }
+
+/* H7 — dynamic-GOP detector (Codec/me_process.c:327-332, TASK_DG_DETECTOR_HME; tasks posted by early_hme, pd_process.c:591-633):
+ * in place of dg_detector_hme_level0(pcs, segment_index). The first segment's task runs the whole picture on the GPU and
+ * completes the frame (metrics + semaphore), the other segments' tasks return at once. Both pictures are resident because
+ * their pyramids went through H1. */
+EbErrorType svtme_hook_dg_detector(SvtMeHandle *svtme, PictureParentControlSet *pcs, uint32_t segment_index) {
+    if (segment_index != 0) return EB_ErrorNone;
+    SvtMeDgMetrics m;
+    if (svtme_dg_detector_hme(svtme, pcs->picture_number, pcs->dg_detector->ref_pic->picture_number, (uint32_t)pcs->input_resolution, &m) != SVTME_OK)
+        return EB_ErrorInsufficientResources;
+    svt_block_on_mutex(pcs->dg_detector->metrics_mutex);
+    pcs->dg_detector->metrics.tot_dist += m.tot_dist;
+    pcs->dg_detector->metrics.tot_cplx += m.tot_cplx;
+    pcs->dg_detector->metrics.tot_active += m.tot_active;
+    pcs->dg_detector->metrics.sum_in_vectors += m.sum_in_vectors;
+    pcs->dg_detector->metrics.seg_completed = (uint16_t)(pcs->me_segments_column_count * pcs->me_segments_row_count);
+    svt_post_semaphore(pcs->dg_detector->frame_done_sem); /* (:584-586: all segments done) */
+    svt_release_mutex(pcs->dg_detector->metrics_mutex);
+    return EB_ErrorNone;
+}

@@ -278,7 +278,7 @@ int svtme_picture_statistics(SvtMeHandle *h, uint64_t pic_num, const SvtMeStatsP
 /* n pictures, one launch sequence, one download (the picture-analysis kernel of the reference handles one picture per
  * call; a look-ahead window's worth is the batch here). */
 int svtme_pictures_statistics(SvtMeHandle *h, uint32_t n, const uint64_t *pic_nums, const SvtMeStatsParams *params, SvtMeStatsOut *outs);
-/* Profiling aid: device milliseconds of the kernels and of the result download of the last svtme_picture(s)_statistics or
+/* Profiling aid: device milliseconds of the kernels and of the result download of the last svtme_picture_statistics, svtme_pictures_statistics or
  * svtme_dg_detector_hme call. */
 int svtme_last_statistics_ms(SvtMeHandle *h, float *kernels_ms, float *download_ms);
 uint32_t svtme_sizeof_stats_params(void);

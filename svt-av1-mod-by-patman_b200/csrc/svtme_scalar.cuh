@@ -148,104 +148,111 @@ __device__ void set_quadrants(StageState *s, int lvl, int li, int ri, int16_t x,
         }
 }
 
-// The post steps read (meta, key) of every job the search round ran and scatter them into the state. Inside a loop
-// over the jobs each iteration's loads wait behind the previous iteration's stores (same struct: the compiler keeps
-// the order) — one memory round trip per job for a thread that has nothing else to do. The loads of POST_BATCH jobs
-// are issued together instead.
-#define POST_BATCH 4
-template <class S>
-__device__ __forceinline__ void load_post_batch(const S *s, int n0, int nj, JobMeta (&mm)[POST_BATCH], unsigned long long (&kk)[POST_BATCH]) {
+// ---------------------------------------------------------------- plan / post steps: a TEAM of 8 lanes per b64
+// The scalar bookkeeping between two search rounds (post: scatter the round's results into the state; plan: decide
+// and describe the next round's searches) loops over the NL x NR = 8 (list, reference) slots. One thread per b64 walked
+// those loops as one long chain of dependent global accesses, 32 b64 = 32 different cache lines per warp instruction.
+// Here lane t of a team owns slot (list, ref) = (t >> 2, t & 3): the chains are 5-8x shorter, the 8 lanes of a team
+// touch neighbouring fields of one state block, and the few values that cross slots (minima, the running search
+// centre) move by shuffles. Jobs keep the order of the reference's loops: a lane counts the jobs its slot will post,
+// an exclusive prefix sum over the team gives its first index, then it writes them.
+struct Team {
+    unsigned mask; // the 8 lanes of this team inside the warp
+    int tl;        // lane inside the team = slot index li * NR + ri
+    int li, ri;
+};
+__device__ __forceinline__ Team team_of() {
+    const int lane = threadIdx.x & 31;
+    Team t;
+    t.tl = lane & 7;
+    t.mask = 0xffu << (lane & 24);
+    t.li = t.tl >> 2;
+    t.ri = t.tl & 3;
+    return t;
+}
+__device__ __forceinline__ uint32_t team_min(const Team &t, uint32_t v) {
 #pragma unroll
-    for (int i = 0; i < POST_BATCH; ++i) {
-        const int n = min(n0 + i, nj - 1); // (clamped: the load is unconditional, the use is not)
-        mm[i] = s->meta[n];
-        kk[i] = s->jobs[n].key;
+    for (int o = 4; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(t.mask, v, o, 8));
+    return v;
+}
+__device__ __forceinline__ unsigned long long team_min(const Team &t, unsigned long long v) {
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) {
+        const unsigned long long u = __shfl_xor_sync(t.mask, v, o, 8);
+        v = u < v ? u : v;
     }
+    return v;
+}
+// first job index of this lane's slot and the team's total, from the per-lane job counts
+__device__ __forceinline__ int team_job_base(const Team &t, int cnt, int &total) {
+    int v = cnt;
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) {
+        const int u = __shfl_up_sync(t.mask, v, o, 8);
+        if (t.tl >= o) v += u;
+    }
+    total = __shfl_sync(t.mask, v, 7, 8);
+    return v - cnt;
+}
+__device__ __forceinline__ bool slot_in_range(const SvtMeParams &p, const Team &t) {
+    return t.li < p.num_of_list_to_search && t.ri < p.num_of_ref_pic_to_search[t.li];
+}
+// The job the last plan step posted for (this slot, quadrant / region q), or -1: add_job left its index in job_idx, the
+// entry is verified against meta[] (a stale index of an earlier round points at another slot's job or beyond nj).
+__device__ __forceinline__ int slot_job(const StageState *s, const Team &t, int q, int nj, JobMeta &m) {
+    const int k = s->job_idx[t.li][t.ri][q];
+    if (k >= nj) return -1;
+    m = s->meta[k];
+    return (m.li == t.li && m.ri == t.ri && ((2 * m.b + m.a) & 3) == q) ? k : -1;
 }
 
-// ---------------------------------------------------------------- plan / post steps (thread 0)
-__device__ void init_state(StageState *s, const SvtMeParams &p) { // init_me_hme_data :3080-3140
-    for (int li = 0; li < NL; ++li)
-        for (int ri = 0; ri < NR; ++ri) {
-            RefResult &r = s->sr[li][ri];
-            r.hme_sc_x = r.hme_sc_y = 0;
-            r.do_ref = 1;
-            r.hme_sad = MAXU32;
-            s->div[li][ri] = 1;
-            s->zz[li][ri] = MAXU32;
-            for (int k = 0; k < 2; ++k) {
-                PreHme &d = s->ph[li][ri][k];
-                d.sa_w = d.sa_h = 0;
-                d.col = d.row = 0;
-                d.sad = 0;
-                d.valid = 0;
-                s->performed_phme[li][ri][k] = 0;
-            }
-            for (int l = 0; l < 3; ++l) set_quadrants(s, l, li, ri, 0, 0, 0);
-        }
-    s->hme_l0_sa = p.hme_l0_sa;
+// init_me_hme_data (:3080-3140) on a state block the host has zero-filled: only the non-zero fields
+__device__ __forceinline__ void team_init_state(StageState *s, const SvtMeParams &p, const Team &t) {
+    s->sr[t.li][t.ri].do_ref = 1;
+    s->sr[t.li][t.ri].hme_sad = MAXU32;
+    s->div[t.li][t.ri] = 1;
+    s->zz[t.li][t.ri] = MAXU32;
+    if (t.tl == 0) s->hme_l0_sa = p.hme_l0_sa;
 }
 
-// init_me_hme_data on a state block the host has zero-filled: only the non-zero fields.
-__device__ void init_state_zeroed(StageState *s, const SvtMeParams &p) {
-    for (int li = 0; li < NL; ++li)
-        for (int ri = 0; ri < NR; ++ri) {
-            s->sr[li][ri].do_ref = 1;
-            s->sr[li][ri].hme_sad = MAXU32;
-            s->div[li][ri] = 1;
-            s->zz[li][ri] = MAXU32;
-        }
-    s->hme_l0_sa = p.hme_l0_sa;
-}
-
-// zz-SAD jobs: one 1x1 search per reference at MV (0,0) (get_zz_sad :1737-1759)
-__device__ void plan_zz(StageState *s, const DevJob &J) {
+// zz-SAD jobs: one 1x1 search per reference at MV (0,0) (get_zz_sad :1737-1759). Returns the number of jobs.
+__device__ __forceinline__ int team_plan_zz(StageState *s, const DevJob &J, const Team &t, int org_x, int org_y) {
     const SvtMeParams &p = J.prm;
-    int nj = 0;
-    const int org_x = s->org_x, org_y = s->org_y;
-    for (int li = 0; li < p.num_of_list_to_search; ++li)
-        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri)
-            if (p.temporal_layer_index > 0 || li == 0) {
-                const DevPlane &pl = J.ref[li][ri].lvl[0];
-                add_job(s, nj, pl, pl.org_x + org_x, pl.org_y + org_y, 1, 1, 0, li, ri, 0, 0, 0, 0);
-            }
-    s->n_jobs = nj;
+    const bool mine = slot_in_range(p, t) && (p.temporal_layer_index > 0 || t.li == 0);
+    int total, nj = team_job_base(t, mine ? 1 : 0, total);
+    if (mine) {
+        const DevPlane &pl = J.ref[t.li][t.ri].lvl[0];
+        add_job(s, nj, pl, pl.org_x + org_x, pl.org_y + org_y, 1, 1, 0, t.li, t.ri, 0, 0, 0, 0);
+    }
+    return total;
 }
 
-__device__ void post_zz(StageState *s, const SvtMeParams &p) { // init_zz_sad :2452-2507
-    uint32_t best = MAXU32;
-    const int nj = s->n_jobs;
-    const uint32_t area = (uint32_t)(s->b64_w * s->b64_h);
-    for (int n0 = 0; n0 < nj; n0 += POST_BATCH) {
-        JobMeta mm[POST_BATCH];
-        unsigned long long kk[POST_BATCH];
-        load_post_batch(s, n0, nj, mm, kk);
-#pragma unroll
-        for (int i = 0; i < POST_BATCH; ++i)
-            if (n0 + i < nj) {
-                const JobMeta &m = mm[i];
-                uint32_t z = (uint32_t)(kk[i] >> 32) << 1;
-                z = (z * 64 * 64) / area;
-                s->zz[m.li][m.ri] = z;
-                best = min(best, z);
-            }
+// init_zz_sad :2452-2507
+__device__ __forceinline__ void team_post_zz(StageState *s, const SvtMeParams &p, const Team &t, int nj) {
+    uint32_t zcur = s->zz[t.li][t.ri], zjob = MAXU32;
+    JobMeta m;
+    const int k = slot_job(s, t, 0, nj, m);
+    if (k >= 0) {
+        uint32_t z = (uint32_t)(s->jobs[k].key >> 32) << 1;
+        z = (z * 64 * 64) / (uint32_t)(s->b64_w * s->b64_h);
+        s->zz[t.li][t.ri] = z;
+        zcur = zjob = z;
     }
-    if (p.temporal_layer_index > 0 && best < p.zz_sad_th)
-        for (int li = 0; li < p.num_of_list_to_search; ++li)
-            for (int ri = 1; ri < p.num_of_ref_pic_to_search[li]; ++ri)
-                if ((uint32_t)((s->zz[li][ri] - best) * 100) > (uint32_t)(p.zz_sad_pct * best)) s->sr[li][ri].do_ref = 0;
+    const uint32_t best = team_min(t, zjob);
+    const bool prunable = slot_in_range(p, t) && t.ri >= 1;
+    if (p.temporal_layer_index > 0 && best < p.zz_sad_th && prunable)
+        if ((uint32_t)((zcur - best) * 100) > (uint32_t)(p.zz_sad_pct * best)) s->sr[t.li][t.ri].do_ref = 0;
+    const uint32_t zz00 = __shfl_sync(t.mask, zcur, 0, 8), zz10 = __shfl_sync(t.mask, zcur, 4, 8);
     if (p.me_safe_limit_zz_th) {
         const bool limit = p.hierarchical_levels > 0 && p.num_of_list_to_search == 2 &&
-            p.temporal_layer_index >= p.hierarchical_levels && p.similar_brightness_refs &&
-            s->zz[0][0] < p.me_safe_limit_zz_th && s->zz[1][0] < p.me_safe_limit_zz_th;
-        if (limit)
-            for (int li = 0; li < p.num_of_list_to_search; ++li)
-                for (int ri = 1; ri < p.num_of_ref_pic_to_search[li]; ++ri) s->sr[li][ri].do_ref = 0;
+            p.temporal_layer_index >= p.hierarchical_levels && p.similar_brightness_refs && zz00 < p.me_safe_limit_zz_th &&
+            zz10 < p.me_safe_limit_zz_th;
+        if (limit && prunable) s->sr[t.li][t.ri].do_ref = 0;
     }
 }
 
 // check_prehme_early_exit :1763-1788
-__device__ bool prehme_early_exit(StageState *s, const SvtMeParams &p, int li, int ri, int sr) {
+__device__ __forceinline__ bool prehme_early_exit(StageState *s, const SvtMeParams &p, int li, int ri, int sr) {
     PreHme &d = s->ph[li][ri][sr];
     if (p.me_early_exit_th && s->zz[li][ri] < p.me_early_exit_th) {
         d.col = d.row = 0;
@@ -266,16 +273,14 @@ __device__ bool prehme_early_exit(StageState *s, const SvtMeParams &p, int li, i
     return false;
 }
 
-// prehme_b64 (:1791-1866) for one list: decide per (ref, region) and emit jobs (prehme_core :1641)
-__device__ void plan_prehme(StageState *s, const DevJob &J, int li, bool append = false) {
+// prehme_b64 (:1791-1866): decide per (ref, region) and emit jobs (prehme_core :1641). do_list[l]: list l is planned in
+// this step (both lists are one round unless list 1 waits for list 0's result, prehme_l1_early_exit). Returns the job count.
+__device__ __forceinline__ int team_plan_prehme(StageState *s, const DevJob &J, const Team &t, bool do_list0, bool do_list1) {
     const SvtMeParams &p = J.prm;
-    int nj = append ? s->n_jobs : 0;
-    if (!(p.temporal_layer_index > 0 || li == 0)) {
-        s->n_jobs = nj;
-        return;
-    }
-    for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
-        const uint32_t factor = scaled_dist(ref_dist(p, li, ri));
+    const int li = t.li, ri = t.ri;
+    const bool mine = slot_in_range(p, t) && (li == 0 ? do_list0 : do_list1) && (p.temporal_layer_index > 0 || li == 0);
+    unsigned emit = 0; // bit sr: region sr gets a search
+    if (mine)
         for (int sr = 0; sr < 2; ++sr) {
             if (prehme_early_exit(s, p, li, ri, sr)) continue;
             PreHme &d = s->ph[li][ri][sr];
@@ -284,13 +289,23 @@ __device__ void plan_prehme(StageState *s, const DevJob &J, int li, bool append 
                 d.sad = MAXU32;
                 continue;
             }
-            d.sa_w = (uint16_t)min(p.prehme_sa_cfg[sr].sa_min.width * factor, (uint32_t)p.prehme_sa_cfg[sr].sa_max.width);
-            d.sa_h = (uint16_t)min(p.prehme_sa_cfg[sr].sa_min.height * factor, (uint32_t)p.prehme_sa_cfg[sr].sa_max.height);
-            const DevPlane &pl = J.ref[li][ri].lvl[2];
-            const int16_t org_x = (int16_t)s->org_x >> 2, org_y = (int16_t)s->org_y >> 2;
-            const int16_t pad_w = 15, pad_h = 15; // sixteenth org (16) - 1
-            const int16_t W = (int16_t)pl.width, H = (int16_t)pl.height;
-            int16_t sa_w = (int16_t)d.sa_w, sa_h = (int16_t)d.sa_h;
+            emit |= 1u << sr;
+        }
+    int total, nj = team_job_base(t, __popc(emit), total);
+    if (emit) {
+        const uint32_t factor = scaled_dist(ref_dist(p, li, ri));
+        const DevPlane &pl = J.ref[li][ri].lvl[2];
+        const int16_t org_x = (int16_t)s->org_x >> 2, org_y = (int16_t)s->org_y >> 2;
+        const int16_t pad_w = 15, pad_h = 15; // sixteenth org (16) - 1
+        const int16_t W = (int16_t)pl.width, H = (int16_t)pl.height;
+        for (int sr = 0; sr < 2; ++sr) {
+            if (!(emit >> sr & 1)) continue;
+            PreHme &d = s->ph[li][ri][sr];
+            const uint16_t dw = (uint16_t)min(p.prehme_sa_cfg[sr].sa_min.width * factor, (uint32_t)p.prehme_sa_cfg[sr].sa_max.width);
+            const uint16_t dh = (uint16_t)min(p.prehme_sa_cfg[sr].sa_min.height * factor, (uint32_t)p.prehme_sa_cfg[sr].sa_max.height);
+            d.sa_w = dw;
+            d.sa_h = dh;
+            int16_t sa_w = (int16_t)dw, sa_h = (int16_t)dh;
             int16_t ox = -(int16_t)(sa_w >> 1), oy = -(int16_t)(sa_h >> 1);
             ox = ((org_x + ox) < -pad_w) ? -pad_w - org_x : ox;
             sa_w = ((org_x + ox) < -pad_w) ? sa_w - (-pad_w - (org_x + ox)) : sa_w;
@@ -300,62 +315,50 @@ __device__ void plan_prehme(StageState *s, const DevJob &J, int li, bool append 
             sa_h = ((org_y + oy) < -pad_h) ? sa_h - (-pad_h - (org_y + oy)) : sa_h;
             oy = ((org_y + oy) > H - 1) ? oy - ((org_y + oy) - (H - 1)) : oy;
             sa_h = (org_y + oy + sa_h > H) ? max(1, sa_h - ((org_y + oy + sa_h) - H)) : sa_h;
-            add_job(s, nj, pl, pl.org_x + org_x + ox, pl.org_y + org_y + oy, sa_w, sa_h, p.prehme_skip_search_line, li, ri, sr,
-                    0, ox, oy);
+            add_job(s, nj, pl, pl.org_x + org_x + ox, pl.org_y + org_y + oy, sa_w, sa_h, p.prehme_skip_search_line, li, ri, sr, 0, ox, oy);
         }
     }
-    s->n_jobs = nj;
+    return total;
 }
 
-__device__ void post_prehme_jobs(StageState *s, const SvtMeParams &p) {
+__device__ __forceinline__ void team_post_prehme_jobs(StageState *s, const SvtMeParams &p, const Team &t, int nj) {
     const bool full = p.hme_search_method == 1;
-    const int nj = s->n_jobs;
-    for (int n0 = 0; n0 < nj; n0 += POST_BATCH) {
-        JobMeta mm[POST_BATCH];
-        unsigned long long kk[POST_BATCH];
-        load_post_batch(s, n0, nj, mm, kk);
-#pragma unroll
-        for (int i = 0; i < POST_BATCH; ++i)
-            if (n0 + i < nj) {
-                const JobMeta &m = mm[i];
-                const unsigned long long k = kk[i];
-                PreHme &d = s->ph[m.li][m.ri][m.a];
-                d.sad = (k >> 32) * (full ? 1 : 2);
-                d.col = (int16_t)((int16_t)((int16_t)(k & 0xffff) + m.ox) * 4);
-                d.row = (int16_t)((int16_t)((int16_t)((k >> 16) & 0xffff) + m.oy) * 4);
-                d.valid = 1;
-                s->performed_phme[m.li][m.ri][m.a] = 1;
-            }
+    for (int q = 0; q < 2; ++q) {
+        JobMeta m;
+        const int k = slot_job(s, t, q, nj, m);
+        if (k < 0) continue;
+        const unsigned long long key = s->jobs[k].key;
+        PreHme &d = s->ph[t.li][t.ri][q];
+        d.sad = (key >> 32) * (full ? 1 : 2);
+        d.col = (int16_t)((int16_t)((int16_t)(key & 0xffff) + m.ox) * 4);
+        d.row = (int16_t)((int16_t)((int16_t)((key >> 16) & 0xffff) + m.oy) * 4);
+        d.valid = 1;
+        s->performed_phme[t.li][t.ri][q] = 1;
     }
 }
 
-__device__ void post_prehme_final(StageState *s, const SvtMeParams &p) { // tail of prehme_b64 :1841-1866
-    uint32_t best_sad = MAXU32;
-    for (int li = 0; li < p.num_of_list_to_search; ++li)
-        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
-            if (p.temporal_layer_index > 0 || li == 0) {
-                uint32_t m = (uint32_t)min(s->ph[li][ri][0].sad, s->ph[li][ri][1].sad);
-                best_sad = min(best_sad, m);
-            } else {
-                for (int sr = 0; sr < 2; ++sr) {
-                    s->ph[1][ri][sr].col = (int16_t)-s->ph[0][ri][sr].col;
-                    s->ph[1][ri][sr].row = (int16_t)-s->ph[0][ri][sr].row;
-                    s->ph[1][ri][sr].sad = s->ph[0][ri][sr].sad;
-                }
+// tail of prehme_b64 :1841-1866 (runs after the team has synchronised on the post step above)
+__device__ __forceinline__ void team_post_prehme_final(StageState *s, const SvtMeParams &p, const Team &t) {
+    const bool inr = slot_in_range(p, t), tlok = p.temporal_layer_index > 0 || t.li == 0;
+    uint32_t mval = MAXU32;
+    if (inr) {
+        if (tlok)
+            mval = (uint32_t)min(s->ph[t.li][t.ri][0].sad, s->ph[t.li][t.ri][1].sad);
+        else
+            for (int sr = 0; sr < 2; ++sr) {
+                s->ph[1][t.ri][sr].col = (int16_t)-s->ph[0][t.ri][sr].col;
+                s->ph[1][t.ri][sr].row = (int16_t)-s->ph[0][t.ri][sr].row;
+                s->ph[1][t.ri][sr].sad = s->ph[0][t.ri][sr].sad;
             }
-        }
-    if (p.temporal_layer_index > 0 && best_sad < p.phme_sad_th)
-        for (int li = 0; li < p.num_of_list_to_search; ++li)
-            for (int ri = 1; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
-                if (!s->sr[li][ri].do_ref) continue;
-                uint32_t m = (uint32_t)min(s->ph[li][ri][0].sad, s->ph[li][ri][1].sad);
-                if ((uint32_t)((m - best_sad) * 100) > (uint32_t)(p.phme_sad_pct * best_sad)) s->sr[li][ri].do_ref = 0;
-            }
+    }
+    const uint32_t best_sad = team_min(t, (inr && tlok) ? mval : MAXU32);
+    if (p.temporal_layer_index > 0 && best_sad < p.phme_sad_th && inr && t.ri >= 1 && s->sr[t.li][t.ri].do_ref)
+        if ((uint32_t)((mval - best_sad) * 100) > (uint32_t)(p.phme_sad_pct * best_sad)) s->sr[t.li][t.ri].do_ref = 0;
 }
 
 // get_hme_l0_search_area :1870-1935 (works on a local copy of hme_l0_sa == modify + restore)
-__device__ void hme_l0_area(const StageState *s, const SvtMeParams &p, int li, int ri, uint16_t dist, int16_t *sa_w,
-                            int16_t *sa_h) {
+__device__ __forceinline__ void hme_l0_area(const StageState *s, const SvtMeParams &p, int li, int ri, uint16_t dist, int16_t *sa_w,
+                                            int16_t *sa_h) {
     SvtMeSearchAreaMinMax a = s->hme_l0_sa;
     if (p.enable_me_sr_adjustment && p.distance_based_hme_resizing) {
         uint8_t is_hor = 1, is_ver = 1, is_still = 0;
@@ -381,182 +384,187 @@ __device__ void hme_l0_area(const StageState *s, const SvtMeParams &p, int li, i
     *sa_h = h;
 }
 
-// hme_level0_b64 :1976-2106. first_only: plan (list0, ref0) only; skip_first: everything else.
-__device__ void plan_l0(StageState *s, const DevJob &J, bool first_only, bool skip_first) {
+// hme_level0_b64 :1976-2106. first_only: plan (list0, ref0) only; skip_first: everything else. Returns the job count.
+__device__ __forceinline__ int team_plan_l0(StageState *s, const DevJob &J, const Team &t, bool first_only, bool skip_first) {
     const SvtMeParams &p = J.prm;
-    int nj = 0;
-    for (int li = 0; li < p.num_of_list_to_search; ++li)
-        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
-            const bool first = (li == 0 && ri == 0);
-            if ((first_only && !first) || (skip_first && first)) continue;
-            if (p.me_early_exit_th && s->zz[li][ri] < (p.me_early_exit_th >> 2)) {
-                set_quadrants(s, 0, li, ri, 0, 0, 0);
-                continue;
-            }
-            if (p.prev_me_stage_based_exit_th) {
-                int sr = s->ph[li][ri][0].sad <= s->ph[li][ri][1].sad ? 0 : 1;
-                if (s->performed_phme[li][ri][sr] && s->ph[li][ri][sr].sad < (p.prev_me_stage_based_exit_th >> 4)) {
-                    set_quadrants(s, 0, li, ri, s->ph[li][ri][sr].col, s->ph[li][ri][sr].row, s->ph[li][ri][sr].sad);
-                    continue;
-                }
-            }
-            if (!s->sr[li][ri].do_ref) {
-                set_quadrants(s, 0, li, ri, 0, 0, MAXU32);
-                continue;
-            }
-            if (!(p.temporal_layer_index > 0 || li == 0)) continue;
-            const DevPlane &pl = J.ref[li][ri].lvl[2];
-            int16_t sa_w0 = 0, sa_h0 = 0;
-            hme_l0_area(s, p, li, ri, ref_dist(p, li, ri), &sa_w0, &sa_h0);
-            const int16_t org_x = (int16_t)s->org_x >> 2, org_y = (int16_t)s->org_y >> 2;
-            for (int sh = 0; sh < p.num_hme_sa_h; ++sh)
-                for (int sw = 0; sw < p.num_hme_sa_w; ++sw) {
-                    int16_t w = (int16_t)((sa_w0 + 7) & ~0x07), h = sa_h0;
-                    int16_t ox = (int16_t)(-(int16_t)((w * p.num_hme_sa_w) >> 1) + (int16_t)(w * sw));
-                    int16_t oy = (int16_t)(-(int16_t)((sa_h0 * p.num_hme_sa_h) >> 1) + (int16_t)(sa_h0 * sh));
-                    clip_hme(org_x, org_y, (int16_t)pl.width, (int16_t)pl.height, 15, 15, w, h, ox, oy);
-                    add_job(s, nj, pl, pl.org_x + org_x + ox, pl.org_y + org_y + oy, w, h, 0, li, ri, sw, sh, ox, oy);
-                }
+    const int li = t.li, ri = t.ri;
+    const bool first = t.tl == 0;
+    bool search = false;
+    if (slot_in_range(p, t) && !((first_only && !first) || (skip_first && first))) {
+        bool done = false;
+        if (p.me_early_exit_th && s->zz[li][ri] < (p.me_early_exit_th >> 2)) {
+            set_quadrants(s, 0, li, ri, 0, 0, 0);
+            done = true;
         }
-    s->n_jobs = nj;
+        if (!done && p.prev_me_stage_based_exit_th) {
+            const int sr = s->ph[li][ri][0].sad <= s->ph[li][ri][1].sad ? 0 : 1;
+            if (s->performed_phme[li][ri][sr] && s->ph[li][ri][sr].sad < (p.prev_me_stage_based_exit_th >> 4)) {
+                set_quadrants(s, 0, li, ri, s->ph[li][ri][sr].col, s->ph[li][ri][sr].row, s->ph[li][ri][sr].sad);
+                done = true;
+            }
+        }
+        if (!done && !s->sr[li][ri].do_ref) {
+            set_quadrants(s, 0, li, ri, 0, 0, MAXU32);
+            done = true;
+        }
+        search = !done && (p.temporal_layer_index > 0 || li == 0);
+    }
+    int total, nj = team_job_base(t, search ? p.num_hme_sa_h * p.num_hme_sa_w : 0, total);
+    if (search) {
+        const DevPlane &pl = J.ref[li][ri].lvl[2];
+        int16_t sa_w0 = 0, sa_h0 = 0;
+        hme_l0_area(s, p, li, ri, ref_dist(p, li, ri), &sa_w0, &sa_h0);
+        const int16_t org_x = (int16_t)s->org_x >> 2, org_y = (int16_t)s->org_y >> 2;
+        for (int sh = 0; sh < p.num_hme_sa_h; ++sh)
+            for (int sw = 0; sw < p.num_hme_sa_w; ++sw) {
+                int16_t w = (int16_t)((sa_w0 + 7) & ~0x07), h = sa_h0;
+                int16_t ox = (int16_t)(-(int16_t)((w * p.num_hme_sa_w) >> 1) + (int16_t)(w * sw));
+                int16_t oy = (int16_t)(-(int16_t)((sa_h0 * p.num_hme_sa_h) >> 1) + (int16_t)(sa_h0 * sh));
+                clip_hme(org_x, org_y, (int16_t)pl.width, (int16_t)pl.height, 15, 15, w, h, ox, oy);
+                add_job(s, nj, pl, pl.org_x + org_x + ox, pl.org_y + org_y + oy, w, h, 0, li, ri, sw, sh, ox, oy);
+            }
+    }
+    return total;
 }
 
-__device__ void post_level_jobs(StageState *s, const SvtMeParams &p, int lvl, int scale) {
+// results of an HME level into lsad / cx / cy of this slot; returns true when the slot had searches in the round
+__device__ __forceinline__ bool team_post_level_jobs(StageState *s, const SvtMeParams &p, const Team &t, int nj, int lvl, int scale) {
     const bool full = p.hme_search_method == 1;
-    const int nj = s->n_jobs;
-    for (int n0 = 0; n0 < nj; n0 += POST_BATCH) {
-        JobMeta mm[POST_BATCH];
-        unsigned long long kk[POST_BATCH];
-        load_post_batch(s, n0, nj, mm, kk);
+    bool any = false;
+    JobMeta mm[4];
+    int kk[4];
 #pragma unroll
-        for (int i = 0; i < POST_BATCH; ++i)
-            if (n0 + i < nj) {
-                const JobMeta &m = mm[i];
-                const unsigned long long k = kk[i];
-                s->lsad[lvl][m.li][m.ri][m.a][m.b] = (k >> 32) * (full ? 1 : 2);
-                s->cx[lvl][m.li][m.ri][m.a][m.b] = (int16_t)((int16_t)((int16_t)(k & 0xffff) + m.ox) * scale);
-                s->cy[lvl][m.li][m.ri][m.a][m.b] = (int16_t)((int16_t)((int16_t)((k >> 16) & 0xffff) + m.oy) * scale);
-            }
+    for (int q = 0; q < 4; ++q) kk[q] = slot_job(s, t, q, nj, mm[q]);
+    unsigned long long key[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) key[q] = kk[q] >= 0 ? s->jobs[kk[q]].key : 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        if (kk[q] < 0) continue;
+        const JobMeta &m = mm[q];
+        const unsigned long long k = key[q];
+        s->lsad[lvl][m.li][m.ri][m.a][m.b] = (k >> 32) * (full ? 1 : 2);
+        s->cx[lvl][m.li][m.ri][m.a][m.b] = (int16_t)((int16_t)((int16_t)(k & 0xffff) + m.ox) * scale);
+        s->cy[lvl][m.li][m.ri][m.a][m.b] = (int16_t)((int16_t)((int16_t)((k >> 16) & 0xffff) + m.oy) * scale);
+        any = true;
     }
+    return any;
 }
 
-// worst-quadrant replacement by the pre-HME result (:2073-2101, get_worst_quadrant :1939-1971)
-__device__ void post_l0_prehme(StageState *s, const SvtMeParams &p) {
+// worst-quadrant replacement by the pre-HME result (:2073-2101, get_worst_quadrant :1939-1971), for a slot that searched
+__device__ __forceinline__ void team_post_l0_prehme(StageState *s, const SvtMeParams &p, const Team &t) {
     if (!p.prehme_enable) return;
-    int last_li = -1, last_ri = -1;
-    const int nj = s->n_jobs;
-    for (int n = 0; n < nj; ++n) {
-        const int li = s->meta[n].li, ri = s->meta[n].ri;
-        if (li == last_li && ri == last_ri) continue;
-        last_li = li;
-        last_ri = ri;
-        unsigned long long(*q)[2] = s->lsad[0][li][ri];
-        int bw = 0, bh = 0;
-        unsigned long long mx = 0;
-        if (q[0][0] > mx) { mx = q[0][0]; bw = 0; bh = 0; }
-        if (q[1][0] > mx) { mx = q[1][0]; bw = 1; bh = 0; }
-        if (q[0][1] > mx) { mx = q[0][1]; bw = 0; bh = 1; }
-        if (q[1][1] > mx) { bw = 1; bh = 1; }
-        const int sr = s->ph[li][ri][0].sad <= s->ph[li][ri][1].sad ? 0 : 1;
-        if (s->ph[li][ri][sr].sad < q[bw][bh]) {
-            q[bw][bh] = s->ph[li][ri][sr].sad;
-            s->cx[0][li][ri][bw][bh] = s->ph[li][ri][sr].col;
-            s->cy[0][li][ri][bw][bh] = s->ph[li][ri][sr].row;
-        }
+    const int li = t.li, ri = t.ri;
+    unsigned long long(*q)[2] = s->lsad[0][li][ri];
+    int bw = 0, bh = 0;
+    unsigned long long mx = 0;
+    if (q[0][0] > mx) { mx = q[0][0]; bw = 0; bh = 0; }
+    if (q[1][0] > mx) { mx = q[1][0]; bw = 1; bh = 0; }
+    if (q[0][1] > mx) { mx = q[0][1]; bw = 0; bh = 1; }
+    if (q[1][1] > mx) { bw = 1; bh = 1; }
+    const int sr = s->ph[li][ri][0].sad <= s->ph[li][ri][1].sad ? 0 : 1;
+    if (s->ph[li][ri][sr].sad < q[bw][bh]) {
+        q[bw][bh] = s->ph[li][ri][sr].sad;
+        s->cx[0][li][ri][bw][bh] = s->ph[li][ri][sr].col;
+        s->cy[0][li][ri][bw][bh] = s->ph[li][ri][sr].row;
     }
 }
 
-// hme_level1_b64 :2111-2192
-__device__ void plan_l1(StageState *s, const DevJob &J) {
+// hme_level1_b64 :2111-2192 (level 1) and hme_level2_b64 :2197-2247 (level 2: no do_ref / early-exit test in the reference)
+__device__ __forceinline__ int team_plan_refine(StageState *s, const DevJob &J, const Team &t, int lvl) {
     const SvtMeParams &p = J.prm;
-    int nj = 0;
-    for (int li = 0; li < p.num_of_list_to_search; ++li)
-        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
-            if (!(p.temporal_layer_index > 0 || li == 0)) continue;
+    const int li = t.li, ri = t.ri, prev = lvl - 1;
+    unsigned emit = 0; // bit 2 * sh + sw
+    if (slot_in_range(p, t) && (p.temporal_layer_index > 0 || li == 0)) {
+        bool done = false;
+        if (lvl == 1) {
             if (p.me_early_exit_th && s->zz[li][ri] < (p.me_early_exit_th >> 2)) {
                 set_quadrants(s, 1, li, ri, 0, 0, 0);
-                continue;
-            }
-            if (!s->sr[li][ri].do_ref) {
+                done = true;
+            } else if (!s->sr[li][ri].do_ref) {
                 set_quadrants(s, 1, li, ri, 0, 0, MAXU32);
-                continue;
+                done = true;
             }
-            const DevPlane &pl = J.ref[li][ri].lvl[1];
-            const int16_t org_x = (int16_t)s->org_x >> 1, org_y = (int16_t)s->org_y >> 1;
+        }
+        if (!done)
             for (int sh = 0; sh < p.num_hme_sa_h; ++sh)
                 for (int sw = 0; sw < p.num_hme_sa_w; ++sw) {
-                    if (p.prev_me_stage_based_exit_th && s->lsad[0][li][ri][sw][sh] < (p.prev_me_stage_based_exit_th >> 5)) {
-                        s->cx[1][li][ri][sw][sh] = s->cx[0][li][ri][sw][sh];
-                        s->cy[1][li][ri][sw][sh] = s->cy[0][li][ri][sw][sh];
-                        s->lsad[1][li][ri][sw][sh] = s->lsad[0][li][ri][sw][sh];
+                    if (p.prev_me_stage_based_exit_th && s->lsad[prev][li][ri][sw][sh] < (p.prev_me_stage_based_exit_th >> (lvl == 1 ? 5 : 2))) {
+                        s->cx[lvl][li][ri][sw][sh] = s->cx[prev][li][ri][sw][sh];
+                        s->cy[lvl][li][ri][sw][sh] = s->cy[prev][li][ri][sw][sh];
+                        s->lsad[lvl][li][ri][sw][sh] = s->lsad[prev][li][ri][sw][sh];
                         continue;
                     }
-                    int16_t w = (int16_t)(((int16_t)p.hme_l1_sa.width + 7) & ~0x07), h = (int16_t)p.hme_l1_sa.height;
-                    int16_t ox = (int16_t)(-(w >> 1) + (s->cx[0][li][ri][sw][sh] >> 1));
-                    int16_t oy = (int16_t)(-(h >> 1) + (s->cy[0][li][ri][sw][sh] >> 1));
-                    clip_hme(org_x, org_y, (int16_t)pl.width, (int16_t)pl.height, 31, 31, w, h, ox, oy);
-                    add_job(s, nj, pl, pl.org_x + org_x + ox, pl.org_y + org_y + oy, w, h, 0, li, ri, sw, sh, ox, oy);
+                    emit |= 1u << (2 * sh + sw);
                 }
-        }
-    s->n_jobs = nj;
+    }
+    int total, nj = team_job_base(t, __popc(emit), total);
+    if (emit) {
+        const DevPlane &pl = J.ref[li][ri].lvl[lvl == 1 ? 1 : 0];
+        const int16_t org_x = lvl == 1 ? (int16_t)s->org_x >> 1 : (int16_t)s->org_x, org_y = lvl == 1 ? (int16_t)s->org_y >> 1 : (int16_t)s->org_y;
+        const int16_t pad = lvl == 1 ? 31 : 63;
+        const SvtMeSearchArea &sa = lvl == 1 ? p.hme_l1_sa : p.hme_l2_sa;
+        for (int sh = 0; sh < p.num_hme_sa_h; ++sh)
+            for (int sw = 0; sw < p.num_hme_sa_w; ++sw) {
+                if (!(emit >> (2 * sh + sw) & 1)) continue;
+                int16_t w = (int16_t)(((int16_t)sa.width + 7) & ~0x07), h = (int16_t)sa.height;
+                const int16_t pcx = s->cx[prev][li][ri][sw][sh], pcy = s->cy[prev][li][ri][sw][sh];
+                int16_t ox = (int16_t)(-(w >> 1) + (lvl == 1 ? (pcx >> 1) : pcx));
+                int16_t oy = (int16_t)(-(h >> 1) + (lvl == 1 ? (pcy >> 1) : pcy));
+                clip_hme(org_x, org_y, (int16_t)pl.width, (int16_t)pl.height, pad, pad, w, h, ox, oy);
+                add_job(s, nj, pl, pl.org_x + org_x + ox, pl.org_y + org_y + oy, w, h, 0, li, ri, sw, sh, ox, oy);
+            }
+    }
+    return total;
 }
 
-// hme_level2_b64 :2197-2247 (no do_ref / early-exit test at this level in the reference)
-__device__ void plan_l2(StageState *s, const DevJob &J) {
-    const SvtMeParams &p = J.prm;
-    int nj = 0;
-    for (int li = 0; li < p.num_of_list_to_search; ++li)
-        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
-            if (!(p.temporal_layer_index > 0 || li == 0)) continue;
-            const DevPlane &pl = J.ref[li][ri].lvl[0];
-            const int16_t org_x = (int16_t)s->org_x, org_y = (int16_t)s->org_y;
-            for (int sh = 0; sh < p.num_hme_sa_h; ++sh)
-                for (int sw = 0; sw < p.num_hme_sa_w; ++sw) {
-                    if (p.prev_me_stage_based_exit_th && s->lsad[1][li][ri][sw][sh] < (p.prev_me_stage_based_exit_th >> 2)) {
-                        s->cx[2][li][ri][sw][sh] = s->cx[1][li][ri][sw][sh];
-                        s->cy[2][li][ri][sw][sh] = s->cy[1][li][ri][sw][sh];
-                        s->lsad[2][li][ri][sw][sh] = s->lsad[1][li][ri][sw][sh];
-                        continue;
-                    }
-                    int16_t w = (int16_t)(((int16_t)p.hme_l2_sa.width + 7) & ~0x07), h = (int16_t)p.hme_l2_sa.height;
-                    int16_t ox = (int16_t)(-(w >> 1) + s->cx[1][li][ri][sw][sh]);
-                    int16_t oy = (int16_t)(-(h >> 1) + s->cy[1][li][ri][sw][sh]);
-                    clip_hme(org_x, org_y, (int16_t)pl.width, (int16_t)pl.height, 63, 63, w, h, ox, oy);
-                    add_job(s, nj, pl, pl.org_x + org_x + ox, pl.org_y + org_y + oy, w, h, 0, li, ri, sw, sh, ox, oy);
+// set_final_seach_centre_sb :2252-2450. The reference walks the slots in loop order with running values (hsad and the
+// centres persist from one slot to the next when a slot does not set them, e.g. list 1 of a base-layer picture keeps the
+// last list-0 SAD): every lane computes its own candidate, then all lanes replay the walk over the 8 slots with shuffles
+// and keep the values the walk has at their own slot. Returns this slot's (hme_sc_x, hme_sc_y, hme_sad) as stored, or the
+// values in memory for a slot outside the searched range.
+__device__ __forceinline__ void team_final_search_centre(StageState *s, const SvtMeParams &p, const Team &t, int16_t &out_x, int16_t &out_y,
+                                                         unsigned long long &out_sad) {
+    const int li = t.li, ri = t.ri;
+    const bool inr = slot_in_range(p, t);
+    const int pass = p.enable_hme_level2_flag ? 2 : (p.enable_hme_level1_flag ? 1 : (p.enable_hme_level0_flag ? 0 : -1));
+    const bool sets = inr && (p.temporal_layer_index > 0 || li == 0) && p.enable_hme_flag && pass >= 0;
+    int16_t ox = 0, oy = 0;
+    unsigned long long osad = 0;
+    if (sets) {
+        ox = s->cx[pass][li][ri][0][0];
+        oy = s->cy[pass][li][ri][0][0];
+        osad = s->lsad[pass][li][ri][0][0];
+        uint32_t w = 1, h = 0;
+        while (h < p.num_hme_sa_h) {
+            while (w < p.num_hme_sa_w) {
+                if (s->lsad[pass][li][ri][w][h] < osad) {
+                    ox = s->cx[pass][li][ri][w][h];
+                    oy = s->cy[pass][li][ri][w][h];
+                    osad = s->lsad[pass][li][ri][w][h];
                 }
+                w++;
+            }
+            w = 0;
+            h++;
         }
-    s->n_jobs = nj;
-}
-
-// set_final_seach_centre_sb :2252-2450 — hsad/centres persist across the (list, ref) loop.
-__device__ void set_final_search_centre(StageState *s, const SvtMeParams &p) {
-    int16_t hx = 0, hy = 0, cx = 0, cy = 0;
-    unsigned long long hsad = 0;
-    for (int li = 0; li < p.num_of_list_to_search; ++li)
-        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ++ri) {
-            if (p.temporal_layer_index > 0 || li == 0) {
+    }
+    int16_t hx = 0, hy = 0, cx = 0, cy = 0, my_x = 0, my_y = 0;
+    unsigned long long hsad = 0, my_sad = 0;
+    const int oxy = ((int)(uint16_t)oy << 16) | (uint16_t)ox;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        const int r_xy = __shfl_sync(t.mask, oxy, r, 8);
+        const unsigned long long r_sad = __shfl_sync(t.mask, osad, r, 8);
+        const int r_flags = __shfl_sync(t.mask, (inr ? 1 : 0) | (sets ? 2 : 0), r, 8);
+        if (r_flags & 1) {
+            const bool r_tlok = p.temporal_layer_index > 0 || (r >> 2) == 0;
+            if (r_tlok) {
                 if (p.enable_hme_flag) {
-                    for (int pass = 0; pass < 3; ++pass) {
-                        const bool on = pass == 0
-                            ? (p.enable_hme_level0_flag && !p.enable_hme_level1_flag && !p.enable_hme_level2_flag)
-                            : pass == 1 ? (p.enable_hme_level1_flag && !p.enable_hme_level2_flag) : p.enable_hme_level2_flag;
-                        if (!on) continue;
-                        hx = s->cx[pass][li][ri][0][0];
-                        hy = s->cy[pass][li][ri][0][0];
-                        hsad = s->lsad[pass][li][ri][0][0];
-                        uint32_t w = 1, h = 0;
-                        while (h < p.num_hme_sa_h) {
-                            while (w < p.num_hme_sa_w) {
-                                if (s->lsad[pass][li][ri][w][h] < hsad) {
-                                    hx = s->cx[pass][li][ri][w][h];
-                                    hy = s->cy[pass][li][ri][w][h];
-                                    hsad = s->lsad[pass][li][ri][w][h];
-                                }
-                                w++;
-                            }
-                            w = 0;
-                            h++;
-                        }
+                    if (r_flags & 2) {
+                        hx = (int16_t)(r_xy & 0xffff);
+                        hy = (int16_t)(r_xy >> 16);
+                        hsad = r_sad;
                     }
                     cx = hx;
                     cy = hy;
@@ -565,34 +573,40 @@ __device__ void set_final_search_centre(StageState *s, const SvtMeParams &p) {
                 cx = 0;
                 cy = 0;
             }
-            s->sr[li][ri].hme_sc_x = cx;
-            s->sr[li][ri].hme_sc_y = cy;
-            s->sr[li][ri].hme_sad = hsad;
+            if (r == t.tl) {
+                my_x = cx;
+                my_y = cy;
+                my_sad = hsad;
+            }
         }
+    }
+    if (inr) {
+        s->sr[li][ri].hme_sc_x = my_x;
+        s->sr[li][ri].hme_sc_y = my_y;
+        s->sr[li][ri].hme_sad = my_sad;
+        out_x = my_x; out_y = my_y; out_sad = my_sad;
+    } else {
+        out_x = s->sr[li][ri].hme_sc_x;
+        out_y = s->sr[li][ri].hme_sc_y;
+        out_sad = s->sr[li][ri].hme_sad;
+    }
 }
 
-// hme_prune_ref_and_adjust_sr :2547-2588 — loops cover all 2x4 slots incl. unused ones.
-__device__ void hme_prune_ref_and_adjust_sr(StageState *s, const SvtMeParams &p) {
+// hme_prune_ref_and_adjust_sr :2547-2588 — covers all 2x4 slots incl. unused ones. (x, y, sad): this slot's search result.
+__device__ __forceinline__ void team_hme_prune_and_adjust(StageState *s, const SvtMeParams &p, const Team &t, int16_t x, int16_t y,
+                                                          unsigned long long sad) {
     const uint16_t th = p.prune_ref_if_hme_sad_dev_bigger_than_th;
     if (p.enable_me_hme_ref_pruning && th != (uint16_t)~0) {
-        unsigned long long best = ~0ULL;
-        for (int li = 0; li < NL; ++li)
-            for (int ri = 0; ri < NR; ++ri)
-                if (s->sr[li][ri].hme_sad < best) best = s->sr[li][ri].hme_sad;
-        for (int li = 0; li < NL; ++li)
-            for (int ri = 1; ri < NR; ++ri)
-                if ((s->sr[li][ri].hme_sad - best) * 100 > ((unsigned long long)th * best)) s->sr[li][ri].do_ref = 0;
+        const unsigned long long best = team_min(t, sad);
+        if (t.ri >= 1 && (sad - best) * 100 > ((unsigned long long)th * best)) s->sr[t.li][t.ri].do_ref = 0;
     }
-    if (p.enable_me_sr_adjustment)
-        for (int li = 0; li < NL; ++li)
-            for (int ri = 0; ri < NR; ++ri) {
-                const RefResult &r = s->sr[li][ri];
-                if (iabs(r.hme_sc_x) <= p.reduce_me_sr_based_on_mv_length_th &&
-                    iabs(r.hme_sc_y) <= p.reduce_me_sr_based_on_mv_length_th && r.hme_sad < p.stationary_hme_sad_abs_th)
-                    s->div[li][ri] = p.stationary_me_sr_divisor;
-                else if (r.hme_sad < p.reduce_me_sr_based_on_hme_sad_abs_th)
-                    s->div[li][ri] = p.me_sr_divisor_for_low_hme_sad;
-            }
+    if (p.enable_me_sr_adjustment) {
+        if (iabs(x) <= p.reduce_me_sr_based_on_mv_length_th && iabs(y) <= p.reduce_me_sr_based_on_mv_length_th &&
+            sad < p.stationary_hme_sad_abs_th)
+            s->div[t.li][t.ri] = p.stationary_me_sr_divisor;
+        else if (sad < p.reduce_me_sr_based_on_hme_sad_abs_th)
+            s->div[t.li][t.ri] = p.me_sr_divisor_for_low_hme_sad;
+    }
 }
 
 // integer_search_b64 :1249-1586, one reference, split at the points where a SAD search is needed.

@@ -45,11 +45,12 @@ __host__ __device__ __forceinline__ bool l0_dependent(const SvtMeParams &p) { //
         p.reduce_hme_l0_sr_th_max;
 }
 
-// ---------------------------------------------------------------- scalar steps (one thread per b64)
+// ---------------------------------------------------------------- scalar steps (a team of 8 lanes per b64, svtme_scalar.cuh)
 enum { S_INIT = 0, S_ZZ, S_PREHME1, S_PREHME2, S_L0A, S_L0B, S_L1, S_L2, S_N };
+#define SCALAR_TEAM 8
 
 template <int STEP>
-__device__ __forceinline__ void scalar_step(const WideArgs &a, int gid) {
+__device__ __forceinline__ void scalar_step(const WideArgs &a, int gid, const Team &t) {
     const DevJob &J = a.jobs[gid / a.b64_per_job];
     const uint32_t b64 = (uint32_t)(gid % a.b64_per_job);
     const SvtMeParams &p = J.prm;
@@ -58,74 +59,77 @@ __device__ __forceinline__ void scalar_step(const WideArgs &a, int gid) {
     const bool hme_l1 = p.enable_hme_flag && p.enable_hme_level1_flag;
     const bool hme_l2 = p.enable_hme_flag && p.enable_hme_level2_flag;
     const bool zz = p.me_early_exit_th || p.me_safe_limit_zz_th;
-    if (STEP != S_INIT) prefetch_hot_state(s);
+    // nj: the jobs of the round that just ran (every lane reads it before lane 0 replaces it at the end of the step);
+    // total: the jobs this step posts for the next round. The team synchronises wherever a lane reads what another wrote.
+    const int nj = STEP == S_INIT ? 0 : s->n_jobs;
+    __syncwarp(t.mask);
+    int total = 0;
     if (STEP == S_INIT) { // the state block was zero-filled by the host (best tables start at 0)
-        s->org_x = (int)(b64 % J.b64_cols) * 64;
-        s->org_y = (int)(b64 / J.b64_cols) * 64;
-        s->pic_w = J.width;
-        s->pic_h = J.height;
-        s->b64_w = min(64, J.width - s->org_x);
-        s->b64_h = min(64, J.height - s->org_y);
-        init_state_zeroed(s, p);
-        s->n_jobs = 0;
-        if (zz) plan_zz(s, J);
-    } else if (STEP == S_ZZ) {
-        if (zz) post_zz(s, p);
-        s->n_jobs = 0;
-        if (p.prehme_enable) {
-            plan_prehme(s, J, 0);
-            // list 1 depends on list 0 only through prehme_l1_early_exit (:1763-1788): otherwise both
-            // lists are one round
-            if (p.num_of_list_to_search > 1 && !p.prehme_l1_early_exit) plan_prehme(s, J, 1, true);
+        const int org_x = (int)(b64 % J.b64_cols) * 64, org_y = (int)(b64 / J.b64_cols) * 64;
+        if (t.tl == 0) {
+            s->org_x = org_x;
+            s->org_y = org_y;
+            s->pic_w = J.width;
+            s->pic_h = J.height;
+            s->b64_w = min(64, J.width - org_x);
+            s->b64_h = min(64, J.height - org_y);
         }
+        team_init_state(s, p, t);
+        if (zz) total = team_plan_zz(s, J, t, org_x, org_y);
+    } else if (STEP == S_ZZ) {
+        if (zz) team_post_zz(s, p, t, nj);
+        __syncwarp(t.mask);
+        // list 1 depends on list 0 only through prehme_l1_early_exit (:1763-1788): otherwise both lists are one round
+        if (p.prehme_enable) total = team_plan_prehme(s, J, t, true, p.num_of_list_to_search > 1 && !p.prehme_l1_early_exit);
     } else if (STEP == S_PREHME1) {
-        if (p.prehme_enable) post_prehme_jobs(s, p);
-        s->n_jobs = 0;
-        if (p.prehme_enable && p.num_of_list_to_search > 1 && p.prehme_l1_early_exit) plan_prehme(s, J, 1);
+        if (p.prehme_enable) team_post_prehme_jobs(s, p, t, nj);
+        __syncwarp(t.mask);
+        if (p.prehme_enable && p.num_of_list_to_search > 1 && p.prehme_l1_early_exit) total = team_plan_prehme(s, J, t, false, true);
     } else if (STEP == S_PREHME2) {
         if (p.prehme_enable) {
-            post_prehme_jobs(s, p);
-            post_prehme_final(s, p);
+            team_post_prehme_jobs(s, p, t, nj);
+            __syncwarp(t.mask);
+            team_post_prehme_final(s, p, t);
         }
-        s->n_jobs = 0;
-        if (hme_l0) plan_l0(s, J, l0_dependent(p), false);
+        __syncwarp(t.mask);
+        if (hme_l0) total = team_plan_l0(s, J, t, l0_dependent(p), false);
     } else if (STEP == S_L0A) {
-        if (hme_l0) {
-            post_level_jobs(s, p, 0, 4);
-            post_l0_prehme(s, p);
-        }
-        s->n_jobs = 0;
-        if (hme_l0 && l0_dependent(p)) plan_l0(s, J, false, true);
+        if (hme_l0 && team_post_level_jobs(s, p, t, nj, 0, 4)) team_post_l0_prehme(s, p, t);
+        __syncwarp(t.mask);
+        if (hme_l0 && l0_dependent(p)) total = team_plan_l0(s, J, t, false, true);
     } else if (STEP == S_L0B) {
-        if (hme_l0 && l0_dependent(p)) {
-            post_level_jobs(s, p, 0, 4);
-            post_l0_prehme(s, p);
-        }
-        s->n_jobs = 0;
-        if (hme_l1) plan_l1(s, J);
+        if (hme_l0 && l0_dependent(p) && team_post_level_jobs(s, p, t, nj, 0, 4)) team_post_l0_prehme(s, p, t);
+        __syncwarp(t.mask);
+        if (hme_l1) total = team_plan_refine(s, J, t, 1);
     } else if (STEP == S_L1) {
-        if (hme_l1) post_level_jobs(s, p, 1, 2);
-        s->n_jobs = 0;
-        if (hme_l2) plan_l2(s, J);
+        if (hme_l1) team_post_level_jobs(s, p, t, nj, 1, 2);
+        __syncwarp(t.mask);
+        if (hme_l2) total = team_plan_refine(s, J, t, 2);
     } else if (STEP == S_L2) {
-        if (hme_l2) post_level_jobs(s, p, 2, 1);
-        s->n_jobs = 0;
-        set_final_search_centre(s, p);
-        if (p.me_type == 1) // ME_MCTF (:3173-3183): no pruning / area adjustment; early return when the HME SAD is small enough
-            s->tf_exit = s->sr[0][0].hme_sad < p.tf_me_exit_th;
-        else if (p.enable_hme_flag)
-            hme_prune_ref_and_adjust_sr(s, p);
+        if (hme_l2) team_post_level_jobs(s, p, t, nj, 2, 1);
+        __syncwarp(t.mask);
+        int16_t x, y;
+        unsigned long long sad;
+        team_final_search_centre(s, p, t, x, y, sad);
+        if (p.me_type == 1) { // ME_MCTF (:3173-3183): no pruning / area adjustment; early return when the HME SAD is small enough
+            if (t.tl == 0) s->tf_exit = sad < p.tf_me_exit_th;
+        } else if (p.enable_hme_flag)
+            team_hme_prune_and_adjust(s, p, t, x, y, sad);
     }
+    __syncwarp(t.mask);
+    if (t.tl == 0) s->n_jobs = total;
+    __syncwarp(t.mask);
 }
 
 // Steps [FIRST, LAST] back to back in one launch: used where no search round separates them in this batch
 // (e.g. the two pre-HME post steps when list 1 does not wait for list 0).
 template <int FIRST, int LAST>
 __global__ void __launch_bounds__(128) scalar_kernel(WideArgs a) {
-    const int gid = blockIdx.x * blockDim.x + threadIdx.x;
-    if (gid >= a.n_b64_total) return;
-    scalar_step<FIRST>(a, gid);
-    if (LAST != FIRST) scalar_step<LAST>(a, gid);
+    const int gid = (int)((blockIdx.x * blockDim.x + threadIdx.x) / SCALAR_TEAM);
+    if (gid >= a.n_b64_total) return; // (whole teams leave together)
+    const Team t = team_of();
+    scalar_step<FIRST>(a, gid, t);
+    if (LAST != FIRST) scalar_step<LAST>(a, gid, t);
 }
 
 // ---------------------------------------------------------------- HME engine launch (one CTA per b64)
@@ -906,7 +910,7 @@ void svtme_launch_me_stage(const DevJob *d_jobs, int n_jobs, int b64_cols, int b
     a.st = reinterpret_cast<StageState *>(d_states);
     a.b64_per_job = b64_per_job;
     a.n_b64_total = n_jobs * b64_per_job;
-    const int N = a.n_b64_total, sg = (N + 127) / 128;
+    const int N = a.n_b64_total, sg = (N * SCALAR_TEAM + 127) / 128;
     int slot = 0;
     auto mark = [&]() {
         if (ev) cudaEventRecord(ev[slot], st);

@@ -631,12 +631,38 @@ __global__ void __launch_bounds__(128) points_kernel(WideArgs a) {
 // SMALL: every search area of the batch is small enough for the raw-staged full-pel path (decided on
 // the host from the parameters; a larger area would still be searched correctly, only slower), so
 // the CTA needs only a 10 KB arena: more CTAs per SM.
+// Outcome of the planning the lean kernel does up front for every reference of its b64 (plan_int_a / _b / _c, one lane per
+// reference): 16 bytes per reference, the budget that keeps 14 CTAs per SM.
+struct IntPlanRec {
+    int16_t fp_sa_w, fp_sa_h, fp_ox, fp_oy, fp_xc, fp_yc;
+    uint8_t fp_do, fp_probe, fp_phase, _pad;
+};
 template <bool SMALL>
 struct IntSmem {
     IntState st;
     DevJob job;
+    IntPlanRec rec[SMALL ? NL * NR : 1];
+    int n_c00;
     __align__(16) uint8_t src64[64 * 64];
     __align__(16) uint8_t arena[SMALL ? SVTME_FP_SMALL_ARENA_BYTES : SVTME_ARENA_BYTES];
+};
+
+// What plan_int_a / _b / _c read and write for ONE reference when a lane plans it on its own: the slot's HME results are
+// read in place from the state block (global memory), the two check_00_center jobs and the plan live with the lane.
+struct IntLaneView {
+    int org_x, org_y, b64_w, b64_h, pic_w, pic_h;
+    const RefResult (*sr)[NR];
+    const uint32_t (*div)[NR];
+    const uint32_t (*zz)[NR];
+    const uint32_t (*best_sad)[NR][SVTME_PU_COUNT];
+    HJob *jobs;
+    JobMeta *meta;
+    uint8_t (*job_idx)[NR][4];
+    int n_jobs;
+    int fp_do, fp_sa_w, fp_sa_h, fp_ox, fp_oy, fp_probe, fp_phase;
+    int16_t fp_xc, fp_yc;
+    int c00_needed;
+    uint32_t fp_var;
 };
 
 #define T0(stmt)                        \
@@ -739,6 +765,129 @@ __device__ __forceinline__ void int_one_ref(IntSmem<SMALL> *sm, StageState *g, i
     }
 }
 
+// The lean kernel's planning, hoisted: lane k of warp 0 plans the k-th reference of the launch's slot list (plan_int_a),
+// the check_00_center SADs of ALL references that need them run as one round of points (two jobs per reference, compacted
+// at the start of the arena, which no search uses yet), then the lanes finish (plan_int_b, and plan_int_c where no probe
+// follows). Before: every reference in turn copied its slot state to shared memory and planned on thread 0 with the
+// other 63 threads at a barrier — a global round trip, ~250 single-lane instructions and three barriers per reference.
+template <bool SMALL>
+__device__ __forceinline__ void int_plan_all(IntSmem<SMALL> *sm, const StageState *g, const IntSlots &sl, unsigned todo, unsigned long long &work) {
+    const int tid = threadIdx.x, lane = tid & 31;
+    const DevJob &J = sm->job;
+    HJob *c00_jobs = reinterpret_cast<HJob *>(sm->arena);               // [2 * NL * NR]
+    JobMeta *junk_meta = reinterpret_cast<JobMeta *>(sm->arena + 1024); // add_job's bookkeeping nobody reads here
+    uint8_t(*junk_idx)[NR][4] = reinterpret_cast<uint8_t(*)[NR][4]>(sm->arena + 1024 + 512);
+    IntLaneView v;
+    HJob mine[2];
+    bool c00 = false, planned = false;
+    int li = 0, ri = 0, base = 0;
+    if (tid < 32) {
+        planned = lane < sl.n && (todo >> lane & 1);
+        if (planned) {
+            li = sl.slot[lane] / NR;
+            ri = sl.slot[lane] % NR;
+            v.org_x = g->org_x; v.org_y = g->org_y;
+            v.b64_w = g->b64_w; v.b64_h = g->b64_h;
+            v.pic_w = g->pic_w; v.pic_h = g->pic_h;
+            v.sr = g->sr; v.div = g->div; v.zz = g->zz; v.best_sad = g->best_sad;
+            v.jobs = mine;
+            v.meta = junk_meta + 2 * lane;
+            v.job_idx = junk_idx;
+            v.fp_sa_w = v.fp_sa_h = v.fp_ox = v.fp_oy = v.fp_probe = 0;
+            v.fp_xc = v.fp_yc = 0;
+            v.fp_var = 0;
+            plan_int_a(&v, J, li, ri);
+            v.fp_phase = 0;
+            c00 = v.n_jobs == 2;
+        }
+        const unsigned cmask = __ballot_sync(0xffffffffu, c00);
+        base = 2 * __popc(cmask & ((1u << lane) - 1u));
+        if (c00) {
+            c00_jobs[base] = mine[0];
+            c00_jobs[base + 1] = mine[1];
+        }
+        if (lane == 0) sm->n_c00 = 2 * __popc(cmask);
+    }
+    __syncthreads(); // (also publishes the source block staged by the caller)
+    const int n_c00 = sm->n_c00;
+    if (n_c00) { // check_00_center: two single-position SADs per reference
+        const HBlk blk_zz = make_hblk(sm->src64, 128, g->b64_w, g->b64_h >> 1, 2);
+        hme_points(blk_zz, c00_jobs, n_c00); // (ends with a barrier)
+        work += (unsigned long long)n_c00 * blk_zz.bw * blk_zz.nrows;
+    }
+    if (planned) {
+        if (c00) v.jobs = c00_jobs + base;
+        plan_int_b(&v, J, li, ri);
+        v.fp_phase = 1;
+        if (!v.fp_probe) {
+            plan_int_c(&v, J);
+            v.fp_phase = 2;
+        }
+        IntPlanRec &r = sm->rec[lane];
+        r.fp_sa_w = (int16_t)v.fp_sa_w; r.fp_sa_h = (int16_t)v.fp_sa_h;
+        r.fp_ox = (int16_t)v.fp_ox; r.fp_oy = (int16_t)v.fp_oy;
+        r.fp_xc = v.fp_xc; r.fp_yc = v.fp_yc;
+        r.fp_do = (uint8_t)v.fp_do; r.fp_probe = (uint8_t)v.fp_probe; r.fp_phase = (uint8_t)v.fp_phase;
+    }
+    __syncthreads();
+}
+
+// integer_search_b64 for ONE (list, reference) whose plan is in sm->rec[k]: tables, the 8x8-variance probe, the search
+// (or parking it for the big-arena kernel), the write-back. All threads call with identical arguments.
+template <bool SMALL>
+__device__ __forceinline__ void int_one_ref_planned(IntSmem<SMALL> *sm, StageState *g, int k, int li, int ri, int mode, unsigned long long &work) {
+    const int tid = threadIdx.x;
+    IntState *s = &sm->st;
+    const DevJob &J = sm->job;
+    const SvtMeParams &p = J.prm;
+    __syncthreads(); // the previous reference of this CTA is done with the state and the tables
+    if (tid == 0) {
+        const IntPlanRec &r = sm->rec[k];
+        s->org_x = g->org_x; s->org_y = g->org_y;
+        s->pic_w = g->pic_w; s->pic_h = g->pic_h;
+        s->fp_do = r.fp_do; s->fp_probe = r.fp_probe; s->fp_phase = r.fp_phase;
+        s->fp_sa_w = r.fp_sa_w; s->fp_sa_h = r.fp_sa_h; s->fp_ox = r.fp_ox; s->fp_oy = r.fp_oy;
+        s->fp_xc = r.fp_xc; s->fp_yc = r.fp_yc;
+    }
+    const int org_x = g->org_x, org_y = g->org_y;
+    // svt_initialize_buffer_32bits(p_sb_best_sad, 21, 1, MAX_SAD_VALUE) :1368
+    for (int pu = tid; pu < SVTME_PU_COUNT; pu += (int)blockDim.x) {
+        s->tab.key[pu] = (unsigned long long)SVTME_MAX_SAD_VALUE << 32;
+        s->tab.mv[pu] = 0;
+    }
+    __syncthreads();
+    const bool sub_sad = p.me_search_method == 0;
+    const DevPlane &pl = J.ref[li][ri].lvl[0];
+    if (s->fp_phase == 1) {
+        const int xc = s->fp_xc, yc = s->fp_yc;
+        fullpel_probe(sm->src64, pl.at(org_x + xc, org_y + yc), pl.stride, xc, yc, sub_sad, 1, &s->tab);
+        work += 64ull * (sub_sad ? 32 : 64);
+        if (tid < 32) {
+            const uint32_t var = probe_variance(s);
+            if (tid == 0) {
+                s->fp_var = var;
+                plan_int_c(s, J);
+            }
+        }
+        __syncthreads();
+    }
+    const bool park = mode == INT_DEFER && s->fp_sa_w * s->fp_sa_h > SVTME_FP_DIRECT_MAX;
+    if (!park) {
+        const int ox = s->fp_ox, oy = s->fp_oy;
+        fullpel_search(sm->src64, pl.at(org_x + ox, org_y + oy), pl.stride, ox, oy, s->fp_sa_w, s->fp_sa_h, sub_sad, 2,
+                       &s->tab, sm->arena, (int)sizeof(sm->arena));
+        work += (unsigned long long)s->fp_sa_w * s->fp_sa_h * 64ull * (sub_sad ? 32 : 64);
+    } else if (tid == 0) {
+        g->fp_parked[li][ri][0] = (int16_t)s->fp_ox; g->fp_parked[li][ri][1] = (int16_t)s->fp_oy;
+        g->fp_parked[li][ri][2] = (int16_t)s->fp_sa_w; g->fp_parked[li][ri][3] = (int16_t)s->fp_sa_h;
+        g->fp_deferred[li][ri] = 1;
+    }
+    for (int pu = tid; pu < SVTME_PU_COUNT; pu += (int)blockDim.x) {
+        g->best_sad[li][ri][pu] = (uint32_t)(s->tab.key[pu] >> 32);
+        g->best_mv[li][ri][pu] = s->tab.mv[pu];
+    }
+}
+
 // One CTA per b64: job descriptor and source block go to shared memory once, then the references of the
 // launch's slot list run one after the other (slot order = the reference's loop order, so a reference that
 // depends on (list 0, ref 0)'s result, :1345-1350, finds it in the state block).
@@ -779,8 +928,13 @@ __global__ void __launch_bounds__(SMALL ? SVTME_INT_SMALL_THREADS : SVTME_THREAD
         cp_async_wait_all(); // (the first __syncthreads of int_one_ref publishes the block to the CTA)
     }
     unsigned long long work = 0;
-    for (int k = 0; k < sl.n; ++k)
-        if (todo >> k & 1) int_one_ref<SMALL>(sm, g, sl.slot[k] / NR, sl.slot[k] % NR, mode, work);
+    if (SMALL && mode != INT_RESUME) { // (the lean kernel: every reference planned up front, then one after the other)
+        int_plan_all<SMALL>(sm, g, sl, todo, work);
+        for (int k = 0; k < sl.n; ++k)
+            if (todo >> k & 1) int_one_ref_planned<SMALL>(sm, g, k, sl.slot[k] / NR, sl.slot[k] % NR, mode, work);
+    } else
+        for (int k = 0; k < sl.n; ++k)
+            if (todo >> k & 1) int_one_ref<SMALL>(sm, g, sl.slot[k] / NR, sl.slot[k] % NR, mode, work);
     if (tid == 0 && Jg.work_ops) atomicAdd(Jg.work_ops + 6, work);
 }
 

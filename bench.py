@@ -378,6 +378,8 @@ def run_kernel_workload(args, wl):
 
 
 def main():
+    if os.environ.get("SVTME_BENCH_LIB"):  # development aid: an experimental build of the library (tools/build_variant.sh)
+        importlib.import_module(PKG + ".abi").LIB_PATH = os.path.join(ROOT, os.environ["SVTME_BENCH_LIB"])
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)

@@ -781,6 +781,7 @@ __device__ __forceinline__ void int_plan_all(IntSmem<SMALL> *sm, const StageStat
     HJob mine[2];
     bool c00 = false, planned = false;
     int li = 0, ri = 0, base = 0;
+    __syncthreads(); // the job descriptor and the source block were staged by all threads (cp.async, each waited for its own)
     if (tid < 32) {
         planned = lane < sl.n && (todo >> lane & 1);
         if (planned) {
@@ -808,7 +809,7 @@ __device__ __forceinline__ void int_plan_all(IntSmem<SMALL> *sm, const StageStat
         }
         if (lane == 0) sm->n_c00 = 2 * __popc(cmask);
     }
-    __syncthreads(); // (also publishes the source block staged by the caller)
+    __syncthreads();
     const int n_c00 = sm->n_c00;
     if (n_c00) { // check_00_center: two single-position SADs per reference
         const HBlk blk_zz = make_hblk(sm->src64, 128, g->b64_w, g->b64_h >> 1, 2);

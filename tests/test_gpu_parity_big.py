@@ -112,3 +112,42 @@ def test_long_line_pictures_strip_segments(size, preset):
         specs.append((U.finish_params(product_params(d), d, c, r), c, r))
     check_against_cpu(seq, specs, W, H)
     check_against_cpu(seq, specs[:1], W, H, one_batch=False)
+
+
+def test_many_small_batches_of_different_pictures_in_flight():
+    """Queued form under stress: 18 batches of one or two pictures each — presets 4 and 8 alternating (different kernels,
+    reference counts and job descriptors) — in flight on the library's two compute streams, three rounds. CTAs of different
+    batches then interleave on every SM; each must work from its own job descriptor and state. (The one bug of this kind so
+    far — a kernel that read its descriptor from shared memory before the staging copy had landed — only showed in the queued
+    4K run of bench.py, whose own parity check and tools/repro_e2e.py cover that size.)"""
+    W, H = 640, 360
+    seq = U.synth_sequence(W, H, 9, seed=5, noise=3.0)
+    groups = []
+    for preset, n_l0, n_l1 in ((4, 2, 2), (8, 2, 1)):
+        specs = workload_specs(W, H, preset, 9, 3, n_l0, n_l1, list(range(8)))
+        groups.append(specs)
+    with me.MeSession(0, W, H, capacity=9) as ses:
+        ses.put_pictures(list(range(9)), [np.ascontiguousarray(f).ctypes.data for f in seq], W)
+        want = []
+        for specs in groups:
+            jobs, outs = ses.make_jobs(specs, deep=True)
+            ses.run_jobs(jobs)
+            want.append(outs)
+        for rnd in range(3):
+            queued = []
+            pos = [0, 0]
+            k = 0
+            while pos[0] < 8 or pos[1] < 8:
+                g = k % 2 if pos[k % 2] < 8 else 1 - k % 2
+                n = 1 + (k + rnd) % 2
+                part = groups[g][pos[g]:pos[g] + n]
+                jobs, outs = ses.make_jobs(part, deep=True)
+                ses.submit_jobs(jobs)
+                queued.append((jobs, outs, g, pos[g]))
+                pos[g] += len(part)
+                k += 1
+            for jobs, outs, g, first in queued:
+                ses.collect_jobs(jobs)
+                for i, o in enumerate(outs):
+                    for name in o:
+                        assert np.array_equal(o[name], want[g][first + i][name]), (rnd, g, first + i, name)

@@ -2,7 +2,8 @@
 # build_encoder.sh — builds the reference ENCODER (C-only, stock cmake) with the dump / replay hooks of svtme_dump.c
 # from a scratch copy of /root/reference, and leaves the binary in oracle/_ref/SvtAv1EncApp_dump (git-ignored; it
 # travels to the GPU box with the snapshot). TEST INFRASTRUCTURE ONLY. Nothing of the reference is copied into the
-# repository: the patch is two inserted calls, applied by pattern to the scratch copy.
+# repository: the patch is four inserted calls (two around the ME of a b64, one in the dynamic-GOP detector, one after
+# the picture statistics), applied by pattern to the scratch copy.
 set -euo pipefail
 HERE="$(cd "$(dirname "$0")" && pwd)"
 REF="${REF:-/root/reference}"
@@ -28,6 +29,25 @@ decl = ("struct MeContext;\nvoid svtme_hook_pre_b64(struct MeContext *ctx);\n"
 m = list(re.finditer(r'^#include .*$', s, re.M))[-1]
 s = s[:m.end()] + "\n" + decl + s[m.end():]
 open(p, "w").write(s)
+# (2) the dynamic-GOP detector: metrics of a finished frame, taken under the detector's mutex right before the frame is
+# signalled done (afterwards picture decision resets them for the next comparison)
+p3 = d + "/pd_process.c"
+s3 = open(p3).read()
+dg = re.search(r"svt_post_semaphore\(ppcs->dg_detector->frame_done_sem\);", s3)
+assert dg, "frame_done_sem post not found in pd_process.c"
+s3 = s3[:dg.start()] + "{ svtme_hook_post_dg(ppcs); " + dg.group(0) + " }" + s3[dg.end():]
+m3 = list(re.finditer(r'^#include .*$', s3, re.M))[-1]
+s3 = s3[:m3.end()] + "\nvoid svtme_hook_post_dg(PictureParentControlSet *pcs);\n" + s3[m3.end():]
+open(p3, "w").write(s3)
+# (3) picture analysis: the statistics right after they are gathered
+p2 = d + "/pic_analysis_process.c"
+s2 = open(p2).read()
+st = re.search(r"pa_ref_obj_->avg_luma\s*=\s*pcs->avg_luma;", s2)
+assert st, "statistics call site not found in pic_analysis_process.c"
+s2 = s2[:st.end()] + "\n                svtme_hook_post_statistics(scs, pcs);" + s2[st.end():]
+m2 = list(re.finditer(r'^#include .*$', s2, re.M))[-1]
+s2 = s2[:m2.end()] + "\nvoid svtme_hook_post_statistics(SequenceControlSet *scs, PictureParentControlSet *pcs);\n" + s2[m2.end():]
+open(p2, "w").write(s2)
 c = d + "/CMakeLists.txt"
 t = open(c).read()
 assert "set(all_files" in t

@@ -231,3 +231,62 @@ void svtme_hook_post_b64(PictureParentControlSet *pcs, uint32_t b64, MeContext *
         free(rec);
     }
 }
+
+/* ---- picture statistics and dynamic-GOP detector: what the real encoder computed, for tests/golden/encdump_aux_*.npz ----
+ * svtme_hook_post_statistics: called right after svt_aom_gathering_picture_statistics (pic_analysis_process.c:2137).
+ *   <dir>/stats_%06llu.bin = 16 uint32 {magic 'SVST', width, height, n_b64, n_var, calc_hist, calculate_variance,
+ *   block_mean_prec_sub, all_block_sizes, scene_change_detection, regions_w, regions_h, pic_avg_variance, 0, 0, 0},
+ *   uint64 avg_luma, uint64 average_intensity[4][4], uint32 histogram[4][4][256], uint16 variance[n_b64][n_var].
+ * svtme_hook_post_dg: called inside dg_detector_hme_level0 (pd_process.c:584-586) when the last segment is done, under the
+ *   detector's mutex, right before the frame is signalled done:
+ *   <dir>/dg_%06llu_%06llu.bin (source, reference) = uint64 tot_dist, uint32 tot_cplx, tot_active, int32 sum_in_vectors,
+ *   uint32 input_resolution. */
+void svtme_hook_post_statistics(SequenceControlSet *scs, PictureParentControlSet *pcs) {
+    hook_init();
+    if (!g_dump_dir) return;
+    char path[600];
+    snprintf(path, sizeof(path), "%s/stats_%06llu.bin", g_dump_dir, (unsigned long long)pcs->picture_number);
+    FILE *f = fopen(path, "wb");
+    if (!f) { perror("svtme_dump stats"); abort(); }
+    const uint32_t all = scs->static_config.enable_adaptive_quantization == 1 || scs->static_config.variance_octile;
+    const uint32_t n_var = all ? 85 : 1;
+    const uint32_t hd[16] = {0x54535653u, pcs->aligned_width, pcs->aligned_height, pcs->b64_total_count, n_var, scs->calc_hist,
+                             scs->calculate_variance, scs->block_mean_calc_prec == BLOCK_MEAN_PREC_SUB, all,
+                             scs->static_config.scene_change_detection != 0, scs->picture_analysis_number_of_regions_per_width,
+                             scs->picture_analysis_number_of_regions_per_height, pcs->pic_avg_variance, 0, 0, 0};
+    fwrite(hd, sizeof(hd), 1, f);
+    const uint64_t luma = pcs->avg_luma;
+    fwrite(&luma, 8, 1, f);
+    uint64_t inten[16];
+    static uint32_t hist[16 * 256];
+    memset(inten, 0, sizeof(inten));
+    memset(hist, 0, sizeof(hist));
+    if (scs->calc_hist)
+        for (uint32_t x = 0; x < scs->picture_analysis_number_of_regions_per_width; ++x)
+            for (uint32_t y = 0; y < scs->picture_analysis_number_of_regions_per_height; ++y) {
+                inten[x * 4 + y] = pcs->average_intensity_per_region[x][y];
+                memcpy(hist + (x * 4 + y) * 256, pcs->picture_histogram[x][y], 256 * sizeof(uint32_t));
+            }
+    fwrite(inten, sizeof(inten), 1, f);
+    fwrite(hist, sizeof(hist), 1, f);
+    if (scs->calculate_variance)
+        for (uint32_t b = 0; b < pcs->b64_total_count; ++b) fwrite(pcs->variance[b], sizeof(uint16_t), n_var, f);
+    fclose(f);
+}
+
+void svtme_hook_post_dg(PictureParentControlSet *pcs) {
+    hook_init();
+    if (!g_dump_dir || !pcs->dg_detector || !pcs->dg_detector->ref_pic) return;
+    const DGDetectorMetrics *m = &pcs->dg_detector->metrics;
+    if (m->seg_completed != (uint16_t)(pcs->me_segments_column_count * pcs->me_segments_row_count)) return;
+    char path[600];
+    snprintf(path, sizeof(path), "%s/dg_%06llu_%06llu.bin", g_dump_dir, (unsigned long long)pcs->picture_number,
+             (unsigned long long)pcs->dg_detector->ref_pic->picture_number);
+    FILE *f = fopen(path, "wb");
+    if (!f) { perror("svtme_dump dg"); abort(); }
+    const uint64_t dist = m->tot_dist;
+    const uint32_t rest[4] = {m->tot_cplx, m->tot_active, (uint32_t)m->sum_in_vectors, (uint32_t)pcs->input_resolution};
+    fwrite(&dist, 8, 1, f);
+    fwrite(rest, sizeof(rest), 1, f);
+    fclose(f);
+}

@@ -92,3 +92,29 @@ def struct_fields_equal(a, b, skip=()):
         elif va != vb:
             bad.append(name)
     return bad
+
+
+def read_stats(path):
+    """stats_%06d.bin of oracle/encoder_dump/svtme_dump.c (svtme_hook_post_statistics): parameters and results of the
+    encoder's own svt_aom_gathering_picture_statistics for one picture."""
+    raw = open(path, "rb").read()
+    hd = np.frombuffer(raw, dtype=np.uint32, count=16)
+    assert hd[0] == 0x54535653
+    n_b64, n_var = int(hd[3]), int(hd[4])
+    off = 64
+    out = {"params": hd[5:12].astype(np.int64), "size": hd[1:3].astype(np.int64),
+           "pic_avg_variance": np.array([hd[12]], np.uint16)}
+    out["avg_luma"] = np.frombuffer(raw, dtype=np.uint64, count=1, offset=off).copy(); off += 8
+    out["average_intensity_per_region"] = np.frombuffer(raw, dtype=np.uint64, count=16, offset=off).reshape(4, 4).copy(); off += 128
+    out["picture_histogram"] = np.frombuffer(raw, dtype=np.uint32, count=16 * 256, offset=off).reshape(4, 4, 256).copy(); off += 16 * 256 * 4
+    if hd[6]:
+        out["variance"] = np.frombuffer(raw, dtype=np.uint16, count=n_b64 * n_var, offset=off).reshape(n_b64, n_var).copy()
+    return out
+
+
+def read_dg(path):
+    """dg_%06d_%06d.bin (svtme_hook_post_dg): (tot_dist, tot_cplx, tot_active, sum_in_vectors, input_resolution)."""
+    raw = open(path, "rb").read()
+    dist = int(np.frombuffer(raw, dtype=np.uint64, count=1)[0])
+    r = np.frombuffer(raw, dtype=np.uint32, count=4, offset=8)
+    return [dist, int(r[0]), int(r[1]), int(np.int32(r[2])), int(r[3])]

@@ -28,6 +28,9 @@ CASES = [
     ("360p_p4", 640, 360, 10, 4, False, []),
     ("1080p_p8", 1920, 1080, 9, 8, False, []),
 ]
+# aux-only case (no ME dump kept): long enough for picture decision to evaluate a 32-picture mini-GOP, which is when the
+# dynamic-GOP detector compares pictures (eval_sub_mini_gop -> early_hme, pd_process.c:591-720)
+AUX_ONLY = [("dg_360p_p8", 640, 360, 67, 8, False, [])]
 ENC_ARGS = ["--fps", "30", "--lp", "1", "--enable-tf", "0", "--scm", "0"]
 
 
@@ -72,14 +75,29 @@ def make_case(name, w, h, n, preset, deep, extra):
             pack["hdr_%d" % pic] = np.frombuffer(bytes(hdr), dtype=np.uint8)
             for k, a in arrays.items():
                 pack["%s_%d" % (k, pic)] = a
-        out = os.path.join(HERE, "encdump_%s.npz" % name)
-        np.savez_compressed(out, **pack)
-        print(name, "pictures", pics, "->", out, os.path.getsize(out) // 1024, "KiB")
+        if (name, w, h, n, preset, deep, extra) not in AUX_ONLY:
+            out = os.path.join(HERE, "encdump_%s.npz" % name)
+            np.savez_compressed(out, **pack)
+            print(name, "pictures", pics, "->", out, os.path.getsize(out) // 1024, "KiB")
+        # what the same encode computed next to ME: picture statistics (every picture) and the dynamic-GOP detector's metrics
+        aux = {"meta": np.array([w, h, n, preset], dtype=np.int64)}
+        spics = sorted(int(f[6:12]) for f in os.listdir(ddir) if f.startswith("stats_"))
+        if n > 20:
+            spics = spics[:4]  # (the long clip is there for the DG detector)
+        aux["stats_pictures"] = np.array(spics, dtype=np.int64)
+        for pic in spics:
+            for k, a in E.read_stats(os.path.join(ddir, "stats_%06d.bin" % pic)).items():
+                aux["%s_%d" % (k, pic)] = a
+        dgs = sorted(f for f in os.listdir(ddir) if f.startswith("dg_"))
+        aux["dg"] = np.array([[int(f[3:9]), int(f[10:16])] + E.read_dg(os.path.join(ddir, f)) for f in dgs], dtype=np.int64).reshape(-1, 7)
+        out = os.path.join(HERE, "encdump_aux_%s.npz" % name)
+        np.savez_compressed(out, **aux)
+        print(name, "statistics of", len(spics), "pictures,", len(dgs), "DG-detector frames ->", out, os.path.getsize(out) // 1024, "KiB")
 
 
 if __name__ == "__main__":
     if not os.path.exists(APP):
         subprocess.check_call(["bash", os.path.join(U.ROOT, "oracle", "encoder_dump", "build_encoder.sh")])
-    for case in CASES:
+    for case in CASES + AUX_ONLY:
         if len(sys.argv) < 2 or case[0] in sys.argv[1:]:
             make_case(*case)

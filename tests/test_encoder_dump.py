@@ -168,3 +168,69 @@ def test_bitstream_is_identical_with_gpu_me_results(name, w, h, n, preset, tmp_p
     assert len(ref) > 1000
     assert ref == gpu, "bitstream written with the GPU's ME results differs from the reference encoder's"
     assert ref != bad, "falsified ME results did not change the bitstream: the replay hook is not live"
+
+
+# ---------------------------------------------------------------- next to ME: picture statistics and the DG detector
+AUX_CASES = [c for c in CASES + [a[0] for a in M.AUX_ONLY] if os.path.exists(os.path.join(GOLD, "encdump_aux_%s.npz" % c))]
+
+
+def load_aux(name):
+    z = np.load(os.path.join(GOLD, "encdump_aux_%s.npz" % name))
+    w, h, n, preset = (int(v) for v in z["meta"])
+    return z, w, h, U.synth_sequence(w, h, n, seed=1)
+
+
+def stats_params_of(z, pic):
+    v = [int(x) for x in z["params_%d" % pic]]  # calc_hist, calculate_variance, prec_sub, all_sizes, scd, regions w / h
+    return U.stats_params(calc_hist=v[0], calculate_variance=v[1], prec_sub=v[2], all_sizes=v[3], scd=v[4], regions=(v[5], v[6]))
+
+
+def assert_stats_equal(z, pic, p, got, what):
+    keys = ["pic_avg_variance", "avg_luma"] + (["variance"] if p.calculate_variance else []) + \
+        (["picture_histogram", "average_intensity_per_region"] if p.calc_hist else [])
+    for k in keys:
+        assert np.array_equal(z["%s_%d" % (k, pic)], got[k]), (what, pic, k)
+
+
+def test_aux_fixtures_exist():
+    assert len(AUX_CASES) >= 3 and "dg_360p_p8" in AUX_CASES, "tests/golden/encdump_aux_*.npz missing (tests/golden/make_encoder_dump.py writes them)"
+
+
+@pytest.mark.parametrize("name", AUX_CASES)
+def test_oracle_reproduces_the_encoders_picture_statistics_and_dg_metrics(name):
+    """What the real encoder's picture-analysis kernel left in pcs->variance / picture_histogram / avg_luma ... and what its
+    dynamic-GOP detector summed up, against the CPU checkers run on the synthetic frames."""
+    z, w, h, seq = load_aux(name)
+    checkers = ["orc"] + (["ref"] if U.ref_lib() is not None else [])
+    for which in checkers:
+        pyr = {}
+        for pic in z["stats_pictures"].tolist():
+            pyr[pic] = U.CpuPyramid(which, seq[pic], pic)
+            p = stats_params_of(z, pic)
+            assert_stats_equal(z, pic, p, U.cpu_picture_statistics(which, pyr[pic], p), which)
+        for src, ref, dist, cplx, active, inv, res in z["dg"].tolist():
+            for pic in (src, ref):
+                if pic not in pyr:
+                    pyr[pic] = U.CpuPyramid(which, seq[pic], pic)
+            assert U.cpu_dg_detector_hme(which, pyr[src], pyr[ref], res) == (dist, cplx, active, inv), (which, src, ref)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", AUX_CASES)
+def test_gpu_reproduces_the_encoders_picture_statistics_and_dg_metrics(name):
+    import importlib
+    me = importlib.import_module(U.PKG + ".me")
+    z, w, h, seq = load_aux(name)
+    n_b64 = ((w + 63) // 64) * ((h + 63) // 64)
+    with me.MeSession(0, w, h, capacity=len(seq)) as ses:
+        host = np.ascontiguousarray(seq)
+        ses.put_pictures(list(range(len(seq))), [host[i].ctypes.data for i in range(len(seq))], w)
+        for pic in z["stats_pictures"].tolist():
+            p = stats_params_of(z, pic)
+            out, arrays = U.abi.alloc_stats_out(n_b64, p)
+            assert ses.lib.svtme_picture_statistics(ses.h, pic, C.byref(p), C.byref(out)) == 0, ses.lib.svtme_last_error()
+            assert_stats_equal(z, pic, p, arrays, "gpu")
+        for src, ref, dist, cplx, active, inv, res in z["dg"].tolist():
+            m = U.abi.SvtMeDgMetrics()
+            assert ses.lib.svtme_dg_detector_hme(ses.h, src, ref, res, C.byref(m)) == 0, ses.lib.svtme_last_error()
+            assert (int(m.tot_dist), int(m.tot_cplx), int(m.tot_active), int(m.sum_in_vectors)) == (dist, cplx, active, inv), (src, ref)

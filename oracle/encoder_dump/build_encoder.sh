@@ -2,8 +2,8 @@
 # build_encoder.sh — builds the reference ENCODER (C-only, stock cmake) with the dump / replay hooks of svtme_dump.c
 # from a scratch copy of /root/reference, and leaves the binary in oracle/_ref/SvtAv1EncApp_dump (git-ignored; it
 # travels to the GPU box with the snapshot). TEST INFRASTRUCTURE ONLY. Nothing of the reference is copied into the
-# repository: the patch is four inserted calls (two around the ME of a b64, one in the dynamic-GOP detector, one after
-# the picture statistics), applied by pattern to the scratch copy.
+# repository: the patch is five inserted calls (two around the ME of a b64, one in the dynamic-GOP detector, one after
+# the picture statistics, one after the temporal filter's ME call), applied by pattern to the scratch copy.
 set -euo pipefail
 HERE="$(cd "$(dirname "$0")" && pwd)"
 REF="${REF:-/root/reference}"
@@ -48,6 +48,17 @@ s2 = s2[:st.end()] + "\n                svtme_hook_post_statistics(scs, pcs);" +
 m2 = list(re.finditer(r'^#include .*$', s2, re.M))[-1]
 s2 = s2[:m2.end()] + "\nvoid svtme_hook_post_statistics(SequenceControlSet *scs, PictureParentControlSet *pcs);\n" + s2[m2.end():]
 open(p2, "w").write(s2)
+# (4) temporal filter: the ME call of produce_temporally_filtered_pic
+p4 = d + "/temporal_filtering.c"
+s4 = open(p4).read()
+tf = re.search(r"svt_aom_motion_estimation_b64\(centre_pcs,.*?input_picture_ptr_central\);[^\n]*", s4, re.S)
+assert tf, "TF call site of svt_aom_motion_estimation_b64 not found in temporal_filtering.c"
+s4 = s4[:tf.end()] + ("\n                    svtme_hook_post_tf_b64(centre_pcs, (uint32_t)blk_row * blk_cols + blk_col, ctx, input_picture_ptr_central);"
+                      ) + s4[tf.end():]
+m4 = list(re.finditer(r'^#include .*$', s4, re.M))[-1]
+s4 = s4[:m4.end()] + ("\nvoid svtme_hook_post_tf_b64(PictureParentControlSet *centre, uint32_t b64, struct MeContext *ctx, "
+                      "EbPictureBufferDesc *central);\n") + s4[m4.end():]
+open(p4, "w").write(s4)
 c = d + "/CMakeLists.txt"
 t = open(c).read()
 assert "set(all_files" in t

@@ -290,3 +290,82 @@ void svtme_hook_post_dg(PictureParentControlSet *pcs) {
     fwrite(rest, sizeof(rest), 1, f);
     fclose(f);
 }
+
+/* ---- temporal-filter ME (ME_MCTF): what the real encoder hands to svt_aom_motion_estimation_b64 from
+ * produce_temporally_filtered_pic (temporal_filtering.c:3046-3080) and what it gets back ----
+ * svtme_hook_post_tf_b64: called right after that call. <dir>/tf_%06llu_%06llu.bin (centre picture, neighbouring frame):
+ *   a 4096-byte header {magic 'SVTMETF1', uint32 width, height, b64_cols, b64_rows, record_bytes, 0; uint64 centre, frame;
+ *   SvtMeTfDeriveInput as the encoder's pcs / scs had it; SvtMeParams rebuilt from the MeContext}, then one 696-byte record
+ *   per block: p_sb_best_sad[0][0][85], p_sb_best_mv[0][0][85], hme_sc_x, hme_sc_y (int16), 4 pad bytes, hme_sad (uint64).
+ *   <dir>/tfluma_%06llu_%06llu_{c,f}.bin: the two luma planes the call read (a neighbouring frame that was itself filtered
+ *   earlier is no longer the source picture; the fixture generator keeps only pairs of untouched frames). */
+typedef struct TfDumpHeader {
+    char               magic[8];
+    uint32_t           width, height, b64_cols, b64_rows, record_bytes, reserved;
+    uint64_t           centre, frame;
+    SvtMeTfDeriveInput tin;
+    SvtMeParams        params;
+} TfDumpHeader;
+#define TF_RECORD_BYTES (85 * 4 * 2 + 8 + 8)
+
+static void write_plane(const char *path, const EbPictureBufferDesc *pl, uint32_t W, uint32_t H) {
+    if (access(path, F_OK) == 0) return;
+    FILE *f = fopen(path, "wb");
+    if (!f) return;
+    for (uint32_t y = 0; y < H; ++y) fwrite(pl->buffer_y + (size_t)(pl->org_y + y) * pl->stride_y + pl->org_x, 1, W, f);
+    fclose(f);
+}
+
+void svtme_hook_post_tf_b64(PictureParentControlSet *centre, uint32_t b64, MeContext *ctx, EbPictureBufferDesc *central) {
+    hook_init();
+    if (!g_dump_dir) return;
+    SequenceControlSet *scs = centre->scs;
+    const uint64_t      frame = ctx->me_ds_ref_array[0][0].picture_number;
+    TfDumpHeader        h;
+    memset(&h, 0, sizeof(h));
+    memcpy(h.magic, "SVTMETF1", 8);
+    h.width = centre->aligned_width; h.height = centre->aligned_height;
+    h.b64_cols = (centre->aligned_width + 63) / 64; h.b64_rows = (centre->aligned_height + 63) / 64;
+    h.record_bytes = TF_RECORD_BYTES;
+    h.centre = centre->picture_number; h.frame = frame;
+    h.tin.enc_mode = centre->enc_mode;
+    h.tin.width = scs->max_input_luma_width; h.tin.height = scs->max_input_luma_height;
+    h.tin.qp = scs->static_config.qp;
+    h.tin.hme_me_level = centre->tf_ctrls.hme_me_level; h.tin.qp_opt = centre->tf_ctrls.qp_opt;
+    h.tin.me_exit_th = centre->tf_ctrls.me_exit_th;
+    h.tin.temporal_layer_index = centre->temporal_layer_index; h.tin.is_ref = centre->is_ref;
+    SvtMeParams *p = &h.params;
+    ctx_to_params(ctx, p);
+    p->num_of_list_to_search = ctx->num_of_list_to_search;
+    p->num_of_ref_pic_to_search[0] = ctx->num_of_ref_pic_to_search[0];
+    p->num_of_ref_pic_to_search[1] = 0;
+    p->temporal_layer_index = ctx->temporal_layer_index;
+    p->is_ref = ctx->is_ref;
+    p->picture_number = centre->picture_number;
+    p->ref_picture_number[0][0] = frame;
+    char path[1024];
+    snprintf(path, sizeof(path), "%s/tf_%06llu_%06llu.bin", g_dump_dir, (unsigned long long)h.centre, (unsigned long long)frame);
+    const int fd = open(path, O_CREAT | O_WRONLY, 0644);
+    if (fd < 0) { perror(path); abort(); }
+    uint8_t rec[TF_RECORD_BYTES];
+    memset(rec, 0, sizeof(rec));
+    memcpy(rec, ctx->p_sb_best_sad[0][0], 85 * 4);
+    memcpy(rec + 340, ctx->p_sb_best_mv[0][0], 85 * 4);
+    const int16_t sc[2] = {ctx->search_results[0][0].hme_sc_x, ctx->search_results[0][0].hme_sc_y};
+    memcpy(rec + 680, sc, 4);
+    const uint64_t hs = ctx->search_results[0][0].hme_sad;
+    memcpy(rec + 688, &hs, 8);
+    uint8_t hdr[DUMP_HEADER_BYTES] = {0};
+    memcpy(hdr, &h, sizeof(h));
+    if (pwrite(fd, hdr, sizeof(hdr), 0) != (ssize_t)sizeof(hdr) ||
+        pwrite(fd, rec, sizeof(rec), (off_t)DUMP_HEADER_BYTES + (off_t)b64 * TF_RECORD_BYTES) != (ssize_t)sizeof(rec)) {
+        perror("svtme_dump tf pwrite"); abort();
+    }
+    close(fd);
+    if (b64 == 0) {
+        snprintf(path, sizeof(path), "%s/tfluma_%06llu_%06llu_c.bin", g_dump_dir, (unsigned long long)h.centre, (unsigned long long)frame);
+        write_plane(path, central, h.width, h.height);
+        snprintf(path, sizeof(path), "%s/tfluma_%06llu_%06llu_f.bin", g_dump_dir, (unsigned long long)h.centre, (unsigned long long)frame);
+        write_plane(path, ctx->me_ds_ref_array[0][0].picture_ptr, h.width, h.height);
+    }
+}

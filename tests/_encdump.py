@@ -118,3 +118,20 @@ def read_dg(path):
     dist = int(np.frombuffer(raw, dtype=np.uint64, count=1)[0])
     r = np.frombuffer(raw, dtype=np.uint32, count=4, offset=8)
     return [dist, int(r[0]), int(r[1]), int(np.int32(r[2])), int(r[3])]
+
+
+class TfDumpHeader(C.Structure):
+    _fields_ = [("magic", C.c_char * 8)] + [(n, C.c_uint32) for n in ("width", "height", "b64_cols", "b64_rows", "record_bytes", "reserved")] + [
+        ("centre", C.c_uint64), ("frame", C.c_uint64), ("tin", abi.SvtMeTfDeriveInput), ("params", abi.SvtMeParams)]
+
+
+def read_tf_dump(path):
+    """tf_%06d_%06d.bin (svtme_hook_post_tf_b64): header + per block the tables / HME results of (list 0, ref 0)."""
+    raw = open(path, "rb").read()
+    h = TfDumpHeader.from_buffer_copy(raw[:C.sizeof(TfDumpHeader)])
+    assert h.magic == b"SVTMETF1" and h.record_bytes == 696
+    n = h.b64_cols * h.b64_rows
+    assert len(raw) == HEADER_BYTES + n * 696, (len(raw), n)
+    recs = np.frombuffer(raw, dtype=np.uint8, offset=HEADER_BYTES).reshape(n, 696)
+    return h, {"p_sb_best_sad": np.ascontiguousarray(recs[:, 0:340]).view("<u4"), "p_sb_best_mv": np.ascontiguousarray(recs[:, 340:680]).view("<u4"),
+               "hme_sc": np.ascontiguousarray(recs[:, 680:684]).view("<i2"), "hme_sad": np.ascontiguousarray(recs[:, 688:696]).view("<u8").reshape(n)}

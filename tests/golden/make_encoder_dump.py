@@ -31,6 +31,8 @@ CASES = [
 # aux-only case (no ME dump kept): long enough for picture decision to evaluate a 32-picture mini-GOP, which is when the
 # dynamic-GOP detector compares pictures (eval_sub_mini_gop -> early_hme, pd_process.c:591-720)
 AUX_ONLY = [("dg_360p_p8", 640, 360, 67, 8, False, [])]
+# temporal filter on: the ME_MCTF calls of produce_temporally_filtered_pic (name, width, height, frames, preset)
+TF_CASES = [("tf_360p_p8", 640, 360, 17, 8), ("tf_360p_p4", 640, 360, 9, 4)]
 ENC_ARGS = ["--fps", "30", "--lp", "1", "--enable-tf", "0", "--scm", "0"]
 
 
@@ -95,9 +97,43 @@ def make_case(name, w, h, n, preset, deep, extra):
         print(name, "statistics of", len(spics), "pictures,", len(dgs), "DG-detector frames ->", out, os.path.getsize(out) // 1024, "KiB")
 
 
+def make_tf_case(name, w, h, n, preset):
+    """encdump_tf_*.npz: per (centre picture, neighbouring frame) whose two planes are untouched synthetic frames, the
+    SvtMeTfDeriveInput of the encoder, the SvtMeParams rebuilt from its MeContext, and the tables / HME results per block."""
+    seq = U.synth_sequence(w, h, n, seed=1)
+    with tempfile.TemporaryDirectory() as tmp:
+        yuv, ddir = os.path.join(tmp, "in.yuv"), os.path.join(tmp, "dump")
+        os.mkdir(ddir)
+        write_yuv(yuv, seq)
+        cmd = [APP, "-i", yuv, "-w", str(w), "-h", str(h), "-n", str(n), "--preset", str(preset), "--fps", "30", "--lp", "1",
+               "--enable-tf", "1", "--scm", "0", "-b", os.path.join(tmp, "out.ivf")]
+        subprocess.run(cmd, check=True, env=dict(os.environ, SVTME_DUMP_DIR=ddir), stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        pack, pairs, dropped = {"meta": np.array([w, h, n, preset], dtype=np.int64)}, [], 0
+        for f in sorted(os.listdir(ddir)):
+            if not f.startswith("tf_"):
+                continue
+            c, fr = int(f[3:9]), int(f[10:16])
+            planes = [np.fromfile(os.path.join(ddir, "tfluma_%06d_%06d_%s.bin" % (c, fr, t)), dtype=np.uint8).reshape(h, w) for t in "cf"]
+            if not (np.array_equal(planes[0], seq[c]) and np.array_equal(planes[1], seq[fr])):
+                dropped += 1  # one of the two was already filtered: not reproducible from the synthetic clip
+                continue
+            hdr, arrays = E.read_tf_dump(os.path.join(ddir, f))
+            pairs.append((c, fr))
+            pack["hdr_%d_%d" % (c, fr)] = np.frombuffer(bytes(hdr), dtype=np.uint8)
+            for k, a in arrays.items():
+                pack["%s_%d_%d" % (k, c, fr)] = a
+        pack["pairs"] = np.array(pairs, dtype=np.int64).reshape(-1, 2)
+        out = os.path.join(HERE, "encdump_%s.npz" % name)
+        np.savez_compressed(out, **pack)
+        print(name, len(pairs), "(centre, frame) pairs kept,", dropped, "dropped ->", out, os.path.getsize(out) // 1024, "KiB")
+
+
 if __name__ == "__main__":
     if not os.path.exists(APP):
         subprocess.check_call(["bash", os.path.join(U.ROOT, "oracle", "encoder_dump", "build_encoder.sh")])
     for case in CASES + AUX_ONLY:
         if len(sys.argv) < 2 or case[0] in sys.argv[1:]:
             make_case(*case)
+    for case in TF_CASES:
+        if len(sys.argv) < 2 or case[0] in sys.argv[1:]:
+            make_tf_case(*case)

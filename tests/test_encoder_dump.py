@@ -234,3 +234,95 @@ def test_gpu_reproduces_the_encoders_picture_statistics_and_dg_metrics(name):
             m = U.abi.SvtMeDgMetrics()
             assert ses.lib.svtme_dg_detector_hme(ses.h, src, ref, res, C.byref(m)) == 0, ses.lib.svtme_last_error()
             assert (int(m.tot_dist), int(m.tot_cplx), int(m.tot_active), int(m.sum_in_vectors)) == (dist, cplx, active, inv), (src, ref)
+
+
+# ---------------------------------------------------------------- temporal-filter ME calls of the real encoder
+TF_CASES = [c[0] for c in M.TF_CASES if os.path.exists(os.path.join(GOLD, "encdump_%s.npz" % c[0]))]
+
+
+def load_tf(name):
+    z = np.load(os.path.join(GOLD, "encdump_%s.npz" % name))
+    w, h, n, preset = (int(v) for v in z["meta"])
+    pairs = []
+    for c, f in z["pairs"].tolist():
+        hdr = E.TfDumpHeader.from_buffer_copy(z["hdr_%d_%d" % (c, f)].tobytes())
+        pairs.append((c, f, hdr, {k: z["%s_%d_%d" % (k, c, f)] for k in ("p_sb_best_sad", "p_sb_best_mv", "hme_sc", "hme_sad")}))
+    return w, h, U.synth_sequence(w, h, n, seed=1), pairs
+
+
+def assert_tf_outputs(hdr, want, got, what):
+    """Slot (list 0, ref 0) of the deep arrays; a block that returned early after HME keeps stale tables in the encoder."""
+    n = hdr.b64_cols * hdr.b64_rows
+    early = want["hme_sad"] < hdr.params.tf_me_exit_th
+    g_sad = np.asarray(got["hme_sad"]).reshape(n, 2, 4)[:, 0, 0]
+    g_sc = np.asarray(got["hme_sc"]).reshape(n, 2, 4, 2)[:, 0, 0]
+    assert np.array_equal(want["hme_sad"], g_sad), (what, "hme_sad")
+    assert np.array_equal(want["hme_sc"], g_sc), (what, "hme_sc")
+    for k in ("p_sb_best_sad", "p_sb_best_mv"):
+        g = np.asarray(got[k]).reshape(n, 2, 4, 85)[:, 0, 0]
+        assert np.array_equal(want[k][~early], g[~early]), (what, k)
+
+
+def test_tf_fixtures_exist():
+    assert len(TF_CASES) == 2
+
+
+@pytest.mark.parametrize("name", TF_CASES)
+def test_tf_parameters_equal_the_encoders_me_context(name):
+    """svtme_derive_params_tf(what the encoder's pcs / scs held) + the per-call fields == the SvtMeParams rebuilt from the
+    MeContext the temporal filter handed to svt_aom_motion_estimation_b64."""
+    lib = U.product_lib()
+    w, h, seq, pairs = load_tf(name)
+    assert len(pairs) >= 8
+    for c, f, hdr, _ in pairs:
+        q = U.abi.SvtMeParams()
+        assert lib.svtme_derive_params_tf(C.byref(hdr.tin), C.byref(q)) == 0
+        q.picture_number, q.ref_picture_number[0][0] = c, f
+        assert E.struct_fields_equal(hdr.params, q, skip=TF_NOT_IN_ME_CONTEXT) == [], (name, c, f)
+
+
+# fields of SvtMeParams that live in the pcs / scs, not in MeContext, and only steer the candidate export that ME_MCTF skips
+# (the dump hook of the temporal filter rebuilds the struct from the MeContext alone and leaves them zero)
+TF_NOT_IN_ME_CONTEXT = ("enable_me_8x8", "enable_me_16x16", "max_number_of_pus_per_sb", "input_resolution_le_480p", "max_cand",
+                        "max_refs", "max_l0")
+
+
+def tf_params(hdr, c, f):
+    q = U.abi.SvtMeParams()
+    assert U.product_lib().svtme_derive_params_tf(C.byref(hdr.tin), C.byref(q)) == 0
+    q.picture_number, q.ref_picture_number[0][0] = c, f
+    return q
+
+
+@pytest.mark.parametrize("name", TF_CASES)
+def test_oracle_reproduces_the_encoders_tf_me_results(name):
+    w, h, seq, pairs = load_tf(name)
+    for which in ["orc"] + (["ref"] if U.ref_lib() is not None else []):
+        pyr = {}
+        for c, f, hdr, want in pairs:
+            for pic in (c, f):
+                if pic not in pyr:
+                    pyr[pic] = U.CpuPyramid(which, seq[pic], pic)
+            got = U.cpu_me_picture(which, tf_params(hdr, c, f), pyr[c], {(0, 0): pyr[f]})
+            assert_tf_outputs(hdr, want, got, (which, c, f))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", TF_CASES)
+def test_gpu_reproduces_the_encoders_tf_me_results(name):
+    import importlib
+    me = importlib.import_module(U.PKG + ".me")
+    w, h, seq, pairs = load_tf(name)
+    with me.MeSession(0, w, h, capacity=len(seq)) as ses:
+        host = np.ascontiguousarray(seq)
+        ses.put_pictures(list(range(len(seq))), [host[i].ctypes.data for i in range(len(seq))], w)
+        specs = []
+        for c, f, hdr, _ in pairs:
+            q = U.abi.SvtMeParams()
+            assert ses.lib.svtme_derive_params_tf(C.byref(hdr.tin), C.byref(q)) == 0
+            q.picture_number, q.ref_picture_number[0][0] = c, f
+            specs.append((q, c, {(0, 0): f}))
+        jobs, outs = ses.make_jobs(specs, deep=True)
+        ses.run_jobs(jobs)
+    for (c, f, hdr, want), got in zip(pairs, outs):
+        assert_tf_outputs(hdr, want, got, ("gpu", c, f))

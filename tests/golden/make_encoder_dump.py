@@ -27,7 +27,15 @@ CASES = [
     ("360p_p8", 640, 360, 16, 8, True, []),
     ("360p_p4", 640, 360, 10, 4, False, []),
     ("1080p_p8", 1920, 1080, 9, 8, False, []),
+    # 10-bit source (16-bit samples = the 8-bit pattern << 2 plus two seeded LSBs, see samples16): ME reads the 8 MSBs
+    ("360p_p6_10bit", 640, 360, 9, 6, False, ["--input-depth", "10"]),
 ]
+
+
+def samples16(seq):
+    """The 10-bit source of a '--input-depth 10' case: what bench.py's 10-bit workloads and the GPU tests upload."""
+    rng = np.random.default_rng(3)
+    return (seq.astype(np.uint16) << 2) | rng.integers(0, 4, size=seq.shape, dtype=np.uint16)
 # aux-only case (no ME dump kept): long enough for picture decision to evaluate a 32-picture mini-GOP, which is when the
 # dynamic-GOP detector compares pictures (eval_sub_mini_gop -> early_hme, pd_process.c:591-720)
 AUX_ONLY = [("dg_360p_p8", 640, 360, 67, 8, False, [])]
@@ -36,12 +44,13 @@ TF_CASES = [("tf_360p_p8", 640, 360, 17, 8), ("tf_360p_p4", 640, 360, 9, 4)]
 ENC_ARGS = ["--fps", "30", "--lp", "1", "--enable-tf", "0", "--scm", "0"]
 
 
-def write_yuv(path, seq):
+def write_yuv(path, seq, bits=8):
     n, h, w = seq.shape
-    chroma = np.full((h // 2) * (w // 2) * 2, 128, np.uint8).tobytes()
+    chroma = (np.full((h // 2) * (w // 2) * 2, 128, np.uint8) if bits == 8 else np.full((h // 2) * (w // 2) * 2, 512, "<u2")).tobytes()
+    src = seq if bits == 8 else samples16(seq).astype("<u2")
     with open(path, "wb") as f:
         for i in range(n):
-            f.write(seq[i].tobytes())
+            f.write(src[i].tobytes())
             f.write(chroma)
 
 
@@ -55,7 +64,7 @@ def make_case(name, w, h, n, preset, deep, extra):
     with tempfile.TemporaryDirectory() as tmp:
         yuv, ddir = os.path.join(tmp, "in.yuv"), os.path.join(tmp, "dump")
         os.mkdir(ddir)
-        write_yuv(yuv, seq)
+        write_yuv(yuv, seq, 10 if "--input-depth" in extra else 8)
         env = {"SVTME_DUMP_DIR": ddir}
         if deep:
             env["SVTME_DUMP_DEEP"] = "1"

@@ -116,8 +116,12 @@ def test_gpu_reproduces_the_encoders_me_results(name):
     me = importlib.import_module(U.PKG + ".me")
     w, h, seq, pics = load_case(name)
     with me.MeSession(0, w, h, capacity=len(seq)) as ses:
-        host = np.ascontiguousarray(seq)
-        ses.put_pictures(list(range(len(seq))), [host[i].ctypes.data for i in range(len(seq))], w)
+        if name.endswith("10bit"):  # the 16-bit samples the encoder was fed: the boundary keeps the 8 MSBs, as the encoder's ME did
+            host = np.ascontiguousarray(M.samples16(seq))
+            ses.put_pictures(list(range(len(seq))), [host[i].ctypes.data for i in range(len(seq))], w, bits=10)
+        else:
+            host = np.ascontiguousarray(seq)
+            ses.put_pictures(list(range(len(seq))), [host[i].ctypes.data for i in range(len(seq))], w)
         specs = []
         for pic, hdr, _ in pics:
             q = ses.derive_params(hdr.din)

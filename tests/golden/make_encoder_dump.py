@@ -29,6 +29,9 @@ CASES = [
     ("1080p_p8", 1920, 1080, 9, 8, False, []),
     # 10-bit source (16-bit samples = the 8-bit pattern << 2 plus two seeded LSBs, see samples16): ME reads the 8 MSBs
     ("360p_p6_10bit", 640, 360, 9, 6, False, ["--input-depth", "10"]),
+    ("360p_p2", 640, 360, 6, 2, False, []),                         # slow preset: large areas, global-motion detection on
+    ("360p_p11", 640, 360, 10, 11, False, []),                      # fast preset
+    ("360p_p9_ld", 640, 360, 9, 9, False, ["--pred-struct", "1"]),  # low delay: list 0 only ... as picture decision posts it
 ]
 
 

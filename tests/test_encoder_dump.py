@@ -54,6 +54,31 @@ def assert_outputs_equal(hdr, want, got, what):
         if k in SLOT_KEYS:
             w = w.reshape(n_b64, 2, 4, -1)[:, used]
             g = g.reshape(n_b64, 2, 4, -1)[:, used]
+        if k == "me_candidate_array":  # entries beyond total_me_candidate_index are leftovers of earlier pictures in the encoder
+            tot = np.asarray(want["total_me_candidate_index"]).reshape(n_b64, hdr.n_pu)
+            live = np.arange(hdr.max_cand)[None, None, :] < tot[:, :, None]
+            w = np.asarray(w).reshape(n_b64, hdr.n_pu, hdr.max_cand)[live]
+            g = np.asarray(g).reshape(n_b64, hdr.n_pu, hdr.max_cand)[live]
+        if k == "me_mv_array":
+            # [pu][max_refs]: the encoder writes a slot only where a candidate of the PU may use it (construct_me_candidate_array,
+            # motion_estimation.c:2658-2695: a reference pruned for the PU is skipped) and recycles the buffers between
+            # pictures, so the other slots hold whatever an earlier picture left; only referenced slots are results
+            cand = np.asarray(want["me_candidate_array"]).reshape(n_b64, hdr.n_pu, hdr.max_cand)
+            tot = np.asarray(want["total_me_candidate_index"]).reshape(n_b64, hdr.n_pu)
+            live = np.arange(hdr.max_cand)[None, None, :] < tot[:, :, None]
+            mask = np.zeros((n_b64, hdr.n_pu, hdr.max_refs), dtype=bool)
+            d, i0, i1, l0, l1 = cand & 3, (cand >> 2) & 3, (cand >> 4) & 3, (cand >> 6) & 1, (cand >> 7) & 1
+            bi, pi = np.meshgrid(np.arange(n_b64), np.arange(hdr.n_pu), indexing="ij")
+            for c in range(hdr.max_cand):
+                for use, lst, idx in (((d[:, :, c] == 0) | (d[:, :, c] == 2), l0[:, :, c], i0[:, :, c]),
+                                      ((d[:, :, c] == 1) | (d[:, :, c] == 2), l1[:, :, c], i1[:, :, c])):
+                    sel = live[:, :, c] & use
+                    slot = np.where(lst == 1, hdr.max_l0, 0) + idx
+                    ok = sel & (slot < hdr.max_refs)
+                    mask[bi[ok], pi[ok], slot[ok]] = True
+            assert mask.any()
+            w = np.asarray(w).reshape(n_b64, hdr.n_pu, hdr.max_refs)[mask]
+            g = np.asarray(g).reshape(n_b64, hdr.n_pu, hdr.max_refs)[mask]
         assert np.array_equal(np.asarray(w).reshape(-1), np.asarray(g).reshape(-1)), (what, int(hdr.picture_number), k)
 
 
@@ -63,7 +88,7 @@ def test_derived_parameters_equal_the_encoders_me_context(name):
     the SvtMeParams rebuilt from the MeContext the encoder handed to svt_aom_motion_estimation_b64."""
     lib = U.product_lib()
     w, h, seq, pics = load_case(name)
-    assert len(pics) >= 8
+    assert len(pics) >= 5
     for pic, hdr, _ in pics:
         q = U.abi.SvtMeParams()
         assert lib.svtme_derive_params(C.byref(hdr.din), C.byref(q)) == 0

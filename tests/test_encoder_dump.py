@@ -159,8 +159,9 @@ def test_gpu_reproduces_the_encoders_me_results(name):
 
 @pytest.mark.gpu
 @pytest.mark.skipif(not os.path.exists(M.APP), reason="oracle/_ref/SvtAv1EncApp_dump not built (needs /root/reference once)")
-@pytest.mark.parametrize("name,w,h,n,preset", [("360p_p8", 640, 360, 16, 8), ("360p_p4", 640, 360, 10, 4)])
-def test_bitstream_is_identical_with_gpu_me_results(name, w, h, n, preset, tmp_path):
+@pytest.mark.parametrize("name,w,h,n,preset,extra", [("360p_p8", 640, 360, 16, 8, []), ("360p_p4", 640, 360, 10, 4, []),
+                                                     ("360p_p9_ld", 640, 360, 9, 9, ["--pred-struct", "1"])])
+def test_bitstream_is_identical_with_gpu_me_results(name, w, h, n, preset, extra, tmp_path):
     """(e) north_star "identical bitstream": the reference encoder is run (1) untouched, (2) with every b64's ME
     results REPLACED by the GPU's (SVTME_REPLAY_DIR), (3) with one GPU motion vector falsified. (1) and (2) must be
     the same file; (3) must not (the replacement really reaches mode decision)."""
@@ -172,7 +173,7 @@ def test_bitstream_is_identical_with_gpu_me_results(name, w, h, n, preset, tmp_p
     ddir, gdir, xdir = tmp_path / "dump", tmp_path / "gpu", tmp_path / "bad"
     for d in (ddir, gdir, xdir):
         d.mkdir()
-    M.encode(yuv, w, h, n, preset, [], str(tmp_path / "ref.ivf"), {"SVTME_DUMP_DIR": str(ddir)})
+    M.encode(yuv, w, h, n, preset, extra, str(tmp_path / "ref.ivf"), {"SVTME_DUMP_DIR": str(ddir)})
     pics = sorted(int(f[3:9]) for f in os.listdir(ddir) if f.startswith("me_"))
     with me.MeSession(0, w, h, capacity=n) as ses:
         host = np.ascontiguousarray(seq)
@@ -191,8 +192,8 @@ def test_bitstream_is_identical_with_gpu_me_results(name, w, h, n, preset, tmp_p
         if pic == pics[len(pics) // 2]:
             bad["me_mv_array"].reshape(-1)[::7] ^= 0x00040008  # falsify motion vectors of one picture
         E.write_dump(str(xdir / ("me_%06d.bin" % pic)), hdr, bad)
-    M.encode(yuv, w, h, n, preset, [], str(tmp_path / "gpu.ivf"), {"SVTME_REPLAY_DIR": str(gdir)})
-    M.encode(yuv, w, h, n, preset, [], str(tmp_path / "bad.ivf"), {"SVTME_REPLAY_DIR": str(xdir)})
+    M.encode(yuv, w, h, n, preset, extra, str(tmp_path / "gpu.ivf"), {"SVTME_REPLAY_DIR": str(gdir)})
+    M.encode(yuv, w, h, n, preset, extra, str(tmp_path / "bad.ivf"), {"SVTME_REPLAY_DIR": str(xdir)})
     ref, gpu, bad = (open(str(tmp_path / f), "rb").read() for f in ("ref.ivf", "gpu.ivf", "bad.ivf"))
     assert len(ref) > 1000
     assert ref == gpu, "bitstream written with the GPU's ME results differs from the reference encoder's"

@@ -315,7 +315,10 @@ __device__ __forceinline__ int team_plan_prehme(StageState *s, const DevJob &J, 
             sa_h = ((org_y + oy) < -pad_h) ? sa_h - (-pad_h - (org_y + oy)) : sa_h;
             oy = ((org_y + oy) > H - 1) ? oy - ((org_y + oy) - (H - 1)) : oy;
             sa_h = (org_y + oy + sa_h > H) ? max(1, sa_h - ((org_y + oy + sa_h) - H)) : sa_h;
-            add_job(s, nj, pl, pl.org_x + org_x + ox, pl.org_y + org_y + oy, sa_w, sa_h, p.prehme_skip_search_line, li, ri, sr, 0, ox, oy);
+            // svt_sad_loop_kernel skips the even search rows only for a block that is 16 wide (compute_sad_c.c:74-79): the
+            // 1/16 block of an incomplete b64 at the right picture edge is narrower and searches every row
+            const int skip = (p.prehme_skip_search_line && (s->b64_w >> 2) == 16) ? 1 : 0;
+            add_job(s, nj, pl, pl.org_x + org_x + ox, pl.org_y + org_y + oy, sa_w, sa_h, skip, li, ri, sr, 0, ox, oy);
         }
     }
     return total;

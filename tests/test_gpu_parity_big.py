@@ -96,7 +96,7 @@ def test_8k_preset6_pictures_of_the_bench_workload():
 
 
 @pytest.mark.parametrize("size", [(2200, 72), (72, 2200), (4160, 136)], ids=lambda s: "%dx%d" % s)
-@pytest.mark.parametrize("preset", [8, 4, 1])
+@pytest.mark.parametrize("preset", [8, 4, 1, 11])  # 11: pre-HME skips even search rows, but not for the narrow last column
 def test_long_line_pictures_strip_segments(size, preset):
     """One or two lines of 35 / 65 b64 (ragged last segment: 35 = 32 + 3, 65 = 2 x 32 + 1; last column 24 wide, last row 8
     high): pre-HME and HME level 0 in strip mode with bx0 > 0 / by0 > 0, several references, motion into the pads."""
